@@ -1,0 +1,243 @@
+"""ctypes bindings to the CPU oracle (oracle/liborb_oracle.so) — TEST INFRASTRUCTURE ONLY.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this module.
+The product package (orb_slam_cuda_b200/) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "liborb_oracle.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+_u8p = C.POINTER(C.c_uint8)
+_f32p = C.POINTER(C.c_float)
+_i32p = C.POINTER(C.c_int)
+
+
+def build(force: bool = False) -> str:
+    srcs = [os.path.join(_HERE, f) for f in ("orb_oracle.cpp", "orb_oracle_capi.cpp", "orb_oracle.hpp")]
+    if force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        L = _lib
+        L.orc_fast_atan2.restype = C.c_float
+        L.orc_fast_atan2.argtypes = [C.c_float, C.c_float]
+        L.orc_ic_angle.restype = C.c_float
+        L.orc_extractor_create.restype = C.c_void_p
+        L.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
+        L.orc_extractor_destroy.argtypes = [C.c_void_p]
+        L.orc_bench_extract.restype = C.c_double
+        L.orc_bench_bruteforce.restype = C.c_double
+    return _lib
+
+
+def _p(a, t=C.c_void_p):
+    return a.ctypes.data_as(t)
+
+
+def cv_round(v: float) -> int:
+    lib().orc_cv_round_f.argtypes = [C.c_float]
+    return lib().orc_cv_round_f(C.c_float(v))
+
+
+def fast_atan2(y, x) -> np.ndarray:
+    y = np.ascontiguousarray(y, dtype=np.float32)
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    out = np.empty_like(y)
+    lib().orc_fast_atan2_array(_p(y), _p(x), _p(out), C.c_int(y.size))
+    return out
+
+
+def sincosf(ang) -> tuple[np.ndarray, np.ndarray]:
+    ang = np.ascontiguousarray(ang, dtype=np.float32)
+    c, s = np.empty_like(ang), np.empty_like(ang)
+    lib().orc_sincosf(_p(ang), _p(c), _p(s), C.c_int(ang.size))
+    return c, s
+
+
+def resize_linear(src: np.ndarray, dw: int, dh: int) -> np.ndarray:
+    src = np.ascontiguousarray(src, dtype=np.uint8)
+    dst = np.empty((dh, dw), dtype=np.uint8)
+    lib().orc_resize_linear_8u(_p(src), src.shape[1], src.shape[0], src.strides[0], _p(dst), dw, dh, dw)
+    return dst
+
+
+def border_reflect101(src: np.ndarray, pad: int) -> np.ndarray:
+    src = np.ascontiguousarray(src, dtype=np.uint8)
+    h, w = src.shape
+    dst = np.empty((h + 2 * pad, w + 2 * pad), dtype=np.uint8)
+    lib().orc_border_reflect101(_p(src), w, h, src.strides[0], _p(dst), w + 2 * pad, pad)
+    return dst
+
+
+def fast9(img: np.ndarray, threshold: int, nms: bool = True) -> np.ndarray:
+    assert img.dtype == np.uint8 and img.strides[1] == 1
+    h, w = img.shape
+    out = np.empty(max(1, h * w), dtype=KP_DTYPE)
+    n = lib().orc_fast9(_p(img), w, h, img.strides[0], threshold, int(nms), _p(out), out.size)
+    return out[:n].copy()
+
+
+def gaussian7(img: np.ndarray) -> np.ndarray:
+    assert img.dtype == np.uint8 and img.strides[1] == 1
+    h, w = img.shape
+    dst = np.empty((h, w), dtype=np.uint8)
+    lib().orc_gaussian7(_p(img), w, h, img.strides[0], _p(dst), w)
+    return dst
+
+
+def ic_angle(plane: np.ndarray, x: int, y: int) -> float:
+    assert plane.dtype == np.uint8 and plane.strides[1] == 1
+    return float(lib().orc_ic_angle(_p(plane), C.c_int(plane.strides[0]), C.c_int(x), C.c_int(y)))
+
+
+def descriptor(plane: np.ndarray, x: int, y: int, angle: float) -> np.ndarray:
+    assert plane.dtype == np.uint8 and plane.strides[1] == 1
+    d = np.empty(32, dtype=np.uint8)
+    lib().orc_descriptor(_p(plane), C.c_int(plane.strides[0]), C.c_int(x), C.c_int(y), C.c_float(angle), _p(d))
+    return d
+
+
+def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    b = np.ascontiguousarray(b, dtype=np.uint8)
+    return int(lib().orc_descriptor_distance(_p(a), _p(b)))
+
+
+def distribute(keys: np.ndarray, minX: int, maxX: int, minY: int, maxY: int, N: int) -> np.ndarray:
+    keys = np.ascontiguousarray(keys, dtype=KP_DTYPE)
+    out = np.empty(max(keys.size, 1), dtype=KP_DTYPE)
+    n = lib().orc_distribute(_p(keys), keys.size, minX, maxX, minY, maxY, N, _p(out), out.size)
+    return out[:n].copy()
+
+
+class Extractor:
+    """CPU oracle of ORBextractor (reference src/ORBextractor.cc, CPU path)."""
+
+    def __init__(self, nfeatures=2000, scale_factor=1.2, nlevels=8, ini_th=20, min_th=7):
+        self.nlevels = nlevels
+        self.nfeatures = nfeatures
+        self._h = C.c_void_p(lib().orc_extractor_create(nfeatures, C.c_float(scale_factor), nlevels, ini_th, min_th))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_extractor_destroy(self._h)
+            self._h = None
+
+    def tables(self):
+        n = self.nlevels
+        sf, inv, s2, inv2 = (np.empty(n, np.float32) for _ in range(4))
+        quota, umax = np.empty(n, np.int32), np.empty(16, np.int32)
+        lib().orc_extractor_tables(self._h, _p(sf), _p(inv), _p(s2), _p(inv2), _p(quota), _p(umax))
+        return dict(scale=sf, inv_scale=inv, sigma2=s2, inv_sigma2=inv2, quota=quota, umax=umax)
+
+    def extract(self, img: np.ndarray):
+        assert img.dtype == np.uint8 and img.ndim == 2 and img.strides[1] == 1
+        h, w = img.shape
+        cap = self.nfeatures + 64 * self.nlevels + 64
+        kps = np.empty(cap, dtype=KP_DTYPE)
+        desc = np.empty((cap, 32), dtype=np.uint8)
+        n = lib().orc_extract(self._h, _p(img), w, h, C.c_int(img.strides[0]), _p(kps), _p(desc), cap)
+        assert n <= cap
+        return kps[:n].copy(), desc[:n].copy()
+
+    def level_size(self, l):
+        w, h = C.c_int(), C.c_int()
+        lib().orc_level_size(self._h, l, C.byref(w), C.byref(h))
+        return w.value, h.value
+
+    def level_padded(self, l) -> np.ndarray:
+        w, h = self.level_size(l)
+        out = np.empty((h + 38, w + 38), dtype=np.uint8)
+        lib().orc_level_padded(self._h, l, _p(out))
+        return out
+
+    def level_blurred(self, l):
+        w, h = self.level_size(l)
+        out = np.empty((h, w), dtype=np.uint8)
+        ok = lib().orc_level_blurred(self._h, l, _p(out))
+        return out if ok else None
+
+    def _kps(self, fn, l):
+        n = fn(self._h, l, None, 0)
+        out = np.empty(max(n, 1), dtype=KP_DTYPE)
+        fn(self._h, l, _p(out), n)
+        return out[:n].copy()
+
+    def level_candidates(self, l):
+        return self._kps(lib().orc_level_candidates, l)
+
+    def level_keypoints(self, l):
+        return self._kps(lib().orc_level_keypoints, l)
+
+
+def search_for_initialization(k1, d1, k2, d2, bounds, prev_xy, window=100, nnratio=0.9, check_ori=True):
+    k1 = np.ascontiguousarray(k1, dtype=KP_DTYPE)
+    k2 = np.ascontiguousarray(k2, dtype=KP_DTYPE)
+    d1 = np.ascontiguousarray(d1, dtype=np.uint8)
+    d2 = np.ascontiguousarray(d2, dtype=np.uint8)
+    prev = np.ascontiguousarray(prev_xy, dtype=np.float32).copy()
+    m12 = np.empty(k1.size, dtype=np.int32)
+    minX, maxX, minY, maxY = (C.c_float(v) for v in bounds)
+    n = lib().orc_search_for_initialization(_p(k1), k1.size, _p(d1), _p(k2), k2.size, _p(d2), minX, maxX, minY, maxY,
+                                            _p(prev), _p(m12), C.c_int(window), C.c_float(nnratio), int(check_ori))
+    return n, m12, prev
+
+
+def match_bruteforce(q, d, th=50, ratio=0.6):
+    q = np.ascontiguousarray(q, dtype=np.uint8)
+    d = np.ascontiguousarray(d, dtype=np.uint8)
+    nq, nd = q.shape[0], d.shape[0]
+    idx, d1, d2, m = (np.empty(nq, np.int32) for _ in range(4))
+    lib().orc_match_bruteforce(_p(q), nq, _p(d), nd, th, C.c_float(ratio), _p(idx), _p(d1), _p(d2), _p(m))
+    return idx, d1, d2, m
+
+
+def stereo_matches(exL: Extractor, exR: Extractor, kL, dL, kR, dR, bf: float, fx: float):
+    kL = np.ascontiguousarray(kL, dtype=KP_DTYPE)
+    kR = np.ascontiguousarray(kR, dtype=KP_DTYPE)
+    dL = np.ascontiguousarray(dL, dtype=np.uint8)
+    dR = np.ascontiguousarray(dR, dtype=np.uint8)
+    u = np.empty(kL.size, np.float32)
+    z = np.empty(kL.size, np.float32)
+    lib().orc_stereo_matches(exL._h, exR._h, _p(kL), kL.size, _p(dL), _p(kR), kR.size, _p(dR), C.c_float(bf),
+                             C.c_float(fx), _p(u), _p(z))
+    return u, z
+
+
+def bench_extract(frames: np.ndarray, nfeatures, scale_factor, nlevels, ini_th, min_th, threads: int):
+    frames = np.ascontiguousarray(frames, dtype=np.uint8)
+    n, h, w = frames.shape
+    nk = C.c_longlong(0)
+    lib().orc_bench_extract.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
+                                        C.c_int, C.c_int, C.POINTER(C.c_longlong)]
+    secs = lib().orc_bench_extract(_p(frames), n, w, h, nfeatures, C.c_float(scale_factor), nlevels, ini_th, min_th,
+                                   threads, C.byref(nk))
+    return secs, nk.value
+
+
+def bench_bruteforce(q, d, threads: int):
+    q = np.ascontiguousarray(q, dtype=np.uint8)
+    d = np.ascontiguousarray(d, dtype=np.uint8)
+    nq, nd = q.shape[0], d.shape[0]
+    idx, d1, d2, m = (np.empty(nq, np.int32) for _ in range(4))
+    secs = lib().orc_bench_bruteforce(_p(q), nq, _p(d), nd, threads, _p(idx), _p(d1), _p(d2), _p(m))
+    return secs, (idx, d1, d2, m)

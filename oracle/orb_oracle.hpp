@@ -1,0 +1,97 @@
+// oracle/orb_oracle.hpp — TEST INFRASTRUCTURE ONLY (CPU oracle for the ORB front end).
+//
+// This is a plain C++17 restatement, with no OpenCV dependency, of the CPU path ("path B") of the
+// reference's ORBextractor / ORBmatcher / Frame::ComputeStereoMatches.  Only tests/, __graft_entry__.smoke()
+// and bench.py's cpu_baseline / --impl reference legs may build, load or call it.  The product
+// (orb_slam_cuda_b200/, include/) never links or calls anything in this directory.
+//
+// Parity pinning: the reference ships no tests or golden vectors and its sources do
+// not compile here (VisionWorks/OpenVX/OpenCV C++ headers absent), so the control flow below follows the
+// reference line ranges cited at each function, and the five OpenCV primitives it calls (resize,
+// copyMakeBorder, FAST, GaussianBlur, fastAtan2) are pinned bit-exactly against cv2 4.13 by
+// tests/test_oracle_cv2.py and the committed fixtures under tests/golden/.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+namespace orc {
+
+// Same field order and size (28 B) as cv::KeyPoint: pt.x, pt.y, size, angle, response, octave, class_id.
+struct KeyPoint {
+    float x, y, size, angle, response;
+    int octave, class_id;
+};
+
+struct Image {  // owning 8-bit plane
+    int w = 0, h = 0;
+    std::vector<uint8_t> px;
+    Image() {}
+    Image(int w_, int h_) : w(w_), h(h_), px((size_t)w_ * h_) {}
+    uint8_t* row(int y) { return px.data() + (size_t)y * w; }
+    const uint8_t* row(int y) const { return px.data() + (size_t)y * w; }
+};
+
+// ---- OpenCV primitive models -------------------------------------------------------------------
+int cv_round(float v);
+int cv_round(double v);
+void resize_linear_8u(const uint8_t* src, int sw, int sh, size_t sstep, uint8_t* dst, int dw, int dh, size_t dstep);
+int reflect101(int p, int n);
+void border_reflect101(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep, int pad);
+void fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, bool nms, std::vector<KeyPoint>& out);
+void gaussian7x7_s2(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst, size_t dstep);
+float fast_atan2(float y, float x);
+
+// ---- ORBextractor (src/ORBextractor.cc, CPU path) -------------------------------------------------
+constexpr int PATCH_SIZE = 31, HALF_PATCH_SIZE = 15, EDGE_THRESHOLD = 19;
+
+std::vector<KeyPoint> distribute_octtree(const std::vector<KeyPoint>& keys, int minX, int maxX, int minY, int maxY,
+                                         int N);
+
+struct Extractor {
+    int nfeatures, nlevels, iniThFAST, minThFAST;
+    double scaleFactor;
+    std::vector<float> mvScaleFactor, mvInvScaleFactor, mvLevelSigma2, mvInvLevelSigma2;
+    std::vector<int> mnFeaturesPerLevel, umax;
+    // Per-frame state (kept for stage-by-stage parity tests)
+    std::vector<Image> padded;               // (w+38) x (h+38) planes; mvImagePyramid[l] = centre ROI
+    std::vector<int> lw, lh;                 // unpadded level sizes
+    std::vector<std::vector<KeyPoint>> candidates;  // vToDistributeKeys per level
+    std::vector<std::vector<KeyPoint>> levelKeys;   // after quadtree + border offset + angle (level coords)
+    std::vector<Image> blurred;              // unpadded blurred planes (empty if level had no keypoints)
+
+    Extractor(int nfeatures, float scaleFactor, int nlevels, int iniThFAST, int minThFAST);
+    void compute_pyramid(const uint8_t* img, int w, int h, size_t step);
+    void compute_keypoints();
+    // Full operator(): returns keypoints (level-0 coords) and N x 32 descriptors.
+    void extract(const uint8_t* img, int w, int h, size_t step, std::vector<KeyPoint>& kps, std::vector<uint8_t>& desc);
+    const uint8_t* level_ptr(int l) const { return padded[l].row(EDGE_THRESHOLD) + EDGE_THRESHOLD; }
+    size_t level_step(int l) const { return (size_t)padded[l].w; }
+};
+
+float ic_angle(const uint8_t* center, size_t step, const std::vector<int>& umax);
+void orb_descriptor(float angle_deg, const uint8_t* center, size_t step, uint8_t* desc);
+
+// ---- ORBmatcher / Frame pieces -------------------------------------------------------------------
+int descriptor_distance(const uint8_t* a, const uint8_t* b);
+
+struct GridFrame {  // the parts of Frame that SearchForInitialization touches
+    static constexpr int COLS = 64, ROWS = 48;
+    float minX, minY, maxX, maxY, invW, invH;
+    const KeyPoint* keys;
+    int n;
+    std::vector<size_t> grid[COLS][ROWS];
+    GridFrame(const KeyPoint* keys, int n, float minX, float maxX, float minY, float maxY);
+    std::vector<size_t> features_in_area(float x, float y, float r, int minLevel, int maxLevel) const;
+};
+
+int search_for_initialization(const GridFrame& F1, const uint8_t* desc1, const GridFrame& F2, const uint8_t* desc2,
+                              float* prevMatchedXY, int* matches12, int windowSize, float nnratio, bool checkOri);
+
+void match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1,
+                      int* d2, int* match);
+
+void stereo_matches(const Extractor& L, const Extractor& R, const KeyPoint* kL, int nL, const uint8_t* dL,
+                    const KeyPoint* kR, int nR, const uint8_t* dR, float bf, float fx, float* uRight, float* depth);
+
+}  // namespace orc
