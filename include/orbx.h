@@ -1,0 +1,146 @@
+/* include/orbx.h — C ABI of the B200-native ORB front end (liborbx.so).
+ *
+ * This is the drop-in boundary.  The reference has no FFI layer for this path: its boundary is
+ * the C++ class surface of ORB_SLAM2::ORBextractor / ORBmatcher / Frame::ComputeStereoMatches.  The C++ classes in
+ * include/ORBextractor.h and include/ORBmatcher.h keep that surface and forward to the entry points below; a
+ * binding from any other host language (ctypes, cgo, JNI …) binds the same symbols.
+ *
+ * Conventions
+ *   - every function returns an int status: 0 = ORBX_OK, negative = error; orbx_last_error() gives the
+ *     thread-local message of the last failing call on this thread;
+ *   - plain pointers and sizes only; "host" entry points take host memory and do their own H2D/D2H,
+ *     "_device" entry points take device pointers + a cudaStream_t (passed as void*) and are asynchronous;
+ *   - there is NO CPU fallback: without a CUDA device every compute entry point fails with ORBX_E_CUDA;
+ *   - a handle is used by one thread at a time; different handles are independent (own stream + scratch),
+ *     like the two extractor objects of the reference's stereo path (src/Frame.cc:77-80).
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ORBX_OK 0
+#define ORBX_E_INVALID (-1)  /* bad argument / unsupported geometry */
+#define ORBX_E_CUDA (-2)     /* CUDA runtime or driver failure (includes "no device") */
+#define ORBX_E_OOM (-3)      /* allocation failure */
+#define ORBX_E_OVERFLOW (-4) /* a fixed-capacity device buffer overflowed (cell slots / candidate lists / output cap) */
+
+#define ORBX_MAX_LEVELS 16
+
+/* Bit-compatible with cv::KeyPoint (28 bytes): pt.x, pt.y, size, angle, response, octave, class_id. */
+typedef struct orbx_keypoint {
+    float x, y, size, angle, response;
+    int octave, class_id;
+} orbx_keypoint;
+
+/* Constructor arguments of ORBextractor (reference include/ORBextractor.h:82-83, src/ORBextractor.cc:496-500).
+ * width/height are hints and may be 0 (size taken from the first frame); max_batch = frames per launch the
+ * scratch is sized for (grown on demand); device = CUDA ordinal, -1 = current device. */
+typedef struct orbx_params {
+    int nfeatures;
+    float scale_factor;
+    int nlevels;
+    int ini_th_fast;
+    int min_th_fast;
+    int width, height;
+    int max_batch;
+    int device;
+} orbx_params;
+
+typedef struct orbx_extractor orbx_extractor;
+
+const char* orbx_last_error(void);
+int orbx_version(void);
+/* number of kernels this library has launched in this process (bench.py's gpu_launches) */
+long long orbx_kernel_launches(void);
+
+/* ---- ORBextractor: ctor / dtor / accessors  (src/ORBextractor.cc:496-560, include/ORBextractor.h:94-114) ---- */
+int orbx_extractor_create(const orbx_params* p, orbx_extractor** out);
+void orbx_extractor_destroy(orbx_extractor* ex);
+/* each array has nlevels entries; any pointer may be NULL */
+int orbx_get_scale_tables(const orbx_extractor* ex, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                          int* features_per_level);
+int orbx_get_umax(const orbx_extractor* ex, int* umax16);
+/* the stream the handle launches on (cudaStream_t as void*) */
+void* orbx_extractor_stream(const orbx_extractor* ex);
+
+/* ---- ORBextractor::operator()  (src/ORBextractor.cc:1538-1548, 1701-1815, CPU path semantics) ----
+ * One 8-bit frame in host memory -> keypoints (level-major, level-0 coordinates) + n x 32 descriptor bytes.
+ * cap = capacity of kps/desc in keypoints; *n = number produced (<= cap, else ORBX_E_OVERFLOW).
+ * An empty image (img NULL or w,h <= 0) returns ORBX_OK with *n = 0, like the reference's silent return. */
+int orbx_extract(orbx_extractor* ex, const uint8_t* img, int w, int h, size_t stride, orbx_keypoint* kps, uint8_t* desc,
+                 int cap, int* n);
+
+/* Batched form: `batch` frames of identical size, frame f at frames + f*frame_stride, rows `stride` bytes apart.
+ * Outputs: kps[f*cap .. ], desc[(f*cap + i)*32 .. ], counts[f].  Host memory; copies are inside the call. */
+int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride,
+                       size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int cap, int* counts);
+
+/* Same with every buffer already resident in device memory; asynchronous on `stream` (NULL = the handle's own
+ * stream).  d_status (device int, may be NULL) receives 0 or ORBX_E_OVERFLOW. */
+int orbx_extract_batch_device(orbx_extractor* ex, const uint8_t* d_frames, int batch, int w, int h, size_t stride,
+                              size_t frame_stride, orbx_keypoint* d_kps, uint8_t* d_desc, int cap, int* d_counts,
+                              int* d_status, void* stream);
+
+/* ---- mvImagePyramid (include/ORBextractor.h:116; read by src/Frame.cc:472,562,574,579) ----
+ * Level `level` of frame `frame` of the last extract call, copied lazily to host memory owned by the handle.
+ * *interior points at pixel (0,0) of the level; it is the centre ROI of a (w+38) x (h+38) parent with row pitch
+ * *pitch, so rows -19..h+18 and columns -19..w+18 are readable (the EDGE_THRESHOLD reflect-101 border). */
+int orbx_pyramid_level_host(orbx_extractor* ex, int frame, int level, const uint8_t** interior, int* w, int* h,
+                            size_t* pitch);
+/* level sizes of the current geometry */
+int orbx_level_size(const orbx_extractor* ex, int level, int* w, int* h);
+
+/* ---- stage taps for parity tests (not used by the product path) ---- */
+/* blurred level (7x7 sigma 2), tightly packed w*h bytes into out */
+int orbx_debug_blurred_level(orbx_extractor* ex, int frame, int level, uint8_t* out);
+/* FAST candidates of one level in the reference's vToDistributeKeys order (x,y relative to minBorder) */
+int orbx_debug_candidates(orbx_extractor* ex, int frame, int level, orbx_keypoint* out, int cap, int* n);
+/* keypoints kept by the quadtree for one level, level coordinates, with angle */
+int orbx_debug_level_keypoints(orbx_extractor* ex, int frame, int level, orbx_keypoint* out, int cap, int* n);
+/* stand-alone DistributeOctTree (src/ORBextractor.cc:889-1120) on caller-supplied candidates */
+int orbx_debug_distribute(const orbx_keypoint* in, int n, int minX, int maxX, int minY, int maxY, int N,
+                          orbx_keypoint* out, int cap, int* nout);
+
+/* ---- ORBmatcher (src/ORBmatcher.cc) ---- */
+/* DescriptorDistance (:1647-1663) for n pairs a[i] vs b[i] on the device; host buffers */
+int orbx_hamming_distance(const uint8_t* a, const uint8_t* b, int n, int* dist);
+
+/* Brute-force best / second-best + acceptance test (inner loop of SearchByBoW, :187-232):
+ * idx[i] = first database row at minimal distance, d1/d2 = best / second-best distance (256 if none),
+ * match[i] = idx[i] if d1 <= th && (float)d1 < ratio*(float)d2 else -1.  Host buffers. */
+int orbx_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1,
+                          int* d2, int* match);
+int orbx_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d_d, int nd, int th, float ratio,
+                                 int* d_idx, int* d_d1, int* d_d2, int* d_match, void* stream);
+
+/* All-vs-all keyframe matching (relocalisation / loop-candidate workload; N x N DescriptorDistance tables as in
+ * src/MapPoint.cc:280-305 generalised to keyframe pairs).  Query keyframes [kq] and database keyframes [kd] hold
+ * n descriptors each (n*32 bytes per keyframe).  score[i*kd + j] = number of descriptors of query keyframe i whose
+ * best match in database keyframe j passes d1 <= th && d1 < ratio*d2.  Device buffers, asynchronous. */
+int orbx_match_allpairs_device(const uint8_t* d_q, int kq, const uint8_t* d_db, int kd, int n, int th, float ratio,
+                               int* d_score, void* stream);
+
+/* SearchForInitialization (:405-520): frame-1 keypoints of octave 0 search a +-window box around prev_xy[i] in
+ * frame 2 (Frame::GetFeaturesInArea over the 64x48 grid, src/Frame.cc:326-379), ratio test, one-to-one stealing,
+ * rotation histogram.  bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}.  prev_xy (2*n1 floats) is updated in place like
+ * vbPrevMatched; matches12[n1] = index into frame 2 or -1; *nmatches = return value.  Host buffers. */
+int orbx_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_t* desc1, const orbx_keypoint* k2,
+                                   int n2, const uint8_t* desc2, const float bounds[4], float* prev_xy, int* matches12,
+                                   int window, float nnratio, int check_ori, int* nmatches);
+
+/* Frame::ComputeStereoMatches (src/Frame.cc:465-639).  exL / exR hold the pyramids of the left / right frame of
+ * their last orbx_extract call.  u_right[nL], depth[nL] as mvuRight / mvDepth (-1 = no match).  Host buffers. */
+int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypoint* kL, int nL, const uint8_t* descL,
+                      const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float fx, float* u_right,
+                      float* depth);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */

@@ -1,0 +1,456 @@
+// csrc/k_quadtree.cu — ORBextractor::DistributeOctTree as a deterministic data-parallel quadtree
+// (reference src/ORBextractor.cc:831-887 DivideNode, :889-1120 DistributeOctTree incl. the fork's early exit at
+// :959-963).  One CTA per (frame, level).
+//
+// The reference walks a std::list serially.  The same result is obtained level-synchronously:
+//   sweep:  every expandable node of the list is split independently (a warp per node does a stable 4-way
+//           partition of the node's key segment into the other ping-pong buffer); a prefix sum of the size deltas in
+//           list order finds the node at which `lNodes.size() >= N` would have stopped the walk (:959-963); the
+//           new list is reverse(children pushed by the processed nodes) ++ survivors, which is what push_front /
+//           erase produce (:974-1020).
+//   final:  when size + 3*nToExpand > N (:1030) the expandable children of the last pass are ordered by
+//           (key count, creation order) descending — the reference sorts pair<int, node*> ascending and walks it
+//           from the back (:1041-1043); the pointer tie-break is allocator-dependent there and is defined as
+//           creation order here and in the oracle — and a prefix sum finds where size >= N breaks the walk (:1087).
+//   keep:   per final node the first key of maximal response (:1098-1117), emitted in list order.
+// tools/quadtree_proto.py checks this formulation against the CPU oracle on random inputs.
+//
+// Keys are 32-bit packed (resp << 24 | y << 12 | x); a node owns a contiguous segment of one of the two key
+// buffers, children own sub-segments of the other buffer, so no key is ever copied except when its node splits.
+#include "orbx_internal.h"
+
+namespace orbx {
+
+struct QNode {
+    uint16_t x0, y0, x1, y1;
+    uint32_t begin;  // bit 31: key buffer (0/1), bits 0..30: first key
+    uint32_t count;
+};
+
+struct QtShared {  // carved out of dynamic shared memory
+    QNode* list[2];
+    uint4* cc;      // child key counts per list position
+    int* sA;        // scan scratch (delta / pushed)
+    int* sB;        // scan scratch (survivors)
+    int* sC;        // processing order of the final phase
+    int* cellOff;   // exclusive prefix of the per-cell counts
+    int* misc;      // [0..15] scalars, [16..31] warp sums, [32..32+MAX_ROOTS] root counters
+};
+
+__device__ __forceinline__ int warp_incl_scan(int v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += n;
+    }
+    return v;
+}
+
+// In-place exclusive prefix sum of a[0..n) in shared memory by the whole block; returns the total.
+// Every thread owns a contiguous chunk, so the result is independent of the thread count.
+__device__ int block_exscan(int* a, int n, int* warpSums) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
+    const int chunk = (n + blockDim.x - 1) / blockDim.x;
+    const int b = min(tid * chunk, n), e = min(b + chunk, n);
+    int local = 0;
+    for (int i = b; i < e; ++i) local += a[i];
+    const int incl = warp_incl_scan(local, lane);
+    if (lane == 31) warpSums[wid] = incl;
+    __syncthreads();
+    int off = 0, total = 0;
+    for (int w = 0; w < nw; ++w) {
+        const int s = warpSums[w];
+        if (w < wid) off += s;
+        total += s;
+    }
+    int run = off + incl - local;
+    for (int i = b; i < e; ++i) {
+        const int v = a[i];
+        a[i] = run;
+        run += v;
+    }
+    __syncthreads();
+    return total;
+}
+
+__device__ __forceinline__ int child_of(uint32_t key, int mx, int my) {
+    return (key_x(key) < mx ? 0 : 1) + (key_y(key) < my ? 0 : 2);
+}
+
+// warp: count the keys of `nd` falling into each of the four children
+__device__ uint4 warp_count_children(const QNode& nd, const uint32_t* bufs, int candCap, int lane) {
+    const int mx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), my = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
+    const uint32_t* k = bufs + ((nd.begin >> 31) ? candCap : 0) + (nd.begin & 0x7FFFFFFFu);
+    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    for (uint32_t base = 0; base < nd.count; base += 32) {
+        const uint32_t i = base + lane;
+        const int c = (i < nd.count) ? child_of(k[i], mx, my) : 4;
+        c0 += __popc(__ballot_sync(0xffffffffu, c == 0));
+        c1 += __popc(__ballot_sync(0xffffffffu, c == 1));
+        c2 += __popc(__ballot_sync(0xffffffffu, c == 2));
+        c3 += __popc(__ballot_sync(0xffffffffu, c == 3));
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+// warp: write the child node records of `nd` (k-th non-empty child goes to list position firstPos - k) and move the
+// keys, stably, into the other buffer
+__device__ void warp_split(const QNode& nd, uint4 cc, uint32_t* bufs, int candCap, QNode* outList, int firstPos, int lane) {
+    const int mx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), my = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
+    const uint32_t srcBuf = nd.begin >> 31, first = nd.begin & 0x7FFFFFFFu;
+    const uint32_t* src = bufs + (srcBuf ? candCap : 0) + first;
+    uint32_t* dst = bufs + (srcBuf ? 0 : candCap) + first;
+    const uint32_t cnt[4] = {cc.x, cc.y, cc.z, cc.w};
+    uint32_t off[4];
+    off[0] = 0; off[1] = cc.x; off[2] = cc.x + cc.y; off[3] = cc.x + cc.y + cc.z;
+    if (lane == 0) {
+        int k = 0;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            if (cnt[c] == 0) continue;
+            QNode ch;
+            ch.x0 = (c & 1) ? (uint16_t)mx : nd.x0;
+            ch.x1 = (c & 1) ? nd.x1 : (uint16_t)mx;
+            ch.y0 = (c & 2) ? (uint16_t)my : nd.y0;
+            ch.y1 = (c & 2) ? nd.y1 : (uint16_t)my;
+            ch.begin = ((srcBuf ^ 1u) << 31) | (first + off[c]);
+            ch.count = cnt[c];
+            outList[firstPos - k] = ch;
+            ++k;
+        }
+    }
+    uint32_t run0 = off[0], run1 = off[1], run2 = off[2], run3 = off[3];
+    const uint32_t below = (1u << lane) - 1;
+    for (uint32_t base = 0; base < nd.count; base += 32) {
+        const uint32_t i = base + lane;
+        uint32_t key = 0;
+        int c = 4;
+        if (i < nd.count) {
+            key = src[i];
+            c = child_of(key, mx, my);
+        }
+        const uint32_t b0 = __ballot_sync(0xffffffffu, c == 0), b1 = __ballot_sync(0xffffffffu, c == 1);
+        const uint32_t b2 = __ballot_sync(0xffffffffu, c == 2), b3 = __ballot_sync(0xffffffffu, c == 3);
+        if (c == 0) dst[run0 + __popc(b0 & below)] = key;
+        else if (c == 1) dst[run1 + __popc(b1 & below)] = key;
+        else if (c == 2) dst[run2 + __popc(b2 & below)] = key;
+        else if (c == 3) dst[run3 + __popc(b3 & below)] = key;
+        run0 += __popc(b0); run1 += __popc(b1); run2 += __popc(b2); run3 += __popc(b3);
+    }
+}
+
+__device__ __forceinline__ int nonzero4(uint4 c) { return (c.x != 0) + (c.y != 0) + (c.z != 0) + (c.w != 0); }
+
+// Core: keys[0..K) sit in buffer 0 of `bufs` in the reference's vToDistributeKeys order.  Returns the number of
+// kept keys (written to outKeys with (addX, addY) added to the coordinates).
+__device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, int nIni, float hX, int N, int addX,
+                             int addY, uint32_t* outKeys, int outCap, const QtShared& S) {
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
+    int* misc = S.misc;
+    int* warpSums = misc + 16;
+    int* rootCnt = misc + 32;
+    if (K == 0 || nIni < 1) return 0;
+    if (nIni > MAX_ROOTS) nIni = MAX_ROOTS;  // rejected on the host; guard only
+
+    // ---- roots: stable partition of the candidates by kp.pt.x / hX (:917-921) into buffer 1 ----
+    for (int i = tid; i < nIni; i += blockDim.x) rootCnt[i] = 0;
+    __syncthreads();
+    for (int i = tid; i < K; i += blockDim.x) {
+        const int r = min((int)__fdiv_rn((float)key_x(bufs[i]), hX), nIni - 1);
+        atomicAdd(&rootCnt[r], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int run = 0, n = 0;
+        for (int r = 0; r < nIni; ++r) {
+            const int c = rootCnt[r];
+            if (c > 0) {
+                QNode nd;
+                nd.x0 = (uint16_t)(int)__fmul_rn(hX, (float)r);
+                nd.x1 = (uint16_t)(int)__fmul_rn(hX, (float)(r + 1));
+                nd.y0 = 0;
+                nd.y1 = (uint16_t)H;
+                nd.begin = (1u << 31) | (uint32_t)run;
+                nd.count = (uint32_t)c;
+                S.list[0][n++] = nd;
+            }
+            rootCnt[r] = run;  // becomes the segment start
+            run += c;
+        }
+        misc[0] = n;
+    }
+    __syncthreads();
+    for (int r = wid; r < nIni; r += nw) {  // warp r compacts its root's keys in candidate order
+        uint32_t* dst = bufs + candCap + rootCnt[r];
+        int run = 0;
+        for (int base = 0; base < K; base += 32) {
+            const int i = base + lane;
+            uint32_t key = 0;
+            bool mine = false;
+            if (i < K) {
+                key = bufs[i];
+                mine = min((int)__fdiv_rn((float)key_x(key), hX), nIni - 1) == r;
+            }
+            const uint32_t b = __ballot_sync(0xffffffffu, mine);
+            if (mine) dst[run + __popc(b & ((1u << lane) - 1))] = key;
+            run += __popc(b);
+        }
+    }
+    __syncthreads();
+    (void)W;
+
+    int cur = 0;          // which list buffer is current
+    int n = misc[0];      // list size
+    int P = 0;            // the first P list positions are the children pushed by the last pass
+    bool finalPhase = false;
+    while (true) {
+        QNode* L = S.list[cur];
+        QNode* Lnew = S.list[cur ^ 1];
+        const int prev = n;
+        if (!finalPhase) {
+            // ---- sweep ----
+            for (int i = wid; i < n; i += nw) {
+                const QNode nd = L[i];
+                uint4 cc = make_uint4(0, 0, 0, 0);
+                if (nd.count > 1) cc = warp_count_children(nd, bufs, candCap, lane);
+                if (lane == 0) {
+                    S.cc[i] = cc;
+                    S.sA[i] = nd.count > 1 ? nonzero4(cc) - 1 : 0;
+                }
+            }
+            if (tid == 0) misc[1] = n;  // cut
+            __syncthreads();
+            block_exscan(S.sA, n, warpSums);
+            for (int i = tid; i < n; i += blockDim.x)
+                if (prev + S.sA[i] >= N) atomicMin(&misc[1], i);
+            __syncthreads();
+            const int cut = misc[1];
+            for (int i = tid; i < n; i += blockDim.x) {
+                const bool split = i < cut && L[i].count > 1;
+                S.sA[i] = split ? nonzero4(S.cc[i]) : 0;
+                S.sB[i] = split ? 0 : 1;
+            }
+            __syncthreads();
+            const int pushed = block_exscan(S.sA, n, warpSums);
+            const int surv = block_exscan(S.sB, n, warpSums);
+            for (int i = wid; i < n; i += nw) {
+                const QNode nd = L[i];
+                if (i < cut && nd.count > 1) warp_split(nd, S.cc[i], bufs, candCap, Lnew, pushed - 1 - S.sA[i], lane);
+                else if (lane == 0) Lnew[pushed + S.sB[i]] = nd;
+            }
+            __syncthreads();
+            n = pushed + surv;
+            P = pushed;
+        } else {
+            // ---- final phase pass over the expandable children of the previous pass (positions < P) ----
+            for (int i = wid; i < P; i += nw) {
+                const QNode nd = L[i];
+                uint4 cc = make_uint4(0, 0, 0, 0);
+                if (nd.count > 1) cc = warp_count_children(nd, bufs, candCap, lane);
+                if (lane == 0) S.cc[i] = cc;
+            }
+            if (tid == 0) misc[1] = 0x7fffffff;  // rank of the node whose split reaches N
+            __syncthreads();
+            // processing order: descending (count, creation order); creation order = P-1-position
+            int E = 0;
+            for (int i = tid; i < P; i += blockDim.x) {
+                const uint32_t ci = L[i].count;
+                if (ci > 1) {
+                    int rank = 0;
+                    for (int j = 0; j < P; ++j) {
+                        const uint32_t cj = L[j].count;
+                        rank += (cj > 1 && (cj > ci || (cj == ci && j < i))) ? 1 : 0;
+                    }
+                    S.sC[rank] = i;
+                }
+                S.sB[i] = ci > 1 ? 1 : 0;
+            }
+            __syncthreads();
+            E = block_exscan(S.sB, P, warpSums);  // only the total is needed
+            for (int r = tid; r < E; r += blockDim.x) S.sA[r] = nonzero4(S.cc[S.sC[r]]);
+            __syncthreads();
+            block_exscan(S.sA, E, warpSums);  // sA[r] = children pushed before rank r
+            for (int r = tid; r < E; r += blockDim.x) {
+                // size after processing ranks 0..r = prev + (pushed through r) - (r + 1)
+                const int after = prev + S.sA[r] + nonzero4(S.cc[S.sC[r]]) - (r + 1);
+                if (after >= N) atomicMin(&misc[1], r);
+            }
+            __syncthreads();
+            const int last = min(misc[1], E - 1);  // ranks 0..last are processed
+            const int pushed = (last >= 0) ? S.sA[last] + nonzero4(S.cc[S.sC[last]]) : 0;
+            // survivors: every list node that is not a processed parent
+            for (int i = tid; i < n; i += blockDim.x) S.sB[i] = 1;
+            __syncthreads();
+            for (int r = tid; r <= last; r += blockDim.x) S.sB[S.sC[r]] = 0;
+            __syncthreads();
+            const int surv = block_exscan(S.sB, n, warpSums);
+            for (int r = wid; r <= last; r += nw) {
+                const int i = S.sC[r];
+                warp_split(L[i], S.cc[i], bufs, candCap, Lnew, pushed - 1 - S.sA[r], lane);
+            }
+            for (int i = tid; i < n; i += blockDim.x) {
+                const bool gone = (i + 1 < n) ? (S.sB[i + 1] == S.sB[i]) : (S.sB[i] == surv);
+                if (!gone) Lnew[pushed + S.sB[i]] = L[i];
+            }
+            __syncthreads();
+            n = pushed + surv;
+            P = pushed;
+        }
+        cur ^= 1;
+        // ---- termination (:1026-1030, :1092-1093) ----
+        if (n >= N || n == prev) break;
+        if (!finalPhase) {
+            // nToExpand = pushed children holding more than one key
+            if (tid == 0) misc[2] = 0;
+            __syncthreads();
+            int mine = 0;
+            for (int i = tid; i < P; i += blockDim.x) mine += S.list[cur][i].count > 1 ? 1 : 0;
+            if (mine) atomicAdd(&misc[2], mine);
+            __syncthreads();
+            if (n + 3 * misc[2] > N) finalPhase = true;
+            __syncthreads();
+        }
+    }
+
+    // ---- keep the best key of every node (:1098-1117): first key of maximal response, list order ----
+    const QNode* L = S.list[cur];
+    const int nOut = min(n, outCap);
+    for (int i = wid; i < nOut; i += nw) {
+        const QNode nd = L[i];
+        const uint32_t* k = bufs + ((nd.begin >> 31) ? candCap : 0) + (nd.begin & 0x7FFFFFFFu);
+        unsigned long long best = 0;
+        for (uint32_t j = lane; j < nd.count; j += 32) {
+            const unsigned long long v = ((unsigned long long)key_resp(k[j]) << 32) | (0xFFFFFFFFu - j);
+            best = v > best ? v : best;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other > best ? other : best;
+        }
+        if (lane == 0) {
+            const uint32_t key = k[0xFFFFFFFFu - (uint32_t)(best & 0xFFFFFFFFu)];
+            outKeys[i] = pack_key(key_x(key) + addX, key_y(key) + addY, key_resp(key));
+        }
+    }
+    return n;
+}
+
+__device__ void carve(uint8_t* smem, int maxNodes, int maxCells, QtShared& S) {
+    size_t o = 0;
+    S.list[0] = reinterpret_cast<QNode*>(smem + o); o += (size_t)maxNodes * sizeof(QNode);
+    S.list[1] = reinterpret_cast<QNode*>(smem + o); o += (size_t)maxNodes * sizeof(QNode);
+    S.cc = reinterpret_cast<uint4*>(smem + o); o += (size_t)maxNodes * sizeof(uint4);
+    S.sA = reinterpret_cast<int*>(smem + o); o += (size_t)maxNodes * 4;
+    S.sB = reinterpret_cast<int*>(smem + o); o += (size_t)maxNodes * 4;
+    S.sC = reinterpret_cast<int*>(smem + o); o += (size_t)maxNodes * 4;
+    S.misc = reinterpret_cast<int*>(smem + o); o += (32 + MAX_ROOTS + 4) * 4;
+    S.cellOff = reinterpret_cast<int*>(smem + o); o += (size_t)(maxCells + 1) * 4;
+}
+
+static size_t qt_smem(int maxNodes, int maxCells) {
+    return (size_t)maxNodes * (2 * sizeof(QNode) + sizeof(uint4) + 12) + (32 + MAX_ROOTS + 4) * 4 + (size_t)(maxCells + 1) * 4;
+}
+
+// grid (nlevels, batch)
+__global__ void __launch_bounds__(QT_THREADS) k_quadtree(const __grid_constant__ FrameGeom g, int maxNodes, int maxCells,
+                                                          const int* __restrict__ cellCnt,
+                                                          const uint32_t* __restrict__ cellKeys, uint32_t* qtScratch,
+                                                          int* __restrict__ lvlCnt, uint32_t* __restrict__ lvlKeys,
+                                                          int* dStatus) {
+    extern __shared__ __align__(16) uint8_t qsmem[];
+    QtShared S;
+    carve(qsmem, maxNodes, maxCells, S);
+    const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    const LevelGeom& L = g.lv[level];
+    const int nCells = L.nCols * L.nRows;
+    const int* cnt = cellCnt + (long long)f * g.nCellsTotal + L.cellBase;
+    const uint32_t* keys = cellKeys + ((long long)f * g.nCellsTotal + L.cellBase) * CELL_CAP;
+    uint32_t* bufs = qtScratch + (long long)f * g.qtFrameStride + L.qtBase;
+    // gather the per-cell slots into one list in cell order = vToDistributeKeys order (:1256-1299)
+    for (int i = tid; i < nCells; i += blockDim.x) S.cellOff[i] = cnt[i];
+    __syncthreads();
+    int K = block_exscan(S.cellOff, nCells, S.misc + 16);
+    if (K > L.candCap) {
+        if (tid == 0) atomicExch(dStatus, ORBX_E_OVERFLOW);
+        K = L.candCap;
+    }
+    for (int c = tid >> 5; c < nCells; c += blockDim.x >> 5) {  // a warp copies one cell's slot
+        const int nc = min(cnt[c], CELL_CAP), o = S.cellOff[c];
+        for (int k = tid & 31; k < nc; k += 32)
+            if (o + k < K) bufs[o + k] = keys[(long long)c * CELL_CAP + k];
+    }
+    __syncthreads();
+    uint32_t* out = lvlKeys + (long long)f * g.slotsTotal + L.slotBase;
+    const int n = quadtree_core(bufs, L.candCap, K, L.maxBX - L.minBX, L.maxBY - L.minBY, L.nIni, L.hX, L.quota, L.minBX,
+                                L.minBY, out, L.quota + 4, S);
+    if (tid == 0) lvlCnt[(long long)f * g.nlevels + level] = min(n, L.quota + 4);
+}
+
+__global__ void __launch_bounds__(QT_THREADS) k_quadtree_single(const uint32_t* keysIn, int K, int W, int H, int nIni,
+                                                                 float hX, int N, int maxNodes, uint32_t* bufs, int candCap,
+                                                                 uint32_t* out, int* outCnt) {
+    extern __shared__ __align__(16) uint8_t qsmem[];
+    QtShared S;
+    carve(qsmem, maxNodes, 0, S);
+    for (int i = threadIdx.x; i < K; i += blockDim.x) bufs[i] = keysIn[i];
+    __syncthreads();
+    const int n = quadtree_core(bufs, candCap, K, W, H, nIni, hX, N, 0, 0, out, N + 4, S);
+    if (threadIdx.x == 0) *outCnt = min(n, N + 4);
+}
+
+int quadtree_smem_bytes(int maxQuota) { return (int)qt_smem(maxQuota + MAX_ROOTS + 8, 0); }
+
+int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uint32_t* cellKeys, uint32_t* qtScratch,
+                    int* lvlCnt, uint32_t* lvlKeys, int* dStatus, cudaStream_t s) {
+    int maxQuota = 0, maxCells = 0;
+    for (int l = 0; l < g.nlevels; ++l) {
+        maxQuota = max(maxQuota, g.lv[l].quota);
+        maxCells = max(maxCells, g.lv[l].nCols * g.lv[l].nRows);
+    }
+    const int maxNodes = maxQuota + MAX_ROOTS + 8;
+    const size_t smem = qt_smem(maxNodes, maxCells);
+    if (smem > 220 * 1024) {
+        set_error("quadtree: %zu bytes of shared memory needed (nfeatures per level %d, cells %d)", smem, maxQuota, maxCells);
+        return ORBX_E_INVALID;
+    }
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        ORBX_CUDA(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    dim3 grid(g.nlevels, batch);
+    k_quadtree<<<grid, QT_THREADS, smem, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int launch_quadtree_single(const uint32_t* dKeysIn, int n, int minX, int maxX, int minY, int maxY, int N,
+                           uint32_t* dScratch, int candCap, uint32_t* dOut, int* dCount, int* dStatus, cudaStream_t s) {
+    (void)dStatus;
+    const int W = maxX - minX, H = maxY - minY;
+    const int nIni = (int)roundf((float)W / (float)H);
+    const float hX = nIni > 0 ? (float)W / (float)nIni : 1.f;
+    if (nIni > MAX_ROOTS) {
+        set_error("quadtree: aspect ratio %d:1 needs more than %d root nodes", nIni, MAX_ROOTS);
+        return ORBX_E_INVALID;
+    }
+    const int maxNodes = N + MAX_ROOTS + 8;
+    const size_t smem = qt_smem(maxNodes, 0);
+    if (smem > 220 * 1024) {
+        set_error("quadtree: N=%d does not fit shared memory", N);
+        return ORBX_E_INVALID;
+    }
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        ORBX_CUDA(cudaFuncSetAttribute(k_quadtree_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    k_quadtree_single<<<1, QT_THREADS, smem, s>>>(dKeysIn, n, W, H, nIni, hX, N, maxNodes, dScratch, candCap, dOut, dCount);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+}  // namespace orbx

@@ -1,0 +1,124 @@
+// csrc/orbx_internal.h — shared declarations of liborbx.so (not installed; the public surface is include/orbx.h).
+//
+// Device data layout (all per extractor handle, B = batch capacity, l = pyramid level):
+//   plane[l]   : uint8  [B][h_l + 38][pitch_l]   padded pyramid plane; interior pixel (x, y) lives at byte
+//                                               (y + 19) * pitch_l + (x + 32): the 19-px reflect-101 border of
+//                                               the reference (EDGE_THRESHOLD, src/ORBextractor.cc:97) sits at
+//                                               bytes 13..31, so interior rows start 32-byte aligned.
+//   blur[l]    : uint8  [B][h_l][bpitch_l]        7x7 sigma-2 blurred level, interior only (descriptor taps stay
+//                                               >= 1 px inside, see k_describe.cu).
+//   cellCnt    : int32  [B][nCellsTotal]          FAST keypoints per 30-px cell (all levels concatenated)
+//   cellKeys   : uint32 [B][nCellsTotal][CELL_CAP] packed (resp << 24 | y << 12 | x), x,y relative to minBorder,
+//                                               row-major inside the cell (cv::FAST output order)
+//   lvlCnt     : int32  [B][nlevels]              keypoints kept by the quadtree
+//   lvlKeys    : uint32 [B][slotsTotal]           packed kept keypoints, level l at slotBase[l], quota_l + 4 slots
+//   qtScratch  : uint32 [B][nlevels][2][candCap_l] key ping-pong buffers of the quadtree
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/orbx.h"
+
+namespace orbx {
+
+constexpr int EDGE = 19;         // EDGE_THRESHOLD
+constexpr int XOFF = 32;         // byte column of interior x = 0 inside a plane row
+constexpr int PADL = XOFF - EDGE;  // byte column of padded x = 0  (13)
+constexpr int HALF_PATCH = 15;
+constexpr int PATCH = 31;
+constexpr int CELL_CAP = 128;    // FAST keypoints per cell (overflow -> ORBX_E_OVERFLOW)
+constexpr int FAST_THREADS = 128;
+constexpr int QT_THREADS = 256;
+constexpr int MAX_ROOTS = 64;
+
+struct LevelGeom {
+    int w, h;               // interior size
+    int pitch, rows;        // plane row pitch (bytes), rows = h + 38
+    long long planeStride;  // bytes per frame in plane[l]
+    int bpitch;
+    long long blurStride;   // bytes per frame in blur[l]
+    // FAST grid (src/ORBextractor.cc:1133-1147)
+    int minBX, minBY, maxBX, maxBY, nCols, nRows, wCell, hCell;
+    int cellBase;           // first cell of this level in the per-frame cell arrays
+    int quota;              // mnFeaturesPerLevel[l]
+    int slotBase;           // first slot of this level in lvlKeys
+    int candCap;            // capacity of one quadtree key buffer
+    long long qtBase;       // offset (in uint32) of this level's scratch inside one frame's qtScratch
+    float scale;            // mvScaleFactor[l]
+    float size;             // (float)(int)(PATCH_SIZE * mvScaleFactor[l])
+    // quadtree roots (src/ORBextractor.cc:894-914)
+    int nIni;
+    float hX;
+    int blurTilesX, blurTileBase;  // 128x32 output tiles of the blur kernel
+    int kpBase;                    // first warp slot of this level in the describe kernel's grid
+    uint8_t* plane;
+    uint8_t* blur;
+};
+
+struct FrameGeom {
+    int nlevels;
+    int nCellsTotal;
+    int slotsTotal;
+    long long qtFrameStride;  // uint32 per frame in qtScratch
+    int fastBoxW, fastBoxH;   // TMA box of the FAST kernel
+    int blurTilesTotal;
+    int iniTh, minTh;
+    LevelGeom lv[ORBX_MAX_LEVELS];
+};
+
+struct ResizeTab {  // one entry per destination column / row: source index pair + 11-bit coefficients
+    uint16_t s0, s1;
+    int16_t c0, c1;
+};
+
+void count_launch();
+void set_error(const char* fmt, ...);
+
+#define ORBX_CUDA(call)                                                                          \
+    do {                                                                                         \
+        cudaError_t e__ = (call);                                                                \
+        if (e__ != cudaSuccess) {                                                                \
+            ::orbx::set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e__)); \
+            return ORBX_E_CUDA;                                                                  \
+        }                                                                                        \
+    } while (0)
+
+// ---- kernel launchers (each file k_*.cu holds the kernels of one stage) ---------------------------------------
+// ComputePyramid: level 0 = frame + reflect-101 border, level l = resize(level l-1) + border
+int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
+                        cudaStream_t s);
+int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, const ResizeTab* ytab, int areaFast,
+                         int batch, cudaStream_t s);
+// per-cell FAST-9 + threshold fallback + NMS
+int launch_fast(const FrameGeom& g, const CUtensorMap* dMaps, int batch, int* cellCnt, uint32_t* cellKeys, int* dStatus,
+                cudaStream_t s);
+// DistributeOctTree per (frame, level)
+int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uint32_t* cellKeys, uint32_t* qtScratch,
+                    int* lvlCnt, uint32_t* lvlKeys, int* dStatus, cudaStream_t s);
+int quadtree_smem_bytes(int maxQuota);
+// stand-alone quadtree on a caller-supplied candidate list (debug / parity entry)
+int launch_quadtree_single(const uint32_t* dKeysIn, int n, int minX, int maxX, int minY, int maxY, int N,
+                           uint32_t* dScratch, int candCap, uint32_t* dOut, int* dCount, int* dStatus, cudaStream_t s);
+// 7x7 sigma=2 fixed-point GaussianBlur of every level
+int launch_blur(const FrameGeom& g, const CUtensorMap* dMaps, int batch, cudaStream_t s);
+// IC_Angle + steered BRIEF + scale-back + level-major compaction into the caller's output
+int launch_describe(const FrameGeom& g, int batch, const int* lvlCnt, const uint32_t* lvlKeys, orbx_keypoint* dKps,
+                    uint8_t* dDesc, int cap, int* dCounts, float* dLvlAngles, int* dStatus, cudaStream_t s);
+// matchers
+int launch_hamming_pairs(const uint8_t* a, const uint8_t* b, int n, int* dist, cudaStream_t s);
+int launch_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2,
+                      int* match, unsigned long long* dPartial, cudaStream_t s);
+size_t bruteforce_scratch_bytes(int nq, int nd);
+int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score,
+                    cudaStream_t s);
+
+// ---- packed keypoint helpers ---------------------------------------------------------------------------------
+__host__ __device__ inline uint32_t pack_key(int x, int y, int resp) {
+    return ((uint32_t)resp << 24) | ((uint32_t)y << 12) | (uint32_t)x;
+}
+__host__ __device__ inline int key_x(uint32_t k) { return (int)(k & 0xFFFu); }
+__host__ __device__ inline int key_y(uint32_t k) { return (int)((k >> 12) & 0xFFFu); }
+__host__ __device__ inline int key_resp(uint32_t k) { return (int)(k >> 24); }
+
+}  // namespace orbx

@@ -74,7 +74,7 @@ def textured_frame(seed: int, h: int, w: int, flat_fraction: float = 0.15) -> np
         img[sl] = base + (0.06 * (patch - patch.mean()) if rng.integers(0, 2) else 0.0)
     img = _smooth(img, 1)
     img += rng.normal(0.0, 1.5, size=(h, w)).astype(np.float32)
-    return np.clip(np.rint(img), 0, 255).astype(np.uint8)
+    return np.ascontiguousarray(np.clip(np.rint(img), 0, 255).astype(np.uint8))
 
 
 def frame(kind: str, k: int) -> np.ndarray:
@@ -110,7 +110,7 @@ def stereo_pair(kind: str, k: int, max_disp: int = 48):
     lf = left.astype(np.float32)
     right = lf[rows, x0] * (1 - f) + lf[rows, x1] * f
     right += rng.normal(0.0, 1.0, size=(h, w)).astype(np.float32)
-    return left, np.clip(np.rint(right), 0, 255).astype(np.uint8)
+    return left, np.ascontiguousarray(np.clip(np.rint(right), 0, 255).astype(np.uint8))
 
 
 def shifted_frame(kind: str, k: int, dx: int = 7, dy: int = -4) -> np.ndarray:
@@ -118,7 +118,7 @@ def shifted_frame(kind: str, k: int, dx: int = 7, dy: int = -4) -> np.ndarray:
     a = frame(kind, k)
     rng = np.random.default_rng(88000000 + k)
     b = np.roll(a, (dy, dx), axis=(0, 1)).astype(np.float32) + rng.normal(0.0, 1.5, size=a.shape)
-    return np.clip(np.rint(b), 0, 255).astype(np.uint8)
+    return np.ascontiguousarray(np.clip(np.rint(b), 0, 255).astype(np.uint8))
 
 
 def descriptor_sets(seed: int, nq: int, nd: int, dup_fraction: float = 0.5, max_flips: int = 30):
