@@ -1,0 +1,718 @@
+// csrc/extractor.cu — host side of the extractor handle behind include/orbx.h: constructor tables, per-geometry
+// device layout, TMA descriptors, the launch sequence of operator() and the C entry points.
+//
+// Reference lines restated here (host arithmetic only; pixel work is in k_*.cu):
+//   ORBextractor::ORBextractor   src/ORBextractor.cc:496-557   scale tables, per-level quotas, umax
+//   ComputePyramid               src/ORBextractor.cc:1843-1844 level sizes = cvRound((float)cols * mvInvScaleFactor)
+//   ComputeKeyPointsOctTree      src/ORBextractor.cc:1133-1147 borders and the 30-px cell grid
+//   DistributeOctTree            src/ORBextractor.cc:894-896   number and width of the root nodes
+//   cv::resize INTER_LINEAR 8U   (OpenCV; call site :1852)     per-column / per-row index + 11-bit coefficient tables
+#include <algorithm>
+#include <atomic>
+#include <cfloat>
+#include <climits>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "orbx_internal.h"
+
+namespace orbx {
+
+static thread_local std::string g_err;
+static std::atomic<long long> g_launches{0};
+
+void set_error(const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_err = buf;
+}
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+static inline int cv_round(float v) { return (int)lrintf(v); }   // cvRound: round half to even
+static inline int cv_round(double v) { return (int)lrint(v); }
+static inline short sat_short(float v) {
+    const int i = cv_round(v);
+    return (short)std::min(std::max(i, (int)SHRT_MIN), (int)SHRT_MAX);
+}
+static inline long long round_up(long long v, long long a) { return (v + a - 1) / a * a; }
+
+struct DevBuf {  // owning device allocation
+    void* p = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t n) {
+        if (n <= bytes) return ORBX_OK;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e != cudaSuccess) {
+            set_error("cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
+            p = nullptr;
+            return e == cudaErrorMemoryAllocation ? ORBX_E_OOM : ORBX_E_CUDA;
+        }
+        bytes = n;
+        return ORBX_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct PinBuf {  // owning pinned host allocation
+    void* p = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t n) {
+        if (n <= bytes) return ORBX_OK;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMallocHost(&p, n);
+        if (e != cudaSuccess) {
+            set_error("cudaMallocHost(%zu) failed: %s", n, cudaGetErrorString(e));
+            p = nullptr;
+            return ORBX_E_OOM;
+        }
+        bytes = n;
+        return ORBX_OK;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+}  // namespace orbx
+
+using namespace orbx;
+
+struct orbx_extractor {
+    orbx_params prm{};
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    // constructor tables (src/ORBextractor.cc:501-555)
+    std::vector<float> scale, invScale, sigma2, invSigma2;
+    std::vector<int> quota;
+    int umax[16];
+    // geometry-dependent state
+    int w = 0, h = 0;        // frame size the layout was built for
+    int batchCap = 0;        // frames the scratch holds
+    int outCap = 0;          // keypoints per frame the output staging holds
+    FrameGeom g{};
+    std::vector<int> areaFast;
+    DevBuf planes[ORBX_MAX_LEVELS], blurs[ORBX_MAX_LEVELS], xtab[ORBX_MAX_LEVELS], ytab[ORBX_MAX_LEVELS];
+    DevBuf cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, lvlAngles, status, maps, dFrames, dKps, dDesc, dCounts;
+    PinBuf hFrames, hKps, hDesc, hCounts, hStatus;
+    // host copies of pyramid levels for mvImagePyramid readers
+    std::vector<uint8_t> hostLevel[ORBX_MAX_LEVELS];
+    int hostLevelFrame[ORBX_MAX_LEVELS];
+    long long hostLevelSerial[ORBX_MAX_LEVELS];
+    long long serial = 0;    // bumped by every extract call
+    int lastBatch = 0;
+};
+
+// ---- constructor tables (src/ORBextractor.cc:501-555) -----------------------------------------------------------
+static void build_tables(orbx_extractor* ex) {
+    const orbx_params& p = ex->prm;
+    const int nl = p.nlevels;
+    const double scaleFactor = p.scale_factor;  // the member is a double initialised from the float argument
+    ex->scale.assign(nl, 1.f);
+    ex->sigma2.assign(nl, 1.f);
+    for (int i = 1; i < nl; ++i) {
+        ex->scale[i] = (float)(ex->scale[i - 1] * scaleFactor);
+        ex->sigma2[i] = ex->scale[i] * ex->scale[i];
+    }
+    ex->invScale.resize(nl);
+    ex->invSigma2.resize(nl);
+    for (int i = 0; i < nl; ++i) {
+        ex->invScale[i] = 1.0f / ex->scale[i];
+        ex->invSigma2[i] = 1.0f / ex->sigma2[i];
+    }
+    ex->quota.assign(nl, 0);
+    const float factor = (float)(1.0f / scaleFactor);
+    float nDesired = p.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; ++l) {
+        ex->quota[l] = cv_round(nDesired);
+        sum += ex->quota[l];
+        nDesired *= factor;
+    }
+    ex->quota[nl - 1] = std::max(p.nfeatures - sum, 0);
+    // umax (:540-555)
+    int* umax = ex->umax;
+    int v, v0;
+    const int vmax = (int)std::floor(HALF_PATCH * std::sqrt(2.f) / 2 + 1);
+    const int vmin = (int)std::ceil(HALF_PATCH * std::sqrt(2.f) / 2);
+    const double hp2 = HALF_PATCH * HALF_PATCH;
+    for (v = 0; v <= vmax; ++v) umax[v] = cv_round(std::sqrt(hp2 - v * v));
+    for (v = HALF_PATCH, v0 = 0; v >= vmin; --v) {
+        while (umax[v0] == umax[v0 + 1]) ++v0;
+        umax[v] = v0;
+        ++v0;
+    }
+}
+
+// cv::resize(INTER_LINEAR, CV_8U) coefficient tables for one axis: n destination samples from `sn` source samples
+static void build_resize_axis(int sn, int dn, bool clampFrac, std::vector<ResizeTab>& tab) {
+    const double inv = (double)dn / sn, scale = 1. / inv;
+    tab.resize(dn);
+    for (int d = 0; d < dn; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)std::floor(f);
+        f -= s;
+        ResizeTab t;
+        if (clampFrac) {  // x axis: OpenCV zeroes the fraction when the index is clamped
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= sn - 1) { f = 0; s = sn - 1; }
+            t.s0 = (uint16_t)s;
+            t.s1 = (uint16_t)std::min(s + 1, sn - 1);
+        } else {          // y axis: rows are clamped, the fraction is kept
+            t.s0 = (uint16_t)std::min(std::max(s, 0), sn - 1);
+            t.s1 = (uint16_t)std::min(std::max(s + 1, 0), sn - 1);
+        }
+        t.c0 = sat_short((1.f - f) * 2048);
+        t.c1 = sat_short(f * 2048);
+        tab[d] = t;
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+// 3-D (byte column, row, frame) view of a padded plane with a (boxW x boxH x 1) box
+static int make_plane_map(CUtensorMap* m, void* base, int pitch, int rows, long long planeStride, int batch, int boxW, int boxH) {
+    EncodeTiledFn enc = get_encode_fn();
+    if (!enc) {
+        set_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+        return ORBX_E_CUDA;
+    }
+    cuuint64_t dims[3] = {(cuuint64_t)pitch, (cuuint64_t)rows, (cuuint64_t)batch};
+    cuuint64_t strides[2] = {(cuuint64_t)pitch, (cuuint64_t)planeStride};
+    cuuint32_t box[3] = {(cuuint32_t)boxW, (cuuint32_t)boxH, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed with CUresult %d (pitch %d rows %d stride %lld batch %d box %dx%d)", (int)r,
+                  pitch, rows, planeStride, batch, boxW, boxH);
+        return ORBX_E_CUDA;
+    }
+    return ORBX_OK;
+}
+
+// Builds the level geometry for a w x h frame and allocates scratch for `batch` frames.
+static int configure(orbx_extractor* ex, int w, int h, int batch) {
+    const int nl = ex->prm.nlevels;
+    if (w == ex->w && h == ex->h && batch <= ex->batchCap) return ORBX_OK;
+    if (w > 4000 || h > 4000) {
+        set_error("frames larger than 4000 x 4000 are not supported (got %d x %d)", w, h);
+        return ORBX_E_INVALID;
+    }
+    ORBX_CUDA(cudaStreamSynchronize(ex->stream));
+    batch = std::max(batch, ex->w == w && ex->h == h ? ex->batchCap : 1);
+    FrameGeom& g = ex->g;
+    memset(&g, 0, sizeof g);
+    g.nlevels = nl;
+    g.iniTh = ex->prm.ini_th_fast;
+    g.minTh = ex->prm.min_th_fast;
+    int cellBase = 0, slotBase = 0, tileBase = 0, maxWCell = 0, maxHCell = 0;
+    long long qtBase = 0;
+    ex->areaFast.assign(nl, 0);
+    for (int l = 0; l < nl; ++l) {
+        LevelGeom& L = g.lv[l];
+        L.w = cv_round((float)w * ex->invScale[l]);
+        L.h = cv_round((float)h * ex->invScale[l]);
+        if (L.w < 1 || L.h < 1) {
+            set_error("pyramid level %d of a %d x %d frame is empty", l, w, h);
+            return ORBX_E_INVALID;
+        }
+        L.pitch = (int)round_up(XOFF + L.w + EDGE + 16, 128);
+        L.rows = L.h + 2 * EDGE;
+        L.planeStride = round_up((long long)L.pitch * L.rows, 256);
+        L.bpitch = (int)round_up(L.w, 128);
+        L.blurStride = (long long)L.bpitch * L.h;
+        L.minBX = L.minBY = EDGE - 3;
+        L.maxBX = L.w - EDGE + 3;
+        L.maxBY = L.h - EDGE + 3;
+        const float width = (float)(L.maxBX - L.minBX), height = (float)(L.maxBY - L.minBY);
+        const float W = 30;
+        L.nCols = width > 0 ? (int)(width / W) : 0;
+        L.nRows = height > 0 ? (int)(height / W) : 0;
+        if (L.nCols < 1 || L.nRows < 1) {  // the reference divides by zero here; such a level yields nothing
+            L.nCols = L.nRows = 0;
+            L.wCell = L.hCell = 1;
+        } else {
+            L.wCell = (int)std::ceil(width / L.nCols);
+            L.hCell = (int)std::ceil(height / L.nRows);
+            maxWCell = std::max(maxWCell, L.wCell);
+            maxHCell = std::max(maxHCell, L.hCell);
+        }
+        L.cellBase = cellBase;
+        cellBase += L.nCols * L.nRows;
+        L.quota = ex->quota[l];
+        L.slotBase = slotBase;
+        slotBase += L.quota + 4;
+        L.candCap = std::max(32, std::min(L.nCols * L.nRows * CELL_CAP, 1 << 20));
+        L.qtBase = qtBase;
+        qtBase += 2LL * L.candCap;
+        L.scale = ex->scale[l];
+        L.size = (float)(int)(PATCH * ex->scale[l]);  // const int scaledPatchSize = PATCH_SIZE*mvScaleFactor[level]
+        L.nIni = 0;
+        L.hX = 1.f;
+        if (L.nCols > 0) {
+            L.nIni = (int)std::round((float)(L.maxBX - L.minBX) / (L.maxBY - L.minBY));
+            if (L.nIni > MAX_ROOTS) {
+                set_error("level %d aspect ratio needs %d quadtree roots (max %d)", l, L.nIni, MAX_ROOTS);
+                return ORBX_E_INVALID;
+            }
+            if (L.nIni >= 1) L.hX = (float)(L.maxBX - L.minBX) / L.nIni;
+        }
+        L.blurTilesX = (L.w + 127) / 128;
+        L.blurTileBase = tileBase;
+        tileBase += L.blurTilesX * ((L.h + 31) / 32);
+        L.kpBase = L.slotBase;
+    }
+    g.nCellsTotal = std::max(cellBase, 1);
+    g.slotsTotal = slotBase;
+    g.qtFrameStride = qtBase;
+    g.blurTilesTotal = tileBase;
+    g.fastBoxW = (int)round_up(std::max(maxWCell, 1) + 6, 16);
+    g.fastBoxH = std::max(maxHCell, 1) + 6;
+    if (g.fastBoxW > 256 || g.fastBoxH > 256 || g.fastBoxW * g.fastBoxH > 60000) {
+        set_error("FAST cell window %d x %d exceeds the TMA box limit", g.fastBoxW, g.fastBoxH);
+        return ORBX_E_INVALID;
+    }
+    // allocations
+    int rc;
+    for (int l = 0; l < nl; ++l) {
+        LevelGeom& L = g.lv[l];
+        if ((rc = ex->planes[l].ensure((size_t)L.planeStride * batch))) return rc;
+        if ((rc = ex->blurs[l].ensure((size_t)L.blurStride * batch + 256))) return rc;
+        L.plane = ex->planes[l].as<uint8_t>();
+        L.blur = ex->blurs[l].as<uint8_t>();
+        if (l > 0) {
+            std::vector<ResizeTab> xt, yt;
+            const LevelGeom& S = g.lv[l - 1];
+            build_resize_axis(S.w, L.w, true, xt);
+            build_resize_axis(S.h, L.h, false, yt);
+            const double sx = 1. / ((double)L.w / S.w), sy = 1. / ((double)L.h / S.h);
+            const int ix = cv_round(sx), iy = cv_round(sy);
+            const bool area = std::abs(sx - ix) < DBL_EPSILON && std::abs(sy - iy) < DBL_EPSILON && ix == 2 && iy == 2;
+            ex->areaFast[l] = area ? 1 : 0;
+            if (area) {  // exact 2x decimation is routed to INTER_AREA by cv::resize: mean of the 2x2 block
+                for (int d = 0; d < L.w; ++d) { xt[d].s0 = (uint16_t)(2 * d); xt[d].s1 = (uint16_t)(2 * d + 1); }
+                for (int d = 0; d < L.h; ++d) { yt[d].s0 = (uint16_t)(2 * d); yt[d].s1 = (uint16_t)(2 * d + 1); }
+            }
+            if ((rc = ex->xtab[l].ensure(xt.size() * sizeof(ResizeTab)))) return rc;
+            if ((rc = ex->ytab[l].ensure(yt.size() * sizeof(ResizeTab)))) return rc;
+            ORBX_CUDA(cudaMemcpy(ex->xtab[l].p, xt.data(), xt.size() * sizeof(ResizeTab), cudaMemcpyHostToDevice));
+            ORBX_CUDA(cudaMemcpy(ex->ytab[l].p, yt.data(), yt.size() * sizeof(ResizeTab), cudaMemcpyHostToDevice));
+        }
+    }
+    if ((rc = ex->cellCnt.ensure((size_t)batch * g.nCellsTotal * 4))) return rc;
+    if ((rc = ex->cellKeys.ensure((size_t)batch * g.nCellsTotal * CELL_CAP * 4))) return rc;
+    if ((rc = ex->qtScratch.ensure((size_t)batch * g.qtFrameStride * 4))) return rc;
+    if ((rc = ex->lvlCnt.ensure((size_t)batch * nl * 4))) return rc;
+    if ((rc = ex->lvlKeys.ensure((size_t)batch * g.slotsTotal * 4))) return rc;
+    if ((rc = ex->lvlAngles.ensure((size_t)batch * g.slotsTotal * 4))) return rc;
+    if ((rc = ex->status.ensure(256))) return rc;
+    if ((rc = ex->hStatus.ensure(64))) return rc;
+    // TMA descriptors: [0..nl) FAST windows, [nl..2nl) blur windows
+    std::vector<CUtensorMap> maps(2 * nl);
+    for (int l = 0; l < nl; ++l) {
+        const LevelGeom& L = g.lv[l];
+        if ((rc = make_plane_map(&maps[l], L.plane, L.pitch, L.rows, L.planeStride, batch, g.fastBoxW, g.fastBoxH))) return rc;
+        if ((rc = make_plane_map(&maps[nl + l], L.plane, L.pitch, L.rows, L.planeStride, batch, 144, 38))) return rc;
+    }
+    if ((rc = ex->maps.ensure(maps.size() * sizeof(CUtensorMap)))) return rc;
+    ORBX_CUDA(cudaMemcpy(ex->maps.p, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
+    ex->w = w;
+    ex->h = h;
+    ex->batchCap = batch;
+    for (int l = 0; l < ORBX_MAX_LEVELS; ++l) ex->hostLevelSerial[l] = -1;
+    return ORBX_OK;
+}
+
+// ---- the launch sequence of operator() (src/ORBextractor.cc:1701-1809) on device-resident buffers ---------------
+static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
+                        orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dCounts, int* dStatus, cudaStream_t s) {
+    const FrameGeom& g = ex->g;
+    const int nl = g.nlevels;
+    int rc;
+    ORBX_CUDA(cudaMemsetAsync(dStatus, 0, sizeof(int), s));
+    if ((rc = launch_pyramid_base(g, dFrames, batch, stride, frameStride, s))) return rc;                 // ComputePyramid
+    for (int l = 1; l < nl; ++l)
+        if ((rc = launch_pyramid_level(g, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->areaFast[l], batch, s)))
+            return rc;
+    const CUtensorMap* maps = ex->maps.as<CUtensorMap>();
+    if ((rc = launch_fast(g, maps, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), dStatus, s))) return rc;
+    if ((rc = launch_quadtree(g, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), ex->qtScratch.as<uint32_t>(),
+                              ex->lvlCnt.as<int>(), ex->lvlKeys.as<uint32_t>(), dStatus, s)))
+        return rc;
+    if ((rc = launch_blur(g, maps + nl, batch, s))) return rc;                                            // GaussianBlur
+    if ((rc = launch_describe(g, batch, ex->lvlCnt.as<int>(), ex->lvlKeys.as<uint32_t>(), dKps, dDesc, cap, dCounts,
+                              ex->lvlAngles.as<float>(), dStatus, s)))
+        return rc;
+    ex->serial++;
+    ex->lastBatch = batch;
+    return ORBX_OK;
+}
+
+static int check_device(const orbx_extractor* ex) {
+    if (!ex) {
+        set_error("null extractor handle");
+        return ORBX_E_INVALID;
+    }
+    ORBX_CUDA(cudaSetDevice(ex->device));
+    return ORBX_OK;
+}
+
+extern "C" {
+
+const char* orbx_last_error(void) { return g_err.c_str(); }
+int orbx_version(void) { return 100; }
+long long orbx_kernel_launches(void) { return g_launches.load(); }
+
+int orbx_extractor_create(const orbx_params* p, orbx_extractor** out) {
+    if (!p || !out) {
+        set_error("orbx_extractor_create: null argument");
+        return ORBX_E_INVALID;
+    }
+    *out = nullptr;
+    if (p->nlevels < 1 || p->nlevels > ORBX_MAX_LEVELS || p->nfeatures < 1 || !(p->scale_factor > 1.0f) || p->nfeatures > 8000) {
+        set_error("orbx_extractor_create: need 1 <= nlevels <= %d, 1 <= nfeatures <= 8000, scaleFactor > 1", ORBX_MAX_LEVELS);
+        return ORBX_E_INVALID;
+    }
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        set_error("no CUDA device: %s (this library has no CPU path)", e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+        return ORBX_E_CUDA;
+    }
+    orbx_extractor* ex = new orbx_extractor();
+    ex->prm = *p;
+    if (p->device >= 0) ex->device = p->device;
+    else ORBX_CUDA(cudaGetDevice(&ex->device));
+    if (ex->device >= ndev) {
+        set_error("device %d requested, %d present", ex->device, ndev);
+        delete ex;
+        return ORBX_E_INVALID;
+    }
+    ORBX_CUDA(cudaSetDevice(ex->device));
+    cudaDeviceProp prop;
+    ORBX_CUDA(cudaGetDeviceProperties(&prop, ex->device));
+    if (prop.major < 10) {
+        set_error("device %d is sm_%d%d; this library carries sm_100a code only", ex->device, prop.major, prop.minor);
+        delete ex;
+        return ORBX_E_CUDA;
+    }
+    ORBX_CUDA(cudaStreamCreateWithFlags(&ex->stream, cudaStreamNonBlocking));
+    build_tables(ex);
+    for (int l = 0; l < ORBX_MAX_LEVELS; ++l) ex->hostLevelSerial[l] = -1;
+    if (p->width > 0 && p->height > 0) {
+        int rc = configure(ex, p->width, p->height, std::max(1, p->max_batch));
+        if (rc) {
+            orbx_extractor_destroy(ex);
+            return rc;
+        }
+    }
+    *out = ex;
+    return ORBX_OK;
+}
+
+void orbx_extractor_destroy(orbx_extractor* ex) {
+    if (!ex) return;
+    cudaSetDevice(ex->device);
+    if (ex->stream) {
+        cudaStreamSynchronize(ex->stream);
+        cudaStreamDestroy(ex->stream);
+    }
+    for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
+        ex->planes[l].release(); ex->blurs[l].release(); ex->xtab[l].release(); ex->ytab[l].release();
+    }
+    for (DevBuf* b : {&ex->cellCnt, &ex->cellKeys, &ex->qtScratch, &ex->lvlCnt, &ex->lvlKeys, &ex->lvlAngles, &ex->status,
+                      &ex->maps, &ex->dFrames, &ex->dKps, &ex->dDesc, &ex->dCounts})
+        b->release();
+    for (PinBuf* b : {&ex->hFrames, &ex->hKps, &ex->hDesc, &ex->hCounts, &ex->hStatus}) b->release();
+    delete ex;
+}
+
+int orbx_get_scale_tables(const orbx_extractor* ex, float* scale, float* inv, float* s2, float* inv2, int* quota) {
+    if (!ex) { set_error("null extractor handle"); return ORBX_E_INVALID; }
+    for (int l = 0; l < ex->prm.nlevels; ++l) {
+        if (scale) scale[l] = ex->scale[l];
+        if (inv) inv[l] = ex->invScale[l];
+        if (s2) s2[l] = ex->sigma2[l];
+        if (inv2) inv2[l] = ex->invSigma2[l];
+        if (quota) quota[l] = ex->quota[l];
+    }
+    return ORBX_OK;
+}
+
+int orbx_get_umax(const orbx_extractor* ex, int* umax16) {
+    if (!ex || !umax16) { set_error("null argument"); return ORBX_E_INVALID; }
+    memcpy(umax16, ex->umax, sizeof ex->umax);
+    return ORBX_OK;
+}
+
+void* orbx_extractor_stream(const orbx_extractor* ex) { return ex ? (void*)ex->stream : nullptr; }
+
+int orbx_level_size(const orbx_extractor* ex, int level, int* w, int* h) {
+    if (!ex || level < 0 || level >= ex->prm.nlevels || ex->w == 0) { set_error("orbx_level_size: no geometry yet"); return ORBX_E_INVALID; }
+    if (w) *w = ex->g.lv[level].w;
+    if (h) *h = ex->g.lv[level].h;
+    return ORBX_OK;
+}
+
+int orbx_extract_batch_device(orbx_extractor* ex, const uint8_t* dFrames, int batch, int w, int h, size_t stride,
+                              size_t frameStride, orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dCounts, int* dStatus,
+                              void* stream) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (!dFrames || batch < 1 || w < 1 || h < 1 || stride < (size_t)w || !dKps || !dDesc || cap < 1 || !dCounts) {
+        set_error("orbx_extract_batch_device: bad argument");
+        return ORBX_E_INVALID;
+    }
+    if ((rc = configure(ex, w, h, batch))) return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : ex->stream;
+    return run_pipeline(ex, dFrames, batch, stride, frameStride, dKps, dDesc, cap, dCounts,
+                        dStatus ? dStatus : ex->status.as<int>(), s);
+}
+
+static bool is_pinned(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride, size_t frameStride,
+                       orbx_keypoint* kps, uint8_t* desc, int cap, int* counts) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (batch < 1 || !counts || cap < 0) { set_error("orbx_extract_batch: bad argument"); return ORBX_E_INVALID; }
+    if (!frames || w <= 0 || h <= 0) {  // empty image: the reference returns without touching the outputs (:1542-1543)
+        for (int f = 0; f < batch; ++f) counts[f] = 0;
+        return ORBX_OK;
+    }
+    if (stride < (size_t)w || !kps || !desc || cap < 1) { set_error("orbx_extract_batch: bad argument"); return ORBX_E_INVALID; }
+    if ((rc = configure(ex, w, h, batch))) return rc;
+    cudaStream_t s = ex->stream;
+    const size_t rowBytes = (size_t)w, frameBytes = rowBytes * h;
+    if ((rc = ex->dFrames.ensure(frameBytes * batch + 16))) return rc;
+    if ((rc = ex->dKps.ensure((size_t)batch * cap * sizeof(orbx_keypoint)))) return rc;
+    if ((rc = ex->dDesc.ensure((size_t)batch * cap * 32))) return rc;
+    if ((rc = ex->dCounts.ensure((size_t)batch * 4))) return rc;
+    // H2D: straight from the caller's buffer when it is pinned and tightly packed, else through pinned staging
+    const bool tight = stride == rowBytes && (frameStride == frameBytes || batch == 1);
+    if (tight && is_pinned(frames)) {
+        ORBX_CUDA(cudaMemcpyAsync(ex->dFrames.p, frames, frameBytes * batch, cudaMemcpyHostToDevice, s));
+    } else {
+        if ((rc = ex->hFrames.ensure(frameBytes * batch))) return rc;
+        uint8_t* st = ex->hFrames.as<uint8_t>();
+        for (int f = 0; f < batch; ++f)
+            for (int y = 0; y < h; ++y)
+                memcpy(st + (size_t)f * frameBytes + (size_t)y * rowBytes, frames + (size_t)f * frameStride + (size_t)y * stride, rowBytes);
+        ORBX_CUDA(cudaMemcpyAsync(ex->dFrames.p, st, frameBytes * batch, cudaMemcpyHostToDevice, s));
+    }
+    if ((rc = run_pipeline(ex, ex->dFrames.as<uint8_t>(), batch, rowBytes, frameBytes, ex->dKps.as<orbx_keypoint>(),
+                           ex->dDesc.as<uint8_t>(), cap, ex->dCounts.as<int>(), ex->status.as<int>(), s)))
+        return rc;
+    // D2H
+    const size_t kpBytes = (size_t)batch * cap * sizeof(orbx_keypoint), dBytes = (size_t)batch * cap * 32;
+    const bool direct = is_pinned(kps) && is_pinned(desc) && is_pinned(counts);
+    orbx_keypoint* hk = kps;
+    uint8_t* hd = desc;
+    int* hc = counts;
+    if (!direct) {
+        if ((rc = ex->hKps.ensure(kpBytes))) return rc;
+        if ((rc = ex->hDesc.ensure(dBytes))) return rc;
+        if ((rc = ex->hCounts.ensure((size_t)batch * 4))) return rc;
+        hk = ex->hKps.as<orbx_keypoint>();
+        hd = ex->hDesc.as<uint8_t>();
+        hc = ex->hCounts.as<int>();
+    }
+    ORBX_CUDA(cudaMemcpyAsync(hc, ex->dCounts.p, (size_t)batch * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(hk, ex->dKps.p, kpBytes, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(hd, ex->dDesc.p, dBytes, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(ex->hStatus.p, ex->status.p, 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    if (!direct) {
+        memcpy(counts, hc, (size_t)batch * 4);
+        for (int f = 0; f < batch; ++f) {
+            memcpy(kps + (size_t)f * cap, hk + (size_t)f * cap, (size_t)hc[f] * sizeof(orbx_keypoint));
+            memcpy(desc + (size_t)f * cap * 32, hd + (size_t)f * cap * 32, (size_t)hc[f] * 32);
+        }
+    }
+    const int st = *ex->hStatus.as<int>();
+    if (st != 0) {
+        set_error("orbx_extract: a device buffer overflowed (more than %d keypoints in a FAST cell, or more than cap=%d keypoints in a frame)",
+                  CELL_CAP, cap);
+        return ORBX_E_OVERFLOW;
+    }
+    return ORBX_OK;
+}
+
+int orbx_extract(orbx_extractor* ex, const uint8_t* img, int w, int h, size_t stride, orbx_keypoint* kps, uint8_t* desc, int cap,
+                 int* n) {
+    if (!n) { set_error("orbx_extract: null count pointer"); return ORBX_E_INVALID; }
+    return orbx_extract_batch(ex, img, 1, w, h, stride, (size_t)h * stride, kps, desc, cap, n);
+}
+
+}  // extern "C"
+
+// ---- mvImagePyramid access and stage taps -----------------------------------------------------------------------
+extern "C" {
+
+int orbx_pyramid_level_host(orbx_extractor* ex, int frame, int level, const uint8_t** interior, int* w, int* h, size_t* pitch) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || frame < 0 || frame >= ex->lastBatch) {
+        set_error("orbx_pyramid_level_host: no such frame/level (frame %d level %d, last batch %d)", frame, level, ex->lastBatch);
+        return ORBX_E_INVALID;
+    }
+    const LevelGeom& L = ex->g.lv[level];
+    if (ex->hostLevelSerial[level] != ex->serial || ex->hostLevelFrame[level] != frame) {  // lazy D2H
+        ex->hostLevel[level].resize((size_t)L.planeStride);
+        ORBX_CUDA(cudaMemcpyAsync(ex->hostLevel[level].data(), L.plane + (size_t)frame * L.planeStride, (size_t)L.pitch * L.rows,
+                                  cudaMemcpyDeviceToHost, ex->stream));
+        ORBX_CUDA(cudaStreamSynchronize(ex->stream));
+        ex->hostLevelSerial[level] = ex->serial;
+        ex->hostLevelFrame[level] = frame;
+    }
+    if (interior) *interior = ex->hostLevel[level].data() + (size_t)EDGE * L.pitch + XOFF;
+    if (w) *w = L.w;
+    if (h) *h = L.h;
+    if (pitch) *pitch = (size_t)L.pitch;
+    return ORBX_OK;
+}
+
+int orbx_debug_blurred_level(orbx_extractor* ex, int frame, int level, uint8_t* out) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || frame < 0 || frame >= ex->lastBatch || !out) {
+        set_error("orbx_debug_blurred_level: bad argument");
+        return ORBX_E_INVALID;
+    }
+    const LevelGeom& L = ex->g.lv[level];
+    ORBX_CUDA(cudaMemcpy2DAsync(out, (size_t)L.w, L.blur + (size_t)frame * L.blurStride, (size_t)L.bpitch, (size_t)L.w, (size_t)L.h,
+                                cudaMemcpyDeviceToHost, ex->stream));
+    ORBX_CUDA(cudaStreamSynchronize(ex->stream));
+    return ORBX_OK;
+}
+
+int orbx_debug_candidates(orbx_extractor* ex, int frame, int level, orbx_keypoint* out, int cap, int* n) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || frame < 0 || frame >= ex->lastBatch || !n) {
+        set_error("orbx_debug_candidates: bad argument");
+        return ORBX_E_INVALID;
+    }
+    const FrameGeom& g = ex->g;
+    const LevelGeom& L = g.lv[level];
+    const int nCells = L.nCols * L.nRows;
+    std::vector<int> cnt(std::max(nCells, 1));
+    std::vector<uint32_t> keys((size_t)std::max(nCells, 1) * CELL_CAP);
+    ORBX_CUDA(cudaStreamSynchronize(ex->stream));
+    if (nCells > 0) {
+        ORBX_CUDA(cudaMemcpy(cnt.data(), ex->cellCnt.as<int>() + (size_t)frame * g.nCellsTotal + L.cellBase, (size_t)nCells * 4,
+                             cudaMemcpyDeviceToHost));
+        ORBX_CUDA(cudaMemcpy(keys.data(), ex->cellKeys.as<uint32_t>() + ((size_t)frame * g.nCellsTotal + L.cellBase) * CELL_CAP,
+                             (size_t)nCells * CELL_CAP * 4, cudaMemcpyDeviceToHost));
+    }
+    int m = 0;
+    for (int c = 0; c < nCells; ++c)
+        for (int k = 0; k < std::min(cnt[c], CELL_CAP); ++k, ++m)
+            if (out && m < cap) {
+                const uint32_t key = keys[(size_t)c * CELL_CAP + k];
+                out[m] = orbx_keypoint{(float)key_x(key), (float)key_y(key), 7.f, -1.f, (float)key_resp(key), 0, -1};
+            }
+    *n = m;
+    return ORBX_OK;
+}
+
+int orbx_debug_level_keypoints(orbx_extractor* ex, int frame, int level, orbx_keypoint* out, int cap, int* n) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || frame < 0 || frame >= ex->lastBatch || !n) {
+        set_error("orbx_debug_level_keypoints: bad argument");
+        return ORBX_E_INVALID;
+    }
+    const FrameGeom& g = ex->g;
+    const LevelGeom& L = g.lv[level];
+    int cnt = 0;
+    std::vector<uint32_t> keys(L.quota + 4);
+    std::vector<float> ang(L.quota + 4);
+    ORBX_CUDA(cudaStreamSynchronize(ex->stream));
+    ORBX_CUDA(cudaMemcpy(&cnt, ex->lvlCnt.as<int>() + (size_t)frame * g.nlevels + level, 4, cudaMemcpyDeviceToHost));
+    ORBX_CUDA(cudaMemcpy(keys.data(), ex->lvlKeys.as<uint32_t>() + (size_t)frame * g.slotsTotal + L.slotBase, keys.size() * 4,
+                         cudaMemcpyDeviceToHost));
+    ORBX_CUDA(cudaMemcpy(ang.data(), ex->lvlAngles.as<float>() + (size_t)frame * g.slotsTotal + L.slotBase, ang.size() * 4,
+                         cudaMemcpyDeviceToHost));
+    for (int i = 0; i < cnt && out && i < cap; ++i)
+        out[i] = orbx_keypoint{(float)key_x(keys[i]), (float)key_y(keys[i]), L.size, ang[i], (float)key_resp(keys[i]), level, -1};
+    *n = cnt;
+    return ORBX_OK;
+}
+
+int orbx_debug_distribute(const orbx_keypoint* in, int n, int minX, int maxX, int minY, int maxY, int N, orbx_keypoint* out,
+                          int cap, int* nout) {
+    if (!nout || n < 0 || N < 1 || N > 8000 || maxX <= minX || maxY <= minY || maxX - minX > 4095 || maxY - minY > 4095) {
+        set_error("orbx_debug_distribute: bad argument");
+        return ORBX_E_INVALID;
+    }
+    std::vector<uint32_t> keys(std::max(n, 1));
+    for (int i = 0; i < n; ++i) keys[i] = pack_key((int)in[i].x, (int)in[i].y, (int)in[i].response);
+    DevBuf dIn, dScratch, dOut, dCnt;
+    const int candCap = std::max(n, 32);
+    int rc;
+    if ((rc = dIn.ensure((size_t)candCap * 4)) || (rc = dScratch.ensure((size_t)candCap * 8)) || (rc = dOut.ensure((size_t)(N + 4) * 4)) ||
+        (rc = dCnt.ensure(8)))
+        return rc;
+    ORBX_CUDA(cudaMemcpy(dIn.p, keys.data(), (size_t)n * 4, cudaMemcpyHostToDevice));
+    rc = launch_quadtree_single(dIn.as<uint32_t>(), n, minX, maxX, minY, maxY, N, dScratch.as<uint32_t>(), candCap, dOut.as<uint32_t>(),
+                                dCnt.as<int>(), dCnt.as<int>() + 1, 0);
+    if (!rc) {
+        int cnt = 0;
+        std::vector<uint32_t> res(N + 4);
+        cudaError_t e = cudaMemcpy(&cnt, dCnt.p, 4, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess) e = cudaMemcpy(res.data(), dOut.p, res.size() * 4, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) {
+            set_error("orbx_debug_distribute: %s", cudaGetErrorString(e));
+            rc = ORBX_E_CUDA;
+        } else {
+            for (int i = 0; i < cnt && out && i < cap; ++i)
+                out[i] = orbx_keypoint{(float)key_x(res[i]), (float)key_y(res[i]), 7.f, -1.f, (float)key_resp(res[i]), 0, -1};
+            *nout = cnt;
+        }
+    }
+    dIn.release(); dScratch.release(); dOut.release(); dCnt.release();
+    return rc;
+}
+
+}  // extern "C"
