@@ -1,0 +1,204 @@
+"""orb_slam_cuda_b200 — B200-native ORB-SLAM2 front end (ORBextractor + Hamming matchers + stereo matching).
+
+The product is `liborbx.so` (hand-written sm_100a CUDA kernels behind the C ABI of include/orbx.h) plus the C++
+classes of include/ORBextractor.h / ORBmatcher.h that keep the reference's class surface.  This Python package is a
+thin ctypes binding of the same C ABI, used by the tests and bench.py; it mirrors the reference names
+(ORBextractor.__call__ = operator(), GetScaleFactors, ..., ORBmatcher.DescriptorDistance, SearchForInitialization).
+
+There is no CPU fallback: importing works anywhere, but every compute call fails with OrbxError when the shared
+library is missing or no B200 is present.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liborbx.so")
+
+KP_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("size", "<f4"), ("angle", "<f4"), ("response", "<f4"),
+                     ("octave", "<i4"), ("class_id", "<i4")])
+assert KP_DTYPE.itemsize == 28
+
+ORBX_OK, ORBX_E_INVALID, ORBX_E_CUDA, ORBX_E_OOM, ORBX_E_OVERFLOW = 0, -1, -2, -3, -4
+TH_LOW, TH_HIGH, HISTO_LENGTH = 50, 100, 30  # ORBmatcher constants, reference src/ORBmatcher.cc:37-39
+
+
+class OrbxError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"orbx error {code}: {msg}")
+        self.code = code
+
+
+class Params(C.Structure):
+    _fields_ = [("nfeatures", C.c_int), ("scale_factor", C.c_float), ("nlevels", C.c_int), ("ini_th_fast", C.c_int),
+                ("min_th_fast", C.c_int), ("width", C.c_int), ("height", C.c_int), ("max_batch", C.c_int),
+                ("device", C.c_int)]
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Loads liborbx.so (built in-tree by orb_slam_cuda_b200/build.py).  Fails loudly when it is missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise OrbxError(ORBX_E_CUDA, f"{LIB_PATH} is missing: run `python orb_slam_cuda_b200/build.py` "
+                                         "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        L.orbx_last_error.restype = C.c_char_p
+        L.orbx_kernel_launches.restype = C.c_longlong
+        L.orbx_extractor_stream.restype = C.c_void_p
+        L.orbx_extractor_stream.argtypes = [C.c_void_p]
+        L.orbx_extractor_destroy.argtypes = [C.c_void_p]
+        L.orbx_extractor_destroy.restype = None
+        _lib = L
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise OrbxError(rc, lib().orbx_last_error().decode(errors="replace"))
+
+
+def _p(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return C.c_void_p(a.ctypes.data)
+    return C.c_void_p(int(a))  # raw address (e.g. torch tensor .data_ptr())
+
+
+def kernel_launches() -> int:
+    return int(lib().orbx_kernel_launches())
+
+
+class ORBextractor:
+    """Mirror of ORB_SLAM2::ORBextractor (reference include/ORBextractor.h:76-160).
+
+    ORBextractor(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST[, width, height]);
+    keypoints, descriptors = extractor(image)      # operator()(image, mask, keypoints, descriptors)
+    """
+
+    HARRIS_SCORE, FAST_SCORE = 0, 1
+
+    def __init__(self, nfeatures: int, scaleFactor: float, nlevels: int, iniThFAST: int, minThFAST: int,
+                 width: int = 0, height: int = 0, max_batch: int = 1, device: int = -1):
+        self._h = C.c_void_p()
+        self.nfeatures, self.nlevels, self.scaleFactor = nfeatures, nlevels, float(np.float32(scaleFactor))
+        p = Params(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST, width, height, max_batch, device)
+        _check(lib().orbx_extractor_create(C.byref(p), C.byref(self._h)))
+        n = nlevels
+        self._sf, self._inv, self._s2, self._inv2 = (np.empty(n, np.float32) for _ in range(4))
+        self._quota = np.empty(n, np.int32)
+        _check(lib().orbx_get_scale_tables(self._h, _p(self._sf), _p(self._inv), _p(self._s2), _p(self._inv2), _p(self._quota)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h and _lib is not None:
+            _lib.orbx_extractor_destroy(h)
+            self._h = None
+
+    # ---- accessors (include/ORBextractor.h:94-114) ----
+    def GetLevels(self): return self.nlevels
+    def GetScaleFactor(self): return self.scaleFactor
+    def GetScaleFactors(self): return self._sf.copy()
+    def GetInverseScaleFactors(self): return self._inv.copy()
+    def GetScaleSigmaSquares(self): return self._s2.copy()
+    def GetInverseScaleSigmaSquares(self): return self._inv2.copy()
+    def features_per_level(self): return self._quota.copy()
+
+    def umax(self):
+        u = np.empty(16, np.int32)
+        _check(lib().orbx_get_umax(self._h, _p(u)))
+        return u
+
+    @property
+    def stream(self) -> int:
+        return int(lib().orbx_extractor_stream(self._h) or 0)
+
+    def default_cap(self) -> int:
+        return self.nfeatures + 4 * self.nlevels
+
+    # ---- operator() ----
+    def __call__(self, image: np.ndarray, mask=None):
+        """image: uint8 [h, w] (mask is ignored, like the reference) -> (keypoints KP_DTYPE[n], descriptors uint8[n, 32])"""
+        if image is None or image.size == 0:
+            return np.empty(0, KP_DTYPE), np.empty((0, 32), np.uint8)
+        assert image.dtype == np.uint8 and image.ndim == 2 and image.strides[1] == 1, "CV_8UC1 image expected"
+        h, w = image.shape
+        cap = self.default_cap()
+        kps = np.empty(cap, KP_DTYPE)
+        desc = np.empty((cap, 32), np.uint8)
+        n = C.c_int(0)
+        _check(lib().orbx_extract(self._h, _p(image), w, h, C.c_size_t(image.strides[0]), _p(kps), _p(desc), cap, C.byref(n)))
+        return kps[:n.value].copy(), desc[:n.value].copy()
+
+    def extract_batch(self, frames: np.ndarray, kps=None, desc=None, counts=None, cap=None):
+        """frames: uint8 [B, h, w] host array (pinned or pageable) -> (kps [B, cap], desc [B, cap, 32], counts [B])"""
+        assert frames.dtype == np.uint8 and frames.ndim == 3 and frames.strides[2] == 1
+        b, h, w = frames.shape
+        cap = cap or self.default_cap()
+        kps = np.empty((b, cap), KP_DTYPE) if kps is None else kps
+        desc = np.empty((b, cap, 32), np.uint8) if desc is None else desc
+        counts = np.empty(b, np.int32) if counts is None else counts
+        _check(lib().orbx_extract_batch(self._h, _p(frames), b, w, h, C.c_size_t(frames.strides[1]), C.c_size_t(frames.strides[0]),
+                                        _p(kps), _p(desc), cap, _p(counts)))
+        return kps, desc, counts
+
+    def extract_batch_device(self, d_frames: int, batch: int, w: int, h: int, d_kps: int, d_desc: int, cap: int,
+                             d_counts: int, d_status: int = 0, stream: int = 0, stride: int = 0, frame_stride: int = 0):
+        """All arguments are raw device addresses; asynchronous on `stream` (0 = the extractor's own stream)."""
+        stride = stride or w
+        frame_stride = frame_stride or stride * h
+        _check(lib().orbx_extract_batch_device(self._h, _p(d_frames), batch, w, h, C.c_size_t(stride), C.c_size_t(frame_stride),
+                                               _p(d_kps), _p(d_desc), cap, _p(d_counts), _p(d_status) if d_status else None,
+                                               _p(stream) if stream else None))
+
+    # ---- mvImagePyramid (include/ORBextractor.h:116) ----
+    def level_size(self, level: int):
+        w, h = C.c_int(), C.c_int()
+        _check(lib().orbx_level_size(self._h, level, C.byref(w), C.byref(h)))
+        return w.value, h.value
+
+    def image_pyramid_level(self, level: int, frame: int = 0, padded: bool = False) -> np.ndarray:
+        """Level `level` of the last extracted frame; padded=True returns the (h+38) x (w+38) parent."""
+        ptr, w, h, pitch = C.c_void_p(), C.c_int(), C.c_int(), C.c_size_t()
+        _check(lib().orbx_pyramid_level_host(self._h, frame, level, C.byref(ptr), C.byref(w), C.byref(h), C.byref(pitch)))
+        e = 19
+        base = ptr.value - e * pitch.value - e
+        buf = (C.c_uint8 * (pitch.value * (h.value + 2 * e))).from_address(base)
+        full = np.frombuffer(buf, np.uint8).reshape(h.value + 2 * e, pitch.value)[:, :w.value + 2 * e]
+        return full.copy() if padded else full[e:e + h.value, e:e + w.value].copy()
+
+    # ---- stage taps (parity tests) ----
+    def debug_blurred_level(self, level: int, frame: int = 0) -> np.ndarray:
+        w, h = self.level_size(level)
+        out = np.empty((h, w), np.uint8)
+        _check(lib().orbx_debug_blurred_level(self._h, frame, level, _p(out)))
+        return out
+
+    def _debug_kps(self, fn, level, frame):
+        n = C.c_int(0)
+        _check(fn(self._h, frame, level, None, 0, C.byref(n)))
+        out = np.empty(max(n.value, 1), KP_DTYPE)
+        _check(fn(self._h, frame, level, _p(out), out.size, C.byref(n)))
+        return out[:n.value].copy()
+
+    def debug_candidates(self, level: int, frame: int = 0) -> np.ndarray:
+        return self._debug_kps(lib().orbx_debug_candidates, level, frame)
+
+    def debug_level_keypoints(self, level: int, frame: int = 0) -> np.ndarray:
+        return self._debug_kps(lib().orbx_debug_level_keypoints, level, frame)
+
+
+def distribute_octtree(keys: np.ndarray, minX: int, maxX: int, minY: int, maxY: int, N: int) -> np.ndarray:
+    """Stand-alone DistributeOctTree (reference src/ORBextractor.cc:889-1120) on the device."""
+    keys = np.ascontiguousarray(keys, dtype=KP_DTYPE)
+    out = np.empty(N + 8, KP_DTYPE)
+    n = C.c_int(0)
+    _check(lib().orbx_debug_distribute(_p(keys), keys.size, minX, maxX, minY, maxY, N, _p(out), out.size, C.byref(n)))
+    return out[:n.value].copy()

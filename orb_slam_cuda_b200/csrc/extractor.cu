@@ -14,6 +14,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -110,9 +111,10 @@ struct orbx_extractor {
     int batchCap = 0;        // frames the scratch holds
     int outCap = 0;          // keypoints per frame the output staging holds
     FrameGeom g{};
+    TmaMaps fastMaps{}, blurMaps{};
     std::vector<int> areaFast;
     DevBuf planes[ORBX_MAX_LEVELS], blurs[ORBX_MAX_LEVELS], xtab[ORBX_MAX_LEVELS], ytab[ORBX_MAX_LEVELS];
-    DevBuf cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, lvlAngles, status, maps, dFrames, dKps, dDesc, dCounts;
+    DevBuf cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, lvlAngles, status, dFrames, dKps, dDesc, dCounts;
     PinBuf hFrames, hKps, hDesc, hCounts, hStatus;
     // host copies of pyramid levels for mvImagePyramid readers
     std::vector<uint8_t> hostLevel[ORBX_MAX_LEVELS];
@@ -299,7 +301,7 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
     g.slotsTotal = slotBase;
     g.qtFrameStride = qtBase;
     g.blurTilesTotal = tileBase;
-    g.fastBoxW = (int)round_up(std::max(maxWCell, 1) + 6, 16);
+    g.fastBoxW = (int)round_up(std::max(maxWCell, 1) + 6 + 15, 16);  // + alignment slack of the box origin
     g.fastBoxH = std::max(maxHCell, 1) + 6;
     if (g.fastBoxW > 256 || g.fastBoxH > 256 || g.fastBoxW * g.fastBoxH > 60000) {
         set_error("FAST cell window %d x %d exceeds the TMA box limit", g.fastBoxW, g.fastBoxH);
@@ -340,15 +342,12 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
     if ((rc = ex->lvlAngles.ensure((size_t)batch * g.slotsTotal * 4))) return rc;
     if ((rc = ex->status.ensure(256))) return rc;
     if ((rc = ex->hStatus.ensure(64))) return rc;
-    // TMA descriptors: [0..nl) FAST windows, [nl..2nl) blur windows
-    std::vector<CUtensorMap> maps(2 * nl);
+    // TMA descriptors of the FAST windows and the blur windows
     for (int l = 0; l < nl; ++l) {
         const LevelGeom& L = g.lv[l];
-        if ((rc = make_plane_map(&maps[l], L.plane, L.pitch, L.rows, L.planeStride, batch, g.fastBoxW, g.fastBoxH))) return rc;
-        if ((rc = make_plane_map(&maps[nl + l], L.plane, L.pitch, L.rows, L.planeStride, batch, 144, 38))) return rc;
+        if ((rc = make_plane_map(&ex->fastMaps.m[l], L.plane, L.pitch, L.rows, L.planeStride, batch, g.fastBoxW, g.fastBoxH))) return rc;
+        if ((rc = make_plane_map(&ex->blurMaps.m[l], L.plane, L.pitch, L.rows, L.planeStride, batch, 160, 38))) return rc;
     }
-    if ((rc = ex->maps.ensure(maps.size() * sizeof(CUtensorMap)))) return rc;
-    ORBX_CUDA(cudaMemcpy(ex->maps.p, maps.data(), maps.size() * sizeof(CUtensorMap), cudaMemcpyHostToDevice));
     ex->w = w;
     ex->h = h;
     ex->batchCap = batch;
@@ -357,25 +356,42 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
 }
 
 // ---- the launch sequence of operator() (src/ORBextractor.cc:1701-1809) on device-resident buffers ---------------
+static int stage_sync(const char* stage, cudaStream_t s) {  // ORBX_DEBUG_SYNC=1: attribute device faults to a stage
+    static const bool on = getenv("ORBX_DEBUG_SYNC") != nullptr;
+    if (!on) return ORBX_OK;
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) {
+        set_error("stage '%s' failed: %s", stage, cudaGetErrorString(e));
+        return ORBX_E_CUDA;
+    }
+    return ORBX_OK;
+}
+
 static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
                         orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dCounts, int* dStatus, cudaStream_t s) {
     const FrameGeom& g = ex->g;
     const int nl = g.nlevels;
     int rc;
     ORBX_CUDA(cudaMemsetAsync(dStatus, 0, sizeof(int), s));
+    if ((rc = stage_sync("input copy", s))) return rc;
     if ((rc = launch_pyramid_base(g, dFrames, batch, stride, frameStride, s))) return rc;                 // ComputePyramid
+    if ((rc = stage_sync("Pyramid/Resize level 0", s))) return rc;
     for (int l = 1; l < nl; ++l)
         if ((rc = launch_pyramid_level(g, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->areaFast[l], batch, s)))
             return rc;
-    const CUtensorMap* maps = ex->maps.as<CUtensorMap>();
-    if ((rc = launch_fast(g, maps, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), dStatus, s))) return rc;
+    if ((rc = stage_sync("Pyramid/Resize", s))) return rc;
+    if ((rc = launch_fast(g, ex->fastMaps, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), dStatus, s))) return rc;
+    if ((rc = stage_sync("FAST+Grid", s))) return rc;
     if ((rc = launch_quadtree(g, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), ex->qtScratch.as<uint32_t>(),
                               ex->lvlCnt.as<int>(), ex->lvlKeys.as<uint32_t>(), dStatus, s)))
         return rc;
-    if ((rc = launch_blur(g, maps + nl, batch, s))) return rc;                                            // GaussianBlur
+    if ((rc = stage_sync("Make quadtree", s))) return rc;
+    if ((rc = launch_blur(g, ex->blurMaps, batch, s))) return rc;                                            // GaussianBlur
+    if ((rc = stage_sync("Gaussian Blur", s))) return rc;
     if ((rc = launch_describe(g, batch, ex->lvlCnt.as<int>(), ex->lvlKeys.as<uint32_t>(), dKps, dDesc, cap, dCounts,
                               ex->lvlAngles.as<float>(), dStatus, s)))
         return rc;
+    if ((rc = stage_sync("Compute angle + ORB descriptor", s))) return rc;
     ex->serial++;
     ex->lastBatch = batch;
     return ORBX_OK;
@@ -454,7 +470,7 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
         ex->planes[l].release(); ex->blurs[l].release(); ex->xtab[l].release(); ex->ytab[l].release();
     }
     for (DevBuf* b : {&ex->cellCnt, &ex->cellKeys, &ex->qtScratch, &ex->lvlCnt, &ex->lvlKeys, &ex->lvlAngles, &ex->status,
-                      &ex->maps, &ex->dFrames, &ex->dKps, &ex->dDesc, &ex->dCounts})
+                      &ex->dFrames, &ex->dKps, &ex->dDesc, &ex->dCounts})
         b->release();
     for (PinBuf* b : {&ex->hFrames, &ex->hKps, &ex->hDesc, &ex->hCounts, &ex->hStatus}) b->release();
     delete ex;

@@ -2,8 +2,9 @@
 // (reference call site src/ORBextractor.cc:1746-1747).  OpenCV's CV_8U path is a bit-exact 8.8 fixed-point
 // separable filter: kernel [18,34,48,56,48,34,18]/256, rows then columns, result = (sum + 32768) >> 16.
 //
-// One CTA produces a 128 x 32 output tile.  The 144 x 38 input window (3-px halo, width rounded up to the 16-byte
-// TMA granule) is staged with one TMA box load from the padded plane — the plane's 19-px border IS the reflect-101
+// One CTA produces a 128 x 32 output tile.  The 134 x 38 input window (3-px halo) is staged with one TMA box load of
+// 160 x 38 bytes from the padded plane (TMA needs the box origin on a 16-byte boundary of the row: measured on B200,
+// tools/tma_probe.cu; the window starts at byte 13 of the box) — the plane's 19-px border IS the reflect-101
 // extension of the level, so no border logic is needed here.  The horizontal pass writes 16-bit partial sums
 // (<= 255*256) to shared memory, the vertical pass emits 4 bytes per thread per row with 32-bit stores.
 //
@@ -13,10 +14,10 @@
 
 namespace orbx {
 
-constexpr int BLUR_TW = 128, BLUR_TH = 32, BLUR_BW = 144, BLUR_BH = 38, BLUR_THREADS = 256;
+constexpr int BLUR_TW = 128, BLUR_TH = 32, BLUR_BW = 160, BLUR_BH = 38, BLUR_THREADS = 256;
 
 __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ FrameGeom g,
-                                                        const CUtensorMap* __restrict__ maps) {
+                                                        const __grid_constant__ TmaMaps maps) {
     __shared__ __align__(128) uint8_t tile[BLUR_BH * BLUR_BW];
     __shared__ __align__(16) uint16_t hsum[BLUR_BH * BLUR_TW];
     __shared__ __align__(8) uint64_t bar;
@@ -34,23 +35,22 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
     __syncthreads();
     if (tid == 0) {
         mbar_expect_tx(&bar, BLUR_BH * BLUR_BW);
-        tma_load_3d(tile, maps + level, XOFF + x0 - 3, EDGE + y0 - 3, f, &bar);
+        tma_load_3d(tile, &maps.m[level], XOFF + x0 - 16, EDGE + y0 - 3, f, &bar);  // window = box columns 13..146
     }
     mbar_wait(&bar, 0);
 
     // horizontal pass: item = (row, group of 4 output columns)
     for (int it = tid; it < BLUR_BH * (BLUR_TW / 4); it += BLUR_THREADS) {
         const int r = it / (BLUR_TW / 4), q = it - r * (BLUR_TW / 4);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(tile + r * BLUR_BW + 4 * q);
-        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(tile + r * BLUR_BW + 12 + 4 * q);
+        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];  // window bytes 4q..4q+9 are bytes 1..10 of these words
         int p[10];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            p[k] = (w0 >> (8 * k)) & 0xFF;
-            p[4 + k] = (w1 >> (8 * k)) & 0xFF;
-        }
-        p[8] = w2 & 0xFF;
-        p[9] = (w2 >> 8) & 0xFF;
+        for (int k = 0; k < 3; ++k) p[k] = (w0 >> (8 * (k + 1))) & 0xFF;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) p[3 + k] = (w1 >> (8 * k)) & 0xFF;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) p[7 + k] = (w2 >> (8 * k)) & 0xFF;
         uint32_t s[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k)
@@ -86,9 +86,9 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
     }
 }
 
-int launch_blur(const FrameGeom& g, const CUtensorMap* dMaps, int batch, cudaStream_t s) {
+int launch_blur(const FrameGeom& g, const TmaMaps& maps, int batch, cudaStream_t s) {
     dim3 grid(g.blurTilesTotal, batch);
-    k_blur7<<<grid, BLUR_THREADS, 0, s>>>(g, dMaps);
+    k_blur7<<<grid, BLUR_THREADS, 0, s>>>(g, maps);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -2,7 +2,7 @@
 // suppression (reference src/ORBextractor.cc:1122-1149 grid set-up, :1256-1299 per-cell cv::FAST calls).
 //
 // One CTA per (cell, frame).  The cell window [ini, ini + cell + 6) (clipped to maxBorder, :1258-1275) is staged
-// into shared memory by one TMA box load from the padded plane; then, at threshold t = iniThFAST:
+// into shared memory by one TMA box load from the padded plane (box origin rounded down to 16 bytes); then, at threshold t = iniThFAST:
 //   A. every detectable pixel (window minus cv::FAST's 3-px rim) takes the 4-point antipodal quick test; survivors
 //      are appended to a shared list (warp-aggregated atomics),
 //   B. survivors run the full 16-point segment test (bit-mask run detection) and, for corners, the OpenCV
@@ -49,7 +49,7 @@ __device__ __forceinline__ int best_arc_min(const int (&e)[16]) {
 }
 
 __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_constant__ FrameGeom g,
-                                                              const CUtensorMap* __restrict__ maps,
+                                                              const __grid_constant__ TmaMaps maps,
                                                               int* __restrict__ cellCnt, uint32_t* __restrict__ cellKeys,
                                                               int* __restrict__ dStatus) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -86,9 +86,10 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
     __syncthreads();
     if (tid == 0) {
         mbar_expect_tx(bar, (uint32_t)TN);
-        tma_load_3d(tile, maps + level, XOFF + iniX, EDGE + iniY, f, bar);
+        tma_load_3d(tile, &maps.m[level], (XOFF + iniX) & ~15, EDGE + iniY, f, bar);  // box origin must be 16-byte aligned
     }
     const int dW = ww - 6, dH = wh - 6, npx = dW * dH;
+    const int xo = (XOFF + iniX) & 15;  // window column 0 inside the box
     mbar_wait(bar, 0);
 
     int n2 = 0;
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
             int pos = 0;
             if (p < npx) {
                 const int y = p / dW, x = p - y * dW;
-                pos = (y + 3) * TW + x + 3;
+                pos = (y + 3) * TW + x + 3 + xo;
                 const int v = tile[pos];
                 const int r0 = tile[pos + 3 * TW], r8 = tile[pos - 3 * TW], r4 = tile[pos + 3], r12 = tile[pos - 3];
                 const int hi = v + t, lo = v - t;
@@ -173,14 +174,14 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
         for (int j = 0; j < n2; ++j) rank += (list2[j] < e) ? 1 : 0;
         const int pos = (int)(e >> 8);
         const int y = pos / TW, x = pos - y * TW;
-        outKeys[rank] = pack_key(x + cj * L.wCell, y + ci * L.hCell, (int)(e & 0xFFu));
+        outKeys[rank] = pack_key(x - xo + cj * L.wCell, y + ci * L.hCell, (int)(e & 0xFFu));
     }
     if (tid == 0) *outCnt = n2;
 }
 
 size_t fast_smem_bytes(const FrameGeom& g) { return (size_t)4 * g.fastBoxW * g.fastBoxH + CELL_CAP * 4 + 8 + 16; }
 
-int launch_fast(const FrameGeom& g, const CUtensorMap* dMaps, int batch, int* cellCnt, uint32_t* cellKeys, int* dStatus,
+int launch_fast(const FrameGeom& g, const TmaMaps& maps, int batch, int* cellCnt, uint32_t* cellKeys, int* dStatus,
                 cudaStream_t s) {
     const size_t smem = fast_smem_bytes(g);
     static size_t configured = 0;
@@ -189,7 +190,7 @@ int launch_fast(const FrameGeom& g, const CUtensorMap* dMaps, int batch, int* ce
         configured = smem;
     }
     dim3 grid(g.nCellsTotal, batch);
-    k_fast_cells<<<grid, FAST_THREADS, smem, s>>>(g, dMaps, cellCnt, cellKeys, dStatus);
+    k_fast_cells<<<grid, FAST_THREADS, smem, s>>>(g, maps, cellCnt, cellKeys, dStatus);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -67,6 +67,10 @@ struct FrameGeom {
     LevelGeom lv[ORBX_MAX_LEVELS];
 };
 
+struct alignas(64) TmaMaps {  // one descriptor per level, passed to kernels as a __grid_constant__ parameter
+    CUtensorMap m[ORBX_MAX_LEVELS];
+};
+
 struct ResizeTab {  // one entry per destination column / row: source index pair + 11-bit coefficients
     uint16_t s0, s1;
     int16_t c0, c1;
@@ -91,7 +95,7 @@ int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, s
 int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, const ResizeTab* ytab, int areaFast,
                          int batch, cudaStream_t s);
 // per-cell FAST-9 + threshold fallback + NMS
-int launch_fast(const FrameGeom& g, const CUtensorMap* dMaps, int batch, int* cellCnt, uint32_t* cellKeys, int* dStatus,
+int launch_fast(const FrameGeom& g, const TmaMaps& maps, int batch, int* cellCnt, uint32_t* cellKeys, int* dStatus,
                 cudaStream_t s);
 // DistributeOctTree per (frame, level)
 int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uint32_t* cellKeys, uint32_t* qtScratch,
@@ -101,7 +105,7 @@ int quadtree_smem_bytes(int maxQuota);
 int launch_quadtree_single(const uint32_t* dKeysIn, int n, int minX, int maxX, int minY, int maxY, int N,
                            uint32_t* dScratch, int candCap, uint32_t* dOut, int* dCount, int* dStatus, cudaStream_t s);
 // 7x7 sigma=2 fixed-point GaussianBlur of every level
-int launch_blur(const FrameGeom& g, const CUtensorMap* dMaps, int batch, cudaStream_t s);
+int launch_blur(const FrameGeom& g, const TmaMaps& maps, int batch, cudaStream_t s);
 // IC_Angle + steered BRIEF + scale-back + level-major compaction into the caller's output
 int launch_describe(const FrameGeom& g, int batch, const int* lvlCnt, const uint32_t* lvlKeys, orbx_keypoint* dKps,
                     uint8_t* dDesc, int cap, int* dCounts, float* dLvlAngles, int* dStatus, cudaStream_t s);

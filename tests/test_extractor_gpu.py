@@ -1,0 +1,146 @@
+"""Parity of the CUDA extractor (through the C ABI) with the CPU oracle, stage by stage and end to end.
+
+Bars (BASELINE.json north_star): pyramid, blurred levels, keypoint sets (x, y, octave, response) and descriptors
+bit-exact; angles bit-exact (tolerance 0, stated here), all on the same seeded synthetic frames.
+"""
+import numpy as np
+import pytest
+
+from oracle import oracle_lib as O
+from orb_slam_cuda_b200 import synth
+import orb_slam_cuda_b200 as X
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = {  # reference YAMLs: Examples/Monocular/KITTI00-02.yaml, TUM1.yaml, Examples/Stereo/EuRoC.yaml
+    "kitti": dict(nfeatures=2000, sf=1.2, nl=8, ini=20, mn=7),
+    "tum": dict(nfeatures=1000, sf=1.2, nl=8, ini=20, mn=7),
+    "euroc": dict(nfeatures=1200, sf=1.2, nl=8, ini=20, mn=7),
+}
+
+
+def make(kind):
+    c = CONFIGS[kind]
+    return (X.ORBextractor(c["nfeatures"], c["sf"], c["nl"], c["ini"], c["mn"]),
+            O.Extractor(c["nfeatures"], c["sf"], c["nl"], c["ini"], c["mn"]))
+
+
+def kp_tuple(k):
+    return [(float(a["x"]), float(a["y"]), float(a["response"])) for a in k]
+
+
+@pytest.fixture(scope="module", params=["kitti", "tum", "euroc"])
+def run(request):
+    kind = request.param
+    gx, ox = make(kind)
+    img = synth.frame(kind, 3)
+    kps, desc = gx(img)
+    okps, odesc = ox.extract(img)
+    return dict(kind=kind, gx=gx, ox=ox, img=img, kps=kps, desc=desc, okps=okps, odesc=odesc)
+
+
+def test_tables(run):
+    t = run["ox"].tables()
+    gx = run["gx"]
+    assert np.array_equal(gx.GetScaleFactors(), t["scale"])
+    assert np.array_equal(gx.GetInverseScaleFactors(), t["inv_scale"])
+    assert np.array_equal(gx.GetScaleSigmaSquares(), t["sigma2"])
+    assert np.array_equal(gx.GetInverseScaleSigmaSquares(), t["inv_sigma2"])
+    assert np.array_equal(gx.features_per_level(), t["quota"])
+    assert np.array_equal(gx.umax(), t["umax"])
+
+
+def test_pyramid_bit_exact(run):
+    gx, ox = run["gx"], run["ox"]
+    for l in range(gx.nlevels):
+        assert gx.level_size(l) == ox.level_size(l)
+        a, b = gx.image_pyramid_level(l, padded=True), ox.level_padded(l)
+        assert a.shape == b.shape
+        assert np.array_equal(a, b), f"level {l}: {(a != b).sum()} of {a.size} padded pixels differ"
+
+
+def test_blur_bit_exact(run):
+    gx, ox = run["gx"], run["ox"]
+    for l in range(gx.nlevels):
+        b = ox.level_blurred(l)
+        if b is None:
+            continue
+        a = gx.debug_blurred_level(l)
+        assert np.array_equal(a, b), f"level {l}: {(a != b).sum()} blurred pixels differ"
+
+
+def test_fast_candidates(run):
+    gx, ox = run["gx"], run["ox"]
+    for l in range(gx.nlevels):
+        a, b = gx.debug_candidates(l), ox.level_candidates(l)
+        assert kp_tuple(a) == kp_tuple(b), f"level {l}: {len(a)} vs {len(b)} candidates"
+
+
+def test_level_keypoints_and_angles(run):
+    gx, ox = run["gx"], run["ox"]
+    for l in range(gx.nlevels):
+        a, b = gx.debug_level_keypoints(l), ox.level_keypoints(l)
+        assert kp_tuple(a) == kp_tuple(b), f"level {l}: quadtree output differs ({len(a)} vs {len(b)})"
+        assert np.array_equal(a["angle"].view(np.uint32), b["angle"].view(np.uint32)), f"level {l}: angle bits differ"
+        assert np.array_equal(a["size"], b["size"]) and np.array_equal(a["octave"], b["octave"])
+
+
+def test_extract_bit_exact(run):
+    k, d, ok, od = run["kps"], run["desc"], run["okps"], run["odesc"]
+    assert len(k) == len(ok)
+    for f in KPF:
+        assert np.array_equal(k[f].view(np.uint32), ok[f].view(np.uint32)), f"field {f} differs"
+    assert np.array_equal(d, od), f"{np.unpackbits(d ^ od).sum()} descriptor bits differ"
+
+
+KPF = ["x", "y", "size", "angle", "response", "octave", "class_id"]
+
+
+def test_batch_equals_single():
+    gx, ox = make("tum")
+    frames = synth.frame_batch("tum", 5, pool=5, first=10)
+    kps, desc, counts = gx.extract_batch(frames)
+    for f in range(frames.shape[0]):
+        ok, od = ox.extract(frames[f])
+        n = counts[f]
+        assert n == len(ok)
+        assert np.array_equal(kps[f, :n].view(np.uint8), ok.view(np.uint8))
+        assert np.array_equal(desc[f, :n], od)
+
+
+def test_strided_input_and_empty():
+    gx, ox = make("tum")
+    big = np.zeros((500, 700), np.uint8)
+    img = synth.frame("tum", 20)
+    big[5:485, 30:670] = img
+    k, d = gx(big[5:485, 30:670])
+    ok, od = ox.extract(img)
+    assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od)
+    k, d = gx(np.empty((0, 0), np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+
+
+def test_small_and_odd_sizes():
+    for (h, w, nf) in [(120, 160, 300), (97, 211, 200), (240, 320, 500)]:
+        gx, ox = X.ORBextractor(nf, 1.2, 8, 20, 7), O.Extractor(nf, 1.2, 8, 20, 7)
+        img = synth.textured_frame(4242 + h, h, w)
+        k, d = gx(img)
+        ok, od = ox.extract(img)
+        assert len(k) == len(ok), (h, w)
+        assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od), (h, w)
+
+
+def test_quadtree_standalone_random():
+    rng = np.random.default_rng(7)
+    for trial in range(40):
+        W, H = int(rng.integers(60, 1300)), int(rng.integers(60, 480))
+        n, N = int(rng.integers(1, 3000)), int(rng.integers(1, 500))
+        pts = np.unique(np.stack([rng.integers(0, H, n), rng.integers(0, W, n)], 1), axis=0)
+        if trial % 2:
+            rng.shuffle(pts)
+        keys = np.zeros(len(pts), X.KP_DTYPE)
+        keys["x"], keys["y"] = pts[:, 1], pts[:, 0]
+        keys["response"] = rng.integers(7, 60, len(pts))
+        a = X.distribute_octtree(keys, 16, 16 + W, 16, 16 + H, N)
+        b = O.distribute(keys, 16, 16 + W, 16, 16 + H, N)
+        assert kp_tuple(a) == kp_tuple(b), f"trial {trial}: W={W} H={H} n={len(pts)} N={N}: {len(a)} vs {len(b)}"
