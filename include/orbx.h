@@ -69,6 +69,14 @@ int orbx_get_umax(const orbx_extractor* ex, int* umax16);
 /* the stream the handle launches on (cudaStream_t as void*) */
 void* orbx_extractor_stream(const orbx_extractor* ex);
 
+/* ---- per-stage timing (the reference's GetTime rows, src/ORBextractor.cc:1876-1904; stage names as at :1841,
+ * :1131, :892, :1737, :1331/:1753) ----  With timing on, CUDA events bracket every stage of the next extract call
+ * on the stream it runs on; orbx_extractor_stage_ms synchronises and returns the milliseconds of the last call. */
+#define ORBX_NUM_STAGES 5
+int orbx_extractor_enable_timing(orbx_extractor* ex, int on);
+int orbx_extractor_stage_ms(orbx_extractor* ex, float* ms /* ORBX_NUM_STAGES */);
+const char* orbx_stage_name(int stage);
+
 /* ---- ORBextractor::operator()  (src/ORBextractor.cc:1538-1548, 1701-1815, CPU path semantics) ----
  * One 8-bit frame in host memory -> keypoints (level-major, level-0 coordinates) + n x 32 descriptor bytes.
  * cap = capacity of kps/desc in keypoints; *n = number produced (<= cap, else ORBX_E_OVERFLOW).

@@ -123,6 +123,16 @@ class ORBextractor:
     def default_cap(self) -> int:
         return self.nfeatures + 4 * self.nlevels
 
+    # ---- per-stage timing (the reference's GetTime rows) ----
+    def enable_timing(self, on: bool = True):
+        _check(lib().orbx_extractor_enable_timing(self._h, int(on)))
+
+    def stage_ms(self) -> dict:
+        ms = np.zeros(5, np.float32)
+        _check(lib().orbx_extractor_stage_ms(self._h, _p(ms)))
+        lib().orbx_stage_name.restype = C.c_char_p
+        return {lib().orbx_stage_name(i).decode(): float(ms[i]) for i in range(5)}
+
     # ---- operator() ----
     def __call__(self, image: np.ndarray, mask=None):
         """image: uint8 [h, w] (mask is ignored, like the reference) -> (keypoints KP_DTYPE[n], descriptors uint8[n, 32])"""

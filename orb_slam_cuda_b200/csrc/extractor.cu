@@ -121,6 +121,9 @@ struct orbx_extractor {
     int hostLevelFrame[ORBX_MAX_LEVELS];
     long long hostLevelSerial[ORBX_MAX_LEVELS];
     long long serial = 0;    // bumped by every extract call
+    bool timing = false;
+    bool timed = false;      // the last call recorded events
+    cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
     int lastBatch = 0;
 };
 
@@ -374,24 +377,32 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     int rc;
     ORBX_CUDA(cudaMemsetAsync(dStatus, 0, sizeof(int), s));
     if ((rc = stage_sync("input copy", s))) return rc;
+    const bool tm = ex->timing;
+    ex->timed = tm;
+    if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[0], s));
     if ((rc = launch_pyramid_base(g, dFrames, batch, stride, frameStride, s))) return rc;                 // ComputePyramid
     if ((rc = stage_sync("Pyramid/Resize level 0", s))) return rc;
     for (int l = 1; l < nl; ++l)
         if ((rc = launch_pyramid_level(g, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->areaFast[l], batch, s)))
             return rc;
     if ((rc = stage_sync("Pyramid/Resize", s))) return rc;
+    if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
     if ((rc = launch_fast(g, ex->fastMaps, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), dStatus, s))) return rc;
     if ((rc = stage_sync("FAST+Grid", s))) return rc;
+    if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
     if ((rc = launch_quadtree(g, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), ex->qtScratch.as<uint32_t>(),
                               ex->lvlCnt.as<int>(), ex->lvlKeys.as<uint32_t>(), dStatus, s)))
         return rc;
     if ((rc = stage_sync("Make quadtree", s))) return rc;
+    if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
     if ((rc = launch_blur(g, ex->blurMaps, batch, s))) return rc;                                            // GaussianBlur
     if ((rc = stage_sync("Gaussian Blur", s))) return rc;
+    if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
     if ((rc = launch_describe(g, batch, ex->lvlCnt.as<int>(), ex->lvlKeys.as<uint32_t>(), dKps, dDesc, cap, dCounts,
                               ex->lvlAngles.as<float>(), dStatus, s)))
         return rc;
     if ((rc = stage_sync("Compute angle + ORB descriptor", s))) return rc;
+    if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
     ex->serial++;
     ex->lastBatch = batch;
     return ORBX_OK;
@@ -466,6 +477,8 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
         cudaStreamSynchronize(ex->stream);
         cudaStreamDestroy(ex->stream);
     }
+    for (cudaEvent_t e : ex->ev)
+        if (e) cudaEventDestroy(e);
     for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
         ex->planes[l].release(); ex->blurs[l].release(); ex->xtab[l].release(); ex->ytab[l].release();
     }
@@ -486,6 +499,31 @@ int orbx_get_scale_tables(const orbx_extractor* ex, float* scale, float* inv, fl
         if (quota) quota[l] = ex->quota[l];
     }
     return ORBX_OK;
+}
+
+int orbx_extractor_enable_timing(orbx_extractor* ex, int on) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (on && !ex->ev[0])
+        for (int i = 0; i <= ORBX_NUM_STAGES; ++i) ORBX_CUDA(cudaEventCreate(&ex->ev[i]));
+    ex->timing = on != 0;
+    ex->timed = false;
+    return ORBX_OK;
+}
+
+int orbx_extractor_stage_ms(orbx_extractor* ex, float* ms) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (!ms || !ex->timed) { set_error("orbx_extractor_stage_ms: the last extract call was not timed"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaEventSynchronize(ex->ev[ORBX_NUM_STAGES]));
+    for (int i = 0; i < ORBX_NUM_STAGES; ++i) ORBX_CUDA(cudaEventElapsedTime(&ms[i], ex->ev[i], ex->ev[i + 1]));
+    return ORBX_OK;
+}
+
+const char* orbx_stage_name(int stage) {
+    static const char* names[ORBX_NUM_STAGES] = {"Pyramid/Resize", "FAST+Grid", "Make quadtree", "Gaussian Blur",
+                                                 "Compute angle + ORB descriptor + Compute scale"};
+    return stage >= 0 && stage < ORBX_NUM_STAGES ? names[stage] : "";
 }
 
 int orbx_get_umax(const orbx_extractor* ex, int* umax16) {
