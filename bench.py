@@ -189,7 +189,10 @@ def run_ours(args):
     d_desc = torch.empty((B, cap, 32), dtype=torch.uint8, device="cuda")
     d_counts = torch.empty(B, dtype=torch.int32, device="cuda")
     d_status = torch.zeros(1, dtype=torch.int32, device="cuda")
-    stream = torch.cuda.current_stream().cuda_stream
+    tstream = torch.cuda.Stream()  # a real (non-default) stream: CUDA events below are recorded on it
+    torch.cuda.set_stream(tstream)
+    stream = tstream.cuda_stream
+    assert stream != 0
 
     def step_device():
         ex.extract_batch_device(d_frames.data_ptr(), B, w, h, d_kps.data_ptr(), d_desc.data_ptr(), cap, d_counts.data_ptr(),

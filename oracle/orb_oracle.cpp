@@ -146,7 +146,13 @@ void fast9_16(const uint8_t* img, int w, int h, size_t step, int threshold, bool
     std::vector<int> score((size_t)w * h, 0);
     for (int y = 3; y < h - 3; ++y)
         for (int x = 3; x < w - 3; ++x) {
-            int s = fast_score_at(img + (size_t)y * step + x, off, threshold);
+            const uint8_t* p = img + (size_t)y * step + x;
+            // quick rejection (same as OpenCV's first tests): an arc of 9 contains one pixel of every antipodal pair
+            const int v = p[0], hi = v + threshold, lo = v - threshold;
+            const int r0 = p[off[0]], r8 = p[off[8]], r4 = p[off[4]], r12 = p[off[12]];
+            const bool br = (r0 > hi || r8 > hi) && (r4 > hi || r12 > hi);
+            const bool dk = (r0 < lo || r8 < lo) && (r4 < lo || r12 < lo);
+            int s = (br || dk) ? fast_score_at(p, off, threshold) : -1;
             score[(size_t)y * w + x] = s < 0 ? 0 : (nms ? s : 1);
             if (!nms && s >= 0) out.push_back({(float)x, (float)y, 7.f, -1.f, 0.f, 0, -1});
         }
@@ -175,15 +181,20 @@ void gaussian7x7_s2(const uint8_t* src, int w, int h, size_t sstep, uint8_t* dst
         const uint8_t* s = src + (size_t)y * sstep;
         for (int x = 0; x < w; ++x) {
             int acc = 0;
-            for (int k = 0; k < 7; ++k) acc += K[k] * s[reflect101(x + k - 3, w)];
+            if (x >= 3 && x < w - 3)
+                for (int k = 0; k < 7; ++k) acc += K[k] * s[x + k - 3];
+            else
+                for (int k = 0; k < 7; ++k) acc += K[k] * s[reflect101(x + k - 3, w)];
             tmp[(size_t)y * w + x] = (uint16_t)acc;
         }
     }
     for (int y = 0; y < h; ++y) {
         uint8_t* d = dst + (size_t)y * dstep;
+        const uint16_t* r[7];
+        for (int k = 0; k < 7; ++k) r[k] = tmp.data() + (size_t)reflect101(y + k - 3, h) * w;
         for (int x = 0; x < w; ++x) {
             uint32_t acc = 0;
-            for (int k = 0; k < 7; ++k) acc += (uint32_t)K[k] * tmp[(size_t)reflect101(y + k - 3, h) * w + x];
+            for (int k = 0; k < 7; ++k) acc += (uint32_t)K[k] * r[k][x];
             d[x] = (uint8_t)((acc + 32768u) >> 16);
         }
     }

@@ -1,0 +1,187 @@
+// csrc/k_match.cu — Hamming matching kernels: ORBmatcher::DescriptorDistance (reference src/ORBmatcher.cc:1647-1663)
+// as XOR (LOP3) + POPC over 8 x u32 per descriptor, and the best / second-best loops built on it
+// (inner loops of SearchByBoW, :187-232; N x N distance tables of MapPoint::ComputeDistinctiveDescriptors,
+// src/MapPoint.cc:280-305).
+//
+// Sequential semantics being reproduced:  best = smallest distance, bestIdx = FIRST index attaining it (updates use
+// a strict '<'), second = second smallest value of the multiset (so second == best when the minimum occurs twice).
+// Both are order independent, so partial results merge exactly:
+//     best = min(b, c) on (distance, index);  second = min(max(b1, c1), min(b2, c2)).
+//
+// Roofline: integer pipe — 8 POPC per descriptor pair; descriptors are tiny (32 B) and stay in shared memory / L2.
+#include <algorithm>
+
+#include "orbx_internal.h"
+
+namespace orbx {
+
+__device__ __forceinline__ int hamming256(const uint32_t (&a)[8], const uint4 b0, const uint4 b1) {
+    return __popc(a[0] ^ b0.x) + __popc(a[1] ^ b0.y) + __popc(a[2] ^ b0.z) + __popc(a[3] ^ b0.w) + __popc(a[4] ^ b1.x) +
+           __popc(a[5] ^ b1.y) + __popc(a[6] ^ b1.z) + __popc(a[7] ^ b1.w);
+}
+
+__global__ void k_hamming_pairs(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, int* __restrict__ dist) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 a0 = a[2 * i], a1 = a[2 * i + 1];
+    const uint32_t q[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    dist[i] = hamming256(q, b[2 * i], b[2 * i + 1]);
+}
+
+constexpr int BF_THREADS = 128;  // queries per CTA
+constexpr int BF_TILE = 256;     // database descriptors staged per tile (8 KB)
+constexpr uint32_t BF_NOIDX = 0x3FFFFFu;
+
+// grid (ceil(nq / BF_THREADS), nsplit): every CTA matches 128 queries against one slice of the database and writes
+// a partial (best = dist << 22 | idx, second) per query.
+__global__ void __launch_bounds__(BF_THREADS) k_bruteforce_partial(const uint4* __restrict__ q, int nq,
+                                                                    const uint4* __restrict__ d, int nd, int sliceLen,
+                                                                    unsigned long long* __restrict__ partial) {
+    __shared__ uint4 tile[BF_TILE * 2];
+    const int qi = blockIdx.x * BF_THREADS + threadIdx.x;
+    const int begin = blockIdx.y * sliceLen, end = min(begin + sliceLen, nd);
+    uint32_t a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (qi < nq) {
+        const uint4 a0 = q[2 * qi], a1 = q[2 * qi + 1];
+        a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+    }
+    uint32_t best = (256u << 22) | BF_NOIDX;
+    int second = 256;
+    for (int t0 = begin; t0 < end; t0 += BF_TILE) {
+        const int m = min(BF_TILE, end - t0);
+        __syncthreads();
+        for (int i = threadIdx.x; i < 2 * m; i += BF_THREADS) tile[i] = d[2 * t0 + i];
+        __syncthreads();
+#pragma unroll 4
+        for (int j = 0; j < m; ++j) {
+            const int dist = hamming256(a, tile[2 * j], tile[2 * j + 1]);
+            const uint32_t cand = ((uint32_t)dist << 22) | (uint32_t)(t0 + j);
+            second = min(second, max(dist, (int)(best >> 22)));
+            best = min(best, cand);
+        }
+    }
+    if (qi < nq) partial[(size_t)blockIdx.y * nq + qi] = ((unsigned long long)best << 32) | (uint32_t)second;
+}
+
+__global__ void k_bruteforce_merge(const unsigned long long* __restrict__ partial, int nq, int nsplit, int th, float ratio,
+                                   int* __restrict__ idx, int* __restrict__ d1, int* __restrict__ d2, int* __restrict__ match) {
+    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (qi >= nq) return;
+    uint32_t best = (256u << 22) | BF_NOIDX;
+    int second = 256;
+    for (int s = 0; s < nsplit; ++s) {
+        const unsigned long long p = partial[(size_t)s * nq + qi];
+        const uint32_t b = (uint32_t)(p >> 32);
+        const int s2 = (int)(uint32_t)p;
+        second = min(max((int)(best >> 22), (int)(b >> 22)), min(second, s2));
+        best = min(best, b);
+    }
+    const int b1 = (int)(best >> 22);
+    const int bi = b1 >= 256 ? -1 : (int)(best & BF_NOIDX);  // a distance of 256 never passes the strict '<' against 256
+    if (idx) idx[qi] = bi;
+    if (d1) d1[qi] = b1;
+    if (d2) d2[qi] = second;
+    if (match) match[qi] = (b1 <= th && (float)b1 < __fmul_rn(ratio, (float)second)) ? bi : -1;
+}
+
+size_t bruteforce_scratch_bytes(int nq, int nd) {
+    (void)nd;
+    return (size_t)64 * (size_t)nq * sizeof(unsigned long long);
+}
+
+int launch_hamming_pairs(const uint8_t* a, const uint8_t* b, int n, int* dist, cudaStream_t s) {
+    if (n <= 0) return ORBX_OK;
+    k_hamming_pairs<<<(n + 255) / 256, 256, 0, s>>>(reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), n, dist);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int launch_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2,
+                      int* match, unsigned long long* dPartial, cudaStream_t s) {
+    if (nq <= 0) return ORBX_OK;
+    const int qBlocks = (nq + BF_THREADS - 1) / BF_THREADS;
+    // enough CTAs to fill 148 SMs a few times over, at least one tile per slice, at most 64 slices
+    int nsplit = std::max(1, std::min(64, (4 * 148 + qBlocks - 1) / qBlocks));
+    nsplit = std::max(1, std::min(nsplit, (nd + BF_TILE - 1) / BF_TILE));
+    const int sliceLen = nd > 0 ? ((nd + nsplit - 1) / nsplit + BF_TILE - 1) / BF_TILE * BF_TILE : BF_TILE;
+    nsplit = nd > 0 ? (nd + sliceLen - 1) / sliceLen : 1;
+    k_bruteforce_partial<<<dim3(qBlocks, nsplit), BF_THREADS, 0, s>>>(reinterpret_cast<const uint4*>(q), nq,
+                                                                       reinterpret_cast<const uint4*>(d), nd, sliceLen, dPartial);
+    count_launch();
+    k_bruteforce_merge<<<(nq + 255) / 256, 256, 0, s>>>(dPartial, nq, nsplit, th, ratio, idx, d1, d2, match);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// ---- all-vs-all keyframe matching ---------------------------------------------------------------------------------
+// One CTA per (query keyframe i, database keyframe j): 256 threads x AP_Q queries in registers, the database keyframe
+// streams through shared memory in tiles; every loaded database descriptor is compared with AP_Q queries, so the
+// shared-memory traffic per pair is 32 B / AP_Q.  score[i][j] = number of queries whose best match passes the test.
+constexpr int AP_THREADS = 256, AP_Q = 4, AP_TILE = 256;
+
+__global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict__ q, const uint4* __restrict__ db, int n, int kd,
+                                                          int th, float ratio, int* __restrict__ score) {
+    __shared__ uint4 tile[AP_TILE * 2];
+    __shared__ int total;
+    const int j = blockIdx.x, i = blockIdx.y;
+    const uint4* __restrict__ qk = q + (size_t)i * n * 2;
+    const uint4* __restrict__ dk = db + (size_t)j * n * 2;
+    if (threadIdx.x == 0) total = 0;
+    int accepted = 0;
+    for (int q0 = 0; q0 < n; q0 += AP_THREADS * AP_Q) {  // query chunk of 1024
+        uint32_t a[AP_Q][8];
+        uint32_t best[AP_Q];
+        int second[AP_Q];
+#pragma unroll
+        for (int k = 0; k < AP_Q; ++k) {
+            const int qi = q0 + k * AP_THREADS + threadIdx.x;
+            uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+            if (qi < n) { a0 = qk[2 * qi]; a1 = qk[2 * qi + 1]; }
+            a[k][0] = a0.x; a[k][1] = a0.y; a[k][2] = a0.z; a[k][3] = a0.w;
+            a[k][4] = a1.x; a[k][5] = a1.y; a[k][6] = a1.z; a[k][7] = a1.w;
+            best[k] = (256u << 22) | BF_NOIDX;
+            second[k] = 256;
+        }
+        for (int t0 = 0; t0 < n; t0 += AP_TILE) {
+            const int m = min(AP_TILE, n - t0);
+            __syncthreads();
+            for (int x = threadIdx.x; x < 2 * m; x += AP_THREADS) tile[x] = dk[2 * t0 + x];
+            __syncthreads();
+#pragma unroll 2
+            for (int jj = 0; jj < m; ++jj) {
+                const uint4 b0 = tile[2 * jj], b1 = tile[2 * jj + 1];
+#pragma unroll
+                for (int k = 0; k < AP_Q; ++k) {
+                    const int dist = hamming256(a[k], b0, b1);
+                    second[k] = min(second[k], max(dist, (int)(best[k] >> 22)));
+                    best[k] = min(best[k], ((uint32_t)dist << 22) | (uint32_t)(t0 + jj));
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < AP_Q; ++k) {
+            const int qi = q0 + k * AP_THREADS + threadIdx.x;
+            const int b1 = (int)(best[k] >> 22);
+            if (qi < n && b1 <= th && (float)b1 < __fmul_rn(ratio, (float)second[k])) ++accepted;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) accepted += __shfl_xor_sync(0xffffffffu, accepted, o);
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0 && accepted) atomicAdd(&total, accepted);
+    __syncthreads();
+    if (threadIdx.x == 0) score[(size_t)i * kd + j] = total;
+}
+
+int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score, cudaStream_t s) {
+    if (kq <= 0 || kd <= 0) return ORBX_OK;
+    k_allpairs<<<dim3(kd, kq), AP_THREADS, 0, s>>>(reinterpret_cast<const uint4*>(q), reinterpret_cast<const uint4*>(db), n, kd, th,
+                                                   ratio, score);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+}  // namespace orbx
