@@ -212,3 +212,76 @@ def distribute_octtree(keys: np.ndarray, minX: int, maxX: int, minY: int, maxY: 
     n = C.c_int(0)
     _check(lib().orbx_debug_distribute(_p(keys), keys.size, minX, maxX, minY, maxY, N, _p(out), out.size, C.byref(n)))
     return out[:n.value].copy()
+
+
+class ORBmatcher:
+    """Mirror of ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:37-102) for the routines on the hot path.
+
+    ORBmatcher(nnratio=0.6, checkOri=True); the static DescriptorDistance, SearchForInitialization and the
+    brute-force best / second-best matcher all run on the device through the C ABI (no CPU path)."""
+
+    TH_LOW, TH_HIGH, HISTO_LENGTH = TH_LOW, TH_HIGH, HISTO_LENGTH
+
+    def __init__(self, nnratio: float = 0.6, checkOri: bool = True):
+        self.mfNNratio, self.mbCheckOrientation = float(nnratio), bool(checkOri)
+
+    @staticmethod
+    def DescriptorDistance(a: np.ndarray, b: np.ndarray):
+        """a, b: uint8 [32] -> int, or uint8 [n, 32] -> int32 [n] (row-wise distances); src/ORBmatcher.cc:1647-1663"""
+        a = np.ascontiguousarray(a, dtype=np.uint8)
+        b = np.ascontiguousarray(b, dtype=np.uint8)
+        assert a.shape == b.shape and a.shape[-1] == 32
+        n = a.size // 32
+        out = np.empty(max(n, 1), np.int32)
+        _check(lib().orbx_hamming_distance(_p(a), _p(b), n, _p(out)))
+        return int(out[0]) if a.ndim == 1 else out[:n]
+
+    def SearchForInitialization(self, kps1, desc1, kps2, desc2, bounds, vbPrevMatched, windowSize: int = 10):
+        """src/ORBmatcher.cc:405-520.  bounds = (mnMinX, mnMaxX, mnMinY, mnMaxY) of the frames; vbPrevMatched is a
+        float32 [n1, 2] array updated in place.  Returns (nmatches, vnMatches12 int32 [n1])."""
+        kps1 = np.ascontiguousarray(kps1, dtype=KP_DTYPE)
+        kps2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+        desc1 = np.ascontiguousarray(desc1, dtype=np.uint8)
+        desc2 = np.ascontiguousarray(desc2, dtype=np.uint8)
+        assert vbPrevMatched.dtype == np.float32 and vbPrevMatched.flags.c_contiguous and vbPrevMatched.size == 2 * kps1.size
+        b = np.asarray(bounds, dtype=np.float32)
+        m12 = np.empty(max(kps1.size, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_search_for_initialization(_p(kps1), kps1.size, _p(desc1), _p(kps2), kps2.size, _p(desc2), _p(b),
+                                                    _p(vbPrevMatched), _p(m12), int(windowSize), C.c_float(self.mfNNratio),
+                                                    int(self.mbCheckOrientation), C.byref(n)))
+        return n.value, m12[:kps1.size]
+
+    def match_bruteforce(self, q, d, th: int = TH_LOW):
+        """best / second-best over the whole database (inner loop of SearchByBoW, src/ORBmatcher.cc:187-232):
+        returns (idx, d1, d2, match) int32 [nq]."""
+        q = np.ascontiguousarray(q, dtype=np.uint8)
+        d = np.ascontiguousarray(d, dtype=np.uint8)
+        nq, nd = q.shape[0], d.shape[0]
+        idx, d1, d2, m = (np.empty(max(nq, 1), np.int32) for _ in range(4))
+        _check(lib().orbx_match_bruteforce(_p(q), nq, _p(d), nd, int(th), C.c_float(self.mfNNratio), _p(idx), _p(d1), _p(d2), _p(m)))
+        return idx[:nq], d1[:nq], d2[:nq], m[:nq]
+
+    def match_bruteforce_device(self, d_q: int, nq: int, d_d: int, nd: int, d_idx: int, d_d1: int, d_d2: int, d_match: int,
+                                th: int = TH_LOW, stream: int = 0):
+        _check(lib().orbx_match_bruteforce_device(_p(d_q), nq, _p(d_d), nd, int(th), C.c_float(self.mfNNratio), _p(d_idx),
+                                                  _p(d_d1), _p(d_d2), _p(d_match), _p(stream) if stream else None))
+
+    def match_allpairs_device(self, d_q: int, kq: int, d_db: int, kd: int, n: int, d_score: int, th: int = TH_LOW, stream: int = 0):
+        """score[i, j] = accepted matches of query keyframe i in database keyframe j (device buffers, asynchronous)."""
+        _check(lib().orbx_match_allpairs_device(_p(d_q), kq, _p(d_db), kd, n, int(th), C.c_float(self.mfNNratio), _p(d_score),
+                                                _p(stream) if stream else None))
+
+
+def ComputeStereoMatches(exL: ORBextractor, exR: ORBextractor, kpsL, descL, kpsR, descR, bf: float, fx: float):
+    """Frame::ComputeStereoMatches (src/Frame.cc:465-639) on the pyramids exL / exR hold from their last call.
+    Returns (mvuRight, mvDepth) float32 [nL], -1 where there is no match."""
+    kpsL = np.ascontiguousarray(kpsL, dtype=KP_DTYPE)
+    kpsR = np.ascontiguousarray(kpsR, dtype=KP_DTYPE)
+    descL = np.ascontiguousarray(descL, dtype=np.uint8)
+    descR = np.ascontiguousarray(descR, dtype=np.uint8)
+    u = np.empty(max(kpsL.size, 1), np.float32)
+    z = np.empty(max(kpsL.size, 1), np.float32)
+    _check(lib().orbx_stereo_match(exL._h, exR._h, _p(kpsL), kpsL.size, _p(descL), _p(kpsR), kpsR.size, _p(descR),
+                                   C.c_float(bf), C.c_float(fx), _p(u), _p(z)))
+    return u[:kpsL.size], z[:kpsL.size]

@@ -44,56 +44,6 @@ static inline short sat_short(float v) {
 }
 static inline long long round_up(long long v, long long a) { return (v + a - 1) / a * a; }
 
-struct DevBuf {  // owning device allocation
-    void* p = nullptr;
-    size_t bytes = 0;
-    int ensure(size_t n) {
-        if (n <= bytes) return ORBX_OK;
-        if (p) cudaFree(p);
-        p = nullptr;
-        bytes = 0;
-        cudaError_t e = cudaMalloc(&p, n);
-        if (e != cudaSuccess) {
-            set_error("cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
-            p = nullptr;
-            return e == cudaErrorMemoryAllocation ? ORBX_E_OOM : ORBX_E_CUDA;
-        }
-        bytes = n;
-        return ORBX_OK;
-    }
-    void release() {
-        if (p) cudaFree(p);
-        p = nullptr;
-        bytes = 0;
-    }
-    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
-};
-
-struct PinBuf {  // owning pinned host allocation
-    void* p = nullptr;
-    size_t bytes = 0;
-    int ensure(size_t n) {
-        if (n <= bytes) return ORBX_OK;
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        bytes = 0;
-        cudaError_t e = cudaMallocHost(&p, n);
-        if (e != cudaSuccess) {
-            set_error("cudaMallocHost(%zu) failed: %s", n, cudaGetErrorString(e));
-            p = nullptr;
-            return ORBX_E_OOM;
-        }
-        bytes = n;
-        return ORBX_OK;
-    }
-    void release() {
-        if (p) cudaFreeHost(p);
-        p = nullptr;
-        bytes = 0;
-    }
-    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
-};
-
 }  // namespace orbx
 
 using namespace orbx;
@@ -416,6 +366,23 @@ static int check_device(const orbx_extractor* ex) {
     ORBX_CUDA(cudaSetDevice(ex->device));
     return ORBX_OK;
 }
+
+namespace orbx {
+int extractor_view(orbx_extractor* ex, ExtractorView* v) {
+    if (!ex || !v) {
+        set_error("null extractor handle");
+        return ORBX_E_INVALID;
+    }
+    v->g = &ex->g;
+    v->stream = ex->stream;
+    v->device = ex->device;
+    v->scale = ex->scale.data();
+    v->invScale = ex->invScale.data();
+    v->serial = ex->serial;
+    v->lastBatch = ex->lastBatch;
+    return ORBX_OK;
+}
+}  // namespace orbx
 
 extern "C" {
 

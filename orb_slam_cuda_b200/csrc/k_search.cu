@@ -1,0 +1,270 @@
+// csrc/k_search.cu — ORBmatcher::SearchForInitialization (reference src/ORBmatcher.cc:405-520) with
+// Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea (src/Frame.cc:229-244, :381-391, :326-379) and
+// ORBmatcher::ComputeThreeMaxima (src/ORBmatcher.cc:1601-1642).
+//
+// The reference loop is sequential and stateful (vMatchedDistance[i2] <= dist skips a candidate, :444; an accepted
+// match steals i2 from its previous owner, :463-467), so the result depends on the i1 order.  What does NOT depend on
+// the order is the expensive part — which frame-2 keypoints fall into the window of i1, in which order the grid walk
+// visits them, and their Hamming distances.  Hence three kernels:
+//   k_sfi_grid       (1 CTA)   frame-2 keypoints binned into the 64 x 48 grid (cell = ix*48 + iy, keypoints of a
+//                              cell in index order = push_back order), as a counting sort
+//   k_sfi_candidates (warp/i1) for every octave-0 keypoint of frame 1: the window's cells are contiguous runs of the
+//                              sorted array per grid column, lanes test box + octave and compute DescriptorDistance,
+//                              survivors are appended in the reference's visiting order as (dist << 16 | i2)
+//   k_sfi_resolve    (1 warp)  replays the i1 loop over the precomputed candidate lists with the mutable state
+//                              (vMatchedDistance, vnMatches21) in shared memory, then the rotation histogram, the
+//                              three maxima, the removal of the other bins and the vbPrevMatched update.
+// best = first candidate (visiting order) of minimal distance, second = second smallest distance of the multiset:
+// both are what the strict-'<' updates of :446-456 produce, and both are order independent given the skip set.
+#include "orbx_internal.h"
+
+namespace orbx {
+
+constexpr int GRID_COLS = 64, GRID_ROWS = 48, GRID_CELLS = GRID_COLS * GRID_ROWS;  // include/Frame.h:37-38
+
+__device__ __forceinline__ int hamming32B(const uint4 a0, const uint4 a1, const uint4 b0, const uint4 b1) {
+    return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) + __popc(a1.x ^ b1.x) +
+           __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+}
+
+// bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}; sorted[] receives the keypoint indices ordered by (cell, index),
+// cellStart[GRID_CELLS + 1] the run boundaries.  cellOf is scratch (n ints).  One CTA of 1024 threads.
+__global__ void __launch_bounds__(1024) k_sfi_grid(const orbx_keypoint* __restrict__ k2, int n, float minX, float minY,
+                                                    float invW, float invH, int* __restrict__ cellOf,
+                                                    int* __restrict__ sorted, int* __restrict__ cellStart) {
+    __shared__ int cnt[GRID_CELLS + 1];
+    __shared__ int warpSums[32];
+    const int tid = threadIdx.x;
+    for (int c = tid; c <= GRID_CELLS; c += blockDim.x) cnt[c] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += blockDim.x) {
+        // PosInGrid (src/Frame.cc:381-391): round((kp.pt.x - mnMinX) * mfGridElementWidthInv)
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(k2[i].x, minX), invW));
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(k2[i].y, minY), invH));
+        const bool in = px >= 0 && px < GRID_COLS && py >= 0 && py < GRID_ROWS;
+        const int c = in ? px * GRID_ROWS + py : -1;
+        cellOf[i] = c;
+        if (in) atomicAdd(&cnt[c], 1);
+    }
+    __syncthreads();
+    // exclusive scan of cnt[0..GRID_CELLS] (3073 entries, 1024 threads -> chunks of 4)
+    {
+        const int lane = tid & 31, wid = tid >> 5;
+        const int chunk = (GRID_CELLS + 1 + blockDim.x - 1) / blockDim.x;
+        const int b = min(tid * chunk, GRID_CELLS + 1), e = min(b + chunk, GRID_CELLS + 1);
+        int local = 0;
+        for (int i = b; i < e; ++i) local += cnt[i];
+        int incl = local;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) warpSums[wid] = incl;
+        __syncthreads();
+        int off = 0;
+        for (int w = 0; w < wid; ++w) off += warpSums[w];
+        int run = off + incl - local;
+        for (int i = b; i < e; ++i) {
+            const int v = cnt[i];
+            cnt[i] = run;
+            run += v;
+        }
+        __syncthreads();
+    }
+    for (int c = tid; c <= GRID_CELLS; c += blockDim.x) cellStart[c] = cnt[c];
+    // stable placement: rank inside the cell = number of earlier keypoints of the same cell
+    for (int i = tid; i < n; i += blockDim.x) {
+        const int c = cellOf[i];
+        if (c < 0) continue;
+        int rank = 0;
+        for (int j = 0; j < i; ++j) rank += (cellOf[j] == c) ? 1 : 0;
+        sorted[cnt[c] + rank] = i;
+    }
+}
+
+// One warp per frame-1 keypoint.  cand[i1 * candCap + k] = (dist << 16) | i2 in visiting order, candCnt[i1] = count
+// (0 for keypoints of octave > 0, which the reference skips at :421-423).
+__global__ void __launch_bounds__(256) k_sfi_candidates(const orbx_keypoint* __restrict__ k1, int n1,
+                                                         const uint4* __restrict__ desc1,
+                                                         const orbx_keypoint* __restrict__ k2,
+                                                         const uint4* __restrict__ desc2, const float* __restrict__ prev,
+                                                         float minX, float minY, float invW, float invH, float r,
+                                                         const int* __restrict__ sorted, const int* __restrict__ cellStart,
+                                                         uint32_t* __restrict__ cand, int candCap, int* __restrict__ candCnt,
+                                                         int* __restrict__ dStatus) {
+    const int lane = threadIdx.x & 31;
+    const int i1 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i1 >= n1) return;
+    int count = 0;
+    if (k1[i1].octave <= 0) {
+        const float x = prev[2 * i1], y = prev[2 * i1 + 1];
+        // GetFeaturesInArea(x, y, r, 0, 0) (src/Frame.cc:326-379)
+        const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, minX), r), invW)));
+        const int cx1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, minX), r), invW)));
+        const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, minY), r), invH)));
+        const int cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, minY), r), invH)));
+        if (cx0 < GRID_COLS && cx1 >= 0 && cy0 < GRID_ROWS && cy1 >= 0) {
+            const uint4 a0 = desc1[2 * i1], a1 = desc1[2 * i1 + 1];
+            uint32_t* out = cand + (size_t)i1 * candCap;
+            for (int ix = cx0; ix <= cx1; ++ix) {
+                const int b = cellStart[ix * GRID_ROWS + cy0], e = cellStart[ix * GRID_ROWS + cy1 + 1];
+                for (int base = b; base < e; base += 32) {
+                    const int p = base + lane;
+                    bool ok = false;
+                    int i2 = 0, dist = 0;
+                    if (p < e) {
+                        i2 = sorted[p];
+                        const orbx_keypoint kp = k2[i2];
+                        // bCheckLevels is true for (0, 0): octave must be 0; then |dx| < r && |dy| < r
+                        ok = kp.octave == 0 && fabsf(__fsub_rn(kp.x, x)) < r && fabsf(__fsub_rn(kp.y, y)) < r;
+                        if (ok) dist = hamming32B(a0, a1, desc2[2 * i2], desc2[2 * i2 + 1]);
+                    }
+                    const uint32_t m = __ballot_sync(0xffffffffu, ok);
+                    if (ok) {
+                        const int o = count + __popc(m & ((1u << lane) - 1));
+                        if (o < candCap) out[o] = ((uint32_t)dist << 16) | (uint32_t)i2;
+                    }
+                    count += __popc(m);
+                }
+            }
+        }
+    }
+    if (lane == 0) {
+        if (count > candCap) {
+            atomicExch(dStatus, ORBX_E_OVERFLOW);
+            count = candCap;
+        }
+        candCnt[i1] = count;
+    }
+}
+
+// One warp replays the sequential loop.  Dynamic shared memory: matchedDist[n2] (uint16, 0xFFFF = INT_MAX),
+// matches21[n2] (int32), matches12[n1] (int32), bin[n1] (int8: histogram bin of the acceptance event or -1).
+__global__ void __launch_bounds__(32) k_sfi_resolve(const orbx_keypoint* __restrict__ k1, int n1,
+                                                     const orbx_keypoint* __restrict__ k2, int n2,
+                                                     const uint32_t* __restrict__ cand, int candCap,
+                                                     const int* __restrict__ candCnt, float nnratio, int checkOri,
+                                                     float* __restrict__ prev, int* __restrict__ matches12Out,
+                                                     int* __restrict__ nmatchesOut) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    int* matches21 = reinterpret_cast<int*>(sm);
+    int* matches12 = matches21 + n2;
+    uint16_t* matchedDist = reinterpret_cast<uint16_t*>(matches12 + n1);
+    signed char* binOf = reinterpret_cast<signed char*>(matchedDist + n2);
+    const int lane = threadIdx.x;
+    for (int i = lane; i < n2; i += 32) { matches21[i] = -1; matchedDist[i] = 0xFFFFu; }
+    for (int i = lane; i < n1; i += 32) { matches12[i] = -1; binOf[i] = -1; }
+    __syncwarp();
+    const float factor = 1.0f / 30.0f;  // 1.0f / HISTO_LENGTH
+    for (int i1 = 0; i1 < n1; ++i1) {
+        const int cnt = candCnt[i1];
+        if (cnt == 0) continue;
+        const uint32_t* c = cand + (size_t)i1 * candCap;
+        // key = dist << 16 | position: minimal key = minimal distance, first in visiting order
+        uint32_t b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;  // two smallest keys seen by this lane
+        for (int p = lane; p < cnt; p += 32) {
+            const uint32_t e = c[p];
+            const uint32_t dist = e >> 16, i2 = e & 0xFFFFu;
+            if ((uint32_t)matchedDist[i2] <= dist) continue;  // :444 (0xFFFF stands for INT_MAX; dist <= 256)
+            const uint32_t key = (dist << 16) | (uint32_t)p;
+            if (key < b1) { b2 = b1; b1 = key; }
+            else if (key < b2) b2 = key;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint32_t o1 = __shfl_xor_sync(0xffffffffu, b1, o), o2 = __shfl_xor_sync(0xffffffffu, b2, o);
+            const uint32_t lo = min(b1, o1), hi = max(b1, o1);
+            b2 = min(hi, min(b2, o2));
+            b1 = lo;
+        }
+        if (b1 == 0xFFFFFFFFu) continue;  // every candidate skipped: bestDist stays INT_MAX
+        const int bestDist = (int)(b1 >> 16);
+        if (bestDist > 50) continue;  // TH_LOW (:459)
+        const float second = b2 == 0xFFFFFFFFu ? 2147483648.0f /* (float)INT_MAX */ : (float)(int)(b2 >> 16);
+        if (!((float)bestDist < __fmul_rn(second, nnratio))) continue;
+        const int bestIdx2 = (int)(c[b1 & 0xFFFFu] & 0xFFFFu);
+        if (lane == 0) {
+            const int owner = matches21[bestIdx2];
+            if (owner >= 0) matches12[owner] = -1;
+            matches12[i1] = bestIdx2;
+            matches21[bestIdx2] = i1;
+            matchedDist[bestIdx2] = (uint16_t)bestDist;
+            if (checkOri) {
+                float rot = __fsub_rn(k1[i1].angle, k2[bestIdx2].angle);
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                int bin = (int)roundf(__fmul_rn(rot, factor));
+                if (bin == 30) bin = 0;
+                binOf[i1] = (signed char)min(max(bin, 0), 29);
+            }
+        }
+        __syncwarp();
+    }
+    __syncwarp();
+    if (checkOri) {
+        // histogram sizes count acceptance events, including matches stolen later (rotHist[bin].push_back(i1), :478)
+        int h = 0;  // lane b owns bin b (30 bins)
+        for (int i = 0; i < n1; ++i) h += (binOf[i] == lane) ? 1 : 0;
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int b = 0; b < 30; ++b) {  // ComputeThreeMaxima (:1601-1642), evaluated redundantly by every lane
+            const int s = __shfl_sync(0xffffffffu, h, b);
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = b; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = b; }
+            else if (s > max3) { max3 = s; ind3 = b; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+        for (int i = lane; i < n1; i += 32) {
+            const int b = binOf[i];
+            if (b >= 0 && b != ind1 && b != ind2 && b != ind3) matches12[i] = -1;
+        }
+        __syncwarp();
+    }
+    int total = 0;
+    for (int i = lane; i < n1; i += 32) {
+        const int m = matches12[i];
+        matches12Out[i] = m;
+        if (m >= 0) {
+            ++total;
+            prev[2 * i] = k2[m].x;  // vbPrevMatched update (:514-517)
+            prev[2 * i + 1] = k2[m].y;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+    // the reference's running nmatches (++ on accept, -- on steal / histogram removal) = surviving matches
+    if (lane == 0) *nmatchesOut = total;
+}
+
+size_t sfi_resolve_smem(int n1, int n2) { return (size_t)n2 * 4 + (size_t)n1 * 4 + (size_t)n2 * 2 + (size_t)n1 + 16; }
+
+int launch_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_t* desc1, const orbx_keypoint* k2, int n2,
+                                     const uint8_t* desc2, const float bounds[4], float* prev, int* matches12, int window,
+                                     float nnratio, int checkOri, int* cellOf, int* sorted, int* cellStart, uint32_t* cand,
+                                     int candCap, int* candCnt, int* nmatches, int* dStatus, cudaStream_t s) {
+    const float minX = bounds[0], maxX = bounds[1], minY = bounds[2], maxY = bounds[3];
+    // mfGridElementWidthInv / HeightInv (src/Frame.cc:104-105)
+    const float invW = (float)GRID_COLS / (maxX - minX), invH = (float)GRID_ROWS / (maxY - minY);
+    const size_t smem = sfi_resolve_smem(n1, n2);
+    if (smem > 200 * 1024) {
+        set_error("SearchForInitialization: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
+        return ORBX_E_INVALID;
+    }
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        ORBX_CUDA(cudaFuncSetAttribute(k_sfi_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, minX, minY, invW, invH, cellOf, sorted, cellStart);
+    count_launch();
+    k_sfi_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(k1, n1, reinterpret_cast<const uint4*>(desc1), k2,
+                                                    reinterpret_cast<const uint4*>(desc2), prev, minX, minY, invW, invH,
+                                                    (float)window, sorted, cellStart, cand, candCap, candCnt, dStatus);
+    count_launch();
+    k_sfi_resolve<<<1, 32, smem, s>>>(k1, n1, k2, n2, cand, candCap, candCnt, nnratio, checkOri, prev, matches12, nmatches);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+}  // namespace orbx

@@ -1,0 +1,223 @@
+// csrc/matcher.cu — C entry points of the matcher half of include/orbx.h: ORBmatcher::DescriptorDistance,
+// brute-force best / second-best, all-vs-all keyframe scoring, SearchForInitialization and
+// Frame::ComputeStereoMatches.  The kernels live in k_match.cu / k_search.cu / k_stereo.cu; this file owns the
+// per-thread device workspace (a stream and grow-only scratch per host thread: ORBmatcher objects are stack-local
+// on three threads in the reference, src/Tracking.cc:671, src/LocalMapping.cc:248, src/LoopClosing.cc:278) and the
+// host <-> device copies of the "host buffer" entry points.  There is no CPU path.
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "orbx_internal.h"
+
+using namespace orbx;
+
+namespace {
+
+struct Workspace {  // one per host thread and device
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    DevBuf a, b, c, d, e, f, g, h, out0, out1, out2, out3, status, partial;
+    PinBuf pin;
+    ~Workspace() {
+        // device memory is reclaimed at process exit; freeing here could run after the CUDA runtime is torn down
+    }
+};
+
+thread_local Workspace tls[8];
+
+int workspace(Workspace** out) {
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        set_error("no CUDA device: %s (this library has no CPU path)", e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+        return ORBX_E_CUDA;
+    }
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 8) {
+        set_error("device ordinal %d not supported by the matcher workspace", dev);
+        return ORBX_E_INVALID;
+    }
+    Workspace& w = tls[dev];
+    if (!w.stream) {
+        ORBX_CUDA(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+        w.device = dev;
+    }
+    *out = &w;
+    return ORBX_OK;
+}
+
+int upload(DevBuf& buf, const void* src, size_t bytes, cudaStream_t s) {
+    int rc = buf.ensure(bytes ? bytes : 16);
+    if (rc) return rc;
+    if (bytes) ORBX_CUDA(cudaMemcpyAsync(buf.p, src, bytes, cudaMemcpyHostToDevice, s));
+    return ORBX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int orbx_hamming_distance(const uint8_t* a, const uint8_t* b, int n, int* dist) {
+    if (n < 0 || (n > 0 && (!a || !b || !dist))) { set_error("orbx_hamming_distance: bad argument"); return ORBX_E_INVALID; }
+    if (n == 0) return ORBX_OK;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = w->stream;
+    if ((rc = upload(w->a, a, (size_t)n * 32, s)) || (rc = upload(w->b, b, (size_t)n * 32, s)) || (rc = w->out0.ensure((size_t)n * 4)))
+        return rc;
+    if ((rc = launch_hamming_pairs(w->a.as<uint8_t>(), w->b.as<uint8_t>(), n, w->out0.as<int>(), s))) return rc;
+    ORBX_CUDA(cudaMemcpyAsync(dist, w->out0.p, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+int orbx_match_bruteforce_device(const uint8_t* dq, int nq, const uint8_t* dd, int nd, int th, float ratio, int* idx, int* d1,
+                                 int* d2, int* match, void* stream) {
+    if (nq < 0 || nd < 0 || nd > 0x3FFFFE || (nq > 0 && !dq) || (nd > 0 && !dd)) {
+        set_error("orbx_match_bruteforce_device: bad argument (nd must be < 4194302)");
+        return ORBX_E_INVALID;
+    }
+    if (nq == 0) return ORBX_OK;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    if ((rc = w->partial.ensure(bruteforce_scratch_bytes(nq, nd)))) return rc;
+    return launch_bruteforce(dq, nq, dd, nd, th, ratio, idx, d1, d2, match, w->partial.as<unsigned long long>(),
+                             stream ? (cudaStream_t)stream : w->stream);
+}
+
+int orbx_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2,
+                          int* match) {
+    if (nq < 0 || nd < 0 || (nq > 0 && !q) || (nd > 0 && !d)) { set_error("orbx_match_bruteforce: bad argument"); return ORBX_E_INVALID; }
+    if (nq == 0) return ORBX_OK;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = w->stream;
+    const size_t ob = (size_t)nq * 4;
+    if ((rc = upload(w->a, q, (size_t)nq * 32, s)) || (rc = upload(w->b, d, (size_t)nd * 32, s)) || (rc = w->out0.ensure(ob)) ||
+        (rc = w->out1.ensure(ob)) || (rc = w->out2.ensure(ob)) || (rc = w->out3.ensure(ob)))
+        return rc;
+    if ((rc = orbx_match_bruteforce_device(w->a.as<uint8_t>(), nq, w->b.as<uint8_t>(), nd, th, ratio, w->out0.as<int>(),
+                                           w->out1.as<int>(), w->out2.as<int>(), w->out3.as<int>(), s)))
+        return rc;
+    if (idx) ORBX_CUDA(cudaMemcpyAsync(idx, w->out0.p, ob, cudaMemcpyDeviceToHost, s));
+    if (d1) ORBX_CUDA(cudaMemcpyAsync(d1, w->out1.p, ob, cudaMemcpyDeviceToHost, s));
+    if (d2) ORBX_CUDA(cudaMemcpyAsync(d2, w->out2.p, ob, cudaMemcpyDeviceToHost, s));
+    if (match) ORBX_CUDA(cudaMemcpyAsync(match, w->out3.p, ob, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+int orbx_match_allpairs_device(const uint8_t* dq, int kq, const uint8_t* ddb, int kd, int n, int th, float ratio, int* dscore,
+                               void* stream) {
+    if (kq < 0 || kd < 0 || n < 1 || n > 0x3FFFFE || !dscore || (kq > 0 && !dq) || (kd > 0 && !ddb)) {
+        set_error("orbx_match_allpairs_device: bad argument");
+        return ORBX_E_INVALID;
+    }
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    return launch_allpairs(dq, kq, ddb, kd, n, th, ratio, dscore, stream ? (cudaStream_t)stream : w->stream);
+}
+
+int orbx_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_t* desc1, const orbx_keypoint* k2, int n2,
+                                   const uint8_t* desc2, const float bounds[4], float* prev_xy, int* matches12, int window,
+                                   float nnratio, int check_ori, int* nmatches) {
+    if (n1 < 0 || n2 < 0 || !bounds || !nmatches || (n1 > 0 && (!k1 || !desc1 || !prev_xy || !matches12)) ||
+        (n2 > 0 && (!k2 || !desc2)) || n2 > 65535 || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) {
+        set_error("orbx_search_for_initialization: bad argument (n2 <= 65535, bounds = {minX, maxX, minY, maxY})");
+        return ORBX_E_INVALID;
+    }
+    *nmatches = 0;
+    if (n1 == 0) return ORBX_OK;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = w->stream;
+    // candidate capacity per frame-1 keypoint: at most every octave-0 keypoint of frame 2
+    int n2lvl0 = 0;
+    for (int i = 0; i < n2; ++i) n2lvl0 += k2[i].octave == 0 ? 1 : 0;
+    const int candCap = std::max(n2lvl0, 1);
+    if ((rc = upload(w->a, k1, (size_t)n1 * sizeof(orbx_keypoint), s)) || (rc = upload(w->b, desc1, (size_t)n1 * 32, s)) ||
+        (rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
+        (rc = upload(w->e, prev_xy, (size_t)n1 * 8, s)) || (rc = w->out0.ensure((size_t)n1 * 4 + 16)) ||
+        (rc = w->f.ensure(((size_t)2 * std::max(n2, 1) + 64 * 48 + 1) * 4)) || (rc = w->g.ensure((size_t)n1 * candCap * 4)) ||
+        (rc = w->h.ensure((size_t)n1 * 4)) || (rc = w->status.ensure(16)))
+        return rc;
+    ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
+    int* cellOf = w->f.as<int>();
+    int* sorted = cellOf + std::max(n2, 1);
+    int* cellStart = sorted + std::max(n2, 1);
+    int* dN = w->status.as<int>() + 1;
+    if ((rc = launch_search_for_initialization(w->a.as<orbx_keypoint>(), n1, w->b.as<uint8_t>(), w->c.as<orbx_keypoint>(), n2,
+                                               w->d.as<uint8_t>(), bounds, w->e.as<float>(), w->out0.as<int>(), window, nnratio,
+                                               check_ori, cellOf, sorted, cellStart, w->g.as<uint32_t>(), candCap, w->h.as<int>(),
+                                               dN, w->status.as<int>(), s)))
+        return rc;
+    int st[2] = {0, 0};
+    ORBX_CUDA(cudaMemcpyAsync(matches12, w->out0.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(prev_xy, w->e.p, (size_t)n1 * 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(st, w->status.p, 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    if (st[0] != 0) {
+        set_error("orbx_search_for_initialization: candidate list overflow");
+        return ORBX_E_OVERFLOW;
+    }
+    *nmatches = st[1];
+    return ORBX_OK;
+}
+
+int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypoint* kL, int nL, const uint8_t* descL,
+                      const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float fx, float* u_right, float* depth) {
+    ExtractorView L, R;
+    int rc;
+    if ((rc = extractor_view(exL, &L)) || (rc = extractor_view(exR, &R))) return rc;
+    if (nL < 0 || nR < 0 || nR > 65535 || (nL > 0 && (!kL || !descL || !u_right || !depth)) || (nR > 0 && (!kR || !descR))) {
+        set_error("orbx_stereo_match: bad argument (nR <= 65535)");
+        return ORBX_E_INVALID;
+    }
+    if (L.serial == 0 || R.serial == 0 || L.device != R.device || L.g->nlevels != R.g->nlevels) {
+        set_error("orbx_stereo_match: both extractors must have extracted a frame on the same device with the same pyramid depth");
+        return ORBX_E_INVALID;
+    }
+    if (nL == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(L.device));
+    Workspace* w;
+    if ((rc = workspace(&w))) return rc;
+    cudaStream_t s = w->stream;
+    ORBX_CUDA(cudaStreamSynchronize(L.stream));  // the pyramids of the last extract calls are complete
+    ORBX_CUDA(cudaStreamSynchronize(R.stream));
+    StereoLevels lv;
+    memset(&lv, 0, sizeof lv);
+    lv.nlevels = L.g->nlevels;
+    for (int l = 0; l < lv.nlevels; ++l) {
+        const LevelGeom &a = L.g->lv[l], &b = R.g->lv[l];
+        lv.left[l] = a.plane + (size_t)EDGE * a.pitch + XOFF;
+        lv.right[l] = b.plane + (size_t)EDGE * b.pitch + XOFF;
+        lv.pitchL[l] = a.pitch;
+        lv.pitchR[l] = b.pitch;
+        lv.widthR[l] = b.w;
+        lv.scale[l] = L.scale[l];       // Frame copies the LEFT extractor's tables (src/Frame.cc:68-74)
+        lv.invScale[l] = L.invScale[l];
+    }
+    const float mb = bf / fx;        // mb = mbf / fx (src/Frame.cc:113)
+    const float maxD = bf / mb;      // minZ = mb, maxD = mbf / minZ (:494-496)
+    const size_t fb = (size_t)nL * 4;
+    if ((rc = upload(w->a, kL, (size_t)nL * sizeof(orbx_keypoint), s)) || (rc = upload(w->b, descL, (size_t)nL * 32, s)) ||
+        (rc = upload(w->c, kR, (size_t)nR * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, descR, (size_t)nR * 32, s)) ||
+        (rc = w->out0.ensure(fb)) || (rc = w->out1.ensure(fb)) || (rc = w->out2.ensure(fb)))
+        return rc;
+    if ((rc = launch_stereo(lv, w->a.as<orbx_keypoint>(), nL, w->b.as<uint8_t>(), w->c.as<orbx_keypoint>(), nR, w->d.as<uint8_t>(), bf,
+                            maxD, w->out0.as<float>(), w->out1.as<float>(), w->out2.as<int>(), s)))
+        return rc;
+    ORBX_CUDA(cudaMemcpyAsync(u_right, w->out0.p, fb, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(depth, w->out1.p, fb, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
+}  // extern "C"

@@ -88,6 +88,78 @@ void set_error(const char* fmt, ...);
         }                                                                                        \
     } while (0)
 
+struct DevBuf {  // owning device allocation (grow-only)
+    void* p = nullptr;
+    size_t bytes = 0;
+    inline int ensure(size_t n) {
+        if (n <= bytes) return ORBX_OK;
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e != cudaSuccess) {
+            set_error("cudaMalloc(%zu) failed: %s", n, cudaGetErrorString(e));
+            p = nullptr;
+            return e == cudaErrorMemoryAllocation ? ORBX_E_OOM : ORBX_E_CUDA;
+        }
+        bytes = n;
+        return ORBX_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct PinBuf {  // owning pinned host allocation
+    void* p = nullptr;
+    size_t bytes = 0;
+    int ensure(size_t n) {
+        if (n <= bytes) return ORBX_OK;
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        bytes = 0;
+        cudaError_t e = cudaMallocHost(&p, n);
+        if (e != cudaSuccess) {
+            set_error("cudaMallocHost(%zu) failed: %s", n, cudaGetErrorString(e));
+            p = nullptr;
+            return ORBX_E_OOM;
+        }
+        bytes = n;
+        return ORBX_OK;
+    }
+    void release() {
+        if (p) cudaFreeHost(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+
+// ---- what the matcher entry points need from an extractor handle (stereo reads both pyramids) -------------------
+struct ExtractorView {
+    const FrameGeom* g;
+    cudaStream_t stream;
+    int device;
+    const float* scale;
+    const float* invScale;
+    long long serial;  // 0 = nothing extracted yet
+    int lastBatch;
+};
+int extractor_view(orbx_extractor* ex, ExtractorView* v);
+
+struct StereoLevels {  // interior pointers (pixel 0,0) of frame 0 of both extractors, per level
+    const uint8_t* left[ORBX_MAX_LEVELS];
+    const uint8_t* right[ORBX_MAX_LEVELS];
+    int pitchL[ORBX_MAX_LEVELS], pitchR[ORBX_MAX_LEVELS];
+    int widthR[ORBX_MAX_LEVELS];
+    float scale[ORBX_MAX_LEVELS], invScale[ORBX_MAX_LEVELS];
+    int nlevels;
+};
+
 // ---- kernel launchers (each file k_*.cu holds the kernels of one stage) ---------------------------------------
 // ComputePyramid: level 0 = frame + reflect-101 border, level l = resize(level l-1) + border
 int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
@@ -116,6 +188,13 @@ int launch_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th
 size_t bruteforce_scratch_bytes(int nq, int nd);
 int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score,
                     cudaStream_t s);
+
+int launch_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_t* desc1, const orbx_keypoint* k2, int n2,
+                                     const uint8_t* desc2, const float bounds[4], float* prev, int* matches12, int window,
+                                     float nnratio, int checkOri, int* cellOf, int* sorted, int* cellStart, uint32_t* cand,
+                                     int candCap, int* candCnt, int* nmatches, int* dStatus, cudaStream_t s);
+int launch_stereo(const StereoLevels& lv, const orbx_keypoint* kL, int nL, const uint8_t* dL, const orbx_keypoint* kR, int nR,
+                  const uint8_t* dR, float mbf, float maxD, float* uRight, float* depth, int* sad, cudaStream_t s);
 
 // ---- packed keypoint helpers ---------------------------------------------------------------------------------
 __host__ __device__ inline uint32_t pack_key(int x, int y, int resp) {
