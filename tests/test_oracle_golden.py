@@ -1,0 +1,125 @@
+"""CPU suite, part 1: the oracle against the committed fixtures and the known-answer vectors derivable from the
+reference source.  Runs without a GPU and without cv2."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle_lib as O
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+@pytest.fixture(scope="module")
+def prim():
+    return np.load(os.path.join(GOLD, "cv2_primitives.npz"))
+
+
+def test_resize_matches_cv2_fixture(prim):
+    img = prim["img"]
+    for name in ("a", "b", "c"):
+        want = prim[f"resize_{name}"]
+        got = O.resize_linear(img, want.shape[1], want.shape[0])
+        assert np.array_equal(got, want), name
+
+
+def test_border_and_blur_match_cv2_fixture(prim):
+    img = prim["img"]
+    assert np.array_equal(O.border_reflect101(img, 19), prim["border19"])
+    assert np.array_equal(O.gaussian7(img), prim["blur"])
+    assert np.array_equal(O.gaussian7(prim["tiny"]), prim["blur_tiny"])  # 9x11: reflect-101 wraps inside 3 px
+
+
+def test_fast_matches_cv2_fixture(prim):
+    img = prim["img"]
+    for th in (20, 7):
+        want = prim[f"fast{th}"]
+        got = O.fast9(img, th, True)
+        assert len(got) == len(want) > 0
+        assert np.array_equal(got["x"], want[:, 0]) and np.array_equal(got["y"], want[:, 1])  # same order
+        assert np.array_equal(got["response"], want[:, 2])
+
+
+def test_fast_atan2_matches_cv2_fixture(prim):
+    got = O.fast_atan2(prim["atan_y"], prim["atan_x"])
+    assert np.array_equal(got.view(np.uint32), prim["atan"].view(np.uint32))
+    assert O.fast_atan2(np.float32([0]), np.float32([0]))[0] == 0.0
+    assert O.fast_atan2(np.float32([0]), np.float32([-5]))[0] == 180.0
+    assert O.fast_atan2(np.float32([-5]), np.float32([0]))[0] == 270.0
+    assert abs(float(O.fast_atan2(np.float32([1]), np.float32([1]))[0]) - 44.990456) < 1e-5
+
+
+def test_oracle_regression_vector():
+    g = np.load(os.path.join(GOLD, "oracle_frame.npz"))
+    nf, nl, ini, mn = (int(v) for v in g["params"])
+    kps, desc = O.Extractor(nf, 1.2, nl, ini, mn).extract(g["frame"])
+    assert np.array_equal(kps.view(np.uint8), g["kps"].view(np.uint8))
+    assert np.array_equal(desc, g["desc"])
+
+
+# ---- known answers derivable from the reference source ----------------------------------------------------------
+def test_constructor_tables():
+    # umax: src/ORBextractor.cc:540-555; quotas: :521-532
+    t = O.Extractor(2000, 1.2, 8, 20, 7).tables()
+    assert list(t["umax"]) == [15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3]
+    assert list(t["quota"]) == [434, 362, 302, 251, 209, 175, 145, 122]
+    assert list(O.Extractor(1000, 1.2, 8, 20, 7).tables()["quota"]) == [217, 181, 151, 126, 105, 87, 73, 60]
+    assert list(O.Extractor(1200, 1.2, 8, 20, 7).tables()["quota"]) == [261, 217, 181, 151, 126, 105, 87, 72]
+    sf = t["scale"]
+    assert sf[0] == 1.0 and sf[1] == np.float32(1.2)
+    for i in range(1, 8):
+        assert sf[i] == np.float32(np.float64(sf[i - 1]) * np.float64(np.float32(1.2)))
+    assert np.array_equal(t["sigma2"], sf * sf)
+    assert np.array_equal(t["inv_scale"], np.float32(1.0) / sf)
+
+
+def test_level_sizes():
+    # SURVEY.md §8 table (src/ORBextractor.cc:1843-1844)
+    want = {(376, 1241): [(1241, 376), (1034, 313), (862, 261), (718, 218), (598, 181), (499, 151), (416, 126), (346, 105)],
+            (480, 640): [(640, 480), (533, 400), (444, 333), (370, 278), (309, 231), (257, 193), (214, 161), (179, 134)],
+            (480, 752): [(752, 480), (627, 400), (522, 333), (435, 278), (363, 231), (302, 193), (252, 161), (210, 134)]}
+    for (h, w), sizes in want.items():
+        ox = O.Extractor(500, 1.2, 8, 20, 7)
+        ox.extract(np.zeros((h, w), np.uint8))
+        assert [ox.level_size(l) for l in range(8)] == sizes
+
+
+def test_pattern_table():
+    inc = os.path.join(os.path.dirname(GOLD), "..", "orb_slam_cuda_b200", "csrc", "orb_pattern_31.inc")
+    vals = []
+    for line in open(inc):
+        if line.startswith("//"):
+            continue
+        vals += [int(t) for t in line.replace(",", " ").split()]
+    assert len(vals) == 1024 and vals[:4] == [8, -3, 9, 5] and vals[-4:] == [-1, -6, 0, -11]
+    assert max(abs(v) for v in vals) <= 13
+
+
+def test_descriptor_distance_kat():
+    z, o = np.zeros(32, np.uint8), np.full(32, 255, np.uint8)
+    assert O.descriptor_distance(z, o) == 256 and O.descriptor_distance(o, o) == 0
+    rng = np.random.default_rng(0)
+    for _ in range(50):
+        a, b = rng.integers(0, 256, 32, dtype=np.uint8), rng.integers(0, 256, 32, dtype=np.uint8)
+        assert O.descriptor_distance(a, b) == int(np.unpackbits(a ^ b).sum())
+
+
+def test_cv_round_half_even():
+    assert [O.cv_round(v) for v in (0.5, 1.5, 2.5, -0.5, -1.5, 2.4999, 2.5001)] == [0, 2, 2, 0, -2, 2, 3]
+
+
+def test_empty_and_flat_images():
+    ox = O.Extractor(500, 1.2, 8, 20, 7)
+    k, d = ox.extract(np.full((120, 160), 77, np.uint8))
+    assert len(k) == 0 and d.shape == (0, 32)
+
+
+def test_bruteforce_semantics():
+    # first index wins ties; second == best when the minimum occurs twice (kills the ratio test)
+    rng = np.random.default_rng(5)
+    d = rng.integers(0, 256, (64, 32), dtype=np.uint8)
+    d[40] = d[7]
+    idx, d1, d2, m = O.match_bruteforce(d[[7, 3]].copy(), d, 50, 0.6)
+    assert list(idx) == [7, 3] and list(d1) == [0, 0] and d2[0] == 0 and m[0] == -1 and m[1] == 3
+    idx, d1, d2, m = O.match_bruteforce(d[:2].copy(), d[:0], 50, 0.6)
+    assert list(idx) == [-1, -1] and list(d1) == [256, 256] and list(m) == [-1, -1]
