@@ -1,0 +1,123 @@
+// include/ORBmatcher.h — the hot-path part of ORB_SLAM2::ORBmatcher (reference include/ORBmatcher.h:37-102,
+// src/ORBmatcher.cc) and Frame::ComputeStereoMatches (src/Frame.cc:465-639) over the C ABI of include/orbx.h.
+//
+// Kept from the reference surface: ORBmatcher(nnratio, checkOri), the static DescriptorDistance(const cv::Mat&,
+// const cv::Mat&), TH_LOW / TH_HIGH / HISTO_LENGTH, and SearchForInitialization with its reference signature.
+// SearchForInitialization and ComputeStereoMatches are templates over the frame type so that they bind to the
+// reference's ORB_SLAM2::Frame (its public members mvKeysUn, mDescriptors, mnMinX ... are used exactly as
+// src/ORBmatcher.cc does) without this repository carrying Frame.h.  The other ten matcher routines
+// (SearchByProjection x4, SearchByBoW x2, SearchForTriangulation, SearchBySim3, Fuse x2) are SURVEY.md §8f "next"
+// rows and stay in the reference's src/ORBmatcher.cc.
+//
+// Every call here runs on the device; there is no CPU implementation behind it (errors throw std::runtime_error).
+// DescriptorDistance on ONE pair is a kernel launch plus two small copies: callers with many pairs should use
+// DescriptorDistances (row-wise, one launch) or BruteForceMatch.
+#ifndef ORBMATCHER_H
+#define ORBMATCHER_H
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "ORBextractor.h"
+#include "orbx.h"
+#include "orbx_cv.h"
+
+namespace ORB_SLAM2 {
+
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {}
+
+    // Hamming distance between two ORB descriptors (rows of a CV_8U N x 32 matrix); src/ORBmatcher.cc:1647-1663
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) {
+        int d = 0;
+        check(orbx_hamming_distance(a.ptr<unsigned char>(), b.ptr<unsigned char>(), 1, &d), "DescriptorDistance");
+        return d;
+    }
+
+    // Row-wise distances of two continuous N x 32 descriptor tables in one launch.
+    static std::vector<int> DescriptorDistances(const cv::Mat& A, const cv::Mat& B) {
+        if (A.rows != B.rows || A.cols != 32 || B.cols != 32 || !A.isContinuous() || !B.isContinuous())
+            throw std::runtime_error("DescriptorDistances: two continuous N x 32 CV_8U tables expected");
+        std::vector<int> d(A.rows);
+        check(orbx_hamming_distance(A.ptr<unsigned char>(), B.ptr<unsigned char>(), A.rows, d.data()), "DescriptorDistances");
+        return d;
+    }
+
+    // Best / second-best of every row of Q in D with the acceptance test of the reference's inner loops
+    // (src/ORBmatcher.cc:187-232): vnMatches[i] = index into D, or -1.  Returns the number of matches.
+    int BruteForceMatch(const cv::Mat& Q, const cv::Mat& D, std::vector<int>& vnMatches, int th = 50 /* TH_LOW */,
+                        std::vector<int>* bestDist = nullptr, std::vector<int>* secondDist = nullptr) const {
+        if (Q.cols != 32 || (D.rows > 0 && D.cols != 32) || !Q.isContinuous() || !D.isContinuous())
+            throw std::runtime_error("BruteForceMatch: continuous N x 32 CV_8U tables expected");
+        vnMatches.assign(Q.rows, -1);
+        std::vector<int> idx(Q.rows), d1(Q.rows), d2(Q.rows);
+        check(orbx_match_bruteforce(Q.ptr<unsigned char>(), Q.rows, D.ptr<unsigned char>(), D.rows, th, mfNNratio, idx.data(),
+                                    d1.data(), d2.data(), vnMatches.data()),
+              "BruteForceMatch");
+        int n = 0;
+        for (int m : vnMatches) n += m >= 0;
+        if (bestDist) bestDist->swap(d1);
+        if (secondDist) secondDist->swap(d2);
+        return n;
+    }
+
+    // Matching for the Map Initialization (only used in the monocular case); src/ORBmatcher.cc:405-520.
+    // FrameT needs: mvKeysUn (std::vector<cv::KeyPoint>), mDescriptors (cv::Mat N x 32 CV_8U) and the static image
+    // bounds mnMinX, mnMaxX, mnMinY, mnMaxY — the members of ORB_SLAM2::Frame the reference routine reads.
+    template <class FrameT>
+    int SearchForInitialization(FrameT& F1, FrameT& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
+                                int windowSize = 10) {
+        const int n1 = (int)F1.mvKeysUn.size(), n2 = (int)F2.mvKeysUn.size();
+        vnMatches12 = std::vector<int>(n1, -1);
+        if (n1 == 0) return 0;
+        if ((int)vbPrevMatched.size() != n1) throw std::runtime_error("SearchForInitialization: vbPrevMatched size");
+        static_assert(sizeof(cv::KeyPoint) == sizeof(orbx_keypoint), "cv::KeyPoint layout");
+        static_assert(sizeof(cv::Point2f) == 8, "cv::Point2f layout");
+        const cv::Mat d1 = continuous(F1.mDescriptors), d2 = continuous(F2.mDescriptors);
+        const float bounds[4] = {(float)FrameT::mnMinX, (float)FrameT::mnMaxX, (float)FrameT::mnMinY, (float)FrameT::mnMaxY};
+        int nmatches = 0;
+        check(orbx_search_for_initialization(reinterpret_cast<const orbx_keypoint*>(F1.mvKeysUn.data()), n1,
+                                             d1.ptr<unsigned char>(), reinterpret_cast<const orbx_keypoint*>(F2.mvKeysUn.data()),
+                                             n2, d2.ptr<unsigned char>(), bounds, reinterpret_cast<float*>(vbPrevMatched.data()),
+                                             vnMatches12.data(), windowSize, mfNNratio, mbCheckOrientation ? 1 : 0, &nmatches),
+              "SearchForInitialization");
+        return nmatches;
+    }
+
+    static const int TH_LOW = 50;
+    static const int TH_HIGH = 100;
+    static const int HISTO_LENGTH = 30;
+
+    static void check(int rc, const char* what) {
+        if (rc != ORBX_OK) throw std::runtime_error(std::string(what) + ": " + orbx_last_error());
+    }
+    static cv::Mat continuous(const cv::Mat& m) { return m.isContinuous() ? m : m.clone(); }
+
+protected:
+    float mfNNratio;
+    bool mbCheckOrientation;
+};
+
+// Frame::ComputeStereoMatches (src/Frame.cc:465-639) for a frame whose two extractors are ORB_SLAM2::ORBextractor
+// objects of this library: reads mvKeys / mvKeysRight / mDescriptors / mDescriptorsRight / mbf / mb / N and the two
+// extractor pointers, fills mvuRight and mvDepth.  The pyramids are read where they already are — in device memory —
+// so mvImagePyramid need not be copied to the host for it.  Body of the reference member function becomes
+//     ORB_SLAM2::ComputeStereoMatches(*this);
+template <class FrameT> void ComputeStereoMatches(FrameT& F) {
+    const int N = (int)F.mvKeys.size(), Nr = (int)F.mvKeysRight.size();
+    F.mvuRight = std::vector<float>(N, -1.0f);
+    F.mvDepth = std::vector<float>(N, -1.0f);
+    if (N == 0) return;
+    const cv::Mat dL = ORBmatcher::continuous(F.mDescriptors), dR = ORBmatcher::continuous(F.mDescriptorsRight);
+    ORBmatcher::check(orbx_stereo_match(F.mpORBextractorLeft->handle(), F.mpORBextractorRight->handle(),
+                                        reinterpret_cast<const orbx_keypoint*>(F.mvKeys.data()), N, dL.template ptr<unsigned char>(),
+                                        reinterpret_cast<const orbx_keypoint*>(F.mvKeysRight.data()), Nr,
+                                        dR.template ptr<unsigned char>(), F.mbf, F.mb, F.mvuRight.data(), F.mvDepth.data()),
+                      "ComputeStereoMatches");
+}
+
+}  // namespace ORB_SLAM2
+
+#endif  // ORBMATCHER_H

@@ -143,9 +143,11 @@ int orbx_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_
                                    int window, float nnratio, int check_ori, int* nmatches);
 
 /* Frame::ComputeStereoMatches (src/Frame.cc:465-639).  exL / exR hold the pyramids of the left / right frame of
- * their last orbx_extract call.  u_right[nL], depth[nL] as mvuRight / mvDepth (-1 = no match).  Host buffers. */
+ * their last orbx_extract call (device resident; nothing is copied to the host).  bf = mbf (baseline x fx),
+ * mb = baseline in metres = mbf / fx (src/Frame.cc:113).  u_right[nL], depth[nL] as mvuRight / mvDepth
+ * (-1 = no match).  Host buffers. */
 int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypoint* kL, int nL, const uint8_t* descL,
-                      const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float fx, float* u_right,
+                      const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float mb, float* u_right,
                       float* depth);
 
 #ifdef __cplusplus

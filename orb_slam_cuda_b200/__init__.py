@@ -283,5 +283,5 @@ def ComputeStereoMatches(exL: ORBextractor, exR: ORBextractor, kpsL, descL, kpsR
     u = np.empty(max(kpsL.size, 1), np.float32)
     z = np.empty(max(kpsL.size, 1), np.float32)
     _check(lib().orbx_stereo_match(exL._h, exR._h, _p(kpsL), kpsL.size, _p(descL), _p(kpsR), kpsR.size, _p(descR),
-                                   C.c_float(bf), C.c_float(fx), _p(u), _p(z)))
+                                   C.c_float(bf), C.c_float(np.float32(bf) / np.float32(fx)), _p(u), _p(z)))
     return u[:kpsL.size], z[:kpsL.size]

@@ -51,5 +51,27 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return SO
 
 
+CLASSES_SO = os.path.join(HERE, "liborbx_classes.so")
+HARNESS = os.path.join(HERE, "..", "tests", "cpp", "frame_harness")
+
+
+def build_host(force: bool = False) -> str:
+    """The C++ class layer (ORB_SLAM2::ORBextractor over the C ABI) and the Frame-shaped harness of the tests."""
+    inc = os.path.join(HERE, "..", "include")
+    src = os.path.join(HERE, "host", "ORBextractor.cc")
+    hdrs = [os.path.join(inc, f) for f in os.listdir(inc)]
+    cxx = os.environ.get("CXX", "g++")
+    flags = ["-std=c++17", "-O2", "-fPIC", "-Wall", "-Wextra", "-ffp-contract=off", "-I", inc]
+    if force or not os.path.exists(CLASSES_SO) or any(os.path.getmtime(d) > os.path.getmtime(CLASSES_SO) for d in hdrs + [src, SO]):
+        subprocess.check_call([cxx] + flags + ["-shared", src, "-o", CLASSES_SO, "-L", HERE, "-lorbx", "-Wl,-rpath,$ORIGIN"])
+    hsrc = os.path.join(HERE, "..", "tests", "cpp", "frame_harness.cpp")
+    if os.path.exists(hsrc) and (force or not os.path.exists(HARNESS) or
+                                 any(os.path.getmtime(d) > os.path.getmtime(HARNESS) for d in hdrs + [hsrc, CLASSES_SO])):
+        subprocess.check_call([cxx] + flags + [hsrc, "-o", HARNESS, "-L", HERE, "-lorbx_classes", "-lorbx", "-pthread",
+                                               "-Wl,-rpath,$ORIGIN/../../orb_slam_cuda_b200"])
+    return CLASSES_SO
+
+
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build_host(force="--force" in sys.argv))

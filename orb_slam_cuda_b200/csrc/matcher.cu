@@ -172,7 +172,7 @@ int orbx_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_
 }
 
 int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypoint* kL, int nL, const uint8_t* descL,
-                      const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float fx, float* u_right, float* depth) {
+                      const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float mb, float* u_right, float* depth) {
     ExtractorView L, R;
     int rc;
     if ((rc = extractor_view(exL, &L)) || (rc = extractor_view(exR, &R))) return rc;
@@ -204,7 +204,6 @@ int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypo
         lv.scale[l] = L.scale[l];       // Frame copies the LEFT extractor's tables (src/Frame.cc:68-74)
         lv.invScale[l] = L.invScale[l];
     }
-    const float mb = bf / fx;        // mb = mbf / fx (src/Frame.cc:113)
     const float maxD = bf / mb;      // minZ = mb, maxD = mbf / minZ (:494-496)
     const size_t fb = (size_t)nL * 4;
     if ((rc = upload(w->a, kL, (size_t)nL * sizeof(orbx_keypoint), s)) || (rc = upload(w->b, descL, (size_t)nL * 32, s)) ||

@@ -1,0 +1,113 @@
+// tests/cpp/frame_harness.cpp — a Frame-shaped C++ caller of the class surface (include/ORBextractor.h,
+// include/ORBmatcher.h), written the way the reference's src/Frame.cc and src/Tracking.cc use it:
+//   Frame::Frame(mono)    : ExtractORB(0, im) -> (*mpORBextractorLeft)(im, cv::Mat(), mvKeys, mDescriptors)   (:246-252)
+//   Frame::Frame(stereo)  : two std::threads, one extractor per eye (:77-80), then ComputeStereoMatches (:89)
+//   Tracking::MonocularInitialization : ORBmatcher(0.9, true).SearchForInitialization(F1, F2, prev, m12, 100) (:671)
+// Input: a raw file of 8-bit frames; output: a raw dump that tests/test_cpp_boundary.py compares with the CPU oracle.
+//   frame_harness mono   in.raw w h nfeatures out.bin          (two frames: extraction + SearchForInitialization)
+//   frame_harness stereo in.raw w h nfeatures bf fx out.bin    (left, right: extraction + ComputeStereoMatches)
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+
+using namespace ORB_SLAM2;
+
+struct Frame {  // the members of ORB_SLAM2::Frame that the front end reads or writes (include/Frame.h)
+    ORBextractor *mpORBextractorLeft = nullptr, *mpORBextractorRight = nullptr;
+    std::vector<cv::KeyPoint> mvKeys, mvKeysRight, mvKeysUn;
+    cv::Mat mDescriptors, mDescriptorsRight;
+    std::vector<float> mvuRight, mvDepth;
+    float mbf = 0, mb = 0;
+    int N = 0;
+    static float mnMinX, mnMaxX, mnMinY, mnMaxY;
+    void ExtractORB(int flag, const cv::Mat& im) {  // src/Frame.cc:246-252
+        if (flag == 0) (*mpORBextractorLeft)(im, cv::Mat(), mvKeys, mDescriptors);
+        else (*mpORBextractorRight)(im, cv::Mat(), mvKeysRight, mDescriptorsRight);
+    }
+};
+float Frame::mnMinX, Frame::mnMaxX, Frame::mnMinY, Frame::mnMaxY;
+
+static void put(FILE* f, const void* p, size_t n) { if (n && fwrite(p, 1, n, f) != n) { perror("fwrite"); exit(3); } }
+static void put_i(FILE* f, int v) { put(f, &v, 4); }
+static void put_keys(FILE* f, const std::vector<cv::KeyPoint>& k, const cv::Mat& d) {
+    put_i(f, (int)k.size());
+    put(f, k.data(), k.size() * sizeof(cv::KeyPoint));
+    for (int i = 0; i < d.rows; ++i) put(f, d.ptr(i), 32);
+}
+
+int main(int argc, char** argv) {
+    if (argc < 7) { fprintf(stderr, "usage: see the header comment\n"); return 2; }
+    const std::string mode = argv[1];
+    const int w = atoi(argv[3]), h = atoi(argv[4]), nf = atoi(argv[5]);
+    std::vector<unsigned char> raw((size_t)2 * w * h);
+    FILE* in = fopen(argv[2], "rb");
+    if (!in || fread(raw.data(), 1, raw.size(), in) != raw.size()) { fprintf(stderr, "cannot read two %dx%d frames from %s\n", w, h, argv[2]); return 2; }
+    fclose(in);
+    cv::Mat im0(h, w, CV_8UC1, raw.data()), im1(h, w, CV_8UC1, raw.data() + (size_t)w * h);
+    try {
+        if (mode == "mono") {
+            FILE* out = fopen(argv[6], "wb");
+            ORBextractor ex(nf, 1.2f, 8, 20, 7, w, h);  // the reference's 7-argument constructor (src/Tracking.cc:127)
+            Frame F1, F2;
+            F1.mpORBextractorLeft = F2.mpORBextractorLeft = &ex;
+            Frame::mnMinX = 0; Frame::mnMaxX = (float)w; Frame::mnMinY = 0; Frame::mnMaxY = (float)h;  // no distortion (:441-446)
+            F1.ExtractORB(0, im0);
+            // mvImagePyramid of the first frame: level 1, including one pixel of the border through the parent
+            const cv::Mat& L1 = ex.mvImagePyramid[1];
+            put_i(out, L1.cols); put_i(out, L1.rows);
+            for (int r = 0; r < L1.rows; ++r) put(out, L1.ptr(r), L1.cols);
+            put(out, L1.ptr(0) - L1.step - 1, 1);  // pixel (-1, -1): reflect-101 border, inside the parent allocation
+            F2.ExtractORB(0, im1);
+            F1.mvKeysUn = F1.mvKeys; F2.mvKeysUn = F2.mvKeys;
+            put_keys(out, F1.mvKeys, F1.mDescriptors);
+            put_keys(out, F2.mvKeys, F2.mDescriptors);
+            std::vector<cv::Point2f> prev(F1.mvKeysUn.size());
+            for (size_t i = 0; i < prev.size(); ++i) prev[i] = F1.mvKeysUn[i].pt;
+            std::vector<int> m12;
+            ORBmatcher matcher(0.9f, true);
+            const int n = matcher.SearchForInitialization(F1, F2, prev, m12, 100);
+            put_i(out, n);
+            put(out, m12.data(), m12.size() * 4);
+            put(out, prev.data(), prev.size() * 8);
+            // accessors + DescriptorDistance + empty image behaviour
+            put_i(out, ex.GetLevels());
+            std::vector<float> sf = ex.GetScaleFactors(), is2 = ex.GetInverseScaleSigmaSquares();
+            put(out, sf.data(), sf.size() * 4); put(out, is2.data(), is2.size() * 4);
+            put_i(out, ORBmatcher::DescriptorDistance(F1.mDescriptors.row(0), F2.mDescriptors.row(0)));
+            std::vector<cv::KeyPoint> keep(3);
+            cv::Mat keepD(2, 32, CV_8U);
+            ex(cv::Mat(), cv::Mat(), keep, keepD);  // silent return, outputs untouched (src/ORBextractor.cc:1542-1543)
+            put_i(out, (int)keep.size() * 100 + keepD.rows);
+            fclose(out);
+        } else if (mode == "stereo" && argc >= 9) {
+            FILE* out = fopen(argv[8], "wb");
+            ORBextractor exL(nf, 1.2f, 8, 20, 7), exR(nf, 1.2f, 8, 20, 7);  // upstream's 5-argument form
+            exL.keepImagePyramid = exR.keepImagePyramid = false;            // the stereo matcher reads device memory
+            Frame F;
+            F.mpORBextractorLeft = &exL; F.mpORBextractorRight = &exR;
+            F.mbf = (float)atof(argv[6]);
+            F.mb = F.mbf / (float)atof(argv[7]);
+            std::thread tl([&] { F.ExtractORB(0, im0); }), tr([&] { F.ExtractORB(1, im1); });  // src/Frame.cc:77-80
+            tl.join(); tr.join();
+            F.N = (int)F.mvKeys.size();
+            ComputeStereoMatches(F);
+            put_keys(out, F.mvKeys, F.mDescriptors);
+            put_keys(out, F.mvKeysRight, F.mDescriptorsRight);
+            put(out, F.mvuRight.data(), F.mvuRight.size() * 4);
+            put(out, F.mvDepth.data(), F.mvDepth.size() * 4);
+            fclose(out);
+        } else {
+            return 2;
+        }
+    } catch (const std::exception& e) {
+        fprintf(stderr, "frame_harness: %s\n", e.what());
+        return 1;
+    }
+    return 0;
+}

@@ -1,0 +1,122 @@
+"""The C++ class surface (include/ORBextractor.h, include/ORBmatcher.h) driven the way the reference's Frame.cc /
+Tracking.cc drive it, through tests/cpp/frame_harness.cpp.  CPU part: it compiles, links and refuses to run without
+a device.  GPU part: its outputs equal the CPU oracle's bit for bit."""
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import oracle_lib as O
+from orb_slam_cuda_b200 import build as B
+from orb_slam_cuda_b200 import synth
+import orb_slam_cuda_b200 as X
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HARNESS = os.path.join(ROOT, "tests", "cpp", "frame_harness")
+
+
+@pytest.fixture(scope="module")
+def harness():
+    B.build()
+    B.build_host()
+    assert os.path.exists(HARNESS)
+    return HARNESS
+
+
+def _has_gpu():
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def test_class_layer_builds_and_fails_loudly_without_a_device(harness, tmp_path):
+    assert os.path.exists(B.CLASSES_SO)
+    if _has_gpu():
+        pytest.skip("a device is present; the refusal path is checked on CPU boxes")
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(bytes(2 * 64 * 48))
+    r = subprocess.run([harness, "mono", str(raw), "64", "48", "100", str(tmp_path / "o.bin")], capture_output=True, text=True)
+    assert r.returncode == 1 and "no CPU path" in r.stderr
+
+
+class Reader:
+    def __init__(self, b):
+        self.b, self.o = b, 0
+
+    def i32(self):
+        v = struct.unpack_from("<i", self.b, self.o)[0]
+        self.o += 4
+        return v
+
+    def arr(self, dtype, n):
+        a = np.frombuffer(self.b, dtype=dtype, count=n, offset=self.o).copy()
+        self.o += a.nbytes
+        return a
+
+    def keys(self):
+        n = self.i32()
+        return self.arr(X.KP_DTYPE, n), self.arr(np.uint8, n * 32).reshape(n, 32)
+
+
+@pytest.mark.gpu
+def test_mono_frame_and_initialization(harness, tmp_path):
+    kind, nf = "tum", 1000
+    a, b = synth.frame(kind, 40), synth.shifted_frame(kind, 40)
+    h, w = a.shape
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(a.tobytes() + b.tobytes())
+    out = tmp_path / "out.bin"
+    r = subprocess.run([harness, "mono", str(raw), str(w), str(h), str(nf), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    rd = Reader(out.read_bytes())
+    ox = O.Extractor(nf, 1.2, 8, 20, 7)
+    k1, d1 = ox.extract(a)
+    lw, lh = rd.i32(), rd.i32()
+    assert (lw, lh) == ox.level_size(1)
+    lvl = rd.arr(np.uint8, lw * lh).reshape(lh, lw)
+    pad = ox.level_padded(1)
+    assert np.array_equal(lvl, pad[19:-19, 19:-19])
+    assert rd.arr(np.uint8, 1)[0] == pad[18, 18]
+    k2, d2 = ox.extract(b)
+    gk1, gd1 = rd.keys()
+    gk2, gd2 = rd.keys()
+    assert np.array_equal(gk1.view(np.uint8), k1.view(np.uint8)) and np.array_equal(gd1, d1)
+    assert np.array_equal(gk2.view(np.uint8), k2.view(np.uint8)) and np.array_equal(gd2, d2)
+    prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+    n_ref, m_ref, prev_ref = O.search_for_initialization(k1, d1, k2, d2, (0.0, float(w), 0.0, float(h)), prev, 100, 0.9, True)
+    assert rd.i32() == n_ref and n_ref > 20
+    assert np.array_equal(rd.arr(np.int32, len(k1)), m_ref)
+    assert np.array_equal(rd.arr(np.float32, 2 * len(k1)).view(np.uint32), prev_ref.ravel().view(np.uint32))
+    t = ox.tables()
+    assert rd.i32() == 8
+    assert np.array_equal(rd.arr(np.float32, 8), t["scale"]) and np.array_equal(rd.arr(np.float32, 8), t["inv_sigma2"])
+    assert rd.i32() == O.descriptor_distance(d1[0], d2[0])
+    assert rd.i32() == 302  # the empty-image call left 3 keypoints and the 2-row descriptor matrix untouched
+
+
+@pytest.mark.gpu
+def test_stereo_frame(harness, tmp_path):
+    left, right = synth.stereo_pair("euroc", 9)
+    h, w = left.shape
+    bf, fx = 47.90639384423901, 435.2046959714599
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(left.tobytes() + right.tobytes())
+    out = tmp_path / "out.bin"
+    r = subprocess.run([harness, "stereo", str(raw), str(w), str(h), "1200", repr(bf), repr(fx), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    rd = Reader(out.read_bytes())
+    oL, oR = O.Extractor(1200, 1.2, 8, 20, 7), O.Extractor(1200, 1.2, 8, 20, 7)
+    kL, dL = oL.extract(left)
+    kR, dR = oR.extract(right)
+    gkL, gdL = rd.keys()
+    gkR, gdR = rd.keys()
+    assert np.array_equal(gkL.view(np.uint8), kL.view(np.uint8)) and np.array_equal(gdL, dL)
+    assert np.array_equal(gkR.view(np.uint8), kR.view(np.uint8)) and np.array_equal(gdR, dR)
+    u_ref, z_ref = O.stereo_matches(oL, oR, kL, dL, kR, dR, float(np.float32(bf)), float(np.float32(fx)))
+    u, z = rd.arr(np.float32, len(kL)), rd.arr(np.float32, len(kL))
+    assert (u_ref >= 0).sum() > 100
+    assert np.array_equal(u.view(np.uint32), u_ref.view(np.uint32)) and np.array_equal(z.view(np.uint32), z_ref.view(np.uint32))
