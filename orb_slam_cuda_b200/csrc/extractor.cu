@@ -64,7 +64,7 @@ struct orbx_extractor {
     TmaMaps fastMaps{}, blurMaps{};
     std::vector<int> areaFast;
     DevBuf planes[ORBX_MAX_LEVELS], blurs[ORBX_MAX_LEVELS], xtab[ORBX_MAX_LEVELS], ytab[ORBX_MAX_LEVELS];
-    DevBuf cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, lvlAngles, status, dFrames, dKps, dDesc, dCounts;
+    DevBuf strips, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, lvlAngles, status, dFrames, dKps, dDesc, dCounts;
     PinBuf hFrames, hKps, hDesc, hCounts, hStatus;
     // host copies of pyramid levels for mvImagePyramid readers
     std::vector<uint8_t> hostLevel[ORBX_MAX_LEVELS];
@@ -193,7 +193,8 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
     g.nlevels = nl;
     g.iniTh = ex->prm.ini_th_fast;
     g.minTh = ex->prm.min_th_fast;
-    int cellBase = 0, slotBase = 0, tileBase = 0, maxWCell = 0, maxHCell = 0;
+    int cellBase = 0, slotBase = 0, tileBase = 0, maxStripW = 0, maxHCell = 0;
+    std::vector<FastStrip> strips;
     long long qtBase = 0;
     ex->areaFast.assign(nl, 0);
     for (int l = 0; l < nl; ++l) {
@@ -222,8 +223,16 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
         } else {
             L.wCell = (int)std::ceil(width / L.nCols);
             L.hCell = (int)std::ceil(height / L.nRows);
-            maxWCell = std::max(maxWCell, L.wCell);
             maxHCell = std::max(maxHCell, L.hCell);
+            // FAST strips: every cell row is cut into runs of `per` cells, sizes balanced
+            const int per = fast_cells_per_strip(L.wCell, L.nCols);
+            const int nRuns = (L.nCols + per - 1) / per;
+            for (int i = 0; i < L.nRows; ++i)
+                for (int r = 0; r < nRuns; ++r) {
+                    const int j0 = (int)((long long)L.nCols * r / nRuns), j1 = (int)((long long)L.nCols * (r + 1) / nRuns);
+                    strips.push_back(FastStrip{(uint16_t)l, (uint16_t)i, (uint16_t)j0, (uint16_t)(j1 - j0)});
+                    maxStripW = std::max(maxStripW, (j1 - j0) * L.wCell);
+                }
         }
         L.cellBase = cellBase;
         cellBase += L.nCols * L.nRows;
@@ -254,7 +263,8 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
     g.slotsTotal = slotBase;
     g.qtFrameStride = qtBase;
     g.blurTilesTotal = tileBase;
-    g.fastBoxW = (int)round_up(std::max(maxWCell, 1) + 6 + 15, 16);  // + alignment slack of the box origin
+    g.nStrips = (int)strips.size();
+    g.fastBoxW = (int)round_up(std::max(maxStripW, 1) + 6 + 15, 16);  // + alignment slack of the box origin
     g.fastBoxH = std::max(maxHCell, 1) + 6;
     if (g.fastBoxW > 256 || g.fastBoxH > 256 || g.fastBoxW * g.fastBoxH > 60000) {
         set_error("FAST cell window %d x %d exceeds the TMA box limit", g.fastBoxW, g.fastBoxH);
@@ -287,6 +297,8 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
             ORBX_CUDA(cudaMemcpy(ex->ytab[l].p, yt.data(), yt.size() * sizeof(ResizeTab), cudaMemcpyHostToDevice));
         }
     }
+    if ((rc = ex->strips.ensure(std::max<size_t>(strips.size(), 1) * sizeof(FastStrip)))) return rc;
+    ORBX_CUDA(cudaMemcpy(ex->strips.p, strips.data(), strips.size() * sizeof(FastStrip), cudaMemcpyHostToDevice));
     if ((rc = ex->cellCnt.ensure((size_t)batch * g.nCellsTotal * 4))) return rc;
     if ((rc = ex->cellKeys.ensure((size_t)batch * g.nCellsTotal * CELL_CAP * 4))) return rc;
     if ((rc = ex->qtScratch.ensure((size_t)batch * g.qtFrameStride * 4))) return rc;
@@ -337,7 +349,7 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
             return rc;
     if ((rc = stage_sync("Pyramid/Resize", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
-    if ((rc = launch_fast(g, ex->fastMaps, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), dStatus, s))) return rc;
+    if ((rc = launch_fast(g, ex->fastMaps, ex->strips.as<FastStrip>(), batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), dStatus, s))) return rc;
     if ((rc = stage_sync("FAST+Grid", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
     if ((rc = launch_quadtree(g, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), ex->qtScratch.as<uint32_t>(),
@@ -449,7 +461,7 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
     for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
         ex->planes[l].release(); ex->blurs[l].release(); ex->xtab[l].release(); ex->ytab[l].release();
     }
-    for (DevBuf* b : {&ex->cellCnt, &ex->cellKeys, &ex->qtScratch, &ex->lvlCnt, &ex->lvlKeys, &ex->lvlAngles, &ex->status,
+    for (DevBuf* b : {&ex->strips, &ex->cellCnt, &ex->cellKeys, &ex->qtScratch, &ex->lvlCnt, &ex->lvlKeys, &ex->lvlAngles, &ex->status,
                       &ex->dFrames, &ex->dKps, &ex->dDesc, &ex->dCounts})
         b->release();
     for (PinBuf* b : {&ex->hFrames, &ex->hKps, &ex->hDesc, &ex->hCounts, &ex->hStatus}) b->release();

@@ -1,24 +1,35 @@
 // csrc/k_fast.cu — per-30-px-cell FAST-9/16 with the iniThFAST -> minThFAST fallback and 3x3 score non-max
 // suppression (reference src/ORBextractor.cc:1122-1149 grid set-up, :1256-1299 per-cell cv::FAST calls).
 //
-// One CTA per (cell, frame).  The cell window [ini, ini + cell + 6) (clipped to maxBorder, :1258-1275) is staged
-// into shared memory by one TMA box load from the padded plane (box origin rounded down to 16 bytes); then, at threshold t = iniThFAST:
-//   A. every detectable pixel (window minus cv::FAST's 3-px rim) takes the 4-point antipodal quick test; survivors
-//      are appended to a shared list (warp-aggregated atomics),
-//   B. survivors run the full 16-point segment test (bit-mask run detection) and, for corners, the OpenCV
-//      cornerScore<16> value = max over the 16 arcs of 9 of the minimum |difference|, minus 1 (doubling minima),
-//      written to a shared score tile (0 = not a corner),
-//   C. corners strictly greater than their 8 neighbours in the score tile survive (rim pixels score 0, exactly
-//      like the zero-initialised score rows of cv::FAST, so NMS never looks across a cell seam),
-//   D. survivors are ranked by position, giving cv::FAST's row-major output order, and stored into the cell's slot.
-// If no keypoint survives, A-D run again at minThFAST (:1281-1285).  Scores do not depend on the threshold.
+// The reference calls cv::FAST once or twice per 30-px cell on the window [ini, ini + cell + 6) (:1258-1275).
+// cv::FAST ignores a 3-px rim, so the DETECTABLE regions [ini + 3, ini + cell + 3) tile a level exactly, and a pixel's
+// corner score does not depend on the cell it is in.  What is per cell is (a) non-max suppression — rim pixels are
+// never scored, so NMS must not look across a cell seam — and (b) the fallback to minThFAST when the cell produced no
+// keypoint.  One CTA therefore handles a STRIP of several horizontally adjacent cells of one cell row:
+//   tile   the strip's window is staged into shared memory by one TMA box load (origin rounded down to 16 bytes);
+//   A      quick reject, four pixels per lane as packed bytes: VABSDIFF4 + carry-less byte compares give, for ring
+//          points 0/4/8/12, the flags |r - v| > t and r > v; a pixel survives if both antipodal pairs hold a brighter
+//          (or both a darker) point.  Warps walk rows, lanes walk 32-bit words, so there is no index division;
+//   B1     survivors (dense list) take the full 16-point segment test (bit-mask run-of-9 detection);
+//   B2     corners (dense list) get OpenCV's cornerScore<16>: max over the 16 arcs of 9 of the min |difference|, both
+//          polarities, minus 1, stored in a shared score tile (0 = not a corner);
+//   C      corners strictly greater than their 8 neighbours OF THE SAME CELL survive and are counted per cell;
+//   pass 2 cells that are still empty repeat A-C at minThFAST (:1281-1285); pixels of other cells are masked out;
+//   D      survivors are ranked by position inside their cell (cv::FAST's row-major order) and written to the cell's slot.
 //
-// Roofline: each level pixel is read once from HBM/L2 (windows of neighbouring cells overlap by 6 px and hit L2);
-// the kernel itself is integer-ALU / shared-memory bound, not HBM bound.
+// Roofline: reads every level pixel once (strip windows overlap by 6 px and hit L2); the kernel is bound by the
+// integer pipe, not by HBM.
+#include <vector>
+
 #include "orbx_internal.h"
 #include "tma.cuh"
 
 namespace orbx {
+
+constexpr int FS_THREADS = 256;
+constexpr int FS_LIST1 = 2048;  // quick-test survivors per row chunk
+constexpr int FS_LIST2 = 1024;  // corners per strip and pass
+constexpr int FS_KP = 1024;     // keypoints per strip
 
 __constant__ int c_ringDx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
 __constant__ int c_ringDy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
@@ -48,149 +59,269 @@ __device__ __forceinline__ int best_arc_min(const int (&e)[16]) {
     return best;
 }
 
-__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_constant__ FrameGeom g,
-                                                              const __grid_constant__ TmaMaps maps,
-                                                              int* __restrict__ cellCnt, uint32_t* __restrict__ cellKeys,
-                                                              int* __restrict__ dStatus) {
+// per-byte unsigned a > b: the most significant bit of every byte of the result is the flag (other bits are junk)
+__device__ __forceinline__ uint32_t gtu4_msb(uint32_t a, uint32_t b, uint32_t notb7) {
+    const uint32_t s = (a & 0x7f7f7f7fu) + notb7;  // notb7 = ~b & 0x7f7f7f7f; bit 7 of each byte = (a & 127) > (b & 127)
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xb2;" : "=r"(r) : "r"(a), "r"(b), "r"(s));  // a7 & ~b7 | ~(a7 ^ b7) & s7
+    return r;
+}
+
+struct FastShared {
+    uint8_t* tile;
+    uint8_t* score;
+    uint8_t* act;        // per tile column: 0x80 where the quick test is enabled in this pass
+    uint8_t* cellOfCol;  // per tile column: cell index inside the strip, 255 = not detectable
+    uint16_t* list1;
+    uint16_t* list2;
+    uint32_t* kp;        // cell << 24 | pos << 8 | score
+    int* cnt;            // [0],[1] n1 (ping-pong per chunk), [2] n2, [3] nkp, [4] pass-2 needed, [5..] per-cell counts
+    uint64_t* bar;
+};
+
+__global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constant__ FrameGeom g,
+                                                             const __grid_constant__ TmaMaps maps,
+                                                             const FastStrip* __restrict__ strips,
+                                                             int* __restrict__ cellCnt, uint32_t* __restrict__ cellKeys,
+                                                             int* __restrict__ dStatus) {
     extern __shared__ __align__(128) uint8_t smem[];
-    const int TW = g.fastBoxW, TH = g.fastBoxH, TN = TW * TH;
-    uint8_t* tile = smem;
-    uint8_t* score = smem + TN;
-    uint16_t* list1 = reinterpret_cast<uint16_t*>(smem + 2 * TN);
-    uint32_t* list2 = reinterpret_cast<uint32_t*>(smem + 4 * TN);
-    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 4 * TN + CELL_CAP * 4);
-    int* cnt = reinterpret_cast<int*>(bar + 1);  // cnt[0] = n1, cnt[1] = n2
+    const int TW = g.fastBoxW, TH = g.fastBoxH, TN = TW * TH, TWq = TW >> 2;
+    FastShared S;
+    S.tile = smem;
+    S.score = smem + TN;
+    S.act = smem + 2 * TN;
+    S.cellOfCol = S.act + TW;
+    S.list1 = reinterpret_cast<uint16_t*>(S.cellOfCol + TW);
+    S.list2 = S.list1 + FS_LIST1;
+    S.kp = reinterpret_cast<uint32_t*>(S.list2 + FS_LIST2);
+    S.cnt = reinterpret_cast<int*>(S.kp + FS_KP);
+    S.bar = reinterpret_cast<uint64_t*>(S.cnt + 16);
 
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int f = blockIdx.y;
-    int cell = blockIdx.x, level = 0;
-    while (level + 1 < g.nlevels && cell >= g.lv[level + 1].cellBase) ++level;
-    const LevelGeom& L = g.lv[level];
-    cell -= L.cellBase;
-    const int ci = cell / L.nCols, cj = cell - ci * L.nCols;
-    int* outCnt = cellCnt + (long long)f * g.nCellsTotal + blockIdx.x;
-    uint32_t* outKeys = cellKeys + ((long long)f * g.nCellsTotal + blockIdx.x) * CELL_CAP;
+    const FastStrip st = strips[blockIdx.x];
+    const LevelGeom& L = g.lv[st.level];
+    const int ci = st.ci, cj0 = st.cj0, nc = st.nc;
+    const int cellGlobal0 = L.cellBase + ci * L.nCols + cj0;
+    int* outCnt = cellCnt + (long long)f * g.nCellsTotal + cellGlobal0;
+    uint32_t* outKeys = cellKeys + ((long long)f * g.nCellsTotal + cellGlobal0) * CELL_CAP;
 
-    // window of this cell (src/ORBextractor.cc:1258-1275)
-    const int iniY = L.minBY + ci * L.hCell, iniX = L.minBX + cj * L.wCell;
-    const int maxY = min(iniY + L.hCell + 6, L.maxBY), maxX = min(iniX + L.wCell + 6, L.maxBX);
-    const int ww = maxX - iniX, wh = maxY - iniY;
-    if (iniY >= L.maxBY - 3 || iniX >= L.maxBX - 6 || ww < 7 || wh < 7) {
-        if (tid == 0) *outCnt = 0;
+    // window of the strip (src/ORBextractor.cc:1258-1275): rows of cell row ci, columns of cells cj0 .. cj0 + nc - 1
+    const int iniY = L.minBY + ci * L.hCell, iniX = L.minBX + cj0 * L.wCell;
+    const int maxY = min(iniY + L.hCell + 6, L.maxBY);
+    const int dH = (iniY >= L.maxBY - 3) ? 0 : maxY - iniY - 6;  // detectable rows
+    // detectable columns: cell j is valid unless iniX_j >= maxBX - 6 or its window is narrower than 7 px
+    int dW = 0;
+    for (int j = 0; j < nc; ++j) {
+        const int ix = iniX + j * L.wCell;
+        const int mx = min(ix + L.wCell + 6, L.maxBX);
+        if (ix < L.maxBX - 6 && mx - ix >= 7) dW = j * L.wCell + (mx - ix - 6);
+    }
+    if (dH < 1 || dW < 1) {
+        if (tid < nc) outCnt[tid] = 0;
         return;
     }
     if (tid == 0) {
-        mbar_init(bar, 1);
+        mbar_init(S.bar, 1);
         fence_mbar_init();
     }
     __syncthreads();
     if (tid == 0) {
-        mbar_expect_tx(bar, (uint32_t)TN);
-        tma_load_3d(tile, &maps.m[level], (XOFF + iniX) & ~15, EDGE + iniY, f, bar);  // box origin must be 16-byte aligned
+        mbar_expect_tx(S.bar, (uint32_t)TN);
+        tma_load_3d(S.tile, &maps.m[st.level], (XOFF + iniX) & ~15, EDGE + iniY, f, S.bar);  // box origin 16-byte aligned
     }
-    const int dW = ww - 6, dH = wh - 6, npx = dW * dH;
     const int xo = (XOFF + iniX) & 15;  // window column 0 inside the box
-    mbar_wait(bar, 0);
+    const int X0 = xo + 3;              // first detectable tile column
+    const int wq0 = X0 >> 2, nW = ((X0 + dW + 3) >> 2) - wq0;
+    // while the tile is in flight: clear the score tile, set up the column tables and counters
+    for (int i = tid; i < TN / 4; i += FS_THREADS) reinterpret_cast<uint32_t*>(S.score)[i] = 0;
+    for (int x = tid; x < TW; x += FS_THREADS) {
+        const int dx = x - X0;
+        const bool det = dx >= 0 && dx < dW;
+        S.cellOfCol[x] = det ? (uint8_t)(dx / L.wCell) : (uint8_t)255;
+        S.act[x] = det ? 0x80 : 0;
+    }
+    if (tid < 16) S.cnt[tid] = 0;
+    __syncthreads();
+    mbar_wait(S.bar, 0);
 
-    int n2 = 0;
+    const uint32_t* tile32 = reinterpret_cast<const uint32_t*>(S.tile);
+    const uint32_t* act32 = reinterpret_cast<const uint32_t*>(S.act);
+    const int rowsPerChunk = max(1, FS_LIST1 / (nW * 4));
+    int off[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) off[k] = c_ringDy[k] * TW + c_ringDx[k];
+
+    int par = 0;  // which n1 counter the current chunk appends to
     for (int pass = 0; pass < 2; ++pass) {
         const int t = min(max(pass == 0 ? g.iniTh : g.minTh, 0), 255);
-        if (tid < 2) cnt[tid] = 0;
-        for (int i = tid; i < TN / 4; i += FAST_THREADS) reinterpret_cast<uint32_t*>(score)[i] = 0;
-        __syncthreads();
-        // ---- A: antipodal quick test on ring points 0, 4, 8, 12 ----
-        for (int base = 0; base < npx; base += FAST_THREADS) {
-            const int p = base + tid;
-            bool pass4 = false;
-            int pos = 0;
-            if (p < npx) {
-                const int y = p / dW, x = p - y * dW;
-                pos = (y + 3) * TW + x + 3 + xo;
-                const int v = tile[pos];
-                const int r0 = tile[pos + 3 * TW], r8 = tile[pos - 3 * TW], r4 = tile[pos + 3], r12 = tile[pos - 3];
-                const int hi = v + t, lo = v - t;
-                const bool br = (r0 > hi || r8 > hi) && (r4 > hi || r12 > hi);
-                const bool dk = (r0 < lo || r8 < lo) && (r4 < lo || r12 < lo);
-                pass4 = br || dk;
+        const uint32_t T4 = (uint32_t)t * 0x01010101u, TN7 = ~T4 & 0x7f7f7f7fu;
+        for (int y0 = 0; y0 < dH; y0 += rowsPerChunk) {
+            const int y1 = min(y0 + rowsPerChunk, dH);
+            // ---- A: packed quick test on ring points 0 (y+3), 8 (y-3), 4 (x+3), 12 (x-3) ----
+            for (int y = y0 + warp; y < y1; y += FS_THREADS / 32) {
+                const uint32_t* rowc = tile32 + (y + 3) * TWq + wq0;
+                for (int w = lane; w < nW; w += 32) {
+                    const uint32_t vm = act32[wq0 + w];
+                    if (vm == 0) continue;
+                    const uint32_t c = rowc[w], cp = rowc[w - 1], cn = rowc[w + 1];
+                    const uint32_t ring[4] = {rowc[w + 3 * TWq], rowc[w - 3 * TWq], __funnelshift_r(c, cn, 24),
+                                              __funnelshift_r(cp, c, 8)};
+                    const uint32_t CN7 = ~c & 0x7f7f7f7fu;
+                    uint32_t br[4], dk[4];
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const uint32_t a = __vabsdiffu4(ring[k], c);
+                        const uint32_t far = gtu4_msb(a, T4, TN7);
+                        const uint32_t gt = gtu4_msb(ring[k], c, CN7);
+                        br[k] = far & gt;
+                        dk[k] = far & ~gt;
+                    }
+                    const uint32_t fl = (((br[0] | br[1]) & (br[2] | br[3])) | ((dk[0] | dk[1]) & (dk[2] | dk[3]))) & vm;
+                    if (fl) {
+                        int o = atomicAdd(&S.cnt[par], __popc(fl));
+                        const int pos0 = (y + 3) * TW + ((wq0 + w) << 2);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (fl & (0x80u << (8 * j))) S.list1[o++] = (uint16_t)(pos0 + j);
+                    }
+                }
             }
-            const unsigned m = __ballot_sync(0xffffffffu, pass4);
-            if (m) {
-                const int lead = __ffs(m) - 1;
-                int off = 0;
-                if (lane == lead) off = atomicAdd(&cnt[0], __popc(m));
-                off = __shfl_sync(0xffffffffu, off, lead);
-                if (pass4) list1[off + __popc(m & ((1u << lane) - 1))] = (uint16_t)pos;
+            __syncthreads();
+            const int n1 = S.cnt[par];
+            if (tid == 0) S.cnt[par ^ 1] = 0;  // nobody touches the other counter before the next barrier
+            par ^= 1;
+            // ---- B1: full segment test ----
+            for (int i = tid; i < n1; i += FS_THREADS) {
+                const int pos = S.list1[i];
+                const int v = S.tile[pos];
+                uint32_t dark = 0, bright = 0;
+#pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const int d = v - (int)S.tile[pos + off[k]];
+                    dark |= (d > t ? 1u : 0u) << k;
+                    bright |= (d < -t ? 1u : 0u) << k;
+                }
+                if (has_run9(dark) || has_run9(bright)) {
+                    const int o = atomicAdd(&S.cnt[2], 1);
+                    if (o < FS_LIST2) S.list2[o] = (uint16_t)pos;
+                }
             }
+            __syncthreads();
         }
-        __syncthreads();
-        const int n1 = cnt[0];
-        // ---- B: full segment test + corner score ----
-        for (int i = tid; i < n1; i += FAST_THREADS) {
-            const int pos = list1[i];
-            const int v = tile[pos];
+        int n2 = S.cnt[2];
+        if (n2 > FS_LIST2) {
+            if (tid == 0) atomicExch(dStatus, ORBX_E_OVERFLOW);
+            n2 = FS_LIST2;
+        }
+        // ---- B2: corner score (both polarities; the polarity without a run never wins the max) ----
+        for (int i = tid; i < n2; i += FS_THREADS) {
+            const int pos = S.list2[i];
+            const int v = S.tile[pos];
             int d[16];
-            uint32_t dark = 0, bright = 0;
 #pragma unroll
-            for (int k = 0; k < 16; ++k) {
-                d[k] = v - (int)tile[pos + c_ringDy[k] * TW + c_ringDx[k]];
-                dark |= (d[k] > t ? 1u : 0u) << k;
-                bright |= (d[k] < -t ? 1u : 0u) << k;
-            }
-            int s = -1;
-            if (has_run9(dark)) s = best_arc_min(d) - 1;
-            if (has_run9(bright)) {
+            for (int k = 0; k < 16; ++k) d[k] = v - (int)S.tile[pos + off[k]];
+            int s = best_arc_min(d);
 #pragma unroll
-                for (int k = 0; k < 16; ++k) d[k] = -d[k];
-                s = max(s, best_arc_min(d) - 1);
-            }
-            if (s > 0) score[pos] = (uint8_t)s;
+            for (int k = 0; k < 16; ++k) d[k] = -d[k];
+            s = max(s, best_arc_min(d)) - 1;
+            S.score[pos] = (uint8_t)s;
         }
         __syncthreads();
-        // ---- C: 3x3 non-max suppression ----
-        for (int i = tid; i < n1; i += FAST_THREADS) {
-            const int pos = list1[i];
-            const int s = score[pos];
-            if (s == 0) continue;
-            const uint8_t* c = score + pos;
-            if (s > c[-1] && s > c[1] && s > c[-TW - 1] && s > c[-TW] && s > c[-TW + 1] && s > c[TW - 1] && s > c[TW] &&
-                s > c[TW + 1]) {
-                const int o = atomicAdd(&cnt[1], 1);
-                if (o < CELL_CAP) list2[o] = ((uint32_t)pos << 8) | (uint32_t)s;
+        // ---- C: 3x3 non-max suppression among pixels of the same cell ----
+        for (int i = tid; i < n2; i += FS_THREADS) {
+            const int pos = S.list2[i];
+            const int s = S.score[pos];
+            const int y = pos / TW, x = pos - y * TW;
+            const int cell = S.cellOfCol[x];
+            const bool lft = S.cellOfCol[x - 1] == cell, rgt = S.cellOfCol[x + 1] == cell;
+            const uint8_t* c = S.score + pos;
+            bool keep = s > c[-TW] && s > c[TW];
+            if (lft) keep = keep && s > c[-1] && s > c[-TW - 1] && s > c[TW - 1];
+            if (rgt) keep = keep && s > c[1] && s > c[-TW + 1] && s > c[TW + 1];
+            if (keep) {
+                const int o = atomicAdd(&S.cnt[3], 1);
+                if (o < FS_KP) S.kp[o] = ((uint32_t)cell << 24) | ((uint32_t)pos << 8) | (uint32_t)s;
+                atomicAdd(&S.cnt[5 + cell], 1);
             }
         }
         __syncthreads();
-        n2 = cnt[1];
-        if (n2 > 0) break;
-        __syncthreads();  // everyone has read cnt[] before the next pass clears it
+        if (pass == 1) break;
+        // ---- cells without a keypoint go again at minThFAST ----
+        if (tid < nc) {
+            const int ix = iniX + tid * L.wCell;
+            const bool valid = ix < L.maxBX - 6 && min(ix + L.wCell + 6, L.maxBX) - ix >= 7;
+            if (valid && S.cnt[5 + tid] == 0) S.cnt[4] = 1;
+        }
+        __syncthreads();
+        if (S.cnt[4] == 0) break;
+        for (int x = tid; x < TW; x += FS_THREADS) {
+            const int cell = S.cellOfCol[x];
+            S.act[x] = (cell != 255 && S.cnt[5 + cell] == 0) ? 0x80 : 0;
+        }
+        if (tid == 0) S.cnt[2] = 0;
+        __syncthreads();
     }
-    if (n2 > CELL_CAP) {
+    // ---- D: row-major order inside every cell (positions are unique; rank = number of smaller keys of the cell) ----
+    int nkp = S.cnt[3];
+    if (nkp > FS_KP) {
         if (tid == 0) atomicExch(dStatus, ORBX_E_OVERFLOW);
-        n2 = CELL_CAP;
+        nkp = FS_KP;
     }
-    // ---- D: row-major order (positions are unique, rank = number of smaller positions) ----
-    for (int i = tid; i < n2; i += FAST_THREADS) {
-        const uint32_t e = list2[i];
+    for (int i = tid; i < nkp; i += FS_THREADS) {
+        const uint32_t e = S.kp[i];
+        const uint32_t cell = e >> 24;
         int rank = 0;
-        for (int j = 0; j < n2; ++j) rank += (list2[j] < e) ? 1 : 0;
-        const int pos = (int)(e >> 8);
-        const int y = pos / TW, x = pos - y * TW;
-        outKeys[rank] = pack_key(x - xo + cj * L.wCell, y + ci * L.hCell, (int)(e & 0xFFu));
+        for (int j = 0; j < nkp; ++j) {
+            const uint32_t o = S.kp[j];
+            rank += ((o >> 24) == cell && o < e) ? 1 : 0;
+        }
+        if (rank < CELL_CAP) {
+            const int pos = (int)((e >> 8) & 0xFFFFu);
+            const int y = pos / TW, x = pos - y * TW;
+            outKeys[(long long)cell * CELL_CAP + rank] = pack_key(x - xo + cj0 * L.wCell, y + ci * L.hCell, (int)(e & 0xFFu));
+        }
     }
-    if (tid == 0) *outCnt = n2;
+    if (tid < nc) {
+        int c = S.cnt[5 + tid];
+        if (c > CELL_CAP) {
+            atomicExch(dStatus, ORBX_E_OVERFLOW);
+            c = CELL_CAP;
+        }
+        outCnt[tid] = c;
+    }
 }
 
-size_t fast_smem_bytes(const FrameGeom& g) { return (size_t)4 * g.fastBoxW * g.fastBoxH + CELL_CAP * 4 + 8 + 16; }
+size_t fast_smem_bytes(const FrameGeom& g) {
+    return (size_t)2 * g.fastBoxW * g.fastBoxH + 2 * g.fastBoxW + FS_LIST1 * 2 + FS_LIST2 * 2 + FS_KP * 4 +
+           16 * 4 + 16;
+}
 
-int launch_fast(const FrameGeom& g, const TmaMaps& maps, int batch, int* cellCnt, uint32_t* cellKeys, int* dStatus,
-                cudaStream_t s) {
+// Chooses how many cells a strip of a level holds: the TMA box (strip window + 15 bytes of origin slack) must stay
+// within 256 columns, and the 32-bit words of a strip row should fill whole warps.
+int fast_cells_per_strip(int wCell, int nCols) {
+    int best = 1;
+    double bestUtil = 0;
+    for (int c = 1; c <= FAST_MAX_STRIP_CELLS && c <= nCols; ++c) {
+        if (c * wCell + 6 + 15 > 256) break;
+        const int words = (3 + c * wCell + 3) / 4 + 1;
+        const double util = (double)words / (32.0 * ((words + 31) / 32));
+        if (util >= bestUtil - 1e-9) { bestUtil = util; best = c; }
+    }
+    return best;
+}
+
+int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrips, int batch, int* cellCnt,
+                uint32_t* cellKeys, int* dStatus, cudaStream_t s) {
+    if (g.nStrips == 0) return ORBX_OK;
     const size_t smem = fast_smem_bytes(g);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
-        ORBX_CUDA(cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ORBX_CUDA(cudaFuncSetAttribute(k_fast_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    dim3 grid(g.nCellsTotal, batch);
-    k_fast_cells<<<grid, FAST_THREADS, smem, s>>>(g, maps, cellCnt, cellKeys, dStatus);
+    dim3 grid(g.nStrips, batch);
+    k_fast_strips<<<grid, FS_THREADS, smem, s>>>(g, maps, dStrips, cellCnt, cellKeys, dStatus);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

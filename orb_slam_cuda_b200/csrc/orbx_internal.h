@@ -28,7 +28,7 @@ constexpr int PADL = XOFF - EDGE;  // byte column of padded x = 0  (13)
 constexpr int HALF_PATCH = 15;
 constexpr int PATCH = 31;
 constexpr int CELL_CAP = 128;    // FAST keypoints per cell (overflow -> ORBX_E_OVERFLOW)
-constexpr int FAST_THREADS = 128;
+constexpr int FAST_MAX_STRIP_CELLS = 8;  // cells one FAST CTA handles (a strip of one cell row)
 constexpr int QT_THREADS = 256;
 constexpr int MAX_ROOTS = 64;
 
@@ -62,9 +62,14 @@ struct FrameGeom {
     int slotsTotal;
     long long qtFrameStride;  // uint32 per frame in qtScratch
     int fastBoxW, fastBoxH;   // TMA box of the FAST kernel
+    int nStrips;              // FAST strips per frame (all levels)
     int blurTilesTotal;
     int iniTh, minTh;
     LevelGeom lv[ORBX_MAX_LEVELS];
+};
+
+struct FastStrip {  // a run of horizontally adjacent cells of one cell row, processed by one CTA of the FAST kernel
+    uint16_t level, ci, cj0, nc;
 };
 
 struct alignas(64) TmaMaps {  // one descriptor per level, passed to kernels as a __grid_constant__ parameter
@@ -167,8 +172,9 @@ int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, s
 int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, const ResizeTab* ytab, int areaFast,
                          int batch, cudaStream_t s);
 // per-cell FAST-9 + threshold fallback + NMS
-int launch_fast(const FrameGeom& g, const TmaMaps& maps, int batch, int* cellCnt, uint32_t* cellKeys, int* dStatus,
-                cudaStream_t s);
+int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrips, int batch, int* cellCnt,
+                uint32_t* cellKeys, int* dStatus, cudaStream_t s);
+int fast_cells_per_strip(int wCell, int nCols);
 // DistributeOctTree per (frame, level)
 int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uint32_t* cellKeys, uint32_t* qtScratch,
                     int* lvlCnt, uint32_t* lvlKeys, int* dStatus, cudaStream_t s);
