@@ -28,7 +28,6 @@ namespace orbx {
 
 constexpr int FS_THREADS = 256;
 constexpr int FS_LIST1 = 2048;  // quick-test survivors per row chunk
-constexpr int FS_LIST2 = 1024;  // corners per strip and pass
 constexpr int FS_KP = 1024;     // keypoints per strip
 
 __constant__ int c_ringDx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
@@ -75,7 +74,7 @@ struct FastShared {
     uint16_t* list1;
     uint16_t* list2;
     uint32_t* kp;        // cell << 24 | pos << 8 | score
-    int* cnt;            // [0],[1] n1 (ping-pong per chunk), [2] n2, [3] nkp, [4] pass-2 needed, [5..] per-cell counts
+    int* cnt;            // [0],[1] n1 and [2],[3] n2 (ping-pong per row chunk), [4] nkp, [5] pass-2 needed, [6..] per-cell counts
     uint64_t* bar;
 };
 
@@ -93,7 +92,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
     S.cellOfCol = S.act + TW;
     S.list1 = reinterpret_cast<uint16_t*>(S.cellOfCol + TW);
     S.list2 = S.list1 + FS_LIST1;
-    S.kp = reinterpret_cast<uint32_t*>(S.list2 + FS_LIST2);
+    S.kp = reinterpret_cast<uint32_t*>(S.list2 + FS_LIST1);
     S.cnt = reinterpret_cast<int*>(S.kp + FS_KP);
     S.bar = reinterpret_cast<uint64_t*>(S.cnt + 16);
 
@@ -189,8 +188,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
             }
             __syncthreads();
             const int n1 = S.cnt[par];
-            if (tid == 0) S.cnt[par ^ 1] = 0;  // nobody touches the other counter before the next barrier
-            par ^= 1;
+            if (tid == 0) S.cnt[par ^ 1] = S.cnt[2 + (par ^ 1)] = 0;  // nobody touches the other pair before the next barrier
             // ---- B1: full segment test ----
             for (int i = tid; i < n1; i += FS_THREADS) {
                 const int pos = S.list1[i];
@@ -202,47 +200,50 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
                     dark |= (d > t ? 1u : 0u) << k;
                     bright |= (d < -t ? 1u : 0u) << k;
                 }
-                if (has_run9(dark) || has_run9(bright)) {
-                    const int o = atomicAdd(&S.cnt[2], 1);
-                    if (o < FS_LIST2) S.list2[o] = (uint16_t)pos;
-                }
+                if (has_run9(dark) || has_run9(bright)) S.list2[atomicAdd(&S.cnt[2 + par], 1)] = (uint16_t)pos;
             }
             __syncthreads();
-        }
-        int n2 = S.cnt[2];
-        if (n2 > FS_LIST2) {
-            if (tid == 0) atomicExch(dStatus, ORBX_E_OVERFLOW);
-            n2 = FS_LIST2;
-        }
-        // ---- B2: corner score (both polarities; the polarity without a run never wins the max) ----
-        for (int i = tid; i < n2; i += FS_THREADS) {
-            const int pos = S.list2[i];
-            const int v = S.tile[pos];
-            int d[16];
+            const int n2 = S.cnt[2 + par];
+            par ^= 1;
+            // ---- B2: corner score (both polarities; the polarity without a run never wins the max) ----
+            for (int i = tid; i < n2; i += FS_THREADS) {
+                const int pos = S.list2[i];
+                const int v = S.tile[pos];
+                int d[16];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) d[k] = v - (int)S.tile[pos + off[k]];
-            int s = best_arc_min(d);
+                for (int k = 0; k < 16; ++k) d[k] = v - (int)S.tile[pos + off[k]];
+                int s = best_arc_min(d);
 #pragma unroll
-            for (int k = 0; k < 16; ++k) d[k] = -d[k];
-            s = max(s, best_arc_min(d)) - 1;
-            S.score[pos] = (uint8_t)s;
+                for (int k = 0; k < 16; ++k) d[k] = -d[k];
+                s = max(s, best_arc_min(d)) - 1;
+                S.score[pos] = (uint8_t)s;
+            }
+            // no barrier here: the next chunk's A only appends to list1 and the barrier after it orders list2 / score
         }
         __syncthreads();
-        // ---- C: 3x3 non-max suppression among pixels of the same cell ----
-        for (int i = tid; i < n2; i += FS_THREADS) {
-            const int pos = S.list2[i];
-            const int s = S.score[pos];
-            const int y = pos / TW, x = pos - y * TW;
-            const int cell = S.cellOfCol[x];
-            const bool lft = S.cellOfCol[x - 1] == cell, rgt = S.cellOfCol[x + 1] == cell;
-            const uint8_t* c = S.score + pos;
-            bool keep = s > c[-TW] && s > c[TW];
-            if (lft) keep = keep && s > c[-1] && s > c[-TW - 1] && s > c[TW - 1];
-            if (rgt) keep = keep && s > c[1] && s > c[-TW + 1] && s > c[TW + 1];
-            if (keep) {
-                const int o = atomicAdd(&S.cnt[3], 1);
-                if (o < FS_KP) S.kp[o] = ((uint32_t)cell << 24) | ((uint32_t)pos << 8) | (uint32_t)s;
-                atomicAdd(&S.cnt[5 + cell], 1);
+        // ---- C: 3x3 non-max suppression among pixels of the same cell; scans the score tile of the active columns ----
+        for (int y = warp; y < dH; y += FS_THREADS / 32) {
+            const uint32_t* srow = reinterpret_cast<const uint32_t*>(S.score) + (y + 3) * TWq + wq0;
+            for (int w = lane; w < nW; w += 32) {
+                const uint32_t sc = srow[w] & ((act32[wq0 + w] >> 7) * 0xFFu);
+                if (sc == 0) continue;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int s = (sc >> (8 * j)) & 0xFF;
+                    if (s == 0) continue;
+                    const int x = ((wq0 + w) << 2) + j, pos = (y + 3) * TW + x;
+                    const int cell = S.cellOfCol[x];
+                    const bool lft = S.cellOfCol[x - 1] == cell, rgt = S.cellOfCol[x + 1] == cell;
+                    const uint8_t* c = S.score + pos;
+                    bool keep = s > c[-TW] && s > c[TW];
+                    if (lft) keep = keep && s > c[-1] && s > c[-TW - 1] && s > c[TW - 1];
+                    if (rgt) keep = keep && s > c[1] && s > c[-TW + 1] && s > c[TW + 1];
+                    if (keep) {
+                        const int o = atomicAdd(&S.cnt[4], 1);
+                        if (o < FS_KP) S.kp[o] = ((uint32_t)cell << 24) | ((uint32_t)pos << 8) | (uint32_t)s;
+                        atomicAdd(&S.cnt[6 + cell], 1);
+                    }
+                }
             }
         }
         __syncthreads();
@@ -251,19 +252,18 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
         if (tid < nc) {
             const int ix = iniX + tid * L.wCell;
             const bool valid = ix < L.maxBX - 6 && min(ix + L.wCell + 6, L.maxBX) - ix >= 7;
-            if (valid && S.cnt[5 + tid] == 0) S.cnt[4] = 1;
+            if (valid && S.cnt[6 + tid] == 0) S.cnt[5] = 1;
         }
         __syncthreads();
-        if (S.cnt[4] == 0) break;
+        if (S.cnt[5] == 0) break;
         for (int x = tid; x < TW; x += FS_THREADS) {
             const int cell = S.cellOfCol[x];
-            S.act[x] = (cell != 255 && S.cnt[5 + cell] == 0) ? 0x80 : 0;
+            S.act[x] = (cell != 255 && S.cnt[6 + cell] == 0) ? 0x80 : 0;
         }
-        if (tid == 0) S.cnt[2] = 0;
         __syncthreads();
     }
     // ---- D: row-major order inside every cell (positions are unique; rank = number of smaller keys of the cell) ----
-    int nkp = S.cnt[3];
+    int nkp = S.cnt[4];
     if (nkp > FS_KP) {
         if (tid == 0) atomicExch(dStatus, ORBX_E_OVERFLOW);
         nkp = FS_KP;
@@ -283,7 +283,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
         }
     }
     if (tid < nc) {
-        int c = S.cnt[5 + tid];
+        int c = S.cnt[6 + tid];
         if (c > CELL_CAP) {
             atomicExch(dStatus, ORBX_E_OVERFLOW);
             c = CELL_CAP;
@@ -293,7 +293,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
 }
 
 size_t fast_smem_bytes(const FrameGeom& g) {
-    return (size_t)2 * g.fastBoxW * g.fastBoxH + 2 * g.fastBoxW + FS_LIST1 * 2 + FS_LIST2 * 2 + FS_KP * 4 +
+    return (size_t)2 * g.fastBoxW * g.fastBoxH + 2 * g.fastBoxW + FS_LIST1 * 2 + FS_LIST1 * 2 + FS_KP * 4 +
            16 * 4 + 16;
 }
 
