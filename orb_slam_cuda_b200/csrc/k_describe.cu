@@ -1,13 +1,16 @@
 // csrc/k_describe.cu — IC_Angle (reference src/ORBextractor.cc:164-191), computeOrbDescriptor (:195-233), the
 // scale-back of keypoint coordinates (:1794-1803) and the level-major output order of operator() (:1701-1809).
 //
-// One warp per kept keypoint.
-//   angle: lanes span the 31 columns of the circular patch, the warp walks its 31 rows (umax gives the row
-//          half-width, :540-555); m10 / m01 are exact int32 sums, reduced by shuffles; cv::fastAtan2 is restated
-//          as its float32 polynomial with every multiply / add / divide individually rounded (no FMA).
-//   BRIEF: lane i produces descriptor byte i from 16 taps of the blurred level at the pattern points rotated by
-//          the keypoint angle: cvRound(x*b + y*a), cvRound(x*a - y*b) with separately rounded products and
-//          round-half-even (__float2int_rn), bit k = tap(2k) < tap(2k+1).
+// One warp per kept keypoint (a warp walks DESC_PER_WARP slots).
+//   angle: the 31 x 31 patch is read as 32-bit words (4 rows x 8 words per step, unaligned rows realigned with a
+//          funnel shift) and dotted with two byte-coefficient tables by dp4a: u inside the circle (umax, :540-555) for
+//          m10, v for m01.  The sums are exact int32, reduced by shuffles; cv::fastAtan2 is restated as its float32
+//          polynomial with every multiply / add / divide individually rounded (no FMA).
+//   BRIEF: the 37 x 37 neighbourhood of the BLURRED level (the rotated pattern reaches +-18) is staged into a per-warp
+//          shared-memory patch with coalesced word loads; lane i then produces descriptor byte i from 16 taps at the
+//          pattern points rotated by the keypoint angle: cvRound(x*b + y*a), cvRound(x*a - y*b) with separately
+//          rounded products; cvRound (round half to even) is done with the 1.5 * 2^23 bias trick, whose result feeds
+//          the address multiply-add directly; bit k = tap(2k) < tap(2k+1).
 //   cos / sin: the reference calls the float overloads, i.e. glibc cosf / sinf.  Those are not correctly rounded
 //          (about 1.3 % of arguments differ by 1 ulp from the rounded exact value), so they are restated here as
 //          glibc does them (sysdeps/ieee754/flt-32/s_sincosf.h since 2.28): reduction by multiples of pi/2 and
@@ -92,8 +95,25 @@ __device__ __forceinline__ void glibc_sincosf(float y, float* sn, float* cs) {
 }
 
 constexpr int DESC_WARPS = 8;
+constexpr int DESC_PER_WARP = 4;   // keypoint slots a warp walks (amortises the table set-up of the CTA)
+constexpr int BP_HALF = 18;        // the rotated pattern reaches |coordinate| <= cvRound(18.38) = 18
+constexpr int BP_ROWS = 2 * BP_HALF + 1, BP_WORDS = 11, BP_STRIDE = BP_WORDS * 4;  // 37 rows of 11 aligned words
 
-// grid (ceil(slotsTotal / DESC_WARPS), batch)
+// Tables the kernel copies into shared memory, filled once per process by init_describe_tables():
+//   d_patF  : the 512 pattern points as floats, laid out [pair k of the lane][lane] as (x0, y0, x1, y1)
+//   d_coefU : [row r = v + 15][word j] 4 signed bytes  u = 4j + q - 15  inside the circular patch (|u| <= umax[|v|]), else 0
+//   d_coefV : same mask, bytes = v
+__device__ float4 d_patF[8 * 32];
+__device__ uint32_t d_coefU[32 * 8];
+__device__ uint32_t d_coefV[32 * 8];
+
+__device__ __forceinline__ int dp4a_us(uint32_t pixels, uint32_t coef, int acc) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(pixels), "r"(coef), "r"(acc));
+    return d;
+}
+
+// grid (ceil(slotsTotal / (DESC_WARPS * DESC_PER_WARP)), batch)
 __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __grid_constant__ FrameGeom g,
                                                                      const int* __restrict__ lvlCnt,
                                                                      const uint32_t* __restrict__ lvlKeys,
@@ -101,97 +121,163 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
                                                                      uint8_t* __restrict__ desc, int cap,
                                                                      int* __restrict__ counts, float* __restrict__ lvlAngles,
                                                                      int* dStatus) {
-    __shared__ signed char pat[1024];
-    for (int i = threadIdx.x; i < 1024; i += blockDim.x) pat[i] = c_pattern[i];
-    __syncthreads();
-    const int lane = threadIdx.x & 31, f = blockIdx.y;
-    const int slot = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5);
-    if (slot >= g.slotsTotal) return;
-    int level = 0;
-    while (level + 1 < g.nlevels && slot >= g.lv[level + 1].slotBase) ++level;
-    const LevelGeom& L = g.lv[level];
-    const int j = slot - L.slotBase;
-    const int* cnt = lvlCnt + (long long)f * g.nlevels;
-    int before = 0, total = 0;
-    for (int l = 0; l < g.nlevels; ++l) {
-        const int c = cnt[l];
-        if (l < level) before += c;
-        total += c;
+    __shared__ float4 patF[8 * 32];
+    __shared__ uint32_t coefU[32 * 8], coefV[32 * 8];
+    __shared__ uint32_t bpatch[DESC_WARPS][BP_ROWS * BP_WORDS + 1];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        patF[i] = d_patF[i];
+        coefU[i] = d_coefU[i];
+        coefV[i] = d_coefV[i];
     }
-    if (slot == 0 && lane == 0) {
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, f = blockIdx.y;
+    const int* cnt = lvlCnt + (long long)f * g.nlevels;
+    int total = 0;
+    for (int l = 0; l < g.nlevels; ++l) total += cnt[l];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
         counts[f] = min(total, cap);
         if (total > cap) atomicExch(dStatus, ORBX_E_OVERFLOW);
     }
-    if (j >= cnt[level]) return;
-    const uint32_t key = lvlKeys[(long long)f * g.slotsTotal + slot];
-    const int x = key_x(key), y = key_y(key);
+    uint32_t* bp = bpatch[warp];
+    const uint8_t* bp8 = reinterpret_cast<const uint8_t*>(bp);
 
-    // ---- IC_Angle on the unblurred level ----
-    const uint8_t* center = L.plane + (long long)f * L.planeStride + (long long)(y + EDGE) * L.pitch + (x + XOFF);
-    const int u = lane - HALF_PATCH;
-    int m10 = 0, m01 = 0;
-    for (int v = -HALF_PATCH; v <= HALF_PATCH; ++v) {
-        const int d = c_umax[v < 0 ? -v : v];
-        if (lane < PATCH && u >= -d && u <= d) {
-            const int val = center[v * L.pitch + u];
-            m10 += u * val;
-            m01 += v * val;
-        }
-    }
+    for (int it = 0; it < DESC_PER_WARP; ++it) {
+        const int slot = (blockIdx.x * DESC_PER_WARP + it) * DESC_WARPS + warp;
+        if (slot >= g.slotsTotal) break;
+        int level = 0;
+        while (level + 1 < g.nlevels && slot >= g.lv[level + 1].slotBase) ++level;
+        const LevelGeom& L = g.lv[level];
+        const int j = slot - L.slotBase;
+        if (j >= cnt[level]) continue;
+        int before = 0;
+        for (int l = 0; l < level; ++l) before += cnt[l];
+        const uint32_t key = lvlKeys[(long long)f * g.slotsTotal + slot];
+        const int x = key_x(key), y = key_y(key);
+
+        // ---- IC_Angle on the unblurred level: lanes = (4 rows) x (8 words of 4 pixels), dp4a against the u / v tables ----
+        int m10 = 0, m01 = 0;
+        {
+            const uint8_t* p0 = L.plane + (long long)f * L.planeStride + (long long)(y - HALF_PATCH + EDGE) * L.pitch +
+                                (x - HALF_PATCH + XOFF) + 4 * (lane & 7);
+            const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(p0) & 3) * 8;
+            const uint32_t* w0 = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(p0) & ~(uintptr_t)3);
+            const int rsub = lane >> 3, pitchq = L.pitch >> 2;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-        m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-    }
-    const float angle = fast_atan2_deg((float)m01, (float)m10);
-    if (lvlAngles && lane == 0) lvlAngles[(long long)f * g.slotsTotal + slot] = angle;
-
-    const int o = before + j;
-    if (o >= cap) return;
-
-    // ---- steered BRIEF on the blurred level ----
-    const float factorPI = 0.01745329238474369f;  // (float)(CV_PI / 180.f)
-    float a, b;
-    glibc_sincosf(__fmul_rn(angle, factorPI), &b, &a);  // a = cos, b = sin
-    const uint8_t* bc = L.blur + (long long)f * L.blurStride + (long long)y * L.bpitch + x;
-    const signed char* p = pat + lane * 32;
-    int val = 0;
+            for (int r4 = 0; r4 < 8; ++r4) {
+                const int r = r4 * 4 + rsub;  // row 31 exists in the padded plane; its coefficients are zero
+                const uint32_t* w = w0 + r * pitchq;
+                const uint32_t px = __funnelshift_r(__ldg(w), __ldg(w + 1), sh);
+                m10 = dp4a_us(px, coefU[r * 8 + (lane & 7)], m10);
+                m01 = dp4a_us(px, coefV[r * 8 + (lane & 7)], m01);
+            }
+        }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-        const float x0 = (float)p[4 * k], y0 = (float)p[4 * k + 1], x1 = (float)p[4 * k + 2], y1 = (float)p[4 * k + 3];
-        const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a)));
-        const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)));
-        const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a)));
-        const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)));
-        const int t0 = bc[r0 * L.bpitch + c0], t1 = bc[r1 * L.bpitch + c1];
-        val |= (t0 < t1 ? 1 : 0) << k;
-    }
-    desc[((long long)f * cap + o) * 32 + lane] = (uint8_t)val;
+        for (int o = 16; o > 0; o >>= 1) {
+            m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+            m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+        }
+        const float angle = fast_atan2_deg((float)m01, (float)m10);
+        if (lvlAngles && lane == 0) lvlAngles[(long long)f * g.slotsTotal + slot] = angle;
+        const int o = before + j;
+        if (o >= cap) continue;
 
-    // ---- keypoint record (cv::KeyPoint layout), coordinates scaled back to level 0 (:1794-1803) ----
-    if (lane < 7) {
-        float fx = (float)x, fy = (float)y;
-        if (level != 0) {
-            fx = __fmul_rn(fx, L.scale);
-            fy = __fmul_rn(fy, L.scale);
+        // ---- stage the 37 x 37 blurred patch (rows of 11 aligned words covering columns x-18 .. x+18) ----
+        const uint8_t* brow = L.blur + (long long)f * L.blurStride + (long long)(y - BP_HALF) * L.bpitch + (x - BP_HALF);
+        const int mis = (int)(reinterpret_cast<uintptr_t>(brow) & 3);
+        const uint32_t* bw = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(brow) & ~(uintptr_t)3);
+        const int bpq = L.bpitch >> 2;
+        __syncwarp();
+        for (int i = lane; i < BP_ROWS * BP_WORDS; i += 32) {
+            const int r = i / BP_WORDS, wq = i - r * BP_WORDS;
+            bp[i] = __ldg(bw + r * bpq + wq);
         }
-        uint32_t w;
-        switch (lane) {
-            case 0: w = __float_as_uint(fx); break;
-            case 1: w = __float_as_uint(fy); break;
-            case 2: w = __float_as_uint(L.size); break;
-            case 3: w = __float_as_uint(angle); break;
-            case 4: w = __float_as_uint((float)key_resp(key)); break;
-            case 5: w = (uint32_t)level; break;
-            default: w = 0xFFFFFFFFu; break;  // class_id = -1
+        __syncwarp();
+
+        // ---- steered BRIEF: lane i -> byte i, 16 rotated taps read from the staged patch ----
+        const float factorPI = 0.01745329238474369f;  // (float)(CV_PI / 180.f)
+        float a, b;
+        glibc_sincosf(__fmul_rn(angle, factorPI), &b, &a);  // a = cos, b = sin
+        // cvRound(v) = bits(v + 1.5 * 2^23) - bits(1.5 * 2^23) (round half to even, |v| < 2^22); the two biases and the
+        // patch origin are folded into one constant of the byte address  row * 44 + col
+        const float MAGIC = 12582912.0f;
+        const uint32_t base = 0u - 0x4B400000u * (uint32_t)(BP_STRIDE + 1) + (uint32_t)(BP_HALF * BP_STRIDE + BP_HALF + mis);  // mod 2^32
+        int val = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float4 p = patF[k * 32 + lane];
+            const float r0 = __fadd_rn(__fadd_rn(__fmul_rn(p.x, b), __fmul_rn(p.y, a)), MAGIC);
+            const float c0 = __fadd_rn(__fsub_rn(__fmul_rn(p.x, a), __fmul_rn(p.y, b)), MAGIC);
+            const float r1 = __fadd_rn(__fadd_rn(__fmul_rn(p.z, b), __fmul_rn(p.w, a)), MAGIC);
+            const float c1 = __fadd_rn(__fsub_rn(__fmul_rn(p.z, a), __fmul_rn(p.w, b)), MAGIC);
+            const int t0 = bp8[__float_as_uint(r0) * (uint32_t)BP_STRIDE + __float_as_uint(c0) + base];
+            const int t1 = bp8[__float_as_uint(r1) * (uint32_t)BP_STRIDE + __float_as_uint(c1) + base];
+            val |= (t0 < t1 ? 1 : 0) << k;
         }
-        reinterpret_cast<uint32_t*>(kps + (long long)f * cap + o)[lane] = w;
+        desc[((long long)f * cap + o) * 32 + lane] = (uint8_t)val;
+
+        // ---- keypoint record (cv::KeyPoint layout), coordinates scaled back to level 0 (:1794-1803) ----
+        if (lane < 7) {
+            float fx = (float)x, fy = (float)y;
+            if (level != 0) {
+                fx = __fmul_rn(fx, L.scale);
+                fy = __fmul_rn(fy, L.scale);
+            }
+            uint32_t w;
+            switch (lane) {
+                case 0: w = __float_as_uint(fx); break;
+                case 1: w = __float_as_uint(fy); break;
+                case 2: w = __float_as_uint(L.size); break;
+                case 3: w = __float_as_uint(angle); break;
+                case 4: w = __float_as_uint((float)key_resp(key)); break;
+                case 5: w = (uint32_t)level; break;
+                default: w = 0xFFFFFFFFu; break;  // class_id = -1
+            }
+            reinterpret_cast<uint32_t*>(kps + (long long)f * cap + o)[lane] = w;
+        }
     }
+}
+
+static int init_describe_tables() {
+    static bool done[16] = {};
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    if (dev < 16 && done[dev]) return ORBX_OK;
+    static const signed char pat[1024] = {
+#include "orb_pattern_31.inc"
+    };
+    static const int umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
+    float4 pf[256];
+    for (int lane = 0; lane < 32; ++lane)
+        for (int k = 0; k < 8; ++k) {
+            const signed char* p = pat + lane * 32 + 4 * k;  // pair 8 * lane + k: (x0, y0, x1, y1)
+            pf[k * 32 + lane] = make_float4((float)p[0], (float)p[1], (float)p[2], (float)p[3]);
+        }
+    uint32_t cu[256], cv[256];
+    for (int r = 0; r < 32; ++r)
+        for (int j = 0; j < 8; ++j) {
+            uint32_t wu = 0, wv = 0;
+            for (int q = 0; q < 4; ++q) {
+                const int c = 4 * j + q, u = c - HALF_PATCH, v = r - HALF_PATCH;
+                const bool in = r <= 30 && c <= 30 && std::abs(u) <= umax[std::abs(v)];
+                wu |= (uint32_t)(uint8_t)(signed char)(in ? u : 0) << (8 * q);
+                wv |= (uint32_t)(uint8_t)(signed char)(in ? v : 0) << (8 * q);
+            }
+            cu[r * 8 + j] = wu;
+            cv[r * 8 + j] = wv;
+        }
+    ORBX_CUDA(cudaMemcpyToSymbol(d_patF, pf, sizeof pf));
+    ORBX_CUDA(cudaMemcpyToSymbol(d_coefU, cu, sizeof cu));
+    ORBX_CUDA(cudaMemcpyToSymbol(d_coefV, cv, sizeof cv));
+    if (dev < 16) done[dev] = true;
+    return ORBX_OK;
 }
 
 int launch_describe(const FrameGeom& g, int batch, const int* lvlCnt, const uint32_t* lvlKeys, orbx_keypoint* dKps,
                     uint8_t* dDesc, int cap, int* dCounts, float* dLvlAngles, int* dStatus, cudaStream_t s) {
-    dim3 grid((g.slotsTotal + DESC_WARPS - 1) / DESC_WARPS, batch);
+    int rc = init_describe_tables();
+    if (rc) return rc;
+    const int perCta = DESC_WARPS * DESC_PER_WARP;
+    dim3 grid((g.slotsTotal + perCta - 1) / perCta, batch);
     k_orient_describe<<<grid, DESC_WARPS * 32, 0, s>>>(g, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts, dLvlAngles, dStatus);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
