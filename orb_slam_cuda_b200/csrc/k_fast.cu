@@ -7,12 +7,13 @@
 // never scored, so NMS must not look across a cell seam — and (b) the fallback to minThFAST when the cell produced no
 // keypoint.  One CTA therefore handles a STRIP of several horizontally adjacent cells of one cell row:
 //   tile   the strip's window is staged into shared memory by one TMA box load (origin rounded down to 16 bytes);
-//   A      quick reject, four pixels per lane as packed bytes: VABSDIFF4 + carry-less byte compares give, for ring
-//          points 0/4/8/12, the flags |r - v| > t and r > v; a pixel survives if both antipodal pairs hold a brighter
-//          (or both a darker) point.  Warps walk rows, lanes walk 32-bit words, so there is no index division;
-//   B1     survivors (dense list) take the full 16-point segment test (bit-mask run-of-9 detection);
-//   B2     corners (dense list) get OpenCV's cornerScore<16>: max over the 16 arcs of 9 of the min |difference|, both
-//          polarities, minus 1, stored in a shared score tile (0 = not a corner);
+//   A      quick reject, four pixels per lane as packed bytes: saturating v +- t once per word, then carry-less byte
+//          compares of the 8 EVEN ring points (rows y+-3, y+-2, y realigned with funnel shifts).  A run of 9 ring points
+//          holds 4 consecutive even ones, so a pixel survives iff 4 consecutive even points are all brighter (or all
+//          darker).  Warps walk rows, lanes walk 32-bit words, so there is no index division;
+//   B      survivors (dense list) take the full 16-point segment test (bit-mask run-of-9 detection); corners get
+//          OpenCV's cornerScore<16>: max over the 16 arcs of 9 of the min |difference|, both polarities, minus 1,
+//          stored in a shared score tile (0 = not a corner), and join the corner list;
 //   C      corners strictly greater than their 8 neighbours OF THE SAME CELL survive and are counted per cell;
 //   pass 2 cells that are still empty repeat A-C at minThFAST (:1281-1285); pixels of other cells are masked out;
 //   D      survivors are ranked by position inside their cell (cv::FAST's row-major order) and written to the cell's slot.
@@ -27,7 +28,8 @@
 namespace orbx {
 
 constexpr int FS_THREADS = 256;
-constexpr int FS_LIST1 = 2048;  // quick-test survivors per row chunk
+constexpr int FS_LIST1 = 4096;  // quick-test survivors per row chunk
+constexpr int FS_LIST2 = 2048;  // corners per strip and pass (beyond that NMS scans the score tile)
 constexpr int FS_KP = 1024;     // keypoints per strip
 
 __constant__ int c_ringDx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
@@ -74,7 +76,7 @@ struct FastShared {
     uint16_t* list1;
     uint16_t* list2;
     uint32_t* kp;        // cell << 24 | pos << 8 | score
-    int* cnt;            // [0],[1] n1 and [2],[3] n2 (ping-pong per row chunk), [4] nkp, [5] pass-2 needed, [6..] per-cell counts
+    int* cnt;            // [0],[1] n1 (ping-pong per row chunk), [2] corners of the pass, [4] nkp, [5] pass-2 needed, [6..] per-cell counts
     uint64_t* bar;
 };
 
@@ -92,7 +94,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
     S.cellOfCol = S.act + TW;
     S.list1 = reinterpret_cast<uint16_t*>(S.cellOfCol + TW);
     S.list2 = S.list1 + FS_LIST1;
-    S.kp = reinterpret_cast<uint32_t*>(S.list2 + FS_LIST1);
+    S.kp = reinterpret_cast<uint32_t*>(S.list2 + FS_LIST2);
     S.cnt = reinterpret_cast<int*>(S.kp + FS_KP);
     S.bar = reinterpret_cast<uint64_t*>(S.cnt + 16);
 
@@ -151,32 +153,70 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
 #pragma unroll
     for (int k = 0; k < 16; ++k) off[k] = c_ringDy[k] * TW + c_ringDx[k];
 
+    // C for one corner: keep it iff its score beats the 8 neighbours that lie in the same cell
+    auto nms_one = [&](int pos, int s) {
+        const int y = pos / TW, x = pos - y * TW;
+        const int cell = S.cellOfCol[x];
+        const bool lft = S.cellOfCol[x - 1] == cell, rgt = S.cellOfCol[x + 1] == cell;
+        const uint8_t* c = S.score + pos;
+        bool keep = s > c[-TW] && s > c[TW];
+        if (lft) keep = keep && s > c[-1] && s > c[-TW - 1] && s > c[TW - 1];
+        if (rgt) keep = keep && s > c[1] && s > c[-TW + 1] && s > c[TW + 1];
+        if (keep) {
+            const int o = atomicAdd(&S.cnt[4], 1);
+            if (o < FS_KP) S.kp[o] = ((uint32_t)cell << 24) | ((uint32_t)pos << 8) | (uint32_t)s;
+            atomicAdd(&S.cnt[6 + cell], 1);
+        }
+    };
+
     int par = 0;  // which n1 counter the current chunk appends to
     for (int pass = 0; pass < 2; ++pass) {
         const int t = min(max(pass == 0 ? g.iniTh : g.minTh, 0), 255);
-        const uint32_t T4 = (uint32_t)t * 0x01010101u, TN7 = ~T4 & 0x7f7f7f7fu;
+        const uint32_t T4 = (uint32_t)t * 0x01010101u;
         for (int y0 = 0; y0 < dH; y0 += rowsPerChunk) {
             const int y1 = min(y0 + rowsPerChunk, dH);
-            // ---- A: packed quick test on ring points 0 (y+3), 8 (y-3), 4 (x+3), 12 (x-3) ----
+            // ---- A: packed quick test on the 8 even ring points: a run of 9 holds 4 consecutive even points ----
             for (int y = y0 + warp; y < y1; y += FS_THREADS / 32) {
                 const uint32_t* rowc = tile32 + (y + 3) * TWq + wq0;
                 for (int w = lane; w < nW; w += 32) {
                     const uint32_t vm = act32[wq0 + w];
                     if (vm == 0) continue;
-                    const uint32_t c = rowc[w], cp = rowc[w - 1], cn = rowc[w + 1];
-                    const uint32_t ring[4] = {rowc[w + 3 * TWq], rowc[w - 3 * TWq], __funnelshift_r(c, cn, 24),
-                                              __funnelshift_r(cp, c, 8)};
-                    const uint32_t CN7 = ~c & 0x7f7f7f7fu;
-                    uint32_t br[4], dk[4];
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        const uint32_t a = __vabsdiffu4(ring[k], c);
-                        const uint32_t far = gtu4_msb(a, T4, TN7);
-                        const uint32_t gt = gtu4_msb(ring[k], c, CN7);
-                        br[k] = far & gt;
-                        dk[k] = far & ~gt;
+                    const uint32_t c = rowc[w];
+                    const uint32_t hi = __vaddus4(c, T4), lo = __vsubus4(c, T4);  // saturating v + t, v - t
+                    const uint32_t HN7 = ~hi & 0x7f7f7f7fu, LO7 = lo & 0x7f7f7f7fu;
+                    uint32_t ring[8];
+                    ring[0] = rowc[w + 3 * TWq];                                                       // ( 0, +3)
+                    ring[4] = rowc[w - 3 * TWq];                                                       // ( 0, -3)
+                    {
+                        const uint32_t* r = rowc + 2 * TWq;
+                        const uint32_t m = r[w];
+                        ring[1] = __funnelshift_r(m, r[w + 1], 16);                                    // (+2, +2)
+                        ring[7] = __funnelshift_r(r[w - 1], m, 16);                                    // (-2, +2)
                     }
-                    const uint32_t fl = (((br[0] | br[1]) & (br[2] | br[3])) | ((dk[0] | dk[1]) & (dk[2] | dk[3]))) & vm;
+                    ring[2] = __funnelshift_r(c, rowc[w + 1], 24);                                     // (+3,  0)
+                    ring[6] = __funnelshift_r(rowc[w - 1], c, 8);                                      // (-3,  0)
+                    {
+                        const uint32_t* r = rowc - 2 * TWq;
+                        const uint32_t m = r[w];
+                        ring[3] = __funnelshift_r(m, r[w + 1], 16);                                    // (+2, -2)
+                        ring[5] = __funnelshift_r(r[w - 1], m, 16);                                    // (-2, -2)
+                    }
+                    uint32_t br[8], dk[8];
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        br[k] = gtu4_msb(ring[k], hi, HN7);  // r > v + t
+                        uint32_t d;
+                        const uint32_t sd = LO7 + (~ring[k] & 0x7f7f7f7fu);
+                        asm("lop3.b32 %0, %1, %2, %3, 0xb2;" : "=r"(d) : "r"(lo), "r"(ring[k]), "r"(sd));  // v - t > r
+                        dk[k] = d;
+                    }
+                    uint32_t anyB = 0, anyD = 0;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        anyB |= br[k] & br[(k + 1) & 7] & br[(k + 2) & 7] & br[(k + 3) & 7];
+                        anyD |= dk[k] & dk[(k + 1) & 7] & dk[(k + 2) & 7] & dk[(k + 3) & 7];
+                    }
+                    const uint32_t fl = (anyB | anyD) & vm;
                     if (fl) {
                         int o = atomicAdd(&S.cnt[par], __popc(fl));
                         const int pos0 = (y + 3) * TW + ((wq0 + w) << 2);
@@ -188,60 +228,50 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
             }
             __syncthreads();
             const int n1 = S.cnt[par];
-            if (tid == 0) S.cnt[par ^ 1] = S.cnt[2 + (par ^ 1)] = 0;  // nobody touches the other pair before the next barrier
-            // ---- B1: full segment test ----
+            if (tid == 0) S.cnt[par ^ 1] = 0;  // nobody touches the other counter before the next barrier
+            par ^= 1;
+            // ---- B: full 16-point segment test; corners get cornerScore<16> (both polarities: the one without a run
+            //         never wins the max) and join the corner list of this pass ----
             for (int i = tid; i < n1; i += FS_THREADS) {
                 const int pos = S.list1[i];
                 const int v = S.tile[pos];
+                int d[16];
                 uint32_t dark = 0, bright = 0;
 #pragma unroll
                 for (int k = 0; k < 16; ++k) {
-                    const int d = v - (int)S.tile[pos + off[k]];
-                    dark |= (d > t ? 1u : 0u) << k;
-                    bright |= (d < -t ? 1u : 0u) << k;
+                    d[k] = v - (int)S.tile[pos + off[k]];
+                    dark |= (d[k] > t ? 1u : 0u) << k;
+                    bright |= (d[k] < -t ? 1u : 0u) << k;
                 }
-                if (has_run9(dark) || has_run9(bright)) S.list2[atomicAdd(&S.cnt[2 + par], 1)] = (uint16_t)pos;
+                if (has_run9(dark) || has_run9(bright)) {
+                    int s = best_arc_min(d);
+#pragma unroll
+                    for (int k = 0; k < 16; ++k) d[k] = -d[k];
+                    s = max(s, best_arc_min(d)) - 1;
+                    S.score[pos] = (uint8_t)s;
+                    const int o = atomicAdd(&S.cnt[2], 1);
+                    if (o < FS_LIST2) S.list2[o] = (uint16_t)pos;
+                }
             }
             __syncthreads();
-            const int n2 = S.cnt[2 + par];
-            par ^= 1;
-            // ---- B2: corner score (both polarities; the polarity without a run never wins the max) ----
+        }
+        // ---- C: 3x3 non-max suppression among pixels of the same cell ----
+        const int n2 = S.cnt[2];
+        if (n2 <= FS_LIST2) {
             for (int i = tid; i < n2; i += FS_THREADS) {
                 const int pos = S.list2[i];
-                const int v = S.tile[pos];
-                int d[16];
-#pragma unroll
-                for (int k = 0; k < 16; ++k) d[k] = v - (int)S.tile[pos + off[k]];
-                int s = best_arc_min(d);
-#pragma unroll
-                for (int k = 0; k < 16; ++k) d[k] = -d[k];
-                s = max(s, best_arc_min(d)) - 1;
-                S.score[pos] = (uint8_t)s;
+                nms_one(pos, S.score[pos]);
             }
-            // no barrier here: the next chunk's A only appends to list1 and the barrier after it orders list2 / score
-        }
-        __syncthreads();
-        // ---- C: 3x3 non-max suppression among pixels of the same cell; scans the score tile of the active columns ----
-        for (int y = warp; y < dH; y += FS_THREADS / 32) {
-            const uint32_t* srow = reinterpret_cast<const uint32_t*>(S.score) + (y + 3) * TWq + wq0;
-            for (int w = lane; w < nW; w += 32) {
-                const uint32_t sc = srow[w] & ((act32[wq0 + w] >> 7) * 0xFFu);
-                if (sc == 0) continue;
+        } else {  // more corners than the list holds: scan the score tile of the active columns instead
+            for (int y = warp; y < dH; y += FS_THREADS / 32) {
+                const uint32_t* srow = reinterpret_cast<const uint32_t*>(S.score) + (y + 3) * TWq + wq0;
+                for (int w = lane; w < nW; w += 32) {
+                    const uint32_t sc = srow[w] & ((act32[wq0 + w] >> 7) * 0xFFu);
+                    if (sc == 0) continue;
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    const int s = (sc >> (8 * j)) & 0xFF;
-                    if (s == 0) continue;
-                    const int x = ((wq0 + w) << 2) + j, pos = (y + 3) * TW + x;
-                    const int cell = S.cellOfCol[x];
-                    const bool lft = S.cellOfCol[x - 1] == cell, rgt = S.cellOfCol[x + 1] == cell;
-                    const uint8_t* c = S.score + pos;
-                    bool keep = s > c[-TW] && s > c[TW];
-                    if (lft) keep = keep && s > c[-1] && s > c[-TW - 1] && s > c[TW - 1];
-                    if (rgt) keep = keep && s > c[1] && s > c[-TW + 1] && s > c[TW + 1];
-                    if (keep) {
-                        const int o = atomicAdd(&S.cnt[4], 1);
-                        if (o < FS_KP) S.kp[o] = ((uint32_t)cell << 24) | ((uint32_t)pos << 8) | (uint32_t)s;
-                        atomicAdd(&S.cnt[6 + cell], 1);
+                    for (int j = 0; j < 4; ++j) {
+                        const int s = (sc >> (8 * j)) & 0xFF;
+                        if (s != 0) nms_one((y + 3) * TW + ((wq0 + w) << 2) + j, s);
                     }
                 }
             }
@@ -260,6 +290,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
             const int cell = S.cellOfCol[x];
             S.act[x] = (cell != 255 && S.cnt[6 + cell] == 0) ? 0x80 : 0;
         }
+        if (tid == 0) S.cnt[2] = 0;
         __syncthreads();
     }
     // ---- D: row-major order inside every cell (positions are unique; rank = number of smaller keys of the cell) ----
@@ -293,7 +324,7 @@ __global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constan
 }
 
 size_t fast_smem_bytes(const FrameGeom& g) {
-    return (size_t)2 * g.fastBoxW * g.fastBoxH + 2 * g.fastBoxW + FS_LIST1 * 2 + FS_LIST1 * 2 + FS_KP * 4 +
+    return (size_t)2 * g.fastBoxW * g.fastBoxH + 2 * g.fastBoxW + FS_LIST1 * 2 + FS_LIST2 * 2 + FS_KP * 4 +
            16 * 4 + 16;
 }
 
