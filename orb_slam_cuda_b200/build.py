@@ -51,6 +51,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
     return SO
 
 
+def build_variant(name: str, defines: list) -> str:
+    """Development aid: liborbx_<name>.so compiled with extra -D flags (select it with ORBX_LIB=<path>)."""
+    out = os.path.join(HERE, f"liborbx_{name}.so")
+    srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+    flags = [f for f in NVCC_FLAGS if f not in ("-Xptxas", "-v")]
+    subprocess.check_call([_nvcc()] + flags + ["-D" + d for d in defines] + ["-shared", "-o", out] + srcs)
+    return out
+
+
 CLASSES_SO = os.path.join(HERE, "liborbx_classes.so")
 HARNESS = os.path.join(HERE, "..", "tests", "cpp", "frame_harness")
 

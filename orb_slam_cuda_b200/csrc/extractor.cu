@@ -287,10 +287,26 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
             const int ix = cv_round(sx), iy = cv_round(sy);
             const bool area = std::abs(sx - ix) < DBL_EPSILON && std::abs(sy - iy) < DBL_EPSILON && ix == 2 && iy == 2;
             ex->areaFast[l] = area ? 1 : 0;
-            if (area) {  // exact 2x decimation is routed to INTER_AREA by cv::resize: mean of the 2x2 block
-                for (int d = 0; d < L.w; ++d) { xt[d].s0 = (uint16_t)(2 * d); xt[d].s1 = (uint16_t)(2 * d + 1); }
-                for (int d = 0; d < L.h; ++d) { yt[d].s0 = (uint16_t)(2 * d); yt[d].s1 = (uint16_t)(2 * d + 1); }
+            if (area) {  // exact 2x decimation is routed to INTER_AREA by cv::resize: mean of the 2x2 block, which
+                         // is the bilinear formula with all coefficients 1024 (((1024 * (1024 (p + q) >> 4)) >> 16) = p + q)
+                for (int d = 0; d < L.w; ++d) xt[d] = ResizeTab{(uint16_t)(2 * d), (uint16_t)(2 * d + 1), 1024, 1024};
+                for (int d = 0; d < L.h; ++d) yt[d] = ResizeTab{(uint16_t)(2 * d), (uint16_t)(2 * d + 1), 1024, 1024};
             }
+            // the word-based kernel needs every group of 4 padded destination columns to read <= 8 consecutive source bytes
+            bool fits = true;
+            for (int bx = 0; bx < L.pitch && fits; bx += 4) {
+                int lo = INT_MAX, hi = -1;
+                for (int j = 0; j < 4; ++j) {
+                    const int px = bx + j - PADL;
+                    if (px < 0 || px >= L.w + 2 * EDGE) continue;
+                    int d = px - EDGE;
+                    while (d < 0 || d >= L.w) d = L.w == 1 ? 0 : (d < 0 ? -d : 2 * L.w - 2 - d);
+                    lo = std::min(lo, (int)xt[d].s0);
+                    hi = std::max(hi, std::max((int)xt[d].s0, (int)xt[d].s1));
+                }
+                if (hi >= 0 && hi - lo > 7) fits = false;
+            }
+            if (fits) ex->areaFast[l] |= 2;
             if ((rc = ex->xtab[l].ensure(xt.size() * sizeof(ResizeTab)))) return rc;
             if ((rc = ex->ytab[l].ensure(yt.size() * sizeof(ResizeTab)))) return rc;
             ORBX_CUDA(cudaMemcpy(ex->xtab[l].p, xt.data(), xt.size() * sizeof(ResizeTab), cudaMemcpyHostToDevice));

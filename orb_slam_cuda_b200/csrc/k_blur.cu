@@ -5,8 +5,8 @@
 // One CTA produces a 128 x 32 output tile.  The 134 x 38 input window (3-px halo) is staged with one TMA box load of
 // 160 x 38 bytes from the padded plane (TMA needs the box origin on a 16-byte boundary of the row: measured on B200,
 // tools/tma_probe.cu; the window starts at byte 13 of the box) — the plane's 19-px border IS the reflect-101
-// extension of the level, so no border logic is needed here.  The horizontal pass writes 16-bit partial sums
-// (<= 255*256) to shared memory, the vertical pass emits 4 bytes per thread per row with 32-bit stores.
+// extension of the level, so no border logic is needed here.  Both passes run in registers (see the kernel comment);
+// a thread emits 4 bytes per row with 32-bit stores.
 //
 // Roofline: HBM-bound (reads each level once, writes it once).
 #include "orbx_internal.h"
@@ -14,12 +14,18 @@
 
 namespace orbx {
 
-constexpr int BLUR_TW = 128, BLUR_TH = 32, BLUR_BW = 160, BLUR_BH = 38, BLUR_THREADS = 256;
+constexpr int BLUR_TW = 128, BLUR_TH = 32, BLUR_BW = 160, BLUR_BH = 38;
+constexpr int BLUR_BAND = 16;                        // output rows per thread (a thread walks BLUR_BAND + 6 input rows)
+constexpr int BLUR_THREADS = 32 * (BLUR_TH / BLUR_BAND);
 
+// One CTA = one 128 x 32 output tile; one thread = 4 output columns x 16 output rows.  Walking down its band, a thread
+// forms the horizontal 7-tap sums of the arriving input row with dp4a (pixels realigned by funnel shifts; coefficient
+// bytes (18,34,48,56) and (48,34,18,0)), keeps the last rows as vertically packed 16-bit pairs in registers and forms the
+// vertical sum with three dp2a + one multiply-add.  The horizontal sums (<= 255 * 256) fit 16 bits, the vertical sum
+// + 32768 fits 32 bits, and the result byte is bits 16..23 of the accumulator (picked with PRMT, no shift).
 __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ FrameGeom g,
                                                         const __grid_constant__ TmaMaps maps) {
     __shared__ __align__(128) uint8_t tile[BLUR_BH * BLUR_BW];
-    __shared__ __align__(16) uint16_t hsum[BLUR_BH * BLUR_TW];
     __shared__ __align__(8) uint64_t bar;
     const int tid = threadIdx.x, f = blockIdx.y;
     int t = blockIdx.x, level = 0;
@@ -37,52 +43,47 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
         mbar_expect_tx(&bar, BLUR_BH * BLUR_BW);
         tma_load_3d(tile, &maps.m[level], XOFF + x0 - 16, EDGE + y0 - 3, f, &bar);  // window = box columns 13..146
     }
+    const int cg = tid & 31, band = tid >> 5;
+    const int xo = x0 + 4 * cg, yb = y0 + band * BLUR_BAND;
+    uint8_t* out = L.blur + (long long)f * L.blurStride + xo;
+    const bool colOk = xo < L.bpitch;
+    const uint32_t K0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), K1 = 48u | (34u << 8) | (18u << 16);
+    const uint32_t V0 = 18u | (34u << 8), V1 = 48u | (56u << 8), V2 = 48u | (34u << 8);
     mbar_wait(&bar, 0);
 
-    // horizontal pass: item = (row, group of 4 output columns)
-    for (int it = tid; it < BLUR_BH * (BLUR_TW / 4); it += BLUR_THREADS) {
-        const int r = it / (BLUR_TW / 4), q = it - r * (BLUR_TW / 4);
-        const uint32_t* w = reinterpret_cast<const uint32_t*>(tile + r * BLUR_BW + 12 + 4 * q);
-        const uint32_t w0 = w[0], w1 = w[1], w2 = w[2];  // window bytes 4q..4q+9 are bytes 1..10 of these words
-        int p[10];
+    const uint32_t* rowp = reinterpret_cast<const uint32_t*>(tile + band * BLUR_BAND * BLUR_BW + 12) + cg;
+    uint32_t pr[8][4];  // pr[i & 7][c] = (h(i), h(i + 1)) of column c as two 16-bit halves
+    uint32_t hp[4] = {0, 0, 0, 0};
 #pragma unroll
-        for (int k = 0; k < 3; ++k) p[k] = (w0 >> (8 * (k + 1))) & 0xFF;
+    for (int i = 0; i < BLUR_BAND + 6; ++i) {
+        // window bytes 4cg .. 4cg + 9 of input row i are bytes 1 .. 10 of these three words
+        const uint32_t w0 = rowp[i * (BLUR_BW / 4)], w1 = rowp[i * (BLUR_BW / 4) + 1], w2 = rowp[i * (BLUR_BW / 4) + 2];
+        uint32_t h[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) p[3 + k] = (w1 >> (8 * k)) & 0xFF;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) p[7 + k] = (w2 >> (8 * k)) & 0xFF;
-        uint32_t s[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            s[k] = 18 * (p[k] + p[k + 6]) + 34 * (p[k + 1] + p[k + 5]) + 48 * (p[k + 2] + p[k + 4]) + 56 * p[k + 3];
-        uint2 o;
-        o.x = s[0] | (s[1] << 16);
-        o.y = s[2] | (s[3] << 16);
-        *reinterpret_cast<uint2*>(hsum + r * BLUR_TW + 4 * q) = o;
-    }
-    __syncthreads();
-    // vertical pass: item = (group of 4 rows, group of 4 columns)
-    uint8_t* out = L.blur + (long long)f * L.blurStride;
-    for (int it = tid; it < (BLUR_TH / 4) * (BLUR_TW / 4); it += BLUR_THREADS) {
-        const int rg = it / (BLUR_TW / 4), q = it - rg * (BLUR_TW / 4);
-        uint32_t c[10][4];
-#pragma unroll
-        for (int r = 0; r < 10; ++r) {
-            const uint2 v = *reinterpret_cast<const uint2*>(hsum + (4 * rg + r) * BLUR_TW + 4 * q);
-            c[r][0] = v.x & 0xFFFF; c[r][1] = v.x >> 16; c[r][2] = v.y & 0xFFFF; c[r][3] = v.y >> 16;
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t a = k == 3 ? w1 : __funnelshift_r(w0, w1, 8 * (k + 1));
+            const uint32_t b = k == 3 ? w2 : __funnelshift_r(w1, w2, 8 * (k + 1));
+            h[k] = __dp4a(a, K0, __dp4a(b, K1, 0u));
         }
+        if (i >= 1) {
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int y = y0 + 4 * rg + r, x = x0 + 4 * q;
-            uint32_t word = 0;
+            for (int k = 0; k < 4; ++k) pr[(i - 1) & 7][k] = hp[k] | (h[k] << 16);
+        }
+        if (i >= 6) {
+            const int o = i - 6;  // output row of the band: inputs o .. o + 6
+            uint32_t acc[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                const uint32_t acc = 18u * (c[r][k] + c[r + 6][k]) + 34u * (c[r + 1][k] + c[r + 5][k]) +
-                                     48u * (c[r + 2][k] + c[r + 4][k]) + 56u * c[r + 3][k];
-                word |= ((acc + 32768u) >> 16) << (8 * k);
+                uint32_t v = __dp2a_lo(pr[o & 7][k], V0, 32768u);
+                v = __dp2a_lo(pr[(o + 2) & 7][k], V1, v);
+                v = __dp2a_lo(pr[(o + 4) & 7][k], V2, v);
+                acc[k] = v + 18u * h[k];
             }
-            if (y < L.h && x < L.bpitch) *reinterpret_cast<uint32_t*>(out + (long long)y * L.bpitch + x) = word;
+            const uint32_t word = __byte_perm(__byte_perm(acc[0], acc[1], 0x0062), __byte_perm(acc[2], acc[3], 0x0062), 0x5410);
+            if (colOk && yb + o < L.h) *reinterpret_cast<uint32_t*>(out + (long long)(yb + o) * L.bpitch) = word;
         }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) hp[k] = h[k];
     }
 }
 

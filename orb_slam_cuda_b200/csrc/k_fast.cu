@@ -27,7 +27,13 @@
 
 namespace orbx {
 
-constexpr int FS_THREADS = 256;
+#ifndef ORBX_FS_THREADS
+#define ORBX_FS_THREADS 128
+#endif
+#ifndef ORBX_FS_MINBLOCKS
+#define ORBX_FS_MINBLOCKS 8  // measured on B200: 128 x 8 beats 256 x {1, 5, 6} and 128 x 12 (tools/variants.py)
+#endif
+constexpr int FS_THREADS = ORBX_FS_THREADS;
 constexpr int FS_LIST1 = 4096;  // quick-test survivors per row chunk
 constexpr int FS_LIST2 = 2048;  // corners per strip and pass (beyond that NMS scans the score tile)
 constexpr int FS_KP = 1024;     // keypoints per strip
@@ -80,7 +86,7 @@ struct FastShared {
     uint64_t* bar;
 };
 
-__global__ void __launch_bounds__(FS_THREADS) k_fast_strips(const __grid_constant__ FrameGeom g,
+__global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(const __grid_constant__ FrameGeom g,
                                                              const __grid_constant__ TmaMaps maps,
                                                              const FastStrip* __restrict__ strips,
                                                              int* __restrict__ cellCnt, uint32_t* __restrict__ cellKeys,

@@ -110,6 +110,70 @@ __global__ void __launch_bounds__(256) k_pyramid_resize(uint8_t* __restrict__ dp
     }
 }
 
+// Word-based resize (the fast path; used when the 4 destination pixels of a thread read at most 8 consecutive source
+// bytes per row, i.e. for scale factors up to 2).  Per source row a thread loads three aligned words, realigns them to
+// an 8-byte window with two funnel shifts, picks each pixel's (left, right) byte pair with one PRMT whose selector is
+// fixed for the thread, and forms the horizontal blend with one dp2a against the packed 16-bit coefficient pair.
+// The vertical blend keeps OpenCV's truncation order: ((b * (h >> 4)) >> 16) is one multiply-high by (b << 16).
+// Exact 2x decimation (cv::resize's INTER_AREA shortcut) is the same formula with all four coefficients = 1024.
+__global__ void __launch_bounds__(256) k_pyramid_resize4(uint8_t* __restrict__ dplane, int dw, int dh, int dpitch, int drows,
+                                                         long long dStride, const uint8_t* __restrict__ splane, int spitch,
+                                                         long long sStride, const ResizeTab* __restrict__ xtab,
+                                                         const ResizeTab* __restrict__ ytab) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int bx = blockIdx.x * 128 + lane * 4;  // byte column of this thread's 4 pixels
+    if (bx >= dpitch) return;
+    const int f = blockIdx.z;
+    int s0[4], s1[4];
+    uint32_t coef[4], vmask = 0;
+    int smin = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int px = bx + j - PADL;
+        const bool valid = px >= 0 && px < dw + 2 * EDGE;
+        const ResizeTab xt = xtab[valid ? reflect101(px - EDGE, dw) : 0];
+        s0[j] = xt.s0; s1[j] = xt.s1;
+        coef[j] = (uint32_t)(uint16_t)xt.c0 | ((uint32_t)(uint16_t)xt.c1 << 16);
+        if (valid) {
+            vmask |= 0xFFu << (8 * j);
+            smin = min(smin, (int)xt.s0);
+        }
+    }
+    if (vmask == 0) smin = 0;
+    uint32_t sel[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const bool valid = (vmask >> (8 * j)) & 1;
+        sel[j] = valid ? (uint32_t)(s0[j] - smin) | ((uint32_t)(s1[j] - smin) << 4) : 0u;
+    }
+    const int q0 = smin >> 2;
+    const uint32_t sh = (uint32_t)(smin & 3) * 8;
+    const uint32_t* __restrict__ sInt =
+        reinterpret_cast<const uint32_t*>(splane + (long long)f * sStride + (long long)EDGE * spitch + XOFF) + q0;
+    const int spq = spitch >> 2;
+    uint8_t* __restrict__ dbase = dplane + (long long)f * dStride + bx;
+    const int rowEnd = min(blockIdx.y * RZ_ROWS + RZ_ROWS, drows);
+    for (int py = blockIdx.y * RZ_ROWS + warp; py < rowEnd; py += 8) {
+        const ResizeTab yt = ytab[reflect101(py - EDGE, dh)];
+        const uint32_t* __restrict__ r0 = sInt + (int)yt.s0 * spq;
+        const uint32_t* __restrict__ r1 = sInt + (int)yt.s1 * spq;
+        const uint32_t a0 = __ldg(r0), a1 = __ldg(r0 + 1), a2 = __ldg(r0 + 2);
+        const uint32_t b0w = __ldg(r1), b1w = __ldg(r1 + 1), b2w = __ldg(r1 + 2);
+        const uint32_t A0 = __funnelshift_r(a0, a1, sh), A1 = __funnelshift_r(a1, a2, sh);
+        const uint32_t B0 = __funnelshift_r(b0w, b1w, sh), B1 = __funnelshift_r(b1w, b2w, sh);
+        const uint32_t m0 = (uint32_t)(uint16_t)yt.c0 << 16, m1 = (uint32_t)(uint16_t)yt.c1 << 16;
+        uint32_t v = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint32_t h0 = __dp2a_lo(coef[j], __byte_perm(A0, A1, sel[j]), 0u);
+            const uint32_t h1 = __dp2a_lo(coef[j], __byte_perm(B0, B1, sel[j]), 0u);
+            const uint32_t val = (__umulhi(m0, h0 >> 4) + __umulhi(m1, h1 >> 4) + 2u) >> 2;  // <= 255
+            v |= val << (8 * j);
+        }
+        *reinterpret_cast<uint32_t*>(dbase + (long long)py * dpitch) = v & vmask;
+    }
+}
+
 int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
                         cudaStream_t s) {
     const LevelGeom& L = g.lv[0];
@@ -126,8 +190,12 @@ int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, c
     const LevelGeom& D = g.lv[level];
     const LevelGeom& S = g.lv[level - 1];
     dim3 grid((D.pitch + 127) / 128, (D.rows + RZ_ROWS - 1) / RZ_ROWS, batch);
-    k_pyramid_resize<<<grid, 256, 0, s>>>(D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, S.plane, S.pitch,
-                                            S.planeStride, xtab, ytab, areaFast);
+    if (areaFast & 2)  // bit 1: every thread's source window fits 8 bytes -> word-based kernel
+        k_pyramid_resize4<<<grid, 256, 0, s>>>(D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, S.plane, S.pitch,
+                                                 S.planeStride, xtab, ytab);
+    else
+        k_pyramid_resize<<<grid, 256, 0, s>>>(D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, S.plane, S.pitch,
+                                                S.planeStride, xtab, ytab, areaFast & 1);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

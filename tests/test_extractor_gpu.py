@@ -144,3 +144,16 @@ def test_quadtree_standalone_random():
         a = X.distribute_octtree(keys, 16, 16 + W, 16, 16 + H, N)
         b = O.distribute(keys, 16, 16 + W, 16, 16 + H, N)
         assert kp_tuple(a) == kp_tuple(b), f"trial {trial}: W={W} H={H} n={len(pts)} N={N}: {len(a)} vs {len(b)}"
+
+
+@pytest.mark.parametrize("sf,nl", [(2.0, 4), (1.5, 5), (2.5, 3), (1.1, 8)])
+def test_other_scale_factors(sf, nl):
+    # 2.0 = cv::resize's INTER_AREA shortcut on even sizes; 2.5 = source windows wider than 8 bytes (byte-gather kernel)
+    gx, ox = X.ORBextractor(800, sf, nl, 20, 7), O.Extractor(800, sf, nl, 20, 7)
+    img = synth.frame("tum", 61)
+    k, d = gx(img)
+    ok, od = ox.extract(img)
+    for l in range(nl):
+        a, b = gx.image_pyramid_level(l, padded=True), ox.level_padded(l)
+        assert np.array_equal(a, b), f"sf {sf} level {l}: {(a != b).sum()} padded pixels differ"
+    assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od)
