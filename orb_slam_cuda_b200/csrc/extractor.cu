@@ -71,10 +71,14 @@ struct orbx_extractor {
     int hostLevelFrame[ORBX_MAX_LEVELS];
     long long hostLevelSerial[ORBX_MAX_LEVELS];
     long long serial = 0;    // bumped by every extract call
+    // host-buffer batches are cut into chunks pipelined over three streams: H2D | kernels (stream) | D2H
+    cudaStream_t h2dStream = nullptr, d2hStream = nullptr;
+    std::vector<cudaEvent_t> pipeEv;  // 2 per chunk: frames landed, kernels done
     bool timing = false;
     bool timed = false;      // the last call recorded events
     cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
     int lastBatch = 0;
+    int lastFrameBase = 0;   // index (within the caller's batch) of frame 0 of the scratch: > 0 after a chunked host batch
 };
 
 // ---- constructor tables (src/ORBextractor.cc:501-555) -----------------------------------------------------------
@@ -349,11 +353,12 @@ static int stage_sync(const char* stage, cudaStream_t s) {  // ORBX_DEBUG_SYNC=1
 }
 
 static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
-                        orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dCounts, int* dStatus, cudaStream_t s) {
+                        orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dCounts, int* dStatus, cudaStream_t s,
+                        bool resetStatus = true) {
     const FrameGeom& g = ex->g;
     const int nl = g.nlevels;
     int rc;
-    ORBX_CUDA(cudaMemsetAsync(dStatus, 0, sizeof(int), s));
+    if (resetStatus) ORBX_CUDA(cudaMemsetAsync(dStatus, 0, sizeof(int), s));
     if ((rc = stage_sync("input copy", s))) return rc;
     const bool tm = ex->timing;
     ex->timed = tm;
@@ -472,6 +477,12 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
         cudaStreamSynchronize(ex->stream);
         cudaStreamDestroy(ex->stream);
     }
+    for (cudaStream_t st : {ex->h2dStream, ex->d2hStream})
+        if (st) {
+            cudaStreamSynchronize(st);
+            cudaStreamDestroy(st);
+        }
+    for (cudaEvent_t e : ex->pipeEv) cudaEventDestroy(e);
     for (cudaEvent_t e : ex->ev)
         if (e) cudaEventDestroy(e);
     for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
@@ -547,6 +558,7 @@ int orbx_extract_batch_device(orbx_extractor* ex, const uint8_t* dFrames, int ba
     }
     if ((rc = configure(ex, w, h, batch))) return rc;
     cudaStream_t s = stream ? (cudaStream_t)stream : ex->stream;
+    ex->lastFrameBase = 0;
     return run_pipeline(ex, dFrames, batch, stride, frameStride, dKps, dDesc, cap, dCounts,
                         dStatus ? dStatus : ex->status.as<int>(), s);
 }
@@ -570,47 +582,87 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
         return ORBX_OK;
     }
     if (stride < (size_t)w || !kps || !desc || cap < 1) { set_error("orbx_extract_batch: bad argument"); return ORBX_E_INVALID; }
-    if ((rc = configure(ex, w, h, batch))) return rc;
+    // The batch is cut into chunks that flow through three streams — H2D | kernels | D2H — so the copies of chunk c+1 and
+    // c-1 overlap the kernels of chunk c.  The scratch (pyramids, cell lists ...) is sized for ONE chunk and reused, since
+    // the kernels of successive chunks are serial on the handle's stream anyway; small batches are a single chunk.
+    static const int chunkPref = []() { const char* e = getenv("ORBX_PIPE_CHUNK"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 64; }();
+    const int nChunks = std::max(1, batch / chunkPref), C = (batch + nChunks - 1) / nChunks;
+    if ((rc = configure(ex, w, h, C))) return rc;
     cudaStream_t s = ex->stream;
     const size_t rowBytes = (size_t)w, frameBytes = rowBytes * h;
     if ((rc = ex->dFrames.ensure(frameBytes * batch + 16))) return rc;
     if ((rc = ex->dKps.ensure((size_t)batch * cap * sizeof(orbx_keypoint)))) return rc;
     if ((rc = ex->dDesc.ensure((size_t)batch * cap * 32))) return rc;
     if ((rc = ex->dCounts.ensure((size_t)batch * 4))) return rc;
-    // H2D: straight from the caller's buffer when it is pinned and tightly packed, else through pinned staging
-    const bool tight = stride == rowBytes && (frameStride == frameBytes || batch == 1);
-    if (tight && is_pinned(frames)) {
-        ORBX_CUDA(cudaMemcpyAsync(ex->dFrames.p, frames, frameBytes * batch, cudaMemcpyHostToDevice, s));
-    } else {
-        if ((rc = ex->hFrames.ensure(frameBytes * batch))) return rc;
-        uint8_t* st = ex->hFrames.as<uint8_t>();
-        for (int f = 0; f < batch; ++f)
-            for (int y = 0; y < h; ++y)
-                memcpy(st + (size_t)f * frameBytes + (size_t)y * rowBytes, frames + (size_t)f * frameStride + (size_t)y * stride, rowBytes);
-        ORBX_CUDA(cudaMemcpyAsync(ex->dFrames.p, st, frameBytes * batch, cudaMemcpyHostToDevice, s));
+    cudaStream_t sIn = s, sOut = s;
+    if (nChunks > 1) {
+        if (!ex->h2dStream) ORBX_CUDA(cudaStreamCreateWithFlags(&ex->h2dStream, cudaStreamNonBlocking));
+        if (!ex->d2hStream) ORBX_CUDA(cudaStreamCreateWithFlags(&ex->d2hStream, cudaStreamNonBlocking));
+        while ((int)ex->pipeEv.size() < 2 * nChunks) {
+            cudaEvent_t e;
+            ORBX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            ex->pipeEv.push_back(e);
+        }
+        sIn = ex->h2dStream;
+        sOut = ex->d2hStream;
     }
-    if ((rc = run_pipeline(ex, ex->dFrames.as<uint8_t>(), batch, rowBytes, frameBytes, ex->dKps.as<orbx_keypoint>(),
-                           ex->dDesc.as<uint8_t>(), cap, ex->dCounts.as<int>(), ex->status.as<int>(), s)))
-        return rc;
-    // D2H
-    const size_t kpBytes = (size_t)batch * cap * sizeof(orbx_keypoint), dBytes = (size_t)batch * cap * 32;
+    // H2D straight from the caller's buffer when it is pinned and tightly packed, else through pinned staging;
+    // D2H straight into the caller's buffers when they are pinned
+    const bool tight = stride == rowBytes && (frameStride == frameBytes || batch == 1);
+    const bool directIn = tight && is_pinned(frames);
     const bool direct = is_pinned(kps) && is_pinned(desc) && is_pinned(counts);
+    if (!directIn && (rc = ex->hFrames.ensure(frameBytes * batch))) return rc;
     orbx_keypoint* hk = kps;
     uint8_t* hd = desc;
     int* hc = counts;
     if (!direct) {
-        if ((rc = ex->hKps.ensure(kpBytes))) return rc;
-        if ((rc = ex->hDesc.ensure(dBytes))) return rc;
+        if ((rc = ex->hKps.ensure((size_t)batch * cap * sizeof(orbx_keypoint)))) return rc;
+        if ((rc = ex->hDesc.ensure((size_t)batch * cap * 32))) return rc;
         if ((rc = ex->hCounts.ensure((size_t)batch * 4))) return rc;
         hk = ex->hKps.as<orbx_keypoint>();
         hd = ex->hDesc.as<uint8_t>();
         hc = ex->hCounts.as<int>();
     }
-    ORBX_CUDA(cudaMemcpyAsync(hc, ex->dCounts.p, (size_t)batch * 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(hk, ex->dKps.p, kpBytes, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(hd, ex->dDesc.p, dBytes, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(ex->hStatus.p, ex->status.p, 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaStreamSynchronize(s));
+    ORBX_CUDA(cudaMemsetAsync(ex->status.p, 0, sizeof(int), s));
+    uint8_t* dF = ex->dFrames.as<uint8_t>();
+    orbx_keypoint* dK = ex->dKps.as<orbx_keypoint>();
+    uint8_t* dD = ex->dDesc.as<uint8_t>();
+    int* dC = ex->dCounts.as<int>();
+    for (int c = 0, f0 = 0; c < nChunks; ++c, f0 += C) {
+        const int nb = std::min(C, batch - f0);
+        const uint8_t* src = frames + (size_t)f0 * frameStride;
+        if (!directIn) {
+            uint8_t* st = ex->hFrames.as<uint8_t>() + (size_t)f0 * frameBytes;
+            for (int f = 0; f < nb; ++f)
+                for (int y = 0; y < h; ++y)
+                    memcpy(st + (size_t)f * frameBytes + (size_t)y * rowBytes, src + (size_t)f * frameStride + (size_t)y * stride, rowBytes);
+            src = st;
+        }
+        ORBX_CUDA(cudaMemcpyAsync(dF + (size_t)f0 * frameBytes, src, frameBytes * nb, cudaMemcpyHostToDevice, sIn));
+        if (nChunks > 1) {
+            ORBX_CUDA(cudaEventRecord(ex->pipeEv[2 * c], sIn));
+            ORBX_CUDA(cudaStreamWaitEvent(s, ex->pipeEv[2 * c], 0));
+        }
+        if ((rc = run_pipeline(ex, dF + (size_t)f0 * frameBytes, nb, rowBytes, frameBytes, dK + (size_t)f0 * cap,
+                               dD + (size_t)f0 * cap * 32, cap, dC + f0, ex->status.as<int>(), s, false)))
+            return rc;
+        if (nChunks > 1) {
+            ORBX_CUDA(cudaEventRecord(ex->pipeEv[2 * c + 1], s));
+            ORBX_CUDA(cudaStreamWaitEvent(sOut, ex->pipeEv[2 * c + 1], 0));
+        }
+        ORBX_CUDA(cudaMemcpyAsync(hc + f0, dC + f0, (size_t)nb * 4, cudaMemcpyDeviceToHost, sOut));
+        ORBX_CUDA(cudaMemcpyAsync(hk + (size_t)f0 * cap, dK + (size_t)f0 * cap, (size_t)nb * cap * sizeof(orbx_keypoint),
+                                  cudaMemcpyDeviceToHost, sOut));
+        ORBX_CUDA(cudaMemcpyAsync(hd + (size_t)f0 * cap * 32, dD + (size_t)f0 * cap * 32, (size_t)nb * cap * 32,
+                                  cudaMemcpyDeviceToHost, sOut));
+        ex->lastFrameBase = f0;
+    }
+    ORBX_CUDA(cudaMemcpyAsync(ex->hStatus.p, ex->status.p, 4, cudaMemcpyDeviceToHost, sOut));
+    ORBX_CUDA(cudaStreamSynchronize(sOut));
+    if (nChunks > 1) {
+        ORBX_CUDA(cudaStreamSynchronize(sIn));
+        ORBX_CUDA(cudaStreamSynchronize(s));
+    }
     if (!direct) {
         memcpy(counts, hc, (size_t)batch * 4);
         for (int f = 0; f < batch; ++f) {
@@ -641,7 +693,7 @@ extern "C" {
 int orbx_pyramid_level_host(orbx_extractor* ex, int frame, int level, const uint8_t** interior, int* w, int* h, size_t* pitch) {
     int rc = check_device(ex);
     if (rc) return rc;
-    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || frame < 0 || frame >= ex->lastBatch) {
+    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || (frame -= ex->lastFrameBase) < 0 || frame >= ex->lastBatch) {
         set_error("orbx_pyramid_level_host: no such frame/level (frame %d level %d, last batch %d)", frame, level, ex->lastBatch);
         return ORBX_E_INVALID;
     }
@@ -664,7 +716,7 @@ int orbx_pyramid_level_host(orbx_extractor* ex, int frame, int level, const uint
 int orbx_debug_blurred_level(orbx_extractor* ex, int frame, int level, uint8_t* out) {
     int rc = check_device(ex);
     if (rc) return rc;
-    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || frame < 0 || frame >= ex->lastBatch || !out) {
+    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || (frame -= ex->lastFrameBase) < 0 || frame >= ex->lastBatch || !out) {
         set_error("orbx_debug_blurred_level: bad argument");
         return ORBX_E_INVALID;
     }
@@ -678,7 +730,7 @@ int orbx_debug_blurred_level(orbx_extractor* ex, int frame, int level, uint8_t* 
 int orbx_debug_candidates(orbx_extractor* ex, int frame, int level, orbx_keypoint* out, int cap, int* n) {
     int rc = check_device(ex);
     if (rc) return rc;
-    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || frame < 0 || frame >= ex->lastBatch || !n) {
+    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || (frame -= ex->lastFrameBase) < 0 || frame >= ex->lastBatch || !n) {
         set_error("orbx_debug_candidates: bad argument");
         return ORBX_E_INVALID;
     }
@@ -708,7 +760,7 @@ int orbx_debug_candidates(orbx_extractor* ex, int frame, int level, orbx_keypoin
 int orbx_debug_level_keypoints(orbx_extractor* ex, int frame, int level, orbx_keypoint* out, int cap, int* n) {
     int rc = check_device(ex);
     if (rc) return rc;
-    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || frame < 0 || frame >= ex->lastBatch || !n) {
+    if (ex->serial == 0 || level < 0 || level >= ex->prm.nlevels || (frame -= ex->lastFrameBase) < 0 || frame >= ex->lastBatch || !n) {
         set_error("orbx_debug_level_keypoints: bad argument");
         return ORBX_E_INVALID;
     }

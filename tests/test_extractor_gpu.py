@@ -108,6 +108,37 @@ def test_batch_equals_single():
         assert np.array_equal(desc[f, :n], od)
 
 
+@pytest.mark.parametrize("pinned", [False, True])
+def test_chunked_host_batch(pinned):
+    """Host batches of >= 128 frames are pipelined in chunks over three streams (H2D | kernels | D2H): every frame
+    must come out as if extracted alone, and the pyramid accessor serves the last chunk by batch index."""
+    import torch
+    h, w, nf, b = 120, 160, 300, 131
+    gx, ox = X.ORBextractor(nf, 1.2, 8, 20, 7), O.Extractor(nf, 1.2, 8, 20, 7)
+    pool = np.stack([synth.textured_frame(900 + i, h, w) for i in range(7)])
+    frames = pool[np.arange(b) % 7].copy()
+    frames[:, 0, 0] = np.arange(b, dtype=np.uint8)  # make every frame distinct
+    cap = gx.default_cap()
+    if pinned:
+        tf = torch.from_numpy(frames).pin_memory()
+        tk = torch.empty((b, cap, 7), dtype=torch.int32).pin_memory()
+        td = torch.empty((b, cap, 32), dtype=torch.uint8).pin_memory()
+        tc = torch.empty(b, dtype=torch.int32).pin_memory()
+        kps, desc, counts = gx.extract_batch(tf.numpy(), tk.numpy().view(X.KP_DTYPE).reshape(b, cap), td.numpy(), tc.numpy(), cap)
+    else:
+        kps, desc, counts = gx.extract_batch(frames)
+    for f in [0, 1, 63, 64, 65, 66, 127, 128, 129, 130]:
+        ok, od = ox.extract(frames[f])
+        n = counts[f]
+        assert n == len(ok), f
+        assert np.array_equal(kps[f, :n].view(np.uint8), ok.view(np.uint8)), f
+        assert np.array_equal(desc[f, :n], od), f
+    ox.extract(frames[b - 1])
+    assert np.array_equal(gx.image_pyramid_level(3, frame=b - 1, padded=True), ox.level_padded(3))
+    with pytest.raises(Exception):
+        gx.image_pyramid_level(0, frame=0)  # not in the last chunk any more
+
+
 def test_strided_input_and_empty():
     gx, ox = make("tum")
     big = np.zeros((500, 700), np.uint8)
