@@ -116,15 +116,96 @@ def make_frames(workload: str, n: int, first: int = 0) -> np.ndarray:
     return synth.frame_batch(workload, n, pool=min(n, 32), first=first)
 
 
-def cpu_extract_rate(workload: str, nframes: int, threads: int):
+def cpu_extract_rate(workload: str, nframes: int, threads: int, min_secs: float = 0.0):
     """frames/s of the CPU oracle, frame-parallel over `threads` host threads (one extractor per thread, as the
     reference runs one per eye, src/Frame.cc:77-80)."""
     from oracle import oracle_lib as O
     wl = WORKLOADS[workload]
     frames = make_frames(workload, nframes, first=1000)
     O.bench_extract(frames[:max(1, min(threads, nframes))], wl["nfeatures"], SCALE, LEVELS, INI_TH, MIN_TH, threads)  # warm
-    secs, nk = O.bench_extract(frames, wl["nfeatures"], SCALE, LEVELS, INI_TH, MIN_TH, threads)
-    return nframes / secs, secs, nk
+    secs, nk, done = 0.0, 0, 0
+    while secs < min_secs or done == 0:  # the same block of frames again until the sample holds >= min_secs of CPU work
+        t, k = O.bench_extract(frames, wl["nfeatures"], SCALE, LEVELS, INI_TH, MIN_TH, threads)
+        secs, nk, done = secs + t, nk + k, done + nframes
+    return done / secs, secs, done
+
+
+def match_leg(X, torch, dist, rank, world, stream, K):
+    """Gmatch/s (descriptor pairs compared per second / 1e9) of the Hamming matchers, device resident, CUDA events on
+    the launching stream: (a) 2000 x 2000 brute force best / second-best + TH_LOW / ratio test (config 4's inner loop),
+    (b) all-vs-all keyframe matching sharded by query block, database all-gathered over NCCL when world > 1
+    (config 5).  Strong scaling for (b): the keyframe count is fixed as N grows."""
+    from orb_slam_cuda_b200 import synth, sharding
+    m = X.ORBmatcher(0.6, True)
+    q, d = synth.descriptor_sets(4, 2000, 2000)
+    dq, dd = torch.from_numpy(q).cuda(), torch.from_numpy(d).cuda()
+    out = [torch.empty(2000, dtype=torch.int32, device="cuda") for _ in range(4)]
+    reps = 200
+
+    def bf():
+        m.match_bruteforce_device(dq.data_ptr(), 2000, dd.data_ptr(), 2000, *[o.data_ptr() for o in out], stream=stream)
+
+    for _ in range(10):
+        bf()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        bf()
+    e1.record()
+    torch.cuda.synchronize()
+    bf_ms = e0.elapsed_time(e1) / reps
+    # (b) all-vs-all: k_total keyframes x 2000 descriptors, query blocks per rank
+    k_total, n = 96, 2000
+    b, e = sharding.block_range(k_total, rank, world)
+    rng = np.random.default_rng(77)
+    all_desc = rng.integers(0, 256, size=(k_total, n, 32), dtype=np.uint8)
+    local = torch.from_numpy(all_desc[b:e]).cuda()
+
+    def score_fn(qq, db, o):
+        m.match_allpairs_device(qq.data_ptr(), qq.shape[0], db.data_ptr(), db.shape[0], n, o.data_ptr(), stream=stream)
+
+    def ap():
+        return sharding.allpairs_sharded(local, k_total, score_fn, chunks=4)
+
+    ap()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(K):
+        sc, moved = ap()
+    e1.record()
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / K], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ap_ms = float(t[0])
+    return {"bruteforce_2000x2000": {"gmatch_per_s": 2000 * 2000 / (bf_ms * 1e-3) / 1e9, "ms": bf_ms, "launches_per_call": 2},
+            "allpairs": {"gmatch_per_s": float(k_total) * k_total * n * n / (ap_ms * 1e-3) / 1e9, "ms": ap_ms,
+                         "keyframes": k_total, "descriptors_per_keyframe": n, "sharding": "query block per rank, database all-gathered in 4 chunks",
+                         "allgather_bytes_per_rank": int(moved), "scaling": "strong"},
+            "unit": "Gmatch/s (descriptor pairs compared / s / 1e9)"}
+
+
+def latency_leg(X, wl, w, h, kind):
+    """p50 / p95 wall-clock latency of single-frame orbx_extract calls (pageable host frame in, keypoints + descriptors
+    out; what ORBextractor::operator() costs the Tracking thread per frame)."""
+    from orb_slam_cuda_b200 import synth
+    ex1 = X.ORBextractor(wl["nfeatures"], SCALE, LEVELS, INI_TH, MIN_TH, w, h, max_batch=1)
+    imgs = [synth.frame(kind, 500 + i) for i in range(8)]
+    for i in range(10):
+        ex1(imgs[i % 8])
+    ts = []
+    for i in range(200):
+        t0 = time.perf_counter()
+        ex1(imgs[i % 8])
+        ts.append((time.perf_counter() - t0) * 1e3)
+    ts = np.sort(np.array(ts))
+    return {"p50_ms": float(ts[len(ts) // 2]), "p95_ms": float(ts[int(len(ts) * 0.95)]), "calls": len(ts),
+            "path": "orbx_extract through the python binding, pageable host buffers"}
 
 
 def run_reference(args):
@@ -134,7 +215,7 @@ def run_reference(args):
         return
     wl = WORKLOADS[args.workload]
     threads = host_threads()
-    per_step = max(threads, 4 * threads)  # bounded sample of the workload per step
+    per_step = max(64, 16 * threads)  # bounded sample of the workload per step
     from oracle import oracle_lib as O
     frames = make_frames(args.workload, per_step, first=1000)
     a = (wl["nfeatures"], SCALE, LEVELS, INI_TH, MIN_TH, threads)
@@ -251,6 +332,8 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     assert np.array_equal(h_counts.numpy(), counts), "host and device paths disagree"
 
+    match = None if args.no_match else match_leg(X, torch, dist, rank, world, stream, max(2, K // 2))
+
     t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -291,14 +374,22 @@ def run_ours(args):
         "stage_ms_per_step": stage,
         "status": status,
     }
+    if match is not None:
+        sm_hz = (clocks or {}).get("sm_mhz") or 1965.0
+        match["popc_bound_gmatch_per_s"] = 148 * 16 * sm_hz * 1e6 / 8 / 1e9 * world
+        match["popc_bound"] = "148 SMs x 16 POPC/clk/SM x SM clock / 8 POPC per pair (x N GPUs)"
+        line["match"] = match
+    if world == 1:
+        line["latency"] = latency_leg(X, wl, w, h, args.workload)
     if not args.no_cpu_baseline and world == 1:
         threads = host_threads()
-        n = args.cpu_frames or max(threads, 8 * threads)
-        rate, secs, _ = cpu_extract_rate(args.workload, n, threads)
+        n = args.cpu_frames or max(threads, 16 * threads)
+        rate, secs, done = cpu_extract_rate(args.workload, n, threads, min_secs=12.0)
         line["cpu_baseline"] = {"value": rate, "unit": "frames/s", "cores": threads, "kind": "port",
-                                "sample": f"{n} frames of the same workload in {secs:.1f} s, frame-parallel over {threads} threads"}
-        rate1, secs1, _ = cpu_extract_rate(args.workload, max(4, n // threads), 1)
+                                "sample": f"{done} frames of the same workload ({n} distinct) in {secs:.1f} s, frame-parallel over {threads} threads"}
+        rate1, secs1, done1 = cpu_extract_rate(args.workload, 16, 1, min_secs=3.0)
         line["cpu_baseline"]["single_thread_frames_per_s"] = rate1
+        line["cpu_baseline"]["single_thread_sample"] = f"{done1} frames in {secs1:.1f} s on 1 thread"
     print(json.dumps(line), flush=True)
     if dist is not None:
         dist.destroy_process_group()

@@ -97,7 +97,8 @@ __device__ __forceinline__ void glibc_sincosf(float y, float* sn, float* cs) {
 constexpr int DESC_WARPS = 8;
 constexpr int DESC_PER_WARP = 4;   // keypoint slots a warp walks (amortises the table set-up of the CTA)
 constexpr int BP_HALF = 18;        // the rotated pattern reaches |coordinate| <= cvRound(18.38) = 18
-constexpr int BP_ROWS = 2 * BP_HALF + 1, BP_WORDS = 11, BP_STRIDE = BP_WORDS * 4;  // 37 rows of 11 aligned words
+constexpr int BP_ROWS = 2 * BP_HALF + 1;  // 37 rows; a row is 48 bytes read from an 8-byte aligned address (6 x 64-bit loads)
+constexpr int BP_WORDS = 13, BP_STRIDE = BP_WORDS * 4;  // shared row stride: 13 words (odd, spreads rows over the banks)
 
 // Tables the kernel copies into shared memory, filled once per process by init_describe_tables():
 //   d_patF  : the 512 pattern points as floats, laid out [pair k of the lane][lane] as (x0, y0, x1, y1)
@@ -124,6 +125,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     __shared__ float4 patF[8 * 32];
     __shared__ uint32_t coefU[32 * 8], coefV[32 * 8];
     __shared__ uint32_t bpatch[DESC_WARPS][BP_ROWS * BP_WORDS + 1];
+    __shared__ int sBefore[ORBX_MAX_LEVELS + 1];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         patF[i] = d_patF[i];
         coefU[i] = d_coefU[i];
@@ -132,12 +134,19 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, f = blockIdx.y;
     const int* cnt = lvlCnt + (long long)f * g.nlevels;
-    int total = 0;
-    for (int l = 0; l < g.nlevels; ++l) total += cnt[l];
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        counts[f] = min(total, cap);
-        if (total > cap) atomicExch(dStatus, ORBX_E_OVERFLOW);
+    if (threadIdx.x == 0) {  // exclusive prefix of the per-level counts = output position of each level's first keypoint
+        int total = 0;
+        for (int l = 0; l < g.nlevels; ++l) {
+            sBefore[l] = total;
+            total += cnt[l];
+        }
+        sBefore[g.nlevels] = total;
+        if (blockIdx.x == 0) {
+            counts[f] = min(total, cap);
+            if (total > cap) atomicExch(dStatus, ORBX_E_OVERFLOW);
+        }
     }
+    __syncthreads();
     uint32_t* bp = bpatch[warp];
     const uint8_t* bp8 = reinterpret_cast<const uint8_t*>(bp);
 
@@ -148,9 +157,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
         while (level + 1 < g.nlevels && slot >= g.lv[level + 1].slotBase) ++level;
         const LevelGeom& L = g.lv[level];
         const int j = slot - L.slotBase;
-        if (j >= cnt[level]) continue;
-        int before = 0;
-        for (int l = 0; l < level; ++l) before += cnt[l];
+        const int before = sBefore[level];
+        if (j >= sBefore[level + 1] - before) continue;
         const uint32_t key = lvlKeys[(long long)f * g.slotsTotal + slot];
         const int x = key_x(key), y = key_y(key);
 
@@ -183,13 +191,21 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
 
         // ---- stage the 37 x 37 blurred patch (rows of 11 aligned words covering columns x-18 .. x+18) ----
         const uint8_t* brow = L.blur + (long long)f * L.blurStride + (long long)(y - BP_HALF) * L.bpitch + (x - BP_HALF);
-        const int mis = (int)(reinterpret_cast<uintptr_t>(brow) & 3);
-        const uint32_t* bw = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(brow) & ~(uintptr_t)3);
-        const int bpq = L.bpitch >> 2;
+        const int mis = (int)(reinterpret_cast<uintptr_t>(brow) & 7);
+        const uint2* bw = reinterpret_cast<const uint2*>(reinterpret_cast<uintptr_t>(brow) & ~(uintptr_t)7);
+        const int bpo = L.bpitch >> 3;
         __syncwarp();
-        for (int i = lane; i < BP_ROWS * BP_WORDS; i += 32) {
-            const int r = i / BP_WORDS, wq = i - r * BP_WORDS;
-            bp[i] = __ldg(bw + r * bpq + wq);
+        if (lane < 30) {  // lanes = 5 rows x 6 double words per step, 8 steps cover rows 0..39 (rows >= 37 are skipped)
+            const int rsub = lane / 6, q = lane - rsub * 6;
+#pragma unroll
+            for (int r5 = 0; r5 < 8; ++r5) {
+                const int r = r5 * 5 + rsub;
+                if (r < BP_ROWS) {
+                    const uint2 v = __ldg(bw + r * bpo + q);
+                    bp[r * BP_WORDS + 2 * q] = v.x;
+                    bp[r * BP_WORDS + 2 * q + 1] = v.y;
+                }
+            }
         }
         __syncwarp();
 

@@ -11,9 +11,10 @@
 //          compares of the 8 EVEN ring points (rows y+-3, y+-2, y realigned with funnel shifts).  A run of 9 ring points
 //          holds 4 consecutive even ones, so a pixel survives iff 4 consecutive even points are all brighter (or all
 //          darker).  Warps walk rows, lanes walk 32-bit words, so there is no index division;
-//   B      survivors (dense list) take the full 16-point segment test (bit-mask run-of-9 detection); corners get
-//          OpenCV's cornerScore<16>: max over the 16 arcs of 9 of the min |difference|, both polarities, minus 1,
-//          stored in a shared score tile (0 = not a corner), and join the corner list;
+//   B      survivors (dense list) get OpenCV's cornerScore<16>: max over the 16 arcs of 9 of the min signed difference,
+//          both polarities at once as packed 16-bit pairs (VIMNMX3.S16x2), minus 1.  score >= t is exactly the
+//          16-point segment test, so no separate run-of-9 detection is needed; corners store the score in a shared
+//          score tile (0 = not a corner) and join the corner list;
 //   C      corners strictly greater than their 8 neighbours OF THE SAME CELL survive and are counted per cell;
 //   pass 2 cells that are still empty repeat A-C at minThFAST (:1281-1285); pixels of other cells are masked out;
 //   D      survivors are ranked by position inside their cell (cv::FAST's row-major order) and written to the cell's slot.
@@ -34,43 +35,39 @@ namespace orbx {
 #define ORBX_FS_MINBLOCKS 8  // measured on B200: 128 x 8 beats 256 x {1, 5, 6} and 128 x 12 (tools/variants.py)
 #endif
 constexpr int FS_THREADS = ORBX_FS_THREADS;
-constexpr int FS_LIST1 = 4096;  // quick-test survivors per row chunk
+#ifndef ORBX_FS_LIST1
+#define ORBX_FS_LIST1 4096
+#endif
+constexpr int FS_LIST1 = ORBX_FS_LIST1;  // quick-test survivors per row chunk
 constexpr int FS_LIST2 = 2048;  // corners per strip and pass (beyond that NMS scans the score tile)
 constexpr int FS_KP = 1024;     // keypoints per strip
 
 __constant__ int c_ringDx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
 __constant__ int c_ringDy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
 
-// true iff the 16-bit circular mask holds a run of >= 9 set bits
-__device__ __forceinline__ bool has_run9(uint32_t m16) {
-    uint32_t x = m16 | (m16 << 16);
-    uint32_t a = x & (x >> 1);
-    a &= a >> 2;
-    a &= a >> 4;
-    a &= x >> 8;
-    return (a & 0xFFFFu) != 0;
+// OpenCV's cornerScore<16> for both polarities at once.  e[k] holds (256 + d_k) in its low and (256 - d_k) in its high
+// 16-bit half, d_k = v - ring_k, so one packed min / max (VIMNMX3.S16x2) serves the "darker ring" and the "brighter
+// ring" case together.  Returns max over the 16 circular arcs of 9 of the arc minimum, per half (still biased by 256).
+__device__ __forceinline__ uint32_t best_arc_min_x2(const uint32_t (&e)[16]) {
+    uint32_t m3[16], m9[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) m3[k] = __vimin3_s16x2(e[k], e[(k + 1) & 15], e[(k + 2) & 15]);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) m9[k] = __vimin3_s16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+    const uint32_t a = __vimax3_s16x2(m9[0], m9[1], m9[2]), b = __vimax3_s16x2(m9[3], m9[4], m9[5]);
+    const uint32_t c = __vimax3_s16x2(m9[6], m9[7], m9[8]), d = __vimax3_s16x2(m9[9], m9[10], m9[11]);
+    const uint32_t f = __vimax3_s16x2(m9[12], m9[13], m9[14]);
+    return __vimax3_s16x2(__vimax3_s16x2(a, b, c), __vimax3_s16x2(d, f, m9[15]), a);
 }
 
-// max over the 16 circular arcs of length 9 of the minimum of e[]
-__device__ __forceinline__ int best_arc_min(const int (&e)[16]) {
-    int m2[16], m4[16], best = -1000;
-#pragma unroll
-    for (int k = 0; k < 16; ++k) m2[k] = min(e[k], e[(k + 1) & 15]);
-#pragma unroll
-    for (int k = 0; k < 16; ++k) m4[k] = min(m2[k], m2[(k + 2) & 15]);
-#pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        const int m8 = min(m4[k], m4[(k + 4) & 15]);
-        best = max(best, min(m8, e[(k + 8) & 15]));
-    }
-    return best;
-}
-
-// per-byte unsigned a > b: the most significant bit of every byte of the result is the flag (other bits are junk)
-__device__ __forceinline__ uint32_t gtu4_msb(uint32_t a, uint32_t b, uint32_t notb7) {
-    const uint32_t s = (a & 0x7f7f7f7fu) + notb7;  // notb7 = ~b & 0x7f7f7f7f; bit 7 of each byte = (a & 127) > (b & 127)
+__device__ __forceinline__ uint32_t lop3_and3(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t r;
-    asm("lop3.b32 %0, %1, %2, %3, 0xb2;" : "=r"(r) : "r"(a), "r"(b), "r"(s));  // a7 & ~b7 | ~(a7 ^ b7) & s7
+    asm("lop3.b32 %0, %1, %2, %3, 0x80;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t lop3_or_and(uint32_t a, uint32_t b, uint32_t c) {  // a | (b & c)
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xf8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
     return r;
 }
 
@@ -189,7 +186,10 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
                     if (vm == 0) continue;
                     const uint32_t c = rowc[w];
                     const uint32_t hi = __vaddus4(c, T4), lo = __vsubus4(c, T4);  // saturating v + t, v - t
-                    const uint32_t HN7 = ~hi & 0x7f7f7f7fu, LO7 = lo & 0x7f7f7f7fu;
+                    // per-byte unsigned compares without cross-byte carries: with r7 = r & 0x7f.., bit 7 of (r7 + (~hi & 0x7f..))
+                    // is (r & 127) > (hi & 127) and bit 7 of (r7 + (~lo & 0x7f..) + 0x01..) is (r & 127) >= (lo & 127); one
+                    // LOP3 per compare merges it with the top bits (0xb2: r > hi; 0x4d: !(r >= lo), i.e. v - t > r)
+                    const uint32_t HN7 = ~hi & 0x7f7f7f7fu, LN7 = (~lo & 0x7f7f7f7fu) + 0x01010101u;
                     uint32_t ring[8];
                     ring[0] = rowc[w + 3 * TWq];                                                       // ( 0, +3)
                     ring[4] = rowc[w - 3 * TWq];                                                       // ( 0, -3)
@@ -210,17 +210,16 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
                     uint32_t br[8], dk[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        br[k] = gtu4_msb(ring[k], hi, HN7);  // r > v + t
-                        uint32_t d;
-                        const uint32_t sd = LO7 + (~ring[k] & 0x7f7f7f7fu);
-                        asm("lop3.b32 %0, %1, %2, %3, 0xb2;" : "=r"(d) : "r"(lo), "r"(ring[k]), "r"(sd));  // v - t > r
-                        dk[k] = d;
+                        const uint32_t r7 = ring[k] & 0x7f7f7f7fu;
+                        const uint32_t sb = r7 + HN7, sd = r7 + LN7;
+                        asm("lop3.b32 %0, %1, %2, %3, 0xb2;" : "=r"(br[k]) : "r"(ring[k]), "r"(hi), "r"(sb));
+                        asm("lop3.b32 %0, %1, %2, %3, 0x4d;" : "=r"(dk[k]) : "r"(ring[k]), "r"(lo), "r"(sd));
                     }
                     uint32_t anyB = 0, anyD = 0;
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        anyB |= br[k] & br[(k + 1) & 7] & br[(k + 2) & 7] & br[(k + 3) & 7];
-                        anyD |= dk[k] & dk[(k + 1) & 7] & dk[(k + 2) & 7] & dk[(k + 3) & 7];
+                        anyB = lop3_or_and(anyB, lop3_and3(br[k], br[(k + 1) & 7], br[(k + 2) & 7]), br[(k + 3) & 7]);
+                        anyD = lop3_or_and(anyD, lop3_and3(dk[k], dk[(k + 1) & 7], dk[(k + 2) & 7]), dk[(k + 3) & 7]);
                     }
                     const uint32_t fl = (anyB | anyD) & vm;
                     if (fl) {
@@ -240,20 +239,14 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
             //         never wins the max) and join the corner list of this pass ----
             for (int i = tid; i < n1; i += FS_THREADS) {
                 const int pos = S.list1[i];
-                const int v = S.tile[pos];
-                int d[16];
-                uint32_t dark = 0, bright = 0;
+                const uint32_t v = S.tile[pos];
+                const uint32_t cv = (v + 256u) + ((256u - v) << 16);  // (256 + v, 256 - v)
+                uint32_t e[16];
 #pragma unroll
-                for (int k = 0; k < 16; ++k) {
-                    d[k] = v - (int)S.tile[pos + off[k]];
-                    dark |= (d[k] > t ? 1u : 0u) << k;
-                    bright |= (d[k] < -t ? 1u : 0u) << k;
-                }
-                if (has_run9(dark) || has_run9(bright)) {
-                    int s = best_arc_min(d);
-#pragma unroll
-                    for (int k = 0; k < 16; ++k) d[k] = -d[k];
-                    s = max(s, best_arc_min(d)) - 1;
+                for (int k = 0; k < 16; ++k) e[k] = (uint32_t)S.tile[pos + off[k]] * 0xFFFFu + cv;  // (256 + d, 256 - d), d = v - ring
+                const uint32_t best = best_arc_min_x2(e);
+                const int s = (int)max(best & 0xFFFFu, best >> 16) - 257;
+                if (s >= t) {  // some arc of 9 has all |differences| > t with one sign: a corner, and s is its score
                     S.score[pos] = (uint8_t)s;
                     const int o = atomicAdd(&S.cnt[2], 1);
                     if (o < FS_LIST2) S.list2[o] = (uint16_t)pos;

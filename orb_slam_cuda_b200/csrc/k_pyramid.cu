@@ -27,10 +27,10 @@ __device__ __forceinline__ int reflect101(int p, int n) {
 // Level 0: a CTA of 8 warps writes a 128-byte x 64-row tile of the padded plane; a thread owns 4 consecutive bytes
 // (one 32-bit store per row), a warp reads 128 consecutive source bytes per row.
 // grid: (ceil(pitch / 128), ceil(rows / 64), batch); block 256
-constexpr int RZ_ROWS = 64;
+constexpr int RZ_ROWS = 64;  // minimum rows per CTA; launchers raise it (rowsPerCta) while the grid still fills the GPU
 __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plane, int w, int h, int pitch, int rows,
                                                       long long planeStride, const uint8_t* __restrict__ frames,
-                                                      long long stride, long long frameStride) {
+                                                      long long stride, long long frameStride, int rowsPerCta) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int bx = blockIdx.x * 128 + lane * 4;
     if (bx >= pitch) return;
@@ -46,8 +46,8 @@ __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plan
     const bool run = valid[0] && valid[3] && sx[3] == sx[0] + 3;  // 4 consecutive interior source bytes
     const uint8_t* __restrict__ fbase = frames + (long long)f * frameStride;
     uint8_t* __restrict__ dbase = plane + (long long)f * planeStride + bx;
-    const int rowEnd = min(blockIdx.y * RZ_ROWS + RZ_ROWS, rows);
-    for (int py = blockIdx.y * RZ_ROWS + warp; py < rowEnd; py += 8) {
+    const int rowEnd = min(blockIdx.y * rowsPerCta + rowsPerCta, rows);
+    for (int py = blockIdx.y * rowsPerCta + warp; py < rowEnd; py += 8) {
         const uint8_t* __restrict__ src = fbase + (long long)reflect101(py - EDGE, h) * stride;
         uint32_t v;
         if (run && ((reinterpret_cast<uintptr_t>(src + sx[0]) & 3) == 0)) {
@@ -68,7 +68,7 @@ __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plan
 __global__ void __launch_bounds__(256) k_pyramid_resize(uint8_t* __restrict__ dplane, int dw, int dh, int dpitch, int drows,
                                                         long long dStride, const uint8_t* __restrict__ splane, int spitch,
                                                         long long sStride, const ResizeTab* __restrict__ xtab,
-                                                        const ResizeTab* __restrict__ ytab, int areaFast) {
+                                                        const ResizeTab* __restrict__ ytab, int areaFast, int rowsPerCta) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int bx = blockIdx.x * 128 + lane * 4;  // byte column of this thread's 4 pixels
     if (bx >= dpitch) return;
@@ -84,8 +84,8 @@ __global__ void __launch_bounds__(256) k_pyramid_resize(uint8_t* __restrict__ dp
     }
     const uint8_t* __restrict__ sInt = splane + (long long)f * sStride + (long long)EDGE * spitch + XOFF;
     uint8_t* __restrict__ dbase = dplane + (long long)f * dStride + bx;
-    const int rowEnd = min(blockIdx.y * RZ_ROWS + RZ_ROWS, drows);
-    for (int py = blockIdx.y * RZ_ROWS + warp; py < rowEnd; py += 8) {
+    const int rowEnd = min(blockIdx.y * rowsPerCta + rowsPerCta, drows);
+    for (int py = blockIdx.y * rowsPerCta + warp; py < rowEnd; py += 8) {
         const ResizeTab yt = ytab[reflect101(py - EDGE, dh)];
         const uint8_t* __restrict__ r0p = sInt + (long long)yt.s0 * spitch;
         const uint8_t* __restrict__ r1p = sInt + (long long)yt.s1 * spitch;
@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(256) k_pyramid_resize(uint8_t* __restrict__ dp
 __global__ void __launch_bounds__(256) k_pyramid_resize4(uint8_t* __restrict__ dplane, int dw, int dh, int dpitch, int drows,
                                                          long long dStride, const uint8_t* __restrict__ splane, int spitch,
                                                          long long sStride, const ResizeTab* __restrict__ xtab,
-                                                         const ResizeTab* __restrict__ ytab) {
+                                                         const ResizeTab* __restrict__ ytab, int rowsPerCta) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int bx = blockIdx.x * 128 + lane * 4;  // byte column of this thread's 4 pixels
     if (bx >= dpitch) return;
@@ -152,8 +152,8 @@ __global__ void __launch_bounds__(256) k_pyramid_resize4(uint8_t* __restrict__ d
         reinterpret_cast<const uint32_t*>(splane + (long long)f * sStride + (long long)EDGE * spitch + XOFF) + q0;
     const int spq = spitch >> 2;
     uint8_t* __restrict__ dbase = dplane + (long long)f * dStride + bx;
-    const int rowEnd = min(blockIdx.y * RZ_ROWS + RZ_ROWS, drows);
-    for (int py = blockIdx.y * RZ_ROWS + warp; py < rowEnd; py += 8) {
+    const int rowEnd = min(blockIdx.y * rowsPerCta + rowsPerCta, drows);
+    for (int py = blockIdx.y * rowsPerCta + warp; py < rowEnd; py += 8) {
         const ResizeTab yt = ytab[reflect101(py - EDGE, dh)];
         const uint32_t* __restrict__ r0 = sInt + (int)yt.s0 * spq;
         const uint32_t* __restrict__ r1 = sInt + (int)yt.s1 * spq;
@@ -174,12 +174,21 @@ __global__ void __launch_bounds__(256) k_pyramid_resize4(uint8_t* __restrict__ d
     }
 }
 
+// Rows one CTA walks: the per-thread column set-up (x-table entries, PRMT selectors) is paid once per CTA, so a CTA
+// takes as many rows as possible while the grid keeps >= 2 full waves of 148 SMs x 8 CTAs.
+static int rows_per_cta(int rows, int gx, int batch) {
+    int rpc = (rows + RZ_ROWS - 1) / RZ_ROWS * RZ_ROWS;
+    while (rpc > RZ_ROWS && (long long)gx * ((rows + rpc - 1) / rpc) * batch < 2 * 148 * 8) rpc = (rpc / 2 + 7) / 8 * 8;
+    return rpc < RZ_ROWS ? RZ_ROWS : rpc;
+}
+
 int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
                         cudaStream_t s) {
     const LevelGeom& L = g.lv[0];
-    dim3 grid((L.pitch + 127) / 128, (L.rows + RZ_ROWS - 1) / RZ_ROWS, batch);
+    const int gx = (L.pitch + 127) / 128, rpc = rows_per_cta(L.rows, gx, batch);
+    dim3 grid(gx, (L.rows + rpc - 1) / rpc, batch);
     k_pyramid_base<<<grid, 256, 0, s>>>(L.plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride,
-                                          (long long)frameStride);
+                                          (long long)frameStride, rpc);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
@@ -189,13 +198,14 @@ int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, c
                          int batch, cudaStream_t s) {
     const LevelGeom& D = g.lv[level];
     const LevelGeom& S = g.lv[level - 1];
-    dim3 grid((D.pitch + 127) / 128, (D.rows + RZ_ROWS - 1) / RZ_ROWS, batch);
+    const int gx = (D.pitch + 127) / 128, rpc = rows_per_cta(D.rows, gx, batch);
+    dim3 grid(gx, (D.rows + rpc - 1) / rpc, batch);
     if (areaFast & 2)  // bit 1: every thread's source window fits 8 bytes -> word-based kernel
         k_pyramid_resize4<<<grid, 256, 0, s>>>(D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, S.plane, S.pitch,
-                                                 S.planeStride, xtab, ytab);
+                                                 S.planeStride, xtab, ytab, rpc);
     else
         k_pyramid_resize<<<grid, 256, 0, s>>>(D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, S.plane, S.pitch,
-                                                S.planeStride, xtab, ytab, areaFast & 1);
+                                                S.planeStride, xtab, ytab, areaFast & 1, rpc);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

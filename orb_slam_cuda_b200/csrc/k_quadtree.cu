@@ -315,21 +315,23 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
     // ---- keep the best key of every node (:1098-1117): first key of maximal response, list order ----
     const QNode* L = S.list[cur];
     const int nOut = min(n, outCap);
-    for (int i = wid; i < nOut; i += nw) {
-        const QNode nd = L[i];
-        const uint32_t* k = bufs + ((nd.begin >> 31) ? candCap : 0) + (nd.begin & 0x7FFFFFFFu);
-        unsigned long long best = 0;
-        for (uint32_t j = lane; j < nd.count; j += 32) {
-            const unsigned long long v = ((unsigned long long)key_resp(k[j]) << 32) | (0xFFFFFFFFu - j);
-            best = v > best ? v : best;
+    // Final nodes hold few keys (about candidates / N), so four lanes share a node: 8 nodes per warp step
+    for (int i0 = wid * 8; i0 < nOut; i0 += nw * 8) {
+        const int i = i0 + (lane >> 2), sub = lane & 3;
+        uint32_t best = 0;
+        const uint32_t* k = bufs;
+        if (i < nOut) {
+            const QNode nd = L[i];
+            k = bufs + ((nd.begin >> 31) ? candCap : 0) + (nd.begin & 0x7FFFFFFFu);
+            for (uint32_t j = sub; j < nd.count; j += 4) {  // (response, first index) packed: counts stay below 2^24
+                const uint32_t v = ((uint32_t)key_resp(k[j]) << 24) | (0xFFFFFFu - j);
+                best = max(best, v);
+            }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
-            best = other > best ? other : best;
-        }
-        if (lane == 0) {
-            const uint32_t key = k[0xFFFFFFFFu - (uint32_t)(best & 0xFFFFFFFFu)];
+        best = max(best, __shfl_xor_sync(0xffffffffu, best, 1));
+        best = max(best, __shfl_xor_sync(0xffffffffu, best, 2));
+        if (i < nOut && sub == 0) {
+            const uint32_t key = k[0xFFFFFFu - (best & 0xFFFFFFu)];
             outKeys[i] = pack_key(key_x(key) + addX, key_y(key) + addY, key_resp(key));
         }
     }
