@@ -86,9 +86,9 @@ int orbx_extract(orbx_extractor* ex, const uint8_t* img, int w, int h, size_t st
 
 /* Batched form: `batch` frames of identical size, frame f at frames + f*frame_stride, rows `stride` bytes apart.
  * Outputs: kps[f*cap .. ], desc[(f*cap + i)*32 .. ], counts[f].  Host memory; copies are inside the call.
- * Batches of >= 128 frames are cut into chunks of about 64 frames pipelined over three streams (H2D | kernels | D2H);
- * pinned caller buffers are used directly, pageable ones go through pinned staging.  The device scratch then holds one
- * chunk: orbx_pyramid_level_host() afterwards serves the frames of the LAST chunk only (by their index in the batch). */
+ * Batches of >= 128 frames are cut into chunks of about 64 frames pipelined over H2D | kernels (two lanes) | D2H streams;
+ * pinned caller buffers are used directly, pageable ones go through pinned staging.  The device scratch then holds two
+ * chunks: orbx_pyramid_level_host() afterwards serves the frames of the LAST chunk only (by their index in the batch). */
 int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride,
                        size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int cap, int* counts);
 

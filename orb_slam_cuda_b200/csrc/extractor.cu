@@ -72,12 +72,13 @@ struct orbx_extractor {
     long long hostLevelSerial[ORBX_MAX_LEVELS];
     long long serial = 0;    // bumped by every extract call
     // host-buffer batches are cut into chunks pipelined over three streams: H2D | kernels (stream) | D2H
-    cudaStream_t h2dStream = nullptr, d2hStream = nullptr;
+    cudaStream_t h2dStream = nullptr, d2hStream = nullptr, stream2 = nullptr;  // stream2: kernels of odd chunks
     std::vector<cudaEvent_t> pipeEv;  // 2 per chunk: frames landed, kernels done
     bool timing = false;
     bool timed = false;      // the last call recorded events
     cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
     int lastBatch = 0;
+    int lastScratchBase = 0; // scratch frame holding frame `lastFrameBase` of the caller's batch
     int lastFrameBase = 0;   // index (within the caller's batch) of frame 0 of the scratch: > 0 after a chunked host batch
 };
 
@@ -354,13 +355,20 @@ static int stage_sync(const char* stage, cudaStream_t s) {  // ORBX_DEBUG_SYNC=1
 
 static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
                         orbx_keypoint* dKps, uint8_t* dDesc, int cap, int* dCounts, int* dStatus, cudaStream_t s,
-                        bool resetStatus = true) {
-    const FrameGeom& g = ex->g;
+                        bool resetStatus = true, int f0 = 0) {
+    FrameGeom g = ex->g;
+    g.f0 = f0;  // scratch frames [f0, f0 + batch)
     const int nl = g.nlevels;
+    int* cellCnt = ex->cellCnt.as<int>() + (size_t)f0 * g.nCellsTotal;
+    uint32_t* cellKeys = ex->cellKeys.as<uint32_t>() + (size_t)f0 * g.nCellsTotal * CELL_CAP;
+    uint32_t* qtScratch = ex->qtScratch.as<uint32_t>() + (size_t)f0 * g.qtFrameStride;
+    int* lvlCnt = ex->lvlCnt.as<int>() + (size_t)f0 * nl;
+    uint32_t* lvlKeys = ex->lvlKeys.as<uint32_t>() + (size_t)f0 * g.slotsTotal;
+    float* lvlAngles = ex->lvlAngles.as<float>() + (size_t)f0 * g.slotsTotal;
     int rc;
     if (resetStatus) ORBX_CUDA(cudaMemsetAsync(dStatus, 0, sizeof(int), s));
     if ((rc = stage_sync("input copy", s))) return rc;
-    const bool tm = ex->timing;
+    const bool tm = ex->timing && f0 == 0;
     ex->timed = tm;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[0], s));
     if ((rc = launch_pyramid_base(g, dFrames, batch, stride, frameStride, s))) return rc;                 // ComputePyramid
@@ -370,24 +378,21 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
             return rc;
     if ((rc = stage_sync("Pyramid/Resize", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
-    if ((rc = launch_fast(g, ex->fastMaps, ex->strips.as<FastStrip>(), batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), dStatus, s))) return rc;
+    if ((rc = launch_fast(g, ex->fastMaps, ex->strips.as<FastStrip>(), batch, cellCnt, cellKeys, dStatus, s))) return rc;
     if ((rc = stage_sync("FAST+Grid", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
-    if ((rc = launch_quadtree(g, batch, ex->cellCnt.as<int>(), ex->cellKeys.as<uint32_t>(), ex->qtScratch.as<uint32_t>(),
-                              ex->lvlCnt.as<int>(), ex->lvlKeys.as<uint32_t>(), dStatus, s)))
-        return rc;
+    if ((rc = launch_quadtree(g, batch, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus, s))) return rc;
     if ((rc = stage_sync("Make quadtree", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
     if ((rc = launch_blur(g, ex->blurMaps, batch, s))) return rc;                                            // GaussianBlur
     if ((rc = stage_sync("Gaussian Blur", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
-    if ((rc = launch_describe(g, batch, ex->lvlCnt.as<int>(), ex->lvlKeys.as<uint32_t>(), dKps, dDesc, cap, dCounts,
-                              ex->lvlAngles.as<float>(), dStatus, s)))
-        return rc;
+    if ((rc = launch_describe(g, batch, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts, lvlAngles, dStatus, s))) return rc;
     if ((rc = stage_sync("Compute angle + ORB descriptor", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
     ex->serial++;
     ex->lastBatch = batch;
+    ex->lastScratchBase = f0;
     return ORBX_OK;
 }
 
@@ -477,7 +482,7 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
         cudaStreamSynchronize(ex->stream);
         cudaStreamDestroy(ex->stream);
     }
-    for (cudaStream_t st : {ex->h2dStream, ex->d2hStream})
+    for (cudaStream_t st : {ex->h2dStream, ex->d2hStream, ex->stream2})
         if (st) {
             cudaStreamSynchronize(st);
             cudaStreamDestroy(st);
@@ -583,22 +588,28 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
     }
     if (stride < (size_t)w || !kps || !desc || cap < 1) { set_error("orbx_extract_batch: bad argument"); return ORBX_E_INVALID; }
     // The batch is cut into chunks that flow through three streams — H2D | kernels | D2H — so the copies of chunk c+1 and
-    // c-1 overlap the kernels of chunk c.  The scratch (pyramids, cell lists ...) is sized for ONE chunk and reused, since
-    // the kernels of successive chunks are serial on the handle's stream anyway; small batches are a single chunk.
+    // c-1 overlap the kernels of chunk c.  The scratch (pyramids, cell lists ...) holds TWO chunks: even and odd chunks
+    // run their kernels on two streams ("lanes") over disjoint halves of it; small batches are a single chunk.
     static const int chunkPref = []() { const char* e = getenv("ORBX_PIPE_CHUNK"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 64; }();
     const int nChunks = std::max(1, batch / chunkPref), C = (batch + nChunks - 1) / nChunks;
-    if ((rc = configure(ex, w, h, C))) return rc;
+    const int lanes = nChunks > 1 ? 2 : 1;  // kernels of even / odd chunks run on two streams over disjoint scratch halves, so
+                                            // the tail of one chunk's kernels overlaps the next chunk's
+    if ((rc = configure(ex, w, h, lanes * C))) return rc;
     cudaStream_t s = ex->stream;
     const size_t rowBytes = (size_t)w, frameBytes = rowBytes * h;
     if ((rc = ex->dFrames.ensure(frameBytes * batch + 16))) return rc;
-    if ((rc = ex->dKps.ensure((size_t)batch * cap * sizeof(orbx_keypoint)))) return rc;
-    if ((rc = ex->dDesc.ensure((size_t)batch * cap * 32))) return rc;
-    if ((rc = ex->dCounts.ensure((size_t)batch * 4))) return rc;
+    // device outputs live in ONE allocation [keypoints | descriptors | counts | status] mirrored by one pinned block, so a
+    // small call returns everything with a single D2H copy
+    const size_t kpBytes = (size_t)round_up((long long)batch * cap * sizeof(orbx_keypoint), 256);
+    const size_t dBytes = (size_t)round_up((long long)batch * cap * 32, 256), cBytes = (size_t)round_up((long long)batch * 4, 256);
+    const size_t outBytes = kpBytes + dBytes + cBytes + 256;
+    if ((rc = ex->dKps.ensure(outBytes))) return rc;
     cudaStream_t sIn = s, sOut = s;
     if (nChunks > 1) {
         if (!ex->h2dStream) ORBX_CUDA(cudaStreamCreateWithFlags(&ex->h2dStream, cudaStreamNonBlocking));
         if (!ex->d2hStream) ORBX_CUDA(cudaStreamCreateWithFlags(&ex->d2hStream, cudaStreamNonBlocking));
-        while ((int)ex->pipeEv.size() < 2 * nChunks) {
+        if (!ex->stream2) ORBX_CUDA(cudaStreamCreateWithFlags(&ex->stream2, cudaStreamNonBlocking));
+        while ((int)ex->pipeEv.size() < 2 * nChunks + 1) {
             cudaEvent_t e;
             ORBX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             ex->pipeEv.push_back(e);
@@ -615,21 +626,31 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
     orbx_keypoint* hk = kps;
     uint8_t* hd = desc;
     int* hc = counts;
+    int* hst = ex->hStatus.as<int>();
     if (!direct) {
-        if ((rc = ex->hKps.ensure((size_t)batch * cap * sizeof(orbx_keypoint)))) return rc;
-        if ((rc = ex->hDesc.ensure((size_t)batch * cap * 32))) return rc;
-        if ((rc = ex->hCounts.ensure((size_t)batch * 4))) return rc;
-        hk = ex->hKps.as<orbx_keypoint>();
-        hd = ex->hDesc.as<uint8_t>();
-        hc = ex->hCounts.as<int>();
+        if ((rc = ex->hKps.ensure(outBytes))) return rc;
+        uint8_t* hb = ex->hKps.as<uint8_t>();
+        hk = reinterpret_cast<orbx_keypoint*>(hb);
+        hd = hb + kpBytes;
+        hc = reinterpret_cast<int*>(hb + kpBytes + dBytes);
+        hst = reinterpret_cast<int*>(hb + kpBytes + dBytes + cBytes);
     }
-    ORBX_CUDA(cudaMemsetAsync(ex->status.p, 0, sizeof(int), s));
+    uint8_t* dOut = ex->dKps.as<uint8_t>();
+    orbx_keypoint* dK = reinterpret_cast<orbx_keypoint*>(dOut);
+    uint8_t* dD = dOut + kpBytes;
+    int* dC = reinterpret_cast<int*>(dOut + kpBytes + dBytes);
+    int* dSt = reinterpret_cast<int*>(dOut + kpBytes + dBytes + cBytes);
+    const bool oneCopy = !direct && nChunks == 1;
+    ORBX_CUDA(cudaMemsetAsync(dSt, 0, sizeof(int), s));
+    if (nChunks > 1) {  // the second lane starts after the status word is cleared
+        ORBX_CUDA(cudaEventRecord(ex->pipeEv[2 * nChunks], s));
+        ORBX_CUDA(cudaStreamWaitEvent(ex->stream2, ex->pipeEv[2 * nChunks], 0));
+    }
     uint8_t* dF = ex->dFrames.as<uint8_t>();
-    orbx_keypoint* dK = ex->dKps.as<orbx_keypoint>();
-    uint8_t* dD = ex->dDesc.as<uint8_t>();
-    int* dC = ex->dCounts.as<int>();
     for (int c = 0, f0 = 0; c < nChunks; ++c, f0 += C) {
         const int nb = std::min(C, batch - f0);
+        const int lane = c & (lanes - 1);
+        cudaStream_t sK = lane ? ex->stream2 : s;
         const uint8_t* src = frames + (size_t)f0 * frameStride;
         if (!directIn) {
             uint8_t* st = ex->hFrames.as<uint8_t>() + (size_t)f0 * frameBytes;
@@ -641,26 +662,31 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
         ORBX_CUDA(cudaMemcpyAsync(dF + (size_t)f0 * frameBytes, src, frameBytes * nb, cudaMemcpyHostToDevice, sIn));
         if (nChunks > 1) {
             ORBX_CUDA(cudaEventRecord(ex->pipeEv[2 * c], sIn));
-            ORBX_CUDA(cudaStreamWaitEvent(s, ex->pipeEv[2 * c], 0));
+            ORBX_CUDA(cudaStreamWaitEvent(sK, ex->pipeEv[2 * c], 0));
         }
         if ((rc = run_pipeline(ex, dF + (size_t)f0 * frameBytes, nb, rowBytes, frameBytes, dK + (size_t)f0 * cap,
-                               dD + (size_t)f0 * cap * 32, cap, dC + f0, ex->status.as<int>(), s, false)))
+                               dD + (size_t)f0 * cap * 32, cap, dC + f0, dSt, sK, false, lane * C)))
             return rc;
         if (nChunks > 1) {
-            ORBX_CUDA(cudaEventRecord(ex->pipeEv[2 * c + 1], s));
+            ORBX_CUDA(cudaEventRecord(ex->pipeEv[2 * c + 1], sK));
             ORBX_CUDA(cudaStreamWaitEvent(sOut, ex->pipeEv[2 * c + 1], 0));
+        }
+        ex->lastFrameBase = f0;
+        if (oneCopy) {
+            ORBX_CUDA(cudaMemcpyAsync(hk, dOut, outBytes, cudaMemcpyDeviceToHost, sOut));
+            break;
         }
         ORBX_CUDA(cudaMemcpyAsync(hc + f0, dC + f0, (size_t)nb * 4, cudaMemcpyDeviceToHost, sOut));
         ORBX_CUDA(cudaMemcpyAsync(hk + (size_t)f0 * cap, dK + (size_t)f0 * cap, (size_t)nb * cap * sizeof(orbx_keypoint),
                                   cudaMemcpyDeviceToHost, sOut));
         ORBX_CUDA(cudaMemcpyAsync(hd + (size_t)f0 * cap * 32, dD + (size_t)f0 * cap * 32, (size_t)nb * cap * 32,
                                   cudaMemcpyDeviceToHost, sOut));
-        ex->lastFrameBase = f0;
     }
-    ORBX_CUDA(cudaMemcpyAsync(ex->hStatus.p, ex->status.p, 4, cudaMemcpyDeviceToHost, sOut));
+    if (!oneCopy) ORBX_CUDA(cudaMemcpyAsync(hst, dSt, 4, cudaMemcpyDeviceToHost, sOut));
     ORBX_CUDA(cudaStreamSynchronize(sOut));
     if (nChunks > 1) {
         ORBX_CUDA(cudaStreamSynchronize(sIn));
+        ORBX_CUDA(cudaStreamSynchronize(ex->stream2));
         ORBX_CUDA(cudaStreamSynchronize(s));
     }
     if (!direct) {
@@ -670,7 +696,7 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
             memcpy(desc + (size_t)f * cap * 32, hd + (size_t)f * cap * 32, (size_t)hc[f] * 32);
         }
     }
-    const int st = *ex->hStatus.as<int>();
+    const int st = *hst;
     if (st != 0) {
         set_error("orbx_extract: a device buffer overflowed (more than %d keypoints in a FAST cell, or more than cap=%d keypoints in a frame)",
                   CELL_CAP, cap);
@@ -697,6 +723,7 @@ int orbx_pyramid_level_host(orbx_extractor* ex, int frame, int level, const uint
         set_error("orbx_pyramid_level_host: no such frame/level (frame %d level %d, last batch %d)", frame, level, ex->lastBatch);
         return ORBX_E_INVALID;
     }
+    frame += ex->lastScratchBase;  // index into the scratch
     const LevelGeom& L = ex->g.lv[level];
     if (ex->hostLevelSerial[level] != ex->serial || ex->hostLevelFrame[level] != frame) {  // lazy D2H
         ex->hostLevel[level].resize((size_t)L.planeStride);
@@ -720,6 +747,7 @@ int orbx_debug_blurred_level(orbx_extractor* ex, int frame, int level, uint8_t* 
         set_error("orbx_debug_blurred_level: bad argument");
         return ORBX_E_INVALID;
     }
+    frame += ex->lastScratchBase;  // index into the scratch
     const LevelGeom& L = ex->g.lv[level];
     ORBX_CUDA(cudaMemcpy2DAsync(out, (size_t)L.w, L.blur + (size_t)frame * L.blurStride, (size_t)L.bpitch, (size_t)L.w, (size_t)L.h,
                                 cudaMemcpyDeviceToHost, ex->stream));
@@ -734,6 +762,7 @@ int orbx_debug_candidates(orbx_extractor* ex, int frame, int level, orbx_keypoin
         set_error("orbx_debug_candidates: bad argument");
         return ORBX_E_INVALID;
     }
+    frame += ex->lastScratchBase;  // index into the scratch
     const FrameGeom& g = ex->g;
     const LevelGeom& L = g.lv[level];
     const int nCells = L.nCols * L.nRows;
@@ -764,6 +793,7 @@ int orbx_debug_level_keypoints(orbx_extractor* ex, int frame, int level, orbx_ke
         set_error("orbx_debug_level_keypoints: bad argument");
         return ORBX_E_INVALID;
     }
+    frame += ex->lastScratchBase;  // index into the scratch
     const FrameGeom& g = ex->g;
     const LevelGeom& L = g.lv[level];
     int cnt = 0;

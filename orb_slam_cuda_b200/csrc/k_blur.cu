@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
                                                         const __grid_constant__ TmaMaps maps) {
     __shared__ __align__(128) uint8_t tile[BLUR_BH * BLUR_BW];
     __shared__ __align__(8) uint64_t bar;
-    const int tid = threadIdx.x, f = blockIdx.y;
+    const int tid = threadIdx.x, f = blockIdx.y + g.f0;  // scratch frame
     int t = blockIdx.x, level = 0;
     while (level + 1 < g.nlevels && t >= g.lv[level + 1].blurTileBase) ++level;
     const LevelGeom& L = g.lv[level];

@@ -98,7 +98,7 @@ constexpr int DESC_WARPS = 8;
 constexpr int DESC_PER_WARP = 4;   // keypoint slots a warp walks (amortises the table set-up of the CTA)
 constexpr int BP_HALF = 18;        // the rotated pattern reaches |coordinate| <= cvRound(18.38) = 18
 constexpr int BP_ROWS = 2 * BP_HALF + 1;  // 37 rows; a row is 48 bytes read from an 8-byte aligned address (6 x 64-bit loads)
-constexpr int BP_WORDS = 13, BP_STRIDE = BP_WORDS * 4;  // shared row stride: 13 words (odd, spreads rows over the banks)
+constexpr int BP_WORDS = 14, BP_STRIDE = BP_WORDS * 4;  // shared row stride: 56 bytes (8-byte aligned rows for cp.async)
 
 // Tables the kernel copies into shared memory, filled once per process by init_describe_tables():
 //   d_patF  : the 512 pattern points as floats, laid out [pair k of the lane][lane] as (x0, y0, x1, y1)
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
                                                                      int* dStatus) {
     __shared__ float4 patF[8 * 32];
     __shared__ uint32_t coefU[32 * 8], coefV[32 * 8];
-    __shared__ uint32_t bpatch[DESC_WARPS][BP_ROWS * BP_WORDS + 1];
+    __shared__ __align__(16) uint32_t bpatch[DESC_WARPS][BP_ROWS * BP_WORDS + 2];
     __shared__ int sBefore[ORBX_MAX_LEVELS + 1];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         patF[i] = d_patF[i];
@@ -162,10 +162,33 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
         const uint32_t key = lvlKeys[(long long)f * g.slotsTotal + slot];
         const int x = key_x(key), y = key_y(key);
 
+        // ---- blurred 37 x 37 patch: rows of 48 bytes from an 8-byte aligned address, copied global -> shared with
+        //      cp.async (no registers).  The copies are issued here, before IC_Angle, so their latency overlaps the moment
+        //      sums and the arctangent (the patch address needs x, y only); lanes = 5 rows x 6 double words per step,
+        //      8 steps cover rows 0..39 (rows >= 37 are skipped) ----
+        const uint8_t* brow = L.blur + (long long)(f + g.f0) * L.blurStride + (long long)(y - BP_HALF) * L.bpitch + (x - BP_HALF);
+        const int mis = (int)(reinterpret_cast<uintptr_t>(brow) & 7);
+        __syncwarp();  // the previous keypoint's taps are done with the patch
+        if (lane < 30) {
+            const int rsub = lane / 6, q = lane - rsub * 6;
+            const uint2* bw = reinterpret_cast<const uint2*>(reinterpret_cast<uintptr_t>(brow) & ~(uintptr_t)7);
+            const int bpo = L.bpitch >> 3;
+            const uint32_t dst0 = (uint32_t)__cvta_generic_to_shared(bp) + (uint32_t)(rsub * BP_STRIDE + q * 8);
+#pragma unroll
+            for (int r5 = 0; r5 < 8; ++r5) {
+                const int r = r5 * 5 + rsub;
+                if (r < BP_ROWS)
+                    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst0 + (uint32_t)(r5 * 5 * BP_STRIDE)),
+                                 "l"(bw + r * bpo + q)
+                                 : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+
         // ---- IC_Angle on the unblurred level: lanes = (4 rows) x (8 words of 4 pixels), dp4a against the u / v tables ----
         int m10 = 0, m01 = 0;
         {
-            const uint8_t* p0 = L.plane + (long long)f * L.planeStride + (long long)(y - HALF_PATCH + EDGE) * L.pitch +
+            const uint8_t* p0 = L.plane + (long long)(f + g.f0) * L.planeStride + (long long)(y - HALF_PATCH + EDGE) * L.pitch +
                                 (x - HALF_PATCH + XOFF) + 4 * (lane & 7);
             const uint32_t sh = (uint32_t)(reinterpret_cast<uintptr_t>(p0) & 3) * 8;
             const uint32_t* w0 = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(p0) & ~(uintptr_t)3);
@@ -187,26 +210,13 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
         const float angle = fast_atan2_deg((float)m01, (float)m10);
         if (lvlAngles && lane == 0) lvlAngles[(long long)f * g.slotsTotal + slot] = angle;
         const int o = before + j;
-        if (o >= cap) continue;
-
-        // ---- stage the 37 x 37 blurred patch (rows of 11 aligned words covering columns x-18 .. x+18) ----
-        const uint8_t* brow = L.blur + (long long)f * L.blurStride + (long long)(y - BP_HALF) * L.bpitch + (x - BP_HALF);
-        const int mis = (int)(reinterpret_cast<uintptr_t>(brow) & 7);
-        const uint2* bw = reinterpret_cast<const uint2*>(reinterpret_cast<uintptr_t>(brow) & ~(uintptr_t)7);
-        const int bpo = L.bpitch >> 3;
-        __syncwarp();
-        if (lane < 30) {  // lanes = 5 rows x 6 double words per step, 8 steps cover rows 0..39 (rows >= 37 are skipped)
-            const int rsub = lane / 6, q = lane - rsub * 6;
-#pragma unroll
-            for (int r5 = 0; r5 < 8; ++r5) {
-                const int r = r5 * 5 + rsub;
-                if (r < BP_ROWS) {
-                    const uint2 v = __ldg(bw + r * bpo + q);
-                    bp[r * BP_WORDS + 2 * q] = v.x;
-                    bp[r * BP_WORDS + 2 * q + 1] = v.y;
-                }
-            }
+        if (o >= cap) {  // output overflow (reported through dStatus): drain the copies before the patch is reused
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            continue;
         }
+
+        // ---- the staged patch has landed ----
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncwarp();
 
         // ---- steered BRIEF: lane i -> byte i, 16 rotated taps read from the staged patch ----

@@ -36,11 +36,17 @@ namespace orbx {
 #endif
 constexpr int FS_THREADS = ORBX_FS_THREADS;
 #ifndef ORBX_FS_LIST1
-#define ORBX_FS_LIST1 4096
+#define ORBX_FS_LIST1 2048
+#endif
+#ifndef ORBX_FS_LIST2
+#define ORBX_FS_LIST2 1024
+#endif
+#ifndef ORBX_FS_MAXCELLS
+#define ORBX_FS_MAXCELLS 4  // measured on B200 (tools/variants.py): 2 / 3 / 4 / 5 / 7 cells -> 2.24 / 2.05 / 1.96 / 2.02 / 2.09 ms per 512 KITTI frames
 #endif
 constexpr int FS_LIST1 = ORBX_FS_LIST1;  // quick-test survivors per row chunk
-constexpr int FS_LIST2 = 2048;  // corners per strip and pass (beyond that NMS scans the score tile)
-constexpr int FS_KP = 1024;     // keypoints per strip
+constexpr int FS_LIST2 = ORBX_FS_LIST2;  // corners per strip and pass (beyond that NMS scans the score tile)
+constexpr int FS_KP = ORBX_FS_MAXCELLS * CELL_CAP;     // keypoints per strip
 
 __constant__ int c_ringDx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
 __constant__ int c_ringDy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
@@ -65,9 +71,14 @@ __device__ __forceinline__ uint32_t lop3_and3(uint32_t a, uint32_t b, uint32_t c
     asm("lop3.b32 %0, %1, %2, %3, 0x80;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
     return r;
 }
-__device__ __forceinline__ uint32_t lop3_or_and(uint32_t a, uint32_t b, uint32_t c) {  // a | (b & c)
+__device__ __forceinline__ uint32_t lop3_and_or(uint32_t a, uint32_t b, uint32_t c) {  // a & (b | c)
     uint32_t r;
-    asm("lop3.b32 %0, %1, %2, %3, 0xf8;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    asm("lop3.b32 %0, %1, %2, %3, 0xe0;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    return r;
+}
+__device__ __forceinline__ uint32_t lop3_or3(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xfe;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
     return r;
 }
 
@@ -132,7 +143,7 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
     __syncthreads();
     if (tid == 0) {
         mbar_expect_tx(S.bar, (uint32_t)TN);
-        tma_load_3d(S.tile, &maps.m[st.level], (XOFF + iniX) & ~15, EDGE + iniY, f, S.bar);  // box origin 16-byte aligned
+        tma_load_3d(S.tile, &maps.m[st.level], (XOFF + iniX) & ~15, EDGE + iniY, f + g.f0, S.bar);  // box origin 16-byte aligned
     }
     const int xo = (XOFF + iniX) & 15;  // window column 0 inside the box
     const int X0 = xo + 3;              // first detectable tile column
@@ -152,6 +163,7 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
     const uint32_t* tile32 = reinterpret_cast<const uint32_t*>(S.tile);
     const uint32_t* act32 = reinterpret_cast<const uint32_t*>(S.act);
     const int rowsPerChunk = max(1, FS_LIST1 / (nW * 4));
+    const int stepY = FS_THREADS / nW, stepW = FS_THREADS - stepY * nW;
     int off[16];
 #pragma unroll
     for (int k = 0; k < 16; ++k) off[k] = c_ringDy[k] * TW + c_ringDx[k];
@@ -179,9 +191,15 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
         for (int y0 = 0; y0 < dH; y0 += rowsPerChunk) {
             const int y1 = min(y0 + rowsPerChunk, dH);
             // ---- A: packed quick test on the 8 even ring points: a run of 9 holds 4 consecutive even points ----
-            for (int y = y0 + warp; y < y1; y += FS_THREADS / 32) {
-                const uint32_t* rowc = tile32 + (y + 3) * TWq + wq0;
-                for (int w = lane; w < nW; w += 32) {
+            // the (row, word) pairs of the chunk are walked as one flat index, so every lane has work whatever the strip
+            // width; the row / word of a thread advance incrementally (no division inside the loop)
+            const int total = (y1 - y0) * nW;
+            int yy = tid / nW, w = tid - yy * nW;
+            for (int idx = tid; idx < total; idx += FS_THREADS, w += stepW, yy += stepY) {
+                if (w >= nW) { w -= nW; ++yy; }
+                {
+                    const int y = y0 + yy;
+                    const uint32_t* rowc = tile32 + (y + 3) * TWq + wq0;
                     const uint32_t vm = act32[wq0 + w];
                     if (vm == 0) continue;
                     const uint32_t c = rowc[w];
@@ -215,13 +233,19 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
                         asm("lop3.b32 %0, %1, %2, %3, 0xb2;" : "=r"(br[k]) : "r"(ring[k]), "r"(hi), "r"(sb));
                         asm("lop3.b32 %0, %1, %2, %3, 0x4d;" : "=r"(dk[k]) : "r"(ring[k]), "r"(lo), "r"(sd));
                     }
-                    uint32_t anyB = 0, anyD = 0;
+                    // a pixel survives iff 4 consecutive even ring points agree: with pair flags p[k] = f[k] & f[k+1] that
+                    // is OR_k (p[k] & p[k+2]), and p[k+2] & (p[k] | p[k+4]) covers two of the eight products per LOP3
+                    uint32_t pb[8], pd[8];
 #pragma unroll
                     for (int k = 0; k < 8; ++k) {
-                        anyB = lop3_or_and(anyB, lop3_and3(br[k], br[(k + 1) & 7], br[(k + 2) & 7]), br[(k + 3) & 7]);
-                        anyD = lop3_or_and(anyD, lop3_and3(dk[k], dk[(k + 1) & 7], dk[(k + 2) & 7]), dk[(k + 3) & 7]);
+                        pb[k] = br[k] & br[(k + 1) & 7];
+                        pd[k] = dk[k] & dk[(k + 1) & 7];
                     }
-                    const uint32_t fl = (anyB | anyD) & vm;
+                    const uint32_t fl = (lop3_or3(lop3_and_or(pb[2], pb[0], pb[4]), lop3_and_or(pb[6], pb[4], pb[0]),
+                                                  lop3_and_or(pb[3], pb[1], pb[5])) |
+                                         lop3_or3(lop3_and_or(pb[7], pb[5], pb[1]), lop3_and_or(pd[2], pd[0], pd[4]),
+                                                  lop3_and_or(pd[6], pd[4], pd[0])) |
+                                         lop3_and_or(pd[3], pd[1], pd[5]) | lop3_and_or(pd[7], pd[5], pd[1])) & vm;
                     if (fl) {
                         int o = atomicAdd(&S.cnt[par], __popc(fl));
                         const int pos0 = (y + 3) * TW + ((wq0 + w) << 2);
@@ -327,16 +351,14 @@ size_t fast_smem_bytes(const FrameGeom& g) {
            16 * 4 + 16;
 }
 
-// Chooses how many cells a strip of a level holds: the TMA box (strip window + 15 bytes of origin slack) must stay
-// within 256 columns, and the 32-bit words of a strip row should fill whole warps.
+// Cells per strip of a level: as many as ORBX_FS_MAXCELLS allows while the TMA box (strip window + 15 bytes of origin
+// slack) stays within 256 columns.  Phase A walks (row, word) pairs as a flat index, so lane utilisation does not depend
+// on the strip width; the width trades shared memory per CTA (occupancy) against halo re-reads and per-CTA set-up.
 int fast_cells_per_strip(int wCell, int nCols) {
     int best = 1;
-    double bestUtil = 0;
-    for (int c = 1; c <= FAST_MAX_STRIP_CELLS && c <= nCols; ++c) {
+    for (int c = 1; c <= ORBX_FS_MAXCELLS && c <= FAST_MAX_STRIP_CELLS && c <= nCols; ++c) {
         if (c * wCell + 6 + 15 > 256) break;
-        const int words = (3 + c * wCell + 3) / 4 + 1;
-        const double util = (double)words / (32.0 * ((words + 31) / 32));
-        if (util >= bestUtil - 1e-9) { bestUtil = util; best = c; }
+        best = c;
     }
     return best;
 }

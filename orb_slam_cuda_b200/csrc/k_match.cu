@@ -33,11 +33,15 @@ constexpr int BF_TILE = 256;     // database descriptors staged per tile (8 KB)
 constexpr uint32_t BF_NOIDX = 0x3FFFFFu;
 
 // grid (ceil(nq / BF_THREADS), nsplit): every CTA matches 128 queries against one slice of the database and writes
-// a partial (best = dist << 22 | idx, second) per query.
-__global__ void __launch_bounds__(BF_THREADS) k_bruteforce_partial(const uint4* __restrict__ q, int nq,
-                                                                    const uint4* __restrict__ d, int nd, int sliceLen,
-                                                                    unsigned long long* __restrict__ partial) {
+// a partial (best = dist << 22 | idx, second) per query; the CTA that finishes a query block LAST (a counter per query
+// block, left at zero for the next call) merges the partials and applies the acceptance test — one launch per call.
+__global__ void __launch_bounds__(BF_THREADS) k_bruteforce(const uint4* __restrict__ q, int nq, const uint4* __restrict__ d, int nd,
+                                                            int sliceLen, unsigned long long* __restrict__ partial,
+                                                            unsigned int* __restrict__ counters, int th, float ratio,
+                                                            int* __restrict__ idx, int* __restrict__ d1, int* __restrict__ d2,
+                                                            int* __restrict__ match) {
     __shared__ uint4 tile[BF_TILE * 2];
+    __shared__ bool isLast;
     const int qi = blockIdx.x * BF_THREADS + threadIdx.x;
     const int begin = blockIdx.y * sliceLen, end = min(begin + sliceLen, nd);
     uint32_t a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -60,22 +64,28 @@ __global__ void __launch_bounds__(BF_THREADS) k_bruteforce_partial(const uint4* 
             best = min(best, cand);
         }
     }
-    if (qi < nq) partial[(size_t)blockIdx.y * nq + qi] = ((unsigned long long)best << 32) | (uint32_t)second;
-}
-
-__global__ void k_bruteforce_merge(const unsigned long long* __restrict__ partial, int nq, int nsplit, int th, float ratio,
-                                   int* __restrict__ idx, int* __restrict__ d1, int* __restrict__ d2, int* __restrict__ match) {
-    const int qi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (qi >= nq) return;
-    uint32_t best = (256u << 22) | BF_NOIDX;
-    int second = 256;
-    for (int s = 0; s < nsplit; ++s) {
-        const unsigned long long p = partial[(size_t)s * nq + qi];
-        const uint32_t b = (uint32_t)(p >> 32);
-        const int s2 = (int)(uint32_t)p;
-        second = min(max((int)(best >> 22), (int)(b >> 22)), min(second, s2));
-        best = min(best, b);
+    const int nsplit = gridDim.y;
+    if (nsplit > 1) {
+        if (qi < nq) partial[(size_t)blockIdx.y * nq + qi] = ((unsigned long long)best << 32) | (uint32_t)second;
+        __threadfence();
+        __syncthreads();
+        if (threadIdx.x == 0) isLast = atomicAdd(&counters[blockIdx.x], 1u) == (unsigned)(nsplit - 1);
+        __syncthreads();
+        if (!isLast) return;
+        __threadfence();
+        if (threadIdx.x == 0) counters[blockIdx.x] = 0;
+        if (qi >= nq) return;
+        best = (256u << 22) | BF_NOIDX;
+        second = 256;
+        for (int s = 0; s < nsplit; ++s) {
+            const unsigned long long p = __ldcg(&partial[(size_t)s * nq + qi]);
+            const uint32_t b = (uint32_t)(p >> 32);
+            const int s2 = (int)(uint32_t)p;
+            second = min(max((int)(best >> 22), (int)(b >> 22)), min(second, s2));
+            best = min(best, b);
+        }
     }
+    if (qi >= nq) return;
     const int b1 = (int)(best >> 22);
     const int bi = b1 >= 256 ? -1 : (int)(best & BF_NOIDX);  // a distance of 256 never passes the strict '<' against 256
     if (idx) idx[qi] = bi;
@@ -88,6 +98,7 @@ size_t bruteforce_scratch_bytes(int nq, int nd) {
     (void)nd;
     return (size_t)64 * (size_t)nq * sizeof(unsigned long long);
 }
+size_t bruteforce_counter_bytes(int nq) { return (size_t)((nq + BF_THREADS - 1) / BF_THREADS) * sizeof(unsigned int); }
 
 int launch_hamming_pairs(const uint8_t* a, const uint8_t* b, int n, int* dist, cudaStream_t s) {
     if (n <= 0) return ORBX_OK;
@@ -98,7 +109,7 @@ int launch_hamming_pairs(const uint8_t* a, const uint8_t* b, int n, int* dist, c
 }
 
 int launch_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2,
-                      int* match, unsigned long long* dPartial, cudaStream_t s) {
+                      int* match, unsigned long long* dPartial, unsigned int* dCounters, cudaStream_t s) {
     if (nq <= 0) return ORBX_OK;
     const int qBlocks = (nq + BF_THREADS - 1) / BF_THREADS;
     // enough CTAs to fill 148 SMs a few times over, at least one tile per slice, at most 64 slices
@@ -106,10 +117,8 @@ int launch_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th
     nsplit = std::max(1, std::min(nsplit, (nd + BF_TILE - 1) / BF_TILE));
     const int sliceLen = nd > 0 ? ((nd + nsplit - 1) / nsplit + BF_TILE - 1) / BF_TILE * BF_TILE : BF_TILE;
     nsplit = nd > 0 ? (nd + sliceLen - 1) / sliceLen : 1;
-    k_bruteforce_partial<<<dim3(qBlocks, nsplit), BF_THREADS, 0, s>>>(reinterpret_cast<const uint4*>(q), nq,
-                                                                       reinterpret_cast<const uint4*>(d), nd, sliceLen, dPartial);
-    count_launch();
-    k_bruteforce_merge<<<(nq + 255) / 256, 256, 0, s>>>(dPartial, nq, nsplit, th, ratio, idx, d1, d2, match);
+    k_bruteforce<<<dim3(qBlocks, nsplit), BF_THREADS, 0, s>>>(reinterpret_cast<const uint4*>(q), nq, reinterpret_cast<const uint4*>(d),
+                                                               nd, sliceLen, dPartial, dCounters, th, ratio, idx, d1, d2, match);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

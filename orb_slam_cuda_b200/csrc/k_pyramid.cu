@@ -187,7 +187,7 @@ int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, s
     const LevelGeom& L = g.lv[0];
     const int gx = (L.pitch + 127) / 128, rpc = rows_per_cta(L.rows, gx, batch);
     dim3 grid(gx, (L.rows + rpc - 1) / rpc, batch);
-    k_pyramid_base<<<grid, 256, 0, s>>>(L.plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride,
+    k_pyramid_base<<<grid, 256, 0, s>>>(L.plane + (long long)g.f0 * L.planeStride, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride,
                                           (long long)frameStride, rpc);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
@@ -198,13 +198,15 @@ int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, c
                          int batch, cudaStream_t s) {
     const LevelGeom& D = g.lv[level];
     const LevelGeom& S = g.lv[level - 1];
+    uint8_t* dPlane = D.plane + (long long)g.f0 * D.planeStride;
+    const uint8_t* sPlane = S.plane + (long long)g.f0 * S.planeStride;
     const int gx = (D.pitch + 127) / 128, rpc = rows_per_cta(D.rows, gx, batch);
     dim3 grid(gx, (D.rows + rpc - 1) / rpc, batch);
     if (areaFast & 2)  // bit 1: every thread's source window fits 8 bytes -> word-based kernel
-        k_pyramid_resize4<<<grid, 256, 0, s>>>(D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, S.plane, S.pitch,
+        k_pyramid_resize4<<<grid, 256, 0, s>>>(dPlane, D.w, D.h, D.pitch, D.rows, D.planeStride, sPlane, S.pitch,
                                                  S.planeStride, xtab, ytab, rpc);
     else
-        k_pyramid_resize<<<grid, 256, 0, s>>>(D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, S.plane, S.pitch,
+        k_pyramid_resize<<<grid, 256, 0, s>>>(dPlane, D.w, D.h, D.pitch, D.rows, D.planeStride, sPlane, S.pitch,
                                                 S.planeStride, xtab, ytab, areaFast & 1, rpc);
     count_launch();
     ORBX_CUDA(cudaGetLastError());

@@ -17,7 +17,7 @@ namespace {
 struct Workspace {  // one per host thread and device
     int device = -1;
     cudaStream_t stream = nullptr;
-    DevBuf a, b, c, d, e, f, g, h, out0, out1, out2, out3, status, partial;
+    DevBuf a, b, c, d, e, f, g, h, out0, out1, out2, out3, status, partial, counters;
     PinBuf pin;
     ~Workspace() {
         // device memory is reclaimed at process exit; freeing here could run after the CUDA runtime is torn down
@@ -85,8 +85,12 @@ int orbx_match_bruteforce_device(const uint8_t* dq, int nq, const uint8_t* dd, i
     int rc = workspace(&w);
     if (rc) return rc;
     if ((rc = w->partial.ensure(bruteforce_scratch_bytes(nq, nd)))) return rc;
+    if (bruteforce_counter_bytes(nq) > w->counters.bytes) {  // per-query-block arrival counters: zero once, the kernel leaves them zero
+        if ((rc = w->counters.ensure(std::max<size_t>(bruteforce_counter_bytes(nq), 4096)))) return rc;
+        ORBX_CUDA(cudaMemset(w->counters.p, 0, w->counters.bytes));
+    }
     return launch_bruteforce(dq, nq, dd, nd, th, ratio, idx, d1, d2, match, w->partial.as<unsigned long long>(),
-                             stream ? (cudaStream_t)stream : w->stream);
+                             w->counters.as<unsigned int>(), stream ? (cudaStream_t)stream : w->stream);
 }
 
 int orbx_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2,

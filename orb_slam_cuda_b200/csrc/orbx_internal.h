@@ -65,6 +65,7 @@ struct FrameGeom {
     int nStrips;              // FAST strips per frame (all levels)
     int blurTilesTotal;
     int iniTh, minTh;
+    int f0;                   // first scratch frame of this launch (lanes of the host-batch pipeline own disjoint ranges)
     LevelGeom lv[ORBX_MAX_LEVELS];
 };
 
@@ -190,8 +191,9 @@ int launch_describe(const FrameGeom& g, int batch, const int* lvlCnt, const uint
 // matchers
 int launch_hamming_pairs(const uint8_t* a, const uint8_t* b, int n, int* dist, cudaStream_t s);
 int launch_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2,
-                      int* match, unsigned long long* dPartial, cudaStream_t s);
+                      int* match, unsigned long long* dPartial, unsigned int* dCounters, cudaStream_t s);
 size_t bruteforce_scratch_bytes(int nq, int nd);
+size_t bruteforce_counter_bytes(int nq);
 int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score,
                     cudaStream_t s);
 

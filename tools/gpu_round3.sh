@@ -1,0 +1,12 @@
+#!/bin/bash
+# GPU-box recipe (iteration): parity tests, variants, bench, ncu of the three heaviest kernels
+set -x
+mkdir -p gpurun_out
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+tail -15 gpurun_out/pytest_gpu.log
+bash tools/bench_variants.sh > gpurun_out/variants.txt 2>&1; grep -v "^+" gpurun_out/variants.txt
+python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
+cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
+ncu --set full --clock-control none --import-source on -k regex:'k_fast_strips|k_orient_describe|k_quadtree' -s 6 -c 3 -o gpurun_out/round3_full -f \
+  python bench.py --steps 1 --warmup 3 --batch 512 --no-cpu-baseline --no-match > gpurun_out/ncu_full.log 2>&1
+ls -la gpurun_out
