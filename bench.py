@@ -33,6 +33,10 @@ WORKLOADS = {  # reference YAMLs: Examples/Monocular/KITTI00-02.yaml, TUM1.yaml,
     "euroc": dict(shape=(480, 752), nfeatures=1200, bytes_per_frame=5_991_655, sum_p=1_117_367),
 }
 SCALE, LEVELS, INI_TH, MIN_TH = 1.2, 8, 20, 7
+# DRAM bytes per frame (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of a 512-frame kitti
+# launch, divided by 512): profiles/r01_ncu_full_b.csv (pyramid, blur) and profiles/r01_ncu_full_c.csv (the others).
+NCU_TRAFFIC_PER_FRAME = {"kitti": {"Pyramid/Resize": 3_425_000, "FAST+Grid": 1_652_000, "Make quadtree": 179_000,
+                                   "Gaussian Blur": 3_282_000, "Compute angle + ORB descriptor + Compute scale": 3_044_000}}
 METRIC = "frames/s ORB extract @1241x376 2k feats"
 
 
@@ -367,7 +371,9 @@ def run_ours(args):
                 "d2h_bytes_per_step": B * cap * 60 + B * 4 + 4, "ms_per_step": e2e_ms / K},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
+                     "traffic": (NCU_TRAFFIC_PER_FRAME.get(args.workload, {}).get(dom) or 0) * B or None,
+                     "traffic_source": "ncu dram__bytes_read+write of this kernel on a 512-frame launch, scaled to this batch (profiles/r01_ncu_full_*.csv)",
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                      "avg_launch_ms": stage[dom],
                      "pipeline": {"bytes_per_frame": wl["bytes_per_frame"], "achieved": value / world * wl["bytes_per_frame"] / 1e9,
                                   "frac": value / world * wl["bytes_per_frame"] / 1e9 / peak}},

@@ -74,6 +74,16 @@ struct orbx_extractor {
     // host-buffer batches are cut into chunks pipelined over three streams: H2D | kernels (stream) | D2H
     cudaStream_t h2dStream = nullptr, d2hStream = nullptr, stream2 = nullptr;  // stream2: kernels of odd chunks
     std::vector<cudaEvent_t> pipeEv;  // 2 per chunk: frames landed, kernels done
+    // single-frame host calls replay a captured CUDA graph (memset + H2D + 12 kernels + one D2H): one launch per frame
+    struct GraphKey {
+        int w = 0, h = 0, cap = 0;
+        const void *hIn = nullptr, *hOut = nullptr, *dIn = nullptr, *dOut = nullptr, *plane0 = nullptr;
+        bool operator==(const GraphKey& o) const {
+            return w == o.w && h == o.h && cap == o.cap && hIn == o.hIn && hOut == o.hOut && dIn == o.dIn && dOut == o.dOut && plane0 == o.plane0;
+        }
+    } graphKey;
+    cudaGraphExec_t graphExec = nullptr;
+    bool graphSeen = false, graphOk = true;
     bool timing = false;
     bool timed = false;      // the last call recorded events
     cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
@@ -488,6 +498,7 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
             cudaStreamDestroy(st);
         }
     for (cudaEvent_t e : ex->pipeEv) cudaEventDestroy(e);
+    if (ex->graphExec) cudaGraphExecDestroy(ex->graphExec);
     for (cudaEvent_t e : ex->ev)
         if (e) cudaEventDestroy(e);
     for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
@@ -591,7 +602,26 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
     // c-1 overlap the kernels of chunk c.  The scratch (pyramids, cell lists ...) holds TWO chunks: even and odd chunks
     // run their kernels on two streams ("lanes") over disjoint halves of it; small batches are a single chunk.
     static const int chunkPref = []() { const char* e = getenv("ORBX_PIPE_CHUNK"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 64; }();
-    const int nChunks = std::max(1, batch / chunkPref), C = (batch + nChunks - 1) / nChunks;
+    static const bool taper = []() { const char* e = getenv("ORBX_PIPE_TAPER"); return !e || atoi(e) != 0; }();
+    const int nFull = std::max(1, batch / chunkPref), C = (batch + nFull - 1) / nFull;
+    // chunk sizes: C each; with >= 4 chunks the first and the last are halved, so the kernels start after a short first
+    // copy and the drain after the last copy is short
+    std::vector<int> sizes;
+    for (int left = batch; left > 0;) {
+        const int n = std::min(C, left);
+        sizes.push_back(n);
+        left -= n;
+    }
+    if (taper && sizes.size() >= 4 && C >= 16) {
+        const int lastN = sizes.back();
+        sizes.pop_back();
+        sizes.erase(sizes.begin());
+        sizes.insert(sizes.begin(), {C / 2, C - C / 2});
+        sizes.push_back(lastN - lastN / 2);
+        sizes.push_back(lastN / 2);
+        if (sizes.back() == 0) sizes.pop_back();
+    }
+    const int nChunks = (int)sizes.size();
     const int lanes = nChunks > 1 ? 2 : 1;  // kernels of even / odd chunks run on two streams over disjoint scratch halves, so
                                             // the tail of one chunk's kernels overlaps the next chunk's
     if ((rc = configure(ex, w, h, lanes * C))) return rc;
@@ -641,14 +671,84 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
     int* dC = reinterpret_cast<int*>(dOut + kpBytes + dBytes);
     int* dSt = reinterpret_cast<int*>(dOut + kpBytes + dBytes + cBytes);
     const bool oneCopy = !direct && nChunks == 1;
+    uint8_t* dF = ex->dFrames.as<uint8_t>();
+    static const bool noGraph = getenv("ORBX_NO_GRAPH") != nullptr || getenv("ORBX_DEBUG_SYNC") != nullptr;
+    if (batch == 1 && oneCopy && !directIn && !ex->timing && ex->graphOk && !noGraph) {
+        // ---- single frame, pageable buffers (what ORBextractor::operator() does per frame): the whole sequence is captured
+        //      into a CUDA graph the second time a geometry is seen and replayed from then on ----
+        uint8_t* st = ex->hFrames.as<uint8_t>();
+        for (int y = 0; y < h; ++y) memcpy(st + (size_t)y * rowBytes, frames + (size_t)y * stride, rowBytes);
+        orbx_extractor::GraphKey key;
+        key.w = w; key.h = h; key.cap = cap;
+        key.hIn = st; key.hOut = hk; key.dIn = dF; key.dOut = dOut; key.plane0 = ex->g.lv[0].plane;
+        bool launched = false;
+        if (ex->graphExec && key == ex->graphKey) {
+            ORBX_CUDA(cudaGraphLaunch(ex->graphExec, s));
+            ex->serial++;
+            for (int i = 0; i < ex->prm.nlevels + 4; ++i) count_launch();  // the kernels of the replayed graph
+            launched = true;
+        } else {
+            if (ex->graphExec) {
+                cudaGraphExecDestroy(ex->graphExec);
+                ex->graphExec = nullptr;
+            }
+            const bool capture = ex->graphSeen && key == ex->graphKey;
+            ex->graphKey = key;
+            ex->graphSeen = true;
+            if (capture && cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+                cudaGetLastError();
+                ex->graphOk = false;
+            } else {
+                rc = ORBX_OK;
+                cudaError_t ce = cudaMemsetAsync(dSt, 0, sizeof(int), s);
+                if (ce == cudaSuccess) ce = cudaMemcpyAsync(dF, st, frameBytes, cudaMemcpyHostToDevice, s);
+                if (ce == cudaSuccess) rc = run_pipeline(ex, dF, 1, rowBytes, frameBytes, dK, dD, cap, dC, dSt, s, false, 0);
+                if (ce == cudaSuccess && !rc) ce = cudaMemcpyAsync(hk, dOut, outBytes, cudaMemcpyDeviceToHost, s);
+                if (capture) {
+                    cudaGraph_t graph = nullptr;
+                    cudaError_t ee = cudaStreamEndCapture(s, &graph);
+                    if (ce == cudaSuccess && !rc && ee == cudaSuccess && graph &&
+                        cudaGraphInstantiate(&ex->graphExec, graph, 0) == cudaSuccess) {
+                        ORBX_CUDA(cudaGraphLaunch(ex->graphExec, s));
+                        launched = true;
+                    } else {  // capture is not possible here: run the plain sequence from now on
+                        cudaGetLastError();
+                        ex->graphExec = nullptr;
+                        ex->graphOk = false;
+                    }
+                    if (graph) cudaGraphDestroy(graph);
+                } else {
+                    if (ce != cudaSuccess) {
+                        set_error("orbx_extract: %s", cudaGetErrorString(ce));
+                        return ORBX_E_CUDA;
+                    }
+                    if (rc) return rc;
+                    launched = true;
+                }
+            }
+        }
+        if (launched) {
+            ex->lastFrameBase = ex->lastScratchBase = 0;
+            ex->lastBatch = 1;
+            ORBX_CUDA(cudaStreamSynchronize(s));
+            counts[0] = hc[0];
+            memcpy(kps, hk, (size_t)hc[0] * sizeof(orbx_keypoint));
+            memcpy(desc, hd, (size_t)hc[0] * 32);
+            if (*hst != 0) {
+                set_error("orbx_extract: a device buffer overflowed (more than %d keypoints in a FAST cell, or more than cap=%d keypoints in a frame)",
+                          CELL_CAP, cap);
+                return ORBX_E_OVERFLOW;
+            }
+            return ORBX_OK;
+        }
+    }
     ORBX_CUDA(cudaMemsetAsync(dSt, 0, sizeof(int), s));
     if (nChunks > 1) {  // the second lane starts after the status word is cleared
         ORBX_CUDA(cudaEventRecord(ex->pipeEv[2 * nChunks], s));
         ORBX_CUDA(cudaStreamWaitEvent(ex->stream2, ex->pipeEv[2 * nChunks], 0));
     }
-    uint8_t* dF = ex->dFrames.as<uint8_t>();
-    for (int c = 0, f0 = 0; c < nChunks; ++c, f0 += C) {
-        const int nb = std::min(C, batch - f0);
+    for (int c = 0, f0 = 0; c < nChunks; f0 += sizes[c], ++c) {
+        const int nb = sizes[c];
         const int lane = c & (lanes - 1);
         cudaStream_t sK = lane ? ex->stream2 : s;
         const uint8_t* src = frames + (size_t)f0 * frameStride;

@@ -163,6 +163,7 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
     const uint32_t* tile32 = reinterpret_cast<const uint32_t*>(S.tile);
     const uint32_t* act32 = reinterpret_cast<const uint32_t*>(S.act);
     const int rowsPerChunk = max(1, FS_LIST1 / (nW * 4));
+    int rpc = dH;  // optimistic: the whole strip is one chunk (survivors are a small fraction of the pixels)
     const int stepY = FS_THREADS / nW, stepW = FS_THREADS - stepY * nW;
     int off[16];
 #pragma unroll
@@ -188,8 +189,8 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
     for (int pass = 0; pass < 2; ++pass) {
         const int t = min(max(pass == 0 ? g.iniTh : g.minTh, 0), 255);
         const uint32_t T4 = (uint32_t)t * 0x01010101u;
-        for (int y0 = 0; y0 < dH; y0 += rowsPerChunk) {
-            const int y1 = min(y0 + rowsPerChunk, dH);
+        for (int y0 = 0; y0 < dH; y0 += rpc) {
+            const int y1 = min(y0 + rpc, dH);
             // ---- A: packed quick test on the 8 even ring points: a run of 9 holds 4 consecutive even points ----
             // the (row, word) pairs of the chunk are walked as one flat index, so every lane has work whatever the strip
             // width; the row / word of a thread advance incrementally (no division inside the loop)
@@ -247,11 +248,14 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
                                                   lop3_and_or(pd[6], pd[4], pd[0])) |
                                          lop3_and_or(pd[3], pd[1], pd[5]) | lop3_and_or(pd[7], pd[5], pd[1])) & vm;
                     if (fl) {
-                        int o = atomicAdd(&S.cnt[par], __popc(fl));
-                        const int pos0 = (y + 3) * TW + ((wq0 + w) << 2);
+                        const int np = __popc(fl);
+                        int o = atomicAdd(&S.cnt[par], np);
+                        if (o + np <= FS_LIST1) {  // (an overflowing optimistic pass is repeated in row chunks, see below)
+                            const int pos0 = (y + 3) * TW + ((wq0 + w) << 2);
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (fl & (0x80u << (8 * j))) S.list1[o++] = (uint16_t)(pos0 + j);
+                            for (int j = 0; j < 4; ++j)
+                                if (fl & (0x80u << (8 * j))) S.list1[o++] = (uint16_t)(pos0 + j);
+                        }
                     }
                 }
             }
@@ -259,6 +263,13 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
             const int n1 = S.cnt[par];
             if (tid == 0) S.cnt[par ^ 1] = 0;  // nobody touches the other counter before the next barrier
             par ^= 1;
+            if (n1 > FS_LIST1) {  // more survivors than the list holds (only possible while rpc == dH): redo the pass in
+                                  // chunks of rows whose pixels all fit.  Nothing but the survivor count was written.
+                rpc = rowsPerChunk;
+                y0 = -rpc;
+                __syncthreads();
+                continue;
+            }
             // ---- B: full 16-point segment test; corners get cornerScore<16> (both polarities: the one without a run
             //         never wins the max) and join the corner list of this pass ----
             for (int i = tid; i < n1; i += FS_THREADS) {

@@ -29,7 +29,7 @@ __global__ void k_hamming_pairs(const uint4* __restrict__ a, const uint4* __rest
 }
 
 constexpr int BF_THREADS = 128;  // queries per CTA
-constexpr int BF_TILE = 256;     // database descriptors staged per tile (8 KB)
+constexpr int BF_TILE = 64;      // database descriptors staged per tile (2 KB): small tiles give a 2000 x 2000 call 512 CTAs
 constexpr uint32_t BF_NOIDX = 0x3FFFFFu;
 
 // grid (ceil(nq / BF_THREADS), nsplit): every CTA matches 128 queries against one slice of the database and writes

@@ -50,8 +50,13 @@ __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plan
     for (int py = blockIdx.y * rowsPerCta + warp; py < rowEnd; py += 8) {
         const uint8_t* __restrict__ src = fbase + (long long)reflect101(py - EDGE, h) * stride;
         uint32_t v;
-        if (run && ((reinterpret_cast<uintptr_t>(src + sx[0]) & 3) == 0)) {
-            v = __ldg(reinterpret_cast<const uint32_t*>(src + sx[0]));
+        if (run) {  // 4 consecutive interior bytes at any alignment: the aligned word(s) holding them + a funnel shift.
+                    // The second word is read only when it holds a needed byte, so no load passes the frame's last word.
+            const uintptr_t a = reinterpret_cast<uintptr_t>(src + sx[0]);
+            const uint32_t* w0 = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+            const uint32_t sh = (uint32_t)(a & 3) * 8;
+            const uint32_t lo = __ldg(w0);
+            v = sh ? __funnelshift_r(lo, __ldg(w0 + 1), sh) : lo;
         } else {
             v = 0;
 #pragma unroll

@@ -161,6 +161,43 @@ def test_small_and_odd_sizes():
         assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od), (h, w)
 
 
+def test_repeated_single_frames_graph_replay():
+    """The second single-frame call of a geometry captures a CUDA graph, later calls replay it: every frame of a stream
+    must still equal the oracle, mvImagePyramid must follow the current frame, and a size change must re-capture."""
+    gx, ox = make("tum")
+    for i in range(6):
+        img = synth.frame("tum", 40 + i)
+        k, d = gx(img)
+        ok, od = ox.extract(img)
+        assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od), i
+        assert np.array_equal(gx.image_pyramid_level(2, padded=True), ox.level_padded(2)), i
+    for i in range(4):  # other geometry on the same handle, then back
+        img = synth.textured_frame(700 + i, 240, 320)
+        k, d = gx(img)
+        ok, od = ox.extract(img)
+        assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od), i
+    img = synth.frame("tum", 77)
+    k, d = gx(img)
+    ok, od = ox.extract(img)
+    assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od)
+
+
+@pytest.mark.parametrize("amp", [255, 120])
+def test_dense_noise_image(amp):
+    """White noise: most pixels pass the FAST quick test, so the optimistic single-chunk survivor list of a strip
+    overflows and the pass is redone in row chunks; cells hold close to CELL_CAP keypoints."""
+    rng = np.random.default_rng(5)
+    img = (128 + (rng.random((240, 320)) - 0.5) * amp).astype(np.uint8)
+    gx, ox = X.ORBextractor(500, 1.2, 8, 20, 7), O.Extractor(500, 1.2, 8, 20, 7)
+    k, d = gx(img)
+    ok, od = ox.extract(img)
+    for l in range(8):
+        a, b = gx.debug_candidates(l), ox.level_candidates(l)
+        assert kp_tuple(a) == kp_tuple(b), f"level {l}: {len(a)} vs {len(b)} candidates"
+    assert len(k) == len(ok)
+    assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od)
+
+
 def test_quadtree_standalone_random():
     rng = np.random.default_rng(7)
     for trial in range(40):
