@@ -212,7 +212,7 @@ def latency_leg(X, wl, w, h, kind):
             "path": "orbx_extract through the python binding, pageable host buffers"}
 
 
-def run_reference(args):
+def run_reference(args, emit=print):
     """--impl reference: the reference's CPU ORBextractor path, restated in oracle/ (kind "port"), on all host threads."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -243,10 +243,10 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
 
 
-def run_ours(args):
+def run_ours(args, emit=print):
     import torch
     import orb_slam_cuda_b200 as X
 
@@ -396,17 +396,38 @@ def run_ours(args):
         rate1, secs1, done1 = cpu_extract_rate(args.workload, 16, 1, min_secs=3.0)
         line["cpu_baseline"]["single_thread_frames_per_s"] = rate1
         line["cpu_baseline"]["single_thread_sample"] = f"{done1} frames in {secs1:.1f} s on 1 thread"
-    print(json.dumps(line), flush=True)
+    emit(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
 
 
+class StdoutToStderr:
+    """Library banners (e.g. "NCCL version ..." printed on stdout by the NCCL runtime) must not mix with the ONE JSON line
+    of the contract: file descriptor 1 points at stderr while the benchmark runs and is restored for the final print."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+        return False
+
+
 def main():
     args = parse()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    lines = []
+    with StdoutToStderr():
+        if args.impl == "reference":
+            run_reference(args, lines.append)
+        else:
+            run_ours(args, lines.append)
+    for l in lines:
+        print(l, flush=True)
 
 
 if __name__ == "__main__":

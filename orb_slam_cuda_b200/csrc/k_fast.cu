@@ -149,11 +149,13 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
     const int X0 = xo + 3;              // first detectable tile column
     const int wq0 = X0 >> 2, nW = ((X0 + dW + 3) >> 2) - wq0;
     // while the tile is in flight: clear the score tile, set up the column tables and counters
-    for (int i = tid; i < TN / 4; i += FS_THREADS) reinterpret_cast<uint32_t*>(S.score)[i] = 0;
+    for (int i = tid; i < TN / 16; i += FS_THREADS) reinterpret_cast<uint4*>(S.score)[i] = make_uint4(0u, 0u, 0u, 0u);  // TW % 16 == 0
     for (int x = tid; x < TW; x += FS_THREADS) {
         const int dx = x - X0;
         const bool det = dx >= 0 && dx < dW;
-        S.cellOfCol[x] = det ? (uint8_t)(dx / L.wCell) : (uint8_t)255;
+        int cell = 0;  // dx / wCell for the few cells of a strip, without a division
+        for (int j = 1; j < nc; ++j) cell += dx >= j * L.wCell ? 1 : 0;
+        S.cellOfCol[x] = det ? (uint8_t)cell : (uint8_t)255;
         S.act[x] = det ? 0x80 : 0;
     }
     if (tid < 16) S.cnt[tid] = 0;
