@@ -15,6 +15,7 @@
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -83,6 +84,78 @@ public:
                                              n2, d2.ptr<unsigned char>(), bounds, reinterpret_cast<float*>(vbPrevMatched.data()),
                                              vnMatches12.data(), windowSize, mfNNratio, mbCheckOrientation ? 1 : 0, &nmatches),
               "SearchForInitialization");
+        return nmatches;
+    }
+
+    // Project MapPoints tracked in last frame into the current frame and search matches; src/ORBmatcher.cc:1328-1470 (used to
+    // track from previous frame, src/Tracking.cc:962,968).  FrameT / MapPoint members read: mTcw (4x4 CV_32F), mb, mbf, fx, fy, cx,
+    // cy, N, mvpMapPoints, mvbOutlier, mvKeys, mvKeysUn, mDescriptors, mvuRight, mvScaleFactors, mnMinX..mnMaxY;
+    // pMP->GetWorldPos(), GetDescriptor(), Observations() — exactly what the reference routine reads.  The pose arithmetic stays
+    // on the host (with OpenCV: the reference's own cv::Mat expressions); window search, Hamming and the assignment run on the GPU.
+    template <class FrameT>
+    int SearchByProjection(FrameT& CurrentFrame, const FrameT& LastFrame, const float th, const bool bMono) {
+        const int n1 = LastFrame.N, n2 = (int)CurrentFrame.mvKeysUn.size();
+        if (n1 == 0 || n2 == 0) return 0;
+        float R[9], t[3], Rl[9], tl[3];
+        for (int r = 0; r < 3; ++r) {
+            for (int c = 0; c < 3; ++c) {
+                R[3 * r + c] = CurrentFrame.mTcw.template at<float>(r, c);
+                Rl[3 * r + c] = LastFrame.mTcw.template at<float>(r, c);
+            }
+            t[r] = CurrentFrame.mTcw.template at<float>(r, 3);
+            tl[r] = LastFrame.mTcw.template at<float>(r, 3);
+        }
+#if ORBX_HAVE_OPENCV
+        const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3), tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+        const cv::Mat twc = -Rcw.t() * tcw;
+        const cv::Mat tlc = LastFrame.mTcw.rowRange(0, 3).colRange(0, 3) * twc + LastFrame.mTcw.rowRange(0, 3).col(3);
+        const float tlcz = tlc.at<float>(2);
+#else  // stand-in Mat without arithmetic: the same expressions in plain float
+        float twc[3];
+        for (int c = 0; c < 3; ++c) twc[c] = -(R[c] * t[0] + R[3 + c] * t[1] + R[6 + c] * t[2]);
+        const float tlcz = Rl[6] * twc[0] + Rl[7] * twc[1] + Rl[8] * twc[2] + tl[2];
+#endif
+        const bool bForward = tlcz > CurrentFrame.mb && !bMono, bBackward = -tlcz > CurrentFrame.mb && !bMono;  // :1348-1349
+        std::vector<float> x3(3 * (size_t)n1, 0.f), angle1(n1, 0.f);
+        std::vector<unsigned char> valid1(n1, 0), obs1(n1, 0), mpDesc((size_t)n1 * 32, 0), occupied2(n2, 0);
+        std::vector<int> octave1(n1, 0);
+        for (int i = 0; i < n1; ++i) {
+            auto* pMP = LastFrame.mvpMapPoints[i];
+            if (!pMP || LastFrame.mvbOutlier[i]) continue;
+            valid1[i] = 1;
+            obs1[i] = pMP->Observations() > 0;
+            const cv::Mat x3Dw = pMP->GetWorldPos();
+#if ORBX_HAVE_OPENCV
+            const cv::Mat x3Dc = Rcw * x3Dw + tcw;  // :1362-1363
+            for (int c = 0; c < 3; ++c) x3[3 * i + c] = x3Dc.at<float>(c);
+#else
+            for (int r = 0; r < 3; ++r)
+                x3[3 * i + r] = R[3 * r] * x3Dw.template at<float>(0, 0) + R[3 * r + 1] * x3Dw.template at<float>(1, 0) +
+                                R[3 * r + 2] * x3Dw.template at<float>(2, 0) + t[r];
+#endif
+            const cv::Mat dMP = pMP->GetDescriptor();
+            std::memcpy(&mpDesc[(size_t)i * 32], dMP.template ptr<unsigned char>(), 32);
+            octave1[i] = LastFrame.mvKeys[i].octave;
+            angle1[i] = LastFrame.mvKeysUn[i].angle;
+        }
+        for (int j = 0; j < n2; ++j) occupied2[j] = CurrentFrame.mvpMapPoints[j] && CurrentFrame.mvpMapPoints[j]->Observations() > 0;
+        const cv::Mat d2 = continuous(CurrentFrame.mDescriptors);
+        const float cam[4] = {CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx, CurrentFrame.cy};
+        const float bounds[4] = {(float)FrameT::mnMinX, (float)FrameT::mnMaxX, (float)FrameT::mnMinY, (float)FrameT::mnMaxY};
+        const bool hasRight = (int)CurrentFrame.mvuRight.size() == n2;
+        std::vector<int> match21(n2, -1);
+        int nmatches = 0;
+        check(orbx_search_by_projection(n1, x3.data(), valid1.data(), obs1.data(), mpDesc.data(), octave1.data(), angle1.data(),
+                                        reinterpret_cast<const orbx_keypoint*>(CurrentFrame.mvKeysUn.data()), n2,
+                                        d2.template ptr<unsigned char>(), hasRight ? CurrentFrame.mvuRight.data() : nullptr,
+                                        occupied2.data(), cam, CurrentFrame.mbf, bounds, CurrentFrame.mvScaleFactors.data(),
+                                        (int)CurrentFrame.mvScaleFactors.size(), th, bForward ? 1 : (bBackward ? 2 : 0),
+                                        mbCheckOrientation ? 1 : 0, match21.data(), &nmatches),
+              "SearchByProjection");
+        for (int j = 0; j < n2; ++j) {
+            if (match21[j] >= 0) CurrentFrame.mvpMapPoints[j] = LastFrame.mvpMapPoints[match21[j]];
+            else if (match21[j] == -2) CurrentFrame.mvpMapPoints[j] = nullptr;
+        }
         return nmatches;
     }
 

@@ -145,6 +145,22 @@ int orbx_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_
                                    int n2, const uint8_t* desc2, const float bounds[4], float* prev_xy, int* matches12,
                                    int window, float nnratio, int check_ori, int* nmatches);
 
+/* SearchByProjection(CurrentFrame, LastFrame, th, bMono) (src/ORBmatcher.cc:1328-1470): the per-frame tracking matcher
+ * (src/Tracking.cc:962,968).  The boundary sits after the pose arithmetic, which stays the caller's cv::Mat expressions:
+ *   x3dc[3*i..]  = Rcw*x3Dw+tcw of LastFrame.mvpMapPoints[i] (:1362-1363);  direction = 0 / 1 (bForward) / 2 (bBackward), :1348-1349
+ *   valid1[i]    = mvpMapPoints[i] != NULL && !mvbOutlier[i];  obs1[i] = that point's Observations() > 0
+ *   mp_desc1     = pMP->GetDescriptor() (32 bytes per point);  octave1 = LastFrame.mvKeys[i].octave;  angle1 = mvKeysUn[i].angle
+ *   k2, desc2    = CurrentFrame.mvKeysUn / mDescriptors;  u_right2 = mvuRight (NULL for monocular frames)
+ *   occupied2[j] = CurrentFrame.mvpMapPoints[j] != NULL && ...->Observations() > 0 on entry
+ *   cam = {fx, fy, cx, cy};  bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY};  scale_factors = mvScaleFactors
+ * match21[j] = i: CurrentFrame.mvpMapPoints[j] = LastFrame.mvpMapPoints[i];  -1: untouched;  -2: set to NULL by the rotation
+ * check (:1451-1467).  *nmatches = return value.  Host buffers. */
+int orbx_search_by_projection(int n1, const float* x3dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mp_desc1,
+                              const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
+                              const float* u_right2, const uint8_t* occupied2, const float cam[4], float mbf,
+                              const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
+                              int check_ori, int* match21, int* nmatches);
+
 /* Frame::ComputeStereoMatches (src/Frame.cc:465-639).  exL / exR hold the pyramids of the left / right frame of
  * their last orbx_extract call (device resident; nothing is copied to the host).  bf = mbf (baseline x fx),
  * mb = baseline in metres = mbf / fx (src/Frame.cc:113).  u_right[nL], depth[nL] as mvuRight / mvDepth

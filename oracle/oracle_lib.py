@@ -202,6 +202,26 @@ def search_for_initialization(k1, d1, k2, d2, bounds, prev_xy, window=100, nnrat
     return n, m12, prev
 
 
+def search_by_projection_frame(x3Dc, valid1, obs1, mp_desc1, octave1, angle1, k2, d2, u_right2, occupied2, cam, mbf, bounds,
+                               scale_factors, th, direction=0, check_ori=True):
+    x3Dc = np.ascontiguousarray(x3Dc, dtype=np.float32)
+    valid1, obs1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, obs1, occupied2))
+    mp_desc1, d2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (mp_desc1, d2))
+    octave1 = np.ascontiguousarray(octave1, dtype=np.int32)
+    angle1 = np.ascontiguousarray(angle1, dtype=np.float32)
+    k2 = np.ascontiguousarray(k2, dtype=KP_DTYPE)
+    ur = None if u_right2 is None else np.ascontiguousarray(u_right2, dtype=np.float32)
+    cam = np.asarray(cam, dtype=np.float32)
+    b = np.asarray(bounds, dtype=np.float32)
+    sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+    m21 = np.empty(max(k2.size, 1), np.int32)
+    n = lib().orc_search_by_projection_frame(valid1.size, _p(x3Dc), _p(valid1), _p(obs1), _p(mp_desc1), _p(octave1), _p(angle1),
+                                             _p(k2), k2.size, _p(d2), _p(ur) if ur is not None else None, _p(occupied2),
+                                             _p(cam), C.c_float(mbf), _p(b), _p(sf), C.c_float(th), int(direction),
+                                             int(check_ori), _p(m21))
+    return n, m21[:k2.size]
+
+
 def match_bruteforce(q, d, th=50, ratio=0.6):
     q = np.ascontiguousarray(q, dtype=np.uint8)
     d = np.ascontiguousarray(d, dtype=np.uint8)

@@ -681,6 +681,79 @@ int search_for_initialization(const GridFrame& F1, const uint8_t* desc1, const G
     return nmatches;
 }
 
+// ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono) — src/ORBmatcher.cc:1328-1470
+// (TH_HIGH=100, HISTO_LENGTH=30 at :37-39).  The boundary is drawn after the pose arithmetic: x3Dc[i] = Rcw*x3Dw+tcw
+// (:1362-1363, cv::Mat expressions evaluated by the caller exactly as the reference does) and `direction` (0: octave +-1,
+// 1: bForward, 2: bBackward, :1348-1349) come in; everything from :1365 on is restated here.
+//   valid1[i]  = LastFrame.mvpMapPoints[i] && !LastFrame.mvbOutlier[i]       (:1353-1357)
+//   obs1[i]    = that map point's Observations() > 0                           (decides whether a keypoint it was assigned to
+//                                                                                is skipped by later iterations, :1404-1406)
+//   occupied2  = CurrentFrame.mvpMapPoints[i2] && ...->Observations() > 0 on entry
+//   match21[i2] = index i of the last-frame point assigned to current keypoint i2 (CurrentFrame.mvpMapPoints[i2] = pMP),
+//                 -1 = untouched, -2 = set to NULL by the rotation-consistency pass (:1451-1467)
+int search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
+                               const int* octave1, const float* angle1, const GridFrame& F2, const uint8_t* desc2,
+                               const float* uRight2, const uint8_t* occupied2, float fx, float fy, float cx, float cy, float mbf,
+                               const float* scaleFactors, float th, int direction, bool checkOri, int* match21) {
+    const int HISTO_LENGTH = 30, TH_HIGH = 100;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<int> owner(F2.n, -1);         // CurrentFrame.mvpMapPoints[i2] as the index of the last-frame point
+    std::vector<uint8_t> taken(F2.n);         // ... && Observations() > 0
+    for (int i = 0; i < F2.n; ++i) taken[i] = occupied2[i];
+    for (int i = 0; i < n1; i++) {
+        if (!valid1[i]) continue;
+        const float xc = x3Dc[3 * i], yc = x3Dc[3 * i + 1];
+        const float invzc = (float)(1.0 / x3Dc[3 * i + 2]);
+        if (invzc < 0) continue;
+        float u = fx * xc * invzc + cx;
+        float v = fy * yc * invzc + cy;
+        if (u < F2.minX || u > F2.maxX) continue;
+        if (v < F2.minY || v > F2.maxY) continue;
+        const int nLastOctave = octave1[i];
+        const float radius = th * scaleFactors[nLastOctave];
+        std::vector<size_t> vIndices2;
+        if (direction == 1) vIndices2 = F2.features_in_area(u, v, radius, nLastOctave, -1);
+        else if (direction == 2) vIndices2 = F2.features_in_area(u, v, radius, 0, nLastOctave);
+        else vIndices2 = F2.features_in_area(u, v, radius, nLastOctave - 1, nLastOctave + 1);
+        if (vIndices2.empty()) continue;
+        const uint8_t* dMP = mpDesc1 + (size_t)i * 32;
+        int bestDist = 256, bestIdx2 = -1;
+        for (size_t i2 : vIndices2) {
+            if (taken[i2]) continue;
+            if (uRight2 && uRight2[i2] > 0) {
+                const float ur = u - mbf * invzc;
+                const float er = std::fabs(ur - uRight2[i2]);
+                if (er > radius) continue;
+            }
+            const int dist = descriptor_distance(dMP, desc2 + i2 * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx2 = (int)i2; }
+        }
+        if (bestDist <= TH_HIGH) {
+            owner[bestIdx2] = i;
+            taken[bestIdx2] = obs1[i];
+            nmatches++;
+            if (checkOri) {
+                float rot = angle1[i] - F2.keys[bestIdx2].angle;
+                if (rot < 0.0) rot += 360.0f;
+                int bin = (int)std::round(rot * factor);
+                if (bin == HISTO_LENGTH) bin = 0;
+                rotHist[bin].push_back(bestIdx2);
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++)
+            if (i != ind1 && i != ind2 && i != ind3)
+                for (int idx : rotHist[i]) { owner[idx] = -2; nmatches--; }  // = static_cast<MapPoint*>(NULL)
+    }
+    for (int i = 0; i < F2.n; ++i) match21[i] = owner[i];
+    return nmatches;
+}
+
 // Brute-force best / second-best with the TH + ratio acceptance test.  There is no single reference function
 // (SURVEY.md §8a16); this follows the inner loop of ORBmatcher::SearchByBoW, src/ORBmatcher.cc:199-232:
 // bestDist1 = bestDist2 = 256, strict '<' updates, accept iff d1 <= th && (float)d1 < ratio*(float)d2.

@@ -92,6 +92,15 @@ int orc_search_for_initialization(const KeyPoint* k1, int n1, const uint8_t* d1,
     GridFrame F1(k1, n1, minX, maxX, minY, maxY), F2(k2, n2, minX, maxX, minY, maxY);
     return search_for_initialization(F1, d1, F2, d2, prevXY, matches12, windowSize, nnratio, checkOri != 0);
 }
+int orc_search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
+                                   const int* octave1, const float* angle1, const KeyPoint* k2, int n2, const uint8_t* desc2,
+                                   const float* uRight2, const uint8_t* occupied2, const float* cam, float mbf,
+                                   const float* bounds, const float* scaleFactors, float th, int direction, int checkOri,
+                                   int* match21) {
+    GridFrame F2(k2, n2, bounds[0], bounds[1], bounds[2], bounds[3]);
+    return search_by_projection_frame(n1, x3Dc, valid1, obs1, mpDesc1, octave1, angle1, F2, desc2, uRight2, occupied2, cam[0],
+                                      cam[1], cam[2], cam[3], mbf, scaleFactors, th, direction, checkOri != 0, match21);
+}
 void orc_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2, int* match) {
     match_bruteforce(q, nq, d, nd, th, ratio, idx, d1, d2, match);
 }

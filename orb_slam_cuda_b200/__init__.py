@@ -252,6 +252,29 @@ class ORBmatcher:
                                                     int(self.mbCheckOrientation), C.byref(n)))
         return n.value, m12[:kps1.size]
 
+    def SearchByProjection(self, x3Dc, valid1, obs1, mp_desc1, octave1, angle1, kps2, desc2, u_right2, occupied2, cam, mbf,
+                           bounds, scale_factors, th: float, direction: int = 0):
+        """SearchByProjection(CurrentFrame, LastFrame, th, bMono), src/ORBmatcher.cc:1328-1470, with the boundary of
+        include/orbx.h (camera-frame points in, assignment per current keypoint out).  Returns (nmatches, match21)."""
+        x3Dc = np.ascontiguousarray(x3Dc, dtype=np.float32)
+        valid1, obs1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, obs1, occupied2))
+        mp_desc1, desc2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (mp_desc1, desc2))
+        octave1 = np.ascontiguousarray(octave1, dtype=np.int32)
+        angle1 = np.ascontiguousarray(angle1, dtype=np.float32)
+        kps2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+        ur = None if u_right2 is None else np.ascontiguousarray(u_right2, dtype=np.float32)
+        cam = np.asarray(cam, dtype=np.float32)
+        b = np.asarray(bounds, dtype=np.float32)
+        sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+        n1, n2 = valid1.size, kps2.size
+        m21 = np.empty(max(n2, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_search_by_projection(n1, _p(x3Dc), _p(valid1), _p(obs1), _p(mp_desc1), _p(octave1), _p(angle1), _p(kps2),
+                                               n2, _p(desc2), _p(ur) if ur is not None else None, _p(occupied2), _p(cam),
+                                               C.c_float(mbf), _p(b), _p(sf), sf.size, C.c_float(th), int(direction),
+                                               int(self.mbCheckOrientation), _p(m21), C.byref(n)))
+        return n.value, m21[:n2]
+
     def match_bruteforce(self, q, d, th: int = TH_LOW):
         """best / second-best over the whole database (inner loop of SearchByBoW, src/ORBmatcher.cc:187-232):
         returns (idx, d1, d2, match) int32 [nq]."""

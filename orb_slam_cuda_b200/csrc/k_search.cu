@@ -267,4 +267,201 @@ int launch_search_for_initialization(const orbx_keypoint* k1, int n1, const uint
     return ORBX_OK;
 }
 
+// ---- ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono)  (reference src/ORBmatcher.cc:1328-1470) ----
+// Same decomposition as above: the window walk and the Hamming distances do not depend on the loop order, the
+// assignment does (a current keypoint that received a map point with observations is skipped by later iterations,
+// :1404-1406), so a warp replays the loop over precomputed candidate lists.
+struct SbpParams {
+    float fx, fy, cx, cy, mbf, th;
+    float minX, maxX, minY, maxY, invW, invH;
+    int direction;  // 0: octave-1 .. octave+1, 1: bForward (>= octave), 2: bBackward (0 .. octave)   (:1381-1386)
+    int hasRight;
+};
+
+// One warp per last-frame keypoint i.  cand[i * candCap + k] = (dist << 16) | i2 in GetFeaturesInArea's visiting order.
+__global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __restrict__ x3Dc, const uint8_t* __restrict__ valid1,
+                                                         const uint4* __restrict__ mpDesc1, const int* __restrict__ octave1,
+                                                         const orbx_keypoint* __restrict__ k2, const uint4* __restrict__ desc2,
+                                                         const float* __restrict__ uRight2, const uint8_t* __restrict__ occupied2,
+                                                         const float* __restrict__ scaleFactors, const SbpParams P,
+                                                         const int* __restrict__ sorted, const int* __restrict__ cellStart,
+                                                         uint32_t* __restrict__ cand, int candCap, int* __restrict__ candCnt,
+                                                         int* __restrict__ dStatus) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= n1) return;
+    int count = 0;
+    if (valid1[i]) {
+        const float xc = x3Dc[3 * i], yc = x3Dc[3 * i + 1];
+        const float invzc = __double2float_rn(__ddiv_rn(1.0, (double)x3Dc[3 * i + 2]));  // const float invzc = 1.0/z  (:1367)
+        const float u = __fadd_rn(__fmul_rn(__fmul_rn(P.fx, xc), invzc), P.cx);             // fx*xc*invzc+cx        (:1372)
+        const float v = __fadd_rn(__fmul_rn(__fmul_rn(P.fy, yc), invzc), P.cy);
+        const bool inImage = !(invzc < 0.f) && !(u < P.minX || u > P.maxX) && !(v < P.minY || v > P.maxY);
+        if (inImage) {
+            const int oct = octave1[i];
+            const float r = __fmul_rn(P.th, scaleFactors[oct]);
+            const int minLevel = P.direction == 1 ? oct : (P.direction == 2 ? 0 : oct - 1);
+            const int maxLevel = P.direction == 1 ? -1 : (P.direction == 2 ? oct : oct + 1);
+            const bool checkLevels = minLevel > 0 || maxLevel >= 0;
+            // GetFeaturesInArea(u, v, r, minLevel, maxLevel)  (src/Frame.cc:326-379)
+            const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, P.minX), r), P.invW)));
+            const int cx1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, P.minX), r), P.invW)));
+            const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, P.minY), r), P.invH)));
+            const int cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, P.minY), r), P.invH)));
+            if (cx0 < GRID_COLS && cx1 >= 0 && cy0 < GRID_ROWS && cy1 >= 0) {
+                const uint4 a0 = mpDesc1[2 * i], a1 = mpDesc1[2 * i + 1];
+                const float ur = __fsub_rn(u, __fmul_rn(P.mbf, invzc));
+                uint32_t* out = cand + (size_t)i * candCap;
+                for (int ix = cx0; ix <= cx1; ++ix) {
+                    const int b = cellStart[ix * GRID_ROWS + cy0], e = cellStart[ix * GRID_ROWS + cy1 + 1];
+                    for (int base = b; base < e; base += 32) {
+                        const int p = base + lane;
+                        bool ok = false;
+                        int i2 = 0, dist = 0;
+                        if (p < e) {
+                            i2 = sorted[p];
+                            const orbx_keypoint kp = k2[i2];
+                            ok = !(checkLevels && (kp.octave < minLevel || (maxLevel >= 0 && kp.octave > maxLevel))) &&
+                                 fabsf(__fsub_rn(kp.x, u)) < r && fabsf(__fsub_rn(kp.y, v)) < r;
+                            // keypoints that hold a map point with observations on entry are skipped by every iteration
+                            ok = ok && !occupied2[i2];
+                            if (ok && P.hasRight) {
+                                const float uR = uRight2[i2];
+                                if (uR > 0.f && fabsf(__fsub_rn(ur, uR)) > r) ok = false;  // :1408-1414
+                            }
+                            if (ok) dist = hamming32B(a0, a1, desc2[2 * i2], desc2[2 * i2 + 1]);
+                        }
+                        const uint32_t m = __ballot_sync(0xffffffffu, ok);
+                        if (ok) {
+                            const int o = count + __popc(m & ((1u << lane) - 1));
+                            if (o < candCap) out[o] = ((uint32_t)dist << 16) | (uint32_t)i2;
+                        }
+                        count += __popc(m);
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) {
+        if (count > candCap) {
+            atomicExch(dStatus, ORBX_E_OVERFLOW);
+            count = candCap;
+        }
+        candCnt[i] = count;
+    }
+}
+
+// One warp replays the loop.  Dynamic shared memory: owner[n2] (int32), evIdx[n1] (int32: bestIdx2 of the acceptance event of
+// iteration i, -1 = none), taken[n2] (uint8), evBin[n1] (int8).
+__global__ void __launch_bounds__(32) k_sbp_resolve(int n1, const uint8_t* __restrict__ obs1, const float* __restrict__ angle1,
+                                                     const orbx_keypoint* __restrict__ k2, int n2,
+                                                     const uint32_t* __restrict__ cand, int candCap,
+                                                     const int* __restrict__ candCnt, int checkOri, int* __restrict__ match21,
+                                                     int* __restrict__ nmatchesOut) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    int* owner = reinterpret_cast<int*>(sm);
+    int* evIdx = owner + n2;
+    uint8_t* taken = reinterpret_cast<uint8_t*>(evIdx + n1);
+    signed char* evBin = reinterpret_cast<signed char*>(taken + n2);
+    const int lane = threadIdx.x;
+    for (int i = lane; i < n2; i += 32) { owner[i] = -1; taken[i] = 0; }
+    for (int i = lane; i < n1; i += 32) { evIdx[i] = -1; evBin[i] = -1; }
+    __syncwarp();
+    const float factor = 1.0f / 30.0f;  // 1.0f / HISTO_LENGTH
+    for (int i = 0; i < n1; ++i) {
+        const int cnt = candCnt[i];
+        if (cnt == 0) continue;
+        const uint32_t* c = cand + (size_t)i * candCap;
+        uint32_t b1 = 0xFFFFFFFFu;  // key = dist << 16 | position: minimal distance, first in visiting order (strict '<', :1420)
+        for (int p = lane; p < cnt; p += 32) {
+            const uint32_t e = c[p];
+            if (taken[e & 0xFFFFu]) continue;
+            b1 = min(b1, ((e >> 16) << 16) | (uint32_t)p);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) b1 = min(b1, __shfl_xor_sync(0xffffffffu, b1, o));
+        if (b1 == 0xFFFFFFFFu) continue;
+        const int bestDist = (int)(b1 >> 16);
+        if (bestDist > 100) continue;  // TH_HIGH (:1427)
+        if (lane == 0) {
+            const int bestIdx2 = (int)(c[b1 & 0xFFFFu] & 0xFFFFu);
+            owner[bestIdx2] = i;
+            taken[bestIdx2] = obs1[i];
+            evIdx[i] = bestIdx2;
+            if (checkOri) {
+                float rot = __fsub_rn(angle1[i], k2[bestIdx2].angle);
+                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+                int bin = (int)roundf(__fmul_rn(rot, factor));
+                if (bin == 30) bin = 0;
+                evBin[i] = (signed char)min(max(bin, 0), 29);
+            }
+        }
+        __syncwarp();
+    }
+    __syncwarp();
+    int total = 0;
+    for (int i = lane; i < n1; i += 32) total += evIdx[i] >= 0 ? 1 : 0;
+    if (checkOri) {
+        int h = 0;  // lane b owns bin b
+        for (int i = 0; i < n1; ++i) h += (evBin[i] == lane) ? 1 : 0;
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int b = 0; b < 30; ++b) {  // ComputeThreeMaxima (:1601-1642)
+            const int s = __shfl_sync(0xffffffffu, h, b);
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = b; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = b; }
+            else if (s > max3) { max3 = s; ind3 = b; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+        for (int i = lane; i < n1; i += 32) {
+            const int b = evBin[i];
+            if (b >= 0 && b != ind1 && b != ind2 && b != ind3) {
+                owner[evIdx[i]] = -2;  // CurrentFrame.mvpMapPoints[idx] = NULL; nmatches--  (:1460-1461)
+                --total;
+            }
+        }
+        __syncwarp();
+    }
+    for (int i = lane; i < n2; i += 32) match21[i] = owner[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+    if (lane == 0) *nmatchesOut = total;
+}
+
+int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
+                                const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
+                                const float* uRight2, const uint8_t* occupied2, const float* scaleFactors, const float cam[4],
+                                float mbf, const float bounds[4], float th, int direction, int checkOri, int* cellOf, int* sorted,
+                                int* cellStart, uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches,
+                                int* dStatus, cudaStream_t s) {
+    SbpParams P;
+    P.fx = cam[0]; P.fy = cam[1]; P.cx = cam[2]; P.cy = cam[3];
+    P.mbf = mbf; P.th = th;
+    P.minX = bounds[0]; P.maxX = bounds[1]; P.minY = bounds[2]; P.maxY = bounds[3];
+    P.invW = (float)GRID_COLS / (P.maxX - P.minX);  // mfGridElementWidthInv (src/Frame.cc:104-105)
+    P.invH = (float)GRID_ROWS / (P.maxY - P.minY);
+    P.direction = direction;
+    P.hasRight = uRight2 != nullptr;
+    const size_t smem = (size_t)n2 * 4 + (size_t)n1 * 4 + (size_t)n2 + (size_t)n1 + 16;
+    if (smem > 200 * 1024) {
+        set_error("SearchByProjection: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
+        return ORBX_E_INVALID;
+    }
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        ORBX_CUDA(cudaFuncSetAttribute(k_sbp_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
+    count_launch();
+    k_sbp_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(n1, x3Dc, valid1, reinterpret_cast<const uint4*>(mpDesc1), octave1, k2,
+                                                    reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, P,
+                                                    sorted, cellStart, cand, candCap, candCnt, dStatus);
+    count_launch();
+    k_sbp_resolve<<<1, 32, smem, s>>>(n1, obs1, angle1, k2, n2, cand, candCap, candCnt, checkOri, match21, nmatches);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
 }  // namespace orbx

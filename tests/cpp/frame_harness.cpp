@@ -6,6 +6,7 @@
 // Input: a raw file of 8-bit frames; output: a raw dump that tests/test_cpp_boundary.py compares with the CPU oracle.
 //   frame_harness mono   in.raw w h nfeatures out.bin          (two frames: extraction + SearchForInitialization)
 //   frame_harness stereo in.raw w h nfeatures bf fx out.bin    (left, right: extraction + ComputeStereoMatches)
+//   frame_harness track  in.raw w h nfeatures th out.bin       (last, current: Tracking::TrackWithMotionModel's SearchByProjection, :962)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -18,7 +19,20 @@
 
 using namespace ORB_SLAM2;
 
+struct MapPoint {  // the members of ORB_SLAM2::MapPoint that SearchByProjection reads (include/MapPoint.h)
+    cv::Mat mWorldPos, mDescriptor;
+    int nObs = 0;
+    cv::Mat GetWorldPos() const { return mWorldPos; }
+    cv::Mat GetDescriptor() const { return mDescriptor; }
+    int Observations() const { return nObs; }
+};
+
 struct Frame {  // the members of ORB_SLAM2::Frame that the front end reads or writes (include/Frame.h)
+    cv::Mat mTcw;
+    float fx = 0, fy = 0, cx = 0, cy = 0;
+    std::vector<MapPoint*> mvpMapPoints;
+    std::vector<bool> mvbOutlier;
+    std::vector<float> mvScaleFactors;
     ORBextractor *mpORBextractorLeft = nullptr, *mpORBextractorRight = nullptr;
     std::vector<cv::KeyPoint> mvKeys, mvKeysRight, mvKeysUn;
     cv::Mat mDescriptors, mDescriptorsRight;
@@ -101,6 +115,53 @@ int main(int argc, char** argv) {
             put_keys(out, F.mvKeysRight, F.mDescriptorsRight);
             put(out, F.mvuRight.data(), F.mvuRight.size() * 4);
             put(out, F.mvDepth.data(), F.mvDepth.size() * 4);
+            fclose(out);
+        } else if (mode == "track") {
+            FILE* out = fopen(argv[7], "wb");
+            const float th = (float)atof(argv[6]);
+            ORBextractor ex(nf, 1.2f, 8, 20, 7, w, h);
+            Frame Last, Cur;
+            Last.mpORBextractorLeft = Cur.mpORBextractorLeft = &ex;
+            Frame::mnMinX = 0; Frame::mnMaxX = (float)w; Frame::mnMinY = 0; Frame::mnMaxY = (float)h;
+            Last.ExtractORB(0, im0);
+            Cur.ExtractORB(0, im1);
+            for (Frame* F : {&Last, &Cur}) {
+                F->mvKeysUn = F->mvKeys;
+                F->N = (int)F->mvKeys.size();
+                F->fx = F->fy = 500.f; F->cx = 0.5f * w; F->cy = 0.5f * h;
+                F->mbf = 40.f; F->mb = 0.08f;
+                F->mvScaleFactors = ex.GetScaleFactors();
+                F->mvpMapPoints.assign(F->N, nullptr);
+                F->mvbOutlier.assign(F->N, false);
+                F->mTcw = cv::Mat(4, 4, CV_32F);
+                for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) F->mTcw.at<float>(r, c) = r == c ? 1.f : 0.f;
+            }
+            // current pose: a small rotation about y and a translation (fixed constants, no libm involved)
+            const float Rc[9] = {0.9998f, 0.f, 0.02f, 0.f, 1.f, 0.f, -0.02f, 0.f, 0.9998f}, tc[3] = {0.01f, -0.005f, 0.02f};
+            for (int r = 0; r < 3; ++r) {
+                for (int c = 0; c < 3; ++c) Cur.mTcw.at<float>(r, c) = Rc[3 * r + c];
+                Cur.mTcw.at<float>(r, 3) = tc[r];
+            }
+            std::vector<MapPoint> points(Last.N);
+            for (int i = 0; i < Last.N; ++i) {
+                if (i % 5 == 0) continue;  // no map point
+                MapPoint& P = points[i];
+                const float z = 2.f + (float)(i % 17);
+                P.mWorldPos = cv::Mat(3, 1, CV_32F);
+                P.mWorldPos.at<float>(0, 0) = (Last.mvKeys[i].pt.x - Last.cx) * z / Last.fx;
+                P.mWorldPos.at<float>(1, 0) = (Last.mvKeys[i].pt.y - Last.cy) * z / Last.fy;
+                P.mWorldPos.at<float>(2, 0) = z;
+                P.mDescriptor = Last.mDescriptors.row(i);
+                P.nObs = i % 7 != 0 ? 2 : 0;
+                Last.mvpMapPoints[i] = &P;
+                Last.mvbOutlier[i] = i % 11 == 0;
+            }
+            ORBmatcher matcher(0.9f, true);
+            const int n = matcher.SearchByProjection(Cur, Last, th, true);
+            put_keys(out, Last.mvKeys, Last.mDescriptors);
+            put_keys(out, Cur.mvKeys, Cur.mDescriptors);
+            put_i(out, n);
+            for (int j = 0; j < Cur.N; ++j) put_i(out, Cur.mvpMapPoints[j] ? (int)(Cur.mvpMapPoints[j] - points.data()) : -1);
             fclose(out);
         } else {
             return 2;

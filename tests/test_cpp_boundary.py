@@ -120,3 +120,42 @@ def test_stereo_frame(harness, tmp_path):
     u, z = rd.arr(np.float32, len(kL)), rd.arr(np.float32, len(kL))
     assert (u_ref >= 0).sum() > 100
     assert np.array_equal(u.view(np.uint32), u_ref.view(np.uint32)) and np.array_equal(z.view(np.uint32), z_ref.view(np.uint32))
+
+
+@pytest.mark.gpu
+def test_track_with_motion_model_projection(harness, tmp_path):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) through the C++ template of include/ORBmatcher.h, with
+    a Frame / MapPoint pair shaped like the reference's (tests/cpp/frame_harness.cpp, mode `track`)."""
+    kind, nf, th = "tum", 1000, 15.0
+    a, b = synth.frame(kind, 41), synth.shifted_frame(kind, 41)
+    h, w = a.shape
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(a.tobytes() + b.tobytes())
+    out = tmp_path / "out.bin"
+    r = subprocess.run([harness, "track", str(raw), str(w), str(h), str(nf), repr(th), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    rd = Reader(out.read_bytes())
+    k1, d1 = rd.keys()
+    k2, d2 = rd.keys()
+    n1, n2 = len(k1), len(k2)
+    f32 = np.float32
+    fx = fy = f32(500.0)
+    cx, cy = f32(0.5) * f32(w), f32(0.5) * f32(h)
+    i = np.arange(n1)
+    z = (f32(2.0) + (i % 17).astype(f32)).astype(f32)
+    X0 = ((k1["x"] - cx) * z / fx).astype(f32)
+    X1 = ((k1["y"] - cy) * z / fy).astype(f32)
+    R = np.array([0.9998, 0, 0.02, 0, 1, 0, -0.02, 0, 0.9998], f32)
+    t = np.array([0.01, -0.005, 0.02], f32)
+    x3 = np.stack([((R[3 * r] * X0 + R[3 * r + 1] * X1).astype(f32) + R[3 * r + 2] * z).astype(f32) + t[r] for r in range(3)], axis=1).astype(f32)
+    has_mp = i % 5 != 0
+    valid1 = (has_mp & (i % 11 != 0)).astype(np.uint8)
+    obs1 = (i % 7 != 0).astype(np.uint8)
+    sf = O.Extractor(nf, 1.2, 8, 20, 7).tables()["scale"]
+    n_ref, m_ref = O.search_by_projection_frame(x3, valid1, obs1, d1, k1["octave"], k1["angle"], k2, d2, None, np.zeros(n2, np.uint8),
+                                                (fx, fy, cx, cy), 40.0, (0.0, float(w), 0.0, float(h)), sf, th, 0, True)
+    assert n_ref > 50
+    assert rd.i32() == n_ref
+    got = rd.arr(np.int32, n2)
+    expect = np.where(m_ref >= 0, m_ref, -1)  # the frame started without map points: NULL-ed and untouched both read as none
+    assert np.array_equal(got, expect)

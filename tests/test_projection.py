@@ -1,0 +1,149 @@
+"""SearchByProjection(CurrentFrame, LastFrame, th, bMono) — reference src/ORBmatcher.cc:1328-1470.
+CPU: known-answer cases that pin the oracle's reading of the reference loop.  GPU: the CUDA path through the C ABI against
+the oracle on keypoints / descriptors of real extractions, bit-exact (integer assignment + match count)."""
+import numpy as np
+import pytest
+
+from oracle import oracle_lib as O
+
+BOUNDS = (0.0, 640.0, 0.0, 480.0)
+CAM = (500.0, 500.0, 320.0, 240.0)
+SF = np.float32(1.2) ** np.arange(8, dtype=np.float32)
+
+
+def kp(x, y, octave=0, angle=0.0):
+    return (x, y, 31.0, angle, 50.0, octave, -1)
+
+
+def point_at(u, v, z=4.0):
+    return ((u - CAM[2]) * z / CAM[0], (v - CAM[3]) * z / CAM[1], z)
+
+
+def test_oracle_kat_competition_and_observations():
+    """Two last-frame points project next to the same current keypoint.  With observations the first one to be processed
+    keeps it and the second falls back to its second-best candidate; a point without observations (a temporal stereo point)
+    does not block the keypoint, so the later iteration overwrites the assignment and nmatches counts both events."""
+    k2 = np.array([kp(100, 100), kp(103, 100), kp(300, 300)], dtype=O.KP_DTYPE)
+    d2 = np.zeros((3, 32), np.uint8)
+    d2[1, 0] = 0x0F          # 4 bits away from the zero descriptor
+    d2[2] = 0xFF
+    x3 = np.array([point_at(101, 100), point_at(101.5, 100)], np.float32)
+    mp = np.zeros((2, 32), np.uint8)
+    one, zero = np.ones(2, np.uint8), np.zeros(2, np.uint8)
+    args = dict(octave1=[0, 0], angle1=[0, 0], k2=k2, d2=d2, u_right2=None, occupied2=np.zeros(3, np.uint8), cam=CAM, mbf=40.0,
+                bounds=BOUNDS, scale_factors=SF, th=7.0, direction=0, check_ori=False)
+    n, m21 = O.search_by_projection_frame(x3, one, one, mp, **args)
+    assert n == 2 and list(m21) == [0, 1, -1]
+    n, m21 = O.search_by_projection_frame(x3, one, zero, mp, **args)
+    assert n == 2 and list(m21) == [1, -1, -1]
+    # behind the camera / outside the image / invalid points are skipped
+    x3b = np.array([(0, 0, -1.0), point_at(-50, 100)], np.float32)
+    n, m21 = O.search_by_projection_frame(x3b, one, one, mp, **args)
+    assert n == 0 and list(m21) == [-1, -1, -1]
+    n, m21 = O.search_by_projection_frame(x3, zero, one, mp, **args)
+    assert n == 0
+    # occupied keypoints are never candidates; TH_HIGH = 100 bounds the distance
+    occ = np.array([1, 0, 0], np.uint8)
+    n, m21 = O.search_by_projection_frame(x3[:1], one[:1], one[:1], mp[:1], **{**args, "occupied2": occ, "octave1": [0], "angle1": [0]})
+    assert n == 1 and list(m21) == [-1, 0, -1]
+    far = np.full((1, 32), 0xFF, np.uint8)
+    n, m21 = O.search_by_projection_frame(x3[:1], one[:1], one[:1], far, **{**args, "octave1": [0], "angle1": [0]})
+    assert n == 0
+
+
+def test_oracle_kat_levels_stereo_and_rotation():
+    k2 = np.array([kp(200, 200, 0), kp(201, 200, 2), kp(202, 200, 4)], dtype=O.KP_DTYPE)
+    d2 = np.zeros((3, 32), np.uint8)
+    d2[0, 0], d2[1, 0], d2[2, 0] = 1, 3, 7
+    x3 = np.array([point_at(200, 200)], np.float32)
+    one = np.ones(1, np.uint8)
+    args = dict(angle1=[0], k2=k2, d2=d2, u_right2=None, occupied2=np.zeros(3, np.uint8), cam=CAM, mbf=40.0, bounds=BOUNDS,
+                scale_factors=SF, th=15.0, check_ori=False)
+    mp = np.zeros((1, 32), np.uint8)
+    # octave 2: +-1 levels -> only keypoint 1; forward (>= 2) -> 1 (closer than 2); backward (0..2) -> 0
+    assert list(O.search_by_projection_frame(x3, one, one, mp, octave1=[2], direction=0, **args)[1]) == [-1, 0, -1]
+    assert list(O.search_by_projection_frame(x3, one, one, mp, octave1=[2], direction=1, **args)[1]) == [-1, 0, -1]
+    assert list(O.search_by_projection_frame(x3, one, one, mp, octave1=[2], direction=2, **args)[1]) == [0, -1, -1]
+    # stereo: a right coordinate further than the radius from u - mbf/z rejects the candidate (mvuRight <= 0: no check)
+    ur_pred = 200.0 - 40.0 / 4.0
+    ur = np.array([ur_pred + 100.0, -1.0, -1.0], np.float32)
+    a2 = {**args, "u_right2": ur}
+    assert list(O.search_by_projection_frame(x3, one, one, mp, octave1=[1], direction=2, **a2)[1]) == [-1, -1, -1]
+    ur[0] = ur_pred + 1.0
+    assert list(O.search_by_projection_frame(x3, one, one, mp, octave1=[1], direction=2, **a2)[1]) == [0, -1, -1]
+    # rotation histogram: 12 matches rotate by ~0 degrees, one by 90: the odd one is set to NULL (-2) and not counted
+    n2 = 13
+    k2 = np.array([kp(50 + 30 * i, 100, 0, 90.0 if i == 12 else 0.0) for i in range(n2)], dtype=O.KP_DTYPE)
+    x3 = np.array([point_at(50 + 30 * i, 100) for i in range(n2)], np.float32)
+    ones = np.ones(n2, np.uint8)
+    n, m21 = O.search_by_projection_frame(x3, ones, ones, np.zeros((n2, 32), np.uint8), octave1=[0] * n2, angle1=[0.0] * n2, k2=k2,
+                                          d2=np.zeros((n2, 32), np.uint8), u_right2=None, occupied2=np.zeros(n2, np.uint8), cam=CAM,
+                                          mbf=40.0, bounds=BOUNDS, scale_factors=SF, th=7.0, direction=0, check_ori=True)
+    assert n == 12 and list(m21) == list(range(12)) + [-2]
+
+
+def scenario(seed, stereo, kind="tum"):
+    """Last frame = an extraction; current frame = the same image shifted by a few pixels (so true correspondences exist);
+    map points = last-frame keypoints back-projected at random depths and moved into the current camera frame."""
+    from orb_slam_cuda_b200 import synth
+    rng = np.random.default_rng(seed)
+    img = synth.frame(kind, seed)
+    sx, sy = int(rng.integers(2, 7)), int(rng.integers(-4, 5))
+    cur = np.roll(np.roll(img, sy, axis=0), sx, axis=1)
+    ox = O.Extractor(1000, 1.2, 8, 20, 7)
+    k1, d1 = ox.extract(img)
+    k1, d1 = k1.copy(), d1.copy()
+    k2, d2 = ox.extract(cur)
+    k2, d2 = k2.copy(), d2.copy()
+    h, w = img.shape
+    cam = (517.3, 516.5, 318.6, 255.3)
+    n1, n2 = k1.size, k2.size
+    z = rng.uniform(1.5, 20.0, n1).astype(np.float32)
+    z[rng.random(n1) < 0.03] *= -1  # some points behind the camera
+    u = k1["x"] + sx + rng.normal(0, 1.5, n1).astype(np.float32)
+    v = k1["y"] + sy + rng.normal(0, 1.5, n1).astype(np.float32)
+    x3 = np.stack([(u - cam[2]) * z / cam[0], (v - cam[3]) * z / cam[1], z], axis=1).astype(np.float32)
+    mp = d1.copy()
+    flips = rng.integers(0, 256, size=mp.shape, dtype=np.uint8) & rng.integers(0, 256, size=mp.shape, dtype=np.uint8) & \
+        rng.integers(0, 256, size=mp.shape, dtype=np.uint8) & rng.integers(0, 256, size=mp.shape, dtype=np.uint8)
+    mp ^= flips  # ~16 flipped bits per descriptor
+    valid1 = (rng.random(n1) < 0.8).astype(np.uint8)
+    obs1 = (rng.random(n1) < 0.85).astype(np.uint8)
+    occupied2 = (rng.random(n2) < 0.1).astype(np.uint8)
+    mbf = 40.0
+    ur = None
+    if stereo:
+        ur = np.where(rng.random(n2) < 0.6, k2["x"] - mbf / rng.uniform(1.5, 20.0, n2), -1.0).astype(np.float32)
+    return dict(x3Dc=x3, valid1=valid1, obs1=obs1, mp_desc1=mp, octave1=k1["octave"], angle1=k1["angle"], k2=k2, d2=d2,
+                u_right2=ur, occupied2=occupied2, cam=cam, mbf=mbf, bounds=(0.0, float(w), 0.0, float(h)),
+                scale_factors=ox.tables()["scale"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,stereo,th,direction,ori", [(1, False, 15.0, 0, True), (2, False, 7.0, 0, True), (3, True, 7.0, 1, True),
+                                                          (4, True, 7.0, 2, True), (5, True, 15.0, 0, False), (6, False, 30.0, 0, True)])
+def test_search_by_projection_gpu(seed, stereo, th, direction, ori):
+    import orb_slam_cuda_b200 as X
+    s = scenario(seed, stereo)
+    n_ref, m_ref = O.search_by_projection_frame(s["x3Dc"], s["valid1"], s["obs1"], s["mp_desc1"], s["octave1"], s["angle1"], s["k2"],
+                                                s["d2"], s["u_right2"], s["occupied2"], s["cam"], s["mbf"], s["bounds"],
+                                                s["scale_factors"], th, direction, ori)
+    m = X.ORBmatcher(0.9, ori)
+    n, m21 = m.SearchByProjection(s["x3Dc"], s["valid1"], s["obs1"], s["mp_desc1"], s["octave1"], s["angle1"], s["k2"], s["d2"],
+                                  s["u_right2"], s["occupied2"], s["cam"], s["mbf"], s["bounds"], s["scale_factors"], th, direction)
+    assert n_ref > 50, "the scenario must produce matches"
+    assert n == n_ref
+    assert np.array_equal(m21, m_ref)
+
+
+@pytest.mark.gpu
+def test_search_by_projection_empty_and_errors():
+    import orb_slam_cuda_b200 as X
+    m = X.ORBmatcher(0.9, True)
+    k2 = np.array([kp(100, 100)], dtype=X.KP_DTYPE)
+    n, m21 = m.SearchByProjection(np.zeros((0, 3), np.float32), [], [], np.zeros((0, 32), np.uint8), [], [], k2,
+                                  np.zeros((1, 32), np.uint8), None, [0], CAM, 40.0, BOUNDS, SF, 7.0)
+    assert n == 0 and list(m21) == [-1]
+    with pytest.raises(Exception):
+        m.SearchByProjection(np.zeros((1, 3), np.float32), [1], [1], np.zeros((1, 32), np.uint8), [9], [0.0], k2,
+                             np.zeros((1, 32), np.uint8), None, [0], CAM, 40.0, BOUNDS, SF, 7.0)
