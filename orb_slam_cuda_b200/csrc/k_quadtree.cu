@@ -253,13 +253,27 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
             __syncthreads();
             // processing order: descending (count, creation order); creation order = P-1-position
             int E = 0;
+            const bool packed = candCap < (1 << 18) && P <= 8192;  // (count, creation order) fits one positive 32-bit sort key
+            if (packed) {
+                for (int i = tid; i < P; i += blockDim.x) {
+                    const uint32_t ci = L[i].count;
+                    S.sA[i] = ci > 1 ? (int)((ci << 13) | (uint32_t)(8191 - i)) : 0;
+                }
+                __syncthreads();
+            }
             for (int i = tid; i < P; i += blockDim.x) {
                 const uint32_t ci = L[i].count;
                 if (ci > 1) {
                     int rank = 0;
-                    for (int j = 0; j < P; ++j) {
-                        const uint32_t cj = L[j].count;
-                        rank += (cj > 1 && (cj > ci || (cj == ci && j < i))) ? 1 : 0;
+                    if (packed) {
+                        const int ki = S.sA[i];
+#pragma unroll 4
+                        for (int j = 0; j < P; ++j) rank += S.sA[j] > ki ? 1 : 0;
+                    } else {
+                        for (int j = 0; j < P; ++j) {
+                            const uint32_t cj = L[j].count;
+                            rank += (cj > 1 && (cj > ci || (cj == ci && j < i))) ? 1 : 0;
+                        }
                     }
                     S.sC[rank] = i;
                 }
