@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     __shared__ uint32_t coefU[32 * 8], coefV[32 * 8];
     __shared__ __align__(16) uint32_t bpatch[DESC_WARPS][BP_ROWS * BP_WORDS + 2];
     __shared__ int sBefore[ORBX_MAX_LEVELS + 1];
+    __shared__ unsigned char sLevelOf[DESC_WARPS * DESC_PER_WARP];  // pyramid level of each of the CTA's slots
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         patF[i] = d_patF[i];
         coefU[i] = d_coefU[i];
@@ -134,6 +135,12 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, f = blockIdx.y;
     const int* cnt = lvlCnt + (long long)f * g.nlevels;
+    if (threadIdx.x >= 32 && threadIdx.x < 32 + DESC_WARPS * DESC_PER_WARP) {
+        const int slot = blockIdx.x * (DESC_WARPS * DESC_PER_WARP) + (threadIdx.x - 32);
+        int level = 0;
+        while (level + 1 < g.nlevels && slot >= g.lv[level + 1].slotBase) ++level;
+        sLevelOf[threadIdx.x - 32] = (unsigned char)level;
+    }
     if (threadIdx.x == 0) {  // exclusive prefix of the per-level counts = output position of each level's first keypoint
         int total = 0;
         for (int l = 0; l < g.nlevels; ++l) {
@@ -153,8 +160,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     for (int it = 0; it < DESC_PER_WARP; ++it) {
         const int slot = (blockIdx.x * DESC_PER_WARP + it) * DESC_WARPS + warp;
         if (slot >= g.slotsTotal) break;
-        int level = 0;
-        while (level + 1 < g.nlevels && slot >= g.lv[level + 1].slotBase) ++level;
+        const int level = sLevelOf[it * DESC_WARPS + warp];
         const LevelGeom& L = g.lv[level];
         const int j = slot - L.slotBase;
         const int before = sBefore[level];
