@@ -208,8 +208,52 @@ def latency_leg(X, wl, w, h, kind):
         ex1(imgs[i % 8])
         ts.append((time.perf_counter() - t0) * 1e3)
     ts = np.sort(np.array(ts))
-    return {"p50_ms": float(ts[len(ts) // 2]), "p95_ms": float(ts[int(len(ts) * 0.95)]), "calls": len(ts),
-            "path": "orbx_extract through the python binding, pageable host buffers"}
+    out = {"p50_ms": float(ts[len(ts) // 2]), "p95_ms": float(ts[int(len(ts) * 0.95)]), "calls": len(ts),
+           "path": "orbx_extract through the python binding, pageable host buffers"}
+
+    def p50(fn, n=100, warm=5):
+        for _ in range(warm):
+            fn()
+        t = []
+        for _ in range(n):
+            t0 = time.perf_counter()
+            fn()
+            t.append((time.perf_counter() - t0) * 1e3)
+        return float(np.sort(np.array(t))[n // 2])
+
+    # config 3: EuRoC-shaped stereo pair, 1200 features per eye, one extractor per eye on two host threads
+    # (src/Frame.cc:77-80), then ComputeStereoMatches on the device-resident pyramids
+    left, right = synth.stereo_pair("euroc", 9)
+    exL, exR = (X.ORBextractor(1200, SCALE, LEVELS, INI_TH, MIN_TH, 752, 480, max_batch=1) for _ in range(2))
+    res = {}
+
+    def eye(name, e, img):
+        res[name] = e(img)
+
+    def stereo_frame():
+        tl, tr = threading.Thread(target=eye, args=("L", exL, left)), threading.Thread(target=eye, args=("R", exR, right))
+        tl.start(); tr.start(); tl.join(); tr.join()
+        (kl, dl), (kr, dr) = res["L"], res["R"]
+        res["u"] = X.ComputeStereoMatches(exL, exR, kl, dl, kr, dr, 47.90639384423901, 435.2046959714599)
+
+    out["stereo_euroc"] = {"p50_ms": p50(stereo_frame), "what": "left + right extraction on two threads + ComputeStereoMatches, 752x480, 1200 features per eye"}
+    out["stereo_euroc"]["matched"] = int((res["u"][0] >= 0).sum())
+    # config 4: frame-to-frame matching of two 2000-feature KITTI frames: SearchForInitialization (window 100, ratio 0.9)
+    a, b = synth.frame("kitti", 40), synth.shifted_frame("kitti", 40)
+    ex2 = X.ORBextractor(2000, SCALE, LEVELS, INI_TH, MIN_TH, 1241, 376, max_batch=1)
+    (k1, d1), (k2, d2) = ex2(a), ex2(b)
+    k1, d1, k2, d2 = k1.copy(), d1.copy(), k2.copy(), d2.copy()
+    m = X.ORBmatcher(0.9, True)
+    bounds = (0.0, 1241.0, 0.0, 376.0)
+    sfi = {}
+
+    def run_sfi():
+        prev = np.stack([k1["x"], k1["y"]], 1).astype(np.float32)
+        sfi["n"], _ = m.SearchForInitialization(k1, d1, k2, d2, bounds, prev, 100)
+
+    out["search_for_initialization_2000x2000"] = {"p50_ms": p50(run_sfi), "matches": int(sfi["n"]),
+                                                   "what": "host buffers in and out, window 100, TH_LOW 50, ratio 0.9, rotation check"}
+    return out
 
 
 def run_reference(args, emit=print):
