@@ -159,6 +159,46 @@ public:
         return nmatches;
     }
 
+    // Search matches between Frame keypoints and projected MapPoints (Tracking::SearchLocalPoints, src/Tracking.cc:1270-1277);
+    // src/ORBmatcher.cc:45-129.  MapPoint members read: mbTrackInView, isBad(), mnTrackScaleLevel, mTrackViewCos, mTrackProjX,
+    // mTrackProjY, mTrackProjXR, GetDescriptor(), Observations().
+    template <class FrameT, class MapPointT>
+    int SearchByProjection(FrameT& F, const std::vector<MapPointT*>& vpMapPoints, const float th = 3) {
+        const int n1 = (int)vpMapPoints.size(), n2 = (int)F.mvKeysUn.size();
+        if (n1 == 0 || n2 == 0) return 0;
+        std::vector<float> proj(3 * (size_t)n1, 0.f), viewCos(n1, 0.f);
+        std::vector<int> level1(n1, 0);
+        std::vector<unsigned char> valid1(n1, 0), obs1(n1, 0), mpDesc((size_t)n1 * 32, 0), occupied2(n2, 0);
+        for (int i = 0; i < n1; ++i) {
+            MapPointT* pMP = vpMapPoints[i];
+            if (!pMP->mbTrackInView || pMP->isBad()) continue;
+            valid1[i] = 1;
+            obs1[i] = pMP->Observations() > 0;
+            proj[3 * i] = pMP->mTrackProjX;
+            proj[3 * i + 1] = pMP->mTrackProjY;
+            proj[3 * i + 2] = pMP->mTrackProjXR;
+            viewCos[i] = pMP->mTrackViewCos;
+            level1[i] = pMP->mnTrackScaleLevel;
+            const cv::Mat d = pMP->GetDescriptor();
+            std::memcpy(&mpDesc[(size_t)i * 32], d.template ptr<unsigned char>(), 32);
+        }
+        for (int j = 0; j < n2; ++j) occupied2[j] = F.mvpMapPoints[j] && F.mvpMapPoints[j]->Observations() > 0;
+        const cv::Mat d2 = continuous(F.mDescriptors);
+        const float bounds[4] = {(float)FrameT::mnMinX, (float)FrameT::mnMaxX, (float)FrameT::mnMinY, (float)FrameT::mnMaxY};
+        const bool hasRight = (int)F.mvuRight.size() == n2;
+        std::vector<int> match21(n2, -1);
+        int nmatches = 0;
+        check(orbx_search_by_projection_map(n1, proj.data(), viewCos.data(), level1.data(), valid1.data(), obs1.data(), mpDesc.data(),
+                                            reinterpret_cast<const orbx_keypoint*>(F.mvKeysUn.data()), n2,
+                                            d2.template ptr<unsigned char>(), hasRight ? F.mvuRight.data() : nullptr,
+                                            occupied2.data(), bounds, F.mvScaleFactors.data(), (int)F.mvScaleFactors.size(), th,
+                                            mfNNratio, match21.data(), &nmatches),
+              "SearchByProjection");
+        for (int j = 0; j < n2; ++j)
+            if (match21[j] >= 0) F.mvpMapPoints[j] = vpMapPoints[match21[j]];
+        return nmatches;
+    }
+
     static const int TH_LOW = 50;
     static const int TH_HIGH = 100;
     static const int HISTO_LENGTH = 30;

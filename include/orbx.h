@@ -161,6 +161,17 @@ int orbx_search_by_projection(int n1, const float* x3dc, const uint8_t* valid1, 
                               const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
                               int check_ori, int* match21, int* nmatches);
 
+/* SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:45-129, RadiusByViewingCos
+ * :131-137): the local-map matcher of Tracking::SearchLocalPoints (src/Tracking.cc:1270-1277).
+ *   valid1[i] = pMP->mbTrackInView && !pMP->isBad();  proj[3*i..] = mTrackProjX, mTrackProjY, mTrackProjXR;
+ *   view_cos = mTrackViewCos;  level1 = mnTrackScaleLevel;  obs1, mp_desc1, k2, desc2, u_right2, occupied2, bounds,
+ *   scale_factors as for orbx_search_by_projection;  nnratio = mfNNratio.
+ * match21[j] = i: F.mvpMapPoints[j] = vpMapPoints[i];  -1: untouched.  *nmatches = return value.  Host buffers. */
+int orbx_search_by_projection_map(int n1, const float* proj, const float* view_cos, const int* level1, const uint8_t* valid1,
+                                  const uint8_t* obs1, const uint8_t* mp_desc1, const orbx_keypoint* k2, int n2,
+                                  const uint8_t* desc2, const float* u_right2, const uint8_t* occupied2, const float bounds[4],
+                                  const float* scale_factors, int nlevels, float th, float nnratio, int* match21, int* nmatches);
+
 /* Frame::ComputeStereoMatches (src/Frame.cc:465-639).  exL / exR hold the pyramids of the left / right frame of
  * their last orbx_extract call (device resident; nothing is copied to the host).  bf = mbf (baseline x fx),
  * mb = baseline in metres = mbf / fx (src/Frame.cc:113).  u_right[nL], depth[nL] as mvuRight / mvDepth

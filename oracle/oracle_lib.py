@@ -222,6 +222,24 @@ def search_by_projection_frame(x3Dc, valid1, obs1, mp_desc1, octave1, angle1, k2
     return n, m21[:k2.size]
 
 
+def search_by_projection_map(proj, view_cos, level1, valid1, obs1, mp_desc1, k2, d2, u_right2, occupied2, bounds, scale_factors,
+                             th, nnratio=0.8):
+    proj = np.ascontiguousarray(proj, dtype=np.float32)
+    view_cos = np.ascontiguousarray(view_cos, dtype=np.float32)
+    level1 = np.ascontiguousarray(level1, dtype=np.int32)
+    valid1, obs1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, obs1, occupied2))
+    mp_desc1, d2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (mp_desc1, d2))
+    k2 = np.ascontiguousarray(k2, dtype=KP_DTYPE)
+    ur = None if u_right2 is None else np.ascontiguousarray(u_right2, dtype=np.float32)
+    b = np.asarray(bounds, dtype=np.float32)
+    sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+    m21 = np.empty(max(k2.size, 1), np.int32)
+    n = lib().orc_search_by_projection_map(valid1.size, _p(proj), _p(view_cos), _p(level1), _p(valid1), _p(obs1), _p(mp_desc1),
+                                           _p(k2), k2.size, _p(d2), _p(ur) if ur is not None else None, _p(occupied2), _p(b),
+                                           _p(sf), C.c_float(th), C.c_float(nnratio), _p(m21))
+    return n, m21[:k2.size]
+
+
 def match_bruteforce(q, d, th=50, ratio=0.6):
     q = np.ascontiguousarray(q, dtype=np.uint8)
     d = np.ascontiguousarray(d, dtype=np.uint8)

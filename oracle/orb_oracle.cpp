@@ -754,6 +754,59 @@ int search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* valid1,
     return nmatches;
 }
 
+// ORBmatcher::SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) — src/ORBmatcher.cc:45-129 with
+// RadiusByViewingCos (:131-137); called by Tracking::SearchLocalPoints (src/Tracking.cc:1270-1277).
+//   valid1[i] = pMP->mbTrackInView && !pMP->isBad();  proj[3i..] = mTrackProjX, mTrackProjY, mTrackProjXR;
+//   viewCos = mTrackViewCos;  level1 = mnTrackScaleLevel;  obs1 / occupied2 / match21 as above (no rotation pass: never -2)
+int search_by_projection_map(int n1, const float* proj, const float* viewCos, const int* level1, const uint8_t* valid1,
+                             const uint8_t* obs1, const uint8_t* mpDesc1, const GridFrame& F, const uint8_t* desc2,
+                             const float* uRight2, const uint8_t* occupied2, const float* scaleFactors, float th, float nnratio,
+                             int* match21) {
+    const int TH_HIGH = 100;
+    int nmatches = 0;
+    const bool bFactor = th != 1.0;
+    std::vector<int> owner(F.n, -1);
+    std::vector<uint8_t> taken(F.n);
+    for (int i = 0; i < F.n; ++i) taken[i] = occupied2[i];
+    for (int iMP = 0; iMP < n1; iMP++) {
+        if (!valid1[iMP]) continue;
+        const int nPredictedLevel = level1[iMP];
+        float r = viewCos[iMP] > 0.998 ? 2.5f : 4.0f;  // RadiusByViewingCos
+        if (bFactor) r *= th;
+        const std::vector<size_t> vIndices = F.features_in_area(proj[3 * iMP], proj[3 * iMP + 1], r * scaleFactors[nPredictedLevel],
+                                                                nPredictedLevel - 1, nPredictedLevel);
+        if (vIndices.empty()) continue;
+        const uint8_t* MPdescriptor = mpDesc1 + (size_t)iMP * 32;
+        int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
+        for (size_t idx : vIndices) {
+            if (taken[idx]) continue;
+            if (uRight2 && uRight2[idx] > 0) {
+                const float er = std::fabs(proj[3 * iMP + 2] - uRight2[idx]);
+                if (er > r * scaleFactors[nPredictedLevel]) continue;
+            }
+            const int dist = descriptor_distance(MPdescriptor, desc2 + idx * 32);
+            if (dist < bestDist) {
+                bestDist2 = bestDist;
+                bestDist = dist;
+                bestLevel2 = bestLevel;
+                bestLevel = F.keys[idx].octave;
+                bestIdx = (int)idx;
+            } else if (dist < bestDist2) {
+                bestLevel2 = F.keys[idx].octave;
+                bestDist2 = dist;
+            }
+        }
+        if (bestDist <= TH_HIGH) {
+            if (bestLevel == bestLevel2 && bestDist > nnratio * bestDist2) continue;
+            owner[bestIdx] = iMP;
+            taken[bestIdx] = obs1[iMP];
+            nmatches++;
+        }
+    }
+    for (int i = 0; i < F.n; ++i) match21[i] = owner[i];
+    return nmatches;
+}
+
 // Brute-force best / second-best with the TH + ratio acceptance test.  There is no single reference function
 // (SURVEY.md §8a16); this follows the inner loop of ORBmatcher::SearchByBoW, src/ORBmatcher.cc:199-232:
 // bestDist1 = bestDist2 = 256, strict '<' updates, accept iff d1 <= th && (float)d1 < ratio*(float)d2.

@@ -93,6 +93,11 @@ int search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* valid1,
                                const float* uRight2, const uint8_t* occupied2, float fx, float fy, float cx, float cy, float mbf,
                                const float* scaleFactors, float th, int direction, bool checkOri, int* match21);
 
+int search_by_projection_map(int n1, const float* proj, const float* viewCos, const int* level1, const uint8_t* valid1,
+                             const uint8_t* obs1, const uint8_t* mpDesc1, const GridFrame& F, const uint8_t* desc2,
+                             const float* uRight2, const uint8_t* occupied2, const float* scaleFactors, float th, float nnratio,
+                             int* match21);
+
 void match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1,
                       int* d2, int* match);
 

@@ -101,6 +101,14 @@ int orc_search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* val
     return search_by_projection_frame(n1, x3Dc, valid1, obs1, mpDesc1, octave1, angle1, F2, desc2, uRight2, occupied2, cam[0],
                                       cam[1], cam[2], cam[3], mbf, scaleFactors, th, direction, checkOri != 0, match21);
 }
+int orc_search_by_projection_map(int n1, const float* proj, const float* viewCos, const int* level1, const uint8_t* valid1,
+                                 const uint8_t* obs1, const uint8_t* mpDesc1, const KeyPoint* k2, int n2, const uint8_t* desc2,
+                                 const float* uRight2, const uint8_t* occupied2, const float* bounds, const float* scaleFactors,
+                                 float th, float nnratio, int* match21) {
+    GridFrame F(k2, n2, bounds[0], bounds[1], bounds[2], bounds[3]);
+    return search_by_projection_map(n1, proj, viewCos, level1, valid1, obs1, mpDesc1, F, desc2, uRight2, occupied2, scaleFactors,
+                                    th, nnratio, match21);
+}
 void orc_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2, int* match) {
     match_bruteforce(q, nq, d, nd, th, ratio, idx, d1, d2, match);
 }

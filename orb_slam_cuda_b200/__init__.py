@@ -275,6 +275,28 @@ class ORBmatcher:
                                                int(self.mbCheckOrientation), _p(m21), C.byref(n)))
         return n.value, m21[:n2]
 
+    def SearchByProjectionMap(self, proj, view_cos, level1, valid1, obs1, mp_desc1, kps2, desc2, u_right2, occupied2, bounds,
+                              scale_factors, th: float):
+        """SearchByProjection(F, vpMapPoints, th), src/ORBmatcher.cc:45-129 (Tracking::SearchLocalPoints).
+        Returns (nmatches, match21)."""
+        proj = np.ascontiguousarray(proj, dtype=np.float32)
+        view_cos = np.ascontiguousarray(view_cos, dtype=np.float32)
+        level1 = np.ascontiguousarray(level1, dtype=np.int32)
+        valid1, obs1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, obs1, occupied2))
+        mp_desc1, desc2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (mp_desc1, desc2))
+        kps2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+        ur = None if u_right2 is None else np.ascontiguousarray(u_right2, dtype=np.float32)
+        b = np.asarray(bounds, dtype=np.float32)
+        sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+        n1, n2 = valid1.size, kps2.size
+        m21 = np.empty(max(n2, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_search_by_projection_map(n1, _p(proj), _p(view_cos), _p(level1), _p(valid1), _p(obs1), _p(mp_desc1),
+                                                   _p(kps2), n2, _p(desc2), _p(ur) if ur is not None else None, _p(occupied2),
+                                                   _p(b), _p(sf), sf.size, C.c_float(th), C.c_float(self.mfNNratio), _p(m21),
+                                                   C.byref(n)))
+        return n.value, m21[:n2]
+
     def match_bruteforce(self, q, d, th: int = TH_LOW):
         """best / second-best over the whole database (inner loop of SearchByBoW, src/ORBmatcher.cc:187-232):
         returns (idx, d1, d2, match) int32 [nq]."""

@@ -16,6 +16,8 @@
 //                              three maxima, the removal of the other bins and the vbPrevMatched update.
 // best = first candidate (visiting order) of minimal distance, second = second smallest distance of the multiset:
 // both are what the strict-'<' updates of :446-456 produce, and both are order independent given the skip set.
+#include <cstring>
+
 #include "orbx_internal.h"
 
 namespace orbx {
@@ -276,6 +278,8 @@ struct SbpParams {
     float minX, maxX, minY, maxY, invW, invH;
     int direction;  // 0: octave-1 .. octave+1, 1: bForward (>= octave), 2: bBackward (0 .. octave)   (:1381-1386)
     int hasRight;
+    int mapMode;    // 1: SearchByProjection(F, vpMapPoints, th) (:45-129): x3Dc holds (mTrackProjX, mTrackProjY, mTrackProjXR),
+                    //    radius = RadiusByViewingCos * th * scale, levels level-1 .. level, no image-bounds test
 };
 
 // One warp per last-frame keypoint i.  cand[i * candCap + k] = (dist << 16) | i2 in GetFeaturesInArea's visiting order.
@@ -283,7 +287,8 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
                                                          const uint4* __restrict__ mpDesc1, const int* __restrict__ octave1,
                                                          const orbx_keypoint* __restrict__ k2, const uint4* __restrict__ desc2,
                                                          const float* __restrict__ uRight2, const uint8_t* __restrict__ occupied2,
-                                                         const float* __restrict__ scaleFactors, const SbpParams P,
+                                                         const float* __restrict__ scaleFactors, const float* __restrict__ viewCos,
+                                                         const SbpParams P,
                                                          const int* __restrict__ sorted, const int* __restrict__ cellStart,
                                                          uint32_t* __restrict__ cand, int candCap, int* __restrict__ candCnt,
                                                          int* __restrict__ dStatus) {
@@ -292,16 +297,31 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
     if (i >= n1) return;
     int count = 0;
     if (valid1[i]) {
-        const float xc = x3Dc[3 * i], yc = x3Dc[3 * i + 1];
-        const float invzc = __double2float_rn(__ddiv_rn(1.0, (double)x3Dc[3 * i + 2]));  // const float invzc = 1.0/z  (:1367)
-        const float u = __fadd_rn(__fmul_rn(__fmul_rn(P.fx, xc), invzc), P.cx);             // fx*xc*invzc+cx        (:1372)
-        const float v = __fadd_rn(__fmul_rn(__fmul_rn(P.fy, yc), invzc), P.cy);
-        const bool inImage = !(invzc < 0.f) && !(u < P.minX || u > P.maxX) && !(v < P.minY || v > P.maxY);
+        float u, v, ur, r = 0.f;
+        bool inImage = true;
+        int minLevel, maxLevel;
+        const int oct = octave1[i];
+        if (P.mapMode) {
+            u = x3Dc[3 * i];
+            v = x3Dc[3 * i + 1];
+            ur = x3Dc[3 * i + 2];
+            r = (double)viewCos[i] > 0.998 ? 2.5f : 4.0f;                  // RadiusByViewingCos (:131-137)
+            if ((double)P.th != 1.0) r = __fmul_rn(r, P.th);               // bFactor (:49, :65-66)
+            r = __fmul_rn(r, scaleFactors[oct]);
+            minLevel = oct - 1;
+            maxLevel = oct;
+        } else {
+            const float xc = x3Dc[3 * i], yc = x3Dc[3 * i + 1];
+            const float invzc = __double2float_rn(__ddiv_rn(1.0, (double)x3Dc[3 * i + 2]));  // const float invzc = 1.0/z  (:1367)
+            u = __fadd_rn(__fmul_rn(__fmul_rn(P.fx, xc), invzc), P.cx);                       // fx*xc*invzc+cx        (:1372)
+            v = __fadd_rn(__fmul_rn(__fmul_rn(P.fy, yc), invzc), P.cy);
+            inImage = !(invzc < 0.f) && !(u < P.minX || u > P.maxX) && !(v < P.minY || v > P.maxY);
+            ur = __fsub_rn(u, __fmul_rn(P.mbf, invzc));
+            r = __fmul_rn(P.th, scaleFactors[oct]);
+            minLevel = P.direction == 1 ? oct : (P.direction == 2 ? 0 : oct - 1);
+            maxLevel = P.direction == 1 ? -1 : (P.direction == 2 ? oct : oct + 1);
+        }
         if (inImage) {
-            const int oct = octave1[i];
-            const float r = __fmul_rn(P.th, scaleFactors[oct]);
-            const int minLevel = P.direction == 1 ? oct : (P.direction == 2 ? 0 : oct - 1);
-            const int maxLevel = P.direction == 1 ? -1 : (P.direction == 2 ? oct : oct + 1);
             const bool checkLevels = minLevel > 0 || maxLevel >= 0;
             // GetFeaturesInArea(u, v, r, minLevel, maxLevel)  (src/Frame.cc:326-379)
             const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, P.minX), r), P.invW)));
@@ -310,7 +330,6 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
             const int cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, P.minY), r), P.invH)));
             if (cx0 < GRID_COLS && cx1 >= 0 && cy0 < GRID_ROWS && cy1 >= 0) {
                 const uint4 a0 = mpDesc1[2 * i], a1 = mpDesc1[2 * i + 1];
-                const float ur = __fsub_rn(u, __fmul_rn(P.mbf, invzc));
                 uint32_t* out = cand + (size_t)i * candCap;
                 for (int ix = cx0; ix <= cx1; ++ix) {
                     const int b = cellStart[ix * GRID_ROWS + cy0], e = cellStart[ix * GRID_ROWS + cy1 + 1];
@@ -442,6 +461,7 @@ int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1
     P.invH = (float)GRID_ROWS / (P.maxY - P.minY);
     P.direction = direction;
     P.hasRight = uRight2 != nullptr;
+    P.mapMode = 0;
     const size_t smem = (size_t)n2 * 4 + (size_t)n1 * 4 + (size_t)n2 + (size_t)n1 + 16;
     if (smem > 200 * 1024) {
         set_error("SearchByProjection: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
@@ -455,10 +475,98 @@ int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1
     k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
     count_launch();
     k_sbp_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(n1, x3Dc, valid1, reinterpret_cast<const uint4*>(mpDesc1), octave1, k2,
-                                                    reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, P,
+                                                    reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, nullptr, P,
                                                     sorted, cellStart, cand, candCap, candCnt, dStatus);
     count_launch();
     k_sbp_resolve<<<1, 32, smem, s>>>(n1, obs1, angle1, k2, n2, cand, candCap, candCnt, checkOri, match21, nmatches);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// SearchByProjection(F, vpMapPoints, th) (:45-129): one warp replays the loop; best / second-best with their octaves, ratio test
+// only when both lie on the same level (:113-117).  Dynamic shared memory: owner[n2] (int32), taken[n2] (uint8).
+__global__ void __launch_bounds__(32) k_sbpm_resolve(int n1, const uint8_t* __restrict__ obs1, const orbx_keypoint* __restrict__ k2,
+                                                      int n2, const uint32_t* __restrict__ cand, int candCap,
+                                                      const int* __restrict__ candCnt, float nnratio, int* __restrict__ match21,
+                                                      int* __restrict__ nmatchesOut) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    int* owner = reinterpret_cast<int*>(sm);
+    uint8_t* taken = reinterpret_cast<uint8_t*>(owner + n2);
+    const int lane = threadIdx.x;
+    for (int i = lane; i < n2; i += 32) { owner[i] = -1; taken[i] = 0; }
+    __syncwarp();
+    int nmatches = 0;
+    for (int i = 0; i < n1; ++i) {
+        const int cnt = candCnt[i];
+        if (cnt == 0) continue;
+        const uint32_t* c = cand + (size_t)i * candCap;
+        uint32_t b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;  // two smallest (dist << 16 | position) keys among the free candidates
+        for (int p = lane; p < cnt; p += 32) {
+            const uint32_t e = c[p];
+            if (taken[e & 0xFFFFu]) continue;
+            const uint32_t key = ((e >> 16) << 16) | (uint32_t)p;
+            if (key < b1) { b2 = b1; b1 = key; }
+            else if (key < b2) b2 = key;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const uint32_t o1 = __shfl_xor_sync(0xffffffffu, b1, o), o2 = __shfl_xor_sync(0xffffffffu, b2, o);
+            const uint32_t lo = min(b1, o1), hi = max(b1, o1);
+            b2 = min(hi, min(b2, o2));
+            b1 = lo;
+        }
+        if (b1 == 0xFFFFFFFFu) continue;
+        const int bestDist = (int)(b1 >> 16);
+        if (bestDist > 100) continue;  // TH_HIGH (:111)
+        const int bestIdx = (int)(c[b1 & 0xFFFFu] & 0xFFFFu);
+        if (b2 != 0xFFFFFFFFu) {       // without a second candidate bestLevel2 stays -1 and the ratio test is skipped
+            const int idx2 = (int)(c[b2 & 0xFFFFu] & 0xFFFFu);
+            if (k2[bestIdx].octave == k2[idx2].octave && (float)bestDist > __fmul_rn(nnratio, (float)(int)(b2 >> 16))) continue;
+        }
+        if (lane == 0) {
+            owner[bestIdx] = i;
+            taken[bestIdx] = obs1[i];
+        }
+        ++nmatches;
+        __syncwarp();
+    }
+    __syncwarp();
+    for (int i = lane; i < n2; i += 32) match21[i] = owner[i];
+    if (lane == 0) *nmatchesOut = nmatches;
+}
+
+int launch_search_by_projection_map(int n1, const float* proj, const float* viewCos, const int* level1, const uint8_t* valid1,
+                                    const uint8_t* obs1, const uint8_t* mpDesc1, const orbx_keypoint* k2, int n2,
+                                    const uint8_t* desc2, const float* uRight2, const uint8_t* occupied2, const float* scaleFactors,
+                                    const float bounds[4], float th, float nnratio, int* cellOf, int* sorted, int* cellStart,
+                                    uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches, int* dStatus,
+                                    cudaStream_t s) {
+    SbpParams P;
+    memset(&P, 0, sizeof P);
+    P.th = th;
+    P.minX = bounds[0]; P.maxX = bounds[1]; P.minY = bounds[2]; P.maxY = bounds[3];
+    P.invW = (float)GRID_COLS / (P.maxX - P.minX);
+    P.invH = (float)GRID_ROWS / (P.maxY - P.minY);
+    P.hasRight = uRight2 != nullptr;
+    P.mapMode = 1;
+    const size_t smem = (size_t)n2 * 4 + (size_t)n2 + 16;
+    if (smem > 200 * 1024) {
+        set_error("SearchByProjection: %d keypoints do not fit the resolve kernel's shared memory", n2);
+        return ORBX_E_INVALID;
+    }
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        ORBX_CUDA(cudaFuncSetAttribute(k_sbpm_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
+    count_launch();
+    k_sbp_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(n1, proj, valid1, reinterpret_cast<const uint4*>(mpDesc1), level1, k2,
+                                                    reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, viewCos,
+                                                    P, sorted, cellStart, cand, candCap, candCnt, dStatus);
+    count_launch();
+    k_sbpm_resolve<<<1, 32, smem, s>>>(n1, obs1, k2, n2, cand, candCap, candCnt, nnratio, match21, nmatches);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -22,6 +22,10 @@ using namespace ORB_SLAM2;
 struct MapPoint {  // the members of ORB_SLAM2::MapPoint that SearchByProjection reads (include/MapPoint.h)
     cv::Mat mWorldPos, mDescriptor;
     int nObs = 0;
+    bool mbTrackInView = false, mbBad = false;  // Tracking::SearchLocalPoints state (include/MapPoint.h:111-117)
+    float mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackViewCos = 0;
+    int mnTrackScaleLevel = 0;
+    bool isBad() const { return mbBad; }
     cv::Mat GetWorldPos() const { return mWorldPos; }
     cv::Mat GetDescriptor() const { return mDescriptor; }
     int Observations() const { return nObs; }
@@ -161,6 +165,25 @@ int main(int argc, char** argv) {
             put_keys(out, Last.mvKeys, Last.mDescriptors);
             put_keys(out, Cur.mvKeys, Cur.mDescriptors);
             put_i(out, n);
+            for (int j = 0; j < Cur.N; ++j) put_i(out, Cur.mvpMapPoints[j] ? (int)(Cur.mvpMapPoints[j] - points.data()) : -1);
+            // Tracking::SearchLocalPoints (:1270-1277): the same map points "in view" of the current frame at the position of
+            // their last-frame keypoint, searched with the local-map matcher on a frame without assignments
+            std::vector<MapPoint*> local;
+            for (int i = 0; i < Last.N; ++i) {
+                MapPoint& P = points[i];
+                P.mbTrackInView = i % 5 != 0 && i % 3 != 0;
+                P.mbBad = i % 13 == 0;
+                P.mTrackProjX = Last.mvKeys[i].pt.x + 7.f;   // synth.shifted_frame moves the image by (7, -4)
+                P.mTrackProjY = Last.mvKeys[i].pt.y - 4.f;
+                P.mTrackProjXR = P.mTrackProjX - 3.f;
+                P.mTrackViewCos = i % 2 ? 0.9995f : 0.9f;
+                P.mnTrackScaleLevel = Last.mvKeys[i].octave;
+                if (i % 5 != 0) local.push_back(&P);
+            }
+            Cur.mvpMapPoints.assign(Cur.N, nullptr);
+            ORBmatcher localMatcher(0.8f);
+            const int nl = localMatcher.SearchByProjection(Cur, local, 3.f);
+            put_i(out, nl);
             for (int j = 0; j < Cur.N; ++j) put_i(out, Cur.mvpMapPoints[j] ? (int)(Cur.mvpMapPoints[j] - points.data()) : -1);
             fclose(out);
         } else {

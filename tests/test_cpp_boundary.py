@@ -159,3 +159,15 @@ def test_track_with_motion_model_projection(harness, tmp_path):
     got = rd.arr(np.int32, n2)
     expect = np.where(m_ref >= 0, m_ref, -1)  # the frame started without map points: NULL-ed and untouched both read as none
     assert np.array_equal(got, expect)
+    # second half of the dump: the local-map matcher (src/ORBmatcher.cc:45-129) on the same two frames
+    keep = np.flatnonzero(has_mp)                       # vpMapPoints = every existing map point, in index order
+    ii = keep
+    proj = np.stack([k1["x"][ii] + f32(7.0), k1["y"][ii] - f32(4.0), k1["x"][ii] + f32(7.0) - f32(3.0)], axis=1).astype(f32)
+    view_cos = np.where(ii % 2 == 1, f32(0.9995), f32(0.9)).astype(f32)
+    valid = ((ii % 3 != 0) & (ii % 13 != 0)).astype(np.uint8)
+    n_ref2, m_ref2 = O.search_by_projection_map(proj, view_cos, k1["octave"][ii], valid, obs1[ii], d1[ii], k2, d2, None,
+                                                np.zeros(n2, np.uint8), (0.0, float(w), 0.0, float(h)), sf, 3.0, 0.8)
+    assert n_ref2 > 50
+    assert rd.i32() == n_ref2
+    got2 = rd.arr(np.int32, n2)
+    assert np.array_equal(got2, np.where(m_ref2 >= 0, keep[np.maximum(m_ref2, 0)], -1))

@@ -147,3 +147,68 @@ def test_search_by_projection_empty_and_errors():
     with pytest.raises(Exception):
         m.SearchByProjection(np.zeros((1, 3), np.float32), [1], [1], np.zeros((1, 32), np.uint8), [9], [0.0], k2,
                              np.zeros((1, 32), np.uint8), None, [0], CAM, 40.0, BOUNDS, SF, 7.0)
+
+
+# ---- SearchByProjection(F, vpMapPoints, th) — src/ORBmatcher.cc:45-129 (Tracking::SearchLocalPoints) -----------------------
+
+def test_oracle_kat_map_projection():
+    """Radius 2.5 / 4.0 by viewing cosine times th times the level's scale; levels level-1 .. level; ratio test only when best
+    and second-best lie on the same level; the stereo coordinate gate; occupied keypoints."""
+    k2 = np.array([kp(100, 100, 1), kp(103, 100, 1), kp(103.5, 100, 0), kp(300, 300, 1)], dtype=O.KP_DTYPE)
+    d2 = np.zeros((4, 32), np.uint8)
+    d2[0, 0] = 0x03   # 2 bits
+    d2[1, 0] = 0x07   # 3 bits
+    d2[2, 0] = 0x0F   # 4 bits
+    base = dict(level1=[1], valid1=[1], obs1=[1], mp_desc1=np.zeros((1, 32), np.uint8), k2=k2, d2=d2, u_right2=None,
+                occupied2=np.zeros(4, np.uint8), bounds=BOUNDS, scale_factors=SF)
+    proj = np.array([[101.0, 100.0, 90.0]], np.float32)
+    # cos 0.999 -> r = 2.5 * 1.2 = 3.0: candidates 0 (dx 1), 1 (dx 2), 2 (dx 2.5).  best 2 bits, second 3 bits on the same level:
+    # 2 > 0.6 * 3 -> rejected by the ratio test; with ratio 0.8 accepted
+    assert O.search_by_projection_map(proj, [0.999], th=1.0, nnratio=0.6, **base)[0] == 0
+    n, m21 = O.search_by_projection_map(proj, [0.999], th=1.0, nnratio=0.8, **base)
+    assert n == 1 and list(m21) == [0, -1, -1, -1]
+    # second-best on another level: no ratio test.  Occupy keypoint 1 -> second = keypoint 2 (octave 0)
+    occ = np.array([0, 1, 0, 0], np.uint8)
+    n, m21 = O.search_by_projection_map(proj, [0.999], th=1.0, nnratio=0.1, **{**base, "occupied2": occ})
+    assert n == 1 and list(m21) == [0, -1, -1, -1]
+    # a narrow window (level 0 point, r = 2.5) does not reach keypoint 1 / 2 and level 0 admits octave 0 (and -1) only
+    n, m21 = O.search_by_projection_map(proj, [0.999], th=1.0, nnratio=0.8, **{**base, "level1": [0]})
+    assert n == 0
+    # stereo gate: |mTrackProjXR - mvuRight| > r rejects
+    ur = np.array([95.0, -1, -1, -1], np.float32)
+    n, m21 = O.search_by_projection_map(proj, [0.999], th=1.0, nnratio=0.9, **{**base, "u_right2": ur})
+    assert list(m21) == [-1, 0, -1, -1]
+    # th != 1 scales the radius; cos <= 0.998 -> 4.0
+    far = np.array([[105.9, 100.0, 90.0]], np.float32)
+    assert O.search_by_projection_map(far, [0.999], th=1.0, nnratio=0.9, **base)[0] == 1  # reaches keypoints 1, 2 only
+    assert list(O.search_by_projection_map(far, [0.5], th=1.0, nnratio=0.9, **base)[1]) == [-1, 0, -1, -1]
+    assert list(O.search_by_projection_map(far, [0.5], th=2.0, nnratio=0.9, **base)[1]) == [0, -1, -1, -1]
+
+
+def map_scenario(seed, stereo):
+    s = scenario(seed, stereo)
+    rng = np.random.default_rng(1000 + seed)
+    n1 = s["valid1"].size
+    cam, z = s["cam"], s["x3Dc"][:, 2]
+    u = (np.float32(cam[0]) * s["x3Dc"][:, 0] / z + np.float32(cam[2])).astype(np.float32)
+    v = (np.float32(cam[1]) * s["x3Dc"][:, 1] / z + np.float32(cam[3])).astype(np.float32)
+    proj = np.stack([u, v, (u - np.float32(s["mbf"]) / z).astype(np.float32)], axis=1).astype(np.float32)
+    view_cos = rng.uniform(0.99, 1.0, n1).astype(np.float32)
+    level = np.clip(s["octave1"] + rng.integers(0, 2, n1), 0, 7).astype(np.int32)
+    valid = (s["valid1"] & (z > 0)).astype(np.uint8)
+    return dict(proj=proj, view_cos=view_cos, level1=level, valid1=valid, obs1=s["obs1"], mp_desc1=s["mp_desc1"], k2=s["k2"],
+                d2=s["d2"], u_right2=s["u_right2"], occupied2=s["occupied2"], bounds=s["bounds"], scale_factors=s["scale_factors"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,stereo,th,ratio", [(1, False, 1.0, 0.8), (2, True, 3.0, 0.8), (3, False, 5.0, 0.6), (4, True, 1.0, 0.9)])
+def test_search_by_projection_map_gpu(seed, stereo, th, ratio):
+    import orb_slam_cuda_b200 as X
+    s = map_scenario(seed, stereo)
+    n_ref, m_ref = O.search_by_projection_map(th=th, nnratio=ratio, **s)
+    m = X.ORBmatcher(ratio, True)
+    n, m21 = m.SearchByProjectionMap(s["proj"], s["view_cos"], s["level1"], s["valid1"], s["obs1"], s["mp_desc1"], s["k2"], s["d2"],
+                                     s["u_right2"], s["occupied2"], s["bounds"], s["scale_factors"], th)
+    assert n_ref > 30, "the scenario must produce matches"
+    assert n == n_ref
+    assert np.array_equal(m21, m_ref)
