@@ -15,7 +15,9 @@
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
+#include <cmath>
 #include <cstring>
+#include <set>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -196,6 +198,74 @@ public:
               "SearchByProjection");
         for (int j = 0; j < n2; ++j)
             if (match21[j] >= 0) F.mvpMapPoints[j] = vpMapPoints[match21[j]];
+        return nmatches;
+    }
+
+    // Project MapPoints seen in KeyFrame into the Frame and search matches (relocalisation, src/Tracking.cc:1445,1484);
+    // src/ORBmatcher.cc:1472-1599.  KeyFrame members read: GetMapPointMatches(), mvKeysUn; MapPoint: isBad(), GetWorldPos(),
+    // GetMinDistanceInvariance(), GetMaxDistanceInvariance(), PredictScale(dist, &Frame), GetDescriptor().
+    template <class FrameT, class KeyFrameT, class MapPointT>
+    int SearchByProjection(FrameT& CurrentFrame, KeyFrameT* pKF, const std::set<MapPointT*>& sAlreadyFound, const float th,
+                           const int ORBdist) {
+        const std::vector<MapPointT*> vpMPs = pKF->GetMapPointMatches();
+        const int n1 = (int)vpMPs.size(), n2 = (int)CurrentFrame.mvKeysUn.size();
+        if (n1 == 0 || n2 == 0) return 0;
+#if ORBX_HAVE_OPENCV
+        const cv::Mat Rcw = CurrentFrame.mTcw.rowRange(0, 3).colRange(0, 3), tcw = CurrentFrame.mTcw.rowRange(0, 3).col(3);
+        const cv::Mat Ow = -Rcw.t() * tcw;
+#else
+        float R[9], t[3], Ow[3];
+        for (int r = 0; r < 3; ++r) {
+            for (int c = 0; c < 3; ++c) R[3 * r + c] = CurrentFrame.mTcw.template at<float>(r, c);
+            t[r] = CurrentFrame.mTcw.template at<float>(r, 3);
+        }
+        for (int c = 0; c < 3; ++c) Ow[c] = -(R[c] * t[0] + R[3 + c] * t[1] + R[6 + c] * t[2]);
+#endif
+        std::vector<float> x3(3 * (size_t)n1, 0.f), angle1(n1, 0.f);
+        std::vector<unsigned char> valid1(n1, 0), obs1(n1, 1), mpDesc((size_t)n1 * 32, 0), occupied2(n2, 0);
+        std::vector<int> level1(n1, 0);
+        for (int i = 0; i < n1; ++i) {
+            MapPointT* pMP = vpMPs[i];
+            if (!pMP || pMP->isBad() || sAlreadyFound.count(pMP)) continue;
+            const cv::Mat x3Dw = pMP->GetWorldPos();
+#if ORBX_HAVE_OPENCV
+            const cv::Mat x3Dc = Rcw * x3Dw + tcw;  // :1494-1495
+            for (int c = 0; c < 3; ++c) x3[3 * i + c] = x3Dc.at<float>(c);
+            const cv::Mat PO = x3Dw - Ow;
+            const float dist3D = (float)cv::norm(PO);  // :1510-1511
+#else
+            double ss = 0;
+            for (int r = 0; r < 3; ++r) {
+                x3[3 * i + r] = R[3 * r] * x3Dw.template at<float>(0, 0) + R[3 * r + 1] * x3Dw.template at<float>(1, 0) +
+                                R[3 * r + 2] * x3Dw.template at<float>(2, 0) + t[r];
+                const float po = x3Dw.template at<float>(r, 0) - Ow[r];
+                ss += (double)po * po;
+            }
+            const float dist3D = (float)std::sqrt(ss);
+#endif
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;  // :1517-1518
+            valid1[i] = 1;
+            level1[i] = pMP->PredictScale(dist3D, &CurrentFrame);
+            const cv::Mat dMP = pMP->GetDescriptor();
+            std::memcpy(&mpDesc[(size_t)i * 32], dMP.template ptr<unsigned char>(), 32);
+            angle1[i] = pKF->mvKeysUn[i].angle;
+        }
+        for (int j = 0; j < n2; ++j) occupied2[j] = CurrentFrame.mvpMapPoints[j] != nullptr;  // :1540-1541
+        const cv::Mat d2 = continuous(CurrentFrame.mDescriptors);
+        const float cam[4] = {CurrentFrame.fx, CurrentFrame.fy, CurrentFrame.cx, CurrentFrame.cy};
+        const float bounds[4] = {(float)FrameT::mnMinX, (float)FrameT::mnMaxX, (float)FrameT::mnMinY, (float)FrameT::mnMaxY};
+        std::vector<int> match21(n2, -1);
+        int nmatches = 0;
+        check(orbx_search_by_projection_ex(n1, x3.data(), valid1.data(), obs1.data(), mpDesc.data(), level1.data(), angle1.data(),
+                                           reinterpret_cast<const orbx_keypoint*>(CurrentFrame.mvKeysUn.data()), n2,
+                                           d2.template ptr<unsigned char>(), nullptr, occupied2.data(), cam, CurrentFrame.mbf, bounds,
+                                           CurrentFrame.mvScaleFactors.data(), (int)CurrentFrame.mvScaleFactors.size(), th, 0,
+                                           mbCheckOrientation ? 1 : 0, ORBdist, ORBX_SBP_NO_DEPTH_TEST, match21.data(), &nmatches),
+              "SearchByProjection");
+        for (int j = 0; j < n2; ++j) {
+            if (match21[j] >= 0) CurrentFrame.mvpMapPoints[j] = vpMPs[match21[j]];
+            else if (match21[j] == -2) CurrentFrame.mvpMapPoints[j] = nullptr;
+        }
         return nmatches;
     }
 

@@ -161,6 +161,19 @@ int orbx_search_by_projection(int n1, const float* x3dc, const uint8_t* valid1, 
                               const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
                               int check_ori, int* match21, int* nmatches);
 
+/* Same kernels with the knobs of the relocalisation variant SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist)
+ * (src/ORBmatcher.cc:1472-1599, called at src/Tracking.cc:1445,1484): orb_dist replaces TH_HIGH (:1552); flag
+ * ORBX_SBP_NO_DEPTH_TEST drops the `invzc < 0` test that only the frame-to-frame routine has (:1369); there
+ *   valid1[i] = pMP && !pMP->isBad() && !sAlreadyFound.count(pMP) && minDistance <= dist3D <= maxDistance  (:1489-1521)
+ *   octave1[i] = pMP->PredictScale(dist3D, &CurrentFrame) (:1523);  angle1[i] = pKF->mvKeysUn[i].angle;  obs1[i] = 1 and
+ *   occupied2[j] = CurrentFrame.mvpMapPoints[j] != NULL (any assigned keypoint is skipped, :1540-1541);  direction = 0. */
+#define ORBX_SBP_NO_DEPTH_TEST 1
+int orbx_search_by_projection_ex(int n1, const float* x3dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mp_desc1,
+                                 const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
+                                 const float* u_right2, const uint8_t* occupied2, const float cam[4], float mbf,
+                                 const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
+                                 int check_ori, int orb_dist, int flags, int* match21, int* nmatches);
+
 /* SearchByProjection(Frame &F, const vector<MapPoint*> &vpMapPoints, th) (src/ORBmatcher.cc:45-129, RadiusByViewingCos
  * :131-137): the local-map matcher of Tracking::SearchLocalPoints (src/Tracking.cc:1270-1277).
  *   valid1[i] = pMP->mbTrackInView && !pMP->isBad();  proj[3*i..] = mTrackProjX, mTrackProjY, mTrackProjXR;

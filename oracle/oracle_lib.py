@@ -203,7 +203,7 @@ def search_for_initialization(k1, d1, k2, d2, bounds, prev_xy, window=100, nnrat
 
 
 def search_by_projection_frame(x3Dc, valid1, obs1, mp_desc1, octave1, angle1, k2, d2, u_right2, occupied2, cam, mbf, bounds,
-                               scale_factors, th, direction=0, check_ori=True):
+                               scale_factors, th, direction=0, check_ori=True, orb_dist=100, depth_test=True):
     x3Dc = np.ascontiguousarray(x3Dc, dtype=np.float32)
     valid1, obs1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, obs1, occupied2))
     mp_desc1, d2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (mp_desc1, d2))
@@ -218,7 +218,7 @@ def search_by_projection_frame(x3Dc, valid1, obs1, mp_desc1, octave1, angle1, k2
     n = lib().orc_search_by_projection_frame(valid1.size, _p(x3Dc), _p(valid1), _p(obs1), _p(mp_desc1), _p(octave1), _p(angle1),
                                              _p(k2), k2.size, _p(d2), _p(ur) if ur is not None else None, _p(occupied2),
                                              _p(cam), C.c_float(mbf), _p(b), _p(sf), C.c_float(th), int(direction),
-                                             int(check_ori), _p(m21))
+                                             int(check_ori), _p(m21), int(orb_dist), int(depth_test))
     return n, m21[:k2.size]
 
 

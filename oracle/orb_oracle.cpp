@@ -683,6 +683,8 @@ int search_for_initialization(const GridFrame& F1, const uint8_t* desc1, const G
 
 // ORBmatcher::SearchByProjection(Frame &CurrentFrame, const Frame &LastFrame, th, bMono) — src/ORBmatcher.cc:1328-1470
 // (TH_HIGH=100, HISTO_LENGTH=30 at :37-39).  The boundary is drawn after the pose arithmetic: x3Dc[i] = Rcw*x3Dw+tcw
+// The relocalisation variant SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) (:1472-1599) is the same loop
+// with orbDist in place of TH_HIGH, no depth-sign test, the predicted level as octave1 and every assigned keypoint taken.
 // (:1362-1363, cv::Mat expressions evaluated by the caller exactly as the reference does) and `direction` (0: octave +-1,
 // 1: bForward, 2: bBackward, :1348-1349) come in; everything from :1365 on is restated here.
 //   valid1[i]  = LastFrame.mvpMapPoints[i] && !LastFrame.mvbOutlier[i]       (:1353-1357)
@@ -694,8 +696,9 @@ int search_for_initialization(const GridFrame& F1, const uint8_t* desc1, const G
 int search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
                                const int* octave1, const float* angle1, const GridFrame& F2, const uint8_t* desc2,
                                const float* uRight2, const uint8_t* occupied2, float fx, float fy, float cx, float cy, float mbf,
-                               const float* scaleFactors, float th, int direction, bool checkOri, int* match21) {
-    const int HISTO_LENGTH = 30, TH_HIGH = 100;
+                               const float* scaleFactors, float th, int direction, bool checkOri, int* match21, int orbDist,
+                               bool depthTest) {
+    const int HISTO_LENGTH = 30, TH_HIGH = orbDist;  // 100 (:39) or the ORBdist argument of the relocalisation variant (:1552)
     int nmatches = 0;
     std::vector<int> rotHist[HISTO_LENGTH];
     const float factor = 1.0f / HISTO_LENGTH;
@@ -706,7 +709,7 @@ int search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* valid1,
         if (!valid1[i]) continue;
         const float xc = x3Dc[3 * i], yc = x3Dc[3 * i + 1];
         const float invzc = (float)(1.0 / x3Dc[3 * i + 2]);
-        if (invzc < 0) continue;
+        if (depthTest && invzc < 0) continue;  // frame-to-frame only (:1369); the relocalisation variant has no such test
         float u = fx * xc * invzc + cx;
         float v = fy * yc * invzc + cy;
         if (u < F2.minX || u > F2.maxX) continue;

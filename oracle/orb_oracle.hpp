@@ -91,7 +91,8 @@ int search_for_initialization(const GridFrame& F1, const uint8_t* desc1, const G
 int search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
                                const int* octave1, const float* angle1, const GridFrame& F2, const uint8_t* desc2,
                                const float* uRight2, const uint8_t* occupied2, float fx, float fy, float cx, float cy, float mbf,
-                               const float* scaleFactors, float th, int direction, bool checkOri, int* match21);
+                               const float* scaleFactors, float th, int direction, bool checkOri, int* match21, int orbDist = 100,
+                               bool depthTest = true);
 
 int search_by_projection_map(int n1, const float* proj, const float* viewCos, const int* level1, const uint8_t* valid1,
                              const uint8_t* obs1, const uint8_t* mpDesc1, const GridFrame& F, const uint8_t* desc2,

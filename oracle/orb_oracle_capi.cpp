@@ -96,10 +96,10 @@ int orc_search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* val
                                    const int* octave1, const float* angle1, const KeyPoint* k2, int n2, const uint8_t* desc2,
                                    const float* uRight2, const uint8_t* occupied2, const float* cam, float mbf,
                                    const float* bounds, const float* scaleFactors, float th, int direction, int checkOri,
-                                   int* match21) {
+                                   int* match21, int orbDist, int depthTest) {
     GridFrame F2(k2, n2, bounds[0], bounds[1], bounds[2], bounds[3]);
     return search_by_projection_frame(n1, x3Dc, valid1, obs1, mpDesc1, octave1, angle1, F2, desc2, uRight2, occupied2, cam[0],
-                                      cam[1], cam[2], cam[3], mbf, scaleFactors, th, direction, checkOri != 0, match21);
+                                      cam[1], cam[2], cam[3], mbf, scaleFactors, th, direction, checkOri != 0, match21, orbDist, depthTest != 0);
 }
 int orc_search_by_projection_map(int n1, const float* proj, const float* viewCos, const int* level1, const uint8_t* valid1,
                                  const uint8_t* obs1, const uint8_t* mpDesc1, const KeyPoint* k2, int n2, const uint8_t* desc2,

@@ -253,7 +253,7 @@ class ORBmatcher:
         return n.value, m12[:kps1.size]
 
     def SearchByProjection(self, x3Dc, valid1, obs1, mp_desc1, octave1, angle1, kps2, desc2, u_right2, occupied2, cam, mbf,
-                           bounds, scale_factors, th: float, direction: int = 0):
+                           bounds, scale_factors, th: float, direction: int = 0, orb_dist: int = TH_HIGH, depth_test: bool = True):
         """SearchByProjection(CurrentFrame, LastFrame, th, bMono), src/ORBmatcher.cc:1328-1470, with the boundary of
         include/orbx.h (camera-frame points in, assignment per current keypoint out).  Returns (nmatches, match21)."""
         x3Dc = np.ascontiguousarray(x3Dc, dtype=np.float32)
@@ -269,10 +269,11 @@ class ORBmatcher:
         n1, n2 = valid1.size, kps2.size
         m21 = np.empty(max(n2, 1), np.int32)
         n = C.c_int(0)
-        _check(lib().orbx_search_by_projection(n1, _p(x3Dc), _p(valid1), _p(obs1), _p(mp_desc1), _p(octave1), _p(angle1), _p(kps2),
-                                               n2, _p(desc2), _p(ur) if ur is not None else None, _p(occupied2), _p(cam),
-                                               C.c_float(mbf), _p(b), _p(sf), sf.size, C.c_float(th), int(direction),
-                                               int(self.mbCheckOrientation), _p(m21), C.byref(n)))
+        _check(lib().orbx_search_by_projection_ex(n1, _p(x3Dc), _p(valid1), _p(obs1), _p(mp_desc1), _p(octave1), _p(angle1), _p(kps2),
+                                                  n2, _p(desc2), _p(ur) if ur is not None else None, _p(occupied2), _p(cam),
+                                                  C.c_float(mbf), _p(b), _p(sf), sf.size, C.c_float(th), int(direction),
+                                                  int(self.mbCheckOrientation), int(orb_dist), 0 if depth_test else 1, _p(m21),
+                                                  C.byref(n)))
         return n.value, m21[:n2]
 
     def SearchByProjectionMap(self, proj, view_cos, level1, valid1, obs1, mp_desc1, kps2, desc2, u_right2, occupied2, bounds,

@@ -278,6 +278,8 @@ struct SbpParams {
     float minX, maxX, minY, maxY, invW, invH;
     int direction;  // 0: octave-1 .. octave+1, 1: bForward (>= octave), 2: bBackward (0 .. octave)   (:1381-1386)
     int hasRight;
+    int noDepthTest;  // relocalisation variant (:1472-1599): no `invzc < 0` test
+    int thDist;       // TH_HIGH (:1427) or the caller's ORBdist (:1552)
     int mapMode;    // 1: SearchByProjection(F, vpMapPoints, th) (:45-129): x3Dc holds (mTrackProjX, mTrackProjY, mTrackProjXR),
                     //    radius = RadiusByViewingCos * th * scale, levels level-1 .. level, no image-bounds test
 };
@@ -315,7 +317,7 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
             const float invzc = __double2float_rn(__ddiv_rn(1.0, (double)x3Dc[3 * i + 2]));  // const float invzc = 1.0/z  (:1367)
             u = __fadd_rn(__fmul_rn(__fmul_rn(P.fx, xc), invzc), P.cx);                       // fx*xc*invzc+cx        (:1372)
             v = __fadd_rn(__fmul_rn(__fmul_rn(P.fy, yc), invzc), P.cy);
-            inImage = !(invzc < 0.f) && !(u < P.minX || u > P.maxX) && !(v < P.minY || v > P.maxY);
+            inImage = (P.noDepthTest || !(invzc < 0.f)) && !(u < P.minX || u > P.maxX) && !(v < P.minY || v > P.maxY);
             ur = __fsub_rn(u, __fmul_rn(P.mbf, invzc));
             r = __fmul_rn(P.th, scaleFactors[oct]);
             minLevel = P.direction == 1 ? oct : (P.direction == 2 ? 0 : oct - 1);
@@ -375,8 +377,8 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
 __global__ void __launch_bounds__(32) k_sbp_resolve(int n1, const uint8_t* __restrict__ obs1, const float* __restrict__ angle1,
                                                      const orbx_keypoint* __restrict__ k2, int n2,
                                                      const uint32_t* __restrict__ cand, int candCap,
-                                                     const int* __restrict__ candCnt, int checkOri, int* __restrict__ match21,
-                                                     int* __restrict__ nmatchesOut) {
+                                                     const int* __restrict__ candCnt, int checkOri, int thDist,
+                                                     int* __restrict__ match21, int* __restrict__ nmatchesOut) {
     extern __shared__ __align__(16) uint8_t sm[];
     int* owner = reinterpret_cast<int*>(sm);
     int* evIdx = owner + n2;
@@ -401,7 +403,7 @@ __global__ void __launch_bounds__(32) k_sbp_resolve(int n1, const uint8_t* __res
         for (int o = 16; o > 0; o >>= 1) b1 = min(b1, __shfl_xor_sync(0xffffffffu, b1, o));
         if (b1 == 0xFFFFFFFFu) continue;
         const int bestDist = (int)(b1 >> 16);
-        if (bestDist > 100) continue;  // TH_HIGH (:1427)
+        if (bestDist > thDist) continue;  // TH_HIGH (:1427) / ORBdist (:1552)
         if (lane == 0) {
             const int bestIdx2 = (int)(c[b1 & 0xFFFFu] & 0xFFFFu);
             owner[bestIdx2] = i;
@@ -450,9 +452,9 @@ __global__ void __launch_bounds__(32) k_sbp_resolve(int n1, const uint8_t* __res
 int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
                                 const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
                                 const float* uRight2, const uint8_t* occupied2, const float* scaleFactors, const float cam[4],
-                                float mbf, const float bounds[4], float th, int direction, int checkOri, int* cellOf, int* sorted,
-                                int* cellStart, uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches,
-                                int* dStatus, cudaStream_t s) {
+                                float mbf, const float bounds[4], float th, int direction, int checkOri, int thDist,
+                                int noDepthTest, int* cellOf, int* sorted, int* cellStart, uint32_t* cand, int candCap,
+                                int* candCnt, int* match21, int* nmatches, int* dStatus, cudaStream_t s) {
     SbpParams P;
     P.fx = cam[0]; P.fy = cam[1]; P.cx = cam[2]; P.cy = cam[3];
     P.mbf = mbf; P.th = th;
@@ -462,6 +464,8 @@ int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1
     P.direction = direction;
     P.hasRight = uRight2 != nullptr;
     P.mapMode = 0;
+    P.thDist = thDist;
+    P.noDepthTest = noDepthTest;
     const size_t smem = (size_t)n2 * 4 + (size_t)n1 * 4 + (size_t)n2 + (size_t)n1 + 16;
     if (smem > 200 * 1024) {
         set_error("SearchByProjection: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
@@ -478,7 +482,7 @@ int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1
                                                     reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, nullptr, P,
                                                     sorted, cellStart, cand, candCap, candCnt, dStatus);
     count_launch();
-    k_sbp_resolve<<<1, 32, smem, s>>>(n1, obs1, angle1, k2, n2, cand, candCap, candCnt, checkOri, match21, nmatches);
+    k_sbp_resolve<<<1, 32, smem, s>>>(n1, obs1, angle1, k2, n2, cand, candCap, candCnt, checkOri, thDist, match21, nmatches);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -180,6 +180,16 @@ int orbx_search_by_projection(int n1, const float* x3dc, const uint8_t* valid1, 
                               const float* u_right2, const uint8_t* occupied2, const float cam[4], float mbf,
                               const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
                               int check_ori, int* match21, int* nmatches) {
+    return orbx_search_by_projection_ex(n1, x3dc, valid1, obs1, mp_desc1, octave1, angle1, k2, n2, desc2, u_right2, occupied2, cam, mbf,
+                                        bounds, scale_factors, nlevels, th, direction, check_ori, 100 /* TH_HIGH */, 0, match21,
+                                        nmatches);
+}
+
+int orbx_search_by_projection_ex(int n1, const float* x3dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mp_desc1,
+                                 const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
+                                 const float* u_right2, const uint8_t* occupied2, const float cam[4], float mbf,
+                                 const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
+                                 int check_ori, int orb_dist, int flags, int* match21, int* nmatches) {
     if (n1 < 0 || n2 < 0 || !bounds || !cam || !nmatches || !scale_factors || nlevels < 1 || nlevels > ORBX_MAX_LEVELS ||
         direction < 0 || direction > 2 || (n1 > 0 && (!x3dc || !valid1 || !obs1 || !mp_desc1 || !octave1 || !angle1)) ||
         (n2 > 0 && (!k2 || !desc2 || !occupied2 || !match21)) || n2 > 65535 || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) {
@@ -229,8 +239,8 @@ int orbx_search_by_projection(int n1, const float* x3dc, const uint8_t* valid1, 
                                           reinterpret_cast<const int*>(dp + oO), reinterpret_cast<const float*>(dp + oA),
                                           w->c.as<orbx_keypoint>(), n2, w->d.as<uint8_t>(),
                                           u_right2 ? reinterpret_cast<const float*>(dp + oU) : nullptr, dp + oC,
-                                          reinterpret_cast<const float*>(dp + oS), cam, mbf, bounds, th, direction, check_ori, cellOf,
-                                          sorted, cellStart, w->g.as<uint32_t>(), candCap, w->h.as<int>(), w->out0.as<int>(), dN,
+                                          reinterpret_cast<const float*>(dp + oS), cam, mbf, bounds, th, direction, check_ori, orb_dist,
+                                          flags & ORBX_SBP_NO_DEPTH_TEST ? 1 : 0, cellOf, sorted, cellStart, w->g.as<uint32_t>(), candCap, w->h.as<int>(), w->out0.as<int>(), dN,
                                           w->status.as<int>(), s)))
         return rc;
     int st[2] = {0, 0};

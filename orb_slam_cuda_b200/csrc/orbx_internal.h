@@ -204,9 +204,9 @@ int launch_search_for_initialization(const orbx_keypoint* k1, int n1, const uint
 int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
                                 const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
                                 const float* uRight2, const uint8_t* occupied2, const float* scaleFactors, const float cam[4],
-                                float mbf, const float bounds[4], float th, int direction, int checkOri, int* cellOf, int* sorted,
-                                int* cellStart, uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches,
-                                int* dStatus, cudaStream_t s);
+                                float mbf, const float bounds[4], float th, int direction, int checkOri, int thDist,
+                                int noDepthTest, int* cellOf, int* sorted, int* cellStart, uint32_t* cand, int candCap,
+                                int* candCnt, int* match21, int* nmatches, int* dStatus, cudaStream_t s);
 int launch_search_by_projection_map(int n1, const float* proj, const float* viewCos, const int* level1, const uint8_t* valid1,
                                     const uint8_t* obs1, const uint8_t* mpDesc1, const orbx_keypoint* k2, int n2,
                                     const uint8_t* desc2, const float* uRight2, const uint8_t* occupied2, const float* scaleFactors,

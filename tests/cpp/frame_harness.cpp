@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <set>
 #include <string>
 #include <thread>
 #include <vector>
@@ -26,9 +27,18 @@ struct MapPoint {  // the members of ORB_SLAM2::MapPoint that SearchByProjection
     float mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackViewCos = 0;
     int mnTrackScaleLevel = 0;
     bool isBad() const { return mbBad; }
+    float GetMinDistanceInvariance() const { return 3.5f; }
+    float GetMaxDistanceInvariance() const { return 15.5f; }
+    template <class F> int PredictScale(float, F*) const { return mnTrackScaleLevel; }
     cv::Mat GetWorldPos() const { return mWorldPos; }
     cv::Mat GetDescriptor() const { return mDescriptor; }
     int Observations() const { return nObs; }
+};
+
+struct KeyFrame {  // the members of ORB_SLAM2::KeyFrame that the relocalisation SearchByProjection reads (include/KeyFrame.h)
+    std::vector<MapPoint*> mvpMapPoints;
+    std::vector<cv::KeyPoint> mvKeysUn;
+    std::vector<MapPoint*> GetMapPointMatches() const { return mvpMapPoints; }
 };
 
 struct Frame {  // the members of ORB_SLAM2::Frame that the front end reads or writes (include/Frame.h)
@@ -184,6 +194,17 @@ int main(int argc, char** argv) {
             ORBmatcher localMatcher(0.8f);
             const int nl = localMatcher.SearchByProjection(Cur, local, 3.f);
             put_i(out, nl);
+            for (int j = 0; j < Cur.N; ++j) put_i(out, Cur.mvpMapPoints[j] ? (int)(Cur.mvpMapPoints[j] - points.data()) : -1);
+            // Tracking::Relocalization (:1445): the last frame as a keyframe, some points already found
+            KeyFrame KF;
+            KF.mvpMapPoints = Last.mvpMapPoints;
+            KF.mvKeysUn = Last.mvKeysUn;
+            std::set<MapPoint*> found;
+            for (int i = 0; i < Last.N; i += 9) if (Last.mvpMapPoints[i]) found.insert(Last.mvpMapPoints[i]);
+            Cur.mvpMapPoints.assign(Cur.N, nullptr);
+            for (int j = 0; j < Cur.N; j += 10) Cur.mvpMapPoints[j] = &points[0];  // keypoints that already hold a point
+            const int nr = matcher.SearchByProjection(Cur, &KF, found, 10.f, 100);
+            put_i(out, nr);
             for (int j = 0; j < Cur.N; ++j) put_i(out, Cur.mvpMapPoints[j] ? (int)(Cur.mvpMapPoints[j] - points.data()) : -1);
             fclose(out);
         } else {

@@ -171,3 +171,16 @@ def test_track_with_motion_model_projection(harness, tmp_path):
     assert rd.i32() == n_ref2
     got2 = rd.arr(np.int32, n2)
     assert np.array_equal(got2, np.where(m_ref2 >= 0, keep[np.maximum(m_ref2, 0)], -1))
+    # third part: the relocalisation variant (src/ORBmatcher.cc:1472-1599) with the last frame as the keyframe
+    Ow = np.array([-((R[c] * t[0] + R[3 + c] * t[1]).astype(f32) + R[6 + c] * t[2]).astype(f32) for c in range(3)], f32)
+    Xw = np.stack([X0, X1, z], axis=1).astype(f32)
+    PO = (Xw - Ow[None, :]).astype(f32)
+    dist3D = np.sqrt((PO.astype(np.float64) ** 2).sum(axis=1)).astype(f32)
+    valid3 = (has_mp & (i % 13 != 0) & (i % 9 != 0) & ~(dist3D < f32(3.5)) & ~(dist3D > f32(15.5))).astype(np.uint8)
+    occ3 = (np.arange(n2) % 10 == 0).astype(np.uint8)
+    n_ref3, m_ref3 = O.search_by_projection_frame(x3, valid3, np.ones(n1, np.uint8), d1, k1["octave"], k1["angle"], k2, d2, None, occ3,
+                                                  (fx, fy, cx, cy), 40.0, (0.0, float(w), 0.0, float(h)), sf, 10.0, 0, True, 100, False)
+    assert n_ref3 > 50
+    assert rd.i32() == n_ref3
+    got3 = rd.arr(np.int32, n2)
+    assert np.array_equal(got3, np.where(occ3 == 1, 0, np.where(m_ref3 >= 0, m_ref3, -1)))

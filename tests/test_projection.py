@@ -136,6 +136,37 @@ def test_search_by_projection_gpu(seed, stereo, th, direction, ori):
     assert np.array_equal(m21, m_ref)
 
 
+def test_oracle_kat_relocalisation_knobs():
+    """SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist), src/ORBmatcher.cc:1472-1599: ORBdist replaces TH_HIGH
+    and a point behind the camera is not rejected (only the frame-to-frame routine tests invzc < 0)."""
+    k2 = np.array([kp(100, 100)], dtype=O.KP_DTYPE)
+    d2 = np.zeros((1, 32), np.uint8)
+    d2[0, :9] = 0xFF  # 72 bits from the zero descriptor
+    args = dict(valid1=[1], obs1=[1], mp_desc1=np.zeros((1, 32), np.uint8), octave1=[0], angle1=[0], k2=k2, d2=d2, u_right2=None,
+                occupied2=[0], cam=CAM, mbf=40.0, bounds=BOUNDS, scale_factors=SF, th=10.0, direction=0, check_ori=False)
+    front = np.array([point_at(101, 100)], np.float32)
+    behind = (-front).astype(np.float32)  # same projection, negative depth
+    assert O.search_by_projection_frame(front, **args)[0] == 1
+    assert O.search_by_projection_frame(front, orb_dist=64, **args)[0] == 0
+    assert O.search_by_projection_frame(behind, **args)[0] == 0
+    assert O.search_by_projection_frame(behind, depth_test=False, **args)[0] == 1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,th,orb_dist", [(7, 10.0, 100), (8, 3.0, 64)])
+def test_search_by_projection_relocalisation_gpu(seed, th, orb_dist):
+    import orb_slam_cuda_b200 as X
+    s = scenario(seed, False)
+    ones = np.ones_like(s["obs1"])
+    a = (s["x3Dc"], s["valid1"], ones, s["mp_desc1"], s["octave1"], s["angle1"], s["k2"], s["d2"], None, s["occupied2"], s["cam"],
+         s["mbf"], s["bounds"], s["scale_factors"], th, 0)
+    n_ref, m_ref = O.search_by_projection_frame(*a, True, orb_dist, False)
+    n, m21 = X.ORBmatcher(0.9, True).SearchByProjection(*a, orb_dist=orb_dist, depth_test=False)
+    assert n_ref > 50 and n == n_ref and np.array_equal(m21, m_ref)
+    n_dt, _ = O.search_by_projection_frame(*a, True, orb_dist, True)
+    assert n_dt != n_ref or (s["x3Dc"][:, 2] > 0).all()  # the points behind the camera make a difference
+
+
 @pytest.mark.gpu
 def test_search_by_projection_empty_and_errors():
     import orb_slam_cuda_b200 as X
