@@ -269,6 +269,92 @@ public:
         return nmatches;
     }
 
+    // Project MapPoints using a Similarity Transformation and search matches (loop detection, src/LoopClosing.cc:278);
+    // src/ORBmatcher.cc:290-403.  KeyFrame members read: fx, fy, cx, cy, mvScaleFactors, mvKeysUn, mDescriptors, IsInImage(),
+    // mnMinX..mnMaxY; MapPoint: isBad(), GetWorldPos(), GetMin/MaxDistanceInvariance(), GetNormal(), PredictScale(), GetDescriptor().
+    template <class KeyFrameT, class MapPointT>
+    int SearchByProjection(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, std::vector<MapPointT*>& vpMatched,
+                           int th) {
+        const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
+        const int n1 = (int)vpPoints.size(), n2 = (int)pKF->mvKeysUn.size();
+        if (n1 == 0 || n2 == 0) return 0;
+#if ORBX_HAVE_OPENCV
+        cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+        const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+        cv::Mat Rcw = sRcw / scw;
+        cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+        cv::Mat Ow = -Rcw.t() * tcw;
+#else
+        float R[9], t[3], Ow[3];
+        double dd = 0;
+        for (int c = 0; c < 3; ++c) dd += (double)Scw.template at<float>(0, c) * Scw.template at<float>(0, c);
+        const float scw = (float)std::sqrt(dd);
+        for (int r = 0; r < 3; ++r) {
+            for (int c = 0; c < 3; ++c) R[3 * r + c] = Scw.template at<float>(r, c) / scw;
+            t[r] = Scw.template at<float>(r, 3) / scw;
+        }
+        for (int c = 0; c < 3; ++c) Ow[c] = -(R[c] * t[0] + R[3 + c] * t[1] + R[6 + c] * t[2]);
+#endif
+        std::set<MapPointT*> spAlreadyFound(vpMatched.begin(), vpMatched.end());
+        spAlreadyFound.erase(static_cast<MapPointT*>(nullptr));
+        std::vector<float> uvr(3 * (size_t)n1, 0.f);
+        std::vector<int> level1(n1, 0);
+        std::vector<unsigned char> valid1(n1, 0), mpDesc((size_t)n1 * 32, 0), occupied2(n2, 0);
+        for (int i = 0; i < n1; ++i) {
+            MapPointT* pMP = vpPoints[i];
+            if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
+            const cv::Mat p3Dw = pMP->GetWorldPos();
+            const cv::Mat Pn = pMP->GetNormal();
+            float pc[3], dist, podotpn;
+#if ORBX_HAVE_OPENCV
+            const cv::Mat p3Dc = Rcw * p3Dw + tcw;
+            for (int c = 0; c < 3; ++c) pc[c] = p3Dc.at<float>(c);
+            const cv::Mat PO = p3Dw - Ow;
+            dist = (float)cv::norm(PO);
+            podotpn = (float)PO.dot(Pn);
+#else
+            double ss = 0, dp = 0;
+            for (int r = 0; r < 3; ++r) {
+                pc[r] = R[3 * r] * p3Dw.template at<float>(0, 0) + R[3 * r + 1] * p3Dw.template at<float>(1, 0) +
+                        R[3 * r + 2] * p3Dw.template at<float>(2, 0) + t[r];
+                const float po = p3Dw.template at<float>(r, 0) - Ow[r];
+                ss += (double)po * po;
+                dp += (double)po * Pn.template at<float>(r, 0);
+            }
+            dist = (float)std::sqrt(ss);
+            podotpn = (float)dp;
+#endif
+            if (pc[2] < 0.0) continue;                   // depth must be positive (:333-334)
+            const float invz = 1 / pc[2];
+            const float x = pc[0] * invz, y = pc[1] * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!pKF->IsInImage(u, v)) continue;
+            if (dist < pMP->GetMinDistanceInvariance() || dist > pMP->GetMaxDistanceInvariance()) continue;
+            if (podotpn < 0.5 * dist) continue;          // viewing angle must be less than 60 deg (:358-359)
+            const int nPredictedLevel = pMP->PredictScale(dist, pKF);
+            valid1[i] = 1;
+            level1[i] = nPredictedLevel;
+            uvr[3 * i] = u;
+            uvr[3 * i + 1] = v;
+            uvr[3 * i + 2] = th * pKF->mvScaleFactors[nPredictedLevel];
+            const cv::Mat dMP = pMP->GetDescriptor();
+            std::memcpy(&mpDesc[(size_t)i * 32], dMP.template ptr<unsigned char>(), 32);
+        }
+        for (int j = 0; j < n2; ++j) occupied2[j] = vpMatched[j] != nullptr;
+        const cv::Mat d2 = continuous(pKF->mDescriptors);
+        const float bounds[4] = {(float)pKF->mnMinX, (float)pKF->mnMaxX, (float)pKF->mnMinY, (float)pKF->mnMaxY};
+        std::vector<int> match21(n2, -1);
+        int nmatches = 0;
+        check(orbx_search_by_projection_sim3(n1, uvr.data(), level1.data(), valid1.data(), mpDesc.data(),
+                                             reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()), n2,
+                                             d2.template ptr<unsigned char>(), occupied2.data(), bounds, TH_LOW, match21.data(),
+                                             &nmatches),
+              "SearchByProjection");
+        for (int j = 0; j < n2; ++j)
+            if (match21[j] >= 0) vpMatched[j] = vpPoints[match21[j]];
+        return nmatches;
+    }
+
     static const int TH_LOW = 50;
     static const int TH_HIGH = 100;
     static const int HISTO_LENGTH = 30;

@@ -185,6 +185,15 @@ int orbx_search_by_projection_map(int n1, const float* proj, const float* view_c
                                   const uint8_t* desc2, const float* u_right2, const uint8_t* occupied2, const float bounds[4],
                                   const float* scale_factors, int nlevels, float th, float nnratio, int* match21, int* nmatches);
 
+/* SearchByProjection(KeyFrame* pKF, cv::Mat Scw, vpPoints, vpMatched, th) (src/ORBmatcher.cc:290-403; loop detection,
+ * src/LoopClosing.cc:278) from the radius search on (:357-398); the Sim3 decomposition and the visibility tests (:298-355) stay
+ * the caller's.  uvr[3*i..] = u, v, th*pKF->mvScaleFactors[nPredictedLevel];  level1[i] = nPredictedLevel;  valid1[i] = the point
+ * passed every `continue` of :318-351;  k2, desc2 = pKF->mvKeysUn / mDescriptors;  occupied2[j] = vpMatched[j] != NULL;
+ * th_dist = TH_LOW.  match21[j] = i: vpMatched[j] = vpPoints[i];  -1: untouched.  Host buffers. */
+int orbx_search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* mp_desc1,
+                                   const orbx_keypoint* k2, int n2, const uint8_t* desc2, const uint8_t* occupied2,
+                                   const float bounds[4], int th_dist, int* match21, int* nmatches);
+
 /* Frame::ComputeStereoMatches (src/Frame.cc:465-639).  exL / exR hold the pyramids of the left / right frame of
  * their last orbx_extract call (device resident; nothing is copied to the host).  bf = mbf (baseline x fx),
  * mb = baseline in metres = mbf / fx (src/Frame.cc:113).  u_right[nL], depth[nL] as mvuRight / mvDepth

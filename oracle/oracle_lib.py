@@ -240,6 +240,19 @@ def search_by_projection_map(proj, view_cos, level1, valid1, obs1, mp_desc1, k2,
     return n, m21[:k2.size]
 
 
+def search_by_projection_sim3(uvr, level1, valid1, mp_desc1, k2, d2, occupied2, bounds, th_dist=50):
+    uvr = np.ascontiguousarray(uvr, dtype=np.float32)
+    level1 = np.ascontiguousarray(level1, dtype=np.int32)
+    valid1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, occupied2))
+    mp_desc1, d2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (mp_desc1, d2))
+    k2 = np.ascontiguousarray(k2, dtype=KP_DTYPE)
+    b = np.asarray(bounds, dtype=np.float32)
+    m21 = np.empty(max(k2.size, 1), np.int32)
+    n = lib().orc_search_by_projection_sim3(valid1.size, _p(uvr), _p(level1), _p(valid1), _p(mp_desc1), _p(k2), k2.size, _p(d2),
+                                            _p(occupied2), _p(b), int(th_dist), _p(m21))
+    return n, m21[:k2.size]
+
+
 def match_bruteforce(q, d, th=50, ratio=0.6):
     q = np.ascontiguousarray(q, dtype=np.uint8)
     d = np.ascontiguousarray(d, dtype=np.uint8)

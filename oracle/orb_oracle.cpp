@@ -810,6 +810,41 @@ int search_by_projection_map(int n1, const float* proj, const float* viewCos, co
     return nmatches;
 }
 
+// ORBmatcher::SearchByProjection(KeyFrame* pKF, cv::Mat Scw, vpPoints, vpMatched, th) — src/ORBmatcher.cc:290-403 (loop
+// detection, src/LoopClosing.cc:278) from the radius search on (:357-398); the Sim3 / visibility arithmetic (:298-355) stays the
+// caller's.  uvr[3i..] = u, v, radius = th*mvScaleFactors[nPredictedLevel];  level1 = nPredictedLevel;  valid1 = survived every
+// `continue` of :318-351;  occupied2[idx] = vpMatched[idx] != NULL.  KeyFrame::GetFeaturesInArea (src/KeyFrame.cc:578-617) is the
+// Frame routine without a level filter; the level gate follows at :377-380.  match21[idx] = iMP (vpMatched[idx] = pMP), -1 = untouched.
+int search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
+                              const GridFrame& KF, const uint8_t* desc2, const uint8_t* occupied2, int thDist, int* match21) {
+    int nmatches = 0;
+    std::vector<int> owner(KF.n, -1);
+    std::vector<uint8_t> taken(KF.n);
+    for (int i = 0; i < KF.n; ++i) taken[i] = occupied2[i];
+    for (int iMP = 0; iMP < n1; iMP++) {
+        if (!valid1[iMP]) continue;
+        const int nPredictedLevel = level1[iMP];
+        const std::vector<size_t> vIndices = KF.features_in_area(uvr[3 * iMP], uvr[3 * iMP + 1], uvr[3 * iMP + 2], -1, -1);
+        if (vIndices.empty()) continue;
+        const uint8_t* dMP = mpDesc1 + (size_t)iMP * 32;
+        int bestDist = 256, bestIdx = -1;
+        for (size_t idx : vIndices) {
+            if (taken[idx]) continue;
+            const int kpLevel = KF.keys[idx].octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            const int dist = descriptor_distance(dMP, desc2 + idx * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)idx; }
+        }
+        if (bestDist <= thDist) {  // TH_LOW (:392)
+            owner[bestIdx] = iMP;
+            taken[bestIdx] = 1;
+            nmatches++;
+        }
+    }
+    for (int i = 0; i < KF.n; ++i) match21[i] = owner[i];
+    return nmatches;
+}
+
 // Brute-force best / second-best with the TH + ratio acceptance test.  There is no single reference function
 // (SURVEY.md §8a16); this follows the inner loop of ORBmatcher::SearchByBoW, src/ORBmatcher.cc:199-232:
 // bestDist1 = bestDist2 = 256, strict '<' updates, accept iff d1 <= th && (float)d1 < ratio*(float)d2.

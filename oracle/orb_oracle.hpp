@@ -99,6 +99,9 @@ int search_by_projection_map(int n1, const float* proj, const float* viewCos, co
                              const float* uRight2, const uint8_t* occupied2, const float* scaleFactors, float th, float nnratio,
                              int* match21);
 
+int search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
+                              const GridFrame& KF, const uint8_t* desc2, const uint8_t* occupied2, int thDist, int* match21);
+
 void match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1,
                       int* d2, int* match);
 

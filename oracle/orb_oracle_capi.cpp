@@ -109,6 +109,12 @@ int orc_search_by_projection_map(int n1, const float* proj, const float* viewCos
     return search_by_projection_map(n1, proj, viewCos, level1, valid1, obs1, mpDesc1, F, desc2, uRight2, occupied2, scaleFactors,
                                     th, nnratio, match21);
 }
+int orc_search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
+                                  const KeyPoint* k2, int n2, const uint8_t* desc2, const uint8_t* occupied2, const float* bounds,
+                                  int thDist, int* match21) {
+    GridFrame KF(k2, n2, bounds[0], bounds[1], bounds[2], bounds[3]);
+    return search_by_projection_sim3(n1, uvr, level1, valid1, mpDesc1, KF, desc2, occupied2, thDist, match21);
+}
 void orc_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2, int* match) {
     match_bruteforce(q, nq, d, nd, th, ratio, idx, d1, d2, match);
 }

@@ -298,6 +298,22 @@ class ORBmatcher:
                                                    C.byref(n)))
         return n.value, m21[:n2]
 
+    def SearchByProjectionSim3(self, uvr, level1, valid1, mp_desc1, kps2, desc2, occupied2, bounds, th_dist: int = TH_LOW):
+        """SearchByProjection(pKF, Scw, vpPoints, vpMatched, th), src/ORBmatcher.cc:290-403, from the radius search on.
+        Returns (nmatches, match21)."""
+        uvr = np.ascontiguousarray(uvr, dtype=np.float32)
+        level1 = np.ascontiguousarray(level1, dtype=np.int32)
+        valid1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, occupied2))
+        mp_desc1, desc2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (mp_desc1, desc2))
+        kps2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+        b = np.asarray(bounds, dtype=np.float32)
+        n1, n2 = valid1.size, kps2.size
+        m21 = np.empty(max(n2, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_search_by_projection_sim3(n1, _p(uvr), _p(level1), _p(valid1), _p(mp_desc1), _p(kps2), n2, _p(desc2),
+                                                    _p(occupied2), _p(b), int(th_dist), _p(m21), C.byref(n)))
+        return n.value, m21[:n2]
+
     def match_bruteforce(self, q, d, th: int = TH_LOW):
         """best / second-best over the whole database (inner loop of SearchByBoW, src/ORBmatcher.cc:187-232):
         returns (idx, d1, d2, match) int32 [nq]."""

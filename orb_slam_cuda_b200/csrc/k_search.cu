@@ -307,9 +307,13 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
             u = x3Dc[3 * i];
             v = x3Dc[3 * i + 1];
             ur = x3Dc[3 * i + 2];
-            r = (double)viewCos[i] > 0.998 ? 2.5f : 4.0f;                  // RadiusByViewingCos (:131-137)
-            if ((double)P.th != 1.0) r = __fmul_rn(r, P.th);               // bFactor (:49, :65-66)
-            r = __fmul_rn(r, scaleFactors[oct]);
+            if (P.mapMode == 2) {  // Sim3 variant (:290-403): the third value is the radius th*mvScaleFactors[level] itself
+                r = ur;
+            } else {
+                r = (double)viewCos[i] > 0.998 ? 2.5f : 4.0f;              // RadiusByViewingCos (:131-137)
+                if ((double)P.th != 1.0) r = __fmul_rn(r, P.th);           // bFactor (:49, :65-66)
+                r = __fmul_rn(r, scaleFactors[oct]);
+            }
             minLevel = oct - 1;
             maxLevel = oct;
         } else {
@@ -571,6 +575,36 @@ int launch_search_by_projection_map(int n1, const float* proj, const float* view
                                                     P, sorted, cellStart, cand, candCap, candCnt, dStatus);
     count_launch();
     k_sbpm_resolve<<<1, 32, smem, s>>>(n1, obs1, k2, n2, cand, candCap, candCnt, nnratio, match21, nmatches);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+int launch_search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* ones1,
+                                     const uint8_t* mpDesc1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
+                                     const uint8_t* occupied2, const float bounds[4], int thDist, int* cellOf, int* sorted,
+                                     int* cellStart, uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches,
+                                     int* dStatus, cudaStream_t s) {
+    SbpParams P;
+    memset(&P, 0, sizeof P);
+    P.minX = bounds[0]; P.maxX = bounds[1]; P.minY = bounds[2]; P.maxY = bounds[3];
+    P.invW = (float)GRID_COLS / (P.maxX - P.minX);
+    P.invH = (float)GRID_ROWS / (P.maxY - P.minY);
+    P.mapMode = 2;
+    const size_t smem = (size_t)n2 * 4 + (size_t)n1 * 4 + (size_t)n2 + (size_t)n1 + 16;
+    if (smem > 200 * 1024) {
+        set_error("SearchByProjection: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
+        return ORBX_E_INVALID;
+    }
+    if (smem > 48 * 1024) ORBX_CUDA(cudaFuncSetAttribute(k_sbp_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
+    count_launch();
+    k_sbp_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(n1, uvr, valid1, reinterpret_cast<const uint4*>(mpDesc1), level1, k2,
+                                                    reinterpret_cast<const uint4*>(desc2), nullptr, occupied2, nullptr, nullptr, P,
+                                                    sorted, cellStart, cand, candCap, candCnt, dStatus);
+    count_launch();
+    // best candidate only, every assigned keypoint is taken (ones1), no rotation pass
+    k_sbp_resolve<<<1, 32, smem, s>>>(n1, ones1, nullptr, k2, n2, cand, candCap, candCnt, 0, thDist, match21, nmatches);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -324,6 +324,61 @@ int orbx_search_by_projection_map(int n1, const float* proj, const float* view_c
     return ORBX_OK;
 }
 
+int orbx_search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* mp_desc1,
+                                   const orbx_keypoint* k2, int n2, const uint8_t* desc2, const uint8_t* occupied2,
+                                   const float bounds[4], int th_dist, int* match21, int* nmatches) {
+    if (n1 < 0 || n2 < 0 || !bounds || !nmatches || (n1 > 0 && (!uvr || !level1 || !valid1 || !mp_desc1)) ||
+        (n2 > 0 && (!k2 || !desc2 || !occupied2 || !match21)) || n2 > 65535 || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) {
+        set_error("orbx_search_by_projection_sim3: bad argument (n2 <= 65535, bounds = {minX, maxX, minY, maxY})");
+        return ORBX_E_INVALID;
+    }
+    *nmatches = 0;
+    for (int i = 0; i < n2; ++i) match21[i] = -1;
+    if (n1 == 0 || n2 == 0) return ORBX_OK;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = w->stream;
+    const int candCap = n2;
+    // one packed upload: [uvr | level1 | mp_desc1 | valid1 | ones | occupied2]
+    const size_t oX = 0, oO = oX + (size_t)n1 * 12, oD = (oO + (size_t)n1 * 4 + 15) / 16 * 16, oV = oD + (size_t)n1 * 32, oB = oV + n1,
+                 oC = oB + n1, total = oC + n2;
+    if ((rc = w->pin.ensure(total)) || (rc = w->a.ensure(total))) return rc;
+    uint8_t* hp = w->pin.as<uint8_t>();
+    memcpy(hp + oX, uvr, (size_t)n1 * 12);
+    memcpy(hp + oO, level1, (size_t)n1 * 4);
+    memcpy(hp + oD, mp_desc1, (size_t)n1 * 32);
+    memcpy(hp + oV, valid1, n1);
+    memset(hp + oB, 1, n1);
+    memcpy(hp + oC, occupied2, n2);
+    ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
+    if ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
+        (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
+        (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure((size_t)n1 * 4)) || (rc = w->status.ensure(16)))
+        return rc;
+    ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
+    const uint8_t* dp = w->a.as<uint8_t>();
+    int* cellOf = w->f.as<int>();
+    int* sorted = cellOf + n2;
+    int* cellStart = sorted + n2;
+    int* dN = w->status.as<int>() + 1;
+    if ((rc = launch_search_by_projection_sim3(n1, reinterpret_cast<const float*>(dp + oX), reinterpret_cast<const int*>(dp + oO),
+                                               dp + oV, dp + oB, dp + oD, w->c.as<orbx_keypoint>(), n2, w->d.as<uint8_t>(), dp + oC,
+                                               bounds, th_dist, cellOf, sorted, cellStart, w->g.as<uint32_t>(), candCap,
+                                               w->h.as<int>(), w->out0.as<int>(), dN, w->status.as<int>(), s)))
+        return rc;
+    int st[2] = {0, 0};
+    ORBX_CUDA(cudaMemcpyAsync(match21, w->out0.p, (size_t)n2 * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(st, w->status.p, 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    if (st[0] != 0) {
+        set_error("orbx_search_by_projection_sim3: candidate list overflow");
+        return ORBX_E_OVERFLOW;
+    }
+    *nmatches = st[1];
+    return ORBX_OK;
+}
+
 int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypoint* kL, int nL, const uint8_t* descL,
                       const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float mb, float* u_right, float* depth) {
     ExtractorView L, R;

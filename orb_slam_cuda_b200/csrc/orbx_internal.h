@@ -213,6 +213,11 @@ int launch_search_by_projection_map(int n1, const float* proj, const float* view
                                     const float bounds[4], float th, float nnratio, int* cellOf, int* sorted, int* cellStart,
                                     uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches, int* dStatus,
                                     cudaStream_t s);
+int launch_search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* ones1,
+                                     const uint8_t* mpDesc1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
+                                     const uint8_t* occupied2, const float bounds[4], int thDist, int* cellOf, int* sorted,
+                                     int* cellStart, uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches,
+                                     int* dStatus, cudaStream_t s);
 int launch_stereo(const StereoLevels& lv, const orbx_keypoint* kL, int nL, const uint8_t* dL, const orbx_keypoint* kR, int nR,
                   const uint8_t* dR, float mbf, float maxD, float* uRight, float* depth, int* sad, cudaStream_t s);
 

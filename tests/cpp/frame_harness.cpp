@@ -30,6 +30,8 @@ struct MapPoint {  // the members of ORB_SLAM2::MapPoint that SearchByProjection
     float GetMinDistanceInvariance() const { return 3.5f; }
     float GetMaxDistanceInvariance() const { return 15.5f; }
     template <class F> int PredictScale(float, F*) const { return mnTrackScaleLevel; }
+    cv::Mat mNormal;
+    cv::Mat GetNormal() const { return mNormal; }
     cv::Mat GetWorldPos() const { return mWorldPos; }
     cv::Mat GetDescriptor() const { return mDescriptor; }
     int Observations() const { return nObs; }
@@ -39,6 +41,11 @@ struct KeyFrame {  // the members of ORB_SLAM2::KeyFrame that the relocalisation
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<cv::KeyPoint> mvKeysUn;
     std::vector<MapPoint*> GetMapPointMatches() const { return mvpMapPoints; }
+    // loop-detection SearchByProjection (src/ORBmatcher.cc:290-403)
+    float fx = 0, fy = 0, cx = 0, cy = 0, mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
+    std::vector<float> mvScaleFactors;
+    cv::Mat mDescriptors;
+    bool IsInImage(const float& x, const float& y) const { return x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY; }
 };
 
 struct Frame {  // the members of ORB_SLAM2::Frame that the front end reads or writes (include/Frame.h)
@@ -206,6 +213,27 @@ int main(int argc, char** argv) {
             const int nr = matcher.SearchByProjection(Cur, &KF, found, 10.f, 100);
             put_i(out, nr);
             for (int j = 0; j < Cur.N; ++j) put_i(out, Cur.mvpMapPoints[j] ? (int)(Cur.mvpMapPoints[j] - points.data()) : -1);
+            // LoopClosing::ComputeSim3 (:278): the current frame as the keyframe, Scw = 2 x its pose (scale 2), every good point a
+            // candidate, every 10th keypoint already matched
+            KeyFrame KC;
+            KC.mvKeysUn = Cur.mvKeysUn; KC.mDescriptors = Cur.mDescriptors; KC.mvScaleFactors = Cur.mvScaleFactors;
+            KC.fx = Cur.fx; KC.fy = Cur.fy; KC.cx = Cur.cx; KC.cy = Cur.cy;
+            KC.mnMinX = 0; KC.mnMaxX = (float)w; KC.mnMinY = 0; KC.mnMaxY = (float)h;
+            cv::Mat Scw(4, 4, CV_32F);
+            for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) Scw.at<float>(r, c) = (r < 3 ? 2.f : 1.f) * Cur.mTcw.at<float>(r, c);
+            std::vector<MapPoint*> cands;
+            for (int i = 0; i < Last.N; ++i) {
+                if (i % 5 == 0) continue;
+                points[i].mNormal = cv::Mat(3, 1, CV_32F);
+                points[i].mNormal.at<float>(0, 0) = 0.f; points[i].mNormal.at<float>(1, 0) = 0.f; points[i].mNormal.at<float>(2, 0) = 1.f;
+                cands.push_back(&points[i]);
+            }
+            std::vector<MapPoint*> matched(Cur.N, nullptr);
+            for (int j = 0; j < Cur.N; j += 10) matched[j] = &points[0];
+            ORBmatcher loopMatcher(0.75f, true);
+            const int ns = loopMatcher.SearchByProjection(&KC, Scw, cands, matched, 10);
+            put_i(out, ns);
+            for (int j = 0; j < Cur.N; ++j) put_i(out, matched[j] ? (int)(matched[j] - points.data()) : -1);
             fclose(out);
         } else {
             return 2;

@@ -184,3 +184,23 @@ def test_track_with_motion_model_projection(harness, tmp_path):
     assert rd.i32() == n_ref3
     got3 = rd.arr(np.int32, n2)
     assert np.array_equal(got3, np.where(occ3 == 1, 0, np.where(m_ref3 >= 0, m_ref3, -1)))
+    # fourth part: the loop-detection variant (src/ORBmatcher.cc:290-403), Scw = scale 2 x the current pose
+    S = (f32(2.0) * R).astype(f32)
+    scw = f32(np.sqrt(float(S[0]) ** 2 + float(S[1]) ** 2 + float(S[2]) ** 2))
+    Rs, ts = (S / scw).astype(f32), ((f32(2.0) * t).astype(f32) / scw).astype(f32)
+    pc = np.stack([((Rs[3 * r] * X0 + Rs[3 * r + 1] * X1).astype(f32) + Rs[3 * r + 2] * z).astype(f32) + ts[r] for r in range(3)], axis=1).astype(f32)
+    Ow2 = np.array([-((Rs[c] * ts[0] + Rs[3 + c] * ts[1]).astype(f32) + Rs[6 + c] * ts[2]).astype(f32) for c in range(3)], f32)
+    PO2 = (Xw - Ow2[None, :]).astype(f32)
+    dist2 = np.sqrt((PO2.astype(np.float64) ** 2).sum(axis=1)).astype(f32)
+    invz = (f32(1.0) / pc[:, 2]).astype(f32)
+    u2 = (fx * (pc[:, 0] * invz).astype(f32)).astype(f32) + cx
+    v2 = (fy * (pc[:, 1] * invz).astype(f32)).astype(f32) + cy
+    ok = has_mp & (i % 13 != 0) & ~(pc[:, 2] < 0) & (u2 >= 0) & (u2 < f32(w)) & (v2 >= 0) & (v2 < f32(h))
+    ok &= ~(dist2 < f32(3.5)) & ~(dist2 > f32(15.5)) & ~(PO2[:, 2].astype(np.float64) < 0.5 * dist2.astype(np.float64))
+    uvr = np.stack([u2, v2, (f32(10.0) * sf[k1["octave"]]).astype(f32)], axis=1).astype(f32)
+    n_ref4, m_ref4 = O.search_by_projection_sim3(uvr[keep], k1["octave"][keep], ok[keep].astype(np.uint8), d1[keep], k2, d2, occ3,
+                                                 (0.0, float(w), 0.0, float(h)), 50)
+    assert n_ref4 > 50
+    assert rd.i32() == n_ref4
+    got4 = rd.arr(np.int32, n2)
+    assert np.array_equal(got4, np.where(occ3 == 1, 0, np.where(m_ref4 >= 0, keep[np.maximum(m_ref4, 0)], -1)))

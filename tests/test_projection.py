@@ -243,3 +243,37 @@ def test_search_by_projection_map_gpu(seed, stereo, th, ratio):
     assert n_ref > 30, "the scenario must produce matches"
     assert n == n_ref
     assert np.array_equal(m21, m_ref)
+
+
+# ---- SearchByProjection(pKF, Scw, vpPoints, vpMatched, th) — src/ORBmatcher.cc:290-403 (loop detection) ------------------
+
+def test_oracle_kat_sim3_projection():
+    k2 = np.array([kp(100, 100, 1), kp(102, 100, 2), kp(101, 101, 0)], dtype=O.KP_DTYPE)
+    d2 = np.zeros((3, 32), np.uint8)
+    d2[0, 0], d2[1, 0], d2[2, 0] = 0x07, 0x01, 0x03
+    uvr = np.array([[101.0, 100.0, 5.0], [101.0, 100.0, 5.0]], np.float32)
+    mp = np.zeros((2, 32), np.uint8)
+    # level 1 admits octaves 0..1: keypoint 2 (2 bits) beats keypoint 0 (3 bits); keypoint 1 (octave 2) is out although closest.
+    # The second point finds keypoint 2 taken (vpMatched set) and falls back to keypoint 0.
+    n, m21 = O.search_by_projection_sim3(uvr, [1, 1], [1, 1], mp, k2, d2, [0, 0, 0], BOUNDS)
+    assert n == 2 and list(m21) == [1, -1, 0]
+    n, m21 = O.search_by_projection_sim3(uvr, [2, 2], [1, 0], mp, k2, d2, [0, 0, 0], BOUNDS)
+    assert n == 1 and list(m21) == [-1, 0, -1]
+    far = mp.copy()
+    far[:, :7] = 0xFF  # 56 - 3 bits > TH_LOW
+    assert O.search_by_projection_sim3(uvr, [1, 1], [1, 1], far, k2, d2, [0, 0, 0], BOUNDS)[0] == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,th", [(11, 10), (12, 4)])
+def test_search_by_projection_sim3_gpu(seed, th):
+    import orb_slam_cuda_b200 as X
+    s = map_scenario(seed, False)
+    rng = np.random.default_rng(seed)
+    uvr = s["proj"].copy()
+    uvr[:, 2] = (np.float32(th) * s["scale_factors"][s["level1"]]).astype(np.float32)
+    occ = (rng.random(s["k2"].size) < 0.15).astype(np.uint8)
+    n_ref, m_ref = O.search_by_projection_sim3(uvr, s["level1"], s["valid1"], s["mp_desc1"], s["k2"], s["d2"], occ, s["bounds"], 50)
+    n, m21 = X.ORBmatcher(0.75, True).SearchByProjectionSim3(uvr, s["level1"], s["valid1"], s["mp_desc1"], s["k2"], s["d2"], occ,
+                                                             s["bounds"], 50)
+    assert n_ref > 50 and n == n_ref and np.array_equal(m21, m_ref)
