@@ -5,9 +5,10 @@
 // const cv::Mat&), TH_LOW / TH_HIGH / HISTO_LENGTH, and SearchForInitialization with its reference signature.
 // SearchForInitialization and ComputeStereoMatches are templates over the frame type so that they bind to the
 // reference's ORB_SLAM2::Frame (its public members mvKeysUn, mDescriptors, mnMinX ... are used exactly as
-// src/ORBmatcher.cc does) without this repository carrying Frame.h.  The other ten matcher routines
-// (SearchByProjection x4, SearchByBoW x2, SearchForTriangulation, SearchBySim3, Fuse x2) are SURVEY.md §8f "next"
-// rows and stay in the reference's src/ORBmatcher.cc.
+// src/ORBmatcher.cc does) without this repository carrying Frame.h.  SearchByProjection (all four overloads) and SearchByBoW
+// (both overloads) bind the same way to Frame / KeyFrame / MapPoint.  The other four matcher routines
+// (SearchForTriangulation, SearchBySim3, Fuse x2) are SURVEY.md §8f "next" rows and stay in the reference's
+// src/ORBmatcher.cc.
 //
 // Every call here runs on the device; there is no CPU implementation behind it (errors throw std::runtime_error).
 // DescriptorDistance on ONE pair is a kernel launch plus two small copies: callers with many pairs should use
@@ -16,6 +17,7 @@
 #define ORBMATCHER_H
 
 #include <cmath>
+#include <cstdint>
 #include <cstring>
 #include <set>
 #include <stdexcept>
@@ -355,6 +357,70 @@ public:
         return nmatches;
     }
 
+    // Search matches between MapPoints in a KeyFrame and ORB in a Frame, brute force constrained to ORB that belong to the same
+    // vocabulary node (TrackReferenceKeyFrame src/Tracking.cc:842, Relocalization :1465); src/ORBmatcher.cc:159-288.
+    // KeyFrame members read: GetMapPointMatches(), mFeatVec, mDescriptors, mvKeysUn; Frame: N, mFeatVec, mDescriptors, mvKeys.
+    template <class KeyFrameT, class FrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT* pKF, FrameT& F, std::vector<MapPointT*>& vpMapPointMatches) {
+        const std::vector<MapPointT*> vpMapPointsKF = pKF->GetMapPointMatches();
+        vpMapPointMatches = std::vector<MapPointT*>(F.N, static_cast<MapPointT*>(nullptr));
+        const int n1 = (int)vpMapPointsKF.size(), n2 = (int)F.N;
+        BowNodes nodes;
+        common_nodes(pKF->mFeatVec, F.mFeatVec, nodes);
+        if (n1 == 0 || n2 == 0 || nodes.idx1.empty() || nodes.idx2.empty()) return 0;
+        std::vector<unsigned char> valid1(n1), valid2(n2, 1);
+        std::vector<float> angle1(n1), angle2(n2);
+        for (int i = 0; i < n1; ++i) {
+            valid1[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad();  // :192-198
+            angle1[i] = pKF->mvKeysUn[i].angle;
+        }
+        for (int j = 0; j < n2; ++j) angle2[j] = F.mvKeys[j].angle;  // :238 reads the distorted keypoints of the frame
+        const cv::Mat d1 = continuous(pKF->mDescriptors), d2 = continuous(F.mDescriptors);
+        std::vector<int> match12(n1, -1), match21(n2, -1);
+        int nmatches = 0;
+        check(orbx_search_by_bow((int)nodes.start1.size() - 1, nodes.start1.data(), nodes.idx1.data(), nodes.start2.data(),
+                                 nodes.idx2.data(), n1, valid1.data(), d1.template ptr<unsigned char>(), angle1.data(), n2, valid2.data(),
+                                 d2.template ptr<unsigned char>(), angle2.data(), TH_LOW, mfNNratio, mbCheckOrientation ? 1 : 0,
+                                 match12.data(), match21.data(), &nmatches),
+              "SearchByBoW");
+        for (int j = 0; j < n2; ++j)
+            if (match21[j] >= 0) vpMapPointMatches[j] = vpMapPointsKF[match21[j]];
+        return nmatches;
+    }
+
+    // Matching between two KeyFrames for loop detection (LoopClosing::ComputeSim3, src/LoopClosing.cc:304);
+    // src/ORBmatcher.cc:522-655.  KeyFrame members read: mvKeysUn, mFeatVec, GetMapPointMatches(), mDescriptors.
+    template <class KeyFrameT, class MapPointT>
+    int SearchByBoW(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12) {
+        const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        vpMatches12 = std::vector<MapPointT*>(vpMapPoints1.size(), static_cast<MapPointT*>(nullptr));
+        const int n1 = (int)vpMapPoints1.size(), n2 = (int)vpMapPoints2.size();
+        BowNodes nodes;
+        common_nodes(pKF1->mFeatVec, pKF2->mFeatVec, nodes);
+        if (n1 == 0 || n2 == 0 || nodes.idx1.empty() || nodes.idx2.empty()) return 0;
+        std::vector<unsigned char> valid1(n1), valid2(n2);
+        std::vector<float> angle1(n1), angle2(n2);
+        for (int i = 0; i < n1; ++i) {
+            valid1[i] = vpMapPoints1[i] && !vpMapPoints1[i]->isBad();  // :556-562
+            angle1[i] = pKF1->mvKeysUn[i].angle;
+        }
+        for (int j = 0; j < n2; ++j) {
+            valid2[j] = vpMapPoints2[j] && !vpMapPoints2[j]->isBad();  // :582-587
+            angle2[j] = pKF2->mvKeysUn[j].angle;
+        }
+        const cv::Mat d1 = continuous(pKF1->mDescriptors), d2 = continuous(pKF2->mDescriptors);
+        std::vector<int> match12(n1, -1), match21(n2, -1);
+        int nmatches = 0;
+        check(orbx_search_by_bow((int)nodes.start1.size() - 1, nodes.start1.data(), nodes.idx1.data(), nodes.start2.data(),
+                                 nodes.idx2.data(), n1, valid1.data(), d1.template ptr<unsigned char>(), angle1.data(), n2, valid2.data(),
+                                 d2.template ptr<unsigned char>(), angle2.data(), TH_LOW - 1 /* bestDist1 < TH_LOW, :605 */, mfNNratio,
+                                 mbCheckOrientation ? 1 : 0, match12.data(), match21.data(), &nmatches),
+              "SearchByBoW");
+        for (int i = 0; i < n1; ++i)
+            if (match12[i] >= 0) vpMatches12[i] = vpMapPoints2[match12[i]];
+        return nmatches;
+    }
+
     static const int TH_LOW = 50;
     static const int TH_HIGH = 100;
     static const int HISTO_LENGTH = 30;
@@ -363,6 +429,30 @@ public:
         if (rc != ORBX_OK) throw std::runtime_error(std::string(what) + ": " + orbx_last_error());
     }
     static cv::Mat continuous(const cv::Mat& m) { return m.isContinuous() ? m : m.clone(); }
+
+    // The common nodes of two DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned int>>) in map order — the walk of
+    // src/ORBmatcher.cc:176-256 — flattened for orbx_search_by_bow.
+    struct BowNodes {
+        std::vector<int> start1{0}, start2{0};
+        std::vector<uint32_t> idx1, idx2;
+    };
+    template <class FeatVecT> static void common_nodes(const FeatVecT& fv1, const FeatVecT& fv2, BowNodes& out) {
+        typename FeatVecT::const_iterator it1 = fv1.begin(), it2 = fv2.begin();
+        while (it1 != fv1.end() && it2 != fv2.end()) {
+            if (it1->first == it2->first) {
+                out.idx1.insert(out.idx1.end(), it1->second.begin(), it1->second.end());
+                out.idx2.insert(out.idx2.end(), it2->second.begin(), it2->second.end());
+                out.start1.push_back((int)out.idx1.size());
+                out.start2.push_back((int)out.idx2.size());
+                ++it1;
+                ++it2;
+            } else if (it1->first < it2->first) {
+                it1 = fv1.lower_bound(it2->first);
+            } else {
+                it2 = fv2.lower_bound(it1->first);
+            }
+        }
+    }
 
 protected:
     float mfNNratio;

@@ -194,6 +194,25 @@ int orbx_search_by_projection_sim3(int n1, const float* uvr, const int* level1, 
                                    const orbx_keypoint* k2, int n2, const uint8_t* desc2, const uint8_t* occupied2,
                                    const float bounds[4], int th_dist, int* match21, int* nmatches);
 
+/* ORBmatcher::SearchByBoW, both overloads: (KeyFrame* pKF, Frame &F, vpMapPointMatches) (src/ORBmatcher.cc:159-288;
+ * Tracking::TrackReferenceKeyFrame, src/Tracking.cc:842, and Relocalization, :1465) and (KeyFrame* pKF1, KeyFrame* pKF2,
+ * vpMatches12) (:522-655; LoopClosing::ComputeSim3, src/LoopClosing.cc:304).  The caller walks the two DBoW2 FeatureVectors
+ * (:176-180 / :541-545) and hands over the n_nodes COMMON nodes in map order: node k holds the feature indices
+ * idx1[start1[k] .. start1[k+1]) of the first and idx2[start2[k] .. start2[k+1]) of the second argument, each in vector order.
+ *   valid1[i] = first argument's map point i exists and !isBad() (:192-198 / :556-562)
+ *   valid2[j] = 1 for the Frame overload;  pMP2 exists and !isBad() for the KeyFrame overload (:582-587)
+ *   desc*, angle* = mDescriptors rows and mvKeysUn[.].angle of the two arguments
+ *   th_dist = TH_LOW for the Frame overload (`bestDist1 <= TH_LOW`, :230), TH_LOW - 1 for the KeyFrame overload
+ *             (`bestDist1 < TH_LOW`, :605);  nnratio = mfNNratio;  check_ori = mbCheckOrientation
+ * match12[i] = j and match21[j] = i for every accepted pair (Frame overload: vpMapPointMatches[j] = vpMapPointsKF[i];
+ * KeyFrame overload: vpMatches12[i] = vpMapPoints2[j]);  -1: untouched;  -2: assigned, then removed by the rotation
+ * histogram (:262-285 / :631-652) — the slot still blocked later features while the loop ran.  *nmatches = return value.
+ * Host buffers; n2 <= 65535 and at most 65535 second-argument features per node. */
+int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                       const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
+                       const uint8_t* desc2, const float* angle2, int th_dist, float nnratio, int check_ori, int* match12,
+                       int* match21, int* nmatches);
+
 /* Frame::ComputeStereoMatches (src/Frame.cc:465-639).  exL / exR hold the pyramids of the left / right frame of
  * their last orbx_extract call (device resident; nothing is copied to the host).  bf = mbf (baseline x fx),
  * mb = baseline in metres = mbf / fx (src/Frame.cc:113).  u_right[nL], depth[nL] as mvuRight / mvDepth

@@ -253,6 +253,25 @@ def search_by_projection_sim3(uvr, level1, valid1, mp_desc1, k2, d2, occupied2, 
     return n, m21[:k2.size]
 
 
+def _bow_args(start1, idx1, start2, idx2, valid1, d1, angle1, valid2, d2, angle2):
+    start1, start2 = (np.ascontiguousarray(a, dtype=np.int32) for a in (start1, start2))
+    idx1, idx2 = (np.ascontiguousarray(a, dtype=np.uint32) for a in (idx1, idx2))
+    valid1, valid2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, valid2))
+    d1, d2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (d1, d2))
+    angle1, angle2 = (np.ascontiguousarray(a, dtype=np.float32) for a in (angle1, angle2))
+    return start1, idx1, start2, idx2, valid1, d1, angle1, valid2, d2, angle2
+
+
+def search_by_bow(start1, idx1, start2, idx2, valid1, d1, angle1, valid2, d2, angle2, th_dist=50, nnratio=0.7, check_ori=True):
+    start1, idx1, start2, idx2, valid1, d1, angle1, valid2, d2, angle2 = _bow_args(start1, idx1, start2, idx2, valid1, d1, angle1,
+                                                                                   valid2, d2, angle2)
+    n1, n2 = valid1.size, valid2.size
+    m12, m21 = np.empty(max(n1, 1), np.int32), np.empty(max(n2, 1), np.int32)
+    n = lib().orc_search_by_bow(start1.size - 1, _p(start1), _p(idx1), _p(start2), _p(idx2), n1, _p(valid1), _p(d1), _p(angle1), n2,
+                                _p(valid2), _p(d2), _p(angle2), int(th_dist), C.c_float(nnratio), int(check_ori), _p(m12), _p(m21))
+    return n, m12[:n1], m21[:n2]
+
+
 def match_bruteforce(q, d, th=50, ratio=0.6):
     q = np.ascontiguousarray(q, dtype=np.uint8)
     d = np.ascontiguousarray(d, dtype=np.uint8)

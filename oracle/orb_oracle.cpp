@@ -845,6 +845,66 @@ int search_by_projection_sim3(int n1, const float* uvr, const int* level1, const
     return nmatches;
 }
 
+// ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) — src/ORBmatcher.cc:159-288, and
+// SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) — :522-655.  The vocabulary walk (DBoW2 FeatureVector merge, :175-181,
+// :264-272) stays the caller's: it hands in the common nodes in order, node k holding the feature indices
+// idx1[start1[k]..start1[k+1]) of the first and idx2[start2[k]..) of the second argument.
+//   valid1[i1] = the keyframe-1 feature has a map point that is not bad (:192-198, :560-564)
+//   valid2[i2] = 1 for the Frame variant; pMP2 && !pMP2->isBad() for the keyframe variant (:577-583)
+//   thDist     = best distance accepted: TH_LOW for `<= TH_LOW` (:230), TH_LOW - 1 for `< TH_LOW` (:600)
+// match12[i1] = i2 / -1 none / -2 removed by the rotation check; match21[i2] likewise (every i2 is assigned at most once).
+int search_by_bow(int nNodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                  const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
+                  const uint8_t* desc2, const float* angle2, int thDist, float nnratio, bool checkOri, int* match12, int* match21) {
+    const int HISTO_LENGTH = 30;
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];  // holds i1 (the keyframe variant stores idx1, the Frame variant bestIdxF = match12[i1])
+    const float factor = 1.0f / HISTO_LENGTH;
+    std::vector<uint8_t> taken(n2, 0);
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    for (int i = 0; i < n2; ++i) match21[i] = -1;
+    for (int k = 0; k < nNodes; ++k) {
+        for (int a = start1[k]; a < start1[k + 1]; ++a) {
+            const int i1 = (int)idx1[a];
+            if (!valid1[i1]) continue;
+            int bestDist1 = 256, bestIdx2 = -1, bestDist2 = 256;
+            for (int b = start2[k]; b < start2[k + 1]; ++b) {
+                const int i2 = (int)idx2[b];
+                if (taken[i2] || !valid2[i2]) continue;
+                const int dist = descriptor_distance(desc1 + (size_t)i1 * 32, desc2 + (size_t)i2 * 32);
+                if (dist < bestDist1) { bestDist2 = bestDist1; bestDist1 = dist; bestIdx2 = i2; }
+                else if (dist < bestDist2) bestDist2 = dist;
+            }
+            if (bestDist1 <= thDist && (float)bestDist1 < nnratio * (float)bestDist2) {
+                match12[i1] = bestIdx2;
+                match21[bestIdx2] = i1;
+                taken[bestIdx2] = 1;
+                if (checkOri) {
+                    float rot = angle1[i1] - angle2[bestIdx2];
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == HISTO_LENGTH) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+                nmatches++;
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int i1 : rotHist[i]) {
+                match21[match12[i1]] = -2;
+                match12[i1] = -2;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 // Brute-force best / second-best with the TH + ratio acceptance test.  There is no single reference function
 // (SURVEY.md §8a16); this follows the inner loop of ORBmatcher::SearchByBoW, src/ORBmatcher.cc:199-232:
 // bestDist1 = bestDist2 = 256, strict '<' updates, accept iff d1 <= th && (float)d1 < ratio*(float)d2.

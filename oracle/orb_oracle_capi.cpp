@@ -115,6 +115,12 @@ int orc_search_by_projection_sim3(int n1, const float* uvr, const int* level1, c
     GridFrame KF(k2, n2, bounds[0], bounds[1], bounds[2], bounds[3]);
     return search_by_projection_sim3(n1, uvr, level1, valid1, mpDesc1, KF, desc2, occupied2, thDist, match21);
 }
+int orc_search_by_bow(int nNodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                      const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
+                      const uint8_t* desc2, const float* angle2, int thDist, float nnratio, int checkOri, int* match12, int* match21) {
+    return search_by_bow(nNodes, start1, idx1, start2, idx2, n1, valid1, desc1, angle1, n2, valid2, desc2, angle2, thDist, nnratio,
+                         checkOri != 0, match12, match21);
+}
 void orc_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2, int* match) {
     match_bruteforce(q, nq, d, nd, th, ratio, idx, d1, d2, match);
 }

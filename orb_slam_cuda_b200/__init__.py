@@ -314,6 +314,23 @@ class ORBmatcher:
                                                     _p(occupied2), _p(b), int(th_dist), _p(m21), C.byref(n)))
         return n.value, m21[:n2]
 
+    def SearchByBoW(self, start1, idx1, start2, idx2, valid1, desc1, angle1, valid2, desc2, angle2, th_dist: int = TH_LOW):
+        """SearchByBoW(pKF, F, ...) (src/ORBmatcher.cc:159-288; th_dist = TH_LOW, valid2 all ones) and
+        SearchByBoW(pKF1, pKF2, ...) (:522-655; th_dist = TH_LOW - 1) over the common vocabulary nodes start*/idx*.
+        Returns (nmatches, match12, match21)."""
+        start1, start2 = (np.ascontiguousarray(a, dtype=np.int32) for a in (start1, start2))
+        idx1, idx2 = (np.ascontiguousarray(a, dtype=np.uint32) for a in (idx1, idx2))
+        valid1, valid2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, valid2))
+        desc1, desc2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (desc1, desc2))
+        angle1, angle2 = (np.ascontiguousarray(a, dtype=np.float32) for a in (angle1, angle2))
+        n_nodes, n1, n2 = max(start1.size - 1, 0), valid1.size, valid2.size
+        m12, m21 = np.empty(max(n1, 1), np.int32), np.empty(max(n2, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_search_by_bow(n_nodes, _p(start1), _p(idx1), _p(start2), _p(idx2), n1, _p(valid1), _p(desc1), _p(angle1),
+                                        n2, _p(valid2), _p(desc2), _p(angle2), int(th_dist), C.c_float(self.mfNNratio),
+                                        int(self.mbCheckOrientation), _p(m12), _p(m21), C.byref(n)))
+        return n.value, m12[:n1], m21[:n2]
+
     def match_bruteforce(self, q, d, th: int = TH_LOW):
         """best / second-best over the whole database (inner loop of SearchByBoW, src/ORBmatcher.cc:187-232):
         returns (idx, d1, d2, match) int32 [nq]."""

@@ -379,6 +379,94 @@ int orbx_search_by_projection_sim3(int n1, const float* uvr, const int* level1, 
     return ORBX_OK;
 }
 
+int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                       const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
+                       const uint8_t* desc2, const float* angle2, int th_dist, float nnratio, int check_ori, int* match12, int* match21,
+                       int* nmatches) {
+    if (n_nodes < 0 || n1 < 0 || n2 < 0 || n2 > 65535 || !nmatches || (n_nodes > 0 && (!start1 || !start2)) ||
+        (n1 > 0 && (!valid1 || !desc1 || !angle1 || !match12)) || (n2 > 0 && (!valid2 || !desc2 || !angle2 || !match21))) {
+        set_error("orbx_search_by_bow: bad argument (n2 <= 65535)");
+        return ORBX_E_INVALID;
+    }
+    *nmatches = 0;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    for (int i = 0; i < n2; ++i) match21[i] = -1;
+    if (n_nodes == 0 || n1 == 0 || n2 == 0) return ORBX_OK;
+    if (start1[0] != 0 || start2[0] != 0) {
+        set_error("orbx_search_by_bow: start1[0] and start2[0] must be 0");
+        return ORBX_E_INVALID;
+    }
+    for (int k = 0; k < n_nodes; ++k)
+        if (start1[k + 1] < start1[k] || start2[k + 1] < start2[k] || start2[k + 1] - start2[k] > 65535) {
+            set_error("orbx_search_by_bow: node %d has a malformed feature range", k);
+            return ORBX_E_INVALID;
+        }
+    const int nItems = start1[n_nodes], nIdx2 = start2[n_nodes];
+    if ((nItems > 0 && !idx1) || (nIdx2 > 0 && !idx2)) {
+        set_error("orbx_search_by_bow: null feature index list");
+        return ORBX_E_INVALID;
+    }
+    for (int i = 0; i < nItems; ++i)
+        if (idx1[i] >= (uint32_t)n1) { set_error("orbx_search_by_bow: idx1[%d] out of range", i); return ORBX_E_INVALID; }
+    for (int i = 0; i < nIdx2; ++i)
+        if (idx2[i] >= (uint32_t)n2) { set_error("orbx_search_by_bow: idx2[%d] out of range", i); return ORBX_E_INVALID; }
+    if (nItems == 0 || nIdx2 == 0) return ORBX_OK;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = w->stream;
+    // one packed upload: [idx1 | nodeOf | candOff | start2 | idx2 | angle1 | angle2 | desc1 | desc2 | valid1 | valid2]
+    const size_t oI1 = 0, oNode = oI1 + (size_t)nItems * 4, oOff = oNode + (size_t)nItems * 4, oS2 = oOff + (size_t)nItems * 4,
+                 oI2 = oS2 + (size_t)(n_nodes + 1) * 4, oA1 = oI2 + (size_t)nIdx2 * 4, oA2 = oA1 + (size_t)n1 * 4,
+                 oD1 = (oA2 + (size_t)n2 * 4 + 15) / 16 * 16, oD2 = oD1 + (size_t)n1 * 32, oV1 = oD2 + (size_t)n2 * 32, oV2 = oV1 + n1,
+                 total = oV2 + n2;
+    if ((rc = w->pin.ensure(total))) return rc;
+    uint8_t* hp = w->pin.as<uint8_t>();
+    int* hNode = reinterpret_cast<int*>(hp + oNode);
+    int* hOff = reinterpret_cast<int*>(hp + oOff);
+    size_t nCand = 0;
+    for (int k = 0; k < n_nodes; ++k) {
+        const size_t len2 = (size_t)(start2[k + 1] - start2[k]);
+        for (int i = start1[k]; i < start1[k + 1]; ++i) {
+            hNode[i] = k;
+            hOff[i] = (int)nCand;
+            nCand += len2;
+            if (nCand > ((size_t)1 << 30)) {
+                set_error("orbx_search_by_bow: more than 2^30 candidate pairs");
+                return ORBX_E_INVALID;
+            }
+        }
+    }
+    memcpy(hp + oI1, idx1, (size_t)nItems * 4);
+    memcpy(hp + oS2, start2, (size_t)(n_nodes + 1) * 4);
+    memcpy(hp + oI2, idx2, (size_t)nIdx2 * 4);
+    memcpy(hp + oA1, angle1, (size_t)n1 * 4);
+    memcpy(hp + oA2, angle2, (size_t)n2 * 4);
+    memcpy(hp + oD1, desc1, (size_t)n1 * 32);
+    memcpy(hp + oD2, desc2, (size_t)n2 * 32);
+    memcpy(hp + oV1, valid1, n1);
+    memcpy(hp + oV2, valid2, n2);
+    if ((rc = w->a.ensure(total)) || (rc = w->g.ensure((nCand + 1) * 4)) || (rc = w->h.ensure((size_t)nItems * 4)) ||
+        (rc = w->out0.ensure((size_t)n1 * 4 + 16)) || (rc = w->out1.ensure((size_t)n2 * 4 + 16)) || (rc = w->status.ensure(16)))
+        return rc;
+    ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
+    const uint8_t* dp = w->a.as<uint8_t>();
+    if ((rc = launch_search_by_bow(nItems, reinterpret_cast<const int*>(dp + oNode), reinterpret_cast<const uint32_t*>(dp + oI1),
+                                   reinterpret_cast<const int*>(dp + oS2), reinterpret_cast<const uint32_t*>(dp + oI2), n1, dp + oV1,
+                                   dp + oD1, reinterpret_cast<const float*>(dp + oA1), n2, dp + oV2, dp + oD2,
+                                   reinterpret_cast<const float*>(dp + oA2), reinterpret_cast<const int*>(dp + oOff), w->g.as<uint32_t>(),
+                                   w->h.as<int>(), th_dist, nnratio, check_ori, w->out0.as<int>(), w->out1.as<int>(),
+                                   w->status.as<int>(), s)))
+        return rc;
+    int st = 0;
+    ORBX_CUDA(cudaMemcpyAsync(match12, w->out0.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(match21, w->out1.p, (size_t)n2 * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(&st, w->status.p, 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    *nmatches = st;
+    return ORBX_OK;
+}
+
 int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypoint* kL, int nL, const uint8_t* descL,
                       const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float mb, float* u_right, float* depth) {
     ExtractorView L, R;

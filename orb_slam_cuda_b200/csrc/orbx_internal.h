@@ -218,6 +218,10 @@ int launch_search_by_projection_sim3(int n1, const float* uvr, const int* level1
                                      const uint8_t* occupied2, const float bounds[4], int thDist, int* cellOf, int* sorted,
                                      int* cellStart, uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches,
                                      int* dStatus, cudaStream_t s);
+int launch_search_by_bow(int nItems, const int* nodeOf, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                         const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
+                         const uint8_t* desc2, const float* angle2, const int* candOff, uint32_t* cand, int* candCnt, int thDist,
+                         float nnratio, int checkOri, int* match12, int* match21, int* nmatches, cudaStream_t s);
 int launch_stereo(const StereoLevels& lv, const orbx_keypoint* kL, int nL, const uint8_t* dL, const orbx_keypoint* kR, int nR,
                   const uint8_t* dR, float mbf, float maxD, float* uRight, float* depth, int* sad, cudaStream_t s);
 
