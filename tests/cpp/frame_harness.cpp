@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 #include <set>
 #include <string>
 #include <thread>
@@ -41,6 +42,7 @@ struct KeyFrame {  // the members of ORB_SLAM2::KeyFrame that the relocalisation
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<cv::KeyPoint> mvKeysUn;
     std::vector<MapPoint*> GetMapPointMatches() const { return mvpMapPoints; }
+    std::map<unsigned int, std::vector<unsigned int>> mFeatVec;  // DBoW2::FeatureVector (SearchByBoW, src/ORBmatcher.cc:159,522)
     // loop-detection SearchByProjection (src/ORBmatcher.cc:290-403)
     float fx = 0, fy = 0, cx = 0, cy = 0, mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
     std::vector<float> mvScaleFactors;
@@ -50,6 +52,7 @@ struct KeyFrame {  // the members of ORB_SLAM2::KeyFrame that the relocalisation
 
 struct Frame {  // the members of ORB_SLAM2::Frame that the front end reads or writes (include/Frame.h)
     cv::Mat mTcw;
+    std::map<unsigned int, std::vector<unsigned int>> mFeatVec;
     float fx = 0, fy = 0, cx = 0, cy = 0;
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<bool> mvbOutlier;
@@ -234,6 +237,28 @@ int main(int argc, char** argv) {
             const int ns = loopMatcher.SearchByProjection(&KC, Scw, cands, matched, 10);
             put_i(out, ns);
             for (int j = 0; j < Cur.N; ++j) put_i(out, matched[j] ? (int)(matched[j] - points.data()) : -1);
+            // Tracking::TrackReferenceKeyFrame (:842): SearchByBoW(keyframe, frame) with a toy vocabulary — node id = 5 descriptor bits,
+            // features appended in index order as DBoW2 does
+            auto featvec = [](const cv::Mat& D, std::map<unsigned int, std::vector<unsigned int>>& fv) {
+                for (int i = 0; i < D.rows; ++i) fv[(D.at<unsigned char>(i, 5) | (D.at<unsigned char>(i, 17) << 8)) & 31u].push_back(i);
+            };
+            KF.mDescriptors = Last.mDescriptors;
+            featvec(Last.mDescriptors, KF.mFeatVec);
+            featvec(Cur.mDescriptors, Cur.mFeatVec);
+            std::vector<MapPoint*> bowMatches;
+            ORBmatcher bowMatcher(0.7f, true);
+            const int nb = bowMatcher.SearchByBoW(&KF, Cur, bowMatches);
+            put_i(out, nb);
+            for (int j = 0; j < Cur.N; ++j) put_i(out, bowMatches[j] ? (int)(bowMatches[j] - points.data()) : -1);
+            // LoopClosing::ComputeSim3 (:304): SearchByBoW(keyframe, keyframe); the second keyframe holds point j % N1 at keypoint j
+            KC.mFeatVec = Cur.mFeatVec;
+            KC.mvpMapPoints.assign(Cur.N, nullptr);
+            for (int j = 0; j < Cur.N; ++j) if (j % 4 != 0) KC.mvpMapPoints[j] = &points[j % Last.N];
+            std::vector<MapPoint*> matches12;
+            ORBmatcher kfMatcher(0.75f, true);
+            const int nk = kfMatcher.SearchByBoW(&KF, &KC, matches12);
+            put_i(out, nk);
+            for (int i = 0; i < Last.N; ++i) put_i(out, matches12[i] ? (int)(matches12[i] - points.data()) : -1);
             fclose(out);
         } else {
             return 2;

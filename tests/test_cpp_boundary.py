@@ -204,3 +204,18 @@ def test_track_with_motion_model_projection(harness, tmp_path):
     assert rd.i32() == n_ref4
     got4 = rd.arr(np.int32, n2)
     assert np.array_equal(got4, np.where(occ3 == 1, 0, np.where(m_ref4 >= 0, keep[np.maximum(m_ref4, 0)], -1)))
+    # fifth part: SearchByBoW(keyframe, frame) (src/ORBmatcher.cc:159-288), node id = 5 descriptor bits
+    from test_bow import common_nodes, feature_vectors
+    s1, i1, s2, i2 = common_nodes(feature_vectors(d1, 5), feature_vectors(d2, 5))
+    valid_kf = (has_mp & (i % 13 != 0)).astype(np.uint8)
+    n_ref5, _, m21_5 = O.search_by_bow(s1, i1, s2, i2, valid_kf, d1, k1["angle"], np.ones(n2, np.uint8), d2, k2["angle"], 50, 0.7, True)
+    assert n_ref5 > 50
+    assert rd.i32() == n_ref5
+    assert np.array_equal(rd.arr(np.int32, n2), np.where(m21_5 >= 0, m21_5, -1))
+    # sixth part: SearchByBoW(keyframe, keyframe) (:522-655); keypoint j of the second keyframe holds point j % n1
+    j = np.arange(n2)
+    valid_kc = ((j % 4 != 0) & ((j % n1) % 13 != 0)).astype(np.uint8)
+    n_ref6, m12_6, _ = O.search_by_bow(s1, i1, s2, i2, valid_kf, d1, k1["angle"], valid_kc, d2, k2["angle"], 49, 0.75, True)
+    assert n_ref6 > 50
+    assert rd.i32() == n_ref6
+    assert np.array_equal(rd.arr(np.int32, n1), np.where(m12_6 >= 0, np.maximum(m12_6, 0) % n1, -1))
