@@ -35,8 +35,8 @@ WORKLOADS = {  # reference YAMLs: Examples/Monocular/KITTI00-02.yaml, TUM1.yaml,
 SCALE, LEVELS, INI_TH, MIN_TH = 1.2, 8, 20, 7
 # DRAM bytes per frame (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of a 512-frame kitti
 # launch, divided by 512): profiles/r01_ncu_full_b.csv (pyramid, blur) and profiles/r01_ncu_full_c.csv (the others).
-NCU_TRAFFIC_PER_FRAME = {"kitti": {"Pyramid/Resize": 3_425_000, "FAST+Grid": 1_652_000, "Make quadtree": 179_000,
-                                   "Gaussian Blur": 3_282_000, "Compute angle + ORB descriptor + Compute scale": 3_044_000}}
+NCU_TRAFFIC_PER_FRAME = {"kitti": {"Pyramid/Resize": 3_415_000, "FAST+Grid": 1_686_000, "Make quadtree": 182_000,
+                                   "Gaussian Blur": 3_283_000, "Compute angle + ORB descriptor + Compute scale": 3_049_000}}
 METRIC = "frames/s ORB extract @1241x376 2k feats"
 
 

@@ -272,6 +272,80 @@ def search_by_bow(start1, idx1, start2, idx2, valid1, d1, angle1, valid2, d2, an
     return n, m12[:n1], m21[:n2]
 
 
+class Vocabulary:
+    """The node table DBoW2's loadFromTextFile builds (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1424): node 0 = root,
+    then one node per line `parent is_leaf d0 .. d31 weight`; first line `k L scoring weighting`."""
+
+    def __init__(self, k, L, scoring, weighting, parent, is_leaf, desc, weight):
+        self.k, self.L, self.scoring, self.weighting = int(k), int(L), int(scoring), int(weighting)
+        self.parent = np.ascontiguousarray(parent, dtype=np.int32)
+        self.is_leaf = np.ascontiguousarray(is_leaf, dtype=np.uint8)
+        self.desc = np.ascontiguousarray(desc, dtype=np.uint8)
+        self.weight = np.ascontiguousarray(weight, dtype=np.float64)
+
+    @classmethod
+    def from_text(cls, path):
+        with open(path) as f:
+            k, L, n1, n2 = (int(t) for t in f.readline().split())
+            parent, leaf, desc, weight = [-1], [0], [[0] * 32], [0.0]
+            for line in f:
+                t = line.split()
+                if not t:
+                    continue
+                parent.append(int(t[0]))
+                leaf.append(int(t[1]) > 0)
+                desc.append([int(x) for x in t[2:34]])
+                weight.append(float(t[34]))
+        return cls(k, L, n1, n2, parent, leaf, desc, weight)
+
+    def to_text(self, path):
+        with open(path, "w") as f:
+            f.write(f"{self.k} {self.L} {self.scoring} {self.weighting}\n")
+            for i in range(1, self.parent.size):
+                f.write(f"{self.parent[i]} {int(self.is_leaf[i])} " + " ".join(str(int(b)) for b in self.desc[i]) + f" {self.weight[i]!r}\n")
+
+    def transform_features(self, feat, levelsup=4):
+        """transform(feature, word_id, weight, &nid, levelsup), :1218-1261, for every row of feat."""
+        feat = np.ascontiguousarray(feat, dtype=np.uint8)
+        n = feat.shape[0]
+        word, node, w = np.empty(max(n, 1), np.uint32), np.empty(max(n, 1), np.uint32), np.empty(max(n, 1), np.float64)
+        lib().orc_vocabulary_transform(self.parent.size, _p(self.parent), _p(self.is_leaf), _p(self.desc), _p(self.weight), self.L, n,
+                                       _p(feat), int(levelsup), _p(word), _p(w), _p(node))
+        return word[:n], w[:n], node[:n]
+
+    def transform(self, feat, levelsup=4):
+        """transform(features, BowVector&, FeatureVector&, levelsup), :1127-1194, with BowVector::addWeight / addIfNotExist /
+        normalize (Thirdparty/DBoW2/DBoW2/BowVector.cpp:33-88).  Returns (bow: {word: value}, fv: {node: [feature indices]}).
+        A descent that ends above the node level leaves `nid` unwritten in the reference; the value it then adds is the one of
+        the previous feature (the variable's stack slot), 0 before any — restated as such."""
+        word, w, node = self.transform_features(feat, levelsup)
+        bow, fv, nid = {}, {}, 0
+        tf = self.weighting in (0, 1)                    # TF_IDF, TF
+        for i in range(word.size):
+            if node[i] != 0xFFFFFFFF:
+                nid = int(node[i])
+            if w[i] > 0:
+                if tf:
+                    bow[int(word[i])] = bow.get(int(word[i]), 0.0) + float(w[i])
+                else:
+                    bow.setdefault(int(word[i]), float(w[i]))
+                fv.setdefault(nid, []).append(i)
+        must, l1 = self.scoring != 5, self.scoring != 1   # all but DOT_PRODUCT normalise, L2 only for L2_NORM (ScoringObject.h:74-89)
+        if tf and bow and not must:
+            nd = float(len(bow))
+            bow = {k: v / nd for k, v in bow.items()}
+        if must:
+            keys = sorted(bow)
+            norm = 0.0
+            for k in keys:
+                norm += abs(bow[k]) if l1 else bow[k] * bow[k]
+            if not l1:
+                norm = float(np.sqrt(norm))
+            if norm > 0.0:
+                bow = {k: bow[k] / norm for k in keys}
+        return dict(sorted(bow.items())), dict(sorted(fv.items()))
+
+
 def match_bruteforce(q, d, th=50, ratio=0.6):
     q = np.ascontiguousarray(q, dtype=np.uint8)
     d = np.ascontiguousarray(d, dtype=np.uint8)

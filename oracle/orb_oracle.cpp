@@ -1013,4 +1013,40 @@ void stereo_matches(const Extractor& EL, const Extractor& ER, const KeyPoint* kL
     }
 }
 
+// ---- DBoW2 tree descent ---------------------------------------------------------------------------------------------
+// Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1218-1261 (transform of one feature) over the node table of
+// loadFromTextFile (:1338-1424): children in file order (push_back :1388), word ids counted over the leaf-flagged lines
+// (:1406-1413), isLeaf() = children.empty() (:111).  F::distance = FORB::distance, the 256-bit Hamming distance
+// (Thirdparty/DBoW2/DBoW2/FORB.cpp:98-121), compared as double with a strict '<' so the first child wins ties.
+void vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLeaf, const uint8_t* desc, const double* weight, int L,
+                          int n, const uint8_t* feat, int levelsup, uint32_t* wordId, double* w, uint32_t* nodeId) {
+    std::vector<std::vector<int>> children(nNodes);
+    std::vector<uint32_t> word(nNodes, 0);
+    uint32_t nWords = 0;
+    for (int i = 1; i < nNodes; ++i) {
+        children[parent[i]].push_back(i);
+        if (isLeaf[i]) word[i] = nWords++;
+    }
+    const int nidLevel = L - levelsup;
+    for (int f = 0; f < n; ++f) {
+        const uint8_t* a = feat + (size_t)32 * f;
+        uint32_t nid = nidLevel <= 0 ? 0u : 0xFFFFFFFFu;
+        int finalId = 0, level = 0;
+        do {
+            ++level;
+            const std::vector<int>& nodes = children[finalId];
+            finalId = nodes[0];
+            double best = (double)descriptor_distance(a, desc + (size_t)32 * finalId);
+            for (size_t c = 1; c < nodes.size(); ++c) {
+                const double d = (double)descriptor_distance(a, desc + (size_t)32 * nodes[c]);
+                if (d < best) { best = d; finalId = nodes[c]; }
+            }
+            if (level == nidLevel) nid = (uint32_t)finalId;
+        } while (!children[finalId].empty());
+        wordId[f] = word[finalId];
+        w[f] = weight[finalId];
+        nodeId[f] = nid;
+    }
+}
+
 }  // namespace orc

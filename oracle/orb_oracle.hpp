@@ -106,6 +106,12 @@ int search_by_bow(int nNodes, const int* start1, const uint32_t* idx1, const int
                   const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
                   const uint8_t* desc2, const float* angle2, int thDist, float nnratio, bool checkOri, int* match12, int* match21);
 
+// DBoW2 vocabulary tree descent (Frame::ComputeBoW, src/Frame.cc:394-401 -> TemplatedVocabulary::transform).  Nodes as
+// loadFromTextFile numbers them: node 0 = root, node i >= 1 in file order with parent[i], isLeaf[i], desc[32 i], weight[i].
+// nodeId[f] = 0xFFFFFFFF when the descent ends above level L - levelsup (the reference leaves *nid unwritten there).
+void vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLeaf, const uint8_t* desc, const double* weight, int L,
+                          int n, const uint8_t* feat, int levelsup, uint32_t* wordId, double* w, uint32_t* nodeId);
+
 void match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1,
                       int* d2, int* match);
 

@@ -155,6 +155,10 @@ double orc_bench_extract(const uint8_t* frames, int nframes, int w, int h, int n
     if (nk) *nk = s;
     return std::chrono::duration<double>(t1 - t0).count();
 }
+void orc_vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLeaf, const uint8_t* desc, const double* weight, int L,
+                              int n, const uint8_t* feat, int levelsup, uint32_t* wordId, double* w, uint32_t* nodeId) {
+    vocabulary_transform(nNodes, parent, isLeaf, desc, weight, L, n, feat, levelsup, wordId, w, nodeId);
+}
 double orc_bench_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int threads, int* idx, int* d1, int* d2, int* match) {
     auto t0 = std::chrono::steady_clock::now();
     std::vector<std::thread> pool;
