@@ -213,6 +213,30 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
                        const uint8_t* desc2, const float* angle2, int th_dist, float nnratio, int check_ori, int* match12,
                        int* match21, int* nmatches);
 
+/* ---- DBoW2 vocabulary: Frame::ComputeBoW (src/Frame.cc:394-401) -------------------------------------------------------
+ * The tree of TemplatedVocabulary<FORB::TDescriptor, FORB> (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) in device memory
+ * and the descent of transform(feature, word_id, weight, nid, levelsup) (:1218-1261) for a whole frame in one launch.  The
+ * std::map bookkeeping around it (BowVector::addWeight / normalize, FeatureVector::addFeature, :1146-1193) is host code in
+ * include/ORBVocabulary.h. */
+typedef struct orbx_vocabulary orbx_vocabulary;
+
+/* Nodes as loadFromTextFile numbers them (:1338-1424): node 0 = root (its parent / is_leaf / desc / weight entries are ignored),
+ * node i >= 1 = line i+1 of the text file: parent[i] < i, is_leaf[i] (gets the next word id), desc[32 i ..], weight[i].
+ * k, L, scoring, weighting = the four integers of the first line (m_k, m_L, ScoringType, WeightingType). */
+int orbx_vocabulary_create(int k, int L, int scoring, int weighting, int n_nodes, const int32_t* parent, const uint8_t* is_leaf,
+                           const uint8_t* desc, const double* weight, orbx_vocabulary** out);
+/* ORBvocabulary::loadFromTextFile (:1338-1424; called at src/System.cc:66-74), including its reading of the trailing newline
+ * (one extra childless child of the root, weight 0). */
+int orbx_vocabulary_load_text(const char* path, orbx_vocabulary** out);
+void orbx_vocabulary_destroy(orbx_vocabulary* v);
+int orbx_vocabulary_info(const orbx_vocabulary* v, int* k, int* L, int* scoring, int* weighting, int* n_nodes, int* n_words);
+/* For every row of desc[n x 32]: word_id / weight of the leaf the descent ends in and node_id = the node passed at level
+ * L - levelsup (0 when that level is <= 0; ORBX_VOC_NO_NODE when the descent ends above it — the reference leaves *nid
+ * unwritten there).  Host buffers. */
+#define ORBX_VOC_NO_NODE 0xFFFFFFFFu
+int orbx_vocabulary_transform(orbx_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* word_id, double* weight,
+                              uint32_t* node_id);
+
 /* Frame::ComputeStereoMatches (src/Frame.cc:465-639).  exL / exR hold the pyramids of the left / right frame of
  * their last orbx_extract call (device resident; nothing is copied to the host).  bf = mbf (baseline x fx),
  * mb = baseline in metres = mbf / fx (src/Frame.cc:113).  u_right[nL], depth[nL] as mvuRight / mvDepth

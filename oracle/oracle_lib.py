@@ -285,24 +285,36 @@ class Vocabulary:
 
     @classmethod
     def from_text(cls, path):
+        """loadFromTextFile, :1338-1424.  `while(!f.eof()) getline` makes a node of every line AND of the empty remainder after the
+        last newline; a failed `>>` reads 0 (C++11) and fails every later one on that line."""
         with open(path) as f:
-            k, L, n1, n2 = (int(t) for t in f.readline().split())
-            parent, leaf, desc, weight = [-1], [0], [[0] * 32], [0.0]
-            for line in f:
-                t = line.split()
-                if not t:
-                    continue
-                parent.append(int(t[0]))
-                leaf.append(int(t[1]) > 0)
-                desc.append([int(x) for x in t[2:34]])
-                weight.append(float(t[34]))
+            text = f.read()
+        lines = text.split("\n")
+        k, L, n1, n2 = (int(t) for t in lines[0].split())
+        parent, leaf, desc, weight = [-1], [0], [[0] * 32], [0.0]
+        for line in lines[1:]:
+            t = line.split()
+            vals, ok = [], True
+            for i in range(35):
+                if ok and i < len(t):
+                    try:
+                        vals.append(float(t[i]) if i == 34 else int(t[i]))
+                        continue
+                    except ValueError:
+                        ok = False
+                ok = False
+                vals.append(0)
+            parent.append(vals[0])
+            leaf.append(vals[1] > 0)
+            desc.append([v & 0xFF for v in vals[2:34]])
+            weight.append(float(vals[34]))
         return cls(k, L, n1, n2, parent, leaf, desc, weight)
 
     def to_text(self, path):
         with open(path, "w") as f:
             f.write(f"{self.k} {self.L} {self.scoring} {self.weighting}\n")
             for i in range(1, self.parent.size):
-                f.write(f"{self.parent[i]} {int(self.is_leaf[i])} " + " ".join(str(int(b)) for b in self.desc[i]) + f" {self.weight[i]!r}\n")
+                f.write(f"{self.parent[i]} {int(self.is_leaf[i])} " + " ".join(str(int(b)) for b in self.desc[i]) + f" {float(self.weight[i])!r}\n")
 
     def transform_features(self, feat, levelsup=4):
         """transform(feature, word_id, weight, &nid, levelsup), :1218-1261, for every row of feat."""

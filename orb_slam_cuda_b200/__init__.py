@@ -55,6 +55,10 @@ def lib() -> C.CDLL:
         L.orbx_extractor_stream.argtypes = [C.c_void_p]
         L.orbx_extractor_destroy.argtypes = [C.c_void_p]
         L.orbx_extractor_destroy.restype = None
+        L.orbx_vocabulary_destroy.argtypes = [C.c_void_p]
+        L.orbx_vocabulary_destroy.restype = None
+        L.orbx_vocabulary_info.argtypes = [C.c_void_p] + [C.c_void_p] * 6
+        L.orbx_vocabulary_transform.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
 
@@ -350,6 +354,82 @@ class ORBmatcher:
         """score[i, j] = accepted matches of query keyframe i in database keyframe j (device buffers, asynchronous)."""
         _check(lib().orbx_match_allpairs_device(_p(d_q), kq, _p(d_db), kd, n, int(th), C.c_float(self.mfNNratio), _p(d_score),
                                                 _p(stream) if stream else None))
+
+
+class ORBVocabulary:
+    """ORB_SLAM2::ORBVocabulary = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (reference include/ORBVocabulary.h:28-31):
+    the tree lives in device memory, transform() is Frame::ComputeBoW's call (src/Frame.cc:394-401)."""
+
+    def __init__(self, k, L, scoring, weighting, parent, is_leaf, desc, weight, _handle=None):
+        self._h = C.c_void_p()
+        if _handle is not None:
+            self._h = _handle
+            return
+        parent = np.ascontiguousarray(parent, dtype=np.int32)
+        is_leaf = np.ascontiguousarray(is_leaf, dtype=np.uint8)
+        desc = np.ascontiguousarray(desc, dtype=np.uint8)
+        weight = np.ascontiguousarray(weight, dtype=np.float64)
+        _check(lib().orbx_vocabulary_create(int(k), int(L), int(scoring), int(weighting), parent.size, _p(parent), _p(is_leaf), _p(desc),
+                                            _p(weight), C.byref(self._h)))
+
+    @classmethod
+    def loadFromTextFile(cls, path: str):
+        h = C.c_void_p()
+        _check(lib().orbx_vocabulary_load_text(str(path).encode(), C.byref(h)))
+        return cls(0, 0, 0, 0, None, None, None, None, _handle=h)
+
+    def info(self):
+        v = [C.c_int(0) for _ in range(6)]
+        _check(lib().orbx_vocabulary_info(self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("k", "L", "scoring", "weighting", "n_nodes", "n_words"), (x.value for x in v)))
+
+    def transform_features(self, desc, levelsup: int = 4):
+        """(word_id, weight, node_id) per descriptor: transform(feature, id, w, &nid, levelsup), TemplatedVocabulary.h:1218-1261."""
+        desc = np.ascontiguousarray(desc, dtype=np.uint8)
+        n = desc.shape[0]
+        word, node, w = np.empty(max(n, 1), np.uint32), np.empty(max(n, 1), np.uint32), np.empty(max(n, 1), np.float64)
+        _check(lib().orbx_vocabulary_transform(self._h, _p(desc), n, int(levelsup), _p(word), _p(w), _p(node)))
+        return word[:n], w[:n], node[:n]
+
+    def transform(self, desc, levelsup: int = 4):
+        """transform(features, BowVector&, FeatureVector&, levelsup), :1127-1194: ({word: value}, {node: [feature indices]}).
+        The descent runs on the device; the two std::map fills and the normalisation are sequential double arithmetic in feature
+        / word order and stay on the host (same code as include/ORBVocabulary.h)."""
+        info = self.info()
+        word, w, node = self.transform_features(desc, levelsup)
+        bow, fv, nid = {}, {}, 0
+        tf = info["weighting"] in (0, 1)
+        for i in range(word.size):
+            if node[i] != 0xFFFFFFFF:
+                nid = int(node[i])
+            if w[i] > 0:
+                if tf:
+                    bow[int(word[i])] = bow.get(int(word[i]), 0.0) + float(w[i])
+                else:
+                    bow.setdefault(int(word[i]), float(w[i]))
+                fv.setdefault(nid, []).append(i)
+        must, l1 = info["scoring"] != 5, info["scoring"] != 1
+        if tf and bow and not must:
+            nd = float(len(bow))
+            bow = {k: v / nd for k, v in bow.items()}
+        if must:
+            keys = sorted(bow)
+            norm = 0.0
+            for k in keys:
+                norm += abs(bow[k]) if l1 else bow[k] * bow[k]
+            if not l1:
+                norm = float(np.sqrt(norm))
+            if norm > 0.0:
+                bow = {k: bow[k] / norm for k in keys}
+        return dict(sorted(bow.items())), dict(sorted(fv.items()))
+
+    def __del__(self):
+        try:
+            if self._h:
+                lib().orbx_vocabulary_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
 
 
 def ComputeStereoMatches(exL: ORBextractor, exR: ORBextractor, kpsL, descL, kpsR, descR, bf: float, fx: float):

@@ -6,6 +6,7 @@
 // Input: a raw file of 8-bit frames; output: a raw dump that tests/test_cpp_boundary.py compares with the CPU oracle.
 //   frame_harness mono   in.raw w h nfeatures out.bin          (two frames: extraction + SearchForInitialization)
 //   frame_harness stereo in.raw w h nfeatures bf fx out.bin    (left, right: extraction + ComputeStereoMatches)
+//   frame_harness bow    in.raw w h nfeatures voc.txt out.bin  (System.cc:64 loadFromTextFile, Frame::ComputeBoW, SearchByBoW)
 //   frame_harness track  in.raw w h nfeatures th out.bin       (last, current: Tracking::TrackWithMotionModel's SearchByProjection, :962)
 #include <cstdio>
 #include <cstdlib>
@@ -17,6 +18,7 @@
 #include <vector>
 
 #include "ORBextractor.h"
+#include "ORBVocabulary.h"
 #include "ORBmatcher.h"
 
 using namespace ORB_SLAM2;
@@ -52,7 +54,9 @@ struct KeyFrame {  // the members of ORB_SLAM2::KeyFrame that the relocalisation
 
 struct Frame {  // the members of ORB_SLAM2::Frame that the front end reads or writes (include/Frame.h)
     cv::Mat mTcw;
-    std::map<unsigned int, std::vector<unsigned int>> mFeatVec;
+    std::map<unsigned int, std::vector<unsigned int>> mFeatVec;  // DBoW2::FeatureVector
+    std::map<unsigned int, double> mBowVec;                      // DBoW2::BowVector
+    ORBVocabulary* mpORBvocabulary = nullptr;
     float fx = 0, fy = 0, cx = 0, cy = 0;
     std::vector<MapPoint*> mvpMapPoints;
     std::vector<bool> mvbOutlier;
@@ -259,6 +263,55 @@ int main(int argc, char** argv) {
             const int nk = kfMatcher.SearchByBoW(&KF, &KC, matches12);
             put_i(out, nk);
             for (int i = 0; i < Last.N; ++i) put_i(out, matches12[i] ? (int)(matches12[i] - points.data()) : -1);
+            fclose(out);
+        } else if (mode == "bow" && argc >= 8) {
+            // System.cc:64-65 loads the vocabulary, Frame::ComputeBoW (src/Frame.cc:394-401) fills mBowVec / mFeatVec of two frames,
+            // Tracking::TrackReferenceKeyFrame (:842) matches them with SearchByBoW
+            FILE* out = fopen(argv[7], "wb");
+            ORBVocabulary voc;
+            if (!voc.loadFromTextFile(argv[6])) { fprintf(stderr, "cannot load %s: %s\n", argv[6], orbx_last_error()); return 1; }
+            ORBVocabulary none;
+            put_i(out, none.loadFromTextFile(std::string(argv[6]) + ".missing") ? 1 : 0);
+            put_i(out, (int)voc.size());
+            ORBextractor ex(nf, 1.2f, 8, 20, 7, w, h);
+            Frame F1, F2;
+            F1.mpORBextractorLeft = F2.mpORBextractorLeft = &ex;
+            F1.mpORBvocabulary = F2.mpORBvocabulary = &voc;
+            F1.ExtractORB(0, im0);
+            F2.ExtractORB(0, im1);
+            for (Frame* F : {&F1, &F2}) {
+                F->mvKeysUn = F->mvKeys;
+                F->N = (int)F->mvKeys.size();
+                ComputeBoW(*F);
+                put_keys(out, F->mvKeys, F->mDescriptors);
+                put_i(out, (int)F->mBowVec.size());
+                for (const auto& kv : F->mBowVec) { put_i(out, (int)kv.first); put(out, &kv.second, 8); }
+                put_i(out, (int)F->mFeatVec.size());
+                for (const auto& kv : F->mFeatVec) {
+                    put_i(out, (int)kv.first); put_i(out, (int)kv.second.size());
+                    put(out, kv.second.data(), kv.second.size() * 4);
+                }
+            }
+            // the vector<cv::Mat> form Frame::ComputeBoW uses (Converter::toDescriptorVector) gives the same maps
+            std::vector<cv::Mat> rows;
+            for (int i = 0; i < F1.mDescriptors.rows; ++i) rows.push_back(F1.mDescriptors.row(i));
+            std::map<unsigned int, double> bow2;
+            std::map<unsigned int, std::vector<unsigned int>> fv2;
+            voc.transform(rows, bow2, fv2, 4);
+            put_i(out, bow2 == F1.mBowVec && fv2 == F1.mFeatVec ? 1 : 0);
+            std::vector<MapPoint> points(F1.N);
+            KeyFrame KF;
+            KF.mvKeysUn = F1.mvKeysUn; KF.mDescriptors = F1.mDescriptors; KF.mFeatVec = F1.mFeatVec;
+            KF.mvpMapPoints.assign(F1.N, nullptr);
+            for (int i = 0; i < F1.N; ++i) {
+                points[i].mbBad = i % 13 == 0;
+                if (i % 5 != 0) KF.mvpMapPoints[i] = &points[i];
+            }
+            std::vector<MapPoint*> matches;
+            ORBmatcher matcher(0.7f, true);
+            const int n = matcher.SearchByBoW(&KF, F2, matches);
+            put_i(out, n);
+            for (int j = 0; j < F2.N; ++j) put_i(out, matches[j] ? (int)(matches[j] - points.data()) : -1);
             fclose(out);
         } else {
             return 2;

@@ -219,3 +219,54 @@ def test_track_with_motion_model_projection(harness, tmp_path):
     assert n_ref6 > 50
     assert rd.i32() == n_ref6
     assert np.array_equal(rd.arr(np.int32, n1), np.where(m12_6 >= 0, np.maximum(m12_6, 0) % n1, -1))
+
+
+@pytest.mark.gpu
+def test_compute_bow_and_search_by_bow(harness, tmp_path):
+    """ORBVocabulary::loadFromTextFile + Frame::ComputeBoW + ORBmatcher::SearchByBoW through include/ORBVocabulary.h and
+    include/ORBmatcher.h (tests/cpp/frame_harness.cpp, mode `bow`): BowVector doubles, FeatureVector lists and the matches equal
+    the oracle's on the same text vocabulary."""
+    from test_bow import common_nodes
+    from test_vocabulary import make_vocabulary
+    kind, nf = "tum", 1000
+    a, b = synth.frame(kind, 41), synth.shifted_frame(kind, 41)
+    h, w = a.shape
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(a.tobytes() + b.tobytes())
+    # a vocabulary whose level-1..3 centroids are ORB descriptors of a third image, so real descriptors spread over the tree
+    _, seed_desc = O.Extractor(1000, 1.2, 8, 20, 7).extract(synth.frame(kind, 7))
+    voc = make_vocabulary(21, 8, 3, p_early=0.05)
+    rng = np.random.default_rng(5)
+    voc.desc[1:] = seed_desc[rng.integers(0, seed_desc.shape[0], voc.desc.shape[0] - 1)]
+    path = tmp_path / "ORBvoc.txt"
+    voc.to_text(path)
+    ref = O.Vocabulary.from_text(path)
+    out = tmp_path / "out.bin"
+    r = subprocess.run([harness, "bow", str(raw), str(w), str(h), str(nf), str(path), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    rd = Reader(out.read_bytes())
+    assert rd.i32() == 0                       # a missing file: loadFromTextFile returns false
+    assert rd.i32() == int(ref.is_leaf[1:].sum())
+    frames = []
+    for _ in range(2):
+        k, d = rd.keys()
+        ref_bow, ref_fv = ref.transform(d, 4)
+        nb = rd.i32()
+        assert nb == len(ref_bow) > 20
+        for word, val in ref_bow.items():
+            assert rd.i32() == word
+            assert rd.arr(np.uint64, 1)[0] == np.float64(val).view(np.uint64)
+        assert rd.i32() == len(ref_fv)
+        for node, idx in ref_fv.items():
+            assert rd.i32() == node and rd.i32() == len(idx)
+            assert list(rd.arr(np.uint32, len(idx))) == idx
+        frames.append((k, d, {n: np.array(v, np.uint32) for n, v in ref_fv.items()}))
+    assert rd.i32() == 1                       # transform(vector<cv::Mat>) == transform_rows
+    (k1, d1, fv1), (k2, d2, fv2) = frames
+    s1, i1, s2, i2 = common_nodes(fv1, fv2)
+    i = np.arange(len(k1))
+    valid1 = ((i % 5 != 0) & (i % 13 != 0)).astype(np.uint8)
+    n_ref, _, m21 = O.search_by_bow(s1, i1, s2, i2, valid1, d1, k1["angle"], np.ones(len(k2), np.uint8), d2, k2["angle"], 50, 0.7, True)
+    assert n_ref > 30
+    assert rd.i32() == n_ref
+    assert np.array_equal(rd.arr(np.int32, len(k2)), np.where(m21 >= 0, m21, -1))
