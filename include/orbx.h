@@ -225,8 +225,9 @@ typedef struct orbx_vocabulary orbx_vocabulary;
  * k, L, scoring, weighting = the four integers of the first line (m_k, m_L, ScoringType, WeightingType). */
 int orbx_vocabulary_create(int k, int L, int scoring, int weighting, int n_nodes, const int32_t* parent, const uint8_t* is_leaf,
                            const uint8_t* desc, const double* weight, orbx_vocabulary** out);
-/* ORBvocabulary::loadFromTextFile (:1338-1424; called at src/System.cc:66-74), including its reading of the trailing newline
- * (one extra childless child of the root, weight 0). */
+/* ORBvocabulary::loadFromTextFile (:1338-1424; called at src/System.cc:64-65).  Blank lines make no node: on the empty
+ * remainder after the file's last newline the reference reads `pid` uninitialised (undefined behaviour), which is not
+ * reproduced.  ORBX_E_INVALID for a file that is not a DBoW2 text vocabulary. */
 int orbx_vocabulary_load_text(const char* path, orbx_vocabulary** out);
 void orbx_vocabulary_destroy(orbx_vocabulary* v);
 int orbx_vocabulary_info(const orbx_vocabulary* v, int* k, int* L, int* scoring, int* weighting, int* n_nodes, int* n_words);

@@ -111,6 +111,7 @@ public:
     Mat rowRange(int a, int b) const { return roi(a, b, 0, cols); }
     Mat colRange(int a, int b) const { return roi(0, rows, a, b); }
     Mat operator()(const Range& rr, const Range& cr) const { return roi(rr.start, rr.end, cr.start, cr.end); }
+    static Mat zeros(int r, int c, int type) { return Mat(r, c, type); }  // create() value-initialises its storage
     Mat clone() const {
         Mat m(rows, cols, type_);
         for (int r = 0; r < rows; ++r) std::memcpy(m.ptr(r), ptr(r), (size_t)cols * elemSize());

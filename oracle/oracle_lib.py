@@ -285,8 +285,9 @@ class Vocabulary:
 
     @classmethod
     def from_text(cls, path):
-        """loadFromTextFile, :1338-1424.  `while(!f.eof()) getline` makes a node of every line AND of the empty remainder after the
-        last newline; a failed `>>` reads 0 (C++11) and fails every later one on that line."""
+        """loadFromTextFile, :1338-1424: one node per line.  The reference's `while(!f.eof()) getline` also runs on the empty
+        remainder after the last newline, where `ssnode >> pid` fails in the sentry and pid / nIsLeaf stay uninitialised
+        (undefined behaviour; checked against the compiled reference: stale value or crash) — blank lines make no node here."""
         with open(path) as f:
             text = f.read()
         lines = text.split("\n")
@@ -294,27 +295,21 @@ class Vocabulary:
         parent, leaf, desc, weight = [-1], [0], [[0] * 32], [0.0]
         for line in lines[1:]:
             t = line.split()
-            vals, ok = [], True
-            for i in range(35):
-                if ok and i < len(t):
-                    try:
-                        vals.append(float(t[i]) if i == 34 else int(t[i]))
-                        continue
-                    except ValueError:
-                        ok = False
-                ok = False
-                vals.append(0)
-            parent.append(vals[0])
-            leaf.append(vals[1] > 0)
-            desc.append([v & 0xFF for v in vals[2:34]])
-            weight.append(float(vals[34]))
+            if not t:
+                continue
+            parent.append(int(t[0]))
+            leaf.append(int(t[1]) > 0)
+            desc.append([int(x) & 0xFF for x in t[2:34]])
+            weight.append(float(t[34]))
         return cls(k, L, n1, n2, parent, leaf, desc, weight)
 
-    def to_text(self, path):
+    def to_text(self, path, trailing_newline=True):
+        """saveToTextFile's format (:1429-1450); it ends every line, the last one too, with a newline."""
+        rows = [f"{self.k} {self.L} {self.scoring} {self.weighting}"]
+        for i in range(1, self.parent.size):
+            rows.append(f"{self.parent[i]} {int(self.is_leaf[i])} " + " ".join(str(int(b)) for b in self.desc[i]) + f" {float(self.weight[i])!r}")
         with open(path, "w") as f:
-            f.write(f"{self.k} {self.L} {self.scoring} {self.weighting}\n")
-            for i in range(1, self.parent.size):
-                f.write(f"{self.parent[i]} {int(self.is_leaf[i])} " + " ".join(str(int(b)) for b in self.desc[i]) + f" {float(self.weight[i])!r}\n")
+            f.write("\n".join(rows) + ("\n" if trailing_newline else ""))
 
     def transform_features(self, feat, levelsup=4):
         """transform(feature, word_id, weight, &nid, levelsup), :1218-1261, for every row of feat."""

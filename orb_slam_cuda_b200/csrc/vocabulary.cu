@@ -112,7 +112,7 @@ int build(orbx_vocabulary* v, int nNodes, const int32_t* parent, const uint8_t* 
     return ORBX_OK;
 }
 
-// One `ssnode >> value` after another: once an extraction fails the stream stays failed and (C++11) every later target reads 0.
+// One `ssnode >> value` after another; `failed` once a token is missing or does not parse.
 struct Tokens {
     const char* p;
     const char* end;
@@ -206,31 +206,41 @@ int orbx_vocabulary_load_text(const char* path, orbx_vocabulary** out) {
     std::vector<int32_t> parent(1, -1);
     std::vector<uint8_t> leaf(1, 0), desc(32, 0);
     std::vector<double> weight(1, 0.0);
-    // `while(!f.eof()) getline(...)` (:1377-1380): every '\n'-terminated line makes a node, and so does the empty remainder after
-    // the last '\n' — the trailing newline saveToTextFile writes yields one extra childless root child with weight 0 and word
-    // id 0 (all extractions fail and read 0).  Its descriptor bytes are never written by the reference (FORB.cpp:131-132 skips
-    // failed reads of a fresh cv::Mat), i.e. indeterminate there; zero here.
+    // One node per line (:1377-1417).  `while(!f.eof()) getline(...)` also runs once more on the empty remainder after the last
+    // newline that saveToTextFile writes; there `ssnode >> pid` fails in the stream's sentry (nothing but end-of-file to skip), so
+    // neither pid nor nIsLeaf is ever written and the reference indexes m_nodes with an uninitialised int — undefined behaviour
+    // (observed with gcc: a stale value of the previous line, or a crash).  A line without any token therefore makes no node
+    // here; a line that starts but does not parse is an error.
     bool more = nl != nullptr;
     p = nl ? nl + 1 : end;
+    int lineNo = 1;
     while (more) {
         nl = (const char*)memchr(p, '\n', end - p);
         Tokens t{p, nl ? nl : end};
+        more = nl != nullptr;
+        p = nl ? nl + 1 : end;
+        ++lineNo;
+        const char *tb, *te;
+        Tokens probe = t;
+        if (!probe.next(&tb, &te)) continue;  // blank line
         const long pid = t.integer();
         const long isLeaf = t.integer();
         uint8_t d[32];
         for (int i = 0; i < 32; ++i) d[i] = (uint8_t)t.integer();  // FORB::fromString (FORB.cpp:120-135): int -> unsigned char
         const double w = t.real();
         const int nid = (int)parent.size();
+        if (t.failed) {
+            set_error("orbx_vocabulary_load_text: line %d is not `parent is_leaf d0 .. d31 weight`", lineNo);
+            return ORBX_E_INVALID;
+        }
         if (pid < 0 || pid >= nid) {
-            set_error("orbx_vocabulary_load_text: line %d names parent %ld before it exists", nid + 1, pid);
+            set_error("orbx_vocabulary_load_text: line %d names parent %ld before it exists", lineNo, pid);
             return ORBX_E_INVALID;
         }
         parent.push_back((int32_t)pid);
         leaf.push_back(isLeaf > 0);
         desc.insert(desc.end(), d, d + 32);
         weight.push_back(w);
-        more = nl != nullptr;
-        p = nl ? nl + 1 : end;
     }
     return orbx_vocabulary_create(k, L, n1, n2, (int)parent.size(), parent.data(), leaf.data(), desc.data(), weight.data(), out);
 }
