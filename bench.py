@@ -194,7 +194,7 @@ def match_leg(X, torch, dist, rank, world, stream, K):
             "unit": "Gmatch/s (descriptor pairs compared / s / 1e9)"}
 
 
-def latency_leg(X, wl, w, h, kind):
+def latency_leg(X, wl, w, h, kind, cpu=False):
     """p50 / p95 wall-clock latency of single-frame orbx_extract calls (pageable host frame in, keypoints + descriptors
     out; what ORBextractor::operator() costs the Tracking thread per frame)."""
     from orb_slam_cuda_b200 import synth
@@ -253,6 +253,113 @@ def latency_leg(X, wl, w, h, kind):
 
     out["search_for_initialization_2000x2000"] = {"p50_ms": p50(run_sfi), "matches": int(sfi["n"]),
                                                    "what": "host buffers in and out, window 100, TH_LOW 50, ratio 0.9, rotation check"}
+    out["tracking"] = tracking_leg(X, k1, d1, k2, d2, bounds, p50, cpu)
+    return out
+
+
+def orbvoc_shaped_vocabulary(k=10, L=6, seed=3):
+    """A synthetic tree with ORBvoc.txt's shape (k = 10, L = 6: 1 111 110 nodes, 10^6 words, 35 MB of descriptors), numbered level
+    by level; a child's descriptor is its parent's with 96 / level random bits flipped."""
+    rng = np.random.default_rng(seed)
+    parent, desc = [np.array([-1], np.int32)], [np.zeros((1, 32), np.uint8)]
+    base, n = 0, 1
+    for level in range(1, L + 1):
+        par = base + np.repeat(np.arange(n, dtype=np.int32), k)
+        if level == 1:
+            d = rng.integers(0, 256, (n * k, 32), dtype=np.uint8)
+        else:
+            nb = max(96 // level, 8)
+            flips = np.zeros((n * k, 32), np.uint8)
+            pos = rng.integers(0, 256, (n * k, nb))
+            np.bitwise_or.at(flips, (np.repeat(np.arange(n * k), nb), (pos >> 3).ravel()), (1 << (pos & 7)).astype(np.uint8).ravel())
+            d = np.repeat(desc[-1], k, axis=0) ^ flips
+        parent.append(par)
+        desc.append(d)
+        base += n
+        n *= k
+    parent, desc = np.concatenate(parent), np.concatenate(desc)
+    leaf = np.zeros(parent.size, np.uint8)
+    leaf[-n:] = 1
+    weight = np.zeros(parent.size, np.float64)
+    weight[-n:] = rng.uniform(0.5, 12.0, n)
+    return k, L, parent, leaf, desc, weight
+
+
+def tracking_leg(X, k1, d1, k2, d2, bounds, p50, cpu):
+    """The per-frame matchers that follow extraction in Tracking on two 2000-feature KITTI frames:
+    SearchByProjection (TrackWithMotionModel, src/Tracking.cc:962), Frame::ComputeBoW and SearchByBoW (TrackReferenceKeyFrame, :842).
+    cpu_port_ms = the oracle's restatement of the same routine on one host thread (what the Tracking thread pays in the reference)."""
+    out = {}
+    n1, n2 = k1.size, k2.size
+    cam = (718.856, 718.856, 607.1928, 185.2157)
+    z = np.full(n1, 10.0, np.float32)
+    x3 = np.stack([(k1["x"] + 7.0 - cam[2]) * z / cam[0], (k1["y"] - 4.0 - cam[3]) * z / cam[1], z], 1).astype(np.float32)
+    one1, zero2 = np.ones(n1, np.uint8), np.zeros(n2, np.uint8)
+    sf = (np.float32(SCALE) ** np.arange(LEVELS, dtype=np.float32)).astype(np.float32)
+    m = X.ORBmatcher(0.9, True)
+    r = {}
+
+    def run_sbp():
+        r["sbp"] = m.SearchByProjection(x3, one1, one1, d1, k1["octave"], k1["angle"], k2, d2, None, zero2, cam, 386.1448, bounds, sf,
+                                        15.0, 0)
+
+    out["search_by_projection_2000"] = {"p50_ms": p50(run_sbp), "matches": int(r["sbp"][0]),
+                                        "what": "frame-to-frame, th 15, mono, TH_HIGH 100, rotation check; host buffers in and out"}
+    k, L, parent, leaf, desc, weight = orbvoc_shaped_vocabulary()
+    voc = X.ORBVocabulary(k, L, 0, 0, parent, leaf, desc, weight)
+    # features that descend like real ones: leaf descriptors of the tree with a few bits flipped
+    rng = np.random.default_rng(8)
+    f1 = desc[-rng.integers(1, 10 ** L, n1)] ^ (rng.integers(0, 256, (n1, 32), dtype=np.uint8) & rng.integers(0, 256, (n1, 32), dtype=np.uint8)
+                                                 & rng.integers(0, 256, (n1, 32), dtype=np.uint8) & rng.integers(0, 256, (n1, 32), dtype=np.uint8))
+    f2 = f1[rng.permutation(n1)[:n2] if n2 <= n1 else rng.integers(0, n1, n2)] ^ (1 << rng.integers(0, 8, (n2, 32))).astype(np.uint8) * (rng.random((n2, 32)) < 0.1)
+
+    def run_bow():
+        r["bow"] = voc.transform_features(f1, 4)
+
+    out["compute_bow_2000"] = {"p50_ms": p50(run_bow), "words": int(np.unique(r["bow"][0]).size),
+                               "what": "DBoW2 descent of 2000 descriptors, synthetic tree of ORBvoc's shape (k 10, L 6, 1.1 M nodes), levelsup 4; "
+                                       "device part of Frame::ComputeBoW (the std::map fills stay on the host)"}
+
+    def node_lists(node):
+        order = np.argsort(node, kind="stable")
+        ids, start = np.unique(node[order], return_index=True)
+        return ids, np.append(start, node.size).astype(np.int32), order.astype(np.uint32)
+
+    na, sa, ia = node_lists(voc.transform_features(f1, 4)[2])
+    nb, sb, ib = node_lists(voc.transform_features(f2, 4)[2])
+    common, pa, pb = np.intersect1d(na, nb, return_indices=True)
+    s1 = np.concatenate([[0], np.cumsum(sa[pa + 1] - sa[pa])]).astype(np.int32)
+    s2 = np.concatenate([[0], np.cumsum(sb[pb + 1] - sb[pb])]).astype(np.int32)
+    i1 = np.concatenate([ia[sa[p]:sa[p + 1]] for p in pa]) if common.size else np.zeros(0, np.uint32)
+    i2 = np.concatenate([ib[sb[p]:sb[p + 1]] for p in pb]) if common.size else np.zeros(0, np.uint32)
+    a1 = np.resize(k1["angle"], n1).astype(np.float32)
+    a2 = np.resize(k2["angle"], n2).astype(np.float32)
+    mb = X.ORBmatcher(0.7, True)
+    one2 = np.ones(n2, np.uint8)
+
+    def run_sbb():
+        r["sbb"] = mb.SearchByBoW(s1, i1, s2, i2, one1, f1, a1, one2, f2, a2, 50)
+
+    out["search_by_bow_2000"] = {"p50_ms": p50(run_sbb), "matches": int(r["sbb"][0]), "common_nodes": int(common.size),
+                                 "what": "keyframe vs frame over the common level-2 nodes, TH_LOW 50, ratio 0.7, rotation check; host buffers"}
+    if cpu:
+        from oracle import oracle_lib as O  # the CPU port, timed as the baseline of these rows
+
+        def t_ms(fn, n=5):
+            fn()
+            t = []
+            for _ in range(n):
+                t0 = time.perf_counter()
+                fn()
+                t.append((time.perf_counter() - t0) * 1e3)
+            return float(np.sort(np.array(t))[n // 2])
+
+        out["search_by_projection_2000"]["cpu_port_ms"] = t_ms(lambda: O.search_by_projection_frame(
+            x3, one1, one1, d1, k1["octave"], k1["angle"], k2, d2, None, zero2, cam, 386.1448, bounds, sf, 15.0, 0, True))
+        ov = O.Vocabulary(k, L, 0, 0, parent, leaf, desc, weight)
+        # the oracle rebuilds its child lists on every call; a 1-feature call measures that and is subtracted
+        out["compute_bow_2000"]["cpu_port_ms"] = max(t_ms(lambda: ov.transform_features(f1, 4), 5) - t_ms(lambda: ov.transform_features(f1[:1], 4), 5), 0.0)
+        out["search_by_bow_2000"]["cpu_port_ms"] = t_ms(lambda: O.search_by_bow(s1, i1, s2, i2, one1, f1, a1, one2, f2, a2, 50, 0.7, True))
     return out
 
 
@@ -430,7 +537,7 @@ def run_ours(args, emit=print):
         match["popc_bound"] = "148 SMs x 16 POPC/clk/SM x SM clock / 8 POPC per pair (x N GPUs)"
         line["match"] = match
     if world == 1:
-        line["latency"] = latency_leg(X, wl, w, h, args.workload)
+        line["latency"] = latency_leg(X, wl, w, h, args.workload, cpu=not args.no_cpu_baseline and world == 1)
     if not args.no_cpu_baseline and world == 1:
         threads = host_threads()
         n = args.cpu_frames or max(threads, 16 * threads)

@@ -9,8 +9,10 @@
 //   k_bow_candidates (warp per first-argument feature, in the reference's iteration order): distances to the valid
 //                    second-argument features of its node, stored in visiting order as (dist << 16 | i2)
 //   k_bow_resolve    (1 warp): replays the loop — two smallest free candidates, threshold, ratio test against 256 when
-//                    there is no second (:200-202), assignment, rotation histogram, ComputeThreeMaxima, removals.
+//                    there is no second (:200-202), assignment, rotation histogram, ComputeThreeMaxima, removals; 32 features
+//                    are scanned in parallel, then decided in order (resolve_common.cuh).
 #include "orbx_internal.h"
+#include "resolve_common.cuh"
 
 namespace orbx {
 
@@ -31,6 +33,8 @@ __global__ void __launch_bounds__(256) k_bow_candidates(int nItems, const int* _
     if (item >= nItems) return;
     const int i1 = (int)idx1[item];
     int count = 0;
+    Top4 mine;
+    mine.clear();
     if (valid1[i1]) {
         const int node = nodeOf[item];
         const uint4 a0 = desc1[2 * i1], a1 = desc1[2 * i1 + 1];
@@ -46,107 +50,115 @@ __global__ void __launch_bounds__(256) k_bow_candidates(int nItems, const int* _
                 if (ok) dist = hamming32(a0, a1, desc2[2 * i2], desc2[2 * i2 + 1]);
             }
             const uint32_t m = __ballot_sync(0xffffffffu, ok);
-            if (ok) out[count + __popc(m & ((1u << lane) - 1))] = ((uint32_t)dist << 16) | (uint32_t)i2;
+            if (ok) {
+                const int o = count + __popc(m & ((1u << lane) - 1));
+                out[o] = ((uint32_t)dist << 16) | (uint32_t)i2;
+                mine.push(((uint32_t)dist << 16) | (uint32_t)o, (uint32_t)i2, true);
+            }
             count += __popc(m);
         }
     }
     if (lane == 0) candCnt[item] = count;
+    warp_store_top(mine, lane, candCnt, nItems, item);
 }
 
-// Dynamic shared memory: taken[n2] (uint8), evBin[nItems] (int8).  match12 / match21 live in global memory.
-__global__ void __launch_bounds__(32) k_bow_resolve(int nItems, const uint32_t* __restrict__ idx1, const float* __restrict__ angle1,
-                                                     const float* __restrict__ angle2, int n1, int n2,
-                                                     const int* __restrict__ candOff, const uint32_t* __restrict__ cand,
-                                                     const int* __restrict__ candCnt, int thDist, float nnratio, int checkOri,
-                                                     int* __restrict__ match12, int* __restrict__ match21,
-                                                     int* __restrict__ nmatchesOut) {
+// One CTA: warp 0 replays the loop on shared memory only (taken[n2] uint8, evI2[nItems] uint16 = the keypoint an item
+// accepted); all warps clear the outputs before and, after it, write match12 / match21, bin the rotations and apply
+// ComputeThreeMaxima.  Dynamic shared memory: hist[32] int, claim[n2] int, evI2[nItems] uint16, taken[n2] uint8, evBin[nItems] int8.
+constexpr int BOW_RESOLVE_THREADS = 256;
+__global__ void __launch_bounds__(BOW_RESOLVE_THREADS) k_bow_resolve(int nItems, const uint32_t* __restrict__ idx1,
+                                                                     const float* __restrict__ angle1, const float* __restrict__ angle2,
+                                                                     int n1, int n2, const int* __restrict__ candOff,
+                                                                     const uint32_t* __restrict__ cand, const int* __restrict__ candCnt,
+                                                                     int thDist, float nnratio, int checkOri, int* __restrict__ match12,
+                                                                     int* __restrict__ match21, int* __restrict__ nmatchesOut) {
     extern __shared__ __align__(16) uint8_t sm[];
-    uint8_t* taken = sm;
-    signed char* evBin = reinterpret_cast<signed char*>(sm + n2);
-    const int lane = threadIdx.x;
-    for (int i = lane; i < n2; i += 32) { taken[i] = 0; match21[i] = -1; }
-    for (int i = lane; i < n1; i += 32) match12[i] = -1;
-    for (int i = lane; i < nItems; i += 32) evBin[i] = -1;
-    __syncwarp();
+    int* hist = reinterpret_cast<int*>(sm);
+    int* claim = hist + 32;
+    uint16_t* evI2 = reinterpret_cast<uint16_t*>(claim + n2);
+    uint8_t* taken = reinterpret_cast<uint8_t*>(evI2 + nItems + (nItems & 1));
+    signed char* evBin = reinterpret_cast<signed char*>(taken + n2);
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int i = tid; i < n2; i += BOW_RESOLVE_THREADS) { taken[i] = 0; claim[i] = RS_CLAIM_FREE; match21[i] = -1; }
+    for (int i = tid; i < n1; i += BOW_RESOLVE_THREADS) match12[i] = -1;
+    for (int i = tid; i < nItems; i += BOW_RESOLVE_THREADS) { evI2[i] = 0xFFFFu; evBin[i] = -1; }
+    if (tid < 32) hist[tid] = 0;
+    __syncthreads();
+    if (tid < 32) {
+        auto isFree = [&](uint32_t i2, uint32_t) { return taken[i2] == 0; };
+        int cntNext;
+        TopK topNext;
+        fetch_feature(candCnt, nItems, lane, cntNext, topNext);
+        for (int base = 0; base < nItems; base += 32) {
+            // lane = feature base + lane; its best candidates come from k_bow_candidates (resolve_common.cuh)
+            const int item = base + lane;
+            const int cnt = cntNext;
+            const TopK top = topNext;
+            fetch_feature(candCnt, nItems, item + 32, cntNext, topNext);
+            const uint32_t* c = cand;  // only the rescan needs the list
+            // decide + commit rounds, shared memory only
+            resolve_rounds(
+                __ballot_sync(0xffffffffu, cnt > 0), lane, claim,
+                [&](uint32_t& b1, uint32_t& i2a, uint32_t& b2, uint32_t& i2b) {
+                    if (!top.pick(isFree, 2, b1, i2a, b2, i2b)) rescan_list(c + candOff[item], cnt, isFree, b1, i2a, b2, i2b);
+                    const int best = (int)(b1 >> 16);
+                    const int second = b2 == RS_NONE ? 256 : (int)(b2 >> 16);
+                    return b1 != RS_NONE && best <= thDist && (float)best < __fmul_rn(nnratio, (float)second);
+                },
+                [&](uint32_t, uint32_t i2a, uint32_t, uint32_t) {
+                    taken[i2a] = 1;
+                    evI2[item] = (uint16_t)i2a;
+                });
+        }
+    }
+    __syncthreads();
+    // every keypoint is accepted at most once (taken), so the writes below do not collide
     const float factor = 1.0f / 30.0f;
     int total = 0;
-    for (int item = 0; item < nItems; ++item) {
-        const int cnt = candCnt[item];
-        if (cnt == 0) continue;
-        const uint32_t* c = cand + candOff[item];
-        uint32_t b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;
-        for (int p = lane; p < cnt; p += 32) {
-            const uint32_t e = c[p];
-            if (taken[e & 0xFFFFu]) continue;
-            const uint32_t key = ((e >> 16) << 16) | (uint32_t)p;
-            if (key < b1) { b2 = b1; b1 = key; }
-            else if (key < b2) b2 = key;
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const uint32_t o1 = __shfl_xor_sync(0xffffffffu, b1, o), o2 = __shfl_xor_sync(0xffffffffu, b2, o);
-            const uint32_t lo = min(b1, o1), hi = max(b1, o1);
-            b2 = min(hi, min(b2, o2));
-            b1 = lo;
-        }
-        if (b1 == 0xFFFFFFFFu) continue;
-        const int best = (int)(b1 >> 16);
-        if (best > thDist) continue;
-        const int second = b2 == 0xFFFFFFFFu ? 256 : (int)(b2 >> 16);
-        if (!((float)best < __fmul_rn(nnratio, (float)second))) continue;
-        if (lane == 0) {
-            const int i1 = (int)idx1[item], i2 = (int)(c[b1 & 0xFFFFu] & 0xFFFFu);
-            match12[i1] = i2;
-            match21[i2] = i1;
-            taken[i2] = 1;
-            if (checkOri) {
-                float rot = __fsub_rn(angle1[i1], angle2[i2]);
-                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                int bin = (int)roundf(__fmul_rn(rot, factor));
-                if (bin == 30) bin = 0;
-                evBin[item] = (signed char)min(max(bin, 0), 29);
-            } else {
-                evBin[item] = 0;
-            }
-        }
+    for (int item = tid; item < nItems; item += BOW_RESOLVE_THREADS) {
+        const int i2 = evI2[item];
+        if (i2 == 0xFFFF) continue;
+        const int i1 = (int)idx1[item];
+        match12[i1] = i2;
+        match21[i2] = i1;
         ++total;
-        __syncwarp();
-    }
-    __syncwarp();
-    if (checkOri) {
-        int h = 0;
-        for (int i = 0; i < nItems; ++i) h += (evBin[i] == lane) ? 1 : 0;
-        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
-        for (int b = 0; b < 30; ++b) {  // ComputeThreeMaxima (:1601-1642)
-            const int s = __shfl_sync(0xffffffffu, h, b);
-            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = b; }
-            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = b; }
-            else if (s > max3) { max3 = s; ind3 = b; }
+        if (checkOri) {
+            float rot = __fsub_rn(angle1[i1], angle2[i2]);
+            if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
+            int bin = (int)roundf(__fmul_rn(rot, factor));
+            if (bin == 30) bin = 0;
+            bin = min(max(bin, 0), 29);
+            evBin[item] = (signed char)bin;
+            atomicAdd(&hist[bin], 1);
         }
-        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
-        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
-        int removed = 0;
-        for (int i = lane; i < nItems; i += 32) {
-            const int b = evBin[i];
+    }
+    __syncthreads();
+    if (checkOri) {
+        int ind1, ind2, ind3;
+        three_maxima(hist, ind1, ind2, ind3);
+        for (int item = tid; item < nItems; item += BOW_RESOLVE_THREADS) {
+            const int b = evBin[item];
             if (b >= 0 && b != ind1 && b != ind2 && b != ind3) {
-                const int i1 = (int)idx1[i];
-                match21[match12[i1]] = -2;
-                match12[i1] = -2;
-                ++removed;
+                match12[(int)idx1[item]] = -2;
+                match21[evI2[item]] = -2;
+                --total;
             }
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) removed += __shfl_xor_sync(0xffffffffu, removed, o);
-        total -= removed;
     }
-    if (lane == 0) *nmatchesOut = total;
+    total = __reduce_add_sync(0xffffffffu, total);
+    __syncthreads();  // hist is reused for the count
+    if (tid == 0) hist[0] = 0;
+    __syncthreads();
+    if (lane == 0 && total) atomicAdd(&hist[0], total);
+    __syncthreads();
+    if (tid == 0) *nmatchesOut = hist[0];
 }
 
 int launch_search_by_bow(int nItems, const int* nodeOf, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
                          const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
                          const uint8_t* desc2, const float* angle2, const int* candOff, uint32_t* cand, int* candCnt, int thDist,
                          float nnratio, int checkOri, int* match12, int* match21, int* nmatches, cudaStream_t s) {
-    const size_t smem = (size_t)n2 + (size_t)nItems + 16;
+    const size_t smem = 128 + (size_t)n2 * 4 + (size_t)2 * (nItems + 1) + (size_t)n2 + (size_t)nItems + 16;
     if (smem > 200 * 1024) {
         set_error("SearchByBoW: %d + %d features do not fit the resolve kernel's shared memory", nItems, n2);
         return ORBX_E_INVALID;
@@ -161,7 +173,7 @@ int launch_search_by_bow(int nItems, const int* nodeOf, const uint32_t* idx1, co
                                                             valid2, reinterpret_cast<const uint4*>(desc2), candOff, cand, candCnt);
         count_launch();
     }
-    k_bow_resolve<<<1, 32, smem, s>>>(nItems, idx1, angle1, angle2, n1, n2, candOff, cand, candCnt, thDist, nnratio, checkOri, match12,
+    k_bow_resolve<<<1, BOW_RESOLVE_THREADS, smem, s>>>(nItems, idx1, angle1, angle2, n1, n2, candOff, cand, candCnt, thDist, nnratio, checkOri, match12,
                                         match21, nmatches);
     count_launch();
     ORBX_CUDA(cudaGetLastError());

@@ -19,6 +19,7 @@
 #include <cstring>
 
 #include "orbx_internal.h"
+#include "resolve_common.cuh"
 
 namespace orbx {
 
@@ -99,6 +100,8 @@ __global__ void __launch_bounds__(256) k_sfi_candidates(const orbx_keypoint* __r
     const int i1 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i1 >= n1) return;
     int count = 0;
+    Top4 mine;
+    mine.clear();
     if (k1[i1].octave <= 0) {
         const float x = prev[2 * i1], y = prev[2 * i1 + 1];
         // GetFeaturesInArea(x, y, r, 0, 0) (src/Frame.cc:326-379)
@@ -126,12 +129,14 @@ __global__ void __launch_bounds__(256) k_sfi_candidates(const orbx_keypoint* __r
                     if (ok) {
                         const int o = count + __popc(m & ((1u << lane) - 1));
                         if (o < candCap) out[o] = ((uint32_t)dist << 16) | (uint32_t)i2;
+                        mine.push(((uint32_t)dist << 16) | (uint32_t)o, (uint32_t)i2, o < candCap);
                     }
                     count += __popc(m);
                 }
             }
         }
     }
+    warp_store_top(mine, lane, candCnt, n1, i1);
     if (lane == 0) {
         if (count > candCap) {
             atomicExch(dStatus, ORBX_E_OVERFLOW);
@@ -141,89 +146,80 @@ __global__ void __launch_bounds__(256) k_sfi_candidates(const orbx_keypoint* __r
     }
 }
 
-// One warp replays the sequential loop.  Dynamic shared memory: matchedDist[n2] (uint16, 0xFFFF = INT_MAX),
-// matches21[n2] (int32), matches12[n1] (int32), bin[n1] (int8: histogram bin of the acceptance event or -1).
-__global__ void __launch_bounds__(32) k_sfi_resolve(const orbx_keypoint* __restrict__ k1, int n1,
-                                                     const orbx_keypoint* __restrict__ k2, int n2,
-                                                     const uint32_t* __restrict__ cand, int candCap,
-                                                     const int* __restrict__ candCnt, float nnratio, int checkOri,
-                                                     float* __restrict__ prev, int* __restrict__ matches12Out,
-                                                     int* __restrict__ nmatchesOut) {
+// Warp 0 replays the sequential loop on shared memory only; all warps initialise, bin the rotations and write the result.
+// Dynamic shared memory: hist[32] (int32), claim[n2] (int32), matches21[n2] (int32), matches12[n1] (int32), matchedDist[n2] (uint16, 0xFFFF =
+// INT_MAX), ev2[n1] (uint16: the keypoint accepted by iteration i1, 0xFFFF = none), bin[n1] (int8).
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_sfi_resolve(const orbx_keypoint* __restrict__ k1, int n1,
+                                                                 const orbx_keypoint* __restrict__ k2, int n2,
+                                                                 const uint32_t* __restrict__ cand, int candCap,
+                                                                 const int* __restrict__ candCnt, float nnratio, int checkOri,
+                                                                 float* __restrict__ prev, int* __restrict__ matches12Out,
+                                                                 int* __restrict__ nmatchesOut) {
     extern __shared__ __align__(16) uint8_t sm[];
-    int* matches21 = reinterpret_cast<int*>(sm);
+    int* hist = reinterpret_cast<int*>(sm);
+    int* claim = hist + 32;
+    int* matches21 = claim + n2;
     int* matches12 = matches21 + n2;
     uint16_t* matchedDist = reinterpret_cast<uint16_t*>(matches12 + n1);
-    signed char* binOf = reinterpret_cast<signed char*>(matchedDist + n2);
-    const int lane = threadIdx.x;
-    for (int i = lane; i < n2; i += 32) { matches21[i] = -1; matchedDist[i] = 0xFFFFu; }
-    for (int i = lane; i < n1; i += 32) { matches12[i] = -1; binOf[i] = -1; }
-    __syncwarp();
-    const float factor = 1.0f / 30.0f;  // 1.0f / HISTO_LENGTH
-    for (int i1 = 0; i1 < n1; ++i1) {
-        const int cnt = candCnt[i1];
-        if (cnt == 0) continue;
-        const uint32_t* c = cand + (size_t)i1 * candCap;
-        // key = dist << 16 | position: minimal key = minimal distance, first in visiting order
-        uint32_t b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;  // two smallest keys seen by this lane
-        for (int p = lane; p < cnt; p += 32) {
-            const uint32_t e = c[p];
-            const uint32_t dist = e >> 16, i2 = e & 0xFFFFu;
-            if ((uint32_t)matchedDist[i2] <= dist) continue;  // :444 (0xFFFF stands for INT_MAX; dist <= 256)
-            const uint32_t key = (dist << 16) | (uint32_t)p;
-            if (key < b1) { b2 = b1; b1 = key; }
-            else if (key < b2) b2 = key;
+    uint16_t* ev2 = matchedDist + n2;
+    signed char* binOf = reinterpret_cast<signed char*>(ev2 + n1);
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int i = tid; i < n2; i += RESOLVE_THREADS) { matches21[i] = -1; matchedDist[i] = 0xFFFFu; claim[i] = RS_CLAIM_FREE; }
+    for (int i = tid; i < n1; i += RESOLVE_THREADS) { matches12[i] = -1; ev2[i] = 0xFFFFu; binOf[i] = -1; }
+    if (tid < 32) hist[tid] = 0;
+    __syncthreads();
+    if (tid < 32) {
+        // a candidate is skipped when the keypoint already holds a match at least as close (:444; 0xFFFF stands for INT_MAX,
+        // dist <= 256); matchedDist only decreases, so the skipped set only grows (resolve_common.cuh)
+        auto isFree = [&](uint32_t i2, uint32_t dist) { return (uint32_t)matchedDist[i2] > dist; };
+        int cntNext;
+        TopK topNext;
+        fetch_feature(candCnt, n1, lane, cntNext, topNext);
+        for (int base = 0; base < n1; base += 32) {
+            const int i1 = base + lane;
+            const int cnt = cntNext;
+            const TopK top = topNext;  // key = dist << 16 | position: minimal key = minimal distance, first in visiting order
+            fetch_feature(candCnt, n1, i1 + 32, cntNext, topNext);
+            const uint32_t* c = cand + (size_t)min(i1, n1 - 1) * candCap;
+            resolve_rounds(
+                __ballot_sync(0xffffffffu, cnt > 0), lane, claim,
+                [&](uint32_t& b1, uint32_t& i2a, uint32_t& b2, uint32_t& i2b) {
+                    if (!top.pick(isFree, 2, b1, i2a, b2, i2b)) rescan_list(c, cnt, isFree, b1, i2a, b2, i2b);
+                    const int bestDist = (int)(b1 >> 16);  // every candidate skipped: bestDist stays INT_MAX
+                    const float second = b2 == RS_NONE ? 2147483648.0f /* (float)INT_MAX */ : (float)(int)(b2 >> 16);
+                    return b1 != RS_NONE && bestDist <= 50 /* TH_LOW (:459) */ && (float)bestDist < __fmul_rn(second, nnratio);
+                },
+                [&](uint32_t b1, uint32_t i2a, uint32_t, uint32_t) {
+                    const int owner = matches21[i2a];
+                    if (owner >= 0) matches12[owner] = -1;
+                    matches12[i1] = (int)i2a;
+                    matches21[i2a] = i1;
+                    matchedDist[i2a] = (uint16_t)(b1 >> 16);
+                    ev2[i1] = (uint16_t)i2a;
+                });
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const uint32_t o1 = __shfl_xor_sync(0xffffffffu, b1, o), o2 = __shfl_xor_sync(0xffffffffu, b2, o);
-            const uint32_t lo = min(b1, o1), hi = max(b1, o1);
-            b2 = min(hi, min(b2, o2));
-            b1 = lo;
-        }
-        if (b1 == 0xFFFFFFFFu) continue;  // every candidate skipped: bestDist stays INT_MAX
-        const int bestDist = (int)(b1 >> 16);
-        if (bestDist > 50) continue;  // TH_LOW (:459)
-        const float second = b2 == 0xFFFFFFFFu ? 2147483648.0f /* (float)INT_MAX */ : (float)(int)(b2 >> 16);
-        if (!((float)bestDist < __fmul_rn(second, nnratio))) continue;
-        const int bestIdx2 = (int)(c[b1 & 0xFFFFu] & 0xFFFFu);
-        if (lane == 0) {
-            const int owner = matches21[bestIdx2];
-            if (owner >= 0) matches12[owner] = -1;
-            matches12[i1] = bestIdx2;
-            matches21[bestIdx2] = i1;
-            matchedDist[bestIdx2] = (uint16_t)bestDist;
-            if (checkOri) {
-                float rot = __fsub_rn(k1[i1].angle, k2[bestIdx2].angle);
-                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                int bin = (int)roundf(__fmul_rn(rot, factor));
-                if (bin == 30) bin = 0;
-                binOf[i1] = (signed char)min(max(bin, 0), 29);
-            }
-        }
-        __syncwarp();
     }
-    __syncwarp();
+    __syncthreads();
     if (checkOri) {
         // histogram sizes count acceptance events, including matches stolen later (rotHist[bin].push_back(i1), :478)
-        int h = 0;  // lane b owns bin b (30 bins)
-        for (int i = 0; i < n1; ++i) h += (binOf[i] == lane) ? 1 : 0;
-        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
-        for (int b = 0; b < 30; ++b) {  // ComputeThreeMaxima (:1601-1642), evaluated redundantly by every lane
-            const int s = __shfl_sync(0xffffffffu, h, b);
-            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = b; }
-            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = b; }
-            else if (s > max3) { max3 = s; ind3 = b; }
+        for (int i = tid; i < n1; i += RESOLVE_THREADS) {
+            const int e = ev2[i];
+            if (e == 0xFFFF) continue;
+            const int bin = rotation_bin(k1[i].angle, k2[e].angle);
+            binOf[i] = (signed char)bin;
+            atomicAdd(&hist[bin], 1);
         }
-        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
-        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
-        for (int i = lane; i < n1; i += 32) {
+        __syncthreads();
+        int ind1, ind2, ind3;
+        three_maxima(hist, ind1, ind2, ind3);
+        for (int i = tid; i < n1; i += RESOLVE_THREADS) {
             const int b = binOf[i];
             if (b >= 0 && b != ind1 && b != ind2 && b != ind3) matches12[i] = -1;
         }
-        __syncwarp();
+        __syncthreads();
     }
     int total = 0;
-    for (int i = lane; i < n1; i += 32) {
+    for (int i = tid; i < n1; i += RESOLVE_THREADS) {
         const int m = matches12[i];
         matches12Out[i] = m;
         if (m >= 0) {
@@ -232,13 +228,17 @@ __global__ void __launch_bounds__(32) k_sfi_resolve(const orbx_keypoint* __restr
             prev[2 * i + 1] = k2[m].y;
         }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+    total = __reduce_add_sync(0xffffffffu, total);
+    __syncthreads();
+    if (tid == 0) hist[0] = 0;
+    __syncthreads();
+    if (lane == 0 && total) atomicAdd(&hist[0], total);
+    __syncthreads();
     // the reference's running nmatches (++ on accept, -- on steal / histogram removal) = surviving matches
-    if (lane == 0) *nmatchesOut = total;
+    if (tid == 0) *nmatchesOut = hist[0];
 }
 
-size_t sfi_resolve_smem(int n1, int n2) { return (size_t)n2 * 4 + (size_t)n1 * 4 + (size_t)n2 * 2 + (size_t)n1 + 16; }
+size_t sfi_resolve_smem(int n1, int n2) { return 128 + (size_t)n2 * 8 + (size_t)n1 * 4 + (size_t)n2 * 2 + (size_t)n1 * 2 + (size_t)n1 + 16; }
 
 int launch_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_t* desc1, const orbx_keypoint* k2, int n2,
                                      const uint8_t* desc2, const float bounds[4], float* prev, int* matches12, int window,
@@ -263,7 +263,7 @@ int launch_search_for_initialization(const orbx_keypoint* k1, int n1, const uint
                                                     reinterpret_cast<const uint4*>(desc2), prev, minX, minY, invW, invH,
                                                     (float)window, sorted, cellStart, cand, candCap, candCnt, dStatus);
     count_launch();
-    k_sfi_resolve<<<1, 32, smem, s>>>(k1, n1, k2, n2, cand, candCap, candCnt, nnratio, checkOri, prev, matches12, nmatches);
+    k_sfi_resolve<<<1, RESOLVE_THREADS, smem, s>>>(k1, n1, k2, n2, cand, candCap, candCnt, nnratio, checkOri, prev, matches12, nmatches);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
@@ -298,6 +298,8 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i >= n1) return;
     int count = 0;
+    Top4 mine;
+    mine.clear();
     if (valid1[i]) {
         float u, v, ur, r = 0.f;
         bool inImage = true;
@@ -360,6 +362,7 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
                         if (ok) {
                             const int o = count + __popc(m & ((1u << lane) - 1));
                             if (o < candCap) out[o] = ((uint32_t)dist << 16) | (uint32_t)i2;
+                            mine.push(((uint32_t)dist << 16) | (uint32_t)o, (uint32_t)i2, o < candCap);
                         }
                         count += __popc(m);
                     }
@@ -367,6 +370,7 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
             }
         }
     }
+    warp_store_top(mine, lane, candCnt, n1, i);
     if (lane == 0) {
         if (count > candCap) {
             atomicExch(dStatus, ORBX_E_OVERFLOW);
@@ -376,81 +380,88 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
     }
 }
 
-// One warp replays the loop.  Dynamic shared memory: owner[n2] (int32), evIdx[n1] (int32: bestIdx2 of the acceptance event of
+// One CTA: warp 0 replays the loop on shared memory and registers only; all warps initialise, bin the rotations and write the
+// result.  Dynamic shared memory: hist[32] (int32), claim[n2] (int32), owner[n2] (int32), evIdx[n1] (int32: bestIdx2 of the acceptance event of
 // iteration i, -1 = none), taken[n2] (uint8), evBin[n1] (int8).
-__global__ void __launch_bounds__(32) k_sbp_resolve(int n1, const uint8_t* __restrict__ obs1, const float* __restrict__ angle1,
-                                                     const orbx_keypoint* __restrict__ k2, int n2,
-                                                     const uint32_t* __restrict__ cand, int candCap,
-                                                     const int* __restrict__ candCnt, int checkOri, int thDist,
-                                                     int* __restrict__ match21, int* __restrict__ nmatchesOut) {
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_sbp_resolve(int n1, const uint8_t* __restrict__ obs1, const float* __restrict__ angle1,
+                                                                 const orbx_keypoint* __restrict__ k2, int n2,
+                                                                 const uint32_t* __restrict__ cand, int candCap,
+                                                                 const int* __restrict__ candCnt, int checkOri, int thDist,
+                                                                 int* __restrict__ match21, int* __restrict__ nmatchesOut) {
     extern __shared__ __align__(16) uint8_t sm[];
-    int* owner = reinterpret_cast<int*>(sm);
+    int* hist = reinterpret_cast<int*>(sm);
+    int* claim = hist + 32;
+    int* owner = claim + n2;
     int* evIdx = owner + n2;
     uint8_t* taken = reinterpret_cast<uint8_t*>(evIdx + n1);
     signed char* evBin = reinterpret_cast<signed char*>(taken + n2);
-    const int lane = threadIdx.x;
-    for (int i = lane; i < n2; i += 32) { owner[i] = -1; taken[i] = 0; }
-    for (int i = lane; i < n1; i += 32) { evIdx[i] = -1; evBin[i] = -1; }
-    __syncwarp();
-    const float factor = 1.0f / 30.0f;  // 1.0f / HISTO_LENGTH
-    for (int i = 0; i < n1; ++i) {
-        const int cnt = candCnt[i];
-        if (cnt == 0) continue;
-        const uint32_t* c = cand + (size_t)i * candCap;
-        uint32_t b1 = 0xFFFFFFFFu;  // key = dist << 16 | position: minimal distance, first in visiting order (strict '<', :1420)
-        for (int p = lane; p < cnt; p += 32) {
-            const uint32_t e = c[p];
-            if (taken[e & 0xFFFFu]) continue;
-            b1 = min(b1, ((e >> 16) << 16) | (uint32_t)p);
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int i = tid; i < n2; i += RESOLVE_THREADS) { owner[i] = -1; taken[i] = 0; claim[i] = RS_CLAIM_FREE; }
+    for (int i = tid; i < n1; i += RESOLVE_THREADS) { evIdx[i] = -1; evBin[i] = -1; }
+    if (tid < 32) hist[tid] = 0;
+    __syncthreads();
+    if (tid < 32) {
+        auto isFree = [&](uint32_t i2, uint32_t) { return taken[i2] == 0; };
+        int cntNext;
+        TopK topNext;
+        fetch_feature(candCnt, n1, lane, cntNext, topNext);
+        uint8_t obsNext = lane < n1 ? obs1[lane] : 0;
+        for (int base = 0; base < n1; base += 32) {
+            // 32 points at a time, their best candidates from k_sbp_candidates (resolve_common.cuh); key = dist << 16 | position: minimal
+            // distance, first in visiting order (strict '<', :1420)
+            const int i = base + lane;
+            const int cnt = cntNext;
+            const uint8_t obs = obsNext;
+            const TopK top = topNext;
+            fetch_feature(candCnt, n1, i + 32, cntNext, topNext);
+            obsNext = i + 32 < n1 ? obs1[i + 32] : 0;
+            const uint32_t* c = cand + (size_t)min(i, n1 - 1) * candCap;
+            resolve_rounds(
+                __ballot_sync(0xffffffffu, cnt > 0), lane, claim,
+                [&](uint32_t& b1, uint32_t& i2a, uint32_t& b2, uint32_t& i2b) {
+                    if (!top.pick(isFree, 1, b1, i2a, b2, i2b)) rescan_list(c, cnt, isFree, b1, i2a, b2, i2b);
+                    b2 = RS_NONE;  // only the best matters here
+                    return b1 != RS_NONE && (int)(b1 >> 16) <= thDist;  // TH_HIGH (:1427) / ORBdist (:1552)
+                },
+                [&](uint32_t, uint32_t i2a, uint32_t, uint32_t) {
+                    owner[i2a] = i;
+                    taken[i2a] = obs;
+                    evIdx[i] = (int)i2a;
+                });
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) b1 = min(b1, __shfl_xor_sync(0xffffffffu, b1, o));
-        if (b1 == 0xFFFFFFFFu) continue;
-        const int bestDist = (int)(b1 >> 16);
-        if (bestDist > thDist) continue;  // TH_HIGH (:1427) / ORBdist (:1552)
-        if (lane == 0) {
-            const int bestIdx2 = (int)(c[b1 & 0xFFFFu] & 0xFFFFu);
-            owner[bestIdx2] = i;
-            taken[bestIdx2] = obs1[i];
-            evIdx[i] = bestIdx2;
-            if (checkOri) {
-                float rot = __fsub_rn(angle1[i], k2[bestIdx2].angle);
-                if (rot < 0.0f) rot = __fadd_rn(rot, 360.0f);
-                int bin = (int)roundf(__fmul_rn(rot, factor));
-                if (bin == 30) bin = 0;
-                evBin[i] = (signed char)min(max(bin, 0), 29);
-            }
-        }
-        __syncwarp();
     }
-    __syncwarp();
+    __syncthreads();
     int total = 0;
-    for (int i = lane; i < n1; i += 32) total += evIdx[i] >= 0 ? 1 : 0;
-    if (checkOri) {
-        int h = 0;  // lane b owns bin b
-        for (int i = 0; i < n1; ++i) h += (evBin[i] == lane) ? 1 : 0;
-        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
-        for (int b = 0; b < 30; ++b) {  // ComputeThreeMaxima (:1601-1642)
-            const int s = __shfl_sync(0xffffffffu, h, b);
-            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = b; }
-            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = b; }
-            else if (s > max3) { max3 = s; ind3 = b; }
+    for (int i = tid; i < n1; i += RESOLVE_THREADS) {
+        const int idx = evIdx[i];
+        if (idx < 0) continue;
+        ++total;
+        if (checkOri) {
+            const int bin = rotation_bin(angle1[i], k2[idx].angle);
+            evBin[i] = (signed char)bin;
+            atomicAdd(&hist[bin], 1);
         }
-        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
-        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
-        for (int i = lane; i < n1; i += 32) {
+    }
+    __syncthreads();
+    if (checkOri) {
+        int ind1, ind2, ind3;
+        three_maxima(hist, ind1, ind2, ind3);
+        for (int i = tid; i < n1; i += RESOLVE_THREADS) {
             const int b = evBin[i];
             if (b >= 0 && b != ind1 && b != ind2 && b != ind3) {
                 owner[evIdx[i]] = -2;  // CurrentFrame.mvpMapPoints[idx] = NULL; nmatches--  (:1460-1461)
                 --total;
             }
         }
-        __syncwarp();
     }
-    for (int i = lane; i < n2; i += 32) match21[i] = owner[i];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
-    if (lane == 0) *nmatchesOut = total;
+    total = __reduce_add_sync(0xffffffffu, total);
+    __syncthreads();
+    if (tid == 0) hist[0] = 0;
+    __syncthreads();
+    if (lane == 0 && total) atomicAdd(&hist[0], total);
+    for (int i = tid; i < n2; i += RESOLVE_THREADS) match21[i] = owner[i];
+    __syncthreads();
+    if (tid == 0) *nmatchesOut = hist[0];
 }
 
 int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
@@ -470,7 +481,7 @@ int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1
     P.mapMode = 0;
     P.thDist = thDist;
     P.noDepthTest = noDepthTest;
-    const size_t smem = (size_t)n2 * 4 + (size_t)n1 * 4 + (size_t)n2 + (size_t)n1 + 16;
+    const size_t smem = 128 + (size_t)n2 * 8 + (size_t)n1 * 4 + (size_t)n2 + (size_t)n1 + 16;
     if (smem > 200 * 1024) {
         set_error("SearchByProjection: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
         return ORBX_E_INVALID;
@@ -486,62 +497,64 @@ int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1
                                                     reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, nullptr, P,
                                                     sorted, cellStart, cand, candCap, candCnt, dStatus);
     count_launch();
-    k_sbp_resolve<<<1, 32, smem, s>>>(n1, obs1, angle1, k2, n2, cand, candCap, candCnt, checkOri, thDist, match21, nmatches);
+    k_sbp_resolve<<<1, RESOLVE_THREADS, smem, s>>>(n1, obs1, angle1, k2, n2, cand, candCap, candCnt, checkOri, thDist, match21, nmatches);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
 }
 
-// SearchByProjection(F, vpMapPoints, th) (:45-129): one warp replays the loop; best / second-best with their octaves, ratio test
-// only when both lie on the same level (:113-117).  Dynamic shared memory: owner[n2] (int32), taken[n2] (uint8).
-__global__ void __launch_bounds__(32) k_sbpm_resolve(int n1, const uint8_t* __restrict__ obs1, const orbx_keypoint* __restrict__ k2,
-                                                      int n2, const uint32_t* __restrict__ cand, int candCap,
-                                                      const int* __restrict__ candCnt, float nnratio, int* __restrict__ match21,
-                                                      int* __restrict__ nmatchesOut) {
+// SearchByProjection(F, vpMapPoints, th) (:45-129): warp 0 replays the loop; best / second-best with their octaves, ratio test
+// only when both lie on the same level (:113-117).  Dynamic shared memory: claim[n2], owner[n2] (int32), taken[n2] (uint8), oct2[n2] (uint8).
+__global__ void __launch_bounds__(RESOLVE_THREADS) k_sbpm_resolve(int n1, const uint8_t* __restrict__ obs1,
+                                                                  const orbx_keypoint* __restrict__ k2, int n2,
+                                                                  const uint32_t* __restrict__ cand, int candCap,
+                                                                  const int* __restrict__ candCnt, float nnratio, int* __restrict__ match21,
+                                                                  int* __restrict__ nmatchesOut) {
     extern __shared__ __align__(16) uint8_t sm[];
-    int* owner = reinterpret_cast<int*>(sm);
+    int* claim = reinterpret_cast<int*>(sm);
+    int* owner = claim + n2;
     uint8_t* taken = reinterpret_cast<uint8_t*>(owner + n2);
-    const int lane = threadIdx.x;
-    for (int i = lane; i < n2; i += 32) { owner[i] = -1; taken[i] = 0; }
-    __syncwarp();
-    int nmatches = 0;
-    for (int i = 0; i < n1; ++i) {
-        const int cnt = candCnt[i];
-        if (cnt == 0) continue;
-        const uint32_t* c = cand + (size_t)i * candCap;
-        uint32_t b1 = 0xFFFFFFFFu, b2 = 0xFFFFFFFFu;  // two smallest (dist << 16 | position) keys among the free candidates
-        for (int p = lane; p < cnt; p += 32) {
-            const uint32_t e = c[p];
-            if (taken[e & 0xFFFFu]) continue;
-            const uint32_t key = ((e >> 16) << 16) | (uint32_t)p;
-            if (key < b1) { b2 = b1; b1 = key; }
-            else if (key < b2) b2 = key;
+    uint8_t* oct2 = taken + n2;
+    const int tid = threadIdx.x, lane = tid & 31;
+    for (int i = tid; i < n2; i += RESOLVE_THREADS) { owner[i] = -1; taken[i] = 0; claim[i] = RS_CLAIM_FREE; oct2[i] = (uint8_t)k2[i].octave; }
+    __syncthreads();
+    if (tid < 32) {
+        int nmatches = 0;  // lane-local
+        auto isFree = [&](uint32_t i2, uint32_t) { return taken[i2] == 0; };
+        int cntNext;
+        TopK topNext;
+        fetch_feature(candCnt, n1, lane, cntNext, topNext);
+        uint8_t obsNext = lane < n1 ? obs1[lane] : 0;
+        for (int base = 0; base < n1; base += 32) {
+            const int i = base + lane;
+            const int cnt = cntNext;
+            const uint8_t obs = obsNext;
+            const TopK top = topNext;  // the smallest (dist << 16 | position) keys of the list
+            fetch_feature(candCnt, n1, i + 32, cntNext, topNext);
+            obsNext = i + 32 < n1 ? obs1[i + 32] : 0;
+            const uint32_t* c = cand + (size_t)min(i, n1 - 1) * candCap;
+            resolve_rounds(
+                __ballot_sync(0xffffffffu, cnt > 0), lane, claim,
+                [&](uint32_t& b1, uint32_t& i2a, uint32_t& b2, uint32_t& i2b) {
+                    if (!top.pick(isFree, 2, b1, i2a, b2, i2b)) rescan_list(c, cnt, isFree, b1, i2a, b2, i2b);
+                    const int bestDist = (int)(b1 >> 16);
+                    bool accept = b1 != RS_NONE && bestDist <= 100;  // TH_HIGH (:111)
+                    // without a second candidate bestLevel2 stays -1 and the ratio test is skipped
+                    if (accept && b2 != RS_NONE && oct2[i2a] == oct2[i2b] && (float)bestDist > __fmul_rn(nnratio, (float)(int)(b2 >> 16)))
+                        accept = false;
+                    return accept;
+                },
+                [&](uint32_t, uint32_t i2a, uint32_t, uint32_t) {
+                    owner[i2a] = i;
+                    taken[i2a] = obs;
+                    ++nmatches;
+                });
         }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const uint32_t o1 = __shfl_xor_sync(0xffffffffu, b1, o), o2 = __shfl_xor_sync(0xffffffffu, b2, o);
-            const uint32_t lo = min(b1, o1), hi = max(b1, o1);
-            b2 = min(hi, min(b2, o2));
-            b1 = lo;
-        }
-        if (b1 == 0xFFFFFFFFu) continue;
-        const int bestDist = (int)(b1 >> 16);
-        if (bestDist > 100) continue;  // TH_HIGH (:111)
-        const int bestIdx = (int)(c[b1 & 0xFFFFu] & 0xFFFFu);
-        if (b2 != 0xFFFFFFFFu) {       // without a second candidate bestLevel2 stays -1 and the ratio test is skipped
-            const int idx2 = (int)(c[b2 & 0xFFFFu] & 0xFFFFu);
-            if (k2[bestIdx].octave == k2[idx2].octave && (float)bestDist > __fmul_rn(nnratio, (float)(int)(b2 >> 16))) continue;
-        }
-        if (lane == 0) {
-            owner[bestIdx] = i;
-            taken[bestIdx] = obs1[i];
-        }
-        ++nmatches;
-        __syncwarp();
+        nmatches = __reduce_add_sync(0xffffffffu, nmatches);
+        if (lane == 0) *nmatchesOut = nmatches;
     }
-    __syncwarp();
-    for (int i = lane; i < n2; i += 32) match21[i] = owner[i];
-    if (lane == 0) *nmatchesOut = nmatches;
+    __syncthreads();
+    for (int i = tid; i < n2; i += RESOLVE_THREADS) match21[i] = owner[i];
 }
 
 int launch_search_by_projection_map(int n1, const float* proj, const float* viewCos, const int* level1, const uint8_t* valid1,
@@ -558,7 +571,7 @@ int launch_search_by_projection_map(int n1, const float* proj, const float* view
     P.invH = (float)GRID_ROWS / (P.maxY - P.minY);
     P.hasRight = uRight2 != nullptr;
     P.mapMode = 1;
-    const size_t smem = (size_t)n2 * 4 + (size_t)n2 + 16;
+    const size_t smem = (size_t)n2 * 8 + (size_t)n2 * 2 + 16;
     if (smem > 200 * 1024) {
         set_error("SearchByProjection: %d keypoints do not fit the resolve kernel's shared memory", n2);
         return ORBX_E_INVALID;
@@ -574,7 +587,7 @@ int launch_search_by_projection_map(int n1, const float* proj, const float* view
                                                     reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, viewCos,
                                                     P, sorted, cellStart, cand, candCap, candCnt, dStatus);
     count_launch();
-    k_sbpm_resolve<<<1, 32, smem, s>>>(n1, obs1, k2, n2, cand, candCap, candCnt, nnratio, match21, nmatches);
+    k_sbpm_resolve<<<1, RESOLVE_THREADS, smem, s>>>(n1, obs1, k2, n2, cand, candCap, candCnt, nnratio, match21, nmatches);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
@@ -591,7 +604,7 @@ int launch_search_by_projection_sim3(int n1, const float* uvr, const int* level1
     P.invW = (float)GRID_COLS / (P.maxX - P.minX);
     P.invH = (float)GRID_ROWS / (P.maxY - P.minY);
     P.mapMode = 2;
-    const size_t smem = (size_t)n2 * 4 + (size_t)n1 * 4 + (size_t)n2 + (size_t)n1 + 16;
+    const size_t smem = 128 + (size_t)n2 * 8 + (size_t)n1 * 4 + (size_t)n2 + (size_t)n1 + 16;
     if (smem > 200 * 1024) {
         set_error("SearchByProjection: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
         return ORBX_E_INVALID;
@@ -604,7 +617,7 @@ int launch_search_by_projection_sim3(int n1, const float* uvr, const int* level1
                                                     sorted, cellStart, cand, candCap, candCnt, dStatus);
     count_launch();
     // best candidate only, every assigned keypoint is taken (ones1), no rotation pass
-    k_sbp_resolve<<<1, 32, smem, s>>>(n1, ones1, nullptr, k2, n2, cand, candCap, candCnt, 0, thDist, match21, nmatches);
+    k_sbp_resolve<<<1, RESOLVE_THREADS, smem, s>>>(n1, ones1, nullptr, k2, n2, cand, candCap, candCnt, 0, thDist, match21, nmatches);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

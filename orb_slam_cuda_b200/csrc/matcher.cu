@@ -150,7 +150,7 @@ int orbx_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_
         (rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
         (rc = upload(w->e, prev_xy, (size_t)n1 * 8, s)) || (rc = w->out0.ensure((size_t)n1 * 4 + 16)) ||
         (rc = w->f.ensure(((size_t)2 * std::max(n2, 1) + 64 * 48 + 1) * 4)) || (rc = w->g.ensure((size_t)n1 * candCap * 4)) ||
-        (rc = w->h.ensure((size_t)n1 * 4)) || (rc = w->status.ensure(16)))
+        (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
     ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
     int* cellOf = w->f.as<int>();
@@ -227,7 +227,7 @@ int orbx_search_by_projection_ex(int n1, const float* x3dc, const uint8_t* valid
     ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
     if ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
         (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
-        (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure((size_t)n1 * 4)) || (rc = w->status.ensure(16)))
+        (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
     ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
     const uint8_t* dp = w->a.as<uint8_t>();
@@ -296,7 +296,7 @@ int orbx_search_by_projection_map(int n1, const float* proj, const float* view_c
     ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
     if ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
         (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
-        (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure((size_t)n1 * 4)) || (rc = w->status.ensure(16)))
+        (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
     ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
     const uint8_t* dp = w->a.as<uint8_t>();
@@ -354,7 +354,7 @@ int orbx_search_by_projection_sim3(int n1, const float* uvr, const int* level1, 
     ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
     if ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
         (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
-        (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure((size_t)n1 * 4)) || (rc = w->status.ensure(16)))
+        (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
     ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
     const uint8_t* dp = w->a.as<uint8_t>();
@@ -446,7 +446,7 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
     memcpy(hp + oD2, desc2, (size_t)n2 * 32);
     memcpy(hp + oV1, valid1, n1);
     memcpy(hp + oV2, valid2, n2);
-    if ((rc = w->a.ensure(total)) || (rc = w->g.ensure((nCand + 1) * 4)) || (rc = w->h.ensure((size_t)nItems * 4)) ||
+    if ((rc = w->a.ensure(total)) || (rc = w->g.ensure((nCand + 1) * 4)) || (rc = w->h.ensure(resolve_aux_bytes(nItems))) ||
         (rc = w->out0.ensure((size_t)n1 * 4 + 16)) || (rc = w->out1.ensure((size_t)n2 * 4 + 16)) || (rc = w->status.ensure(16)))
         return rc;
     ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));

@@ -197,6 +197,8 @@ size_t bruteforce_counter_bytes(int nq);
 int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score,
                     cudaStream_t s);
 
+// candCnt[n] followed (16-byte aligned) by key[n][8] and idx[n][8] (uint32): see resolve_common.cuh
+inline size_t resolve_aux_bytes(int n) { return ((size_t)n + 3) / 4 * 16 + (size_t)n * 64; }
 int launch_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_t* desc1, const orbx_keypoint* k2, int n2,
                                      const uint8_t* desc2, const float bounds[4], float* prev, int* matches12, int window,
                                      float nnratio, int checkOri, int* cellOf, int* sorted, int* cellStart, uint32_t* cand,
