@@ -103,7 +103,13 @@ __global__ void __launch_bounds__(BOW_RESOLVE_THREADS) k_bow_resolve(int nItems,
                     if (!top.pick(isFree, 2, b1, i2a, b2, i2b)) rescan_list(c + candOff[item], cnt, isFree, b1, i2a, b2, i2b);
                     const int best = (int)(b1 >> 16);
                     const int second = b2 == RS_NONE ? 256 : (int)(b2 >> 16);
-                    return b1 != RS_NONE && best <= thDist && (float)best < __fmul_rn(nnratio, (float)second);
+                    const bool near = b1 != RS_NONE && best <= thDist;
+                    const bool acc = near && (float)best < __fmul_rn(nnratio, (float)second);
+                    // what an earlier lane of the round can still change: nothing once the best is too far (it only gets
+                    // farther); not the second of an accepted match (the second only grows, the ratio test keeps passing)
+                    if (!near) b1 = RS_NONE;
+                    if (!near || acc) b2 = RS_NONE;
+                    return acc;
                 },
                 [&](uint32_t, uint32_t i2a, uint32_t, uint32_t) {
                     taken[i2a] = 1;

@@ -36,6 +36,7 @@ __global__ void __launch_bounds__(1024) k_sfi_grid(const orbx_keypoint* __restri
                                                     float invW, float invH, int* __restrict__ cellOf,
                                                     int* __restrict__ sorted, int* __restrict__ cellStart) {
     __shared__ int cnt[GRID_CELLS + 1];
+    __shared__ int fill[GRID_CELLS];
     __shared__ int warpSums[32];
     const int tid = threadIdx.x;
     for (int c = tid; c <= GRID_CELLS; c += blockDim.x) cnt[c] = 0;
@@ -76,13 +77,23 @@ __global__ void __launch_bounds__(1024) k_sfi_grid(const orbx_keypoint* __restri
         __syncthreads();
     }
     for (int c = tid; c <= GRID_CELLS; c += blockDim.x) cellStart[c] = cnt[c];
-    // stable placement: rank inside the cell = number of earlier keypoints of the same cell
+    // placement: any order inside the cell first (one atomic per keypoint), then every cell run is sorted by index, which is
+    // the order Frame::AssignFeaturesToGrid pushes (src/Frame.cc:229-244) — runs hold a handful of keypoints
+    for (int c = tid; c < GRID_CELLS; c += blockDim.x) fill[c] = 0;
+    __syncthreads();
     for (int i = tid; i < n; i += blockDim.x) {
         const int c = cellOf[i];
-        if (c < 0) continue;
-        int rank = 0;
-        for (int j = 0; j < i; ++j) rank += (cellOf[j] == c) ? 1 : 0;
-        sorted[cnt[c] + rank] = i;
+        if (c >= 0) sorted[cnt[c] + atomicAdd(&fill[c], 1)] = i;
+    }
+    __syncthreads();
+    for (int c = tid; c < GRID_CELLS; c += blockDim.x) {
+        const int b = cnt[c], e = cnt[c + 1];
+        for (int i = b + 1; i < e; ++i) {
+            const int v = sorted[i];
+            int j = i - 1;
+            while (j >= b && sorted[j] > v) { sorted[j + 1] = sorted[j]; --j; }
+            sorted[j + 1] = v;
+        }
     }
 }
 
@@ -187,7 +198,13 @@ __global__ void __launch_bounds__(RESOLVE_THREADS) k_sfi_resolve(const orbx_keyp
                     if (!top.pick(isFree, 2, b1, i2a, b2, i2b)) rescan_list(c, cnt, isFree, b1, i2a, b2, i2b);
                     const int bestDist = (int)(b1 >> 16);  // every candidate skipped: bestDist stays INT_MAX
                     const float second = b2 == RS_NONE ? 2147483648.0f /* (float)INT_MAX */ : (float)(int)(b2 >> 16);
-                    return b1 != RS_NONE && bestDist <= 50 /* TH_LOW (:459) */ && (float)bestDist < __fmul_rn(second, nnratio);
+                    const bool near = b1 != RS_NONE && bestDist <= 50;  // TH_LOW (:459)
+                    const bool acc = near && (float)bestDist < __fmul_rn(second, nnratio);
+                    // what an earlier lane of the round can still change: nothing once the best is too far (it only gets
+                    // farther); not the second of an accepted match (the second only grows, the ratio test keeps passing)
+                    if (!near) b1 = RS_NONE;
+                    if (!near || acc) b2 = RS_NONE;
+                    return acc;
                 },
                 [&](uint32_t b1, uint32_t i2a, uint32_t, uint32_t) {
                     const int owner = matches21[i2a];

@@ -12,7 +12,8 @@
 //           ones, so the first one / two free cached entries ARE the best / second best — unless too few are left while the
 //           list had more than 8 candidates; then that lane rescans its list;
 //   commit  a lane's decision equals the sequential one iff no EARLIER lane of the same round accepts the keypoint that is this
-//           lane's best or second best (nothing else it looked at changes rank).  Accepting lanes claim their keypoint with
+//           lane's best or second best (nothing else it looked at changes rank); decide() clears b1 / b2 where even that cannot
+//           change the outcome.  Accepting lanes claim their keypoint with
 //           atomicMin(lane); lanes before the first conflicting lane commit, the rest decide again in the next round.  The
 //           lowest undecided lane never conflicts, so every round retires at least one feature; without conflicts, all 32.
 // The global-memory latency is paid once per 32 features, and the decisions run 32 wide except where the order matters.
