@@ -172,3 +172,32 @@ def test_search_by_bow_one_big_node_and_empty():
     with pytest.raises(X.OrbxError):
         m.SearchByBoW(np.array([0, 1], np.int32), np.array([n1], np.uint32), np.array([0, 1], np.int32), np.array([0], np.uint32),
                       np.ones(n1, np.uint8), s["desc1"], s["angle1"], s["valid2"], s["desc2"], s["angle2"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,ratio,nodes", [(1, 0.95, 4), (2, 0.7, 1), (3, 0.99, 16)])
+def test_search_by_bow_dense_competition(seed, ratio, nodes):
+    """Few distinct descriptors in big nodes: ties everywhere, every feature's best candidates are taken by earlier ones — the replay
+    kernel's conflict rounds, exhausted candidate caches and rescans all fire."""
+    import orb_slam_cuda_b200 as X
+    rng = np.random.default_rng(seed)
+    n1, n2 = 700, 650
+    base = rng.integers(0, 256, (12, 32), dtype=np.uint8)
+
+    def table(n):
+        d = base[rng.integers(0, 12, n)].copy()
+        d[:, :2] ^= rng.integers(0, 256, (n, 2), dtype=np.uint8)  # up to 16 flipped bits: close neighbours, few exact ties
+        return d
+
+    d1, d2 = table(n1), table(n2)
+    node1, node2 = rng.integers(0, nodes, n1), rng.integers(0, nodes, n2)
+    fv1 = {k: np.flatnonzero(node1 == k).astype(np.uint32) for k in range(nodes)}
+    fv2 = {k: np.flatnonzero(node2 == k).astype(np.uint32) for k in range(nodes)}
+    s1, i1, s2, i2 = common_nodes(fv1, fv2)
+    a1, a2 = rng.uniform(0, 360, n1).astype(np.float32), rng.uniform(0, 360, n2).astype(np.float32)
+    v1, v2 = (rng.random(n1) < 0.9).astype(np.uint8), (rng.random(n2) < 0.9).astype(np.uint8)
+    for ori in (False, True):
+        ref = O.search_by_bow(s1, i1, s2, i2, v1, d1, a1, v2, d2, a2, 50, ratio, ori)
+        got = X.ORBmatcher(ratio, ori).SearchByBoW(s1, i1, s2, i2, v1, d1, a1, v2, d2, a2, 50)
+        assert got[0] == ref[0] and np.array_equal(got[1], ref[1]) and np.array_equal(got[2], ref[2])
+    assert O.search_by_bow(s1, i1, s2, i2, v1, d1, a1, v2, d2, a2, 50, ratio, False)[0] > 100

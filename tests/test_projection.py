@@ -277,3 +277,43 @@ def test_search_by_projection_sim3_gpu(seed, th):
     n, m21 = X.ORBmatcher(0.75, True).SearchByProjectionSim3(uvr, s["level1"], s["valid1"], s["mp_desc1"], s["k2"], s["d2"], occ,
                                                              s["bounds"], 50)
     assert n_ref > 50 and n == n_ref and np.array_equal(m21, m_ref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,th", [(21, 30.0), (22, 60.0)])
+def test_search_by_projection_dense_competition(seed, th):
+    """Few distinct descriptors and wide windows: many points want the same keypoint, best candidates are taken by earlier
+    points — conflict rounds, exhausted candidate caches and rescans of the replay kernels (frame-to-frame, local map, Sim3)."""
+    import orb_slam_cuda_b200 as X
+    s = scenario(seed, True)
+    rng = np.random.default_rng(seed)
+    base = rng.integers(0, 256, (10, 32), dtype=np.uint8)
+    n1, n2 = s["valid1"].size, s["k2"].size
+    mp = base[rng.integers(0, 10, n1)].copy()
+    d2 = base[rng.integers(0, 10, n2)].copy()
+    mp[:, 3] ^= rng.integers(0, 8, n1).astype(np.uint8)
+    d2[:, 7] ^= rng.integers(0, 8, n2).astype(np.uint8)
+    s["mp_desc1"], s["d2"] = mp, d2
+    n_ref, m_ref = O.search_by_projection_frame(s["x3Dc"], s["valid1"], s["obs1"], mp, s["octave1"], s["angle1"], s["k2"], d2,
+                                                s["u_right2"], s["occupied2"], s["cam"], s["mbf"], s["bounds"], s["scale_factors"], th, 0,
+                                                True)
+    m = X.ORBmatcher(0.9, True)
+    n, m21 = m.SearchByProjection(s["x3Dc"], s["valid1"], s["obs1"], mp, s["octave1"], s["angle1"], s["k2"], d2, s["u_right2"],
+                                  s["occupied2"], s["cam"], s["mbf"], s["bounds"], s["scale_factors"], th, 0)
+    assert n_ref > 100 and n == n_ref and np.array_equal(m21, m_ref)
+    # local map and Sim3 variants on the same crowded data
+    ms = map_scenario(seed, True)
+    ms["mp_desc1"] = base[rng.integers(0, 10, ms["valid1"].size)].copy()
+    ms["d2"] = base[rng.integers(0, 10, ms["k2"].size)].copy()
+    ms["d2"][:, 5] ^= rng.integers(0, 4, ms["k2"].size).astype(np.uint8)
+    occ = np.zeros(ms["k2"].size, np.uint8)
+    r = O.search_by_projection_map(ms["proj"], ms["view_cos"], ms["level1"], ms["valid1"], ms["obs1"], ms["mp_desc1"], ms["k2"], ms["d2"],
+                                   ms["u_right2"], occ, ms["bounds"], ms["scale_factors"], th / 3, 0.95)
+    g = X.ORBmatcher(0.95, True).SearchByProjectionMap(ms["proj"], ms["view_cos"], ms["level1"], ms["valid1"], ms["obs1"], ms["mp_desc1"],
+                                                       ms["k2"], ms["d2"], ms["u_right2"], occ, ms["bounds"], ms["scale_factors"], th / 3)
+    assert r[0] > 50 and g[0] == r[0] and np.array_equal(g[1], r[1])
+    uvr = ms["proj"].copy()
+    uvr[:, 2] = (np.float32(th) * ms["scale_factors"][ms["level1"]]).astype(np.float32)
+    r = O.search_by_projection_sim3(uvr, ms["level1"], ms["valid1"], ms["mp_desc1"], ms["k2"], ms["d2"], occ, ms["bounds"], 50)
+    g = m.SearchByProjectionSim3(uvr, ms["level1"], ms["valid1"], ms["mp_desc1"], ms["k2"], ms["d2"], occ, ms["bounds"], 50)
+    assert r[0] > 50 and g[0] == r[0] and np.array_equal(g[1], r[1])
