@@ -213,6 +213,13 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
                        const uint8_t* desc2, const float* angle2, int th_dist, float nnratio, int check_ori, int* match12,
                        int* match21, int* nmatches);
 
+/* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:246-312; called after every new observation, src/LocalMapping.cc:
+ * 137,356,373,…, src/Tracking.cc:619,…) for a batch of map points: point p owns the descriptors desc[32 * start[p] ..
+ * 32 * start[p+1]) = the rows pKF->mDescriptors.row(idx) of its good observations in map order (:266-273).
+ * best_idx[p] = BestIdx within the point's rows (the row that becomes mDescriptor), -1 for a point without rows (the reference
+ * returns early, :275-276); best_median[p] (may be NULL) = its median distance.  Host buffers. */
+int orbx_distinctive_descriptors(int n_points, const int* start, const uint8_t* desc, int* best_idx, int* best_median);
+
 /* ---- DBoW2 vocabulary: Frame::ComputeBoW (src/Frame.cc:394-401) -------------------------------------------------------
  * The tree of TemplatedVocabulary<FORB::TDescriptor, FORB> (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h) in device memory
  * and the descent of transform(feature, word_id, weight, nid, levelsup) (:1218-1261) for a whole frame in one launch.  The

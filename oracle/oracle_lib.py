@@ -272,6 +272,15 @@ def search_by_bow(start1, idx1, start2, idx2, valid1, d1, angle1, valid2, d2, an
     return n, m12[:n1], m21[:n2]
 
 
+def distinctive_descriptors(start, desc):
+    start = np.ascontiguousarray(start, dtype=np.int32)
+    desc = np.ascontiguousarray(desc, dtype=np.uint8)
+    n = max(start.size - 1, 0)
+    idx, med = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
+    lib().orc_distinctive_descriptors(n, _p(start), _p(desc), _p(idx), _p(med))
+    return idx[:n], med[:n]
+
+
 class Vocabulary:
     """The node table DBoW2's loadFromTextFile builds (Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1338-1424): node 0 = root,
     then one node per line `parent is_leaf d0 .. d31 weight`; first line `k L scoring weighting`."""

@@ -1049,4 +1049,19 @@ void vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLeaf, 
     }
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:246-312) on the N gathered descriptors: N x N distance table
+// (:281-291, stored as float there; the values are small integers), per row sort + vDists[0.5 * (N - 1)] (:296-298), strict '<'.
+int distinctive_descriptor(const uint8_t* desc, int n, int* medianOut) {
+    int bestMedian = INT_MAX, bestIdx = 0;
+    std::vector<int> row(n);
+    for (int i = 0; i < n; ++i) {
+        for (int j = 0; j < n; ++j) row[j] = i == j ? 0 : descriptor_distance(desc + (size_t)32 * i, desc + (size_t)32 * j);
+        std::sort(row.begin(), row.end());
+        const int median = row[(size_t)(0.5 * (n - 1))];
+        if (median < bestMedian) { bestMedian = median; bestIdx = i; }
+    }
+    if (medianOut) *medianOut = n > 0 ? bestMedian : -1;
+    return n > 0 ? bestIdx : -1;
+}
+
 }  // namespace orc

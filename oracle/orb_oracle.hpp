@@ -112,6 +112,8 @@ int search_by_bow(int nNodes, const int* start1, const uint32_t* idx1, const int
 void vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLeaf, const uint8_t* desc, const double* weight, int L,
                           int n, const uint8_t* feat, int levelsup, uint32_t* wordId, double* w, uint32_t* nodeId);
 
+int distinctive_descriptor(const uint8_t* desc, int n, int* medianOut);
+
 void match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1,
                       int* d2, int* match);
 

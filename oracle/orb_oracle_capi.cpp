@@ -159,6 +159,9 @@ void orc_vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLe
                               int n, const uint8_t* feat, int levelsup, uint32_t* wordId, double* w, uint32_t* nodeId) {
     vocabulary_transform(nNodes, parent, isLeaf, desc, weight, L, n, feat, levelsup, wordId, w, nodeId);
 }
+void orc_distinctive_descriptors(int nPoints, const int* start, const uint8_t* desc, int* bestIdx, int* bestMedian) {
+    for (int p = 0; p < nPoints; ++p) bestIdx[p] = distinctive_descriptor(desc + (size_t)32 * start[p], start[p + 1] - start[p], bestMedian + p);
+}
 double orc_bench_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int threads, int* idx, int* d1, int* d2, int* match) {
     auto t0 = std::chrono::steady_clock::now();
     std::vector<std::thread> pool;

@@ -356,6 +356,17 @@ class ORBmatcher:
                                                 _p(stream) if stream else None))
 
 
+def ComputeDistinctiveDescriptors(start, desc):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:246-312) for a batch of map points: rows start[p]..start[p+1] of
+    desc are point p's observed descriptors.  Returns (best_idx, best_median) int32 [n_points]."""
+    start = np.ascontiguousarray(start, dtype=np.int32)
+    desc = np.ascontiguousarray(desc, dtype=np.uint8)
+    n = max(start.size - 1, 0)
+    idx, med = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
+    _check(lib().orbx_distinctive_descriptors(n, _p(start), _p(desc), _p(idx), _p(med)))
+    return idx[:n], med[:n]
+
+
 class ORBVocabulary:
     """ORB_SLAM2::ORBVocabulary = DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (reference include/ORBVocabulary.h:28-31):
     the tree lives in device memory, transform() is Frame::ComputeBoW's call (src/Frame.cc:394-401)."""

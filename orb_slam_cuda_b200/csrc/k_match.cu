@@ -184,6 +184,46 @@ __global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict
     if (threadIdx.x == 0) score[(size_t)i * kd + j] = total;
 }
 
+// ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:246-312) ---------------------------------------------------
+// One warp per map point; lane i takes observation i (then i + 32, ...): its row of the N x N distance table, the row's median
+// vDists[0.5 * (N - 1)] (:297-298) by bisection on the value (distances are 0..256: 9 counting passes over the N descriptors,
+// which every lane reads at the same address), then the warp keeps the smallest (median, index): strict '<' = first index wins.
+__global__ void __launch_bounds__(256) k_distinctive(int nPoints, const int* __restrict__ start, const uint4* __restrict__ desc,
+                                                      int* __restrict__ bestIdx, int* __restrict__ bestMedian) {
+    const int lane = threadIdx.x & 31;
+    const int pt = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (pt >= nPoints) return;
+    const int b = start[pt], n = start[pt + 1] - b;
+    const int k = (n - 1) / 2;  // (size_t)(0.5 * (N - 1))
+    uint32_t best = 0xFFFFFFFFu;
+    for (int i = lane; i < n; i += 32) {
+        const uint4 a0 = desc[2 * (b + i)], a1 = desc[2 * (b + i) + 1];
+        const uint32_t a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        int lo = 0, hi = 256;  // smallest v with #(d <= v) >= k + 1
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            int cnt = 0;
+            for (int j = 0; j < n; ++j) cnt += hamming256(a, __ldg(&desc[2 * (b + j)]), __ldg(&desc[2 * (b + j) + 1])) <= mid ? 1 : 0;
+            if (cnt >= k + 1) hi = mid;
+            else lo = mid + 1;
+        }
+        best = min(best, ((uint32_t)lo << 16) | (uint32_t)min(i, 0xFFFF));
+    }
+    best = __reduce_min_sync(0xffffffffu, best);
+    if (lane == 0) {
+        bestIdx[pt] = n > 0 ? (int)(best & 0xFFFFu) : -1;
+        bestMedian[pt] = n > 0 ? (int)(best >> 16) : -1;
+    }
+}
+
+int launch_distinctive(int nPoints, const int* start, const uint8_t* desc, int* bestIdx, int* bestMedian, cudaStream_t s) {
+    if (nPoints <= 0) return ORBX_OK;
+    k_distinctive<<<(nPoints + 7) / 8, 256, 0, s>>>(nPoints, start, reinterpret_cast<const uint4*>(desc), bestIdx, bestMedian);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
 int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score, cudaStream_t s) {
     if (kq <= 0 || kd <= 0) return ORBX_OK;
     k_allpairs<<<dim3(kd, kq), AP_THREADS, 0, s>>>(reinterpret_cast<const uint4*>(q), reinterpret_cast<const uint4*>(db), n, kd, th,

@@ -467,6 +467,42 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
     return ORBX_OK;
 }
 
+int orbx_distinctive_descriptors(int n_points, const int* start, const uint8_t* desc, int* best_idx, int* best_median) {
+    if (n_points < 0 || (n_points > 0 && (!start || !best_idx))) {
+        set_error("orbx_distinctive_descriptors: bad argument");
+        return ORBX_E_INVALID;
+    }
+    if (n_points == 0) return ORBX_OK;
+    if (start[0] != 0) {
+        set_error("orbx_distinctive_descriptors: start[0] must be 0");
+        return ORBX_E_INVALID;
+    }
+    for (int i = 0; i < n_points; ++i)
+        if (start[i + 1] < start[i] || start[i + 1] - start[i] > 65535) {
+            set_error("orbx_distinctive_descriptors: point %d has a malformed observation range (at most 65535 observations)", i);
+            return ORBX_E_INVALID;
+        }
+    const int total = start[n_points];
+    if (total > 0 && !desc) {
+        set_error("orbx_distinctive_descriptors: null descriptor table");
+        return ORBX_E_INVALID;
+    }
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = w->stream;
+    if ((rc = upload(w->a, start, (size_t)(n_points + 1) * 4, s)) || (rc = upload(w->b, desc, (size_t)std::max(total, 1) * 32, s)) ||
+        (rc = w->out0.ensure((size_t)n_points * 4)) || (rc = w->out1.ensure((size_t)n_points * 4)))
+        return rc;
+    if ((rc = launch_distinctive(n_points, w->a.as<int>(), w->b.as<uint8_t>(), w->out0.as<int>(), w->out1.as<int>(), s))) return rc;
+    std::vector<int> med;
+    if (!best_median) med.resize(n_points);
+    ORBX_CUDA(cudaMemcpyAsync(best_idx, w->out0.p, (size_t)n_points * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(best_median ? best_median : med.data(), w->out1.p, (size_t)n_points * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypoint* kL, int nL, const uint8_t* descL,
                       const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float mb, float* u_right, float* depth) {
     ExtractorView L, R;

@@ -224,6 +224,7 @@ int launch_search_by_bow(int nItems, const int* nodeOf, const uint32_t* idx1, co
                          const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
                          const uint8_t* desc2, const float* angle2, const int* candOff, uint32_t* cand, int* candCnt, int thDist,
                          float nnratio, int checkOri, int* match12, int* match21, int* nmatches, cudaStream_t s);
+int launch_distinctive(int nPoints, const int* start, const uint8_t* desc, int* bestIdx, int* bestMedian, cudaStream_t s);
 int launch_stereo(const StereoLevels& lv, const orbx_keypoint* kL, int nL, const uint8_t* dL, const orbx_keypoint* kR, int nR,
                   const uint8_t* dR, float mbf, float maxD, float* uRight, float* depth, int* sad, cudaStream_t s);
 
