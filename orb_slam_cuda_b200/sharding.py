@@ -84,14 +84,27 @@ def allpairs_sharded(local_desc: torch.Tensor, k_total: int,
         moved += recv.numel()
     for (c0, c1), recv, work in zip(plan, gathered, works):
         work.wait()  # stream-orders the consumer after this chunk only; later chunks are still in flight
+        if k_local == 0:
+            continue
+        # ONE scoring launch per chunk over the keyframes of every source rank (world x chunk database keyframes): a launch per
+        # (chunk, source) would be a grid of k_local x chunk CTAs — a fraction of the GPU at 8 ranks.  Padded keyframes are
+        # scored and dropped by the column selection below.
+        width = c1 - c0
+        sel, cols = [], []
         for src in range(world):
             sb, se = block_range(k_total, src, world)
             valid = min(c1, se - sb) - c0
-            if valid <= 0 or k_local == 0:
-                continue
-            tmp = torch.empty((k_local, valid), dtype=torch.int32, device=local_desc.device)
-            score_fn(local_desc, recv[src, :valid], tmp)
-            scores[:, sb + c0: sb + c0 + valid] = tmp
+            if valid > 0:
+                sel.extend(range(src * width, src * width + valid))
+                cols.extend(range(sb + c0, sb + c0 + valid))
+        if not cols:
+            continue
+        tmp = torch.empty((k_local, world * width), dtype=torch.int32, device=local_desc.device)
+        score_fn(local_desc, recv.view(world * width, n, 32), tmp)
+        if len(sel) == world * width and cols == list(range(cols[0], cols[0] + len(cols))):
+            scores[:, cols[0]: cols[0] + len(cols)] = tmp
+        else:
+            scores[:, torch.tensor(cols, device=local_desc.device)] = tmp[:, torch.tensor(sel, device=local_desc.device)]
     return scores, moved
 
 
