@@ -213,6 +213,21 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
                        const uint8_t* desc2, const float* angle2, int th_dist, float nnratio, int check_ori, int* match12,
                        int* match21, int* nmatches);
 
+/* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:657-823 with
+ * CheckDistEpipolarLine :140-157; LocalMapping::CreateNewMapPoints, src/LocalMapping.cc:248ff).  Common vocabulary nodes as for
+ * orbx_search_by_bow.  k*, desc* = mvKeysUn / mDescriptors of the two keyframes;
+ *   valid1[i] = !pKF1->GetMapPoint(i) && (!bOnlyStereo || mvuRight[i] >= 0)  (:697-706),  stereo1[i] = mvuRight[i] >= 0;
+ *   valid2[j], stereo2[j] likewise for pKF2 (:724-733);  f12 = F12 row major;  (ex, ey) = the epipole in image 2 (:664-672);
+ *   scale_factors2 / level_sigma2_2 = pKF2->mvScaleFactors / mvLevelSigma2.
+ * match12[i] = j: the pair (i, j) of vMatchedPairs (which lists them in ascending i);  -1: none.  *nmatches = return value.
+ * The reference never sets vbMatched2 (:683), so a second-keyframe feature may be paired with several first-keyframe ones; that is
+ * reproduced.  Host buffers. */
+int orbx_search_for_triangulation(int n_nodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                                  const orbx_keypoint* k1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n2,
+                                  const orbx_keypoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2,
+                                  const float f12[9], float ex, float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                  int nlevels, int check_ori, int* match12, int* nmatches);
+
 /* MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:246-312; called after every new observation, src/LocalMapping.cc:
  * 137,356,373,…, src/Tracking.cc:619,…) for a batch of map points: point p owns the descriptors desc[32 * start[p] ..
  * 32 * start[p+1]) = the rows pKF->mDescriptors.row(idx) of its good observations in map order (:266-273).

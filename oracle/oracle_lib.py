@@ -272,6 +272,21 @@ def search_by_bow(start1, idx1, start2, idx2, valid1, d1, angle1, valid2, d2, an
     return n, m12[:n1], m21[:n2]
 
 
+def search_for_triangulation(start1, idx1, start2, idx2, k1, d1, valid1, stereo1, k2, d2, valid2, stereo2, F12, ex, ey, scale_factors2,
+                             level_sigma2_2, check_ori=True):
+    start1, start2 = (np.ascontiguousarray(a, dtype=np.int32) for a in (start1, start2))
+    idx1, idx2 = (np.ascontiguousarray(a, dtype=np.uint32) for a in (idx1, idx2))
+    k1, k2 = (np.ascontiguousarray(a, dtype=KP_DTYPE) for a in (k1, k2))
+    d1, d2, valid1, valid2, stereo1, stereo2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (d1, d2, valid1, valid2, stereo1, stereo2))
+    F = np.ascontiguousarray(F12, dtype=np.float32).reshape(9)
+    sf, sg = (np.ascontiguousarray(a, dtype=np.float32) for a in (scale_factors2, level_sigma2_2))
+    m12 = np.empty(max(k1.size, 1), np.int32)
+    n = lib().orc_search_for_triangulation(max(start1.size - 1, 0), _p(start1), _p(idx1), _p(start2), _p(idx2), k1.size, _p(k1), _p(d1),
+                                           _p(valid1), _p(stereo1), k2.size, _p(k2), _p(d2), _p(valid2), _p(stereo2), _p(F),
+                                           C.c_float(ex), C.c_float(ey), _p(sf), _p(sg), int(check_ori), _p(m12))
+    return n, m12[:k1.size]
+
+
 def distinctive_descriptors(start, desc):
     start = np.ascontiguousarray(start, dtype=np.int32)
     desc = np.ascontiguousarray(desc, dtype=np.uint8)

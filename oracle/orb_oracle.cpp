@@ -1049,6 +1049,74 @@ void vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLeaf, 
     }
 }
 
+// ORBmatcher::SearchForTriangulation (src/ORBmatcher.cc:657-823) over the common vocabulary nodes, CheckDistEpipolarLine
+// (:140-157) inlined.  vbMatched2 (:683) is never set by the reference, so it is not modelled.
+int search_for_triangulation(int nNodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                             const KeyPoint* k1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n2,
+                             const KeyPoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2, const float* F12,
+                             float ex, float ey, const float* scaleFactors2, const float* levelSigma2, bool checkOri, int* match12) {
+    (void)n2;
+    int nmatches = 0;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    std::vector<int> rotHist[30];
+    const float factor = 1.0f / 30;
+    for (int node = 0; node < nNodes; ++node) {
+        for (int p1 = start1[node]; p1 < start1[node + 1]; ++p1) {
+            const int i1 = (int)idx1[p1];
+            if (!valid1[i1]) continue;  // :697-706
+            const bool bStereo1 = stereo1[i1] != 0;
+            const KeyPoint& kp1 = k1[i1];
+            int bestDist = 50, bestIdx2 = -1;  // TH_LOW
+            for (int p2 = start2[node]; p2 < start2[node + 1]; ++p2) {
+                const int i2 = (int)idx2[p2];
+                if (!valid2[i2]) continue;  // :724-733
+                const bool bStereo2 = stereo2[i2] != 0;
+                const int dist = descriptor_distance(desc1 + (size_t)32 * i1, desc2 + (size_t)32 * i2);
+                if (dist > 50 || dist > bestDist) continue;
+                const KeyPoint& kp2 = k2[i2];
+                if (!bStereo1 && !bStereo2) {
+                    const float distex = ex - kp2.x, distey = ey - kp2.y;
+                    if (distex * distex + distey * distey < 100 * scaleFactors2[kp2.octave]) continue;
+                }
+                const float a = kp1.x * F12[0] + kp1.y * F12[3] + F12[6];
+                const float b = kp1.x * F12[1] + kp1.y * F12[4] + F12[7];
+                const float c = kp1.x * F12[2] + kp1.y * F12[5] + F12[8];
+                const float num = a * kp2.x + b * kp2.y + c;
+                const float den = a * a + b * b;
+                if (den == 0) continue;
+                const float dsqr = num * num / den;
+                if (dsqr < 3.84 * levelSigma2[kp2.octave]) {
+                    bestIdx2 = i2;
+                    bestDist = dist;
+                }
+            }
+            if (bestIdx2 >= 0) {
+                match12[i1] = bestIdx2;
+                nmatches++;
+                if (checkOri) {
+                    float rot = kp1.angle - k2[bestIdx2].angle;
+                    if (rot < 0.0) rot += 360.0f;
+                    int bin = (int)std::round(rot * factor);
+                    if (bin == 30) bin = 0;
+                    rotHist[bin].push_back(i1);
+                }
+            }
+        }
+    }
+    if (checkOri) {
+        int ind1 = -1, ind2 = -1, ind3 = -1;
+        three_maxima(rotHist, 30, ind1, ind2, ind3);
+        for (int i = 0; i < 30; ++i) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (size_t j = 0; j < rotHist[i].size(); ++j) {
+                match12[rotHist[i][j]] = -1;
+                nmatches--;
+            }
+        }
+    }
+    return nmatches;
+}
+
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:246-312) on the N gathered descriptors: N x N distance table
 // (:281-291, stored as float there; the values are small integers), per row sort + vDists[0.5 * (N - 1)] (:296-298), strict '<'.
 int distinctive_descriptor(const uint8_t* desc, int n, int* medianOut) {

@@ -112,6 +112,11 @@ int search_by_bow(int nNodes, const int* start1, const uint32_t* idx1, const int
 void vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLeaf, const uint8_t* desc, const double* weight, int L,
                           int n, const uint8_t* feat, int levelsup, uint32_t* wordId, double* w, uint32_t* nodeId);
 
+int search_for_triangulation(int nNodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                             const KeyPoint* k1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n2,
+                             const KeyPoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2, const float* F12,
+                             float ex, float ey, const float* scaleFactors2, const float* levelSigma2, bool checkOri, int* match12);
+
 int distinctive_descriptor(const uint8_t* desc, int n, int* medianOut);
 
 void match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1,

@@ -159,6 +159,13 @@ void orc_vocabulary_transform(int nNodes, const int* parent, const uint8_t* isLe
                               int n, const uint8_t* feat, int levelsup, uint32_t* wordId, double* w, uint32_t* nodeId) {
     vocabulary_transform(nNodes, parent, isLeaf, desc, weight, L, n, feat, levelsup, wordId, w, nodeId);
 }
+int orc_search_for_triangulation(int nNodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                                 const KeyPoint* k1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n2,
+                                 const KeyPoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2, const float* F12,
+                                 float ex, float ey, const float* scaleFactors2, const float* levelSigma2, int checkOri, int* match12) {
+    return search_for_triangulation(nNodes, start1, idx1, start2, idx2, n1, k1, desc1, valid1, stereo1, n2, k2, desc2, valid2, stereo2,
+                                    F12, ex, ey, scaleFactors2, levelSigma2, checkOri != 0, match12);
+}
 void orc_distinctive_descriptors(int nPoints, const int* start, const uint8_t* desc, int* bestIdx, int* bestMedian) {
     for (int p = 0; p < nPoints; ++p) bestIdx[p] = distinctive_descriptor(desc + (size_t)32 * start[p], start[p + 1] - start[p], bestMedian + p);
 }

@@ -335,6 +335,26 @@ class ORBmatcher:
                                         int(self.mbCheckOrientation), _p(m12), _p(m21), C.byref(n)))
         return n.value, m12[:n1], m21[:n2]
 
+    def SearchForTriangulation(self, start1, idx1, start2, idx2, kps1, desc1, valid1, stereo1, kps2, desc2, valid2, stereo2, F12, ex, ey,
+                               scale_factors2, level_sigma2_2):
+        """SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo), src/ORBmatcher.cc:657-823.
+        Returns (nmatches, match12); vMatchedPairs = [(i, match12[i]) for i where match12[i] >= 0]."""
+        start1, start2 = (np.ascontiguousarray(a, dtype=np.int32) for a in (start1, start2))
+        idx1, idx2 = (np.ascontiguousarray(a, dtype=np.uint32) for a in (idx1, idx2))
+        kps1, kps2 = (np.ascontiguousarray(a, dtype=KP_DTYPE) for a in (kps1, kps2))
+        desc1, desc2, valid1, valid2, stereo1, stereo2 = (np.ascontiguousarray(a, dtype=np.uint8)
+                                                          for a in (desc1, desc2, valid1, valid2, stereo1, stereo2))
+        F = np.ascontiguousarray(F12, dtype=np.float32).reshape(9)
+        sf, sg = (np.ascontiguousarray(a, dtype=np.float32) for a in (scale_factors2, level_sigma2_2))
+        n1, n2 = kps1.size, kps2.size
+        m12 = np.empty(max(n1, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_search_for_triangulation(max(start1.size - 1, 0), _p(start1), _p(idx1), _p(start2), _p(idx2), n1, _p(kps1),
+                                                   _p(desc1), _p(valid1), _p(stereo1), n2, _p(kps2), _p(desc2), _p(valid2), _p(stereo2),
+                                                   _p(F), C.c_float(ex), C.c_float(ey), _p(sf), _p(sg), sf.size,
+                                                   int(self.mbCheckOrientation), _p(m12), C.byref(n)))
+        return n.value, m12[:n1]
+
     def match_bruteforce(self, q, d, th: int = TH_LOW):
         """best / second-best over the whole database (inner loop of SearchByBoW, src/ORBmatcher.cc:187-232):
         returns (idx, d1, d2, match) int32 [nq]."""

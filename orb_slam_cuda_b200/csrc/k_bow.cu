@@ -11,6 +11,8 @@
 //   k_bow_resolve    (1 warp): replays the loop — two smallest free candidates, threshold, ratio test against 256 when
 //                    there is no second (:200-202), assignment, rotation histogram, ComputeThreeMaxima, removals; 32 features
 //                    are scanned in parallel, then decided in order (resolve_common.cuh).
+#include <algorithm>
+
 #include "orbx_internal.h"
 #include "resolve_common.cuh"
 
@@ -158,6 +160,123 @@ __global__ void __launch_bounds__(BOW_RESOLVE_THREADS) k_bow_resolve(int nItems,
     if (lane == 0 && total) atomicAdd(&hist[0], total);
     __syncthreads();
     if (tid == 0) *nmatchesOut = hist[0];
+}
+
+// ---- SearchForTriangulation (src/ORBmatcher.cc:657-823; LocalMapping::CreateNewMapPoints, src/LocalMapping.cc:248ff) ------
+// vbMatched2 is declared (:683) but never set, so the iterations are independent: feature idx1 takes, among the features of its
+// vocabulary node in the other keyframe that are free (no map point, stereo filter), within TH_LOW, far enough from the epipole
+// (:739-745) and close enough to the epipolar line (CheckDistEpipolarLine, :140-157), the one at the smallest distance — the LAST
+// such one in visiting order, because `dist > bestDist` lets an equal distance replace the best (:734, :751-755).
+struct SftParams {
+    float f[9];  // F12, row major
+    float ex, ey;
+    int checkOri;
+};
+
+__global__ void __launch_bounds__(256) k_sft_match(int nItems, const int* __restrict__ nodeOf, const uint32_t* __restrict__ idx1,
+                                                    const int* __restrict__ start2, const uint32_t* __restrict__ idx2,
+                                                    const orbx_keypoint* __restrict__ k1, const uint4* __restrict__ desc1,
+                                                    const uint8_t* __restrict__ valid1, const uint8_t* __restrict__ stereo1,
+                                                    const orbx_keypoint* __restrict__ k2, const uint4* __restrict__ desc2,
+                                                    const uint8_t* __restrict__ valid2, const uint8_t* __restrict__ stereo2,
+                                                    const float* __restrict__ scaleFactors2, const float* __restrict__ levelSigma2,
+                                                    const SftParams P, int* __restrict__ match12, signed char* __restrict__ evBin,
+                                                    int* __restrict__ hist) {
+    const int lane = threadIdx.x & 31;
+    const int item = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (item >= nItems) return;
+    const int i1 = (int)idx1[item];
+    uint32_t best = RS_NONE;  // dist << 16 | (0xFFFF - position): smallest distance, last position
+    uint32_t bestI2 = 0;
+    if (valid1[i1]) {
+        const orbx_keypoint kp1 = k1[i1];
+        const bool st1 = stereo1[i1] != 0;
+        // epipolar line in the second image l = x1' F12 = [a b c] (:143-145)
+        const float a = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.f[0]), __fmul_rn(kp1.y, P.f[3])), P.f[6]);
+        const float b = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.f[1]), __fmul_rn(kp1.y, P.f[4])), P.f[7]);
+        const float c = __fadd_rn(__fadd_rn(__fmul_rn(kp1.x, P.f[2]), __fmul_rn(kp1.y, P.f[5])), P.f[8]);
+        const float den = __fadd_rn(__fmul_rn(a, a), __fmul_rn(b, b));
+        const uint4 a0 = desc1[2 * i1], a1 = desc1[2 * i1 + 1];
+        const int node = nodeOf[item];
+        const int s = start2[node], e = start2[node + 1];
+        for (int p = s + lane; p < e; p += 32) {
+            const int i2 = (int)idx2[p];
+            if (!valid2[i2]) continue;
+            const int dist = hamming32(a0, a1, desc2[2 * i2], desc2[2 * i2 + 1]);
+            if (dist > 50) continue;  // TH_LOW
+            const orbx_keypoint kp2 = k2[i2];
+            if (!st1 && !stereo2[i2]) {
+                const float dx = __fsub_rn(P.ex, kp2.x), dy = __fsub_rn(P.ey, kp2.y);
+                if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.0f, scaleFactors2[kp2.octave])) continue;
+            }
+            if (den == 0.0f) continue;
+            const float num = __fadd_rn(__fadd_rn(__fmul_rn(a, kp2.x), __fmul_rn(b, kp2.y)), c);
+            const float dsqr = __fdiv_rn(__fmul_rn(num, num), den);
+            if (!((double)dsqr < __dmul_rn(3.84, (double)levelSigma2[kp2.octave]))) continue;
+            const uint32_t key = ((uint32_t)dist << 16) | (uint32_t)(0xFFFF - (p - s));
+            if (key < best) { best = key; bestI2 = (uint32_t)i2; }
+        }
+    }
+    const uint32_t m = __reduce_min_sync(0xffffffffu, best);
+    const unsigned who = __ballot_sync(0xffffffffu, best == m && m != RS_NONE);
+    if (!who) return;
+    const int i2 = (int)__shfl_sync(0xffffffffu, bestI2, __ffs(who) - 1);
+    if (lane == 0) {
+        match12[i1] = i2;
+        if (P.checkOri) {
+            const int bin = rotation_bin(k1[i1].angle, k2[i2].angle);
+            evBin[item] = (signed char)bin;
+            atomicAdd(&hist[bin], 1);
+        }
+    }
+}
+
+// ComputeThreeMaxima + removals (:789-806) and the count; one CTA.
+__global__ void __launch_bounds__(256) k_sft_finish(int nItems, const uint32_t* __restrict__ idx1, const signed char* __restrict__ evBin,
+                                                     const int* __restrict__ hist, int checkOri, int n1, int* __restrict__ match12,
+                                                     int* __restrict__ nmatchesOut) {
+    __shared__ int total;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    if (checkOri) {
+        int ind1, ind2, ind3;
+        three_maxima(hist, ind1, ind2, ind3);
+        for (int item = threadIdx.x; item < nItems; item += blockDim.x) {
+            const int b = evBin[item];
+            if (b >= 0 && b != ind1 && b != ind2 && b != ind3) match12[(int)idx1[item]] = -1;
+        }
+    }
+    __syncthreads();
+    int mine = 0;
+    for (int i = threadIdx.x; i < n1; i += blockDim.x) mine += match12[i] >= 0 ? 1 : 0;
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&total, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) *nmatchesOut = total;
+}
+
+int launch_search_for_triangulation(int nItems, const int* nodeOf, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                                    const orbx_keypoint* k1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n2,
+                                    const orbx_keypoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2,
+                                    const float* scaleFactors2, const float* levelSigma2, const float F12[9], float ex, float ey,
+                                    int checkOri, int* match12, signed char* evBin, int* hist, int* nmatches, cudaStream_t s) {
+    (void)n2;
+    SftParams P;
+    for (int i = 0; i < 9; ++i) P.f[i] = F12[i];
+    P.ex = ex; P.ey = ey; P.checkOri = checkOri;
+    ORBX_CUDA(cudaMemsetAsync(match12, 0xFF, (size_t)n1 * 4, s));
+    ORBX_CUDA(cudaMemsetAsync(evBin, 0xFF, (size_t)std::max(nItems, 1), s));
+    ORBX_CUDA(cudaMemsetAsync(hist, 0, 32 * 4, s));
+    if (nItems > 0) {
+        k_sft_match<<<(nItems + 7) / 8, 256, 0, s>>>(nItems, nodeOf, idx1, start2, idx2, k1, reinterpret_cast<const uint4*>(desc1), valid1,
+                                                       stereo1, k2, reinterpret_cast<const uint4*>(desc2), valid2, stereo2, scaleFactors2,
+                                                       levelSigma2, P, match12, evBin, hist);
+        count_launch();
+    }
+    k_sft_finish<<<1, 256, 0, s>>>(nItems, idx1, evBin, hist, checkOri, n1, match12, nmatches);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
 }
 
 int launch_search_by_bow(int nItems, const int* nodeOf, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,

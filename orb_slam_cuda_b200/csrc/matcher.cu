@@ -467,6 +467,93 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
     return ORBX_OK;
 }
 
+int orbx_search_for_triangulation(int n_nodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                                  const orbx_keypoint* k1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n2,
+                                  const orbx_keypoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2,
+                                  const float f12[9], float ex, float ey, const float* scale_factors2, const float* level_sigma2_2,
+                                  int nlevels, int check_ori, int* match12, int* nmatches) {
+    if (n_nodes < 0 || n1 < 0 || n2 < 0 || !nmatches || !f12 || nlevels <= 0 || nlevels > 64 || !scale_factors2 || !level_sigma2_2 ||
+        (n_nodes > 0 && (!start1 || !start2)) || (n1 > 0 && (!k1 || !desc1 || !valid1 || !stereo1 || !match12)) ||
+        (n2 > 0 && (!k2 || !desc2 || !valid2 || !stereo2))) {
+        set_error("orbx_search_for_triangulation: bad argument");
+        return ORBX_E_INVALID;
+    }
+    *nmatches = 0;
+    for (int i = 0; i < n1; ++i) match12[i] = -1;
+    if (n_nodes == 0 || n1 == 0 || n2 == 0) return ORBX_OK;
+    if (start1[0] != 0 || start2[0] != 0) {
+        set_error("orbx_search_for_triangulation: start1[0] and start2[0] must be 0");
+        return ORBX_E_INVALID;
+    }
+    for (int k = 0; k < n_nodes; ++k)
+        if (start1[k + 1] < start1[k] || start2[k + 1] < start2[k] || start2[k + 1] - start2[k] > 65535) {
+            set_error("orbx_search_for_triangulation: node %d has a malformed feature range", k);
+            return ORBX_E_INVALID;
+        }
+    const int nItems = start1[n_nodes], nIdx2 = start2[n_nodes];
+    if ((nItems > 0 && !idx1) || (nIdx2 > 0 && !idx2)) {
+        set_error("orbx_search_for_triangulation: null feature index list");
+        return ORBX_E_INVALID;
+    }
+    for (int i = 0; i < nItems; ++i)
+        if (idx1[i] >= (uint32_t)n1) { set_error("orbx_search_for_triangulation: idx1[%d] out of range", i); return ORBX_E_INVALID; }
+    for (int i = 0; i < nIdx2; ++i)
+        if (idx2[i] >= (uint32_t)n2) { set_error("orbx_search_for_triangulation: idx2[%d] out of range", i); return ORBX_E_INVALID; }
+    for (int i = 0; i < n1; ++i)
+        if (k1[i].octave < 0 || k1[i].octave >= nlevels) { set_error("orbx_search_for_triangulation: k1[%d].octave out of range", i); return ORBX_E_INVALID; }
+    for (int i = 0; i < n2; ++i)
+        if (k2[i].octave < 0 || k2[i].octave >= nlevels) { set_error("orbx_search_for_triangulation: k2[%d].octave out of range", i); return ORBX_E_INVALID; }
+    if (nItems == 0 || nIdx2 == 0) return ORBX_OK;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = w->stream;
+    // one packed upload: [idx1 | nodeOf | start2 | idx2 | scale | sigma2 | k1 | k2 | desc1 | desc2 | valid1 | stereo1 | valid2 | stereo2]
+    const size_t kb = sizeof(orbx_keypoint);
+    const size_t oI1 = 0, oNode = oI1 + (size_t)nItems * 4, oS2 = oNode + (size_t)nItems * 4, oI2 = oS2 + (size_t)(n_nodes + 1) * 4,
+                 oSF = oI2 + (size_t)nIdx2 * 4, oSG = oSF + (size_t)nlevels * 4, oK1 = oSG + (size_t)nlevels * 4, oK2 = oK1 + (size_t)n1 * kb,
+                 oD1 = (oK2 + (size_t)n2 * kb + 15) / 16 * 16, oD2 = oD1 + (size_t)n1 * 32, oV1 = oD2 + (size_t)n2 * 32, oT1 = oV1 + n1,
+                 oV2 = oT1 + n1, oT2 = oV2 + n2, total = oT2 + n2;
+    if ((rc = w->pin.ensure(total))) return rc;
+    uint8_t* hp = w->pin.as<uint8_t>();
+    int* hNode = reinterpret_cast<int*>(hp + oNode);
+    for (int k = 0; k < n_nodes; ++k)
+        for (int i = start1[k]; i < start1[k + 1]; ++i) hNode[i] = k;
+    memcpy(hp + oI1, idx1, (size_t)nItems * 4);
+    memcpy(hp + oS2, start2, (size_t)(n_nodes + 1) * 4);
+    memcpy(hp + oI2, idx2, (size_t)nIdx2 * 4);
+    memcpy(hp + oSF, scale_factors2, (size_t)nlevels * 4);
+    memcpy(hp + oSG, level_sigma2_2, (size_t)nlevels * 4);
+    memcpy(hp + oK1, k1, (size_t)n1 * kb);
+    memcpy(hp + oK2, k2, (size_t)n2 * kb);
+    memcpy(hp + oD1, desc1, (size_t)n1 * 32);
+    memcpy(hp + oD2, desc2, (size_t)n2 * 32);
+    memcpy(hp + oV1, valid1, n1);
+    memcpy(hp + oT1, stereo1, n1);
+    memcpy(hp + oV2, valid2, n2);
+    memcpy(hp + oT2, stereo2, n2);
+    if ((rc = w->a.ensure(total)) || (rc = w->out0.ensure((size_t)n1 * 4 + 16)) || (rc = w->h.ensure((size_t)nItems + 16)) ||
+        (rc = w->status.ensure(32 * 4 + 16)))
+        return rc;
+    ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
+    const uint8_t* dp = w->a.as<uint8_t>();
+    int* dHist = w->status.as<int>();
+    int* dN = dHist + 32;
+    if ((rc = launch_search_for_triangulation(
+             nItems, reinterpret_cast<const int*>(dp + oNode), reinterpret_cast<const uint32_t*>(dp + oI1),
+             reinterpret_cast<const int*>(dp + oS2), reinterpret_cast<const uint32_t*>(dp + oI2), n1,
+             reinterpret_cast<const orbx_keypoint*>(dp + oK1), dp + oD1, dp + oV1, dp + oT1, n2,
+             reinterpret_cast<const orbx_keypoint*>(dp + oK2), dp + oD2, dp + oV2, dp + oT2, reinterpret_cast<const float*>(dp + oSF),
+             reinterpret_cast<const float*>(dp + oSG), f12, ex, ey, check_ori, w->out0.as<int>(), w->h.as<signed char>(), dHist, dN, s)))
+        return rc;
+    int st = 0;
+    ORBX_CUDA(cudaMemcpyAsync(match12, w->out0.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(&st, dN, 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    *nmatches = st;
+    return ORBX_OK;
+}
+
 int orbx_distinctive_descriptors(int n_points, const int* start, const uint8_t* desc, int* best_idx, int* best_median) {
     if (n_points < 0 || (n_points > 0 && (!start || !best_idx))) {
         set_error("orbx_distinctive_descriptors: bad argument");

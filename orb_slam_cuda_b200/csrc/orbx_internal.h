@@ -224,6 +224,11 @@ int launch_search_by_bow(int nItems, const int* nodeOf, const uint32_t* idx1, co
                          const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
                          const uint8_t* desc2, const float* angle2, const int* candOff, uint32_t* cand, int* candCnt, int thDist,
                          float nnratio, int checkOri, int* match12, int* match21, int* nmatches, cudaStream_t s);
+int launch_search_for_triangulation(int nItems, const int* nodeOf, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
+                                    const orbx_keypoint* k1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n2,
+                                    const orbx_keypoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2,
+                                    const float* scaleFactors2, const float* levelSigma2, const float F12[9], float ex, float ey,
+                                    int checkOri, int* match12, signed char* evBin, int* hist, int* nmatches, cudaStream_t s);
 int launch_distinctive(int nPoints, const int* start, const uint8_t* desc, int* bestIdx, int* bestMedian, cudaStream_t s);
 int launch_stereo(const StereoLevels& lv, const orbx_keypoint* kL, int nL, const uint8_t* dL, const orbx_keypoint* kR, int nR,
                   const uint8_t* dR, float mbf, float maxD, float* uRight, float* depth, int* sad, cudaStream_t s);
