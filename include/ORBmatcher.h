@@ -6,8 +6,8 @@
 // SearchForInitialization and ComputeStereoMatches are templates over the frame type so that they bind to the
 // reference's ORB_SLAM2::Frame (its public members mvKeysUn, mDescriptors, mnMinX ... are used exactly as
 // src/ORBmatcher.cc does) without this repository carrying Frame.h.  SearchByProjection (all four overloads) and SearchByBoW
-// (both overloads) bind the same way to Frame / KeyFrame / MapPoint.  The other four matcher routines
-// (SearchForTriangulation, SearchBySim3, Fuse x2) are SURVEY.md §8f "next" rows and stay in the reference's
+// (both overloads) and SearchForTriangulation bind the same way to Frame / KeyFrame / MapPoint.  The other three matcher routines
+// (SearchBySim3, Fuse x2) are SURVEY.md §8f "next" rows and stay in the reference's
 // src/ORBmatcher.cc.
 //
 // Every call here runs on the device; there is no CPU implementation behind it (errors throw std::runtime_error).
@@ -22,6 +22,7 @@
 #include <set>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "ORBextractor.h"
@@ -418,6 +419,62 @@ public:
               "SearchByBoW");
         for (int i = 0; i < n1; ++i)
             if (match12[i] >= 0) vpMatches12[i] = vpMapPoints2[match12[i]];
+        return nmatches;
+    }
+
+    // Matching to triangulate new MapPoints, with the epipolar constraint (LocalMapping::CreateNewMapPoints, src/LocalMapping.cc:248ff);
+    // src/ORBmatcher.cc:657-823.  KeyFrame members read: GetCameraCenter(), GetRotation(), GetTranslation(), fx, fy, cx, cy, N,
+    // mFeatVec, GetMapPoint(idx), mvuRight, mvKeysUn, mDescriptors, mvScaleFactors, mvLevelSigma2.
+    template <class KeyFrameT>
+    int SearchForTriangulation(KeyFrameT* pKF1, KeyFrameT* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
+                               const bool bOnlyStereo) {
+        // epipole in the second image (:664-672)
+        const cv::Mat Cw = pKF1->GetCameraCenter(), R2w = pKF2->GetRotation(), t2w = pKF2->GetTranslation();
+#if ORBX_HAVE_OPENCV
+        const cv::Mat C2 = R2w * Cw + t2w;
+        const float c2[3] = {C2.at<float>(0), C2.at<float>(1), C2.at<float>(2)};
+#else
+        float c2[3];  // cv::gemm on CV_32F accumulates in double
+        for (int r = 0; r < 3; ++r) {
+            double acc = 0;
+            for (int c = 0; c < 3; ++c) acc += (double)R2w.template at<float>(r, c) * (double)Cw.template at<float>(c, 0);
+            c2[r] = (float)(acc + (double)t2w.template at<float>(r, 0));
+        }
+#endif
+        const float invz = 1.0f / c2[2];
+        const float ex = pKF2->fx * c2[0] * invz + pKF2->cx;
+        const float ey = pKF2->fy * c2[1] * invz + pKF2->cy;
+        vMatchedPairs.clear();
+        const int n1 = (int)pKF1->N, n2 = (int)pKF2->N;
+        BowNodes nodes;
+        common_nodes(pKF1->mFeatVec, pKF2->mFeatVec, nodes);
+        if (n1 == 0 || n2 == 0 || nodes.idx1.empty() || nodes.idx2.empty()) return 0;
+        std::vector<unsigned char> valid1(n1), stereo1(n1), valid2(n2), stereo2(n2);
+        for (int i = 0; i < n1; ++i) {
+            stereo1[i] = pKF1->mvuRight[i] >= 0;
+            valid1[i] = !pKF1->GetMapPoint(i) && (!bOnlyStereo || stereo1[i]);  // :697-706
+        }
+        for (int j = 0; j < n2; ++j) {
+            stereo2[j] = pKF2->mvuRight[j] >= 0;
+            valid2[j] = !pKF2->GetMapPoint(j) && (!bOnlyStereo || stereo2[j]);  // :724-733
+        }
+        float f12[9];
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) f12[3 * r + c] = F12.template at<float>(r, c);
+        const cv::Mat d1 = continuous(pKF1->mDescriptors), d2 = continuous(pKF2->mDescriptors);
+        std::vector<int> match12(n1, -1);
+        int nmatches = 0;
+        check(orbx_search_for_triangulation((int)nodes.start1.size() - 1, nodes.start1.data(), nodes.idx1.data(), nodes.start2.data(),
+                                            nodes.idx2.data(), n1, reinterpret_cast<const orbx_keypoint*>(pKF1->mvKeysUn.data()),
+                                            d1.template ptr<unsigned char>(), valid1.data(), stereo1.data(), n2,
+                                            reinterpret_cast<const orbx_keypoint*>(pKF2->mvKeysUn.data()), d2.template ptr<unsigned char>(),
+                                            valid2.data(), stereo2.data(), f12, ex, ey, pKF2->mvScaleFactors.data(),
+                                            pKF2->mvLevelSigma2.data(), (int)pKF2->mvScaleFactors.size(), mbCheckOrientation ? 1 : 0,
+                                            match12.data(), &nmatches),
+              "SearchForTriangulation");
+        vMatchedPairs.reserve(nmatches);
+        for (int i = 0; i < n1; ++i)
+            if (match12[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)match12[i]));  // :808-818
         return nmatches;
     }
 

@@ -45,6 +45,14 @@ struct KeyFrame {  // the members of ORB_SLAM2::KeyFrame that the relocalisation
     std::vector<cv::KeyPoint> mvKeysUn;
     std::vector<MapPoint*> GetMapPointMatches() const { return mvpMapPoints; }
     std::map<unsigned int, std::vector<unsigned int>> mFeatVec;  // DBoW2::FeatureVector (SearchByBoW, src/ORBmatcher.cc:159,522)
+    // SearchForTriangulation (src/ORBmatcher.cc:657-823)
+    int N = 0;
+    std::vector<float> mvuRight, mvLevelSigma2;
+    cv::Mat mRcw, mtcw, mOw;
+    cv::Mat GetRotation() const { return mRcw; }
+    cv::Mat GetTranslation() const { return mtcw; }
+    cv::Mat GetCameraCenter() const { return mOw; }
+    MapPoint* GetMapPoint(size_t i) const { return mvpMapPoints[i]; }
     // loop-detection SearchByProjection (src/ORBmatcher.cc:290-403)
     float fx = 0, fy = 0, cx = 0, cy = 0, mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
     std::vector<float> mvScaleFactors;
@@ -312,6 +320,39 @@ int main(int argc, char** argv) {
             const int n = matcher.SearchByBoW(&KF, F2, matches);
             put_i(out, n);
             for (int j = 0; j < F2.N; ++j) put_i(out, matches[j] ? (int)(matches[j] - points.data()) : -1);
+            // LocalMapping::CreateNewMapPoints (:248ff): SearchForTriangulation between the two keyframes.  Camera 2 sits 0.5 m to the
+            // right of camera 1 at the same orientation, so the epipole is at infinity on the x axis (here: 1e6-ish) and the
+            // epipolar line of (x1, y1) is y = y1 + dy with the fundamental matrix the test passes in argv[8].
+            if (argc >= 9) {
+                KeyFrame K2;
+                K2.mvKeysUn = F2.mvKeysUn; K2.mDescriptors = F2.mDescriptors; K2.mFeatVec = F2.mFeatVec;
+                KF.N = F1.N; K2.N = F2.N;
+                KF.mvuRight.assign(F1.N, -1.f); K2.mvuRight.assign(F2.N, -1.f);
+                for (int i = 0; i < F1.N; i += 3) KF.mvuRight[i] = 1.f;
+                for (int j = 0; j < F2.N; j += 4) K2.mvuRight[j] = 1.f;
+                K2.mvpMapPoints.assign(F2.N, nullptr);
+                for (int j = 0; j < F2.N; j += 6) K2.mvpMapPoints[j] = &points[0];
+                K2.mvScaleFactors = ex.GetScaleFactors();
+                K2.mvLevelSigma2 = ex.GetScaleSigmaSquares();
+                K2.fx = K2.fy = 500.f; K2.cx = 0.5f * w; K2.cy = 0.5f * h;
+                auto mat = [](int r, int c, std::initializer_list<float> v) {
+                    cv::Mat m(r, c, CV_32F);
+                    int i = 0;
+                    for (float x : v) { m.at<float>(i / c, i % c) = x; ++i; }
+                    return m;
+                };
+                KF.mOw = mat(3, 1, {0.f, 0.f, 0.f});
+                K2.mRcw = mat(3, 3, {1.f, 0.f, 0.f, 0.f, 1.f, 0.f, 0.f, 0.f, 1.f});
+                K2.mtcw = mat(3, 1, {-0.5f, 0.01f, 1e-3f});
+                const float dy = (float)atof(argv[8]);
+                cv::Mat F12 = mat(3, 3, {0.f, 0.f, 0.f, 0.f, 0.f, -1.f, 0.f, 1.f, -dy});
+                std::vector<std::pair<size_t, size_t> > pairs;
+                ORBmatcher triMatcher(0.6f, false);
+                const int nt = triMatcher.SearchForTriangulation(&KF, &K2, F12, pairs, false);
+                put_i(out, nt);
+                put_i(out, (int)pairs.size());
+                for (const auto& pr : pairs) { put_i(out, (int)pr.first); put_i(out, (int)pr.second); }
+            }
             fclose(out);
         } else {
             return 2;

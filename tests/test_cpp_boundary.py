@@ -242,7 +242,7 @@ def test_compute_bow_and_search_by_bow(harness, tmp_path):
     voc.to_text(path)
     ref = O.Vocabulary.from_text(path)
     out = tmp_path / "out.bin"
-    r = subprocess.run([harness, "bow", str(raw), str(w), str(h), str(nf), str(path), str(out)], capture_output=True, text=True)
+    r = subprocess.run([harness, "bow", str(raw), str(w), str(h), str(nf), str(path), str(out), "-4"], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     rd = Reader(out.read_bytes())
     assert rd.i32() == 0                       # a missing file: loadFromTextFile returns false
@@ -270,3 +270,23 @@ def test_compute_bow_and_search_by_bow(harness, tmp_path):
     assert n_ref > 30
     assert rd.i32() == n_ref
     assert np.array_equal(rd.arr(np.int32, len(k2)), np.where(m21 >= 0, m21, -1))
+    # SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, false) through the template (src/ORBmatcher.cc:657-823); the second image
+    # is the first moved by (7, -4), so the harness passes F12 for the lines y = y1 - 4 and a camera 0.5 m to the right
+    f32 = np.float32
+    i, j = np.arange(len(k1)), np.arange(len(k2))
+    v1, t1 = (i % 5 == 0).astype(np.uint8), (i % 3 == 0).astype(np.uint8)
+    v2, t2 = (j % 6 != 0).astype(np.uint8), (j % 4 == 0).astype(np.uint8)
+    invz = f32(1.0) / f32(1e-3)
+    ex = f32(f32(f32(500.0) * f32(-0.5)) * invz) + f32(0.5) * f32(w)
+    ey = f32(f32(f32(500.0) * f32(0.01)) * invz) + f32(0.5) * f32(h)
+    sf = (np.float32(1.2) ** np.arange(8)).astype(np.float32)
+    ox = O.Extractor(nf, 1.2, 8, 20, 7)
+    sf, sg = ox.tables()["scale"], ox.tables()["sigma2"]
+    F12 = np.array([[0, 0, 0], [0, 0, -1], [0, 1, 4]], np.float32)
+    n_tri, m_tri = O.search_for_triangulation(s1, i1, s2, i2, k1, d1, v1, t1, k2, d2, v2, t2, F12, float(ex), float(ey), sf, sg, False)
+    assert n_tri > 10
+    assert rd.i32() == n_tri
+    assert rd.i32() == n_tri
+    pairs = rd.arr(np.int32, 2 * n_tri).reshape(-1, 2)
+    want = np.flatnonzero(m_tri >= 0)
+    assert np.array_equal(pairs[:, 0], want) and np.array_equal(pairs[:, 1], m_tri[want])
