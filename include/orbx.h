@@ -213,6 +213,19 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
                        const uint8_t* desc2, const float* angle2, int th_dist, float nnratio, int check_ori, int* match12,
                        int* match21, int* nmatches);
 
+/* The matching core of both ORBmatcher::Fuse overloads: Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-975; candidate loop
+ * :886-945; LocalMapping::SearchInNeighbors, src/LocalMapping.cc:600ff) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
+ * (:977-1100; candidate loop :1049-1075; LoopClosing::SearchAndFuse).  Per map point i that passed the caller's projection and
+ * visibility tests (valid1[i]): uvr[3i..] = u, v, radius = th * mvScaleFactors[nPredictedLevel];  level1[i] = nPredictedLevel;
+ * ur1[i] = u - bf * invz and inv_level_sigma2 = pKF->mvInvLevelSigma2 switch the chi-square gate of the first overload on
+ * (:904-932; ur1 = NULL for the Sim3 overload, which has none);  k2, desc2, u_right2 = pKF->mvKeysUn / mDescriptors / mvuRight
+ * (u_right2 may be NULL: no stereo).  best_idx[i] / best_dist[i] = bestIdx / bestDist of the loop (-1 / 256 when nothing
+ * qualified); the caller applies `bestDist <= TH_LOW` and the map surgery (:948-972 / :1078-1092), which walks pointers and whose
+ * order matters, in its own loop.  Host buffers. */
+int orbx_fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mp_desc1,
+                    const orbx_keypoint* k2, int n2, const uint8_t* desc2, const float* u_right2, const float* inv_level_sigma2,
+                    int nlevels, const float bounds[4], int* best_idx, int* best_dist);
+
 /* ORBmatcher::SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo) (src/ORBmatcher.cc:657-823 with
  * CheckDistEpipolarLine :140-157; LocalMapping::CreateNewMapPoints, src/LocalMapping.cc:248ff).  Common vocabulary nodes as for
  * orbx_search_by_bow.  k*, desc* = mvKeysUn / mDescriptors of the two keyframes;

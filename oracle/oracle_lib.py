@@ -50,7 +50,7 @@ def lib():
 
 
 def _p(a, t=C.c_void_p):
-    return a.ctypes.data_as(t)
+    return None if a is None else a.ctypes.data_as(t)
 
 
 def cv_round(v: float) -> int:
@@ -270,6 +270,22 @@ def search_by_bow(start1, idx1, start2, idx2, valid1, d1, angle1, valid2, d2, an
     n = lib().orc_search_by_bow(start1.size - 1, _p(start1), _p(idx1), _p(start2), _p(idx2), n1, _p(valid1), _p(d1), _p(angle1), n2,
                                 _p(valid2), _p(d2), _p(angle2), int(th_dist), C.c_float(nnratio), int(check_ori), _p(m12), _p(m21))
     return n, m12[:n1], m21[:n2]
+
+
+def fuse_match(uvr, ur1, level1, valid1, mp_desc1, k2, d2, u_right2, inv_level_sigma2, bounds):
+    uvr = np.ascontiguousarray(uvr, dtype=np.float32)
+    ur1 = None if ur1 is None else np.ascontiguousarray(ur1, dtype=np.float32)
+    level1 = np.ascontiguousarray(level1, dtype=np.int32)
+    valid1, mp_desc1, d2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, mp_desc1, d2))
+    k2 = np.ascontiguousarray(k2, dtype=KP_DTYPE)
+    u_right2 = None if u_right2 is None else np.ascontiguousarray(u_right2, dtype=np.float32)
+    sg = np.ascontiguousarray(inv_level_sigma2, dtype=np.float32)
+    b = np.asarray(bounds, dtype=np.float32)
+    n1 = valid1.size
+    idx, dist = np.empty(max(n1, 1), np.int32), np.empty(max(n1, 1), np.int32)
+    lib().orc_fuse_match(n1, _p(uvr), _p(ur1), _p(level1), _p(valid1), _p(mp_desc1), _p(k2), k2.size, _p(d2), _p(u_right2), _p(sg), _p(b),
+                         _p(idx), _p(dist))
+    return idx[:n1], dist[:n1]
 
 
 def search_for_triangulation(start1, idx1, start2, idx2, k1, d1, valid1, stereo1, k2, d2, valid2, stereo2, F12, ex, ey, scale_factors2,

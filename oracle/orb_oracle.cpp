@@ -845,6 +845,45 @@ int search_by_projection_sim3(int n1, const float* uvr, const int* level1, const
     return nmatches;
 }
 
+// The matching core of both ORBmatcher::Fuse overloads: (pKF, vpMapPoints, th) src/ORBmatcher.cc:825-975 (candidate loop
+// :893-945, with the chi-square gate on the reprojection error) and (pKF, Scw, vpPoints, th, vpReplacePoint) :977-1100 (candidate
+// loop :1055-1075, no gate).  The projection and visibility tests before it and the map surgery after it (Replace /
+// AddObservation / AddMapPoint, :948-972) are the caller's.  uvr = (u, v, radius); ur1 = u - bf*invz or NULL for the Sim3 overload.
+void fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
+                const GridFrame& KF, const uint8_t* desc2, const float* uRight2, const float* invLevelSigma2, int* bestIdxOut,
+                int* bestDistOut) {
+    for (int i = 0; i < n1; ++i) {
+        bestIdxOut[i] = -1;
+        bestDistOut[i] = 256;
+        if (!valid1[i]) continue;
+        const float u = uvr[3 * i], v = uvr[3 * i + 1], radius = uvr[3 * i + 2];
+        const int nPredictedLevel = level1[i];
+        const std::vector<size_t> vIndices = KF.features_in_area(u, v, radius, -1, -1);
+        const uint8_t* dMP = mpDesc1 + (size_t)i * 32;
+        int bestDist = 256, bestIdx = -1;
+        for (size_t idx : vIndices) {
+            const KeyPoint& kp = KF.keys[idx];
+            const int kpLevel = kp.octave;
+            if (kpLevel < nPredictedLevel - 1 || kpLevel > nPredictedLevel) continue;
+            if (ur1) {
+                if (uRight2 && uRight2[idx] >= 0) {  // reprojection error in stereo (:904-917)
+                    const float ex = u - kp.x, ey = v - kp.y, er = ur1[i] - uRight2[idx];
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * invLevelSigma2[kpLevel] > 7.8) continue;
+                } else {
+                    const float ex = u - kp.x, ey = v - kp.y;
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * invLevelSigma2[kpLevel] > 5.99) continue;
+                }
+            }
+            const int dist = descriptor_distance(dMP, desc2 + idx * 32);
+            if (dist < bestDist) { bestDist = dist; bestIdx = (int)idx; }
+        }
+        bestIdxOut[i] = bestIdx;
+        bestDistOut[i] = bestDist;
+    }
+}
+
 // ORBmatcher::SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches) — src/ORBmatcher.cc:159-288, and
 // SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) — :522-655.  The vocabulary walk (DBoW2 FeatureVector merge, :175-181,
 // :264-272) stays the caller's: it hands in the common nodes in order, node k holding the feature indices

@@ -102,6 +102,10 @@ int search_by_projection_map(int n1, const float* proj, const float* viewCos, co
 int search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
                               const GridFrame& KF, const uint8_t* desc2, const uint8_t* occupied2, int thDist, int* match21);
 
+void fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
+                const GridFrame& KF, const uint8_t* desc2, const float* uRight2, const float* invLevelSigma2, int* bestIdxOut,
+                int* bestDistOut);
+
 int search_by_bow(int nNodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
                   const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
                   const uint8_t* desc2, const float* angle2, int thDist, float nnratio, bool checkOri, int* match12, int* match21);

@@ -115,6 +115,12 @@ int orc_search_by_projection_sim3(int n1, const float* uvr, const int* level1, c
     GridFrame KF(k2, n2, bounds[0], bounds[1], bounds[2], bounds[3]);
     return search_by_projection_sim3(n1, uvr, level1, valid1, mpDesc1, KF, desc2, occupied2, thDist, match21);
 }
+void orc_fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
+                    const KeyPoint* k2, int n2, const uint8_t* desc2, const float* uRight2, const float* invLevelSigma2,
+                    const float* bounds, int* bestIdx, int* bestDist) {
+    GridFrame KF(k2, n2, bounds[0], bounds[1], bounds[2], bounds[3]);
+    fuse_match(n1, uvr, ur1, level1, valid1, mpDesc1, KF, desc2, uRight2, invLevelSigma2, bestIdx, bestDist);
+}
 int orc_search_by_bow(int nNodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
                       const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
                       const uint8_t* desc2, const float* angle2, int thDist, float nnratio, int checkOri, int* match12, int* match21) {

@@ -335,6 +335,23 @@ class ORBmatcher:
                                         int(self.mbCheckOrientation), _p(m12), _p(m21), C.byref(n)))
         return n.value, m12[:n1], m21[:n2]
 
+    def FuseMatch(self, uvr, ur1, level1, valid1, mp_desc1, kps2, desc2, u_right2, inv_level_sigma2, bounds):
+        """The candidate loop of ORBmatcher::Fuse (src/ORBmatcher.cc:886-945 with the chi-square gate, ur1 given; :1049-1075 without,
+        ur1 = None).  Returns (best_idx, best_dist) per map point."""
+        uvr = np.ascontiguousarray(uvr, dtype=np.float32)
+        ur1 = None if ur1 is None else np.ascontiguousarray(ur1, dtype=np.float32)
+        level1 = np.ascontiguousarray(level1, dtype=np.int32)
+        valid1, mp_desc1, desc2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, mp_desc1, desc2))
+        kps2 = np.ascontiguousarray(kps2, dtype=KP_DTYPE)
+        u_right2 = None if u_right2 is None else np.ascontiguousarray(u_right2, dtype=np.float32)
+        sg = np.ascontiguousarray(inv_level_sigma2, dtype=np.float32)
+        b = np.asarray(bounds, dtype=np.float32)
+        n1 = valid1.size
+        idx, dist = np.empty(max(n1, 1), np.int32), np.empty(max(n1, 1), np.int32)
+        _check(lib().orbx_fuse_match(n1, _p(uvr), _p(ur1), _p(level1), _p(valid1), _p(mp_desc1), _p(kps2), kps2.size, _p(desc2),
+                                     _p(u_right2), _p(sg), sg.size, _p(b), _p(idx), _p(dist)))
+        return idx[:n1], dist[:n1]
+
     def SearchForTriangulation(self, start1, idx1, start2, idx2, kps1, desc1, valid1, stereo1, kps2, desc2, valid2, stereo2, F12, ex, ey,
                                scale_factors2, level_sigma2_2):
         """SearchForTriangulation(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo), src/ORBmatcher.cc:657-823.

@@ -640,4 +640,83 @@ int launch_search_by_projection_sim3(int n1, const float* uvr, const int* level1
     return ORBX_OK;
 }
 
+// ---- Fuse (both overloads): the candidate loop (src/ORBmatcher.cc:893-945 and :1055-1075) ----------------------------------
+// Independent per map point: KeyFrame::GetFeaturesInArea(u, v, radius), level gate, optional chi-square gate on the reprojection
+// error (stereo 7.8 / mono 5.99, float product compared in double), smallest Hamming distance, first in visiting order.
+__global__ void __launch_bounds__(256) k_fuse_match(int n1, const float* __restrict__ uvr, const float* __restrict__ ur1,
+                                                     const int* __restrict__ level1, const uint8_t* __restrict__ valid1,
+                                                     const uint4* __restrict__ mpDesc1, const orbx_keypoint* __restrict__ k2,
+                                                     const uint4* __restrict__ desc2, const float* __restrict__ uRight2,
+                                                     const float* __restrict__ invLevelSigma2, float minX, float minY, float invW,
+                                                     float invH, const int* __restrict__ sorted, const int* __restrict__ cellStart,
+                                                     int* __restrict__ bestIdx, int* __restrict__ bestDist) {
+    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (i >= n1) return;
+    uint32_t best = RS_NONE, bestI2 = 0;
+    if (valid1[i]) {
+        const float u = uvr[3 * i], v = uvr[3 * i + 1], r = uvr[3 * i + 2];
+        const int pred = level1[i];
+        const int cx0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(u, minX), r), invW)));
+        const int cx1 = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(u, minX), r), invW)));
+        const int cy0 = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(v, minY), r), invH)));
+        const int cy1 = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(v, minY), r), invH)));
+        if (cx0 < GRID_COLS && cx1 >= 0 && cy0 < GRID_ROWS && cy1 >= 0) {
+            const uint4 a0 = mpDesc1[2 * i], a1 = mpDesc1[2 * i + 1];
+            int visited = 0;
+            for (int ix = cx0; ix <= cx1; ++ix) {
+                const int b = cellStart[ix * GRID_ROWS + cy0], e = cellStart[ix * GRID_ROWS + cy1 + 1];
+                for (int base = b; base < e; base += 32) {
+                    const int p = base + lane;
+                    if (p < e) {
+                        const int i2 = sorted[p];
+                        const orbx_keypoint kp = k2[i2];
+                        bool ok = fabsf(__fsub_rn(kp.x, u)) < r && fabsf(__fsub_rn(kp.y, v)) < r && !(kp.octave < pred - 1 || kp.octave > pred);
+                        if (ok && ur1) {
+                            const float ex = __fsub_rn(u, kp.x), ey = __fsub_rn(v, kp.y);
+                            float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                            double lim = 5.99;
+                            const float uR = uRight2 ? uRight2[i2] : -1.0f;
+                            if (uR >= 0.0f) {
+                                const float er = __fsub_rn(ur1[i], uR);
+                                e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                                lim = 7.8;
+                            }
+                            ok = !((double)__fmul_rn(e2, invLevelSigma2[kp.octave]) > lim);
+                        }
+                        if (ok) {
+                            const uint32_t dist = (uint32_t)hamming32B(a0, a1, desc2[2 * i2], desc2[2 * i2 + 1]);
+                            const uint32_t key = (dist << 20) | (uint32_t)min(visited + (p - base), 0xFFFFF);
+                            if (key < best) { best = key; bestI2 = (uint32_t)i2; }
+                        }
+                    }
+                    visited += min(32, e - base);
+                }
+            }
+        }
+    }
+    const uint32_t m = __reduce_min_sync(0xffffffffu, best);
+    const unsigned who = __ballot_sync(0xffffffffu, best == m && m != RS_NONE);
+    const int src = who ? __ffs(who) - 1 : 0;
+    const uint32_t i2 = __shfl_sync(0xffffffffu, bestI2, src);
+    if (lane == 0) {
+        bestIdx[i] = who ? (int)i2 : -1;
+        bestDist[i] = who ? (int)(m >> 20) : 256;
+    }
+}
+
+int launch_fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
+                      const orbx_keypoint* k2, int n2, const uint8_t* desc2, const float* uRight2, const float* invLevelSigma2,
+                      const float bounds[4], int* cellOf, int* sorted, int* cellStart, int* bestIdx, int* bestDist, cudaStream_t s) {
+    const float invW = (float)GRID_COLS / (bounds[1] - bounds[0]), invH = (float)GRID_ROWS / (bounds[3] - bounds[2]);
+    k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, bounds[0], bounds[2], invW, invH, cellOf, sorted, cellStart);
+    count_launch();
+    k_fuse_match<<<(n1 + 7) / 8, 256, 0, s>>>(n1, uvr, ur1, level1, valid1, reinterpret_cast<const uint4*>(mpDesc1), k2,
+                                                reinterpret_cast<const uint4*>(desc2), uRight2, invLevelSigma2, bounds[0], bounds[2], invW,
+                                                invH, sorted, cellStart, bestIdx, bestDist);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
 }  // namespace orbx

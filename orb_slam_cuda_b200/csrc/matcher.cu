@@ -467,6 +467,57 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
     return ORBX_OK;
 }
 
+int orbx_fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mp_desc1,
+                    const orbx_keypoint* k2, int n2, const uint8_t* desc2, const float* u_right2, const float* inv_level_sigma2,
+                    int nlevels, const float bounds[4], int* best_idx, int* best_dist) {
+    if (n1 < 0 || n2 < 0 || !bounds || nlevels <= 0 || nlevels > 64 || (n1 > 0 && (!uvr || !level1 || !valid1 || !mp_desc1 || !best_idx)) ||
+        (n2 > 0 && (!k2 || !desc2)) || (ur1 && !inv_level_sigma2) || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) {
+        set_error("orbx_fuse_match: bad argument (bounds = {minX, maxX, minY, maxY})");
+        return ORBX_E_INVALID;
+    }
+    for (int i = 0; i < n1; ++i) {
+        best_idx[i] = -1;
+        if (best_dist) best_dist[i] = 256;
+    }
+    if (n1 == 0 || n2 == 0) return ORBX_OK;
+    for (int j = 0; j < n2; ++j)
+        if (k2[j].octave < 0 || k2[j].octave >= nlevels) { set_error("orbx_fuse_match: k2[%d].octave out of range", j); return ORBX_E_INVALID; }
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = w->stream;
+    // one packed upload: [uvr | ur1 | level1 | uRight2 | invSigma2 | mp_desc1 | valid1]
+    const size_t oX = 0, oU = oX + (size_t)n1 * 12, oL = oU + (size_t)n1 * 4, oR = oL + (size_t)n1 * 4, oS = oR + (size_t)n2 * 4,
+                 oD = (oS + (size_t)nlevels * 4 + 15) / 16 * 16, oV = oD + (size_t)n1 * 32, total = oV + n1;
+    if ((rc = w->pin.ensure(total)) || (rc = w->a.ensure(total))) return rc;
+    uint8_t* hp = w->pin.as<uint8_t>();
+    memcpy(hp + oX, uvr, (size_t)n1 * 12);
+    if (ur1) memcpy(hp + oU, ur1, (size_t)n1 * 4);
+    memcpy(hp + oL, level1, (size_t)n1 * 4);
+    if (u_right2) memcpy(hp + oR, u_right2, (size_t)n2 * 4);
+    if (inv_level_sigma2) memcpy(hp + oS, inv_level_sigma2, (size_t)nlevels * 4);
+    memcpy(hp + oD, mp_desc1, (size_t)n1 * 32);
+    memcpy(hp + oV, valid1, n1);
+    ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
+    if ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
+        (rc = w->out0.ensure((size_t)n1 * 4)) || (rc = w->out1.ensure((size_t)n1 * 4)) ||
+        (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)))
+        return rc;
+    const uint8_t* dp = w->a.as<uint8_t>();
+    int* cellOf = w->f.as<int>();
+    int* sorted = cellOf + n2;
+    int* cellStart = sorted + n2;
+    if ((rc = launch_fuse_match(n1, reinterpret_cast<const float*>(dp + oX), ur1 ? reinterpret_cast<const float*>(dp + oU) : nullptr,
+                                reinterpret_cast<const int*>(dp + oL), dp + oV, dp + oD, w->c.as<orbx_keypoint>(), n2, w->d.as<uint8_t>(),
+                                u_right2 ? reinterpret_cast<const float*>(dp + oR) : nullptr, reinterpret_cast<const float*>(dp + oS),
+                                bounds, cellOf, sorted, cellStart, w->out0.as<int>(), w->out1.as<int>(), s)))
+        return rc;
+    ORBX_CUDA(cudaMemcpyAsync(best_idx, w->out0.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
+    if (best_dist) ORBX_CUDA(cudaMemcpyAsync(best_dist, w->out1.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 int orbx_search_for_triangulation(int n_nodes, const int* start1, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
                                   const orbx_keypoint* k1, const uint8_t* desc1, const uint8_t* valid1, const uint8_t* stereo1, int n2,
                                   const orbx_keypoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2,

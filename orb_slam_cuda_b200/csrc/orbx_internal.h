@@ -229,6 +229,9 @@ int launch_search_for_triangulation(int nItems, const int* nodeOf, const uint32_
                                     const orbx_keypoint* k2, const uint8_t* desc2, const uint8_t* valid2, const uint8_t* stereo2,
                                     const float* scaleFactors2, const float* levelSigma2, const float F12[9], float ex, float ey,
                                     int checkOri, int* match12, signed char* evBin, int* hist, int* nmatches, cudaStream_t s);
+int launch_fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
+                      const orbx_keypoint* k2, int n2, const uint8_t* desc2, const float* uRight2, const float* invLevelSigma2,
+                      const float bounds[4], int* cellOf, int* sorted, int* cellStart, int* bestIdx, int* bestDist, cudaStream_t s);
 int launch_distinctive(int nPoints, const int* start, const uint8_t* desc, int* bestIdx, int* bestMedian, cudaStream_t s);
 int launch_stereo(const StereoLevels& lv, const orbx_keypoint* kL, int nL, const uint8_t* dL, const orbx_keypoint* kR, int nR,
                   const uint8_t* dR, float mbf, float maxD, float* uRight, float* depth, int* sad, cudaStream_t s);

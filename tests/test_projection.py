@@ -317,3 +317,41 @@ def test_search_by_projection_dense_competition(seed, th):
     r = O.search_by_projection_sim3(uvr, ms["level1"], ms["valid1"], ms["mp_desc1"], ms["k2"], ms["d2"], occ, ms["bounds"], 50)
     g = m.SearchByProjectionSim3(uvr, ms["level1"], ms["valid1"], ms["mp_desc1"], ms["k2"], ms["d2"], occ, ms["bounds"], 50)
     assert r[0] > 50 and g[0] == r[0] and np.array_equal(g[1], r[1])
+
+
+def test_oracle_kat_fuse_match():
+    """Fuse's candidate loop (src/ORBmatcher.cc:886-945): level gate, chi-square gate (mono 5.99 / stereo 7.8 on e2 * invSigma2), best
+    distance with the first candidate winning ties; the Sim3 overload (:1049-1075) has no gate."""
+    k2 = np.array([kp(200, 200, 1), kp(202, 200, 1), kp(201, 201, 3), kp(210, 200, 1)], dtype=O.KP_DTYPE)
+    d2 = np.zeros((4, 32), np.uint8)
+    d2[0, 0], d2[1, 0], d2[2, 0], d2[3, 0] = 0x03, 0x0C, 0x00, 0x00       # 2, 2, 0, 0 bits from the zero descriptor
+    inv = (1.0 / (SF * SF)).astype(np.float32)
+    uvr = np.array([[200.5, 200.0, 20.0]], np.float32)
+    mp = np.zeros((1, 32), np.uint8)
+    # level 3 is outside [pred - 1, pred] = [0, 1]; keypoint 3 is 9.5 px away: e2 * inv = 90 / 1.44 > 5.99 -> gated; 0 beats 1 (first)
+    idx, dist = O.fuse_match(uvr, [190.0], [1], [1], mp, k2, d2, None, inv, BOUNDS)
+    assert (idx[0], dist[0]) == (0, 2)
+    # without the gate (Sim3 overload) the far keypoint with distance 0 wins
+    idx, dist = O.fuse_match(uvr, None, [1], [1], mp, k2, d2, None, inv, BOUNDS)
+    assert (idx[0], dist[0]) == (3, 0)
+    # stereo keypoints add the right-image error: er = 190 - 150 = 40 -> gated, so keypoint 1 (mono) is left
+    ur2 = np.array([150.0, -1.0, -1.0, -1.0], np.float32)
+    idx, dist = O.fuse_match(uvr, [190.0], [1], [1], mp, k2, d2, ur2, inv, BOUNDS)
+    assert (idx[0], dist[0]) == (1, 2)
+    assert O.fuse_match(uvr, [190.0], [1], [0], mp, k2, d2, None, inv, BOUNDS)[0][0] == -1
+    assert tuple(a[0] for a in O.fuse_match(np.array([[50.0, 50.0, 5.0]], np.float32), None, [1], [1], mp, k2, d2, None, inv, BOUNDS)) == (-1, 256)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,stereo,gate,th", [(31, True, True, 3.0), (32, False, True, 4.0), (33, True, False, 4.0), (34, False, False, 10.0)])
+def test_fuse_match_gpu(seed, stereo, gate, th):
+    import orb_slam_cuda_b200 as X
+    s = map_scenario(seed, stereo)
+    uvr = s["proj"].copy()
+    uvr[:, 2] = (np.float32(th) * s["scale_factors"][s["level1"]]).astype(np.float32)
+    ur1 = s["proj"][:, 2].copy() if gate else None
+    inv = (np.float32(1.0) / (s["scale_factors"] * s["scale_factors"])).astype(np.float32)
+    r_idx, r_dist = O.fuse_match(uvr, ur1, s["level1"], s["valid1"], s["mp_desc1"], s["k2"], s["d2"], s["u_right2"], inv, s["bounds"])
+    idx, dist = X.ORBmatcher().FuseMatch(uvr, ur1, s["level1"], s["valid1"], s["mp_desc1"], s["k2"], s["d2"], s["u_right2"], inv, s["bounds"])
+    assert (r_idx >= 0).sum() > 50 and np.array_equal(idx, r_idx) and np.array_equal(dist, r_dist)
+    assert ((r_dist <= 50) & (r_idx >= 0)).sum() > 20
