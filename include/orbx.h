@@ -213,6 +213,18 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
                        const uint8_t* desc2, const float* angle2, int th_dist, float nnratio, int check_ori, int* match12,
                        int* match21, int* nmatches);
 
+/* cvtColor(im, im, CV_RGB2GRAY | CV_BGR2GRAY | CV_RGBA2GRAY | CV_BGRA2GRAY) of Tracking::GrabImageStereo / RGBD / Monocular
+ * (src/Tracking.cc:221-246, :261-274, :294-307): channels = 3 or 4 (alpha ignored), 8 bit, strides in bytes.
+ *   ORBX_GRAY_BGR          the first channel is blue (mbRGB == false)
+ *   ORBX_GRAY_CV2_COEFFS   OpenCV 2.4 / 3.x fixed point (4899, 9617, 1868, >> 14); default is OpenCV 4.x (9798, 19235, 3735, >> 15)
+ * The host form copies in and out; the device form converts device buffers on `stream` so that the gray frame feeds
+ * orbx_extract_device without leaving the GPU. */
+#define ORBX_GRAY_BGR 1
+#define ORBX_GRAY_CV2_COEFFS 2
+int orbx_cvt_color_gray(const uint8_t* src, long long src_stride, int w, int h, int channels, int flags, uint8_t* dst, long long dst_stride);
+int orbx_cvt_color_gray_device(const uint8_t* d_src, long long src_stride, int w, int h, int channels, int flags, uint8_t* d_dst,
+                               long long dst_stride, void* stream);
+
 /* The matching core of both ORBmatcher::Fuse overloads: Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-975; candidate loop
  * :886-945; LocalMapping::SearchInNeighbors, src/LocalMapping.cc:600ff) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
  * (:977-1100; candidate loop :1049-1075; LoopClosing::SearchAndFuse).  Per map point i that passed the caller's projection and

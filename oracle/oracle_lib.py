@@ -303,6 +303,17 @@ def search_for_triangulation(start1, idx1, start2, idx2, k1, d1, valid1, stereo1
     return n, m12[:k1.size]
 
 
+def cvt_color_gray(img, bgr=False, cv2_coeffs=False):
+    """cv::cvtColor 8-bit RGB(A)/BGR(A) -> gray in OpenCV's fixed point (numpy restatement; pinned against cv2 4.13 for the default
+    coefficients in tests/test_color.py; the 14-bit set is OpenCV 2.4 / 3.x's published constants)."""
+    img = np.asarray(img, dtype=np.uint8)
+    c = [img[..., i].astype(np.int64) for i in range(3)]
+    r, g, b = (c[2], c[1], c[0]) if bgr else (c[0], c[1], c[2])
+    if cv2_coeffs:
+        return ((r * 4899 + g * 9617 + b * 1868 + (1 << 13)) >> 14).astype(np.uint8)
+    return ((r * 9798 + g * 19235 + b * 3735 + (1 << 14)) >> 15).astype(np.uint8)
+
+
 def distinctive_descriptors(start, desc):
     start = np.ascontiguousarray(start, dtype=np.int32)
     desc = np.ascontiguousarray(desc, dtype=np.uint8)

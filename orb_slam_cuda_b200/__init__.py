@@ -393,6 +393,20 @@ class ORBmatcher:
                                                 _p(stream) if stream else None))
 
 
+GRAY_BGR, GRAY_CV2_COEFFS = 1, 2
+
+
+def cvtColorGray(img, bgr: bool = False, cv2_coeffs: bool = False):
+    """cvtColor(img, CV_RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) as Tracking::GrabImage* does (src/Tracking.cc:221-246):
+    img uint8 [h, w, 3 or 4] -> uint8 [h, w]."""
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w, ch = img.shape
+    out = np.empty((h, w), np.uint8)
+    _check(lib().orbx_cvt_color_gray(_p(img), C.c_longlong(w * ch), w, h, ch, (GRAY_BGR if bgr else 0) | (GRAY_CV2_COEFFS if cv2_coeffs else 0),
+                                     _p(out), C.c_longlong(w)))
+    return out
+
+
 def ComputeDistinctiveDescriptors(start, desc):
     """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:246-312) for a batch of map points: rows start[p]..start[p+1] of
     desc are point p's observed descriptors.  Returns (best_idx, best_median) int32 [n_points]."""

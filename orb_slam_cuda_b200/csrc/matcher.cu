@@ -467,6 +467,36 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
     return ORBX_OK;
 }
 
+int orbx_cvt_color_gray_device(const uint8_t* d_src, long long src_stride, int w, int h, int channels, int flags, uint8_t* d_dst,
+                               long long dst_stride, void* stream) {
+    if (!d_src || !d_dst || w <= 0 || h <= 0 || (channels != 3 && channels != 4) || src_stride < (long long)w * channels || dst_stride < w) {
+        set_error("orbx_cvt_color_gray: bad argument (channels 3 or 4, strides in bytes)");
+        return ORBX_E_INVALID;
+    }
+    return launch_gray(d_src, src_stride, w, h, channels, (flags & ORBX_GRAY_BGR) ? 1 : 0, (flags & ORBX_GRAY_CV2_COEFFS) ? 14 : 15, d_dst,
+                       dst_stride, static_cast<cudaStream_t>(stream));
+}
+
+int orbx_cvt_color_gray(const uint8_t* src, long long src_stride, int w, int h, int channels, int flags, uint8_t* dst, long long dst_stride) {
+    if (!src || !dst || w <= 0 || h <= 0 || (channels != 3 && channels != 4) || src_stride < (long long)w * channels || dst_stride < w) {
+        set_error("orbx_cvt_color_gray: bad argument (channels 3 or 4, strides in bytes)");
+        return ORBX_E_INVALID;
+    }
+    Workspace* wk;
+    int rc = workspace(&wk);
+    if (rc) return rc;
+    cudaStream_t s = wk->stream;
+    const size_t inBytes = (size_t)w * channels * h, outBytes = (size_t)w * h;
+    if ((rc = wk->a.ensure(inBytes)) || (rc = wk->out0.ensure(outBytes))) return rc;
+    ORBX_CUDA(cudaMemcpy2DAsync(wk->a.p, (size_t)w * channels, src, (size_t)src_stride, (size_t)w * channels, h, cudaMemcpyHostToDevice, s));
+    if ((rc = launch_gray(wk->a.as<uint8_t>(), (long long)w * channels, w, h, channels, (flags & ORBX_GRAY_BGR) ? 1 : 0,
+                          (flags & ORBX_GRAY_CV2_COEFFS) ? 14 : 15, wk->out0.as<uint8_t>(), w, s)))
+        return rc;
+    ORBX_CUDA(cudaMemcpy2DAsync(dst, (size_t)dst_stride, wk->out0.p, (size_t)w, (size_t)w, h, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 int orbx_fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mp_desc1,
                     const orbx_keypoint* k2, int n2, const uint8_t* desc2, const float* u_right2, const float* inv_level_sigma2,
                     int nlevels, const float bounds[4], int* best_idx, int* best_dist) {

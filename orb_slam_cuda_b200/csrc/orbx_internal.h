@@ -232,6 +232,8 @@ int launch_search_for_triangulation(int nItems, const int* nodeOf, const uint32_
 int launch_fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mpDesc1,
                       const orbx_keypoint* k2, int n2, const uint8_t* desc2, const float* uRight2, const float* invLevelSigma2,
                       const float bounds[4], int* cellOf, int* sorted, int* cellStart, int* bestIdx, int* bestDist, cudaStream_t s);
+int launch_gray(const uint8_t* src, long long srcStride, int w, int h, int channels, int bgr, int shift, uint8_t* dst, long long dstStride,
+                cudaStream_t s);
 int launch_distinctive(int nPoints, const int* start, const uint8_t* desc, int* bestIdx, int* bestMedian, cudaStream_t s);
 int launch_stereo(const StereoLevels& lv, const orbx_keypoint* kL, int nL, const uint8_t* dL, const orbx_keypoint* kR, int nR,
                   const uint8_t* dR, float mbf, float maxD, float* uRight, float* depth, int* sad, cudaStream_t s);
