@@ -37,7 +37,24 @@ SCALE, LEVELS, INI_TH, MIN_TH = 1.2, 8, 20, 7
 # launch, divided by 512): profiles/r01_ncu_full_b.csv (pyramid, blur) and profiles/r01_ncu_full_c.csv (the others).
 NCU_TRAFFIC_PER_FRAME = {"kitti": {"Pyramid/Resize": 3_415_000, "FAST+Grid": 1_686_000, "Make quadtree": 182_000,
                                    "Gaussian Blur": 3_283_000, "Compute angle + ORB descriptor + Compute scale": 3_049_000}}
+# warp instructions per frame of the whole extractor step (ncu smsp__inst_executed.sum over the 12 kernels of a 512-frame launch,
+# profiles/r01_ncu_full_final.csv): the path is bound by instruction issue, not by HBM
+NCU_WARP_INST_PER_FRAME = {"kitti": 4_017_030_987 / 512}
 METRIC = "frames/s ORB extract @1241x376 2k feats"
+
+
+def issue_roofline(workload, frames_per_s_per_gpu, clocks):
+    """The bound that actually holds for this integer path: warp instructions issued per second against 148 SMs x 4 schedulers x
+    SM clock (one warp instruction per scheduler per cycle)."""
+    per_frame = NCU_WARP_INST_PER_FRAME.get(workload)
+    if not per_frame:
+        return None
+    sm_hz = ((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
+    peak = 148 * 4 * sm_hz
+    ach = frames_per_s_per_gpu * per_frame
+    return {"bound": "warp-instruction issue", "achieved": ach / 1e12, "peak": peak / 1e12, "unit": "T warp-inst/s", "frac": ach / peak,
+            "warp_instructions_per_frame": per_frame,
+            "source": "ncu smsp__inst_executed.sum over the step's 12 kernels (profiles/r01_ncu_full_final.csv), whole step, all stages"}
 
 
 def parse():
@@ -527,7 +544,8 @@ def run_ours(args, emit=print):
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                      "avg_launch_ms": stage[dom],
                      "pipeline": {"bytes_per_frame": wl["bytes_per_frame"], "achieved": value / world * wl["bytes_per_frame"] / 1e9,
-                                  "frac": value / world * wl["bytes_per_frame"] / 1e9 / peak}},
+                                  "frac": value / world * wl["bytes_per_frame"] / 1e9 / peak},
+                     "issue": issue_roofline(args.workload, value / world, clocks)},
         "stage_ms_per_step": stage,
         "status": status,
     }
