@@ -225,3 +225,36 @@ def test_other_scale_factors(sf, nl):
         a, b = gx.image_pyramid_level(l, padded=True), ox.level_padded(l)
         assert np.array_equal(a, b), f"sf {sf} level {l}: {(a != b).sum()} padded pixels differ"
     assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od)
+
+
+def test_full_size_batch_properties():
+    """BASELINE.json's full size (512 KITTI frames of 1241x376, 2000 features per frame) through the chunked host pipeline, checked by
+    properties that do not need the oracle on every frame: copies of the same frame anywhere in the batch give byte-identical
+    keypoints and descriptors, a second run of the batch reproduces the first (no state leaks between chunks, lanes or runs), every
+    frame holds nfeatures..nfeatures+3 keypoints in level-major order inside the image, and the distinct frames equal the oracle."""
+    nf, b, pool = 2000, 512, 8
+    gx, ox = X.ORBextractor(nf, 1.2, 8, 20, 7), O.Extractor(nf, 1.2, 8, 20, 7)
+    base = np.stack([synth.frame("kitti", 300 + i) for i in range(pool)])
+    frames = base[np.arange(b) % pool].copy()
+    kps, desc, counts = gx.extract_batch(frames)
+    kps, desc, counts = kps.copy(), desc.copy(), counts.copy()
+    kps2, desc2, counts2 = gx.extract_batch(frames)
+    assert np.array_equal(counts, counts2)
+    for f in range(b):  # slots beyond counts[f] are not written
+        n = counts[f]
+        assert np.array_equal(kps[f, :n].view(np.uint8), kps2[f, :n].view(np.uint8)) and np.array_equal(desc[f, :n], desc2[f, :n]), f
+    first_of = {}
+    for f in range(b):
+        key = f % pool
+        n = counts[f]
+        assert nf <= n <= nf + 8 * 3, (f, n)   # the quadtree may overshoot by up to 3 per level
+        k = kps[f, :n]
+        assert (np.diff(k["octave"]) >= 0).all() and k["x"].min() >= 0 and k["x"].max() < 1241 and k["y"].min() >= 0 and k["y"].max() < 376
+        if key in first_of:
+            g = first_of[key]
+            assert counts[g] == n and np.array_equal(kps[g, :n].view(np.uint8), k.view(np.uint8)) and np.array_equal(desc[g, :n], desc[f, :n])
+        else:
+            first_of[key] = f
+            ok, od = ox.extract(frames[f])
+            assert n == len(ok) and np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(desc[f, :n], od)
+    assert len(first_of) == pool
