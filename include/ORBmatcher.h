@@ -6,8 +6,8 @@
 // SearchForInitialization and ComputeStereoMatches are templates over the frame type so that they bind to the
 // reference's ORB_SLAM2::Frame (its public members mvKeysUn, mDescriptors, mnMinX ... are used exactly as
 // src/ORBmatcher.cc does) without this repository carrying Frame.h.  SearchByProjection (all four overloads) and SearchByBoW
-// (both overloads) and SearchForTriangulation bind the same way to Frame / KeyFrame / MapPoint.  The other three matcher routines
-// (SearchBySim3, Fuse x2) are SURVEY.md §8f "next" rows and stay in the reference's
+// (both overloads), SearchForTriangulation and SearchBySim3 bind the same way to Frame / KeyFrame / MapPoint.  The two Fuse overloads
+// (their candidate loops are orbx_fuse_match; the map surgery around them is pointer work) are SURVEY.md §8f "next" rows and stay in the reference's
 // src/ORBmatcher.cc.
 //
 // Every call here runs on the device; there is no CPU implementation behind it (errors throw std::runtime_error).
@@ -478,6 +478,66 @@ public:
         return nmatches;
     }
 
+    // Search matches between MapPoints seen in KF1 and KF2 transforming by a Sim3 [s12*R12|t12] (LoopClosing::ComputeSim3,
+    // src/LoopClosing.cc:357); src/ORBmatcher.cc:1102-1326.  The two projection passes (:1150-1225, :1228-1305) gather their
+    // candidates' inputs here and run their candidate loops on the device (orbx_fuse_match without the chi-square gate); the
+    // agreement check (:1307-1323) is host code.  KeyFrame members read: fx, fy, cx, cy, GetRotation(), GetTranslation(),
+    // GetMapPointMatches(), IsInImage(), mvScaleFactors, mvKeysUn, mDescriptors, mnMinX..mnMaxY; MapPoint: isBad(), GetWorldPos(),
+    // GetIndexInKeyFrame(), GetMin/MaxDistanceInvariance(), PredictScale(), GetDescriptor().
+    template <class KeyFrameT, class MapPointT>
+    int SearchBySim3(KeyFrameT* pKF1, KeyFrameT* pKF2, std::vector<MapPointT*>& vpMatches12, const float& s12, const cv::Mat& R12,
+                     const cv::Mat& t12, const float th) {
+        const std::vector<MapPointT*> vpMapPoints1 = pKF1->GetMapPointMatches(), vpMapPoints2 = pKF2->GetMapPointMatches();
+        const int N1 = (int)vpMapPoints1.size(), N2 = (int)vpMapPoints2.size();
+        std::vector<bool> vbAlreadyMatched1(N1, false), vbAlreadyMatched2(N2, false);
+        for (int i = 0; i < N1; i++) {
+            MapPointT* pMP = vpMatches12[i];
+            if (pMP) {
+                vbAlreadyMatched1[i] = true;
+                const int idx2 = pMP->GetIndexInKeyFrame(pKF2);
+                if (idx2 >= 0 && idx2 < N2) vbAlreadyMatched2[idx2] = true;
+            }
+        }
+        // transformation between the cameras (:1119-1122)
+        float sR12[9], sR21[9], t12f[3], t21[3];
+#if ORBX_HAVE_OPENCV
+        {
+            const cv::Mat a = s12 * R12, b = (1.0 / s12) * R12.t();
+            const cv::Mat c = -b * t12;
+            mat3(a, sR12); mat3(b, sR21); vec3(t12, t12f); vec3(c, t21);
+        }
+#else
+        {
+            float r[9];
+            mat3(R12, r);
+            vec3(t12, t12f);
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) {
+                    sR12[3 * i + j] = (float)((double)s12 * (double)r[3 * i + j]);
+                    sR21[3 * i + j] = (float)((1.0 / (double)s12) * (double)r[3 * j + i]);
+                }
+            for (int i = 0; i < 3; ++i) {
+                double acc = 0;
+                for (int j = 0; j < 3; ++j) acc += (double)sR21[3 * i + j] * (double)t12f[j];
+                t21[i] = (float)(-acc);
+            }
+        }
+#endif
+        std::vector<int> vnMatch1(N1, -1), vnMatch2(N2, -1);
+        // transform from KF1 to KF2 and search (:1150-1225), then from KF2 to KF1 (:1228-1305); both project with pKF1's intrinsics
+        sim3_pass(pKF1, pKF2, vpMapPoints1, vbAlreadyMatched1, sR21, t21, pKF1->fx, pKF1->fy, pKF1->cx, pKF1->cy, th, vnMatch1);
+        sim3_pass(pKF2, pKF1, vpMapPoints2, vbAlreadyMatched2, sR12, t12f, pKF1->fx, pKF1->fy, pKF1->cx, pKF1->cy, th, vnMatch2);
+        int nFound = 0;  // check agreement (:1307-1323)
+        for (int i1 = 0; i1 < N1; i1++) {
+            const int idx2 = vnMatch1[i1];
+            if (idx2 >= 0 && vnMatch2[idx2] == i1) {
+                vpMatches12[i1] = vpMapPoints2[idx2];
+                nFound++;
+            }
+        }
+        return nFound;
+    }
+
     static const int TH_LOW = 50;
     static const int TH_HIGH = 100;
     static const int HISTO_LENGTH = 30;
@@ -486,6 +546,67 @@ public:
         if (rc != ORBX_OK) throw std::runtime_error(std::string(what) + ": " + orbx_last_error());
     }
     static cv::Mat continuous(const cv::Mat& m) { return m.isContinuous() ? m : m.clone(); }
+
+    // SearchBySim3 helpers.  gemm3: out = M * p + t for a 3x3 float M the way cv::gemm evaluates it on CV_32F (double accumulator).
+    static void gemm3(const float* M, const float* p, const float* t, float* out) {
+        for (int r = 0; r < 3; ++r) {
+            double acc = 0;
+            for (int c = 0; c < 3; ++c) acc += (double)M[3 * r + c] * (double)p[c];
+            out[r] = (float)(acc + (double)t[r]);
+        }
+    }
+    static void mat3(const cv::Mat& m, float* out) {
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) out[3 * r + c] = m.template at<float>(r, c);
+    }
+    static void vec3(const cv::Mat& m, float* out) {
+        for (int r = 0; r < 3; ++r) out[r] = m.template at<float>(r, 0);
+    }
+    // One projection pass of SearchBySim3: the map points seen in pSrc, moved into pSrc's camera (R p + t of pSrc) and across the
+    // Sim3 ([M | t]), projected into pDst's image; the candidate loop runs on the device.
+    template <class KeyFrameT, class MapPointT>
+    void sim3_pass(KeyFrameT* pSrc, KeyFrameT* pDst, const std::vector<MapPointT*>& vpPoints, const std::vector<bool>& vbAlready,
+                   const float* M, const float* t, float fx, float fy, float cx, float cy, float th, std::vector<int>& vnMatch) const {
+        const int n1 = (int)vpPoints.size(), n2 = (int)pDst->mvKeysUn.size();
+        if (n1 == 0 || n2 == 0) return;
+        float Rs[9], ts[3];
+        mat3(pSrc->GetRotation(), Rs);
+        vec3(pSrc->GetTranslation(), ts);
+        std::vector<float> uvr(3 * (size_t)n1, 0.f);
+        std::vector<int> level(n1, 0);
+        std::vector<unsigned char> valid(n1, 0), mpDesc((size_t)n1 * 32, 0);
+        for (int i = 0; i < n1; ++i) {
+            MapPointT* pMP = vpPoints[i];
+            if (!pMP || vbAlready[i] || pMP->isBad()) continue;
+            float pw[3], own[3], pc[3];
+            vec3(pMP->GetWorldPos(), pw);
+            gemm3(Rs, pw, ts, own);   // p3Dc1 = R1w*p3Dw + t1w
+            gemm3(M, own, t, pc);     // p3Dc2 = sR21*p3Dc1 + t21
+            if (pc[2] < 0.0) continue;  // depth must be positive
+            const float invz = 1.0 / pc[2];
+            const float x = pc[0] * invz, y = pc[1] * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!pDst->IsInImage(u, v)) continue;
+            const float dist3D = (float)std::sqrt((double)pc[0] * pc[0] + (double)pc[1] * pc[1] + (double)pc[2] * pc[2]);  // cv::norm
+            if (dist3D < pMP->GetMinDistanceInvariance() || dist3D > pMP->GetMaxDistanceInvariance()) continue;
+            level[i] = pMP->PredictScale(dist3D, pDst);
+            uvr[3 * i] = u;
+            uvr[3 * i + 1] = v;
+            uvr[3 * i + 2] = th * pDst->mvScaleFactors[level[i]];
+            const cv::Mat d = pMP->GetDescriptor();
+            std::memcpy(&mpDesc[(size_t)i * 32], d.template ptr<unsigned char>(), 32);
+            valid[i] = 1;
+        }
+        const cv::Mat d2 = continuous(pDst->mDescriptors);
+        const float bounds[4] = {(float)pDst->mnMinX, (float)pDst->mnMaxX, (float)pDst->mnMinY, (float)pDst->mnMaxY};
+        std::vector<int> bestIdx(n1, -1), bestDist(n1, 256);
+        check(orbx_fuse_match(n1, uvr.data(), nullptr, level.data(), valid.data(), mpDesc.data(),
+                              reinterpret_cast<const orbx_keypoint*>(pDst->mvKeysUn.data()), n2, d2.template ptr<unsigned char>(), nullptr,
+                              nullptr, 64, bounds, bestIdx.data(), bestDist.data()),
+              "SearchBySim3");
+        for (int i = 0; i < n1; ++i)
+            if (bestIdx[i] >= 0 && bestDist[i] <= TH_HIGH) vnMatch[i] = bestIdx[i];  // :1221-1224
+    }
 
     // The common nodes of two DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned int>>) in map order — the walk of
     // src/ORBmatcher.cc:176-256 — flattened for orbx_search_by_bow.

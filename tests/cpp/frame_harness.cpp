@@ -30,6 +30,8 @@ struct MapPoint {  // the members of ORB_SLAM2::MapPoint that SearchByProjection
     float mTrackProjX = 0, mTrackProjY = 0, mTrackProjXR = 0, mTrackViewCos = 0;
     int mnTrackScaleLevel = 0;
     bool isBad() const { return mbBad; }
+    int idxInOther = -1;  // SearchBySim3: GetIndexInKeyFrame(pKF2)
+    template <class K> int GetIndexInKeyFrame(K*) const { return idxInOther; }
     float GetMinDistanceInvariance() const { return 3.5f; }
     float GetMaxDistanceInvariance() const { return 15.5f; }
     template <class F> int PredictScale(float, F*) const { return mnTrackScaleLevel; }
@@ -249,6 +251,46 @@ int main(int argc, char** argv) {
             const int ns = loopMatcher.SearchByProjection(&KC, Scw, cands, matched, 10);
             put_i(out, ns);
             for (int j = 0; j < Cur.N; ++j) put_i(out, matched[j] ? (int)(matched[j] - points.data()) : -1);
+            // LoopClosing::ComputeSim3 (:357): SearchBySim3 between the last frame (keyframe 1, its points at depth 5 in its camera)
+            // and the current one (keyframe 2, own points likewise), both at the identity pose, Sim3 = translation (-0.07, 0.04, 0),
+            // which at fx = 500 and z = 5 is the image shift (7, -4)
+            {
+                std::vector<MapPoint> p1(Last.N), p2(Cur.N);
+                KeyFrame K1, K2;
+                auto setup = [&](KeyFrame& K, Frame& F, std::vector<MapPoint>& pts, int skip) {
+                    K.mvKeysUn = F.mvKeysUn; K.mDescriptors = F.mDescriptors; K.mvScaleFactors = F.mvScaleFactors;
+                    K.fx = K.fy = 500.f; K.cx = 0.5f * w; K.cy = 0.5f * h;
+                    K.mnMinX = 0; K.mnMaxX = (float)w; K.mnMinY = 0; K.mnMaxY = (float)h;
+                    K.mRcw = cv::Mat(3, 3, CV_32F); K.mtcw = cv::Mat(3, 1, CV_32F);
+                    for (int r = 0; r < 3; ++r) { K.mtcw.at<float>(r, 0) = 0.f; for (int c = 0; c < 3; ++c) K.mRcw.at<float>(r, c) = r == c ? 1.f : 0.f; }
+                    K.mvpMapPoints.assign(F.N, nullptr);
+                    for (int i = 0; i < F.N; ++i) {
+                        if (i % skip == 0) continue;
+                        MapPoint& P = pts[i];
+                        P.mWorldPos = cv::Mat(3, 1, CV_32F);
+                        P.mWorldPos.at<float>(0, 0) = (F.mvKeysUn[i].pt.x - K.cx) * 5.f / K.fx;
+                        P.mWorldPos.at<float>(1, 0) = (F.mvKeysUn[i].pt.y - K.cy) * 5.f / K.fy;
+                        P.mWorldPos.at<float>(2, 0) = 5.f;
+                        P.mDescriptor = F.mDescriptors.row(i);
+                        P.mnTrackScaleLevel = F.mvKeysUn[i].octave;
+                        P.mbBad = i % 17 == 0;
+                        K.mvpMapPoints[i] = &P;
+                    }
+                };
+                setup(K1, Last, p1, 6);
+                setup(K2, Cur, p2, 7);
+                cv::Mat R12(3, 3, CV_32F), t12(3, 1, CV_32F);
+                for (int r = 0; r < 3; ++r) for (int c = 0; c < 3; ++c) R12.at<float>(r, c) = r == c ? 1.f : 0.f;
+                t12.at<float>(0, 0) = -0.07f; t12.at<float>(1, 0) = 0.04f; t12.at<float>(2, 0) = 0.f;
+                std::vector<MapPoint*> m12(Last.N, nullptr);
+                for (int i = 4; i < Last.N; i += 25) if (K1.mvpMapPoints[i]) { m12[i] = &p2[1]; }   // already matched: skipped
+                p2[1].idxInOther = 1;
+                ORBmatcher simMatcher(0.75f, true);
+                const float s12 = 1.f;
+                const int nf2 = simMatcher.SearchBySim3(&K1, &K2, m12, s12, R12, t12, 7.5f);
+                put_i(out, nf2);
+                for (int i = 0; i < Last.N; ++i) put_i(out, m12[i] ? (int)(m12[i] - p2.data()) : -1);
+            }
             // Tracking::TrackReferenceKeyFrame (:842): SearchByBoW(keyframe, frame) with a toy vocabulary — node id = 5 descriptor bits,
             // features appended in index order as DBoW2 does
             auto featvec = [](const cv::Mat& D, std::map<unsigned int, std::vector<unsigned int>>& fv) {

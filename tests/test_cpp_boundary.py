@@ -204,6 +204,39 @@ def test_track_with_motion_model_projection(harness, tmp_path):
     assert rd.i32() == n_ref4
     got4 = rd.arr(np.int32, n2)
     assert np.array_equal(got4, np.where(occ3 == 1, 0, np.where(m_ref4 >= 0, keep[np.maximum(m_ref4, 0)], -1)))
+    # SearchBySim3 (src/ORBmatcher.cc:1102-1326) through the template: both keyframes at the identity pose, points at depth 5 in their
+    # own camera, Sim3 = translation (-0.07, 0.04, 0) = the image shift (7, -4) at fx = 500
+    inv_any = np.ones(8, f32)
+    bounds = (0.0, float(w), 0.0, float(h))
+
+    def sim3_pass(ks, ds, skip, already, tvec, kd, dd):
+        n = len(ks)
+        j = np.arange(n)
+        pw = np.stack([((ks["x"] - cx) * f32(5.0) / fx).astype(f32), ((ks["y"] - cy) * f32(5.0) / fy).astype(f32), np.full(n, 5.0, f32)], 1)
+        pc = (pw.astype(np.float64) + tvec.astype(np.float64)[None, :]).astype(f32)
+        invz = (1.0 / pc[:, 2].astype(np.float64)).astype(f32)
+        u = (fx * (pc[:, 0] * invz).astype(f32)).astype(f32) + cx
+        v = (fy * (pc[:, 1] * invz).astype(f32)).astype(f32) + cy
+        d3 = np.sqrt((pc.astype(np.float64) ** 2).sum(axis=1)).astype(f32)
+        ok = (j % skip != 0) & (j % 17 != 0) & ~already & ~(pc[:, 2] < 0) & (u >= 0) & (u < f32(w)) & (v >= 0) & (v < f32(h))
+        ok &= ~(d3 < f32(3.5)) & ~(d3 > f32(15.5))
+        uvr = np.stack([u, v, (f32(7.5) * sf[ks["octave"]]).astype(f32)], 1).astype(f32)
+        idx, dist = O.fuse_match(uvr, None, ks["octave"], ok.astype(np.uint8), ds, kd, dd, None, inv_any, bounds)
+        return np.where((idx >= 0) & (dist <= 100), idx, -1)
+
+    t12 = np.array([-0.07, 0.04, 0.0], f32)
+    t21 = (-(t12.astype(np.float64))).astype(f32)
+    already1 = (i % 25 == 4) & (i % 6 != 0)
+    already2 = np.zeros(n2, bool)
+    already2[1] = already1.any()
+    vn1 = sim3_pass(k1, d1, 6, already1, t21, k2, d2)
+    vn2 = sim3_pass(k2, d2, 7, already2, t12, k1, d1)
+    want = np.where(already1, 1, -1)
+    agree = (vn1 >= 0) & (vn2[np.maximum(vn1, 0)] == i)
+    want = np.where(agree, vn1, want)
+    assert agree.sum() > 50
+    assert rd.i32() == int(agree.sum())
+    assert np.array_equal(rd.arr(np.int32, n1), want)
     # fifth part: SearchByBoW(keyframe, frame) (src/ORBmatcher.cc:159-288), node id = 5 descriptor bits
     from test_bow import common_nodes, feature_vectors
     s1, i1, s2, i2 = common_nodes(feature_vectors(d1, 5), feature_vectors(d2, 5))
