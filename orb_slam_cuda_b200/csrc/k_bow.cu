@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(256) k_bow_candidates(int nItems, const int* _
     if (item >= nItems) return;
     const int i1 = (int)idx1[item];
     int count = 0;
-    Top4 mine;
+    TopK mine;
     mine.clear();
     if (valid1[i1]) {
         const int node = nodeOf[item];

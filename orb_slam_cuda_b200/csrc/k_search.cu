@@ -111,7 +111,7 @@ __global__ void __launch_bounds__(256) k_sfi_candidates(const orbx_keypoint* __r
     const int i1 = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i1 >= n1) return;
     int count = 0;
-    Top4 mine;
+    TopK mine;
     mine.clear();
     if (k1[i1].octave <= 0) {
         const float x = prev[2 * i1], y = prev[2 * i1 + 1];
@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(256) k_sbp_candidates(int n1, const float* __r
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i >= n1) return;
     int count = 0;
-    Top4 mine;
+    TopK mine;
     mine.clear();
     if (valid1[i]) {
         float u, v, ur, r = 0.f;

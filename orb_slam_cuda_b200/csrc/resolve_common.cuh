@@ -66,9 +66,8 @@ struct TopK {
         return found >= need || kept <= RS_K;
     }
 };
-using Top4 = TopK;  // historical name in the kernels
 
-// Candidate kernels: every lane pushed the candidates it wrote into its own Top4; the warp merges them into the feature's 4
+// Candidate kernels: every lane pushed the candidates it wrote into its own TopK; the warp merges them into the feature's RS_K
 // smallest keys (keys are unique: the position is part of the key) and lane 0 stores them.
 __device__ __forceinline__ uint32_t* top_keys(int* candCnt, int n) { return reinterpret_cast<uint32_t*>(candCnt + (n + 3) / 4 * 4); }
 __device__ __forceinline__ const uint32_t* top_keys(const int* candCnt, int n) {
@@ -118,17 +117,8 @@ __device__ __forceinline__ void fetch_feature(const int* candCnt, int n, int i, 
     }
 }
 
-// Lane-local walk of one candidate list (entries dist << 16 | i2, in visiting order).
-template <class Free> __device__ __forceinline__ void scan_list(const uint32_t* __restrict__ c, int cnt, Free free, Top4& t) {
-    t.clear();
-#pragma unroll 4
-    for (int p = 0; p < cnt; ++p) {
-        const uint32_t e = __ldg(c + p);
-        t.push((e & 0xFFFF0000u) | (uint32_t)p, e & 0xFFFFu, free(e & 0xFFFFu, e >> 16));
-    }
-}
-
-// The rescan of the slow path: best / second best over the whole list.
+// The rescan of the slow path: a lane-local walk of the candidate list (entries dist << 16 | i2, in visiting order) for the best /
+// second best among the entries that are still free.
 template <class Free>
 __device__ __forceinline__ void rescan_list(const uint32_t* __restrict__ c, int cnt, Free free, uint32_t& b1, uint32_t& i1, uint32_t& b2,
                                             uint32_t& i2) {
