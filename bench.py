@@ -68,6 +68,7 @@ def parse():
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames of the cpu_baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-match", action="store_true")
+    ap.add_argument("--no-latency", action="store_true")
     return ap.parse_args()
 
 
@@ -554,7 +555,7 @@ def run_ours(args, emit=print):
         match["popc_bound_gmatch_per_s"] = 148 * 16 * sm_hz * 1e6 / 8 / 1e9 * world
         match["popc_bound"] = "148 SMs x 16 POPC/clk/SM x SM clock / 8 POPC per pair (x N GPUs)"
         line["match"] = match
-    if world == 1:
+    if world == 1 and not args.no_latency:
         line["latency"] = latency_leg(X, wl, w, h, args.workload, cpu=not args.no_cpu_baseline and world == 1)
     if not args.no_cpu_baseline and world == 1:
         threads = host_threads()

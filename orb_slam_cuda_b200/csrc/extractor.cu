@@ -203,6 +203,17 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
     }
     ORBX_CUDA(cudaStreamSynchronize(ex->stream));
     batch = std::max(batch, ex->w == w && ex->h == h ? ex->batchCap : 1);
+    // the layout is rebuilt in place: until it is complete the handle has NO geometry, so a failure below (OOM while growing,
+    // an empty level, a TMA encode error) leaves a handle that reconfigures on the next call instead of one that launches on
+    // half-built state
+    ex->w = ex->h = 0;
+    ex->batchCap = 0;
+    ex->lastBatch = 0;
+    if (ex->graphExec) {
+        cudaGraphExecDestroy(ex->graphExec);
+        ex->graphExec = nullptr;
+    }
+    ex->graphSeen = false;
     FrameGeom& g = ex->g;
     memset(&g, 0, sizeof g);
     g.nlevels = nl;
@@ -575,8 +586,33 @@ int orbx_extract_batch_device(orbx_extractor* ex, const uint8_t* dFrames, int ba
     if ((rc = configure(ex, w, h, batch))) return rc;
     cudaStream_t s = stream ? (cudaStream_t)stream : ex->stream;
     ex->lastFrameBase = 0;
-    return run_pipeline(ex, dFrames, batch, stride, frameStride, dKps, dDesc, cap, dCounts,
-                        dStatus ? dStatus : ex->status.as<int>(), s);
+    int* dSt = dStatus ? dStatus : ex->status.as<int>();
+    // Large batches run as SUB-BATCHES whose intermediates (planes, blurred levels, cell lists: ~3.8 MB per KITTI frame) stay
+    // in the 126 MB L2 between the stages, alternating over two streams so one sub-batch's small tail kernels overlap the
+    // next one's wide ones.  Stage timing (orbx_extractor_enable_timing) measures the unsplit sequence.
+    static const int subPref = []() { const char* e = getenv("ORBX_SUB_BATCH"); return e ? atoi(e) : 0; }();
+    if (subPref <= 0 || batch <= subPref || ex->timing)
+        return run_pipeline(ex, dFrames, batch, stride, frameStride, dKps, dDesc, cap, dCounts, dSt, s);
+    if (!ex->stream2) ORBX_CUDA(cudaStreamCreateWithFlags(&ex->stream2, cudaStreamNonBlocking));
+    while (ex->pipeEv.size() < 2) {
+        cudaEvent_t e;
+        ORBX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ex->pipeEv.push_back(e);
+    }
+    ORBX_CUDA(cudaMemsetAsync(dSt, 0, sizeof(int), s));
+    ORBX_CUDA(cudaEventRecord(ex->pipeEv[0], s));
+    ORBX_CUDA(cudaStreamWaitEvent(ex->stream2, ex->pipeEv[0], 0));
+    for (int f0 = 0, k = 0; f0 < batch; f0 += subPref, ++k) {
+        const int nb = std::min(subPref, batch - f0);
+        if ((rc = run_pipeline(ex, dFrames + (size_t)f0 * frameStride, nb, stride, frameStride, dKps + (size_t)f0 * cap,
+                               dDesc + (size_t)f0 * cap * 32, cap, dCounts + f0, dSt, (k & 1) ? ex->stream2 : s, false, f0)))
+            return rc;
+    }
+    ORBX_CUDA(cudaEventRecord(ex->pipeEv[1], ex->stream2));
+    ORBX_CUDA(cudaStreamWaitEvent(s, ex->pipeEv[1], 0));
+    ex->lastBatch = batch;
+    ex->lastScratchBase = 0;
+    return ORBX_OK;
 }
 
 static bool is_pinned(const void* p) {

@@ -288,11 +288,8 @@ int launch_search_by_bow(int nItems, const int* nodeOf, const uint32_t* idx1, co
         set_error("SearchByBoW: %d + %d features do not fit the resolve kernel's shared memory", nItems, n2);
         return ORBX_E_INVALID;
     }
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        ORBX_CUDA(cudaFuncSetAttribute(k_bow_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static size_t configured[ORBX_MAX_DEVICES] = {};
+    if (int rcAttr = ensure_dynamic_smem((const void*)k_bow_resolve, smem, configured)) return rcAttr;
     if (nItems > 0) {
         k_bow_candidates<<<(nItems + 7) / 8, 256, 0, s>>>(nItems, nodeOf, idx1, start2, idx2, valid1, reinterpret_cast<const uint4*>(desc1),
                                                             valid2, reinterpret_cast<const uint4*>(desc2), candOff, cand, candCnt);

@@ -5,22 +5,31 @@
 // cv::FAST ignores a 3-px rim, so the DETECTABLE regions [ini + 3, ini + cell + 3) tile a level exactly, and a pixel's
 // corner score does not depend on the cell it is in.  What is per cell is (a) non-max suppression — rim pixels are
 // never scored, so NMS must not look across a cell seam — and (b) the fallback to minThFAST when the cell produced no
-// keypoint.  One CTA therefore handles a STRIP of several horizontally adjacent cells of one cell row:
-//   tile   the strip's window is staged into shared memory by one TMA box load (origin rounded down to 16 bytes);
-//   A      quick reject, four pixels per lane as packed bytes: saturating v +- t once per word, then carry-less byte
-//          compares of the 8 EVEN ring points (rows y+-3, y+-2, y realigned with funnel shifts).  A run of 9 ring points
-//          holds 4 consecutive even ones, so a pixel survives iff 4 consecutive even points are all brighter (or all
-//          darker).  Warps walk rows, lanes walk 32-bit words, so there is no index division;
-//   B      survivors (dense list) get OpenCV's cornerScore<16>: max over the 16 arcs of 9 of the min signed difference,
-//          both polarities at once as packed 16-bit pairs (VIMNMX3.S16x2), minus 1.  score >= t is exactly the
-//          16-point segment test, so no separate run-of-9 detection is needed; corners store the score in a shared
-//          score tile (0 = not a corner) and join the corner list;
-//   C      corners strictly greater than their 8 neighbours OF THE SAME CELL survive and are counted per cell;
+// keypoint.  One CTA owns a STRIP of several horizontally adjacent cells of one cell row and is PERSISTENT OVER FRAMES:
+// it walks a slice of the batch with a two-stage TMA / mbarrier ring (the window of frame f + 1 is in flight while
+// frame f is scored), so the strip geometry, the column tables and the thread -> (row, word) mapping are built once per
+// CTA instead of once per frame.  Per frame:
+//   A1     opposite-pair reject, four pixels per lane as packed bytes: an arc of 9 ring points holds one point of every
+//          diametral pair, so a pixel can only be a corner if ring point (0,+3) or (0,-3) is brighter than v + t, or one
+//          of them is darker than v - t (OpenCV's own first test, d = tab[ptr[0]] | tab[ptr[8]]).  Three row loads, no
+//          realignment; words with a live pixel are compacted into a word list (one ballot per warp);
+//   A2     the words of the list get the test on all 8 EVEN ring points (rows y+-3, y+-2, y realigned with funnel
+//          shifts): a run of 9 holds 4 consecutive even points, so a pixel survives iff 4 consecutive even points are
+//          all brighter (or all darker); survivors join a pixel list;
+//   B      survivors get OpenCV's cornerScore<16>: max over the 16 arcs of 9 of the min signed difference, both
+//          polarities at once as packed 16-bit pairs (VIMNMX3.S16x2), minus 1.  score >= t is exactly the 16-point
+//          segment test; corners store the score in a shared score tile (0 = not a corner) and join the corner list;
+//   C      corners strictly greater than their 8 neighbours OF THE SAME CELL set their bit in a keep bitmap;
 //   pass 2 cells that are still empty repeat A-C at minThFAST (:1281-1285); pixels of other cells are masked out;
-//   D      survivors are ranked by position inside their cell (cv::FAST's row-major order) and written to the cell's slot.
+//   D      one warp per cell walks the cell's bitmap rows (lane = row), a warp prefix sum of the row counts gives every
+//          keypoint its rank in cv::FAST's row-major order, and the keys go straight to the cell's slot.
+// The byte compares never saturate: with s = (v & 127) + t and u = (v & 127) + 128 - t (no carries between bytes for
+// t < 128) the top bits of v + t / v - t are (v ^ s) / (v & u), an overflowing v + t is bit 7 of (v & s) and an
+// underflowing v - t is bit 7 of ~(v | u); both only mask the final flags.
 //
 // Roofline: reads every level pixel once (strip windows overlap by 6 px and hit L2); the kernel is bound by the
 // integer pipe, not by HBM.
+#include <mutex>
 #include <vector>
 
 #include "orbx_internal.h"
@@ -32,9 +41,12 @@ namespace orbx {
 #define ORBX_FS_THREADS 128
 #endif
 #ifndef ORBX_FS_MINBLOCKS
-#define ORBX_FS_MINBLOCKS 8  // measured on B200: 128 x 8 beats 256 x {1, 5, 6} and 128 x 12 (tools/variants.py)
+#define ORBX_FS_MINBLOCKS 7
 #endif
 constexpr int FS_THREADS = ORBX_FS_THREADS;
+#ifndef ORBX_FS_WL
+#define ORBX_FS_WL 1280
+#endif
 #ifndef ORBX_FS_LIST1
 #define ORBX_FS_LIST1 2048
 #endif
@@ -42,14 +54,17 @@ constexpr int FS_THREADS = ORBX_FS_THREADS;
 #define ORBX_FS_LIST2 1024
 #endif
 #ifndef ORBX_FS_MAXCELLS
-#define ORBX_FS_MAXCELLS 4  // measured on B200 (tools/variants.py): 2 / 3 / 4 / 5 / 7 cells -> 2.24 / 2.05 / 1.96 / 2.02 / 2.09 ms per 512 KITTI frames
+#define ORBX_FS_MAXCELLS 4
 #endif
-constexpr int FS_LIST1 = ORBX_FS_LIST1;  // quick-test survivors per row chunk
-constexpr int FS_LIST2 = ORBX_FS_LIST2;  // corners per strip and pass (beyond that NMS scans the score tile)
-constexpr int FS_KP = ORBX_FS_MAXCELLS * CELL_CAP;     // keypoints per strip
-
-__constant__ int c_ringDx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
-__constant__ int c_ringDy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+#ifndef ORBX_FS_FPC
+#define ORBX_FS_FPC 8   // frames one CTA walks (per-CTA set-up is paid once per slice)
+#endif
+#ifndef ORBX_FS_A1_COMPASS
+#define ORBX_FS_A1_COMPASS 0  // 1: A1 also tests the horizontal pair (two of the four compass points must agree)
+#endif
+constexpr int FS_WL = ORBX_FS_WL;        // words with a live pixel after A1, per row chunk
+constexpr int FS_LIST1 = ORBX_FS_LIST1;  // even-point survivors per row chunk
+constexpr int FS_LIST2 = ORBX_FS_LIST2;  // corners per strip and frame (beyond that NMS scans the score tile)
 
 // OpenCV's cornerScore<16> for both polarities at once.  e[k] holds (256 + d_k) in its low and (256 - d_k) in its high
 // 16-bit half, d_k = v - ring_k, so one packed min / max (VIMNMX3.S16x2) serves the "darker ring" and the "brighter
@@ -66,176 +81,277 @@ __device__ __forceinline__ uint32_t best_arc_min_x2(const uint32_t (&e)[16]) {
     return __vimax3_s16x2(__vimax3_s16x2(a, b, c), __vimax3_s16x2(d, f, m9[15]), a);
 }
 
-__device__ __forceinline__ uint32_t lop3_and3(uint32_t a, uint32_t b, uint32_t c) {
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t r;
-    asm("lop3.b32 %0, %1, %2, %3, 0x80;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(LUT));
     return r;
 }
-__device__ __forceinline__ uint32_t lop3_and_or(uint32_t a, uint32_t b, uint32_t c) {  // a & (b | c)
-    uint32_t r;
-    asm("lop3.b32 %0, %1, %2, %3, 0xe0;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
+__device__ __forceinline__ uint32_t lop3_and_or(uint32_t a, uint32_t b, uint32_t c) { return lop3<0xe0>(a, b, c); }  // a & (b | c)
+__device__ __forceinline__ uint32_t lop3_or3(uint32_t a, uint32_t b, uint32_t c) { return lop3<0xfe>(a, b, c); }
+
+// Thresholds of four centre pixels (one word) for the carry-less byte compares.
+struct Thr {
+    uint32_t hx, HN7;  // brighter: bit 7 of hx = top bit of v + t; HN7 = 127 - ((v + t) & 127)
+    uint32_t lx, LN7;  // darker:   bit 7 of lx = top bit of v - t; LN7 = 128 - ((v - t) & 127)
+    uint32_t okB, okD; // bit 7: v + t <= 255 / v - t >= 0 (a saturated threshold can never be passed)
+};
+// t < 128: no saturating arithmetic needed (see the header); t >= 128: the generic saturating form
+__device__ __forceinline__ Thr make_thr(uint32_t c, uint32_t T4, uint32_t K4, bool small) {
+    Thr r;
+    if (small) {
+        const uint32_t c7 = c & 0x7f7f7f7fu;
+        const uint32_t s = c7 + T4;  // (v & 127) + t            <= 254
+        const uint32_t u = c7 + K4;  // (v & 127) + 128 - t      in [1, 255]
+        r.hx = c ^ s;
+        r.HN7 = ~s & 0x7f7f7f7fu;
+        r.lx = c & u;
+        r.LN7 = (~u & 0x7f7f7f7fu) + 0x01010101u;
+        r.okB = ~(c & s);
+        r.okD = c | u;
+    } else {
+        const uint32_t hi = __vaddus4(c, T4), lo = __vsubus4(c, T4);
+        r.hx = hi;
+        r.HN7 = ~hi & 0x7f7f7f7fu;
+        r.lx = lo;
+        r.LN7 = (~lo & 0x7f7f7f7fu) + 0x01010101u;
+        r.okB = 0xFFFFFFFFu;  // ring > 255 and ring < 0 are false by themselves
+        r.okD = 0xFFFFFFFFu;
+    }
     return r;
 }
-__device__ __forceinline__ uint32_t lop3_or3(uint32_t a, uint32_t b, uint32_t c) {
-    uint32_t r;
-    asm("lop3.b32 %0, %1, %2, %3, 0xfe;" : "=r"(r) : "r"(a), "r"(b), "r"(c));
-    return r;
+// bit 7 of every byte: ring > v + t (br) and ring < v - t (dk).  With r7 = ring & 127, bit 7 of r7 + HN7 is
+// (ring & 127) > (hi & 127) and bit 7 of r7 + LN7 is (ring & 127) >= (lo & 127); one LOP3 per compare merges it with the
+// top bits (0xb2: ring > hi; 0x4d: !(ring >= lo)).
+__device__ __forceinline__ void cmp_ring(uint32_t ring, const Thr& th, uint32_t& br, uint32_t& dk) {
+    const uint32_t r7 = ring & 0x7f7f7f7fu;
+    br = lop3<0xb2>(ring, th.hx, r7 + th.HN7);
+    dk = lop3<0x4d>(ring, th.lx, r7 + th.LN7);
 }
 
-struct FastShared {
-    uint8_t* tile;
-    uint8_t* score;
-    uint8_t* act;        // per tile column: 0x80 where the quick test is enabled in this pass
-    uint8_t* cellOfCol;  // per tile column: cell index inside the strip, 255 = not detectable
-    uint16_t* list1;
-    uint16_t* list2;
-    uint32_t* kp;        // cell << 24 | pos << 8 | score
-    int* cnt;            // [0],[1] n1 (ping-pong per row chunk), [2] corners of the pass, [4] nkp, [5] pass-2 needed, [6..] per-cell counts
-    uint64_t* bar;
-};
+// A1 for one lane = one (row segment, word column) pair: SEGH rows of the column, walked top to bottom with the rows in
+// registers (branch-free, so the compiler interleaves the rows); then the warp appends its live words to the word list, one
+// ballot per row.  p points at tile row ya (= row ya - 3 of the detectable area) of the column; rows past the window's end
+// are read but never used (the bytes behind a ring stage belong to this CTA's shared memory too).
+template <int SEGH>
+__device__ __forceinline__ void fast_a1_unit(const uint32_t* p, int TWq, uint32_t vm, int nr, int ya, int w, uint32_t T4, uint32_t K4,
+                                             bool small, uint32_t laneLt, int lane, int* cntLive, uint16_t* wlist) {
+    uint32_t live = 0;  // bit j: row ya + j of this column has a pixel that passes
+    if (vm != 0) {
+        uint32_t rw[SEGH + 6];
+#pragma unroll
+        for (int k = 0; k < SEGH + 6; ++k) {
+            rw[k] = *p;
+            p += TWq;
+        }
+#pragma unroll
+        for (int j = 0; j < SEGH; ++j) {
+            const Thr th = make_thr(rw[j + 3], T4, K4, small);
+            uint32_t b0, d0, b4, d4;
+            cmp_ring(rw[j + 6], th, b0, d0);  // ( 0, +3)
+            cmp_ring(rw[j], th, b4, d4);      // ( 0, -3)
+            const uint32_t al = (((b0 | b4) & th.okB) | ((d0 | d4) & th.okD)) & vm;
+            if (al != 0 && j < nr) live |= 1u << j;
+        }
+    }
+    if (__any_sync(0xffffffffu, live != 0)) {
+        uint32_t bal[SEGH];
+        int total = 0;
+#pragma unroll
+        for (int j = 0; j < SEGH; ++j) {
+            bal[j] = __ballot_sync(0xffffffffu, (live >> j) & 1u);
+            total += __popc(bal[j]);
+        }
+        int o = 0;
+        if (lane == 0) o = atomicAdd(cntLive, total);
+        o = __shfl_sync(0xffffffffu, o, 0);
+#pragma unroll
+        for (int j = 0; j < SEGH; ++j) {
+            if ((live >> j) & 1u) wlist[o + __popc(bal[j] & laneLt)] = (uint16_t)(((ya + j) << 6) | w);
+            o += __popc(bal[j]);
+        }
+    }
+}
 
 __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(const __grid_constant__ FrameGeom g,
                                                              const __grid_constant__ TmaMaps maps,
                                                              const FastStrip* __restrict__ strips,
                                                              int* __restrict__ cellCnt, uint32_t* __restrict__ cellKeys,
-                                                             int* __restrict__ dStatus) {
+                                                             int* __restrict__ dStatus, int batch, int fpc) {
     extern __shared__ __align__(128) uint8_t smem[];
     const int TW = g.fastBoxW, TH = g.fastBoxH, TN = TW * TH, TWq = TW >> 2;
-    FastShared S;
-    S.tile = smem;
-    S.score = smem + TN;
-    S.act = smem + 2 * TN;
-    S.cellOfCol = S.act + TW;
-    S.list1 = reinterpret_cast<uint16_t*>(S.cellOfCol + TW);
-    S.list2 = S.list1 + FS_LIST1;
-    S.kp = reinterpret_cast<uint32_t*>(S.list2 + FS_LIST2);
-    S.cnt = reinterpret_cast<int*>(S.kp + FS_KP);
-    S.bar = reinterpret_cast<uint64_t*>(S.cnt + 16);
+    const int TNa = (TN + 127) & ~127;  // a ring stage (TMA destinations are 128-byte aligned)
+    const int BW = (TW + 31) >> 5;      // keep-bitmap words per tile row
+    uint8_t* const score = smem + 2 * TNa;
+    uint64_t* const bar = reinterpret_cast<uint64_t*>(score + TNa);
+    int* const cntAll = reinterpret_cast<int*>(bar + 2);  // two sets (frame parity) of [0] live words, [1] survivors, [2] corners, [6..] per-cell keypoints
+    uint32_t* const keep = reinterpret_cast<uint32_t*>(cntAll + 32);
+    uint8_t* const act = reinterpret_cast<uint8_t*>(keep + TH * BW);  // per tile column: 0x80 where the tests are enabled in this pass
+    uint8_t* const cellOfCol = act + TW;                               // per tile column: cell index inside the strip, 255 = not detectable
+    uint8_t* const colList = cellOfCol + TW;                           // pass 2: the word columns of the empty cells
+    uint16_t* const wlist = reinterpret_cast<uint16_t*>(colList + 64);  // y << 6 | word
+    uint16_t* const list1 = wlist + FS_WL;                                // tile row << 8 | tile column
+    uint16_t* const list2 = list1 + FS_LIST1;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int f = blockIdx.y;
+    const int fBeg = blockIdx.y * fpc, fEnd = min(fBeg + fpc, batch);
     const FastStrip st = strips[blockIdx.x];
     const LevelGeom& L = g.lv[st.level];
-    const int ci = st.ci, cj0 = st.cj0, nc = st.nc;
+    const int ci = st.ci, cj0 = st.cj0, nc = st.nc, wCell = L.wCell;
     const int cellGlobal0 = L.cellBase + ci * L.nCols + cj0;
-    int* outCnt = cellCnt + (long long)f * g.nCellsTotal + cellGlobal0;
-    uint32_t* outKeys = cellKeys + ((long long)f * g.nCellsTotal + cellGlobal0) * CELL_CAP;
 
     // window of the strip (src/ORBextractor.cc:1258-1275): rows of cell row ci, columns of cells cj0 .. cj0 + nc - 1
-    const int iniY = L.minBY + ci * L.hCell, iniX = L.minBX + cj0 * L.wCell;
+    const int iniY = L.minBY + ci * L.hCell, iniX = L.minBX + cj0 * wCell;
     const int maxY = min(iniY + L.hCell + 6, L.maxBY);
     const int dH = (iniY >= L.maxBY - 3) ? 0 : maxY - iniY - 6;  // detectable rows
     // detectable columns: cell j is valid unless iniX_j >= maxBX - 6 or its window is narrower than 7 px
     int dW = 0;
     for (int j = 0; j < nc; ++j) {
-        const int ix = iniX + j * L.wCell;
-        const int mx = min(ix + L.wCell + 6, L.maxBX);
-        if (ix < L.maxBX - 6 && mx - ix >= 7) dW = j * L.wCell + (mx - ix - 6);
+        const int ix = iniX + j * wCell;
+        const int mx = min(ix + wCell + 6, L.maxBX);
+        if (ix < L.maxBX - 6 && mx - ix >= 7) dW = j * wCell + (mx - ix - 6);
     }
     if (dH < 1 || dW < 1) {
-        if (tid < nc) outCnt[tid] = 0;
+        if (tid < nc)
+            for (int f = fBeg; f < fEnd; ++f) cellCnt[(long long)f * g.nCellsTotal + cellGlobal0 + tid] = 0;
         return;
     }
     if (tid == 0) {
-        mbar_init(S.bar, 1);
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
         fence_mbar_init();
+        tma_prefetch_desc(&maps.m[st.level]);
     }
-    __syncthreads();
-    if (tid == 0) {
-        mbar_expect_tx(S.bar, (uint32_t)TN);
-        tma_load_3d(S.tile, &maps.m[st.level], (XOFF + iniX) & ~15, EDGE + iniY, f + g.f0, S.bar);  // box origin 16-byte aligned
-    }
-    const int xo = (XOFF + iniX) & 15;  // window column 0 inside the box
-    const int X0 = xo + 3;              // first detectable tile column
+    const int boxX = (XOFF + iniX) & ~15, boxY = EDGE + iniY;  // box origin 16-byte aligned
+    const int xo = (XOFF + iniX) & 15;                         // window column 0 inside the box
+    const int X0 = xo + 3;                                     // first detectable tile column
     const int wq0 = X0 >> 2, nW = ((X0 + dW + 3) >> 2) - wq0;
-    // while the tile is in flight: clear the score tile, set up the column tables and counters
-    for (int i = tid; i < TN / 16; i += FS_THREADS) reinterpret_cast<uint4*>(S.score)[i] = make_uint4(0u, 0u, 0u, 0u);  // TW % 16 == 0
+    // once per CTA: clear the score tile and the bitmap, set up the column tables and counters
+    for (int i = tid; i < TNa / 16; i += FS_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = tid; i < TH * BW; i += FS_THREADS) keep[i] = 0u;
     for (int x = tid; x < TW; x += FS_THREADS) {
         const int dx = x - X0;
         const bool det = dx >= 0 && dx < dW;
         int cell = 0;  // dx / wCell for the few cells of a strip, without a division
-        for (int j = 1; j < nc; ++j) cell += dx >= j * L.wCell ? 1 : 0;
-        S.cellOfCol[x] = det ? (uint8_t)cell : (uint8_t)255;
-        S.act[x] = det ? 0x80 : 0;
+        for (int j = 1; j < nc; ++j) cell += dx >= j * wCell ? 1 : 0;
+        cellOfCol[x] = det ? (uint8_t)cell : (uint8_t)255;
+        act[x] = det ? 0x80 : 0;
     }
-    if (tid < 16) S.cnt[tid] = 0;
+    if (tid < 32) cntAll[tid] = 0;
     __syncthreads();
-    mbar_wait(S.bar, 0);
+    if (tid == 0) {
+        mbar_expect_tx(&bar[0], (uint32_t)TN);
+        tma_load_3d(smem, &maps.m[st.level], boxX, boxY, fBeg + g.f0, &bar[0]);
+    }
 
-    const uint32_t* tile32 = reinterpret_cast<const uint32_t*>(S.tile);
-    const uint32_t* act32 = reinterpret_cast<const uint32_t*>(S.act);
-    const int rowsPerChunk = max(1, FS_LIST1 / (nW * 4));
-    int rpc = dH;  // optimistic: the whole strip is one chunk (survivors are a small fraction of the pixels)
-    const int stepY = FS_THREADS / nW, stepW = FS_THREADS - stepY * nW;
-    int off[16];
-#pragma unroll
-    for (int k = 0; k < 16; ++k) off[k] = c_ringDy[k] * TW + c_ringDx[k];
+    const uint32_t* act32 = reinterpret_cast<const uint32_t*>(act);
+    // row chunks: the word list always holds a chunk; the survivor list holds it in the common case (a denser chunk is
+    // redone with rpcSafe rows, whose pixels all fit)
+    const int rpcOpt = max(1, min(dH, FS_WL / nW)), rpcSafe = max(1, FS_LIST1 / (nW * 4));
+    const int nWG = (nW + 31) >> 5;  // A1: a warp owns 32 word columns x 8 rows at a time (nW <= 64)
+    const uint32_t laneLt = (1u << lane) - 1u;
+    // emptiness test of the strip's cells after pass 1 (src/ORBextractor.cc:1281): which cells exist at all
+    uint32_t validCells = 0;
+    for (int j = 0; j < nc; ++j) {
+        const int ix = iniX + j * wCell;
+        if (ix < L.maxBX - 6 && min(ix + wCell + 6, L.maxBX) - ix >= 7) validCells |= 1u << j;
+    }
 
-    // C for one corner: keep it iff its score beats the 8 neighbours that lie in the same cell
-    auto nms_one = [&](int pos, int s) {
-        const int y = pos / TW, x = pos - y * TW;
-        const int cell = S.cellOfCol[x];
-        const bool lft = S.cellOfCol[x - 1] == cell, rgt = S.cellOfCol[x + 1] == cell;
-        const uint8_t* c = S.score + pos;
-        bool keep = s > c[-TW] && s > c[TW];
-        if (lft) keep = keep && s > c[-1] && s > c[-TW - 1] && s > c[TW - 1];
-        if (rgt) keep = keep && s > c[1] && s > c[-TW + 1] && s > c[TW + 1];
-        if (keep) {
-            const int o = atomicAdd(&S.cnt[4], 1);
-            if (o < FS_KP) S.kp[o] = ((uint32_t)cell << 24) | ((uint32_t)pos << 8) | (uint32_t)s;
-            atomicAdd(&S.cnt[6 + cell], 1);
+    for (int f = fBeg, it = 0; f < fEnd; ++f, ++it) {
+        const int stg = it & 1;
+        int* const cnt = cntAll + stg * 16;  // this frame's counters; the other set is cleared below for frame f + 1
+        if (tid == 0 && f + 1 < fEnd) {  // the other stage was released by the barrier that ended frame f - 1
+            mbar_expect_tx(&bar[stg ^ 1], (uint32_t)TN);
+            tma_load_3d(smem + (stg ^ 1) * TNa, &maps.m[st.level], boxX, boxY, f + 1 + g.f0, &bar[stg ^ 1]);
         }
-    };
+        if (tid < 16) cntAll[(stg ^ 1) * 16 + tid] = 0;  // last used by frame f - 1, next used after this frame's last barrier
+        const uint8_t* tile = smem + stg * TNa;
+        const uint32_t* tile32 = reinterpret_cast<const uint32_t*>(tile);
+        mbar_wait(&bar[stg], (uint32_t)(it >> 1) & 1u);
 
-    int par = 0;  // which n1 counter the current chunk appends to
-    for (int pass = 0; pass < 2; ++pass) {
-        const int t = min(max(pass == 0 ? g.iniTh : g.minTh, 0), 255);
-        const uint32_t T4 = (uint32_t)t * 0x01010101u;
-        for (int y0 = 0; y0 < dH; y0 += rpc) {
-            const int y1 = min(y0 + rpc, dH);
-            // ---- A: packed quick test on the 8 even ring points: a run of 9 holds 4 consecutive even points ----
-            // the (row, word) pairs of the chunk are walked as one flat index, so every lane has work whatever the strip
-            // width; the row / word of a thread advance incrementally (no division inside the loop)
-            const int total = (y1 - y0) * nW;
-            int yy = tid / nW, w = tid - yy * nW;
-            for (int idx = tid; idx < total; idx += FS_THREADS, w += stepW, yy += stepY) {
-                if (w >= nW) { w -= nW; ++yy; }
+        // C for one corner: keep it iff its score beats the 8 neighbours that lie in the same cell
+        auto nms_one = [&](int e, int s) {
+            const int y = e >> 8, x = e & 255;
+            const int cell = cellOfCol[x];
+            const bool lft = cellOfCol[x - 1] == cell, rgt = cellOfCol[x + 1] == cell;
+            const uint8_t* c = score + y * TW + x;
+            bool kp = s > c[-TW] && s > c[TW];
+            if (lft) kp = kp && s > c[-1] && s > c[-TW - 1] && s > c[TW - 1];
+            if (rgt) kp = kp && s > c[1] && s > c[-TW + 1] && s > c[TW + 1];
+            if (kp) {
+                atomicOr(&keep[y * BW + (x >> 5)], 1u << (x & 31));
+                atomicAdd(&cnt[6 + cell], 1);
+            }
+        };
+
+        int n2done = 0;     // corners of list2 that C has already seen (pass 1)
+        int nCols = nW;     // word columns A1 walks in this pass
+        bool pass2 = false;
+        for (int pass = 0; pass < 2; ++pass) {
+            const int t = min(max(pass == 0 ? g.iniTh : g.minTh, 0), 255);
+            const bool small = t < 128;
+            const uint32_t T4 = (uint32_t)t * 0x01010101u, K4 = 0x80808080u - T4;
+            int rpc = rpcOpt;
+            for (int y0 = 0; y0 < dH;) {
+                const int y1 = min(y0 + rpc, dH);
+                // ---- A1: opposite-pair reject on (0, +-3).  A lane walks down one word column 8 rows at a time with the
+                //      rows in registers; live words -> word list, one ballot per row ----
                 {
-                    const int y = y0 + yy;
-                    const uint32_t* rowc = tile32 + (y + 3) * TWq + wq0;
+                    // a lane takes one (row segment, word column) pair of a flat list — all columns in pass 1, the empty cells'
+                    // columns in pass 2.  The segment height is the smallest of 8..12 rows with which the pairs fill the CTA's
+                    // lanes once (32 columns x 4 segments of 8 rows, 33 x 3 of 11 ...); otherwise 8 rows and several rounds
+                    const int rows = y1 - y0;
+                    int segH = 8;
+                    if (small)
+                        for (int h = 8; h <= 12; ++h)
+                            if (((rows + h - 1) / h) * nCols <= FS_THREADS) { segH = h; break; }
+                    const int nSeg = (rows + segH - 1) / segH, nUnits = nSeg * nCols;
+                    for (int u0 = warp * 32; u0 < nUnits; u0 += FS_THREADS) {
+                        const int idx = u0 + lane, seg = idx / nCols, ci = idx - seg * nCols;
+                        const bool unitOk = idx < nUnits;
+                        const int w = !unitOk ? 0 : pass == 0 ? ci : colList[ci];
+                        const int ya = y0 + seg * segH, nr = min(segH, y1 - ya);
+                        const uint32_t vm = unitOk ? act32[wq0 + w] : 0u;
+                        const uint32_t* p = tile32 + ya * TWq + wq0 + w;
+                        switch (segH) {
+                            case 8: fast_a1_unit<8>(p, TWq, vm, nr, ya, w, T4, K4, small, laneLt, lane, &cnt[0], wlist); break;
+                            case 9: fast_a1_unit<9>(p, TWq, vm, nr, ya, w, T4, K4, true, laneLt, lane, &cnt[0], wlist); break;
+                            case 10: fast_a1_unit<10>(p, TWq, vm, nr, ya, w, T4, K4, true, laneLt, lane, &cnt[0], wlist); break;
+                            case 11: fast_a1_unit<11>(p, TWq, vm, nr, ya, w, T4, K4, true, laneLt, lane, &cnt[0], wlist); break;
+                            default: fast_a1_unit<12>(p, TWq, vm, nr, ya, w, T4, K4, true, laneLt, lane, &cnt[0], wlist); break;
+                        }
+                    }
+                }
+                __syncthreads();
+                // ---- A2: the 8 even ring points of the live words: a run of 9 holds 4 consecutive even points ----
+                const int n0 = cnt[0];
+                for (int i = tid; i < n0; i += FS_THREADS) {
+                    const int e = wlist[i];
+                    const int y = e >> 6, w = e & 63;
+                    const uint32_t* rowc = tile32 + (y + 3) * TWq + wq0 + w;
                     const uint32_t vm = act32[wq0 + w];
-                    if (vm == 0) continue;
-                    const uint32_t c = rowc[w];
-                    const uint32_t hi = __vaddus4(c, T4), lo = __vsubus4(c, T4);  // saturating v + t, v - t
-                    // per-byte unsigned compares without cross-byte carries: with r7 = r & 0x7f.., bit 7 of (r7 + (~hi & 0x7f..))
-                    // is (r & 127) > (hi & 127) and bit 7 of (r7 + (~lo & 0x7f..) + 0x01..) is (r & 127) >= (lo & 127); one
-                    // LOP3 per compare merges it with the top bits (0xb2: r > hi; 0x4d: !(r >= lo), i.e. v - t > r)
-                    const uint32_t HN7 = ~hi & 0x7f7f7f7fu, LN7 = (~lo & 0x7f7f7f7fu) + 0x01010101u;
+                    const uint32_t c = rowc[0];
+                    const Thr th = make_thr(c, T4, K4, small);
                     uint32_t ring[8];
-                    ring[0] = rowc[w + 3 * TWq];                                                       // ( 0, +3)
-                    ring[4] = rowc[w - 3 * TWq];                                                       // ( 0, -3)
+                    ring[0] = rowc[3 * TWq];                                                        // ( 0, +3)
+                    ring[4] = rowc[-3 * TWq];                                                       // ( 0, -3)
                     {
                         const uint32_t* r = rowc + 2 * TWq;
-                        const uint32_t m = r[w];
-                        ring[1] = __funnelshift_r(m, r[w + 1], 16);                                    // (+2, +2)
-                        ring[7] = __funnelshift_r(r[w - 1], m, 16);                                    // (-2, +2)
+                        const uint32_t m = r[0];
+                        ring[1] = __funnelshift_r(m, r[1], 16);                                     // (+2, +2)
+                        ring[7] = __funnelshift_r(r[-1], m, 16);                                    // (-2, +2)
                     }
-                    ring[2] = __funnelshift_r(c, rowc[w + 1], 24);                                     // (+3,  0)
-                    ring[6] = __funnelshift_r(rowc[w - 1], c, 8);                                      // (-3,  0)
+                    ring[2] = __funnelshift_r(c, rowc[1], 24);                                      // (+3,  0)
+                    ring[6] = __funnelshift_r(rowc[-1], c, 8);                                      // (-3,  0)
                     {
                         const uint32_t* r = rowc - 2 * TWq;
-                        const uint32_t m = r[w];
-                        ring[3] = __funnelshift_r(m, r[w + 1], 16);                                    // (+2, -2)
-                        ring[5] = __funnelshift_r(r[w - 1], m, 16);                                    // (-2, -2)
+                        const uint32_t m = r[0];
+                        ring[3] = __funnelshift_r(m, r[1], 16);                                     // (+2, -2)
+                        ring[5] = __funnelshift_r(r[-1], m, 16);                                    // (-2, -2)
                     }
                     uint32_t br[8], dk[8];
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const uint32_t r7 = ring[k] & 0x7f7f7f7fu;
-                        const uint32_t sb = r7 + HN7, sd = r7 + LN7;
-                        asm("lop3.b32 %0, %1, %2, %3, 0xb2;" : "=r"(br[k]) : "r"(ring[k]), "r"(hi), "r"(sb));
-                        asm("lop3.b32 %0, %1, %2, %3, 0x4d;" : "=r"(dk[k]) : "r"(ring[k]), "r"(lo), "r"(sd));
-                    }
+                    for (int k = 0; k < 8; ++k) cmp_ring(ring[k], th, br[k], dk[k]);
                     // a pixel survives iff 4 consecutive even ring points agree: with pair flags p[k] = f[k] & f[k+1] that
                     // is OR_k (p[k] & p[k+2]), and p[k+2] & (p[k] | p[k+4]) covers two of the eight products per LOP3
                     uint32_t pb[8], pd[8];
@@ -244,129 +360,202 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
                         pb[k] = br[k] & br[(k + 1) & 7];
                         pd[k] = dk[k] & dk[(k + 1) & 7];
                     }
-                    const uint32_t fl = (lop3_or3(lop3_and_or(pb[2], pb[0], pb[4]), lop3_and_or(pb[6], pb[4], pb[0]),
-                                                  lop3_and_or(pb[3], pb[1], pb[5])) |
-                                         lop3_or3(lop3_and_or(pb[7], pb[5], pb[1]), lop3_and_or(pd[2], pd[0], pd[4]),
-                                                  lop3_and_or(pd[6], pd[4], pd[0])) |
-                                         lop3_and_or(pd[3], pd[1], pd[5]) | lop3_and_or(pd[7], pd[5], pd[1])) & vm;
+                    const uint32_t fb = lop3_or3(lop3_and_or(pb[2], pb[0], pb[4]), lop3_and_or(pb[6], pb[4], pb[0]),
+                                                 lop3_and_or(pb[3], pb[1], pb[5])) | lop3_and_or(pb[7], pb[5], pb[1]);
+                    const uint32_t fd = lop3_or3(lop3_and_or(pd[2], pd[0], pd[4]), lop3_and_or(pd[6], pd[4], pd[0]),
+                                                 lop3_and_or(pd[3], pd[1], pd[5])) | lop3_and_or(pd[7], pd[5], pd[1]);
+                    const uint32_t fl = ((fb & th.okB) | (fd & th.okD)) & vm;
                     if (fl) {
                         const int np = __popc(fl);
-                        int o = atomicAdd(&S.cnt[par], np);
-                        if (o + np <= FS_LIST1) {  // (an overflowing optimistic pass is repeated in row chunks, see below)
-                            const int pos0 = (y + 3) * TW + ((wq0 + w) << 2);
+                        int o = atomicAdd(&cnt[1], np);
+                        if (o + np <= FS_LIST1) {  // (an overflowing chunk is redone with fewer rows, see below)
+                            const int e0 = ((y + 3) << 8) | ((wq0 + w) << 2);
 #pragma unroll
                             for (int j = 0; j < 4; ++j)
-                                if (fl & (0x80u << (8 * j))) S.list1[o++] = (uint16_t)(pos0 + j);
+                                if (fl & (0x80u << (8 * j))) list1[o++] = (uint16_t)(e0 + j);
+                        }
+                    }
+                }
+                __syncthreads();
+                const int n1 = cnt[1];
+                if (tid == 0) cnt[0] = 0;  // every thread has read n0
+                if (n1 > FS_LIST1) {       // more survivors than the list holds: redo this chunk with rows that always fit
+                    __syncthreads();
+                    if (tid == 0) cnt[1] = 0;
+                    rpc = rpcSafe;
+                    __syncthreads();
+                    continue;
+                }
+                // ---- B: full 16-point segment test; corners get cornerScore<16> (both polarities: the one without a run
+                //         never wins the max) and join the corner list ----
+                for (int i = tid; i < n1; i += FS_THREADS) {
+                    const int e = list1[i];
+                    const uint8_t* p = tile + (e >> 8) * TW + (e & 255);
+                    const uint32_t v = p[0];
+                    const uint32_t cv = (v + 256u) + ((256u - v) << 16);  // (256 + v, 256 - v)
+                    const uint8_t *pu3 = p + 3 * TW, *pu2 = p + 2 * TW, *pu1 = p + TW, *pd1 = p - TW, *pd2 = p - 2 * TW, *pd3 = p - 3 * TW;
+                    uint32_t ev[16];  // (256 + d, 256 - d), d = v - ring
+                    ev[0] = (uint32_t)pu3[0] * 0xFFFFu + cv;
+                    ev[1] = (uint32_t)pu3[1] * 0xFFFFu + cv;
+                    ev[2] = (uint32_t)pu2[2] * 0xFFFFu + cv;
+                    ev[3] = (uint32_t)pu1[3] * 0xFFFFu + cv;
+                    ev[4] = (uint32_t)p[3] * 0xFFFFu + cv;
+                    ev[5] = (uint32_t)pd1[3] * 0xFFFFu + cv;
+                    ev[6] = (uint32_t)pd2[2] * 0xFFFFu + cv;
+                    ev[7] = (uint32_t)pd3[1] * 0xFFFFu + cv;
+                    ev[8] = (uint32_t)pd3[0] * 0xFFFFu + cv;
+                    ev[9] = (uint32_t)pd3[-1] * 0xFFFFu + cv;
+                    ev[10] = (uint32_t)pd2[-2] * 0xFFFFu + cv;
+                    ev[11] = (uint32_t)pd1[-3] * 0xFFFFu + cv;
+                    ev[12] = (uint32_t)p[-3] * 0xFFFFu + cv;
+                    ev[13] = (uint32_t)pu1[-3] * 0xFFFFu + cv;
+                    ev[14] = (uint32_t)pu2[-2] * 0xFFFFu + cv;
+                    ev[15] = (uint32_t)pu3[-1] * 0xFFFFu + cv;
+                    const uint32_t best = best_arc_min_x2(ev);
+                    const int s = (int)max(best & 0xFFFFu, best >> 16) - 257;
+                    if (s >= t) {  // some arc of 9 has all |differences| > t with one sign: a corner, and s is its score
+                        score[(e >> 8) * TW + (e & 255)] = (uint8_t)s;
+                        const int o = atomicAdd(&cnt[2], 1);
+                        if (o < FS_LIST2) list2[o] = (uint16_t)e;
+                    }
+                }
+                __syncthreads();
+                if (tid == 0) cnt[1] = 0;  // ordered before the next chunk's A2 by the barrier after its A1
+                y0 = y1;
+            }
+            // ---- C: 3x3 non-max suppression among pixels of the same cell ----
+            const int n2 = cnt[2];
+            if (n2 <= FS_LIST2) {
+                for (int i = n2done + tid; i < n2; i += FS_THREADS) {
+                    const int e = list2[i];
+                    nms_one(e, score[(e >> 8) * TW + (e & 255)]);
+                }
+                n2done = n2;
+            } else {  // more corners than the list holds: scan the score tile of the active columns instead
+                for (int y = warp; y < dH; y += FS_THREADS / 32) {
+                    const uint32_t* srow = reinterpret_cast<const uint32_t*>(score) + (y + 3) * TWq + wq0;
+                    for (int w = lane; w < nW; w += 32) {
+                        const uint32_t sc = srow[w] & ((act32[wq0 + w] >> 7) * 0xFFu);
+                        if (sc == 0) continue;
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const int s = (sc >> (8 * j)) & 0xFF;
+                            if (s != 0) nms_one(((y + 3) << 8) | (((wq0 + w) << 2) + j), s);
                         }
                     }
                 }
             }
             __syncthreads();
-            const int n1 = S.cnt[par];
-            if (tid == 0) S.cnt[par ^ 1] = 0;  // nobody touches the other counter before the next barrier
-            par ^= 1;
-            if (n1 > FS_LIST1) {  // more survivors than the list holds (only possible while rpc == dH): redo the pass in
-                                  // chunks of rows whose pixels all fit.  Nothing but the survivor count was written.
-                rpc = rowsPerChunk;
-                y0 = -rpc;
-                __syncthreads();
-                continue;
-            }
-            // ---- B: full 16-point segment test; corners get cornerScore<16> (both polarities: the one without a run
-            //         never wins the max) and join the corner list of this pass ----
-            for (int i = tid; i < n1; i += FS_THREADS) {
-                const int pos = S.list1[i];
-                const uint32_t v = S.tile[pos];
-                const uint32_t cv = (v + 256u) + ((256u - v) << 16);  // (256 + v, 256 - v)
-                uint32_t e[16];
-#pragma unroll
-                for (int k = 0; k < 16; ++k) e[k] = (uint32_t)S.tile[pos + off[k]] * 0xFFFFu + cv;  // (256 + d, 256 - d), d = v - ring
-                const uint32_t best = best_arc_min_x2(e);
-                const int s = (int)max(best & 0xFFFFu, best >> 16) - 257;
-                if (s >= t) {  // some arc of 9 has all |differences| > t with one sign: a corner, and s is its score
-                    S.score[pos] = (uint8_t)s;
-                    const int o = atomicAdd(&S.cnt[2], 1);
-                    if (o < FS_LIST2) S.list2[o] = (uint16_t)pos;
-                }
+            if (pass == 1) break;
+            // ---- cells without a keypoint go again at minThFAST ----
+            uint32_t empty = 0;
+            for (int j = 0; j < nc; ++j)
+                if (cnt[6 + j] == 0) empty |= 1u << j;
+            empty &= validCells;
+            if (empty == 0) break;
+            pass2 = true;
+            for (int x = tid; x < TW; x += FS_THREADS) {
+                const int cell = cellOfCol[x];
+                act[x] = (cell != 255 && ((empty >> cell) & 1u)) ? 0x80 : 0;
             }
             __syncthreads();
-        }
-        // ---- C: 3x3 non-max suppression among pixels of the same cell ----
-        const int n2 = S.cnt[2];
-        if (n2 <= FS_LIST2) {
-            for (int i = tid; i < n2; i += FS_THREADS) {
-                const int pos = S.list2[i];
-                nms_one(pos, S.score[pos]);
+            // the word columns pass 2 walks (every warp writes the same list, so no further barrier is needed)
+            nCols = 0;
+            for (int q = 0; q < nWG; ++q) {
+                const int w = (q << 5) + lane;
+                const bool a = w < nW && act32[wq0 + w] != 0;
+                const uint32_t bal = __ballot_sync(0xffffffffu, a);
+                if (a) colList[nCols + __popc(bal & laneLt)] = (uint8_t)w;
+                nCols += __popc(bal);
             }
-        } else {  // more corners than the list holds: scan the score tile of the active columns instead
-            for (int y = warp; y < dH; y += FS_THREADS / 32) {
-                const uint32_t* srow = reinterpret_cast<const uint32_t*>(S.score) + (y + 3) * TWq + wq0;
-                for (int w = lane; w < nW; w += 32) {
-                    const uint32_t sc = srow[w] & ((act32[wq0 + w] >> 7) * 0xFFu);
-                    if (sc == 0) continue;
+            __syncwarp();
+        }
+        // ---- D: cv::FAST's row-major order inside every cell, straight from the bitmap: one warp per cell, lane = row of
+        //      the cell; a warp prefix sum of the row counts ranks every keypoint and the keys go to the cell's slot ----
+        const int n2all = cnt[2];
+        {
+            int* outCnt = cellCnt + (long long)f * g.nCellsTotal + cellGlobal0;
+            uint32_t* outKeys = cellKeys + ((long long)f * g.nCellsTotal + cellGlobal0) * CELL_CAP;
+            for (int cj = warp; cj < nc; cj += FS_THREADS / 32) {
+                const int cx0 = X0 + min(cj * wCell, dW), cx1 = X0 + min(cj * wCell + wCell, dW);  // tile columns of the cell
+                int run = 0;
+                if (cx1 > cx0 && cnt[6 + cj] > 0) {
+                    // the cell's columns as one 64-bit row mask (a cell is < 64 px wide): bit i = column cx0 + i
+                    const int k0 = cx0 >> 5, cw = cx1 - cx0;
+                    const uint32_t sh = (uint32_t)(cx0 & 31);
+                    const uint32_t wLo = cw >= 32 ? 0xFFFFFFFFu : (1u << cw) - 1u, wHi = cw > 32 ? (1u << (cw - 32)) - 1u : 0u;
+                    for (int r0 = 0; r0 < dH; r0 += 32) {
+                        const int yT = r0 + lane + 3;
+                        uint32_t lo = 0, hi = 0;
+                        if (r0 + lane < dH) {
+                            const uint32_t* kr = keep + yT * BW + k0;
+                            const uint32_t a0 = kr[0], a1 = k0 + 1 < BW ? kr[1] : 0u, a2 = k0 + 2 < BW ? kr[2] : 0u;
+                            lo = __funnelshift_r(a0, a1, sh) & wLo;
+                            hi = __funnelshift_r(a1, a2, sh) & wHi;
+                        }
+                        const int c = __popc(lo) + __popc(hi);
+                        int incl = c;
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const int s = (sc >> (8 * j)) & 0xFF;
-                        if (s != 0) nms_one((y + 3) * TW + ((wq0 + w) << 2) + j, s);
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                            if (lane >= o) incl += v;
+                        }
+                        int rank = run + incl - c;
+                        run += __shfl_sync(0xffffffffu, incl, 31);
+                        const uint8_t* srow = score + yT * TW + cx0;
+                        const uint32_t keyRow = pack_key(cx0 - xo + cj0 * wCell, yT + ci * L.hCell, 0);
+                        while (lo) {
+                            const int i = __ffs(lo) - 1;
+                            lo &= lo - 1;
+                            if (rank < CELL_CAP) outKeys[cj * CELL_CAP + rank] = keyRow + (uint32_t)i + ((uint32_t)srow[i] << 24);
+                            ++rank;
+                        }
+                        while (hi) {
+                            const int i = __ffs(hi) + 31;
+                            hi &= hi - 1;
+                            if (rank < CELL_CAP) outKeys[cj * CELL_CAP + rank] = keyRow + (uint32_t)i + ((uint32_t)srow[i] << 24);
+                            ++rank;
+                        }
                     }
+                }
+                if (lane == 0) {
+                    if (run > CELL_CAP) {
+                        atomicExch(dStatus, ORBX_E_OVERFLOW);
+                        run = CELL_CAP;
+                    }
+                    outCnt[cj] = run;
                 }
             }
         }
-        __syncthreads();
-        if (pass == 1) break;
-        // ---- cells without a keypoint go again at minThFAST ----
-        if (tid < nc) {
-            const int ix = iniX + tid * L.wCell;
-            const bool valid = ix < L.maxBX - 6 && min(ix + L.wCell + 6, L.maxBX) - ix >= 7;
-            if (valid && S.cnt[6 + tid] == 0) S.cnt[5] = 1;
+        // ---- leave the score tile, the bitmap and the column mask clean for the next frame (D reads the scores of the
+        //      kept corners, so the clean-up waits for it) ----
+        if (f + 1 < fEnd) {
+            if (pass2)
+                for (int x = tid; x < TW; x += FS_THREADS) act[x] = cellOfCol[x] != 255 ? 0x80 : 0;
+            __syncthreads();
+            if (n2all <= FS_LIST2) {
+                for (int i = tid; i < n2all; i += FS_THREADS) {
+                    const int e = list2[i];
+                    score[(e >> 8) * TW + (e & 255)] = 0;
+                }
+            } else {
+                for (int i = tid; i < TNa / 16; i += FS_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
+            }
+            for (int i = tid; i < TH * BW; i += FS_THREADS) keep[i] = 0u;
+            __syncthreads();
         }
-        __syncthreads();
-        if (S.cnt[5] == 0) break;
-        for (int x = tid; x < TW; x += FS_THREADS) {
-            const int cell = S.cellOfCol[x];
-            S.act[x] = (cell != 255 && S.cnt[6 + cell] == 0) ? 0x80 : 0;
-        }
-        if (tid == 0) S.cnt[2] = 0;
-        __syncthreads();
-    }
-    // ---- D: row-major order inside every cell (positions are unique; rank = number of smaller keys of the cell) ----
-    int nkp = S.cnt[4];
-    if (nkp > FS_KP) {
-        if (tid == 0) atomicExch(dStatus, ORBX_E_OVERFLOW);
-        nkp = FS_KP;
-    }
-    for (int i = tid; i < nkp; i += FS_THREADS) {
-        const uint32_t e = S.kp[i];
-        const uint32_t cell = e >> 24;
-        int rank = 0;
-        for (int j = 0; j < nkp; ++j) {
-            const uint32_t o = S.kp[j];
-            rank += ((o >> 24) == cell && o < e) ? 1 : 0;
-        }
-        if (rank < CELL_CAP) {
-            const int pos = (int)((e >> 8) & 0xFFFFu);
-            const int y = pos / TW, x = pos - y * TW;
-            outKeys[(long long)cell * CELL_CAP + rank] = pack_key(x - xo + cj0 * L.wCell, y + ci * L.hCell, (int)(e & 0xFFu));
-        }
-    }
-    if (tid < nc) {
-        int c = S.cnt[6 + tid];
-        if (c > CELL_CAP) {
-            atomicExch(dStatus, ORBX_E_OVERFLOW);
-            c = CELL_CAP;
-        }
-        outCnt[tid] = c;
     }
 }
 
 size_t fast_smem_bytes(const FrameGeom& g) {
-    return (size_t)2 * g.fastBoxW * g.fastBoxH + 2 * g.fastBoxW + FS_LIST1 * 2 + FS_LIST2 * 2 + FS_KP * 4 +
-           16 * 4 + 16;
+    const size_t TN = (size_t)g.fastBoxW * g.fastBoxH, TNa = (TN + 127) & ~(size_t)127;
+    const size_t BW = (g.fastBoxW + 31) >> 5;
+    return 3 * TNa + 2 * 8 + 32 * 4 + (size_t)g.fastBoxH * BW * 4 + 2 * g.fastBoxW + 64 + (FS_WL + FS_LIST1 + FS_LIST2) * 2;
 }
 
 // Cells per strip of a level: as many as ORBX_FS_MAXCELLS allows while the TMA box (strip window + 15 bytes of origin
-// slack) stays within 256 columns.  Phase A walks (row, word) pairs as a flat index, so lane utilisation does not depend
-// on the strip width; the width trades shared memory per CTA (occupancy) against halo re-reads and per-CTA set-up.
+// slack) stays within 256 columns.  A1 walks (row, word) pairs as a flat index, so lane utilisation does not depend
+// on the strip width; the width trades shared memory per CTA (occupancy) against halo re-reads.
 int fast_cells_per_strip(int wCell, int nCols) {
     int best = 1;
     for (int c = 1; c <= ORBX_FS_MAXCELLS && c <= FAST_MAX_STRIP_CELLS && c <= nCols; ++c) {
@@ -376,17 +565,31 @@ int fast_cells_per_strip(int wCell, int nCols) {
     return best;
 }
 
+// cudaFuncAttributeMaxDynamicSharedMemorySize is per device: remember what each device has been given
+int ensure_dynamic_smem(const void* func, size_t bytes, size_t* perDevice /* [ORBX_MAX_DEVICES] */) {
+    static std::mutex mu;
+    if (bytes <= 48 * 1024) return ORBX_OK;
+    int dev = 0;
+    ORBX_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    if (dev >= 0 && dev < ORBX_MAX_DEVICES && perDevice[dev] >= bytes) return ORBX_OK;
+    ORBX_CUDA(cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    if (dev >= 0 && dev < ORBX_MAX_DEVICES) perDevice[dev] = bytes;
+    return ORBX_OK;
+}
+
 int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrips, int batch, int* cellCnt,
                 uint32_t* cellKeys, int* dStatus, cudaStream_t s) {
     if (g.nStrips == 0) return ORBX_OK;
     const size_t smem = fast_smem_bytes(g);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        ORBX_CUDA(cudaFuncSetAttribute(k_fast_strips, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
-    dim3 grid(g.nStrips, batch);
-    k_fast_strips<<<grid, FS_THREADS, smem, s>>>(g, maps, dStrips, cellCnt, cellKeys, dStatus);
+    static size_t configured[ORBX_MAX_DEVICES] = {};
+    int rc = ensure_dynamic_smem((const void*)k_fast_strips, smem, configured);
+    if (rc) return rc;
+    // frames per CTA: ORBX_FS_FPC while the grid keeps >= 4 waves of 148 SMs x 7 CTAs
+    int fpc = ORBX_FS_FPC;
+    while (fpc > 1 && (long long)g.nStrips * ((batch + fpc - 1) / fpc) < 4LL * 148 * ORBX_FS_MINBLOCKS) fpc >>= 1;
+    dim3 grid(g.nStrips, (batch + fpc - 1) / fpc);
+    k_fast_strips<<<grid, FS_THREADS, smem, s>>>(g, maps, dStrips, cellCnt, cellKeys, dStatus, batch, fpc);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

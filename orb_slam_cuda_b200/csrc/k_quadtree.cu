@@ -430,11 +430,8 @@ int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uin
         set_error("quadtree: %zu bytes of shared memory needed (nfeatures per level %d, cells %d)", smem, maxQuota, maxCells);
         return ORBX_E_INVALID;
     }
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        ORBX_CUDA(cudaFuncSetAttribute(k_quadtree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static size_t configured[ORBX_MAX_DEVICES] = {};
+    if (int rcAttr = ensure_dynamic_smem((const void*)k_quadtree, smem, configured)) return rcAttr;
     dim3 grid(g.nlevels, batch);
     k_quadtree<<<grid, QT_THREADS, smem, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
     count_launch();
@@ -458,11 +455,8 @@ int launch_quadtree_single(const uint32_t* dKeysIn, int n, int minX, int maxX, i
         set_error("quadtree: N=%d does not fit shared memory", N);
         return ORBX_E_INVALID;
     }
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        ORBX_CUDA(cudaFuncSetAttribute(k_quadtree_single, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static size_t configured[ORBX_MAX_DEVICES] = {};
+    if (int rcAttr = ensure_dynamic_smem((const void*)k_quadtree_single, smem, configured)) return rcAttr;
     k_quadtree_single<<<1, QT_THREADS, smem, s>>>(dKeysIn, n, W, H, nIni, hX, N, maxNodes, dScratch, candCap, dOut, dCount);
     count_launch();
     ORBX_CUDA(cudaGetLastError());

@@ -269,11 +269,8 @@ int launch_search_for_initialization(const orbx_keypoint* k1, int n1, const uint
         set_error("SearchForInitialization: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
         return ORBX_E_INVALID;
     }
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        ORBX_CUDA(cudaFuncSetAttribute(k_sfi_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static size_t configured[ORBX_MAX_DEVICES] = {};
+    if (int rcAttr = ensure_dynamic_smem((const void*)k_sfi_resolve, smem, configured)) return rcAttr;
     k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, minX, minY, invW, invH, cellOf, sorted, cellStart);
     count_launch();
     k_sfi_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(k1, n1, reinterpret_cast<const uint4*>(desc1), k2,
@@ -503,11 +500,8 @@ int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1
         set_error("SearchByProjection: %d + %d keypoints do not fit the resolve kernel's shared memory", n1, n2);
         return ORBX_E_INVALID;
     }
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        ORBX_CUDA(cudaFuncSetAttribute(k_sbp_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static size_t configured[ORBX_MAX_DEVICES] = {};
+    if (int rcAttr = ensure_dynamic_smem((const void*)k_sbp_resolve, smem, configured)) return rcAttr;
     k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
     count_launch();
     k_sbp_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(n1, x3Dc, valid1, reinterpret_cast<const uint4*>(mpDesc1), octave1, k2,
@@ -593,11 +587,8 @@ int launch_search_by_projection_map(int n1, const float* proj, const float* view
         set_error("SearchByProjection: %d keypoints do not fit the resolve kernel's shared memory", n2);
         return ORBX_E_INVALID;
     }
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        ORBX_CUDA(cudaFuncSetAttribute(k_sbpm_resolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    static size_t configured[ORBX_MAX_DEVICES] = {};
+    if (int rcAttr = ensure_dynamic_smem((const void*)k_sbpm_resolve, smem, configured)) return rcAttr;
     k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
     count_launch();
     k_sbp_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(n1, proj, valid1, reinterpret_cast<const uint4*>(mpDesc1), level1, k2,

@@ -31,6 +31,7 @@ constexpr int CELL_CAP = 128;    // FAST keypoints per cell (overflow -> ORBX_E_
 constexpr int FAST_MAX_STRIP_CELLS = 8;  // cells one FAST CTA handles (a strip of one cell row)
 constexpr int QT_THREADS = 256;
 constexpr int MAX_ROOTS = 64;
+constexpr int ORBX_MAX_DEVICES = 64;  // per-device attribute caches (ensure_dynamic_smem)
 
 struct LevelGeom {
     int w, h;               // interior size
@@ -176,6 +177,9 @@ int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, c
 int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrips, int batch, int* cellCnt,
                 uint32_t* cellKeys, int* dStatus, cudaStream_t s);
 int fast_cells_per_strip(int wCell, int nCols);
+// opt-in to > 48 KB of dynamic shared memory, once per (kernel, device): perDevice is the kernel's own
+// size_t[ORBX_MAX_DEVICES] cache (the attribute is per device; the cache is guarded by a mutex)
+int ensure_dynamic_smem(const void* func, size_t bytes, size_t* perDevice);
 // DistributeOctTree per (frame, level)
 int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uint32_t* cellKeys, uint32_t* qtScratch,
                     int* lvlCnt, uint32_t* lvlKeys, int* dStatus, cudaStream_t s);
