@@ -92,6 +92,17 @@ int orbx_extract(orbx_extractor* ex, const uint8_t* img, int w, int h, size_t st
 int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride,
                        size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int cap, int* counts);
 
+/* Offline sequences (BASELINE config 5): the same call split into "enqueue" and "collect", so that consecutive batches
+ * overlap — the host->device copies of batch k + 1 run while the kernels and device->host copies of batch k are still
+ * going.  All buffers must be pinned host memory (cudaHostAlloc / cudaHostRegister) and the frames tightly packed
+ * (stride == w, frame_stride == w*h); they stay owned by the call until orbx_extract_batch_wait returns for it, so two
+ * calls in flight need two sets of output buffers.  At most two calls may be in flight; orbx_extract_batch_wait collects
+ * the OLDEST one and returns its status (ORBX_OK / ORBX_E_OVERFLOW / ORBX_E_CUDA).  The reference has no counterpart:
+ * its operator() is one synchronous frame (src/ORBextractor.cc:1538). */
+int orbx_extract_batch_async(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride,
+                             size_t frame_stride, orbx_keypoint* kps, uint8_t* desc, int cap, int* counts);
+int orbx_extract_batch_wait(orbx_extractor* ex);
+
 /* Same with every buffer already resident in device memory; asynchronous on `stream` (NULL = the handle's own
  * stream).  d_status (device int, may be NULL) receives 0 or ORBX_E_OVERFLOW. */
 int orbx_extract_batch_device(orbx_extractor* ex, const uint8_t* d_frames, int batch, int w, int h, size_t stride,

@@ -55,6 +55,7 @@ def lib() -> C.CDLL:
         L.orbx_extractor_stream.argtypes = [C.c_void_p]
         L.orbx_extractor_destroy.argtypes = [C.c_void_p]
         L.orbx_extractor_destroy.restype = None
+        L.orbx_extract_batch_wait.argtypes = [C.c_void_p]
         L.orbx_vocabulary_destroy.argtypes = [C.c_void_p]
         L.orbx_vocabulary_destroy.restype = None
         L.orbx_vocabulary_info.argtypes = [C.c_void_p] + [C.c_void_p] * 6
@@ -162,6 +163,18 @@ class ORBextractor:
         _check(lib().orbx_extract_batch(self._h, _p(frames), b, w, h, C.c_size_t(frames.strides[1]), C.c_size_t(frames.strides[0]),
                                         _p(kps), _p(desc), cap, _p(counts)))
         return kps, desc, counts
+
+    def extract_batch_async(self, frames: np.ndarray, kps, desc, counts, cap=None):
+        """orbx_extract_batch_async: enqueue one batch (all arrays pinned host memory, frames tightly packed) and return; at
+        most two calls in flight, each with its own output arrays.  extract_batch_wait() collects the oldest one."""
+        assert frames.dtype == np.uint8 and frames.ndim == 3 and frames.strides[2] == 1
+        b, h, w = frames.shape
+        cap = cap or self.default_cap()
+        _check(lib().orbx_extract_batch_async(self._h, _p(frames), b, w, h, C.c_size_t(frames.strides[1]), C.c_size_t(frames.strides[0]),
+                                              _p(kps), _p(desc), cap, _p(counts)))
+
+    def extract_batch_wait(self):
+        _check(lib().orbx_extract_batch_wait(self._h))
 
     def extract_batch_device(self, d_frames: int, batch: int, w: int, h: int, d_kps: int, d_desc: int, cap: int,
                              d_counts: int, d_status: int = 0, stream: int = 0, stride: int = 0, frame_stride: int = 0):

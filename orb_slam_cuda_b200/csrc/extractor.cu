@@ -48,6 +48,10 @@ static inline long long round_up(long long v, long long a) { return (v + a - 1) 
 
 using namespace orbx;
 
+#ifndef ORBX_DESC_SUB_DEFAULT
+#define ORBX_DESC_SUB_DEFAULT 0  // frames per blur + describe sub-batch (0 = whole batch); ORBX_DESC_SUB overrides
+#endif
+
 struct orbx_extractor {
     orbx_params prm{};
     int device = 0;
@@ -64,8 +68,16 @@ struct orbx_extractor {
     TmaMaps fastMaps{}, blurMaps{};
     std::vector<int> areaFast;
     DevBuf planes[ORBX_MAX_LEVELS], blurs[ORBX_MAX_LEVELS], xtab[ORBX_MAX_LEVELS], ytab[ORBX_MAX_LEVELS];
-    DevBuf strips, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, lvlAngles, status, dFrames, dKps, dDesc, dCounts;
+    DevBuf strips, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, lvlAngles, status, dDesc, dCounts;
+    DevBuf dFrames[2], dKps[2];  // device input / output staging of host-buffer calls, one set per in-flight call (slot)
     PinBuf hFrames, hKps, hDesc, hCounts, hStatus;
+    // orbx_extract_batch_async: up to two calls in flight; slot k of a call = its sequence number & 1
+    struct Pending {
+        cudaEvent_t done = nullptr;  // recorded after the call's last D2H
+        const int* hst = nullptr;    // pinned status word of the call
+        int cap = 0;
+    } pend[2];
+    int pendHead = 0, pendCount = 0;  // oldest in-flight slot, calls in flight
     // host copies of pyramid levels for mvImagePyramid readers
     std::vector<uint8_t> hostLevel[ORBX_MAX_LEVELS];
     int hostLevelFrame[ORBX_MAX_LEVELS];
@@ -87,6 +99,8 @@ struct orbx_extractor {
     bool timing = false;
     bool timed = false;      // the last call recorded events
     cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
+    std::vector<cudaEvent_t> subEv;  // timing of the blur / describe sub-batches: (blur done, describe done) per sub-batch
+    int nSub = 0;
     int lastBatch = 0;
     int lastScratchBase = 0; // scratch frame holding frame `lastFrameBase` of the caller's batch
     int lastFrameBase = 0;   // index (within the caller's batch) of frame 0 of the scratch: > 0 after a chunked host batch
@@ -405,11 +419,33 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     if ((rc = launch_quadtree(g, batch, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus, s))) return rc;
     if ((rc = stage_sync("Make quadtree", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[3], s));
-    if ((rc = launch_blur(g, ex->blurMaps, batch, s))) return rc;                                            // GaussianBlur
-    if ((rc = stage_sync("Gaussian Blur", s))) return rc;
-    if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[4], s));
-    if ((rc = launch_describe(g, batch, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts, lvlAngles, dStatus, s))) return rc;
-    if ((rc = stage_sync("Compute angle + ORB descriptor", s))) return rc;
+    // GaussianBlur + descriptors run over SUB-BATCHES: the blurred levels of `sub` frames (1.47 MB per KITTI frame) are
+    // still in the 126 MB L2 when the descriptor kernel gathers its 37 x 37 patches from them, instead of coming back from
+    // HBM as they do when all frames are blurred first (ncu: 1.5 GB of DRAM reads for 62 MB of output on 512 frames).
+    static const int subPref = []() { const char* e = getenv("ORBX_DESC_SUB"); return e ? atoi(e) : ORBX_DESC_SUB_DEFAULT; }();
+    const int sub = subPref > 0 && batch > subPref ? (batch + (batch + subPref - 1) / subPref - 1) / ((batch + subPref - 1) / subPref) : batch;
+    ex->nSub = 0;
+    for (int b0 = 0; b0 < batch; b0 += sub) {
+        const int nb = std::min(sub, batch - b0);
+        FrameGeom gs = g;
+        gs.f0 = g.f0 + b0;
+        if ((rc = launch_blur(gs, ex->blurMaps, nb, s))) return rc;                                          // GaussianBlur
+        if ((rc = stage_sync("Gaussian Blur", s))) return rc;
+        if (tm) {
+            while ((int)ex->subEv.size() < 2 * (ex->nSub + 1)) {
+                cudaEvent_t e;
+                ORBX_CUDA(cudaEventCreate(&e));
+                ex->subEv.push_back(e);
+            }
+            ORBX_CUDA(cudaEventRecord(ex->subEv[2 * ex->nSub], s));
+        }
+        if ((rc = launch_describe(gs, nb, lvlCnt + (size_t)b0 * nl, lvlKeys + (size_t)b0 * g.slotsTotal, dKps + (size_t)b0 * cap,
+                                  dDesc + (size_t)b0 * cap * 32, cap, dCounts + b0, lvlAngles + (size_t)b0 * g.slotsTotal, dStatus, s)))
+            return rc;
+        if ((rc = stage_sync("Compute angle + ORB descriptor", s))) return rc;
+        if (tm) ORBX_CUDA(cudaEventRecord(ex->subEv[2 * ex->nSub + 1], s));
+        ex->nSub++;
+    }
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
     ex->serial++;
     ex->lastBatch = batch;
@@ -509,14 +545,17 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
             cudaStreamDestroy(st);
         }
     for (cudaEvent_t e : ex->pipeEv) cudaEventDestroy(e);
+    for (auto& pd : ex->pend)
+        if (pd.done) cudaEventDestroy(pd.done);
     if (ex->graphExec) cudaGraphExecDestroy(ex->graphExec);
     for (cudaEvent_t e : ex->ev)
         if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : ex->subEv) cudaEventDestroy(e);
     for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
         ex->planes[l].release(); ex->blurs[l].release(); ex->xtab[l].release(); ex->ytab[l].release();
     }
     for (DevBuf* b : {&ex->strips, &ex->cellCnt, &ex->cellKeys, &ex->qtScratch, &ex->lvlCnt, &ex->lvlKeys, &ex->lvlAngles, &ex->status,
-                      &ex->dFrames, &ex->dKps, &ex->dDesc, &ex->dCounts})
+                      &ex->dFrames[0], &ex->dFrames[1], &ex->dKps[0], &ex->dKps[1], &ex->dDesc, &ex->dCounts})
         b->release();
     for (PinBuf* b : {&ex->hFrames, &ex->hKps, &ex->hDesc, &ex->hCounts, &ex->hStatus}) b->release();
     delete ex;
@@ -549,7 +588,15 @@ int orbx_extractor_stage_ms(orbx_extractor* ex, float* ms) {
     if (rc) return rc;
     if (!ms || !ex->timed) { set_error("orbx_extractor_stage_ms: the last extract call was not timed"); return ORBX_E_INVALID; }
     ORBX_CUDA(cudaEventSynchronize(ex->ev[ORBX_NUM_STAGES]));
-    for (int i = 0; i < ORBX_NUM_STAGES; ++i) ORBX_CUDA(cudaEventElapsedTime(&ms[i], ex->ev[i], ex->ev[i + 1]));
+    for (int i = 0; i < 3; ++i) ORBX_CUDA(cudaEventElapsedTime(&ms[i], ex->ev[i], ex->ev[i + 1]));
+    ms[3] = ms[4] = 0.f;  // blur and describe alternate over sub-batches: their times are summed per kind
+    for (int k = 0; k < ex->nSub; ++k) {
+        float a = 0.f, b = 0.f;
+        ORBX_CUDA(cudaEventElapsedTime(&a, k == 0 ? ex->ev[3] : ex->subEv[2 * k - 1], ex->subEv[2 * k]));
+        ORBX_CUDA(cudaEventElapsedTime(&b, ex->subEv[2 * k], ex->subEv[2 * k + 1]));
+        ms[3] += a;
+        ms[4] += b;
+    }
     return ORBX_OK;
 }
 
@@ -624,16 +671,35 @@ static bool is_pinned(const void* p) {
     return a.type == cudaMemoryTypeHost;
 }
 
-int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride, size_t frameStride,
-                       orbx_keypoint* kps, uint8_t* desc, int cap, int* counts) {
+static int overflow_error(int cap) {
+    set_error("orbx_extract: a device buffer overflowed (more than %d keypoints in a FAST cell, or more than cap=%d keypoints in a frame)",
+              CELL_CAP, cap);
+    return ORBX_E_OVERFLOW;
+}
+
+// async = true: everything is enqueued (pinned, tightly packed caller buffers only) and the call returns; the caller collects
+// it with orbx_extract_batch_wait.  Two calls may be in flight: they use disjoint device staging (slot) and share the
+// streams, so call k + 1's H2D copies run while call k's kernels and D2H copies are still going.
+static int extract_batch_impl(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride, size_t frameStride,
+                              orbx_keypoint* kps, uint8_t* desc, int cap, int* counts, bool async) {
     int rc = check_device(ex);
     if (rc) return rc;
     if (batch < 1 || !counts || cap < 0) { set_error("orbx_extract_batch: bad argument"); return ORBX_E_INVALID; }
+    if (!async && ex->pendCount > 0) {
+        set_error("orbx_extract_batch: %d asynchronous call(s) in flight; collect them with orbx_extract_batch_wait first", ex->pendCount);
+        return ORBX_E_INVALID;
+    }
+    if (async && ex->pendCount >= 2) {
+        set_error("orbx_extract_batch_async: two calls are in flight already; orbx_extract_batch_wait one first");
+        return ORBX_E_INVALID;
+    }
     if (!frames || w <= 0 || h <= 0) {  // empty image: the reference returns without touching the outputs (:1542-1543)
+        if (async) { set_error("orbx_extract_batch_async: empty frames"); return ORBX_E_INVALID; }
         for (int f = 0; f < batch; ++f) counts[f] = 0;
         return ORBX_OK;
     }
     if (stride < (size_t)w || !kps || !desc || cap < 1) { set_error("orbx_extract_batch: bad argument"); return ORBX_E_INVALID; }
+    const int slot = async ? ((ex->pendHead + ex->pendCount) & 1) : 0;
     // The batch is cut into chunks that flow through three streams — H2D | kernels | D2H — so the copies of chunk c+1 and
     // c-1 overlap the kernels of chunk c.  The scratch (pyramids, cell lists ...) holds TWO chunks: even and odd chunks
     // run their kernels on two streams ("lanes") over disjoint halves of it; small batches are a single chunk.
@@ -660,16 +726,20 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
     const int nChunks = (int)sizes.size();
     const int lanes = nChunks > 1 ? 2 : 1;  // kernels of even / odd chunks run on two streams over disjoint scratch halves, so
                                             // the tail of one chunk's kernels overlaps the next chunk's
+    if (ex->pendCount > 0 && !(w == ex->w && h == ex->h && lanes * C <= ex->batchCap)) {
+        set_error("orbx_extract_batch_async: the geometry or the chunk size changes while a call is in flight; wait for it first");
+        return ORBX_E_INVALID;
+    }
     if ((rc = configure(ex, w, h, lanes * C))) return rc;
     cudaStream_t s = ex->stream;
     const size_t rowBytes = (size_t)w, frameBytes = rowBytes * h;
-    if ((rc = ex->dFrames.ensure(frameBytes * batch + 16))) return rc;
+    if ((rc = ex->dFrames[slot].ensure(frameBytes * batch + 16))) return rc;
     // device outputs live in ONE allocation [keypoints | descriptors | counts | status] mirrored by one pinned block, so a
     // small call returns everything with a single D2H copy
     const size_t kpBytes = (size_t)round_up((long long)batch * cap * sizeof(orbx_keypoint), 256);
     const size_t dBytes = (size_t)round_up((long long)batch * cap * 32, 256), cBytes = (size_t)round_up((long long)batch * 4, 256);
     const size_t outBytes = kpBytes + dBytes + cBytes + 256;
-    if ((rc = ex->dKps.ensure(outBytes))) return rc;
+    if ((rc = ex->dKps[slot].ensure(outBytes))) return rc;
     cudaStream_t sIn = s, sOut = s;
     if (nChunks > 1) {
         if (!ex->h2dStream) ORBX_CUDA(cudaStreamCreateWithFlags(&ex->h2dStream, cudaStreamNonBlocking));
@@ -688,11 +758,15 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
     const bool tight = stride == rowBytes && (frameStride == frameBytes || batch == 1);
     const bool directIn = tight && is_pinned(frames);
     const bool direct = is_pinned(kps) && is_pinned(desc) && is_pinned(counts);
+    if (async && !(directIn && direct)) {
+        set_error("orbx_extract_batch_async needs pinned (cudaHostAlloc / cudaHostRegister) tightly packed frames and pinned outputs");
+        return ORBX_E_INVALID;
+    }
     if (!directIn && (rc = ex->hFrames.ensure(frameBytes * batch))) return rc;
     orbx_keypoint* hk = kps;
     uint8_t* hd = desc;
     int* hc = counts;
-    int* hst = ex->hStatus.as<int>();
+    int* hst = ex->hStatus.as<int>() + 4 * slot;
     if (!direct) {
         if ((rc = ex->hKps.ensure(outBytes))) return rc;
         uint8_t* hb = ex->hKps.as<uint8_t>();
@@ -701,15 +775,15 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
         hc = reinterpret_cast<int*>(hb + kpBytes + dBytes);
         hst = reinterpret_cast<int*>(hb + kpBytes + dBytes + cBytes);
     }
-    uint8_t* dOut = ex->dKps.as<uint8_t>();
+    uint8_t* dOut = ex->dKps[slot].as<uint8_t>();
     orbx_keypoint* dK = reinterpret_cast<orbx_keypoint*>(dOut);
     uint8_t* dD = dOut + kpBytes;
     int* dC = reinterpret_cast<int*>(dOut + kpBytes + dBytes);
     int* dSt = reinterpret_cast<int*>(dOut + kpBytes + dBytes + cBytes);
     const bool oneCopy = !direct && nChunks == 1;
-    uint8_t* dF = ex->dFrames.as<uint8_t>();
+    uint8_t* dF = ex->dFrames[slot].as<uint8_t>();
     static const bool noGraph = getenv("ORBX_NO_GRAPH") != nullptr || getenv("ORBX_DEBUG_SYNC") != nullptr;
-    if (batch == 1 && oneCopy && !directIn && !ex->timing && ex->graphOk && !noGraph) {
+    if (batch == 1 && oneCopy && !directIn && !ex->timing && ex->graphOk && !noGraph && !async) {
         // ---- single frame, pageable buffers (what ORBextractor::operator() does per frame): the whole sequence is captured
         //      into a CUDA graph the second time a geometry is seen and replayed from then on ----
         uint8_t* st = ex->hFrames.as<uint8_t>();
@@ -819,6 +893,15 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
                                   cudaMemcpyDeviceToHost, sOut));
     }
     if (!oneCopy) ORBX_CUDA(cudaMemcpyAsync(hst, dSt, 4, cudaMemcpyDeviceToHost, sOut));
+    if (async) {  // every chunk's D2H waits for its kernels, which wait for its H2D: this event closes the whole call
+        orbx_extractor::Pending& pd = ex->pend[slot];
+        if (!pd.done) ORBX_CUDA(cudaEventCreateWithFlags(&pd.done, cudaEventDisableTiming));
+        ORBX_CUDA(cudaEventRecord(pd.done, sOut));
+        pd.hst = hst;
+        pd.cap = cap;
+        ex->pendCount++;
+        return ORBX_OK;
+    }
     ORBX_CUDA(cudaStreamSynchronize(sOut));
     if (nChunks > 1) {
         ORBX_CUDA(cudaStreamSynchronize(sIn));
@@ -832,13 +915,31 @@ int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int
             memcpy(desc + (size_t)f * cap * 32, hd + (size_t)f * cap * 32, (size_t)hc[f] * 32);
         }
     }
-    const int st = *hst;
-    if (st != 0) {
-        set_error("orbx_extract: a device buffer overflowed (more than %d keypoints in a FAST cell, or more than cap=%d keypoints in a frame)",
-                  CELL_CAP, cap);
-        return ORBX_E_OVERFLOW;
+    return *hst != 0 ? overflow_error(cap) : ORBX_OK;
+}
+
+int orbx_extract_batch(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride, size_t frameStride,
+                       orbx_keypoint* kps, uint8_t* desc, int cap, int* counts) {
+    return extract_batch_impl(ex, frames, batch, w, h, stride, frameStride, kps, desc, cap, counts, false);
+}
+
+int orbx_extract_batch_async(orbx_extractor* ex, const uint8_t* frames, int batch, int w, int h, size_t stride, size_t frameStride,
+                             orbx_keypoint* kps, uint8_t* desc, int cap, int* counts) {
+    return extract_batch_impl(ex, frames, batch, w, h, stride, frameStride, kps, desc, cap, counts, true);
+}
+
+int orbx_extract_batch_wait(orbx_extractor* ex) {
+    int rc = check_device(ex);
+    if (rc) return rc;
+    if (ex->pendCount == 0) {
+        set_error("orbx_extract_batch_wait: no asynchronous call in flight");
+        return ORBX_E_INVALID;
     }
-    return ORBX_OK;
+    orbx_extractor::Pending& pd = ex->pend[ex->pendHead];
+    ex->pendHead ^= 1;
+    ex->pendCount--;
+    ORBX_CUDA(cudaEventSynchronize(pd.done));
+    return *pd.hst != 0 ? overflow_error(pd.cap) : ORBX_OK;
 }
 
 int orbx_extract(orbx_extractor* ex, const uint8_t* img, int w, int h, size_t stride, orbx_keypoint* kps, uint8_t* desc, int cap,

@@ -10,9 +10,10 @@
 // frame f is scored), so the strip geometry, the column tables and the thread -> (row, word) mapping are built once per
 // CTA instead of once per frame.  Per frame:
 //   A1     opposite-pair reject, four pixels per lane as packed bytes: an arc of 9 ring points holds one point of every
-//          diametral pair, so a pixel can only be a corner if ring point (0,+3) or (0,-3) is brighter than v + t, or one
-//          of them is darker than v - t (OpenCV's own first test, d = tab[ptr[0]] | tab[ptr[8]]).  Three row loads, no
-//          realignment; words with a live pixel are compacted into a word list (one ballot per warp);
+//          diametral pair, so a pixel can only be a corner if ring point (0,+3) or (0,-3) differs from v by more than t
+//          (OpenCV's own first test, d = tab[ptr[0]] | tab[ptr[8]], without the sign).  Three row loads, no realignment,
+//          two VABSDIFF4 and a carry test per word; words with a live pixel are compacted into a word list (one ballot
+//          per warp step);
 //   A2     the words of the list get the test on all 8 EVEN ring points (rows y+-3, y+-2, y realigned with funnel
 //          shifts): a run of 9 holds 4 consecutive even points, so a pixel survives iff 4 consecutive even points are
 //          all brighter (or all darker); survivors join a pixel list;
@@ -58,9 +59,6 @@ constexpr int FS_THREADS = ORBX_FS_THREADS;
 #endif
 #ifndef ORBX_FS_FPC
 #define ORBX_FS_FPC 8   // frames one CTA walks (per-CTA set-up is paid once per slice)
-#endif
-#ifndef ORBX_FS_A1_COMPASS
-#define ORBX_FS_A1_COMPASS 0  // 1: A1 also tests the horizontal pair (two of the four compass points must agree)
 #endif
 constexpr int FS_WL = ORBX_FS_WL;        // words with a live pixel after A1, per row chunk
 constexpr int FS_LIST1 = ORBX_FS_LIST1;  // even-point survivors per row chunk
@@ -129,48 +127,14 @@ __device__ __forceinline__ void cmp_ring(uint32_t ring, const Thr& th, uint32_t&
     dk = lop3<0x4d>(ring, th.lx, r7 + th.LN7);
 }
 
-// A1 for one lane = one (row segment, word column) pair: SEGH rows of the column, walked top to bottom with the rows in
-// registers (branch-free, so the compiler interleaves the rows); then the warp appends its live words to the word list, one
-// ballot per row.  p points at tile row ya (= row ya - 3 of the detectable area) of the column; rows past the window's end
-// are read but never used (the bytes behind a ring stage belong to this CTA's shared memory too).
-template <int SEGH>
-__device__ __forceinline__ void fast_a1_unit(const uint32_t* p, int TWq, uint32_t vm, int nr, int ya, int w, uint32_t T4, uint32_t K4,
-                                             bool small, uint32_t laneLt, int lane, int* cntLive, uint16_t* wlist) {
-    uint32_t live = 0;  // bit j: row ya + j of this column has a pixel that passes
-    if (vm != 0) {
-        uint32_t rw[SEGH + 6];
-#pragma unroll
-        for (int k = 0; k < SEGH + 6; ++k) {
-            rw[k] = *p;
-            p += TWq;
-        }
-#pragma unroll
-        for (int j = 0; j < SEGH; ++j) {
-            const Thr th = make_thr(rw[j + 3], T4, K4, small);
-            uint32_t b0, d0, b4, d4;
-            cmp_ring(rw[j + 6], th, b0, d0);  // ( 0, +3)
-            cmp_ring(rw[j], th, b4, d4);      // ( 0, -3)
-            const uint32_t al = (((b0 | b4) & th.okB) | ((d0 | d4) & th.okD)) & vm;
-            if (al != 0 && j < nr) live |= 1u << j;
-        }
-    }
-    if (__any_sync(0xffffffffu, live != 0)) {
-        uint32_t bal[SEGH];
-        int total = 0;
-#pragma unroll
-        for (int j = 0; j < SEGH; ++j) {
-            bal[j] = __ballot_sync(0xffffffffu, (live >> j) & 1u);
-            total += __popc(bal[j]);
-        }
-        int o = 0;
-        if (lane == 0) o = atomicAdd(cntLive, total);
-        o = __shfl_sync(0xffffffffu, o, 0);
-#pragma unroll
-        for (int j = 0; j < SEGH; ++j) {
-            if ((live >> j) & 1u) wlist[o + __popc(bal[j] & laneLt)] = (uint16_t)(((ya + j) << 6) | w);
-            o += __popc(bal[j]);
-        }
-    }
+// A1 for the four pixels of one word: is ring point (0, +3) or (0, -3) further than t from the centre?  |ring - v| is one
+// VABSDIFF4 (a full-rate ALU instruction on sm_100a, tools/pipe_rates.cu); a byte a exceeds t iff a >= 128 or (a & 127) +
+// 127 - t carries into bit 7 (t < 128), resp. a >= 128 and (a & 127) + 127 - (t - 128) carries (t >= 128).  K7 holds
+// 127 - (t & 127) in every byte.  Returns bit 7 of every byte that passes.
+__device__ __forceinline__ uint32_t a1_word(uint32_t up, uint32_t c, uint32_t dn, uint32_t K7, bool small) {
+    const uint32_t a = __vabsdiffu4(up, c), b = __vabsdiffu4(dn, c);
+    const uint32_t ga = (a & 0x7f7f7f7fu) + K7, gb = (b & 0x7f7f7f7fu) + K7;
+    return small ? (ga | a | gb | b) : ((ga & a) | (gb & b));
 }
 
 __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(const __grid_constant__ FrameGeom g,
@@ -248,7 +212,7 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
     // row chunks: the word list always holds a chunk; the survivor list holds it in the common case (a denser chunk is
     // redone with rpcSafe rows, whose pixels all fit)
     const int rpcOpt = max(1, min(dH, FS_WL / nW)), rpcSafe = max(1, FS_LIST1 / (nW * 4));
-    const int nWG = (nW + 31) >> 5;  // A1: a warp owns 32 word columns x 8 rows at a time (nW <= 64)
+    const int nWG = (nW + 31) >> 5;  // 32-column groups of the strip (nW <= 64)
     const uint32_t laneLt = (1u << lane) - 1u;
     // emptiness test of the strip's cells after pass 1 (src/ORBextractor.cc:1281): which cells exist at all
     uint32_t validCells = 0;
@@ -291,34 +255,40 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
             const int t = min(max(pass == 0 ? g.iniTh : g.minTh, 0), 255);
             const bool small = t < 128;
             const uint32_t T4 = (uint32_t)t * 0x01010101u, K4 = 0x80808080u - T4;
+            const uint32_t K7 = (uint32_t)(127 - (t & 127)) * 0x01010101u;
             int rpc = rpcOpt;
             for (int y0 = 0; y0 < dH;) {
                 const int y1 = min(y0 + rpc, dH);
-                // ---- A1: opposite-pair reject on (0, +-3).  A lane walks down one word column 8 rows at a time with the
-                //      rows in registers; live words -> word list, one ballot per row ----
+                // ---- A1: opposite-pair reject on (0, +-3) over the flat (row, word column) index of the chunk — all columns in
+                //      pass 1, the empty cells' columns in pass 2; a lane keeps its (row, column) pair and steps it by the CTA
+                //      width without a division.  Words with a passing pixel join the word list, one ballot per warp step ----
                 {
-                    // a lane takes one (row segment, word column) pair of a flat list — all columns in pass 1, the empty cells'
-                    // columns in pass 2.  The segment height is the smallest of 8..12 rows with which the pairs fill the CTA's
-                    // lanes once (32 columns x 4 segments of 8 rows, 33 x 3 of 11 ...); otherwise 8 rows and several rounds
-                    const int rows = y1 - y0;
-                    int segH = 8;
-                    if (small)
-                        for (int h = 8; h <= 12; ++h)
-                            if (((rows + h - 1) / h) * nCols <= FS_THREADS) { segH = h; break; }
-                    const int nSeg = (rows + segH - 1) / segH, nUnits = nSeg * nCols;
+                    const int rows = y1 - y0, nUnits = rows * nCols;
+                    const int stepRow = FS_THREADS / nCols, stepCol = FS_THREADS - stepRow * nCols;
+                    int row = tid / nCols, col = tid - row * nCols;
                     for (int u0 = warp * 32; u0 < nUnits; u0 += FS_THREADS) {
-                        const int idx = u0 + lane, seg = idx / nCols, ci = idx - seg * nCols;
-                        const bool unitOk = idx < nUnits;
-                        const int w = !unitOk ? 0 : pass == 0 ? ci : colList[ci];
-                        const int ya = y0 + seg * segH, nr = min(segH, y1 - ya);
-                        const uint32_t vm = unitOk ? act32[wq0 + w] : 0u;
-                        const uint32_t* p = tile32 + ya * TWq + wq0 + w;
-                        switch (segH) {
-                            case 8: fast_a1_unit<8>(p, TWq, vm, nr, ya, w, T4, K4, small, laneLt, lane, &cnt[0], wlist); break;
-                            case 9: fast_a1_unit<9>(p, TWq, vm, nr, ya, w, T4, K4, true, laneLt, lane, &cnt[0], wlist); break;
-                            case 10: fast_a1_unit<10>(p, TWq, vm, nr, ya, w, T4, K4, true, laneLt, lane, &cnt[0], wlist); break;
-                            case 11: fast_a1_unit<11>(p, TWq, vm, nr, ya, w, T4, K4, true, laneLt, lane, &cnt[0], wlist); break;
-                            default: fast_a1_unit<12>(p, TWq, vm, nr, ya, w, T4, K4, true, laneLt, lane, &cnt[0], wlist); break;
+                        const bool unitOk = u0 + lane < nUnits;
+                        uint32_t al = 0;
+                        int e = 0;
+                        if (unitOk) {
+                            const int w = pass == 0 ? col : colList[col];
+                            const int y = y0 + row;
+                            const uint32_t* p = tile32 + y * TWq + wq0 + w;
+                            al = a1_word(p[0], p[3 * TWq], p[6 * TWq], K7, small) & act32[wq0 + w];
+                            e = (y << 6) | w;
+                        }
+                        const uint32_t bal = __ballot_sync(0xffffffffu, al != 0);
+                        if (bal != 0) {
+                            int o = 0;
+                            if (lane == 0) o = atomicAdd(&cnt[0], __popc(bal));
+                            o = __shfl_sync(0xffffffffu, o, 0);
+                            if (al != 0) wlist[o + __popc(bal & laneLt)] = (uint16_t)e;
+                        }
+                        row += stepRow;
+                        col += stepCol;
+                        if (col >= nCols) {
+                            col -= nCols;
+                            ++row;
                         }
                     }
                 }

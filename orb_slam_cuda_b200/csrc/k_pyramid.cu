@@ -24,45 +24,68 @@ __device__ __forceinline__ int reflect101(int p, int n) {
     return p;
 }
 
-// Level 0: a CTA of 8 warps writes a 128-byte x 64-row tile of the padded plane; a thread owns 4 consecutive bytes
-// (one 32-bit store per row), a warp reads 128 consecutive source bytes per row.
-// grid: (ceil(pitch / 128), ceil(rows / 64), batch); block 256
+// Level 0: a CTA of 8 warps writes a 512-byte x rowsPerCta tile of the padded plane; a thread owns 16 consecutive bytes
+// (one 128-bit store per row).  A frame row starts at any byte alignment (w is odd for KITTI), so a lane whose group lies
+// inside the interior loads the ALIGNED 16-byte chunk that holds its first byte (a warp reads 512 consecutive bytes),
+// takes the following chunk from its neighbour lane by shuffle (the misalignment is the same for every lane of a row), and
+// realigns the 32 bytes with four funnel shifts.  Groups holding the reflected border or the row padding gather bytes.
+// grid: (ceil(pitch / 512), ceil(rows / rowsPerCta), batch); block 256
 constexpr int RZ_ROWS = 64;  // minimum rows per CTA; launchers raise it (rowsPerCta) while the grid still fills the GPU
 __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plane, int w, int h, int pitch, int rows,
                                                       long long planeStride, const uint8_t* __restrict__ frames,
                                                       long long stride, long long frameStride, int rowsPerCta) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int bx = blockIdx.x * 128 + lane * 4;
-    if (bx >= pitch) return;
+    const int bx = blockIdx.x * 512 + lane * 16;
+    const bool inRow = bx < pitch;                         // (whole warps stay: the shuffles below need every lane)
     const int f = blockIdx.z;
-    int sx[4];
-    bool valid[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int px = bx + j - PADL;
-        valid[j] = px >= 0 && px < w + 2 * EDGE;
-        sx[j] = valid[j] ? reflect101(px - EDGE, w) : 0;
-    }
-    const bool run = valid[0] && valid[3] && sx[3] == sx[0] + 3;  // 4 consecutive interior source bytes
+    const int px0 = bx - XOFF;                             // interior x of byte 0 of the group
+    const bool run = inRow && px0 >= 0 && px0 + 16 <= w;   // 16 consecutive interior source bytes
+    const bool nextRun = lane < 31 && px0 + 32 <= w && bx + 16 < pitch && px0 + 16 >= 0;  // lane + 1 loads the chunk after mine
     const uint8_t* __restrict__ fbase = frames + (long long)f * frameStride;
     uint8_t* __restrict__ dbase = plane + (long long)f * planeStride + bx;
     const int rowEnd = min(blockIdx.y * rowsPerCta + rowsPerCta, rows);
+    int sx[16];
+    uint32_t validMask = 0;
+    if (inRow && !run) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const int px = bx + j - PADL;
+            const bool valid = px >= 0 && px < w + 2 * EDGE;
+            validMask |= (valid ? 1u : 0u) << j;
+            sx[j] = valid ? reflect101(px - EDGE, w) : 0;
+        }
+    }
     for (int py = blockIdx.y * rowsPerCta + warp; py < rowEnd; py += 8) {
         const uint8_t* __restrict__ src = fbase + (long long)reflect101(py - EDGE, h) * stride;
-        uint32_t v;
-        if (run) {  // 4 consecutive interior bytes at any alignment: the aligned word(s) holding them + a funnel shift.
-                    // The second word is read only when it holds a needed byte, so no load passes the frame's last word.
-            const uintptr_t a = reinterpret_cast<uintptr_t>(src + sx[0]);
-            const uint32_t* w0 = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-            const uint32_t sh = (uint32_t)(a & 3) * 8;
-            const uint32_t lo = __ldg(w0);
-            v = sh ? __funnelshift_r(lo, __ldg(w0 + 1), sh) : lo;
-        } else {
-            v = 0;
+        const uintptr_t a = reinterpret_cast<uintptr_t>(src + px0);
+        const uint4* c0 = reinterpret_cast<const uint4*>(a & ~(uintptr_t)15);
+        const uint32_t mis = (uint32_t)(a & 15);           // the same in every lane: px0 is a multiple of 16
+        uint4 A = make_uint4(0u, 0u, 0u, 0u);
+        if (run) A = __ldg(c0);
+        uint4 N;
+        N.x = __shfl_down_sync(0xffffffffu, A.x, 1);
+        N.y = __shfl_down_sync(0xffffffffu, A.y, 1);
+        N.z = __shfl_down_sync(0xffffffffu, A.z, 1);
+        N.w = __shfl_down_sync(0xffffffffu, A.w, 1);
+        uint4 v;
+        if (run) {
+            // the following chunk is read by this lane only when no neighbour has it, and only when it holds a needed
+            // byte (mis != 0), so no load passes the 16-byte chunk of the frame's last byte
+            if (!nextRun) N = mis ? __ldg(c0 + 1) : make_uint4(0u, 0u, 0u, 0u);
+            const uint32_t sh = (mis & 3u) * 8u;
+            switch (mis >> 2) {
+                case 0: v = make_uint4(__funnelshift_r(A.x, A.y, sh), __funnelshift_r(A.y, A.z, sh), __funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh)); break;
+                case 1: v = make_uint4(__funnelshift_r(A.y, A.z, sh), __funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh)); break;
+                case 2: v = make_uint4(__funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh), __funnelshift_r(N.y, N.z, sh)); break;
+                default: v = make_uint4(__funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh), __funnelshift_r(N.y, N.z, sh), __funnelshift_r(N.z, N.w, sh)); break;
+            }
+        } else if (inRow) {
+            uint32_t q[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
-            for (int j = 0; j < 4; ++j) v |= (valid[j] ? (uint32_t)__ldg(src + sx[j]) : 0u) << (8 * j);
+            for (int j = 0; j < 16; ++j) q[j >> 2] |= (((validMask >> j) & 1u) ? (uint32_t)__ldg(src + sx[j]) : 0u) << (8 * (j & 3));
+            v = make_uint4(q[0], q[1], q[2], q[3]);
         }
-        *reinterpret_cast<uint32_t*>(dbase + (long long)py * pitch) = v;
+        if (inRow) *reinterpret_cast<uint4*>(dbase + (long long)py * pitch) = v;
     }
 }
 
@@ -190,7 +213,7 @@ static int rows_per_cta(int rows, int gx, int batch) {
 int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
                         cudaStream_t s) {
     const LevelGeom& L = g.lv[0];
-    const int gx = (L.pitch + 127) / 128, rpc = rows_per_cta(L.rows, gx, batch);
+    const int gx = (L.pitch + 511) / 512, rpc = rows_per_cta(L.rows, gx, batch);
     dim3 grid(gx, (L.rows + rpc - 1) / rpc, batch);
     k_pyramid_base<<<grid, 256, 0, s>>>(L.plane + (long long)g.f0 * L.planeStride, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride,
                                           (long long)frameStride, rpc);

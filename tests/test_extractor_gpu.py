@@ -139,6 +139,60 @@ def test_chunked_host_batch(pinned):
         gx.image_pyramid_level(0, frame=0)  # not in the last chunk any more
 
 
+def test_async_host_batches_two_in_flight():
+    """orbx_extract_batch_async / orbx_extract_batch_wait: three different batches enqueued back to back, two in flight at
+    any time (their copies and kernels overlap on the device); every batch must equal the blocking call's result and —
+    for sample frames — the oracle; the misuse cases fail cleanly."""
+    import torch
+    h, w, nf, b = 120, 160, 300, 150
+    gx, ox = X.ORBextractor(nf, 1.2, 8, 20, 7), O.Extractor(nf, 1.2, 8, 20, 7)
+    cap = gx.default_cap()
+    pool = np.stack([synth.textured_frame(940 + i, h, w) for i in range(9)])
+
+    def batch(k):
+        fr = pool[(np.arange(b) + k) % 9].copy()
+        fr[:, 0, 0] = (np.arange(b) * 3 + k) % 251
+        return torch.from_numpy(fr).pin_memory()
+
+    def outputs():
+        tk = torch.empty((b, cap, 7), dtype=torch.int32).pin_memory()
+        td = torch.empty((b, cap, 32), dtype=torch.uint8).pin_memory()
+        tc = torch.empty(b, dtype=torch.int32).pin_memory()
+        return tk.numpy().view(X.KP_DTYPE).reshape(b, cap), td.numpy(), tc.numpy(), (tk, td, tc)
+
+    ins = [batch(k) for k in range(3)]
+    ref = [gx.extract_batch(t.numpy().copy()) for t in ins]  # blocking, pageable
+    outs = [outputs() for _ in range(3)]
+    gx.extract_batch_async(ins[0].numpy(), *outs[0][:3], cap)
+    gx.extract_batch_async(ins[1].numpy(), *outs[1][:3], cap)
+    with pytest.raises(X.OrbxError):  # a third call in flight is refused
+        gx.extract_batch_async(ins[2].numpy(), *outs[2][:3], cap)
+    with pytest.raises(X.OrbxError):  # and so is a blocking call while asynchronous ones are pending
+        gx.extract_batch(ins[2].numpy())
+    gx.extract_batch_wait()
+    gx.extract_batch_async(ins[2].numpy(), *outs[2][:3], cap)
+    gx.extract_batch_wait()
+    gx.extract_batch_wait()
+    with pytest.raises(X.OrbxError):
+        gx.extract_batch_wait()  # nothing left
+    with pytest.raises(X.OrbxError):  # pageable buffers cannot be used asynchronously
+        gx.extract_batch_async(ins[0].numpy().copy(), *outs[0][:3], cap)
+    for k in range(3):
+        kps, desc, counts = outs[k][:3]
+        rk, rd, rc = ref[k]
+        assert np.array_equal(counts, rc), k
+        for f in range(b):
+            n = counts[f]
+            assert np.array_equal(kps[f, :n].view(np.uint8), rk[f, :n].view(np.uint8)), (k, f)
+            assert np.array_equal(desc[f, :n], rd[f, :n]), (k, f)
+        for f in (0, 77, b - 1):
+            ok, od = ox.extract(ins[k].numpy()[f])
+            n = counts[f]
+            assert n == len(ok) and np.array_equal(kps[f, :n].view(np.uint8), ok.view(np.uint8)) and np.array_equal(desc[f, :n], od), (k, f)
+    kps, desc, counts = gx.extract_batch(ins[0].numpy())  # the blocking call works again afterwards
+    assert np.array_equal(counts, ref[0][2])
+
+
 def test_strided_input_and_empty():
     gx, ox = make("tum")
     big = np.zeros((500, 700), np.uint8)

@@ -4,6 +4,7 @@
 #   variants              stage times of every liborbx*.so variant (tools/variants.py builds them)
 #   sweep VAR v1 v2 ...   bench the default build with the environment variable VAR set to each value
 #   evidence TAG          tests, smoke, both bench arms, tum/euroc lines, ncu launch list, ncu --set full of one step
+#   ncu REGEX TAG SKIP N   ncu --set full --import-source of N launches matching REGEX after SKIP of them (device-resident step only)
 #   multi N               bench.py under torchrun on N GPUs
 mkdir -p gpurun_out
 mode=$1; shift
@@ -44,6 +45,12 @@ evidence)
   python bench.py --steps 2 --warmup 3 --batch 512 --no-cpu-baseline --no-match --no-latency > gpurun_out/plain.log 2>&1 &&
   ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_$tag.csv \
     python bench.py --steps 2 --warmup 3 --batch 512 --no-cpu-baseline --no-match --no-latency > gpurun_out/ncu_launches.log 2>&1
+  ;;
+ncu)  # ncu KERNEL_REGEX TAG SKIP COUNT [bench args]: --set full with source of the matching launches of one device-resident step
+  k=$1; tag=$2; skip=${3:-0}; cnt=${4:-1}; shift 4
+  ncu --set full --import-source on --clock-control none -k regex:$k -s $skip -c $cnt -f -o gpurun_out/ncu_$tag \
+    python bench.py --profile --steps 1 --warmup 1 --batch 512 "$@" > gpurun_out/ncu_$tag.log 2>&1; echo "ncu rc=$?"
+  ls -la gpurun_out/ncu_$tag.ncu-rep
   ;;
 multi)
   n=$1
