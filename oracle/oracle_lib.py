@@ -189,6 +189,15 @@ class Extractor:
         return self._kps(lib().orc_level_keypoints, l)
 
 
+def features_in_area(keys, bounds, x, y, r, min_level=-1, max_level=-1):
+    """Frame::GetFeaturesInArea (src/Frame.cc:326-379) over the grid of AssignFeaturesToGrid (:229-244)."""
+    keys = np.ascontiguousarray(keys, dtype=KP_DTYPE)
+    out = np.empty(max(keys.size, 1), np.int32)
+    b = [C.c_float(v) for v in bounds]
+    n = lib().orc_features_in_area(_p(keys), keys.size, *b, C.c_float(x), C.c_float(y), C.c_float(r), int(min_level), int(max_level), _p(out))
+    return out[:n].copy()
+
+
 def search_for_initialization(k1, d1, k2, d2, bounds, prev_xy, window=100, nnratio=0.9, check_ori=True):
     k1 = np.ascontiguousarray(k1, dtype=KP_DTYPE)
     k2 = np.ascontiguousarray(k2, dtype=KP_DTYPE)

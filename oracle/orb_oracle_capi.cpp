@@ -92,6 +92,15 @@ int orc_search_for_initialization(const KeyPoint* k1, int n1, const uint8_t* d1,
     GridFrame F1(k1, n1, minX, maxX, minY, maxY), F2(k2, n2, minX, maxX, minY, maxY);
     return search_for_initialization(F1, d1, F2, d2, prevXY, matches12, windowSize, nnratio, checkOri != 0);
 }
+// Frame::GetFeaturesInArea on the 64 x 48 grid (src/Frame.cc:229-244, :326-379): indices in the reference's visiting order
+int orc_features_in_area(const KeyPoint* k, int n, float minX, float maxX, float minY, float maxY, float x, float y, float r,
+                         int minLevel, int maxLevel, int* out) {
+    GridFrame F(k, n, minX, maxX, minY, maxY);
+    const std::vector<size_t> v = F.features_in_area(x, y, r, minLevel, maxLevel);
+    for (size_t i = 0; i < v.size(); ++i) out[i] = (int)v[i];
+    return (int)v.size();
+}
+
 int orc_search_by_projection_frame(int n1, const float* x3Dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mpDesc1,
                                    const int* octave1, const float* angle1, const KeyPoint* k2, int n2, const uint8_t* desc2,
                                    const float* uRight2, const uint8_t* occupied2, const float* cam, float mbf,

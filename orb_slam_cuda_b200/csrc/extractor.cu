@@ -86,7 +86,7 @@ struct orbx_extractor {
     // host-buffer batches are cut into chunks pipelined over three streams: H2D | kernels (stream) | D2H
     cudaStream_t h2dStream = nullptr, d2hStream = nullptr, stream2 = nullptr;  // stream2: kernels of odd chunks
     std::vector<cudaEvent_t> pipeEv;  // 2 per chunk: frames landed, kernels done
-    // single-frame host calls replay a captured CUDA graph (memset + H2D + 12 kernels + one D2H): one launch per frame
+    // single-frame host calls replay a captured CUDA graph (memset + H2D + 13 kernels + one D2H): one launch per frame
     struct GraphKey {
         int w = 0, h = 0, cap = 0;
         const void *hIn = nullptr, *hOut = nullptr, *dIn = nullptr, *dOut = nullptr, *plane0 = nullptr;
@@ -795,7 +795,7 @@ static int extract_batch_impl(orbx_extractor* ex, const uint8_t* frames, int bat
         if (ex->graphExec && key == ex->graphKey) {
             ORBX_CUDA(cudaGraphLaunch(ex->graphExec, s));
             ex->serial++;
-            for (int i = 0; i < ex->prm.nlevels + 4; ++i) count_launch();  // the kernels of the replayed graph
+            for (int i = 0; i < ex->prm.nlevels + 5; ++i) count_launch();  // the kernels of the replayed graph
             launched = true;
         } else {
             if (ex->graphExec) {

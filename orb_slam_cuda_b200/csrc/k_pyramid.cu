@@ -9,6 +9,8 @@
 // border pass is needed.
 //
 // Roofline: HBM-bound streaming (reads level l-1 once through L1/L2, writes level l once).
+#include <algorithm>
+
 #include "orbx_internal.h"
 
 namespace orbx {
@@ -24,11 +26,12 @@ __device__ __forceinline__ int reflect101(int p, int n) {
     return p;
 }
 
-// Level 0: a CTA of 8 warps writes a 512-byte x rowsPerCta tile of the padded plane; a thread owns 16 consecutive bytes
-// (one 128-bit store per row).  A frame row starts at any byte alignment (w is odd for KITTI), so a lane whose group lies
-// inside the interior loads the ALIGNED 16-byte chunk that holds its first byte (a warp reads 512 consecutive bytes),
-// takes the following chunk from its neighbour lane by shuffle (the misalignment is the same for every lane of a row), and
-// realigns the 32 bytes with four funnel shifts.  Groups holding the reflected border or the row padding gather bytes.
+// Level 0, interior: a CTA of 8 warps writes a 512-byte x rowsPerCta tile of the padded plane; a thread owns 16 consecutive
+// bytes (one 128-bit store per row).  A frame row starts at any byte alignment (w is odd for KITTI), so a lane loads the
+// ALIGNED 16-byte chunk that holds its first byte (a warp reads 512 consecutive bytes), takes the following chunk from its
+// neighbour lane by shuffle (the misalignment is the same for every lane of a row), and realigns the 32 bytes with four
+// funnel shifts.  Only groups that lie fully inside the interior are written here; the two ends of a row (reflected border,
+// the last partial interior group, row padding) are k_pyramid_base_edges' job, so no warp of this kernel diverges.
 // grid: (ceil(pitch / 512), ceil(rows / rowsPerCta), batch); block 256
 constexpr int RZ_ROWS = 64;  // minimum rows per CTA; launchers raise it (rowsPerCta) while the grid still fills the GPU
 __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plane, int w, int h, int pitch, int rows,
@@ -36,30 +39,17 @@ __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plan
                                                       long long stride, long long frameStride, int rowsPerCta) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int bx = blockIdx.x * 512 + lane * 16;
-    const bool inRow = bx < pitch;                         // (whole warps stay: the shuffles below need every lane)
     const int f = blockIdx.z;
-    const int px0 = bx - XOFF;                             // interior x of byte 0 of the group
-    const bool run = inRow && px0 >= 0 && px0 + 16 <= w;   // 16 consecutive interior source bytes
-    const bool nextRun = lane < 31 && px0 + 32 <= w && bx + 16 < pitch && px0 + 16 >= 0;  // lane + 1 loads the chunk after mine
-    const uint8_t* __restrict__ fbase = frames + (long long)f * frameStride;
+    const int px0 = bx - XOFF;                                   // interior x of byte 0 of the group (a multiple of 16)
+    const bool run = bx < pitch && px0 >= 0 && px0 + 16 <= w;    // 16 consecutive interior source bytes
+    const bool nextRun = lane < 31 && px0 + 16 >= 0 && px0 + 32 <= w;  // lane + 1 loads the chunk after mine
+    const uint8_t* __restrict__ fbase = frames + (long long)f * frameStride + px0;
     uint8_t* __restrict__ dbase = plane + (long long)f * planeStride + bx;
     const int rowEnd = min(blockIdx.y * rowsPerCta + rowsPerCta, rows);
-    int sx[16];
-    uint32_t validMask = 0;
-    if (inRow && !run) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) {
-            const int px = bx + j - PADL;
-            const bool valid = px >= 0 && px < w + 2 * EDGE;
-            validMask |= (valid ? 1u : 0u) << j;
-            sx[j] = valid ? reflect101(px - EDGE, w) : 0;
-        }
-    }
     for (int py = blockIdx.y * rowsPerCta + warp; py < rowEnd; py += 8) {
-        const uint8_t* __restrict__ src = fbase + (long long)reflect101(py - EDGE, h) * stride;
-        const uintptr_t a = reinterpret_cast<uintptr_t>(src + px0);
+        const uintptr_t a = reinterpret_cast<uintptr_t>(fbase + (long long)reflect101(py - EDGE, h) * stride);
         const uint4* c0 = reinterpret_cast<const uint4*>(a & ~(uintptr_t)15);
-        const uint32_t mis = (uint32_t)(a & 15);           // the same in every lane: px0 is a multiple of 16
+        const uint32_t mis = (uint32_t)(a & 15);  // the same in every lane
         uint4 A = make_uint4(0u, 0u, 0u, 0u);
         if (run) A = __ldg(c0);
         uint4 N;
@@ -67,26 +57,41 @@ __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plan
         N.y = __shfl_down_sync(0xffffffffu, A.y, 1);
         N.z = __shfl_down_sync(0xffffffffu, A.z, 1);
         N.w = __shfl_down_sync(0xffffffffu, A.w, 1);
+        if (!run) continue;
+        // the following chunk is read by this lane only when no neighbour has it, and only when it holds a needed byte
+        // (mis != 0), so no load passes the 16-byte chunk of the frame's last byte
+        if (!nextRun) N = mis ? __ldg(c0 + 1) : make_uint4(0u, 0u, 0u, 0u);
+        const uint32_t sh = (mis & 3u) * 8u;
         uint4 v;
-        if (run) {
-            // the following chunk is read by this lane only when no neighbour has it, and only when it holds a needed
-            // byte (mis != 0), so no load passes the 16-byte chunk of the frame's last byte
-            if (!nextRun) N = mis ? __ldg(c0 + 1) : make_uint4(0u, 0u, 0u, 0u);
-            const uint32_t sh = (mis & 3u) * 8u;
-            switch (mis >> 2) {
-                case 0: v = make_uint4(__funnelshift_r(A.x, A.y, sh), __funnelshift_r(A.y, A.z, sh), __funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh)); break;
-                case 1: v = make_uint4(__funnelshift_r(A.y, A.z, sh), __funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh)); break;
-                case 2: v = make_uint4(__funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh), __funnelshift_r(N.y, N.z, sh)); break;
-                default: v = make_uint4(__funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh), __funnelshift_r(N.y, N.z, sh), __funnelshift_r(N.z, N.w, sh)); break;
-            }
-        } else if (inRow) {
-            uint32_t q[4] = {0u, 0u, 0u, 0u};
-#pragma unroll
-            for (int j = 0; j < 16; ++j) q[j >> 2] |= (((validMask >> j) & 1u) ? (uint32_t)__ldg(src + sx[j]) : 0u) << (8 * (j & 3));
-            v = make_uint4(q[0], q[1], q[2], q[3]);
+        switch (mis >> 2) {
+            case 0: v = make_uint4(__funnelshift_r(A.x, A.y, sh), __funnelshift_r(A.y, A.z, sh), __funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh)); break;
+            case 1: v = make_uint4(__funnelshift_r(A.y, A.z, sh), __funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh)); break;
+            case 2: v = make_uint4(__funnelshift_r(A.z, A.w, sh), __funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh), __funnelshift_r(N.y, N.z, sh)); break;
+            default: v = make_uint4(__funnelshift_r(A.w, N.x, sh), __funnelshift_r(N.x, N.y, sh), __funnelshift_r(N.y, N.z, sh), __funnelshift_r(N.z, N.w, sh)); break;
         }
-        if (inRow) *reinterpret_cast<uint4*>(dbase + (long long)py * pitch) = v;
+        *reinterpret_cast<uint4*>(dbase + (long long)py * pitch) = v;
     }
+}
+
+// Level 0, row ends: one thread per (row, 16-byte group outside the fully interior range) gathers its bytes one by one at
+// the reflected coordinate (BORDER_REFLECT_101) and writes zeros into the row padding.  nEdge = groups per row it owns:
+// groups 0, 1 (left border) and the groups from the first not fully interior one to the end of the row.
+__global__ void __launch_bounds__(256) k_pyramid_base_edges(uint8_t* __restrict__ plane, int w, int h, int pitch, int rows,
+                                                            long long planeStride, const uint8_t* __restrict__ frames,
+                                                            long long stride, long long frameStride, int firstRight, int nEdge) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= rows * nEdge) return;
+    const int py = i / nEdge, e = i - py * nEdge;
+    const int bx = (e < 2 ? e : firstRight + (e - 2)) * 16;
+    const int f = blockIdx.y;
+    const uint8_t* __restrict__ src = frames + (long long)f * frameStride + (long long)reflect101(py - EDGE, h) * stride;
+    uint32_t q[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+        const int px = bx + j - PADL;
+        if (px >= 0 && px < w + 2 * EDGE) q[j >> 2] |= (uint32_t)__ldg(src + reflect101(px - EDGE, w)) << (8 * (j & 3));
+    }
+    *reinterpret_cast<uint4*>(plane + (long long)f * planeStride + (long long)py * pitch + bx) = make_uint4(q[0], q[1], q[2], q[3]);
 }
 
 // Resize: a CTA of 8 warps produces a 128-px x 64-row tile of the padded destination plane.  A thread owns 4
@@ -215,8 +220,14 @@ int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, s
     const LevelGeom& L = g.lv[0];
     const int gx = (L.pitch + 511) / 512, rpc = rows_per_cta(L.rows, gx, batch);
     dim3 grid(gx, (L.rows + rpc - 1) / rpc, batch);
-    k_pyramid_base<<<grid, 256, 0, s>>>(L.plane + (long long)g.f0 * L.planeStride, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride,
-                                          (long long)frameStride, rpc);
+    uint8_t* plane = L.plane + (long long)g.f0 * L.planeStride;
+    k_pyramid_base<<<grid, 256, 0, s>>>(plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride, (long long)frameStride, rpc);
+    count_launch();
+    // row ends: groups 0, 1 and everything from the first group that is not fully interior (interior x0 + 16 > w)
+    const int firstRight = std::max(2, XOFF / 16 + L.w / 16), nEdge = 2 + (L.pitch / 16 - firstRight);
+    dim3 egrid((L.rows * nEdge + 255) / 256, batch);
+    k_pyramid_base_edges<<<egrid, 256, 0, s>>>(plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride,
+                                                 (long long)frameStride, firstRight, nEdge);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -84,15 +84,53 @@ def test_level_sizes():
         assert [ox.level_size(l) for l in range(8)] == sizes
 
 
-def test_pattern_table():
+def _pattern_values():
     inc = os.path.join(os.path.dirname(GOLD), "..", "orb_slam_cuda_b200", "csrc", "orb_pattern_31.inc")
     vals = []
     for line in open(inc):
         if line.startswith("//"):
             continue
         vals += [int(t) for t in line.replace(",", " ").split()]
+    return vals
+
+
+PATTERN_SHA256 = "88df8ca875cc8db56799edd57bb914edad8acb2d48c202b7a464a575b55dbdb8"  # of ",".join(the 1024 integers)
+
+
+def test_pattern_table():
+    """All 1024 integers of bit_pattern_31_ (src/ORBextractor.cc:236-494): pinned by a SHA-256 everywhere, and re-parsed from the
+    reference source where /root/reference is mounted (comments and the stray VX_FAILURE token of :261 removed)."""
+    import hashlib
+    import re
+    vals = _pattern_values()
     assert len(vals) == 1024 and vals[:4] == [8, -3, 9, 5] and vals[-4:] == [-1, -6, 0, -11]
     assert max(abs(v) for v in vals) <= 13
+    assert hashlib.sha256(",".join(map(str, vals)).encode()).hexdigest() == PATTERN_SHA256
+    ref = "/root/reference/src/ORBextractor.cc"
+    if os.path.exists(ref):
+        body = "\n".join(open(ref).read().split("\n")[235:495])
+        body = re.sub(r"//.*", "", re.sub(r"/\*.*?\*/", "", body, flags=re.S))
+        toks = [int(t) for t in re.findall(r"-?\d+", body[body.index("{") + 1:body.rindex("}")])]
+        assert toks == vals
+
+
+def test_pattern_against_cv2_orb():
+    """An independent holder of the same table: cv2.ORB computes steered BRIEF with OpenCV's copy of bit_pattern_31_.  At angle 0
+    every one of the 512 test points is used unrotated, so equal descriptors pin the whole table and the comparison / bit order
+    against OpenCV 4.x.  (cv2.ORB 4.13 blurs its pyramid level in float — its descriptors equal ours on the rounded float blur and
+    differ in about 0.5 % of the bits on the 8-bit fixed-point GaussianBlur that ORB-SLAM2 calls itself, which test_oracle_cv2.py pins.)"""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(4)
+    img = cv2.GaussianBlur(rng.integers(0, 256, (240, 320), dtype=np.uint8), (5, 5), 1.5)
+    orb = cv2.ORB_create(nfeatures=100, scaleFactor=1.2, nlevels=1, edgeThreshold=31, patchSize=31, WTA_K=2)
+    pts = [(60.0, 70.0), (160.0, 120.0), (250.0, 200.0), (99.0, 181.0)]
+    kps = [cv2.KeyPoint(x, y, 31.0, 0.0, 1.0, 0) for x, y in pts]
+    kps, desc = orb.compute(img, kps)
+    assert len(kps) == len(pts)
+    blurred = np.clip(np.rint(cv2.GaussianBlur(img.astype(np.float32), (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)), 0, 255).astype(np.uint8)
+    for kp, d in zip(kps, desc):
+        ours = O.descriptor(blurred, int(kp.pt[0]), int(kp.pt[1]), 0.0)
+        assert np.array_equal(ours, d)
 
 
 def test_descriptor_distance_kat():
