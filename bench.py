@@ -68,6 +68,7 @@ def parse():
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames of the cpu_baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-match", action="store_true")
+    ap.add_argument("--keyframes", type=int, default=1024, help="keyframes of the all-vs-all leg (config 5 names 4096: 16x the time)")
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="profiling runs only: skip the host-buffer leg (the line then has no e2e)")
     ap.add_argument("--profile", action="store_true", help="profiling runs only: one warm-up and the timed steps, nothing else")
@@ -154,7 +155,7 @@ def cpu_extract_rate(workload: str, nframes: int, threads: int, min_secs: float 
     return done / secs, secs, done
 
 
-def match_leg(X, torch, dist, rank, world, stream, K):
+def match_leg(X, torch, dist, rank, world, stream, K, args_keyframes=1024):
     """Gmatch/s (descriptor pairs compared per second / 1e9) of the Hamming matchers, device resident, CUDA events on
     the launching stream: (a) 2000 x 2000 brute force best / second-best + TH_LOW / ratio test (config 4's inner loop),
     (b) all-vs-all keyframe matching sharded by query block, database all-gathered over NCCL when world > 1
@@ -179,18 +180,23 @@ def match_leg(X, torch, dist, rank, world, stream, K):
     e1.record()
     torch.cuda.synchronize()
     bf_ms = e0.elapsed_time(e1) / reps
-    # (b) all-vs-all: k_total keyframes x 2000 descriptors, query blocks per rank
-    k_total, n = 96, 2000
+    # (b) all-vs-all (config 5): k_total keyframes x 2000 descriptors, query block per rank, database all-gathered over NCCL
+    # inside liborbx.so (orbx_allpairs_sharded: own block first, chunked ncclAllGather overlapped with the scoring).
+    k_total, n = args_keyframes, 2000
     b, e = sharding.block_range(k_total, rank, world)
     rng = np.random.default_rng(77)
-    all_desc = rng.integers(0, 256, size=(k_total, n, 32), dtype=np.uint8)
-    local = torch.from_numpy(all_desc[b:e]).cuda()
-
-    def score_fn(qq, db, o):
-        m.match_allpairs_device(qq.data_ptr(), qq.shape[0], db.data_ptr(), db.shape[0], n, o.data_ptr(), stream=stream)
+    pool = rng.integers(0, 256, size=(64, n, 32), dtype=np.uint8)  # 64 distinct keyframes, every further one a row rotation + bit noise
+    def keyframe(i):
+        kf = np.roll(pool[i % 64], i // 64, axis=0)
+        if i >= 64:
+            kf = kf ^ (np.random.default_rng(i).random((n, 32)) < 0.02).astype(np.uint8)
+        return kf
+    local = torch.from_numpy(np.stack([keyframe(i) for i in range(b, e)]) if e > b else np.zeros((0, n, 32), np.uint8)).cuda()
+    comm = sharding.NcclComm(torch.device("cuda", torch.cuda.current_device()))
+    scores = torch.empty((e - b, k_total), dtype=torch.int32, device="cuda")
 
     def ap():
-        return sharding.allpairs_sharded(local, k_total, score_fn, chunks=4)
+        return sharding.allpairs_sharded_native(comm, local, k_total, 50, 0.6, chunks=4, stream=stream, scores=scores)
 
     ap()
     if dist is not None:
@@ -207,10 +213,38 @@ def match_leg(X, torch, dist, rank, world, stream, K):
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ap_ms = float(t[0])
+    # ---- outside the timed region: the sharded result is checked on every rank ----
+    # (1) a sample of query rows of this rank against the single-GPU kernel over the FULL database, built locally (every rank
+    #     can regenerate every keyframe), (2) on rank 0 a sample of entries against the CPU oracle's brute-force matcher
+    check = {"rows_vs_single_gpu": 0, "entries_vs_cpu_oracle": 0, "ok": True}
+    if e > b:
+        full = torch.from_numpy(np.stack([keyframe(i) for i in range(k_total)])).cuda()
+        rows = sorted(set([0, (e - b) // 2, e - b - 1]))
+        ref = torch.empty((len(rows), k_total), dtype=torch.int32, device="cuda")
+        m.match_allpairs_device(local[rows].contiguous().data_ptr(), len(rows), full.data_ptr(), k_total, n, ref.data_ptr(), stream=stream)
+        torch.cuda.synchronize()
+        check["rows_vs_single_gpu"] = len(rows)
+        check["ok"] = bool(torch.equal(ref, sc[rows]))
+        if rank == 0 and check["ok"]:
+            from oracle import oracle_lib as O  # the checker, outside the timed region
+            sc_h = sc.cpu().numpy()
+            for (qi, dj) in [(0, b), (0, (b + 64) % k_total), ((e - b) // 2, (b + (e - b) // 2 + 128) % k_total), (e - b - 1, 3 % k_total)]:
+                _, d1, d2, mt = O.match_bruteforce(keyframe(b + qi), keyframe(dj), 50, 0.6)
+                check["ok"] = check["ok"] and int((mt >= 0).sum()) == int(sc_h[qi, dj])
+                check["entries_vs_cpu_oracle"] += 1
+        del full
+    ok = torch.tensor([1 if check["ok"] else 0], dtype=torch.int32, device="cuda")
+    if dist is not None:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    check["ok"] = bool(int(ok[0]) == 1)
+    comm.destroy()
+    if not check["ok"]:
+        raise SystemExit("bench.py: the sharded all-vs-all scores differ from the single-GPU kernel / the CPU oracle")
     return {"bruteforce_2000x2000": {"gmatch_per_s": 2000 * 2000 / (bf_ms * 1e-3) / 1e9, "ms": bf_ms, "launches_per_call": 1},
             "allpairs": {"gmatch_per_s": float(k_total) * k_total * n * n / (ap_ms * 1e-3) / 1e9, "ms": ap_ms,
-                         "keyframes": k_total, "descriptors_per_keyframe": n, "sharding": "query block per rank, database all-gathered in 4 chunks",
-                         "allgather_bytes_per_rank": int(moved), "scaling": "strong"},
+                         "keyframes": k_total, "descriptors_per_keyframe": n,
+                         "sharding": "query block per rank; orbx_allpairs_sharded: own block first, database ncclAllGather'ed in 4 chunks on a second stream",
+                         "allgather_bytes_per_rank": int(moved), "scaling": "strong", "steps": K, "check": check},
             "unit": "Gmatch/s (descriptor pairs compared / s / 1e9)"}
 
 
@@ -540,7 +574,7 @@ def run_ours(args, emit=print):
                 assert np.array_equal(np.ascontiguousarray(hk_np[f, :n]).view(np.int32).reshape(n, 7), d_k[f, :n]), "keypoints differ"
                 assert np.array_equal(hd_np[f, :n], d_d[f, :n]), "descriptors differ"
 
-    match = None if args.no_match else match_leg(X, torch, dist, rank, world, stream, max(2, K // 2))
+    match = None if args.no_match else match_leg(X, torch, dist, rank, world, stream, 2, args.keyframes)
 
     t = torch.tensor([ms, e2e_s * 1e3, e2e_sync_s * 1e3], dtype=torch.float64, device="cuda")
     if dist is not None:
@@ -590,8 +624,12 @@ def run_ours(args, emit=print):
     }
     if match is not None:
         sm_hz = (clocks or {}).get("sm_mhz") or 1965.0
-        match["popc_bound_gmatch_per_s"] = 148 * 16 * sm_hz * 1e6 / 8 / 1e9 * world
-        match["popc_bound"] = "148 SMs x 16 POPC/clk/SM x SM clock / 8 POPC per pair (x N GPUs)"
+        # measured on this GPU (tools/pipe_rates.cu -> profiles/r02_pipe_rates.json): POPC 0.5, LOP3 2.0 warp instructions / clk / SM.
+        # The carry-save Hamming distance costs 4 POPC + 16 LOP3 + 3 min/max per descriptor pair: 8 clk of POPC pipe, 9.5 clk of ALU pipe.
+        match["popc_bound_gmatch_per_s"] = 148 * 0.5 * 32 * sm_hz * 1e6 / 4 / 1e9 * world
+        match["alu_bound_gmatch_per_s"] = 148 * 2.0 * 32 * sm_hz * 1e6 / 19 / 1e9 * world
+        match["popc_bound"] = ("148 SMs x 0.5 POPC warp-instructions/clk/SM (measured, profiles/r02_pipe_rates.json) x 32 lanes x SM clock / "
+                               "4 POPC per pair (x N GPUs); alu_bound: 2.0 LOP3-class warp-instructions/clk/SM / 19 per pair")
         line["match"] = match
     if world == 1 and not args.no_latency:
         line["latency"] = latency_leg(X, wl, w, h, args.workload, cpu=not args.no_cpu_baseline and world == 1)

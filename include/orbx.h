@@ -148,6 +148,17 @@ int orbx_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d_d,
 int orbx_match_allpairs_device(const uint8_t* d_q, int kq, const uint8_t* d_db, int kd, int n, int th, float ratio,
                                int* d_score, void* stream);
 
+/* The same workload over `world` GPUs, one process per GPU (BASELINE config 5; the reference is single-GPU):
+ * the k_total keyframes are split into contiguous blocks (block sizes differ by at most one, earlier ranks larger; rank r
+ * holds the descriptors of its block in d_local [k_local][n][32]) and every rank scores its block of QUERY keyframes against
+ * all k_total keyframes: d_scores [k_local][k_total].  The database is all-gathered over NCCL in `chunks` pieces on an
+ * internal stream; the rank's own block is scored while the first piece is in flight and every further piece while the
+ * next one arrives.  nccl_comm = the caller's ncclComm_t for these `world` ranks (ignored when world == 1); NCCL is resolved
+ * at run time from the library the process has loaded (libnccl.so.2, or ORBX_NCCL_LIB).  Asynchronous on `stream`.
+ * gathered_bytes (may be NULL) receives the bytes this rank received. */
+int orbx_allpairs_sharded(void* nccl_comm, int rank, int world, const uint8_t* d_local, int k_total, int n, int th, float ratio,
+                          int* d_scores, int chunks, void* stream, unsigned long long* gathered_bytes);
+
 /* SearchForInitialization (:405-520): frame-1 keypoints of octave 0 search a +-window box around prev_xy[i] in
  * frame 2 (Frame::GetFeaturesInArea over the 64x48 grid, src/Frame.cc:326-379), ratio test, one-to-one stealing,
  * rotation histogram.  bounds = {mnMinX, mnMaxX, mnMinY, mnMaxY}.  prev_xy (2*n1 floats) is updated in place like

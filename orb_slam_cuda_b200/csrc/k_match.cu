@@ -20,6 +20,26 @@ __device__ __forceinline__ int hamming256(const uint32_t (&a)[8], const uint4 b0
            __popc(a[5] ^ b1.y) + __popc(a[6] ^ b1.z) + __popc(a[7] ^ b1.w);
 }
 
+// The same distance with HALF the POPC instructions, for the throughput kernels.  POPC issues at 0.5 warp instructions / clk /
+// SM on B200 and LOP3 at 2 (tools/pipe_rates.cu, profiles/r02_pipe_rates.json), so 8 POPC per pair bound the plain form at
+// 16 clk per warp-pair.  Four carry-save adders (sum = x ^ y ^ z: LUT 0x96, carry = majority: LUT 0xE8) fold seven of the
+// eight XOR words into a ones, a twos and a fours plane: 4 POPC (8 clk on the POPC pipe) + 16 LOP3 (8 clk on the ALU pipe).
+template <int LUT>
+__device__ __forceinline__ uint32_t lop3m(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t r;
+    asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(r) : "r"(a), "r"(b), "r"(c), "n"(LUT));
+    return r;
+}
+__device__ __forceinline__ uint32_t hamming256_csa(const uint32_t (&a)[8], const uint4 b0, const uint4 b1) {
+    const uint32_t x0 = a[0] ^ b0.x, x1 = a[1] ^ b0.y, x2 = a[2] ^ b0.z, x3 = a[3] ^ b0.w;
+    const uint32_t x4 = a[4] ^ b1.x, x5 = a[5] ^ b1.y, x6 = a[6] ^ b1.z, x7 = a[7] ^ b1.w;
+    const uint32_t s1 = lop3m<0x96>(x0, x1, x2), c1 = lop3m<0xE8>(x0, x1, x2);
+    const uint32_t s2 = lop3m<0x96>(s1, x3, x4), c2 = lop3m<0xE8>(s1, x3, x4);
+    const uint32_t s3 = lop3m<0x96>(s2, x5, x6), c3 = lop3m<0xE8>(s2, x5, x6);
+    const uint32_t t = lop3m<0x96>(c1, c2, c3), f = lop3m<0xE8>(c1, c2, c3);
+    return (uint32_t)(__popc(s3) + __popc(x7)) + 2u * (uint32_t)__popc(t) + 4u * (uint32_t)__popc(f);
+}
+
 __global__ void k_hamming_pairs(const uint4* __restrict__ a, const uint4* __restrict__ b, int n, int* __restrict__ dist) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -49,8 +69,9 @@ __global__ void __launch_bounds__(BF_THREADS) k_bruteforce(const uint4* __restri
         const uint4 a0 = q[2 * qi], a1 = q[2 * qi + 1];
         a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
     }
-    uint32_t best = (256u << 22) | BF_NOIDX;
-    int second = 256;
+    // best and second are both kept as packed (distance << 22 | index) keys: the larger of two keys carries the larger
+    // distance, so second's distance field is the second smallest value of the multiset
+    uint32_t best = (256u << 22) | BF_NOIDX, second2 = (256u << 22) | BF_NOIDX;
     for (int t0 = begin; t0 < end; t0 += BF_TILE) {
         const int m = min(BF_TILE, end - t0);
         __syncthreads();
@@ -58,12 +79,12 @@ __global__ void __launch_bounds__(BF_THREADS) k_bruteforce(const uint4* __restri
         __syncthreads();
 #pragma unroll 4
         for (int j = 0; j < m; ++j) {
-            const int dist = hamming256(a, tile[2 * j], tile[2 * j + 1]);
-            const uint32_t cand = ((uint32_t)dist << 22) | (uint32_t)(t0 + j);
-            second = min(second, max(dist, (int)(best >> 22)));
+            const uint32_t cand = (hamming256_csa(a, tile[2 * j], tile[2 * j + 1]) << 22) + (uint32_t)(t0 + j);
+            second2 = min(second2, max(cand, best));
             best = min(best, cand);
         }
     }
+    int second = (int)(second2 >> 22);
     const int nsplit = gridDim.y;
     if (nsplit > 1) {
         if (qi < nq) partial[(size_t)blockIdx.y * nq + qi] = ((unsigned long long)best << 32) | (uint32_t)second;
@@ -130,19 +151,22 @@ int launch_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th
 // shared-memory traffic per pair is 32 B / AP_Q.  score[i][j] = number of queries whose best match passes the test.
 constexpr int AP_THREADS = 256, AP_Q = 4, AP_TILE = 256;
 
-__global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict__ q, const uint4* __restrict__ db, int n, int kd,
-                                                          int th, float ratio, int* __restrict__ score) {
+// colMap (may be null): database keyframe j goes to column colMap[j] of the score row (row pitch ldScore); a negative entry
+// skips the keyframe (padding of a gathered chunk, or a block that was scored already).
+__global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict__ q, const uint4* __restrict__ db, int n, int ldScore,
+                                                          const int* __restrict__ colMap, int th, float ratio, int* __restrict__ score) {
     __shared__ uint4 tile[AP_TILE * 2];
     __shared__ int total;
     const int j = blockIdx.x, i = blockIdx.y;
+    const int col = colMap ? colMap[j] : j;
+    if (col < 0) return;
     const uint4* __restrict__ qk = q + (size_t)i * n * 2;
     const uint4* __restrict__ dk = db + (size_t)j * n * 2;
     if (threadIdx.x == 0) total = 0;
     int accepted = 0;
     for (int q0 = 0; q0 < n; q0 += AP_THREADS * AP_Q) {  // query chunk of 1024
         uint32_t a[AP_Q][8];
-        uint32_t best[AP_Q];
-        int second[AP_Q];
+        uint32_t best[AP_Q], second[AP_Q];  // packed (distance << 22 | index) keys, see k_bruteforce
 #pragma unroll
         for (int k = 0; k < AP_Q; ++k) {
             const int qi = q0 + k * AP_THREADS + threadIdx.x;
@@ -150,8 +174,7 @@ __global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict
             if (qi < n) { a0 = qk[2 * qi]; a1 = qk[2 * qi + 1]; }
             a[k][0] = a0.x; a[k][1] = a0.y; a[k][2] = a0.z; a[k][3] = a0.w;
             a[k][4] = a1.x; a[k][5] = a1.y; a[k][6] = a1.z; a[k][7] = a1.w;
-            best[k] = (256u << 22) | BF_NOIDX;
-            second[k] = 256;
+            best[k] = second[k] = (256u << 22) | BF_NOIDX;
         }
         for (int t0 = 0; t0 < n; t0 += AP_TILE) {
             const int m = min(AP_TILE, n - t0);
@@ -163,9 +186,9 @@ __global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict
                 const uint4 b0 = tile[2 * jj], b1 = tile[2 * jj + 1];
 #pragma unroll
                 for (int k = 0; k < AP_Q; ++k) {
-                    const int dist = hamming256(a[k], b0, b1);
-                    second[k] = min(second[k], max(dist, (int)(best[k] >> 22)));
-                    best[k] = min(best[k], ((uint32_t)dist << 22) | (uint32_t)(t0 + jj));
+                    const uint32_t cand = (hamming256_csa(a[k], b0, b1) << 22) + (uint32_t)(t0 + jj);
+                    second[k] = min(second[k], max(cand, best[k]));
+                    best[k] = min(best[k], cand);
                 }
             }
         }
@@ -173,7 +196,7 @@ __global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict
         for (int k = 0; k < AP_Q; ++k) {
             const int qi = q0 + k * AP_THREADS + threadIdx.x;
             const int b1 = (int)(best[k] >> 22);
-            if (qi < n && b1 <= th && (float)b1 < __fmul_rn(ratio, (float)second[k])) ++accepted;
+            if (qi < n && b1 <= th && (float)b1 < __fmul_rn(ratio, (float)(second[k] >> 22))) ++accepted;
         }
     }
 #pragma unroll
@@ -181,7 +204,7 @@ __global__ void __launch_bounds__(AP_THREADS) k_allpairs(const uint4* __restrict
     __syncthreads();
     if ((threadIdx.x & 31) == 0 && accepted) atomicAdd(&total, accepted);
     __syncthreads();
-    if (threadIdx.x == 0) score[(size_t)i * kd + j] = total;
+    if (threadIdx.x == 0) score[(size_t)i * ldScore + col] = total;
 }
 
 // ---- MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:246-312) ---------------------------------------------------
@@ -224,10 +247,11 @@ int launch_distinctive(int nPoints, const int* start, const uint8_t* desc, int* 
     return ORBX_OK;
 }
 
-int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score, cudaStream_t s) {
+int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score, int ldScore,
+                    const int* colMap, cudaStream_t s) {
     if (kq <= 0 || kd <= 0) return ORBX_OK;
-    k_allpairs<<<dim3(kd, kq), AP_THREADS, 0, s>>>(reinterpret_cast<const uint4*>(q), reinterpret_cast<const uint4*>(db), n, kd, th,
-                                                   ratio, score);
+    k_allpairs<<<dim3(kd, kq), AP_THREADS, 0, s>>>(reinterpret_cast<const uint4*>(q), reinterpret_cast<const uint4*>(db), n, ldScore,
+                                                   colMap, th, ratio, score);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

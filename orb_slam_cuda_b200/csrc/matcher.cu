@@ -4,6 +4,8 @@
 // per-thread device workspace (a stream and grow-only scratch per host thread: ORBmatcher objects are stack-local
 // on three threads in the reference, src/Tracking.cc:671, src/LocalMapping.cc:248, src/LoopClosing.cc:278) and the
 // host <-> device copies of the "host buffer" entry points.  There is no CPU path.
+#include <dlfcn.h>
+
 #include <algorithm>
 #include <cstring>
 #include <vector>
@@ -19,6 +21,15 @@ struct Workspace {  // one per host thread and device
     cudaStream_t stream = nullptr;
     DevBuf a, b, c, d, e, f, g, h, out0, out1, out2, out3, status, partial, counters;
     PinBuf pin;
+    // brute force: the split-K partials and arrival counters are shared by every call of this thread; a call on another
+    // stream waits for the previous one (bfDone) instead of racing it
+    cudaEvent_t bfDone = nullptr;
+    cudaStream_t bfStream = nullptr;
+    // sharded all-vs-all: communication stream, gathered database, column maps, events (one per chunk + "previous call done")
+    cudaStream_t commStream = nullptr;
+    DevBuf gathered, pad, colMaps;
+    std::vector<cudaEvent_t> apEv;
+    cudaEvent_t apDone = nullptr;
     ~Workspace() {
         // device memory is reclaimed at process exit; freeing here could run after the CUDA runtime is torn down
     }
@@ -85,12 +96,20 @@ int orbx_match_bruteforce_device(const uint8_t* dq, int nq, const uint8_t* dd, i
     int rc = workspace(&w);
     if (rc) return rc;
     if ((rc = w->partial.ensure(bruteforce_scratch_bytes(nq, nd)))) return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : w->stream;
+    if (!w->bfDone) ORBX_CUDA(cudaEventCreateWithFlags(&w->bfDone, cudaEventDisableTiming));
+    if (w->bfStream && w->bfStream != s) ORBX_CUDA(cudaStreamWaitEvent(s, w->bfDone, 0));  // the scratch is still the previous call's
     if (bruteforce_counter_bytes(nq) > w->counters.bytes) {  // per-query-block arrival counters: zero once, the kernel leaves them zero
+        ORBX_CUDA(cudaStreamSynchronize(s));                 // (the old, smaller array is freed below)
         if ((rc = w->counters.ensure(std::max<size_t>(bruteforce_counter_bytes(nq), 4096)))) return rc;
-        ORBX_CUDA(cudaMemset(w->counters.p, 0, w->counters.bytes));
+        ORBX_CUDA(cudaMemsetAsync(w->counters.p, 0, w->counters.bytes, s));  // on the launch stream: ordered before the kernel
     }
-    return launch_bruteforce(dq, nq, dd, nd, th, ratio, idx, d1, d2, match, w->partial.as<unsigned long long>(),
-                             w->counters.as<unsigned int>(), stream ? (cudaStream_t)stream : w->stream);
+    rc = launch_bruteforce(dq, nq, dd, nd, th, ratio, idx, d1, d2, match, w->partial.as<unsigned long long>(),
+                           w->counters.as<unsigned int>(), s);
+    if (rc) return rc;
+    ORBX_CUDA(cudaEventRecord(w->bfDone, s));
+    w->bfStream = s;
+    return ORBX_OK;
 }
 
 int orbx_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th, float ratio, int* idx, int* d1, int* d2,
@@ -125,7 +144,143 @@ int orbx_match_allpairs_device(const uint8_t* dq, int kq, const uint8_t* ddb, in
     Workspace* w;
     int rc = workspace(&w);
     if (rc) return rc;
-    return launch_allpairs(dq, kq, ddb, kd, n, th, ratio, dscore, stream ? (cudaStream_t)stream : w->stream);
+    return launch_allpairs(dq, kq, ddb, kd, n, th, ratio, dscore, kd, nullptr, stream ? (cudaStream_t)stream : w->stream);
+}
+
+// ---- all-vs-all sharded by query block, database all-gathered over NCCL (BASELINE config 5) -----------------
+// NCCL is reached through dlsym: liborbx.so has no link-time dependency on it, and the communicator handed in belongs to
+// the NCCL the caller's process already holds (ORBX_NCCL_LIB names another one).
+namespace {
+typedef int (*NcclAllGatherFn)(const void*, void*, size_t, int, void*, cudaStream_t);
+typedef const char* (*NcclErrFn)(int);
+struct NcclApi {
+    NcclAllGatherFn allGather = nullptr;
+    NcclErrFn errString = nullptr;
+};
+const NcclApi* nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void* h = nullptr;
+        if (const char* e = getenv("ORBX_NCCL_LIB")) h = dlopen(e, RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);  // the copy the process has loaded already (e.g. torch's)
+        if (!h) h = dlopen("libnccl.so.2", RTLD_NOW);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW);
+        if (h) {
+            api.allGather = (NcclAllGatherFn)dlsym(h, "ncclAllGather");
+            api.errString = (NcclErrFn)dlsym(h, "ncclGetErrorString");
+        }
+    }
+    return api.allGather ? &api : nullptr;
+}
+void block_range(int n, int rank, int world, int* b, int* e) {  // contiguous blocks, sizes differ by at most one, earlier ranks larger
+    const int base = n / world, rem = n % world;
+    *b = rank * base + std::min(rank, rem);
+    *e = *b + base + (rank < rem ? 1 : 0);
+}
+}  // namespace
+
+int orbx_allpairs_sharded(void* nccl_comm, int rank, int world, const uint8_t* d_local, int k_total, int n, int th, float ratio,
+                          int* d_scores, int chunks, void* stream, unsigned long long* gathered_bytes) {
+    if (world < 1 || rank < 0 || rank >= world || k_total < 0 || n < 1 || n > 0x3FFFFE || (k_total > 0 && !d_scores)) {
+        set_error("orbx_allpairs_sharded: bad argument");
+        return ORBX_E_INVALID;
+    }
+    if (gathered_bytes) *gathered_bytes = 0;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    cudaStream_t s = stream ? (cudaStream_t)stream : w->stream;
+    int begin, end;
+    block_range(k_total, rank, world, &begin, &end);
+    const int kLocal = end - begin;
+    if (kLocal > 0 && !d_local) { set_error("orbx_allpairs_sharded: this rank owns %d keyframes but d_local is null", kLocal); return ORBX_E_INVALID; }
+    // the rank's own block needs no communication: it is scored first, while the first chunk of the gather is in flight
+    if (kLocal > 0 && (rc = launch_allpairs(d_local, kLocal, d_local, kLocal, n, th, ratio, d_scores + begin, k_total, nullptr, s))) return rc;
+    if (world == 1) return ORBX_OK;
+    const NcclApi* nccl = nccl_api();
+    if (!nccl || !nccl_comm) {
+        set_error("orbx_allpairs_sharded: %s", nccl ? "null NCCL communicator" : "libnccl.so.2 could not be loaded (set ORBX_NCCL_LIB)");
+        return ORBX_E_INVALID;
+    }
+    int b0, kMax;
+    block_range(k_total, 0, world, &b0, &kMax);  // rank 0 owns the largest block
+    chunks = std::max(1, std::min(chunks > 0 ? chunks : 4, std::max(kMax, 1)));
+    const int step = (kMax + chunks - 1) / chunks;
+    const size_t kfBytes = (size_t)n * 32;
+    if (!w->commStream) ORBX_CUDA(cudaStreamCreateWithFlags(&w->commStream, cudaStreamNonBlocking));
+    if (!w->apDone) ORBX_CUDA(cudaEventCreateWithFlags(&w->apDone, cudaEventDisableTiming));
+    while ((int)w->apEv.size() < chunks + 1) {
+        cudaEvent_t e;
+        ORBX_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        w->apEv.push_back(e);
+    }
+    // gathered database: chunk c holds [world][width_c] keyframes; every chunk is padded to the same width on every rank
+    if ((size_t)world * kMax * kfBytes > w->gathered.bytes || (size_t)step * kfBytes > w->pad.bytes ||
+        (size_t)world * kMax * sizeof(int) > w->colMaps.bytes) {
+        ORBX_CUDA(cudaStreamSynchronize(w->commStream));
+        ORBX_CUDA(cudaStreamSynchronize(s));
+        if ((rc = w->gathered.ensure((size_t)world * kMax * kfBytes)) || (rc = w->pad.ensure((size_t)step * kfBytes)) ||
+            (rc = w->colMaps.ensure((size_t)world * kMax * sizeof(int))))
+            return rc;
+    }
+    // column maps of every chunk: gathered keyframe (src, i) of chunk [c0, c1) is global keyframe begin(src) + c0 + i; the
+    // rank's own block (scored above) and the padding are skipped
+    std::vector<int> maps((size_t)world * kMax, -1);
+    size_t mapOff = 0;
+    for (int c0 = 0; c0 < kMax; c0 += step) {
+        const int width = std::min(step, kMax - c0);
+        for (int src = 0; src < world; ++src) {
+            int sb, se;
+            block_range(k_total, src, world, &sb, &se);
+            for (int i = 0; i < width; ++i)
+                maps[mapOff + (size_t)src * width + i] = (src != rank && sb + c0 + i < se) ? sb + c0 + i : -1;
+        }
+        mapOff += (size_t)world * width;
+    }
+    ORBX_CUDA(cudaMemcpyAsync(w->colMaps.p, maps.data(), maps.size() * sizeof(int), cudaMemcpyHostToDevice, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));  // `maps` is pageable host memory of this call (a few KB; the scoring takes seconds)
+    // the previous call's kernels may still read the gathered database; d_local must be complete before it is sent
+    ORBX_CUDA(cudaEventRecord(w->apEv[chunks], s));
+    ORBX_CUDA(cudaStreamWaitEvent(w->commStream, w->apEv[chunks], 0));
+    ORBX_CUDA(cudaStreamWaitEvent(w->commStream, w->apDone, 0));
+    uint8_t* recv = w->gathered.as<uint8_t>();
+    size_t recvOff = 0;
+    int ci = 0;
+    for (int c0 = 0; c0 < kMax; c0 += step, ++ci) {  // every chunk's all-gather is issued up front; they complete in order
+        const int width = std::min(step, kMax - c0);
+        const uint8_t* send = d_local + (size_t)c0 * kfBytes;
+        if (c0 + width > kLocal) {  // this rank's block is shorter than the chunk: send a zero-padded copy
+            ORBX_CUDA(cudaMemsetAsync(w->pad.p, 0, (size_t)width * kfBytes, w->commStream));
+            if (kLocal > c0)
+                ORBX_CUDA(cudaMemcpyAsync(w->pad.p, d_local + (size_t)c0 * kfBytes, (size_t)(kLocal - c0) * kfBytes, cudaMemcpyDeviceToDevice,
+                                          w->commStream));
+            send = w->pad.as<uint8_t>();
+        }
+        const int nr = nccl->allGather(send, recv + recvOff, (size_t)width * kfBytes, 1 /* ncclUint8 */, nccl_comm, w->commStream);
+        if (nr != 0) {
+            set_error("ncclAllGather failed: %s", nccl->errString ? nccl->errString(nr) : "?");
+            return ORBX_E_CUDA;
+        }
+        ORBX_CUDA(cudaEventRecord(w->apEv[ci], w->commStream));
+        recvOff += (size_t)world * width * kfBytes;
+        if (gathered_bytes) *gathered_bytes += (unsigned long long)world * width * kfBytes;
+    }
+    recvOff = 0;
+    mapOff = 0;
+    ci = 0;
+    for (int c0 = 0; c0 < kMax; c0 += step, ++ci) {  // one scoring launch per landed chunk over the keyframes of every source rank
+        const int width = std::min(step, kMax - c0);
+        ORBX_CUDA(cudaStreamWaitEvent(s, w->apEv[ci], 0));
+        if (kLocal > 0 && (rc = launch_allpairs(d_local, kLocal, recv + recvOff, world * width, n, th, ratio, d_scores, k_total,
+                                                w->colMaps.as<int>() + mapOff, s)))
+            return rc;
+        recvOff += (size_t)world * width * kfBytes;
+        mapOff += (size_t)world * width;
+    }
+    ORBX_CUDA(cudaEventRecord(w->apDone, s));
+    return ORBX_OK;
 }
 
 int orbx_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_t* desc1, const orbx_keypoint* k2, int n2,

@@ -198,8 +198,9 @@ int launch_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, int th
                       int* match, unsigned long long* dPartial, unsigned int* dCounters, cudaStream_t s);
 size_t bruteforce_scratch_bytes(int nq, int nd);
 size_t bruteforce_counter_bytes(int nq);
-int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score,
-                    cudaStream_t s);
+// score[i * ldScore + (colMap ? colMap[j] : j)]; colMap[j] < 0 skips database keyframe j
+int launch_allpairs(const uint8_t* q, int kq, const uint8_t* db, int kd, int n, int th, float ratio, int* score, int ldScore,
+                    const int* colMap, cudaStream_t s);
 
 // candCnt[n] followed (16-byte aligned) by key[n][8] and idx[n][8] (uint32): see resolve_common.cuh
 inline size_t resolve_aux_bytes(int n) { return ((size_t)n + 3) / 4 * 16 + (size_t)n * 64; }

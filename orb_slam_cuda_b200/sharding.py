@@ -108,6 +108,70 @@ def allpairs_sharded(local_desc: torch.Tensor, k_total: int,
     return scores, moved
 
 
+class NcclComm:
+    """An ncclComm_t of this process group's ranks for the native entry point orbx_allpairs_sharded (the C ABI takes the
+    communicator as a plain pointer; torch.distributed keeps its own private).  Created through ctypes on the NCCL library the
+    process has loaded already — the same one liborbx.so resolves at run time — with the unique id broadcast over
+    torch.distributed.  One process per GPU; plumbing only."""
+
+    def __init__(self, device: torch.device, group: Optional[dist.ProcessGroup] = None):
+        import ctypes as C
+        self._C = C
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.comm = C.c_void_p()
+        self._lib = None
+        if self.world == 1:
+            return
+
+        class UniqueId(C.Structure):
+            _fields_ = [("internal", C.c_byte * 128)]
+
+        self._lib = C.CDLL("libnccl.so.2")  # resolves to the already loaded copy (torch's)
+        uid = UniqueId()
+        if self.rank == 0:
+            self._check(self._lib.ncclGetUniqueId(C.byref(uid)))
+        t = torch.frombuffer(bytearray(bytes(uid)), dtype=torch.uint8).to(device)
+        dist.broadcast(t, src=0, group=group)
+        C.memmove(C.byref(uid), bytes(t.cpu().numpy().tobytes()), 128)
+        self._lib.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, UniqueId, C.c_int]
+        torch.cuda.set_device(device)
+        self._check(self._lib.ncclCommInitRank(C.byref(self.comm), self.world, uid, self.rank))
+
+    def _check(self, rc):
+        if rc != 0:
+            self._lib.ncclGetErrorString.restype = self._C.c_char_p
+            raise RuntimeError("NCCL: " + self._lib.ncclGetErrorString(rc).decode())
+
+    def destroy(self):
+        if self._lib is not None and self.comm:
+            self._lib.ncclCommDestroy.argtypes = [self._C.c_void_p]
+            self._lib.ncclCommDestroy(self.comm)
+            self.comm = self._C.c_void_p()
+
+
+def allpairs_sharded_native(comm: NcclComm, local_desc: torch.Tensor, k_total: int, th: int = 50, ratio: float = 0.6, chunks: int = 4,
+                            stream: int = 0, scores: Optional[torch.Tensor] = None):
+    """orbx_allpairs_sharded (include/orbx.h): the whole sharded workload — own block first, chunked ncclAllGather on an internal
+    stream, one scoring launch per landed chunk — inside liborbx.so.  Returns (scores int32 [k_local, k_total], gathered bytes);
+    asynchronous on `stream` (0 = the library's own stream: synchronise the device before reading)."""
+    import ctypes as C
+    from . import lib, _check, _p
+    begin, end = block_range(k_total, comm.rank, comm.world)
+    if local_desc.shape[0] != end - begin:
+        raise ValueError(f"rank {comm.rank} owns keyframes [{begin}, {end}) but got {local_desc.shape[0]} descriptor sets")
+    n = local_desc.shape[1]
+    if scores is None:
+        scores = torch.empty((end - begin, k_total), dtype=torch.int32, device=local_desc.device)
+    moved = C.c_ulonglong(0)
+    f = lib().orbx_allpairs_sharded
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_int, C.c_void_p,
+                  C.POINTER(C.c_ulonglong)]
+    _check(f(comm.comm, comm.rank, comm.world, _p(local_desc.data_ptr()), k_total, n, th, ratio, _p(scores.data_ptr()), chunks,
+             _p(stream) if stream else None, C.byref(moved)))
+    return scores, int(moved.value)
+
+
 def frames_for_rank(n_frames: int, rank: int, world: int) -> range:
     """Frame indices of an offline sequence extracted by `rank` (contiguous block, no collective)."""
     b, e = block_range(n_frames, rank, world)

@@ -3,6 +3,8 @@ SearchForInitialization, ComputeStereoMatches, all-vs-all keyframe scoring.
 
 Bars (BASELINE.json north_star): match indices and distances bit-exact; the float outputs of the stereo matcher
 (mvuRight, mvDepth) are compared bit for bit as well (tolerance 0)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -165,3 +167,36 @@ def test_allpairs_scores():
     torch.cuda.synchronize()
     assert np.array_equal(score.cpu().numpy(), want)
     assert want.max() > 50
+
+
+def test_allpairs_sharded_entry_single_rank():
+    """orbx_allpairs_sharded with world = 1 (no communicator) is the plain all-vs-all kernel; the column-mapped form of the
+    kernel (strided score rows) is what the multi-GPU path launches — tools/multi_gpu_check.py covers world > 1."""
+    import torch
+    from orb_slam_cuda_b200 import sharding
+    rng = np.random.default_rng(5)
+    k, n = 9, 700
+    base = rng.integers(0, 256, size=(3, n, 32), dtype=np.uint8)
+    desc = np.stack([np.roll(base[i % 3], i, axis=0) ^ (rng.random((n, 32)) < 0.02).astype(np.uint8) for i in range(k)])
+    d = torch.from_numpy(desc).cuda()
+    want = torch.empty((k, k), dtype=torch.int32, device="cuda")
+    m = X.ORBmatcher(0.6, True)
+    m.match_allpairs_device(d.data_ptr(), k, d.data_ptr(), k, n, want.data_ptr())
+    comm = sharding.NcclComm(torch.device("cuda", 0))
+    got, moved = sharding.allpairs_sharded_native(comm, d, k)
+    torch.cuda.synchronize()
+    assert moved == 0 and torch.equal(got, want) and int((want > 0).sum()) >= k
+    for qi, dj in [(0, 0), (4, 7), (8, 2)]:
+        _, _, _, mt = O.match_bruteforce(desc[qi], desc[dj], 50, 0.6)
+        assert int((mt >= 0).sum()) == int(want[qi, dj])
+
+
+def test_allpairs_sharded_multi_gpu():
+    """world = 2 under torchrun when the box has two GPUs (the 1-GPU box skips; tools/gpu_run.sh multi runs it on N GPUs)."""
+    import subprocess, sys, torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29533", os.path.join(root, "tools", "multi_gpu_check.py")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]

@@ -54,6 +54,8 @@ ncu)  # ncu KERNEL_REGEX TAG SKIP COUNT [bench args]: --set full with source of 
   ;;
 multi)
   n=$1
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29512 tools/multi_gpu_check.py \
+    > gpurun_out/multi_check_n$n.json 2> gpurun_out/multi_check_n$n.err; echo "check rc=$?"; cat gpurun_out/multi_check_n$n.json; tail -3 gpurun_out/multi_check_n$n.err
   python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n --steps 10 --warmup 3 \
     > gpurun_out/bench_n$n.json 2> gpurun_out/bench_n$n.err; echo "rc=$?"; cat gpurun_out/bench_n$n.json; tail -3 gpurun_out/bench_n$n.err
   ;;
