@@ -183,7 +183,7 @@ void block_range(int n, int rank, int world, int* b, int* e) {  // contiguous bl
 
 int orbx_allpairs_sharded(void* nccl_comm, int rank, int world, const uint8_t* d_local, int k_total, int n, int th, float ratio,
                           int* d_scores, int chunks, void* stream, unsigned long long* gathered_bytes) {
-    if (world < 1 || rank < 0 || rank >= world || k_total < 0 || n < 1 || n > 0x3FFFFE || (k_total > 0 && !d_scores)) {
+    if (world < 1 || rank < 0 || rank >= world || k_total < 0 || n < 1 || n > 0x3FFFFE) {
         set_error("orbx_allpairs_sharded: bad argument");
         return ORBX_E_INVALID;
     }
@@ -195,7 +195,10 @@ int orbx_allpairs_sharded(void* nccl_comm, int rank, int world, const uint8_t* d
     int begin, end;
     block_range(k_total, rank, world, &begin, &end);
     const int kLocal = end - begin;
-    if (kLocal > 0 && !d_local) { set_error("orbx_allpairs_sharded: this rank owns %d keyframes but d_local is null", kLocal); return ORBX_E_INVALID; }
+    if (kLocal > 0 && (!d_local || !d_scores)) {  // a rank with an empty block still takes part in the gather
+        set_error("orbx_allpairs_sharded: this rank owns %d keyframes but d_local / d_scores is null", kLocal);
+        return ORBX_E_INVALID;
+    }
     // the rank's own block needs no communication: it is scored first, while the first chunk of the gather is in flight
     if (kLocal > 0 && (rc = launch_allpairs(d_local, kLocal, d_local, kLocal, n, th, ratio, d_scores + begin, k_total, nullptr, s))) return rc;
     if (world == 1) return ORBX_OK;

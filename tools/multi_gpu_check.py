@@ -23,6 +23,10 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     m = X.ORBmatcher(0.6, True)
     comm = sharding.NcclComm(torch.device("cuda", local))
+    # a real (non-default) stream for the torch-side work: a stream argument of 0 means "the library's own stream" in the C ABI, which
+    # is not ordered with torch's default stream
+    tstream = torch.cuda.Stream()
+    torch.cuda.set_stream(tstream)
     results = []
     ok_all = True
     for k_total, n, chunks in [(37, 300, 4), (world * 6, 500, 3), (world - 1 if world > 1 else 1, 200, 2), (64, 2000, 1), (5 * world + 3, 257, 8)]:
