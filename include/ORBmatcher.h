@@ -6,9 +6,9 @@
 // SearchForInitialization and ComputeStereoMatches are templates over the frame type so that they bind to the
 // reference's ORB_SLAM2::Frame (its public members mvKeysUn, mDescriptors, mnMinX ... are used exactly as
 // src/ORBmatcher.cc does) without this repository carrying Frame.h.  SearchByProjection (all four overloads) and SearchByBoW
-// (both overloads), SearchForTriangulation and SearchBySim3 bind the same way to Frame / KeyFrame / MapPoint.  The two Fuse overloads
-// (their candidate loops are orbx_fuse_match; the map surgery around them is pointer work) are SURVEY.md §8f "next" rows and stay in the reference's
-// src/ORBmatcher.cc.
+// (both overloads), SearchForTriangulation, SearchBySim3 and Fuse (both overloads) bind the same way to Frame / KeyFrame / MapPoint.
+// In Fuse the projection tests and the candidate loops of ALL map points run first (one orbx_fuse_match call); the map surgery
+// (Replace / AddObservation / AddMapPoint: pointer work whose order matters) then runs point by point in the reference's order.
 //
 // Every call here runs on the device; there is no CPU implementation behind it (errors throw std::runtime_error).
 // DescriptorDistance on ONE pair is a kernel launch plus two small copies: callers with many pairs should use
@@ -308,13 +308,14 @@ public:
             if (pMP->isBad() || spAlreadyFound.count(pMP)) continue;
             const cv::Mat p3Dw = pMP->GetWorldPos();
             const cv::Mat Pn = pMP->GetNormal();
-            float pc[3], dist, podotpn;
+            float pc[3], dist;
+            double podotpn;  // the reference compares the double PO.dot(Pn) with 0.5*dist
 #if ORBX_HAVE_OPENCV
             const cv::Mat p3Dc = Rcw * p3Dw + tcw;
             for (int c = 0; c < 3; ++c) pc[c] = p3Dc.at<float>(c);
             const cv::Mat PO = p3Dw - Ow;
             dist = (float)cv::norm(PO);
-            podotpn = (float)PO.dot(Pn);
+            podotpn = PO.dot(Pn);
 #else
             double ss = 0, dp = 0;
             for (int r = 0; r < 3; ++r) {
@@ -325,7 +326,7 @@ public:
                 dp += (double)po * Pn.template at<float>(r, 0);
             }
             dist = (float)std::sqrt(ss);
-            podotpn = (float)dp;
+            podotpn = dp;
 #endif
             if (pc[2] < 0.0) continue;                   // depth must be positive (:333-334)
             const float invz = 1 / pc[2];
@@ -538,6 +539,84 @@ public:
         return nFound;
     }
 
+
+    // Project MapPoints into KeyFrame and search for duplicated MapPoints (LocalMapping::SearchInNeighbors, src/LocalMapping.cc:519ff);
+    // src/ORBmatcher.cc:825-975.  KeyFrame members read: GetRotation(), GetTranslation(), GetCameraCenter(), fx, fy, cx, cy, mbf,
+    // IsInImage(), mvScaleFactors, mvInvLevelSigma2, mvKeysUn, mvuRight, mDescriptors, mnMinX..mnMaxY, GetMapPoint(), AddMapPoint();
+    // MapPoint: isBad(), IsInKeyFrame(), GetWorldPos(), GetMin/MaxDistanceInvariance(), GetNormal(), PredictScale(), GetDescriptor(),
+    // Observations(), Replace(), AddObservation().  The candidate loop of a point (:886-945) reads nothing the surgery of earlier
+    // points changes, so all candidate loops run first; `isBad() || IsInKeyFrame(pKF)` (:849), which the surgery DOES change (a
+    // point listed twice, a point replaced on the way), is evaluated in the surgery loop, in the reference's order.
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, const std::vector<MapPointT*>& vpMapPoints, const float th = 3.0) {
+        const int n1 = (int)vpMapPoints.size(), n2 = (int)pKF->mvKeysUn.size();
+        if (n1 == 0 || n2 == 0) return 0;
+        float R[9], t[3], Ow[3];
+        mat3(pKF->GetRotation(), R);
+        vec3(pKF->GetTranslation(), t);
+        vec3(pKF->GetCameraCenter(), Ow);
+        FuseCandidates c;
+        project_for_fuse(pKF, R, t, Ow, vpMapPoints, th, pKF->mbf, true, c);
+        fuse_candidates(pKF, c, true, "Fuse");
+        int nFused = 0;
+        for (int i = 0; i < n1; i++) {
+            MapPointT* pMP = vpMapPoints[i];
+            if (!pMP) continue;
+            if (pMP->isBad() || pMP->IsInKeyFrame(pKF)) continue;
+            if (!c.valid[i] || c.bestIdx[i] < 0) continue;
+            if (c.bestDist[i] <= TH_LOW) {  // if there is already a MapPoint replace, otherwise add a new measurement (:947-970)
+                const int bestIdx = c.bestIdx[i];
+                MapPointT* pMPinKF = pKF->GetMapPoint(bestIdx);
+                if (pMPinKF) {
+                    if (!pMPinKF->isBad()) {
+                        if (pMPinKF->Observations() > pMP->Observations()) pMP->Replace(pMPinKF);
+                        else pMPinKF->Replace(pMP);
+                    }
+                } else {
+                    pMP->AddObservation(pKF, bestIdx);
+                    pKF->AddMapPoint(pMP, bestIdx);
+                }
+                nFused++;
+            }
+        }
+        return nFused;
+    }
+
+    // Project MapPoints into KeyFrame using a given Sim3 and search for duplicated MapPoints (LoopClosing::SearchAndFuse,
+    // src/LoopClosing.cc:644); src/ORBmatcher.cc:977-1100.  Reads GetMapPoints() in addition; no chi-square gate, no Replace: a
+    // keypoint that already holds a good point is reported through vpReplacePoint.
+    template <class KeyFrameT, class MapPointT>
+    int Fuse(KeyFrameT* pKF, cv::Mat Scw, const std::vector<MapPointT*>& vpPoints, float th, std::vector<MapPointT*>& vpReplacePoint) {
+        const int n1 = (int)vpPoints.size(), n2 = (int)pKF->mvKeysUn.size();
+        if (n1 == 0 || n2 == 0) return 0;
+        float R[9], t[3], Ow[3];
+        decompose_sim3(Scw, R, t, Ow);
+        const std::set<MapPointT*> spAlreadyFound = pKF->GetMapPoints();  // fixed for the whole call (:993)
+        std::vector<MapPointT*> pts(vpPoints);
+        for (int i = 0; i < n1; ++i)
+            if (pts[i] && (pts[i]->isBad() || spAlreadyFound.count(pts[i]))) pts[i] = nullptr;  // :1005-1006 (nothing in this overload changes it)
+        FuseCandidates c;
+        project_for_fuse(pKF, R, t, Ow, pts, th, 0.f, false, c);
+        fuse_candidates(pKF, c, false, "Fuse");
+        int nFused = 0;
+        for (int iMP = 0; iMP < n1; iMP++) {
+            MapPointT* pMP = pts[iMP];
+            if (!pMP || !c.valid[iMP] || c.bestIdx[iMP] < 0) continue;
+            if (c.bestDist[iMP] <= TH_LOW) {  // :1077-1095
+                const int bestIdx = c.bestIdx[iMP];
+                MapPointT* pMPinKF = pKF->GetMapPoint(bestIdx);
+                if (pMPinKF) {
+                    if (!pMPinKF->isBad()) vpReplacePoint[iMP] = pMPinKF;
+                } else {
+                    pMP->AddObservation(pKF, bestIdx);
+                    pKF->AddMapPoint(pMP, bestIdx);
+                }
+                nFused++;
+            }
+        }
+        return nFused;
+    }
+
     static const int TH_LOW = 50;
     static const int TH_HIGH = 100;
     static const int HISTO_LENGTH = 30;
@@ -606,6 +685,122 @@ public:
               "SearchBySim3");
         for (int i = 0; i < n1; ++i)
             if (bestIdx[i] >= 0 && bestDist[i] <= TH_HIGH) vnMatch[i] = bestIdx[i];  // :1221-1224
+    }
+
+
+    // ---- Fuse helpers ----
+    struct FuseCandidates {  // per map point: the projection of :852-888 / :1009-1046 and the result of the candidate loop
+        std::vector<float> uvr, ur;
+        std::vector<int> level, bestIdx, bestDist;
+        std::vector<unsigned char> valid, desc;
+    };
+    // Scw -> Rcw, tcw, Ow (:986-990)
+    static void decompose_sim3(const cv::Mat& Scw, float* R, float* t, float* Ow) {
+#if ORBX_HAVE_OPENCV
+        cv::Mat sRcw = Scw.rowRange(0, 3).colRange(0, 3);
+        const float scw = sqrt(sRcw.row(0).dot(sRcw.row(0)));
+        cv::Mat Rcw = sRcw / scw;
+        cv::Mat tcw = Scw.rowRange(0, 3).col(3) / scw;
+        cv::Mat O = -Rcw.t() * tcw;
+        mat3(Rcw, R); vec3(tcw, t); vec3(O, Ow);
+#else
+        double dd = 0;
+        for (int c = 0; c < 3; ++c) dd += (double)Scw.template at<float>(0, c) * Scw.template at<float>(0, c);
+        const float scw = (float)std::sqrt(dd);
+        const float inv = (float)(1.0 / (double)scw);  // cv::Mat / scalar multiplies by the float-rounded reciprocal
+        for (int r = 0; r < 3; ++r) {
+            for (int c = 0; c < 3; ++c) R[3 * r + c] = Scw.template at<float>(r, c) * inv;
+            t[r] = Scw.template at<float>(r, 3) * inv;
+        }
+        for (int c = 0; c < 3; ++c) Ow[c] = -(float)((double)R[c] * t[0] + (double)R[3 + c] * t[1] + (double)R[6 + c] * t[2]);
+#endif
+    }
+    // The per-point projection and visibility tests shared by both Fuse overloads (null entries are skipped).  Products and the norm /
+    // dot accumulate in double and round once, as cv::Mat's CV_32F paths do; comparisons against 0.5 * dist3D are made in double
+    // like the reference's `PO.dot(Pn) < 0.5*dist3D`.
+    template <class KeyFrameT, class MapPointT>
+    static void project_for_fuse(KeyFrameT* pKF, const float* R, const float* t, const float* Ow, const std::vector<MapPointT*>& pts, float th,
+                                 float bf, bool stereoGate, FuseCandidates& c) {
+        const int n1 = (int)pts.size();
+        const float fx = pKF->fx, fy = pKF->fy, cx = pKF->cx, cy = pKF->cy;
+        c.uvr.assign(3 * (size_t)n1, 0.f);
+        c.ur.assign(n1, 0.f);
+        c.level.assign(n1, 0);
+        c.valid.assign(n1, 0);
+        c.desc.assign((size_t)n1 * 32, 0);
+        (void)stereoGate;
+#if ORBX_HAVE_OPENCV
+        const cv::Mat Rcw(3, 3, CV_32F, (void*)R), tcw(3, 1, CV_32F, (void*)t), Owm(3, 1, CV_32F, (void*)Ow);
+#endif
+        for (int i = 0; i < n1; ++i) {
+            MapPointT* pMP = pts[i];
+            if (!pMP) continue;
+            float pw[3], pc[3], pn[3];
+            vec3(pMP->GetWorldPos(), pw);
+#if ORBX_HAVE_OPENCV
+            {  // the reference's own expression, evaluated by OpenCV
+                const cv::Mat p3Dw = pMP->GetWorldPos();
+                const cv::Mat p3Dc = Rcw * p3Dw + tcw;
+                vec3(p3Dc, pc);
+            }
+#else
+            for (int r = 0; r < 3; ++r) {  // p3Dc = Rcw*p3Dw + tcw
+                double acc = 0;
+                for (int k = 0; k < 3; ++k) acc += (double)R[3 * r + k] * (double)pw[k];
+                pc[r] = (float)acc + t[r];
+            }
+#endif
+            if (pc[2] < 0.0f) continue;  // depth must be positive
+            const float invz = 1 / pc[2];
+            const float x = pc[0] * invz, y = pc[1] * invz;
+            const float u = fx * x + cx, v = fy * y + cy;
+            if (!pKF->IsInImage(u, v)) continue;
+            const float ur = u - bf * invz;
+            const float maxDistance = pMP->GetMaxDistanceInvariance(), minDistance = pMP->GetMinDistanceInvariance();
+            vec3(pMP->GetNormal(), pn);
+            double ss = 0, dp = 0;
+#if ORBX_HAVE_OPENCV
+            {
+                const cv::Mat PO = pMP->GetWorldPos() - Owm;
+                ss = cv::norm(PO);
+                ss *= ss;
+                dp = PO.dot(pMP->GetNormal());
+            }
+            const float dist3D = (float)cv::norm(pMP->GetWorldPos() - Owm);
+#else
+            for (int r = 0; r < 3; ++r) {
+                const float po = pw[r] - Ow[r];
+                ss += (double)po * (double)po;
+                dp += (double)po * (double)pn[r];
+            }
+            const float dist3D = (float)std::sqrt(ss);
+#endif
+            if (dist3D < minDistance || dist3D > maxDistance) continue;  // depth must be inside the scale pyramid of the image
+            if (dp < 0.5 * dist3D) continue;                              // viewing angle must be less than 60 deg
+            const int nPredictedLevel = pMP->PredictScale(dist3D, pKF);
+            c.valid[i] = 1;
+            c.level[i] = nPredictedLevel;
+            c.uvr[3 * i] = u;
+            c.uvr[3 * i + 1] = v;
+            c.uvr[3 * i + 2] = th * pKF->mvScaleFactors[nPredictedLevel];
+            c.ur[i] = ur;
+            const cv::Mat dMP = pMP->GetDescriptor();
+            std::memcpy(&c.desc[(size_t)i * 32], dMP.template ptr<unsigned char>(), 32);
+        }
+    }
+    template <class KeyFrameT>
+    static void fuse_candidates(KeyFrameT* pKF, FuseCandidates& c, bool gate, const char* what) {
+        const int n1 = (int)c.valid.size(), n2 = (int)pKF->mvKeysUn.size();
+        const cv::Mat d2 = continuous(pKF->mDescriptors);
+        const float bounds[4] = {(float)pKF->mnMinX, (float)pKF->mnMaxX, (float)pKF->mnMinY, (float)pKF->mnMaxY};
+        c.bestIdx.assign(n1, -1);
+        c.bestDist.assign(n1, 256);
+        const bool hasRight = gate && (int)pKF->mvuRight.size() == n2;
+        check(orbx_fuse_match(n1, c.uvr.data(), gate ? c.ur.data() : nullptr, c.level.data(), c.valid.data(), c.desc.data(),
+                              reinterpret_cast<const orbx_keypoint*>(pKF->mvKeysUn.data()), n2, d2.template ptr<unsigned char>(),
+                              hasRight ? pKF->mvuRight.data() : nullptr, gate ? pKF->mvInvLevelSigma2.data() : nullptr,
+                              gate ? (int)pKF->mvInvLevelSigma2.size() : 64, bounds, c.bestIdx.data(), c.bestDist.data()),
+              what);
     }
 
     // The common nodes of two DBoW2::FeatureVector (std::map<NodeId, std::vector<unsigned int>>) in map order — the walk of

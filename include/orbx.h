@@ -247,6 +247,15 @@ int orbx_cvt_color_gray(const uint8_t* src, long long src_stride, int w, int h, 
 int orbx_cvt_color_gray_device(const uint8_t* d_src, long long src_stride, int w, int h, int channels, int flags, uint8_t* d_dst,
                                long long dst_stride, void* stream);
 
+/* Frame::UndistortKeyPoints (src/Frame.cc:403-433): cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) on the keypoint
+ * coordinates — OpenCV's five-iteration inverse of the k1 k2 p1 p2 [k3] model in double, re-projected with the same K — every
+ * other field of the keypoint copied (mvKeysUn[i] = mvKeys[i] with the new pt).  K = {fx, fy, cx, cy}; dist = ndist (0..5)
+ * coefficients in OpenCV's order.  dist[0] == 0 (or ndist == 0) copies the keypoints, like the reference's early return
+ * (:405-409); the device form always runs the model.  in == out is allowed. */
+int orbx_undistort_keypoints(const orbx_keypoint* in, int n, const float K[4], const float* dist, int ndist, orbx_keypoint* out);
+int orbx_undistort_keypoints_device(const orbx_keypoint* d_in, int n, const float K[4], const float* dist, int ndist,
+                                    orbx_keypoint* d_out, void* stream);
+
 /* The matching core of both ORBmatcher::Fuse overloads: Fuse(pKF, vpMapPoints, th) (src/ORBmatcher.cc:825-975; candidate loop
  * :886-945; LocalMapping::SearchInNeighbors, src/LocalMapping.cc:600ff) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint)
  * (:977-1100; candidate loop :1049-1075; LoopClosing::SearchAndFuse).  Per map point i that passed the caller's projection and

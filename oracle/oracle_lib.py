@@ -323,6 +323,40 @@ def cvt_color_gray(img, bgr=False, cv2_coeffs=False):
     return ((r * 9798 + g * 19235 + b * 3735 + (1 << 14)) >> 15).astype(np.uint8)
 
 
+def undistort_keypoints(kps, K, dist):
+    """Frame::UndistortKeyPoints (src/Frame.cc:403-433) = cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK): OpenCV's
+    cvUndistortPointsInternal restated in numpy float64 (individually rounded operations in its order: normalise with 1/fx, five
+    iterations of the inverse distortion model, re-project with P = K, one rounding to float).  Pinned against cv2.undistortPoints
+    (tests/test_undistort.py).  dist[0] == 0: the reference's early return, keypoints unchanged."""
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE).copy()
+    d = np.zeros(5, np.float64)
+    dd = np.asarray(dist, np.float32).reshape(-1)
+    d[:dd.size] = dd.astype(np.float64)
+    if dd.size == 0 or dd[0] == 0:
+        return kps
+    fx, fy, cx, cy = (np.float64(np.float32(v)) for v in K)
+    k1, k2, p1, p2, k3 = d
+    ifx, ify = 1.0 / fx, 1.0 / fy
+    u, v = kps["x"].astype(np.float64), kps["y"].astype(np.float64)
+    x, y = (u - cx) * ifx, (v - cy) * ify
+    x0, y0 = x.copy(), y.copy()
+    frozen = np.zeros(x.shape, bool)
+    for _ in range(5):
+        r2 = x * x + y * y
+        icdist = 1.0 / (1.0 + ((k3 * r2 + k2) * r2 + k1) * r2)
+        neg = (icdist < 0) & ~frozen
+        deltaX = 2 * p1 * x * y + p2 * (r2 + 2 * x * x)
+        deltaY = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y
+        nx, ny = (x0 - deltaX) * icdist, (y0 - deltaY) * icdist
+        nx = np.where(neg, (u - cx) * ifx, nx)
+        ny = np.where(neg, (v - cy) * ify, ny)
+        x, y = np.where(frozen, x, nx), np.where(frozen, y, ny)
+        frozen |= neg
+    xx, yy, ww = fx * x + 0.0 * y + cx, 0.0 * x + fy * y + cy, 1.0 / (0.0 * x + 0.0 * y + 1.0)
+    kps["x"], kps["y"] = (xx * ww).astype(np.float32), (yy * ww).astype(np.float32)
+    return kps
+
+
 def distinctive_descriptors(start, desc):
     start = np.ascontiguousarray(start, dtype=np.int32)
     desc = np.ascontiguousarray(desc, dtype=np.uint8)

@@ -519,3 +519,13 @@ def ComputeStereoMatches(exL: ORBextractor, exR: ORBextractor, kpsL, descL, kpsR
     _check(lib().orbx_stereo_match(exL._h, exR._h, _p(kpsL), kpsL.size, _p(descL), _p(kpsR), kpsR.size, _p(descR),
                                    C.c_float(bf), C.c_float(np.float32(bf) / np.float32(fx)), _p(u), _p(z)))
     return u[:kpsL.size], z[:kpsL.size]
+
+
+def UndistortKeyPoints(kps: np.ndarray, K, dist) -> np.ndarray:
+    """Frame::UndistortKeyPoints (reference src/Frame.cc:403-433): K = (fx, fy, cx, cy), dist = k1 k2 p1 p2 [k3]."""
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)
+    Kf = np.asarray(K, dtype=np.float32)
+    d = np.asarray(dist, dtype=np.float32).reshape(-1)
+    out = np.empty_like(kps)
+    _check(lib().orbx_undistort_keypoints(_p(kps), kps.size, _p(Kf), _p(d) if d.size else None, int(d.size), _p(out)))
+    return out

@@ -655,6 +655,40 @@ int orbx_cvt_color_gray(const uint8_t* src, long long src_stride, int w, int h, 
     return ORBX_OK;
 }
 
+int orbx_undistort_keypoints_device(const orbx_keypoint* d_in, int n, const float K[4], const float* dist, int ndist, orbx_keypoint* d_out,
+                                    void* stream) {
+    if (n < 0 || !K || ndist < 0 || ndist > 5 || (ndist > 0 && !dist) || (n > 0 && (!d_in || !d_out)) || !(K[0] != 0.f) || !(K[1] != 0.f)) {
+        set_error("orbx_undistort_keypoints: bad argument (K = fx, fy, cx, cy; up to 5 distortion coefficients k1 k2 p1 p2 k3)");
+        return ORBX_E_INVALID;
+    }
+    Workspace* wk;
+    int rc = workspace(&wk);
+    if (rc) return rc;
+    return launch_undistort(d_in, n, K, dist, ndist, d_out, stream ? static_cast<cudaStream_t>(stream) : wk->stream);
+}
+
+int orbx_undistort_keypoints(const orbx_keypoint* in, int n, const float K[4], const float* dist, int ndist, orbx_keypoint* out) {
+    if (n < 0 || !K || ndist < 0 || ndist > 5 || (ndist > 0 && !dist) || (n > 0 && (!in || !out)) || !(K[0] != 0.f) || !(K[1] != 0.f)) {
+        set_error("orbx_undistort_keypoints: bad argument (K = fx, fy, cx, cy; up to 5 distortion coefficients k1 k2 p1 p2 k3)");
+        return ORBX_E_INVALID;
+    }
+    if (n == 0) return ORBX_OK;
+    if (ndist == 0 || dist[0] == 0.0f) {  // src/Frame.cc:405-409: no distortion, mvKeysUn = mvKeys
+        if (out != in) memcpy(out, in, (size_t)n * sizeof(orbx_keypoint));
+        return ORBX_OK;
+    }
+    Workspace* wk;
+    int rc = workspace(&wk);
+    if (rc) return rc;
+    cudaStream_t s = wk->stream;
+    const size_t bytes = (size_t)n * sizeof(orbx_keypoint);
+    if ((rc = upload(wk->a, in, bytes, s)) || (rc = wk->b.ensure(bytes))) return rc;
+    if ((rc = launch_undistort(wk->a.as<orbx_keypoint>(), n, K, dist, ndist, wk->b.as<orbx_keypoint>(), s))) return rc;
+    ORBX_CUDA(cudaMemcpyAsync(out, wk->b.p, bytes, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    return ORBX_OK;
+}
+
 int orbx_fuse_match(int n1, const float* uvr, const float* ur1, const int* level1, const uint8_t* valid1, const uint8_t* mp_desc1,
                     const orbx_keypoint* k2, int n2, const uint8_t* desc2, const float* u_right2, const float* inv_level_sigma2,
                     int nlevels, const float bounds[4], int* best_idx, int* best_dist) {

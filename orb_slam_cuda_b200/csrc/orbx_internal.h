@@ -239,6 +239,8 @@ int launch_fuse_match(int n1, const float* uvr, const float* ur1, const int* lev
                       const float bounds[4], int* cellOf, int* sorted, int* cellStart, int* bestIdx, int* bestDist, cudaStream_t s);
 int launch_gray(const uint8_t* src, long long srcStride, int w, int h, int channels, int bgr, int shift, uint8_t* dst, long long dstStride,
                 cudaStream_t s);
+// Frame::UndistortKeyPoints: K = fx, fy, cx, cy; dist = k1 k2 p1 p2 [k3]
+int launch_undistort(const orbx_keypoint* in, int n, const float K[4], const float* dist, int ndist, orbx_keypoint* out, cudaStream_t s);
 int launch_distinctive(int nPoints, const int* start, const uint8_t* desc, int* bestIdx, int* bestMedian, cudaStream_t s);
 int launch_stereo(const StereoLevels& lv, const orbx_keypoint* kL, int nL, const uint8_t* dL, const orbx_keypoint* kR, int nR,
                   const uint8_t* dR, float mbf, float maxD, float* uRight, float* depth, int* sad, cudaStream_t s);

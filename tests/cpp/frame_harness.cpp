@@ -8,6 +8,7 @@
 //   frame_harness stereo in.raw w h nfeatures bf fx out.bin    (left, right: extraction + ComputeStereoMatches)
 //   frame_harness bow    in.raw w h nfeatures voc.txt out.bin  (System.cc:64 loadFromTextFile, Frame::ComputeBoW, SearchByBoW)
 //   frame_harness track  in.raw w h nfeatures th out.bin       (last, current: Tracking::TrackWithMotionModel's SearchByProjection, :962)
+//   frame_harness fuse   in.raw w h nfeatures th out.bin       (last, current: both ORBmatcher::Fuse overloads incl. their map surgery)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -23,7 +24,18 @@
 
 using namespace ORB_SLAM2;
 
+struct KeyFrame;
+struct SurgeryOp { int op; long a, b; };  // 0 AddObservation(point a, idx b), 1 AddMapPoint(point a, idx b), 2 a->Replace(b)
+static std::vector<SurgeryOp> g_surgery;
+
 struct MapPoint {  // the members of ORB_SLAM2::MapPoint that SearchByProjection reads (include/MapPoint.h)
+    // Fuse (src/ORBmatcher.cc:825-1100): the observation bookkeeping of src/MapPoint.cc:83-95 (AddObservation), :179-220 (Replace)
+    long mnId = -1;
+    std::map<KeyFrame*, size_t> mObservations;
+    bool IsInKeyFrame(KeyFrame* k) const { return mObservations.count(k) != 0; }
+    void addObservationQuiet(KeyFrame* k, size_t idx);
+    void AddObservation(KeyFrame* k, size_t idx);
+    void Replace(MapPoint* pMP);
     cv::Mat mWorldPos, mDescriptor;
     int nObs = 0;
     bool mbTrackInView = false, mbBad = false;  // Tracking::SearchLocalPoints state (include/MapPoint.h:111-117)
@@ -55,12 +67,48 @@ struct KeyFrame {  // the members of ORB_SLAM2::KeyFrame that the relocalisation
     cv::Mat GetTranslation() const { return mtcw; }
     cv::Mat GetCameraCenter() const { return mOw; }
     MapPoint* GetMapPoint(size_t i) const { return mvpMapPoints[i]; }
+    // Fuse: src/KeyFrame.cc:209-213 (AddMapPoint), :215-225, :236-249 (GetMapPoints)
+    float mbf = 0;
+    std::vector<float> mvInvLevelSigma2;
+    void AddMapPoint(MapPoint* pMP, size_t idx) { g_surgery.push_back({1, pMP->mnId, (long)idx}); mvpMapPoints[idx] = pMP; }
+    void EraseMapPointMatch(size_t idx) { mvpMapPoints[idx] = nullptr; }
+    void ReplaceMapPointMatch(size_t idx, MapPoint* pMP) { mvpMapPoints[idx] = pMP; }
+    std::set<MapPoint*> GetMapPoints() const {
+        std::set<MapPoint*> s;
+        for (MapPoint* p : mvpMapPoints) if (p && !p->isBad()) s.insert(p);
+        return s;
+    }
     // loop-detection SearchByProjection (src/ORBmatcher.cc:290-403)
     float fx = 0, fy = 0, cx = 0, cy = 0, mnMinX = 0, mnMaxX = 0, mnMinY = 0, mnMaxY = 0;
     std::vector<float> mvScaleFactors;
     cv::Mat mDescriptors;
     bool IsInImage(const float& x, const float& y) const { return x >= mnMinX && x < mnMaxX && y >= mnMinY && y < mnMaxY; }
 };
+
+void MapPoint::addObservationQuiet(KeyFrame* k, size_t idx) {
+    if (mObservations.count(k)) return;
+    mObservations[k] = idx;
+    nObs += (idx < k->mvuRight.size() && k->mvuRight[idx] >= 0) ? 2 : 1;
+}
+void MapPoint::AddObservation(KeyFrame* k, size_t idx) {
+    g_surgery.push_back({0, mnId, (long)idx});
+    addObservationQuiet(k, idx);
+}
+void MapPoint::Replace(MapPoint* pMP) {
+    if (pMP->mnId == mnId) return;
+    g_surgery.push_back({2, mnId, pMP->mnId});
+    std::map<KeyFrame*, size_t> obs = mObservations;
+    mObservations.clear();
+    mbBad = true;
+    for (auto& kv : obs) {
+        if (!pMP->IsInKeyFrame(kv.first)) {
+            kv.first->ReplaceMapPointMatch(kv.second, pMP);
+            pMP->addObservationQuiet(kv.first, kv.second);
+        } else {
+            kv.first->EraseMapPointMatch(kv.second);
+        }
+    }
+}
 
 struct Frame {  // the members of ORB_SLAM2::Frame that the front end reads or writes (include/Frame.h)
     cv::Mat mTcw;
@@ -313,6 +361,80 @@ int main(int argc, char** argv) {
             const int nk = kfMatcher.SearchByBoW(&KF, &KC, matches12);
             put_i(out, nk);
             for (int i = 0; i < Last.N; ++i) put_i(out, matches12[i] ? (int)(matches12[i] - points.data()) : -1);
+            fclose(out);
+        } else if (mode == "fuse") {
+            // LocalMapping::SearchInNeighbors (src/LocalMapping.cc:519ff) and LoopClosing::SearchAndFuse (src/LoopClosing.cc:644): the
+            // current frame is the keyframe (identity pose), the last frame's map points sit at depth 5 where the image shift (7, -4)
+            // puts them; some keyframe features already hold points of their own
+            FILE* out = fopen(argv[7], "wb");
+            const float th = (float)atof(argv[6]);
+            ORBextractor ex(nf, 1.2f, 8, 20, 7, w, h);
+            Frame Last, Cur;
+            Last.mpORBextractorLeft = Cur.mpORBextractorLeft = &ex;
+            Last.ExtractORB(0, im0);
+            Cur.ExtractORB(0, im1);
+            const int N1 = (int)Last.mvKeys.size(), N2 = (int)Cur.mvKeys.size();
+            put_keys(out, Last.mvKeys, Last.mDescriptors);
+            put_keys(out, Cur.mvKeys, Cur.mDescriptors);
+            for (int pass = 0; pass < 2; ++pass) {
+                KeyFrame KF;
+                KF.mvKeysUn = Cur.mvKeys; KF.mDescriptors = Cur.mDescriptors; KF.N = N2;
+                KF.mvScaleFactors = ex.GetScaleFactors(); KF.mvInvLevelSigma2 = ex.GetInverseScaleSigmaSquares();
+                KF.fx = KF.fy = 500.f; KF.cx = 0.5f * w; KF.cy = 0.5f * h; KF.mbf = 40.f;
+                KF.mnMinX = 0; KF.mnMaxX = (float)w; KF.mnMinY = 0; KF.mnMaxY = (float)h;
+                KF.mRcw = cv::Mat(3, 3, CV_32F); KF.mtcw = cv::Mat(3, 1, CV_32F); KF.mOw = cv::Mat(3, 1, CV_32F);
+                for (int r = 0; r < 3; ++r) {
+                    KF.mtcw.at<float>(r, 0) = 0.f; KF.mOw.at<float>(r, 0) = 0.f;
+                    for (int c = 0; c < 3; ++c) KF.mRcw.at<float>(r, c) = r == c ? 1.f : 0.f;
+                }
+                KF.mvuRight.assign(N2, -1.f);
+                for (int j = 0; j < N2; j += 3) KF.mvuRight[j] = Cur.mvKeys[j].pt.x - 8.f;  // stereo keypoints: depth 5 at bf 40
+                std::vector<MapPoint> own(N2), pts(N1);
+                KF.mvpMapPoints.assign(N2, nullptr);
+                for (int j = 0; j < N2; ++j) {
+                    if (j % 4 != 1) continue;
+                    own[j].mnId = N1 + j;
+                    own[j].nObs = 1 + j % 5;
+                    own[j].mbBad = j % 29 == 1;
+                    own[j].mObservations[&KF] = j;
+                    KF.mvpMapPoints[j] = &own[j];
+                }
+                std::vector<MapPoint*> cands;
+                for (int i = 0; i < N1; ++i) {
+                    MapPoint& P = pts[i];
+                    P.mnId = i;
+                    P.mWorldPos = cv::Mat(3, 1, CV_32F);
+                    P.mWorldPos.at<float>(0, 0) = (Last.mvKeys[i].pt.x + 7.f - KF.cx) * 5.f / KF.fx;
+                    P.mWorldPos.at<float>(1, 0) = (Last.mvKeys[i].pt.y - 4.f - KF.cy) * 5.f / KF.fy;
+                    P.mWorldPos.at<float>(2, 0) = 5.f;
+                    P.mNormal = cv::Mat(3, 1, CV_32F);
+                    P.mNormal.at<float>(0, 0) = 0.f; P.mNormal.at<float>(1, 0) = 0.f; P.mNormal.at<float>(2, 0) = i % 19 == 0 ? -1.f : 1.f;
+                    P.mDescriptor = Last.mDescriptors.row(i);
+                    P.mnTrackScaleLevel = Last.mvKeys[i].octave;   // PredictScale
+                    P.nObs = i % 6;
+                    P.mbBad = i % 23 == 0;
+                    cands.push_back(i % 5 == 0 ? nullptr : &P);
+                }
+                for (int i = 1; i < N1; i += 37) cands.push_back(&pts[i]);  // listed twice: in the keyframe by then, or still free
+                g_surgery.clear();
+                ORBmatcher matcher(0.6f, true);
+                std::vector<MapPoint*> replaced(cands.size(), nullptr);
+                int nFused;
+                if (pass == 0) {
+                    nFused = matcher.Fuse(&KF, cands, th);
+                } else {
+                    for (auto& c : cands) if (!c) c = &pts[0];  // the Sim3 overload has no null test (:1002): point 0 is bad (0 % 23 == 0)
+                    cv::Mat Scw(4, 4, CV_32F);
+                    for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) Scw.at<float>(r, c) = r == c ? (r < 3 ? 2.f : 1.f) : 0.f;
+                    nFused = matcher.Fuse(&KF, Scw, cands, th, replaced);
+                }
+                put_i(out, nFused);
+                put_i(out, (int)g_surgery.size());
+                for (const SurgeryOp& o : g_surgery) { put_i(out, o.op); put_i(out, (int)o.a); put_i(out, (int)o.b); }
+                for (int j = 0; j < N2; ++j) put_i(out, KF.mvpMapPoints[j] ? (int)KF.mvpMapPoints[j]->mnId : -1);
+                put_i(out, (int)cands.size());
+                for (size_t e = 0; e < cands.size(); ++e) put_i(out, replaced[e] ? (int)replaced[e]->mnId : -1);
+            }
             fclose(out);
         } else if (mode == "bow" && argc >= 8) {
             // System.cc:64-65 loads the vocabulary, Frame::ComputeBoW (src/Frame.cc:394-401) fills mBowVec / mFeatVec of two frames,

@@ -204,20 +204,26 @@ def case_sbp_sim3(seed, th):
     return oracle, reference
 
 
-def fuse_surgery(idx, dist, obs1, kf_point_obs, u_right2, n1):
-    """The map surgery that follows Fuse's candidate loop (src/ORBmatcher.cc:947-970) replayed on (bestIdx, bestDist) per point:
-    the op log the reference harness records, with the state changes of MapPoint::Replace / AddObservation and
-    KeyFrame::AddMapPoint (src/MapPoint.cc:83-95, :179-220; src/KeyFrame.cc:209-213)."""
+def fuse_surgery(idx, dist, obs1, kf_point_obs, u_right2, n1, entry_point=None, bad_points=(), kf_bad=()):
+    """The map surgery that follows Fuse's candidate loop (src/ORBmatcher.cc:947-970) replayed on (bestIdx, bestDist) per list
+    entry: the op log the reference harness records, with the state changes of MapPoint::Replace / AddObservation and
+    KeyFrame::AddMapPoint (src/MapPoint.cc:83-95, :179-220; src/KeyFrame.cc:209-213).  entry_point[e] = the map point (0 .. n1-1, or
+    None for a null pointer) listed at entry e — a point may be listed twice; the keyframe's own points are numbered
+    n1 + feature index.  `isBad() || IsInKeyFrame(pKF)` (:849) is evaluated when the entry's turn comes."""
+    if entry_point is None:
+        entry_point = list(range(n1))
     slot = {i: n1 + i for i in range(len(kf_point_obs)) if kf_point_obs[i] >= 0}   # feature -> point id held by the keyframe
     nobs = {i: int(obs1[i]) for i in range(n1)}
     nobs.update({n1 + i: int(kf_point_obs[i]) for i in slot})
     in_kf = {pid: i for i, pid in slot.items()}                                     # point id -> feature index it observes
-    bad = set()
+    bad = set(int(b) for b in bad_points) | set(n1 + int(j) for j in kf_bad)
     ops, fused = [], 0
-    for i in range(n1):
-        if idx[i] < 0 or dist[i] > 50:
+    for e, i in enumerate(entry_point):
+        if i is None or i in bad or i in in_kf:
             continue
-        b = int(idx[i])
+        if idx[e] < 0 or dist[e] > 50:
+            continue
+        b = int(idx[e])
         held = slot.get(b)
         if held is not None:
             if held not in bad:
@@ -228,19 +234,16 @@ def fuse_surgery(idx, dist, obs1, kf_point_obs, u_right2, n1):
                     ops.append((2, held, i))          # pMPinKF->Replace(pMP): its observation of the keyframe moves to pMP
                     bad.add(held)
                     f = in_kf.pop(held)
-                    if i not in in_kf:
-                        slot[f] = i
-                        in_kf[i] = f
-                        nobs[i] += 2 if u_right2 is not None and u_right2[f] >= 0 else 1
-                    else:
-                        del slot[f]
+                    slot[f] = i
+                    in_kf[i] = f
+                    nobs[i] += 2 if u_right2 is not None and u_right2[f] >= 0 else 1
         else:
             ops += [(0, i, b), (1, i, b)]
             in_kf[i] = b
             slot[b] = i
             nobs[i] += 2 if u_right2 is not None and u_right2[b] >= 0 else 1
         fused += 1
-    return fused, np.array(ops, np.int64).reshape(-1, 3)
+    return fused, np.array(ops, np.int64).reshape(-1, 3), slot
 
 
 def case_fuse(seed, stereo, th):
@@ -258,7 +261,7 @@ def case_fuse(seed, stereo, th):
 
     def oracle():
         idx, dist = O.fuse_match(uvr, ur1, level, valid, s["mp_desc1"], s["k2"], s["d2"], s["u_right2"], inv, s["bounds"])
-        fused, ops = fuse_surgery(idx, dist, obs1, kf_point_obs, s["u_right2"], n1)
+        fused, ops, _ = fuse_surgery(idx, dist, obs1, kf_point_obs, s["u_right2"], n1)
         return (np.array([fused], np.int32), ops)
 
     def reference():

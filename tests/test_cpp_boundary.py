@@ -323,3 +323,99 @@ def test_compute_bow_and_search_by_bow(harness, tmp_path):
     pairs = rd.arr(np.int32, 2 * n_tri).reshape(-1, 2)
     want = np.flatnonzero(m_tri >= 0)
     assert np.array_equal(pairs[:, 0], want) and np.array_equal(pairs[:, 1], m_tri[want])
+
+
+@pytest.mark.gpu
+def test_fuse_both_overloads_with_map_surgery(harness, tmp_path):
+    """ORBmatcher::Fuse(pKF, vpMapPoints, th) and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) through the templates of
+    include/ORBmatcher.h with mock KeyFrame / MapPoint classes that record the map surgery (tests/cpp/frame_harness.cpp, mode
+    `fuse`).  Expected: the oracle's candidate loop (O.fuse_match) followed by the replay of src/ORBmatcher.cc:947-970 /
+    :1077-1095 (tests/ref_matcher_cases.fuse_surgery — the replay that tests/test_oracle_ref_matcher.py pins to the reference's
+    own Fuse compiled from /root/reference).  nFused, the op log in order, the keyframe's final slots and vpReplacePoint equal."""
+    import ref_matcher_cases as RC
+    kind, nf, th = "tum", 1000, 3.0
+    a, b = synth.frame(kind, 43), synth.shifted_frame(kind, 43)
+    h, w = a.shape
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(a.tobytes() + b.tobytes())
+    out = tmp_path / "out.bin"
+    r = subprocess.run([harness, "fuse", str(raw), str(w), str(h), str(nf), repr(th), str(out)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    rd = Reader(out.read_bytes())
+    k1, d1 = rd.keys()
+    k2, d2 = rd.keys()
+    n1, n2 = len(k1), len(k2)
+    f32 = np.float32
+    fx = fy = f32(500.0)
+    cx, cy = f32(0.5) * f32(w), f32(0.5) * f32(h)
+    t = O.Extractor(nf, 1.2, 8, 20, 7).tables()
+    sf, inv_sigma2 = t["scale"], t["inv_sigma2"]
+    i = np.arange(n1)
+    # the harness' world points (float expressions in its order), projected as project_for_fuse does with the identity pose
+    X0 = (((k1["x"] + f32(7.0)).astype(f32) - cx).astype(f32) * f32(5.0) / fx).astype(f32)
+    X1 = (((k1["y"] - f32(4.0)).astype(f32) - cy).astype(f32) * f32(5.0) / fy).astype(f32)
+    z = np.full(n1, 5.0, f32)
+    invz = (f32(1.0) / z).astype(f32)
+    u = (fx * (X0 * invz).astype(f32)).astype(f32) + cx
+    v = (fy * (X1 * invz).astype(f32)).astype(f32) + cy
+    dist3 = np.sqrt(X0.astype(np.float64) ** 2 + X1.astype(np.float64) ** 2 + 25.0).astype(f32)
+    nz = np.where(i % 19 == 0, -1.0, 1.0)
+    ok = (u >= 0) & (u < w) & (v >= 0) & (v < h) & ~((dist3 < f32(3.5)) | (dist3 > f32(15.5))) & ~(5.0 * nz < 0.5 * dist3.astype(np.float64))
+    level = k1["octave"].astype(np.int32)
+    u_right2 = np.full(n2, -1.0, f32)
+    u_right2[::3] = k2["x"][::3] - f32(8.0)
+    kf_point_obs = np.where(np.arange(n2) % 4 == 1, 1 + np.arange(n2) % 5, -1).astype(np.int32)
+    kf_bad = [j for j in range(n2) if j % 4 == 1 and j % 29 == 1]
+    obs1 = (i % 6).astype(np.int32)
+    bad_points = [p for p in range(n1) if p % 23 == 0]
+    entries = [None if p % 5 == 0 else p for p in range(n1)] + list(range(1, n1, 37))
+    bounds = (0.0, float(w), 0.0, float(h))
+    assert len(set(e for e in entries if e is not None)) < len([e for e in entries if e is not None])  # some points are listed twice
+
+    def gather(ent, gate):
+        e_idx = np.array([0 if e is None else e for e in ent])
+        valid = np.array([e is not None for e in ent]) & ok[e_idx]
+        uvr = np.stack([u[e_idx], v[e_idx], (f32(th) * sf[level[e_idx]]).astype(f32)], 1).astype(f32)
+        ur1 = (u[e_idx] - (f32(40.0) * invz[e_idx]).astype(f32)).astype(f32) if gate else None
+        return O.fuse_match(uvr, ur1, level[e_idx], valid.astype(np.uint8), d1[e_idx], k2, d2, u_right2 if gate else None, inv_sigma2, bounds)
+
+    # ---- overload 1 ----
+    idx, dist = gather(entries, True)
+    fused, ops, slot = RC.fuse_surgery(idx, dist, obs1, kf_point_obs, u_right2, n1, entries, bad_points, kf_bad)
+    assert fused > 100 and (ops[:, 0] == 2).sum() > 10 and (ops[:, 0] == 0).sum() > 50
+    assert rd.i32() == fused
+    n_ops = rd.i32()
+    got_ops = rd.arr(np.int32, 3 * n_ops).reshape(-1, 3)
+    assert np.array_equal(got_ops, ops)
+    got_slots = rd.arr(np.int32, n2)
+    want_slots = np.array([slot.get(j, -1) for j in range(n2)], np.int32)
+    assert np.array_equal(got_slots, want_slots)
+    assert rd.i32() == len(entries)
+    assert (rd.arr(np.int32, len(entries)) == -1).all()  # the first overload has no vpReplacePoint
+    # ---- overload 2 (Scw = 2 * identity: scale 2, rotation I, translation 0): no chi-square gate, no Replace ----
+    entries2 = [0 if e is None else e for e in entries]  # the harness puts (bad) point 0 where overload 1 had null pointers
+    idx, dist = gather(entries2, False)
+    in_kf = set()
+    slot2 = {j: n1 + j for j in range(n2) if kf_point_obs[j] >= 0}
+    ops2, replaced, fused2 = [], np.full(len(entries2), -1, np.int32), 0
+    for e, p in enumerate(entries2):
+        if p in bad_points or not ok[p] or idx[e] < 0 or dist[e] > 50:   # spAlreadyFound holds keyframe points only: never a candidate
+            continue
+        bI = int(idx[e])
+        held = slot2.get(bI)
+        if held is not None:
+            if held >= n1 and (held - n1) in kf_bad:
+                pass
+            else:
+                replaced[e] = held
+        else:
+            ops2 += [(0, p, bI), (1, p, bI)]
+            slot2[bI] = p
+        fused2 += 1
+    assert fused2 > 100 and (replaced >= 0).sum() > 10
+    assert rd.i32() == fused2
+    n_ops = rd.i32()
+    assert np.array_equal(rd.arr(np.int32, 3 * n_ops).reshape(-1, 3), np.array(ops2, np.int64).reshape(-1, 3))
+    assert np.array_equal(rd.arr(np.int32, n2), np.array([slot2.get(j, -1) for j in range(n2)], np.int32))
+    assert rd.i32() == len(entries2)
+    assert np.array_equal(rd.arr(np.int32, len(entries2)), replaced)

@@ -193,6 +193,27 @@ def test_async_host_batches_two_in_flight():
     assert np.array_equal(counts, ref[0][2])
 
 
+@pytest.mark.parametrize("kind,nfeatures", [("kitti", 4000), ("tum", 2000)])
+def test_monocular_initialisation_extractor(kind, nfeatures):
+    """Tracking builds a second extractor with 2 * nFeatures for the monocular initialisation (src/Tracking.cc:133:
+    mpIniORBextractor = new ORBextractor(2*nFeatures, ...)): 4000 features for KITTI, 2000 for TUM.  Bigger per-level quotas mean
+    deeper quadtrees and more shared memory in the quadtree kernel; the result must still equal the oracle bit for bit, single and
+    batched."""
+    gx, ox = X.ORBextractor(nfeatures, 1.2, 8, 20, 7), O.Extractor(nfeatures, 1.2, 8, 20, 7)
+    assert np.array_equal(gx.features_per_level(), ox.tables()["quota"])
+    frames = np.stack([synth.frame(kind, 70 + i) for i in range(3)])
+    kps, desc, counts = gx.extract_batch(frames)
+    for f in range(3):
+        ok, od = ox.extract(frames[f])
+        n = counts[f]
+        assert n == len(ok) and n > nfeatures * 0.8
+        assert np.array_equal(kps[f, :n].view(np.uint8), ok.view(np.uint8))
+        assert np.array_equal(desc[f, :n], od)
+    k1, d1 = gx(frames[1])
+    ok, od = ox.extract(frames[1])
+    assert np.array_equal(k1.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d1, od)
+
+
 def test_strided_input_and_empty():
     gx, ox = make("tum")
     big = np.zeros((500, 700), np.uint8)

@@ -63,6 +63,18 @@ def main():
     kps, desc = ox.extract(frame)
     np.savez_compressed(os.path.join(OUT, "oracle_frame.npz"), frame=frame, kps=kps, desc=desc,
                         params=np.array([300, 8, 20, 7], np.int32))
+    # cv2.undistortPoints on the keypoint sets of tests/test_undistort.py (Frame::UndistortKeyPoints, src/Frame.cc:403-433)
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
+    import test_undistort as TU
+    und = {}
+    for name, (K4, dist, _) in TU.CAMERAS.items():
+        if dist[0] == 0:
+            continue
+        k = TU.keypoints(name)
+        K = np.array([[K4[0], 0, K4[2]], [0, K4[1], K4[3]], [0, 0, 1]], np.float32)
+        pts = np.stack([k["x"], k["y"]], 1).reshape(-1, 1, 2).astype(np.float32)
+        und[name] = cv2.undistortPoints(pts, K, np.array(dist, np.float32), None, K).reshape(-1, 2).view(np.uint32)
+    np.savez_compressed(os.path.join(OUT, "undistort.npz"), **und)
     print("wrote", OUT, "fast20", len(out["fast20"]), "fast7", len(out["fast7"]), "oracle kps", len(kps))
 
 
