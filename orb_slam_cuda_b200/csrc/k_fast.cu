@@ -11,9 +11,9 @@
 // CTA instead of once per frame.  Per frame:
 //   A1     opposite-pair reject, four pixels per lane as packed bytes: an arc of 9 ring points holds one point of every
 //          diametral pair, so a pixel can only be a corner if ring point (0,+3) or (0,-3) differs from v by more than t
-//          (OpenCV's own first test, d = tab[ptr[0]] | tab[ptr[8]], without the sign).  Three row loads, no realignment,
-//          two VABSDIFF4 and a carry test per word; words with a live pixel are compacted into a word list (one ballot
-//          per warp step);
+//          (OpenCV's own first test, d = tab[ptr[0]] | tab[ptr[8]], without the sign).  A lane walks a word column three
+//          rows at a time, so every row difference serves two rows: one row load, one VABSDIFF4 and a carry test per
+//          word; words with a live pixel are compacted into a word list (one warp scan and one atomic per warp round);
 //   A2     the words of the list get the test on all 8 EVEN ring points (rows y+-3, y+-2, y realigned with funnel
 //          shifts): a run of 9 holds 4 consecutive even points, so a pixel survives iff 4 consecutive even points are
 //          all brighter (or all darker); survivors join a pixel list;
@@ -127,14 +127,14 @@ __device__ __forceinline__ void cmp_ring(uint32_t ring, const Thr& th, uint32_t&
     dk = lop3<0x4d>(ring, th.lx, r7 + th.LN7);
 }
 
-// A1 for the four pixels of one word: is ring point (0, +3) or (0, -3) further than t from the centre?  |ring - v| is one
-// VABSDIFF4 (a full-rate ALU instruction on sm_100a, tools/pipe_rates.cu); a byte a exceeds t iff a >= 128 or (a & 127) +
-// 127 - t carries into bit 7 (t < 128), resp. a >= 128 and (a & 127) + 127 - (t - 128) carries (t >= 128).  K7 holds
-// 127 - (t & 127) in every byte.  Returns bit 7 of every byte that passes.
-__device__ __forceinline__ uint32_t a1_word(uint32_t up, uint32_t c, uint32_t dn, uint32_t K7, bool small) {
-    const uint32_t a = __vabsdiffu4(up, c), b = __vabsdiffu4(dn, c);
-    const uint32_t ga = (a & 0x7f7f7f7fu) + K7, gb = (b & 0x7f7f7f7fu) + K7;
-    return small ? (ga | a | gb | b) : ((ga & a) | (gb & b));
+// A1 building block: the bytes in which two rows three apart differ by more than t.  |a - b| is one VABSDIFF4 (a full-rate ALU
+// instruction on sm_100a, tools/pipe_rates.cu); a byte d exceeds t iff d >= 128 or (d & 127) + 127 - t carries into bit 7
+// (t < 128), resp. d >= 128 and (d & 127) + 127 - (t - 128) carries (t >= 128).  K7 holds 127 - (t & 127) in every byte.
+// Bit 7 of every byte that passes is set; the other bits are not meaningful.
+__device__ __forceinline__ uint32_t a1_flag(uint32_t a, uint32_t b, uint32_t K7, bool small) {
+    const uint32_t d = __vabsdiffu4(a, b);
+    const uint32_t g = (d & 0x7f7f7f7fu) + K7;
+    return small ? (g | d) : (g & d);
 }
 
 __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(const __grid_constant__ FrameGeom g,
@@ -259,36 +259,58 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
             int rpc = rpcOpt;
             for (int y0 = 0; y0 < dH;) {
                 const int y1 = min(y0 + rpc, dH);
-                // ---- A1: opposite-pair reject on (0, +-3) over the flat (row, word column) index of the chunk — all columns in
-                //      pass 1, the empty cells' columns in pass 2; a lane keeps its (row, column) pair and steps it by the CTA
-                //      width without a division.  Words with a passing pixel join the word list, one ballot per warp step ----
+                // ---- A1: opposite-pair reject on (0, +-3).  |T[k + 3] - T[k]| > t of tile rows k, k + 3 is the "down" test of
+                //      detectable row k and the "up" test of row k + 3, so a lane walks one word column in steps of THREE rows
+                //      (task = residue class x word column; all columns in pass 1, the empty cells' columns in pass 2): one
+                //      row load and one difference test per word.  A lane collects its live rows in a bit mask; a warp prefix
+                //      sum and ONE shared atomic per warp round place them in the word list ----
                 {
-                    const int rows = y1 - y0, nUnits = rows * nCols;
-                    const int stepRow = FS_THREADS / nCols, stepCol = FS_THREADS - stepRow * nCols;
-                    int row = tid / nCols, col = tid - row * nCols;
-                    for (int u0 = warp * 32; u0 < nUnits; u0 += FS_THREADS) {
-                        const bool unitOk = u0 + lane < nUnits;
-                        uint32_t al = 0;
-                        int e = 0;
-                        if (unitOk) {
-                            const int w = pass == 0 ? col : colList[col];
-                            const int y = y0 + row;
-                            const uint32_t* p = tile32 + y * TWq + wq0 + w;
-                            al = a1_word(p[0], p[3 * TWq], p[6 * TWq], K7, small) & act32[wq0 + w];
-                            e = (y << 6) | w;
+                    const int rows = y1 - y0, nTasks = 3 * nCols;
+                    const int per = min(32, (nTasks + FS_THREADS / 32 - 1) / (FS_THREADS / 32));  // tasks per warp and round
+                    for (int tb = warp * per; tb < nTasks; tb += (FS_THREADS / 32) * per) {
+                        const int task = tb + lane;
+                        uint32_t live = 0;
+                        int e0 = 0;
+                        if (lane < per && task < nTasks) {
+                            const int res = (task >= nCols ? 1 : 0) + (task >= 2 * nCols ? 1 : 0);
+                            const int ci = task - res * nCols;
+                            const int w = pass == 0 ? ci : colList[ci];
+                            const uint32_t vm = act32[wq0 + w];
+                            e0 = ((y0 + res) << 6) | w;
+                            if (vm != 0 && res < rows) {
+                                const uint32_t* p = tile32 + (y0 + res) * TWq + wq0 + w;
+                                uint32_t cur = p[3 * TWq];
+                                uint32_t fPrev = a1_flag(p[0], cur, K7, small);
+                                p += 6 * TWq;
+                                const int nu = (rows - res + 2) / 3;
+#pragma unroll 4
+                                for (int j = 0; j < nu; ++j) {
+                                    const uint32_t next = *p;
+                                    p += 3 * TWq;
+                                    const uint32_t fNext = a1_flag(cur, next, K7, small);
+                                    if (((fPrev | fNext) & vm) != 0) live |= 1u << j;
+                                    cur = next;
+                                    fPrev = fNext;
+                                }
+                            }
                         }
-                        const uint32_t bal = __ballot_sync(0xffffffffu, al != 0);
-                        if (bal != 0) {
-                            int o = 0;
-                            if (lane == 0) o = atomicAdd(&cnt[0], __popc(bal));
-                            o = __shfl_sync(0xffffffffu, o, 0);
-                            if (al != 0) wlist[o + __popc(bal & laneLt)] = (uint16_t)e;
+                        const int c = __popc(live);
+                        int incl = c;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                            if (lane >= o) incl += v;
                         }
-                        row += stepRow;
-                        col += stepCol;
-                        if (col >= nCols) {
-                            col -= nCols;
-                            ++row;
+                        const int total = __shfl_sync(0xffffffffu, incl, 31);
+                        if (total != 0) {
+                            int base = 0;
+                            if (lane == 31) base = atomicAdd(&cnt[0], total);
+                            int o = __shfl_sync(0xffffffffu, base, 31) + incl - c;
+                            while (live) {
+                                const int j = __ffs(live) - 1;
+                                live &= live - 1;
+                                wlist[o++] = (uint16_t)(e0 + ((3 * j) << 6));
+                            }
                         }
                     }
                 }

@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(256) k_pyramid_resize4(uint8_t* __restrict__ d
                                                          const ResizeTab* __restrict__ ytab, int rowsPerCta) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int bx = blockIdx.x * 128 + lane * 4;  // byte column of this thread's 4 pixels
-    if (bx >= dpitch) return;
+    const bool inRow = bx < dpitch;  // (every thread helps to fill the row table below)
     const int f = blockIdx.z;
     int s0[4], s1[4];
     uint32_t coef[4], vmask = 0;
@@ -181,20 +181,36 @@ __global__ void __launch_bounds__(256) k_pyramid_resize4(uint8_t* __restrict__ d
     }
     const int q0 = smin >> 2;
     const uint32_t sh = (uint32_t)(smin & 3) * 8;
+    // per-row constants of the CTA's rows, computed once: word offsets of the two source rows and the vertical coefficients
+    // (<< 16 for the multiply-high) — the row loop then costs one 128-bit shared load instead of a reflect, a table load and
+    // two 64-bit address computations per row and thread
+    extern __shared__ uint4 rowTab[];
+    const int row0 = blockIdx.y * rowsPerCta, rowEnd = min(row0 + rowsPerCta, drows);
+    const int spq = spitch >> 2;
+    for (int r = row0 + threadIdx.x; r < rowEnd; r += blockDim.x) {
+        const ResizeTab yt = ytab[reflect101(r - EDGE, dh)];
+        rowTab[r - row0] = make_uint4((uint32_t)((int)yt.s0 * spq), (uint32_t)((int)yt.s1 * spq), (uint32_t)(uint16_t)yt.c0 << 16,
+                                      (uint32_t)(uint16_t)yt.c1 << 16);
+    }
+    __syncthreads();
+    if (!inRow) return;
     const uint32_t* __restrict__ sInt =
         reinterpret_cast<const uint32_t*>(splane + (long long)f * sStride + (long long)EDGE * spitch + XOFF) + q0;
-    const int spq = spitch >> 2;
     uint8_t* __restrict__ dbase = dplane + (long long)f * dStride + bx;
-    const int rowEnd = min(blockIdx.y * rowsPerCta + rowsPerCta, drows);
-    for (int py = blockIdx.y * rowsPerCta + warp; py < rowEnd; py += 8) {
-        const ResizeTab yt = ytab[reflect101(py - EDGE, dh)];
-        const uint32_t* __restrict__ r0 = sInt + (int)yt.s0 * spq;
-        const uint32_t* __restrict__ r1 = sInt + (int)yt.s1 * spq;
-        const uint32_t a0 = __ldg(r0), a1 = __ldg(r0 + 1), a2 = __ldg(r0 + 2);
-        const uint32_t b0w = __ldg(r1), b1w = __ldg(r1 + 1), b2w = __ldg(r1 + 2);
+    // software pipeline: the six source words of the NEXT row are in flight while the current row is blended and stored
+    int py = row0 + warp;
+    if (py >= rowEnd) return;
+    uint4 rt = rowTab[py - row0];
+    uint32_t a0 = __ldg(sInt + rt.x), a1 = __ldg(sInt + rt.x + 1), a2 = __ldg(sInt + rt.x + 2);
+    uint32_t b0w = __ldg(sInt + rt.y), b1w = __ldg(sInt + rt.y + 1), b2w = __ldg(sInt + rt.y + 2);
+    for (; py < rowEnd; py += 8) {
+        const int pn = py + 8 < rowEnd ? py + 8 : py;  // (the last row loads itself again: harmless)
+        const uint4 rn = rowTab[pn - row0];
+        const uint32_t na0 = __ldg(sInt + rn.x), na1 = __ldg(sInt + rn.x + 1), na2 = __ldg(sInt + rn.x + 2);
+        const uint32_t nb0 = __ldg(sInt + rn.y), nb1 = __ldg(sInt + rn.y + 1), nb2 = __ldg(sInt + rn.y + 2);
         const uint32_t A0 = __funnelshift_r(a0, a1, sh), A1 = __funnelshift_r(a1, a2, sh);
         const uint32_t B0 = __funnelshift_r(b0w, b1w, sh), B1 = __funnelshift_r(b1w, b2w, sh);
-        const uint32_t m0 = (uint32_t)(uint16_t)yt.c0 << 16, m1 = (uint32_t)(uint16_t)yt.c1 << 16;
+        const uint32_t m0 = rt.z, m1 = rt.w;
         uint32_t v = 0;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -203,7 +219,10 @@ __global__ void __launch_bounds__(256) k_pyramid_resize4(uint8_t* __restrict__ d
             const uint32_t val = (__umulhi(m0, h0 >> 4) + __umulhi(m1, h1 >> 4) + 2u) >> 2;  // <= 255
             v |= val << (8 * j);
         }
-        *reinterpret_cast<uint32_t*>(dbase + (long long)py * dpitch) = v & vmask;
+        *reinterpret_cast<uint32_t*>(dbase + (uint32_t)py * (uint32_t)dpitch) = v & vmask;
+        rt = rn;
+        a0 = na0; a1 = na1; a2 = na2;
+        b0w = nb0; b1w = nb1; b2w = nb2;
     }
 }
 
@@ -242,7 +261,7 @@ int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, c
     const int gx = (D.pitch + 127) / 128, rpc = rows_per_cta(D.rows, gx, batch);
     dim3 grid(gx, (D.rows + rpc - 1) / rpc, batch);
     if (areaFast & 2)  // bit 1: every thread's source window fits 8 bytes -> word-based kernel
-        k_pyramid_resize4<<<grid, 256, 0, s>>>(dPlane, D.w, D.h, D.pitch, D.rows, D.planeStride, sPlane, S.pitch,
+        k_pyramid_resize4<<<grid, 256, (size_t)rpc * sizeof(uint4), s>>>(dPlane, D.w, D.h, D.pitch, D.rows, D.planeStride, sPlane, S.pitch,
                                                  S.planeStride, xtab, ytab, rpc);
     else
         k_pyramid_resize<<<grid, 256, 0, s>>>(dPlane, D.w, D.h, D.pitch, D.rows, D.planeStride, sPlane, S.pitch,
