@@ -33,28 +33,59 @@ WORKLOADS = {  # reference YAMLs: Examples/Monocular/KITTI00-02.yaml, TUM1.yaml,
     "euroc": dict(shape=(480, 752), nfeatures=1200, bytes_per_frame=5_991_655, sum_p=1_117_367),
 }
 SCALE, LEVELS, INI_TH, MIN_TH = 1.2, 8, 20, 7
-# DRAM bytes per frame (dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of a 512-frame kitti
-# launch, divided by 512): profiles/r01_ncu_full_b.csv (pyramid, blur) and profiles/r01_ncu_full_c.csv (the others).
-NCU_TRAFFIC_PER_FRAME = {"kitti": {"Pyramid/Resize": 3_415_000, "FAST+Grid": 1_686_000, "Make quadtree": 182_000,
-                                   "Gaussian Blur": 3_283_000, "Compute angle + ORB descriptor + Compute scale": 3_049_000}}
-# warp instructions per frame of the whole extractor step (ncu smsp__inst_executed.sum over the 12 kernels of a 512-frame launch,
-# profiles/r01_ncu_full_final.csv): the path is bound by instruction issue, not by HBM
-NCU_WARP_INST_PER_FRAME = {"kitti": 4_017_030_987 / 512}
+# roofline.traffic / roofline.issue come from profiles/ncu_latest.json, which tools/ncu_summary.py --json writes from an
+# `ncu --set full` capture of one device-resident step (per workload; the file records the SHA-256 of the kernel sources it was
+# taken from, and the line says whether they still match)
+STAGE_KERNELS = {"Pyramid/Resize": ("k_pyramid_base", "k_pyramid_base_edges", "k_pyramid_resize4", "k_pyramid_resize"), "FAST+Grid": ("k_fast_strips",),
+                 "Make quadtree": ("k_quadtree",), "Gaussian Blur": ("k_blur7",),
+                 "Compute angle + ORB descriptor + Compute scale": ("k_orient_describe",)}
+
+
+def ncu_latest(workload):
+    import hashlib
+    path = os.path.join(ROOT, "profiles", "ncu_latest.json")
+    try:
+        w = json.load(open(path))["workloads"][workload]
+    except Exception:
+        return None
+    src = os.path.join(ROOT, "orb_slam_cuda_b200", "csrc")
+    cur = {f: hashlib.sha256(open(os.path.join(src, f), "rb").read()).hexdigest()[:12] for f in w.get("kernel_sources_sha256_12", {}) if os.path.exists(os.path.join(src, f))}
+    w["sources_match"] = cur == w.get("kernel_sources_sha256_12")
+    return w
+
+
+def ncu_stage(workload, stage, key):
+    w = ncu_latest(workload)
+    if not w:
+        return None
+    return sum(k[key] for n, k in w["kernels"].items() if n in STAGE_KERNELS.get(stage, ()))
+
+
 METRIC = "frames/s ORB extract @1241x376 2k feats"
 
 
 def issue_roofline(workload, frames_per_s_per_gpu, clocks):
     """The bound that actually holds for this integer path: warp instructions issued per second against 148 SMs x 4 schedulers x
     SM clock (one warp instruction per scheduler per cycle)."""
-    per_frame = NCU_WARP_INST_PER_FRAME.get(workload)
-    if not per_frame:
+    w = ncu_latest(workload)
+    if not w:
         return None
+    per_frame = sum(k["warp_inst_per_frame"] for k in w["kernels"].values())
     sm_hz = ((clocks or {}).get("sm_mhz") or 1965.0) * 1e6
     peak = 148 * 4 * sm_hz
     ach = frames_per_s_per_gpu * per_frame
     return {"bound": "warp-instruction issue", "achieved": ach / 1e12, "peak": peak / 1e12, "unit": "T warp-inst/s", "frac": ach / peak,
             "warp_instructions_per_frame": per_frame,
-            "source": "ncu smsp__inst_executed.sum over the step's 12 kernels (profiles/r01_ncu_full_final.csv), whole step, all stages"}
+            "source": f"ncu smsp__inst_executed.sum over the step's kernels (profiles/ncu_latest.json <- {w['report']}; sources match: {w['sources_match']})"}
+
+
+def config_for(args):
+    """The `config` object of both arms (the reference arm times a bounded sample of the same workload: cpu_baseline.sample)."""
+    wl = WORKLOADS[args.workload]
+    h, w = wl["shape"]
+    return {"workload": f"{args.workload}: offline batch of {w}x{h} frames, {wl['nfeatures']} features, {LEVELS} levels x{SCALE}, FAST {INI_TH}/{MIN_TH}",
+            "frames_per_gpu_per_step": args.batch, "sharding": "frame k -> rank k mod N, no collective",
+            "l2": f"inputs {args.batch * w * h / 1e6:.0f} MB + intermediates per step exceed the 126 MB L2"}
 
 
 def parse():
@@ -67,6 +98,7 @@ def parse():
     ap.add_argument("--batch", type=int, default=512, help="frames per GPU per step")
     ap.add_argument("--cpu-frames", type=int, default=0, help="frames of the cpu_baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-threads", type=int, default=0, help="--impl reference: host threads (0 = all the process may use)")
     ap.add_argument("--no-match", action="store_true")
     ap.add_argument("--keyframes", type=int, default=1024, help="keyframes of the all-vs-all leg (config 5 names 4096: 16x the time)")
     ap.add_argument("--no-latency", action="store_true")
@@ -359,6 +391,15 @@ def tracking_leg(X, k1, d1, k2, d2, bounds, p50, cpu):
 
     out["search_by_projection_2000"] = {"p50_ms": p50(run_sbp), "matches": int(r["sbp"][0]),
                                         "what": "frame-to-frame, th 15, mono, TH_HIGH 100, rotation check; host buffers in and out"}
+    # the same call with the current frame resident on the device (orbx_frame: keypoints, descriptors and the 64 x 48 grid uploaded and
+    # binned once per frame, as Tracking matches against the current frame several times)
+    fr = X.DeviceFrame(k2, d2, bounds)
+
+    def run_sbp_h():
+        r["sbph"] = m.SearchByProjectionFrame(x3, one1, one1, d1, k1["octave"], k1["angle"], fr, zero2, cam, 386.1448, sf, 15.0, 0)
+
+    out["search_by_projection_2000"]["p50_ms_frame_handle"] = p50(run_sbp_h)
+    assert r["sbph"][0] == r["sbp"][0] and np.array_equal(r["sbph"][1], r["sbp"][1])
     k, L, parent, leaf, desc, weight = orbvoc_shaped_vocabulary()
     voc = X.ORBVocabulary(k, L, 0, 0, parent, leaf, desc, weight)
     # features that descend like real ones: leaf descriptors of the tree with a few bits flipped
@@ -423,8 +464,8 @@ def run_reference(args, emit=print):
     if rank != 0:
         return
     wl = WORKLOADS[args.workload]
-    threads = host_threads()
-    per_step = max(64, 16 * threads)  # bounded sample of the workload per step
+    threads = args.cpu_threads or host_threads()
+    per_step = max(64, 16 * threads) if threads > 1 else 24  # bounded sample of the workload per step
     from oracle import oracle_lib as O
     frames = make_frames(args.workload, per_step, first=1000)
     a = (wl["nfeatures"], SCALE, LEVELS, INI_TH, MIN_TH, threads)
@@ -441,8 +482,7 @@ def run_reference(args, emit=print):
         "value": value, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {w}x{h} frames, {wl['nfeatures']} features, {LEVELS} levels x{SCALE}, FAST {INI_TH}/{MIN_TH}",
-                   "frames_per_step": per_step},
+        "config": config_for(args),
         "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "port",
                          "sample": f"{per_step} frames per step x {args.steps} steps, frame-parallel over {threads} threads"},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -550,7 +590,29 @@ def run_ours(args, emit=print):
         ex.extract_batch_wait()
 
     e2e_s = e2e_sync_s = float("nan")
+    h2d_gbs = d2h_gbs = float("nan")
     if not args.no_e2e:
+        # what the box gives this rank while every rank copies at once: the bare pinned-host -> device and device -> pinned-host
+        # rates of the step's own buffers (no kernels).  e2e cannot beat frames_per_step / (H2D time) on this box.
+        d_tmp = torch.empty_like(d_kps)
+        h_tmp = torch.empty((B, cap, 7), dtype=torch.int32).pin_memory()
+        for direction in ("h2d", "d2h"):
+            barrier()
+            c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            c0.record()
+            for _ in range(5):
+                if direction == "h2d":
+                    d_frames.copy_(h_frames, non_blocking=True)
+                else:
+                    h_tmp.copy_(d_tmp, non_blocking=True)
+            c1.record()
+            barrier()
+            gbs = (B * w * h if direction == "h2d" else d_tmp.numel() * 4) * 5 / (c0.elapsed_time(c1) * 1e-3) / 1e9
+            if direction == "h2d":
+                h2d_gbs = gbs
+            else:
+                d2h_gbs = gbs
+        del d_tmp, h_tmp
         for _ in range(W):
             step_host()
         barrier()
@@ -576,10 +638,10 @@ def run_ours(args, emit=print):
 
     match = None if args.no_match else match_leg(X, torch, dist, rank, world, stream, 2, args.keyframes)
 
-    t = torch.tensor([ms, e2e_s * 1e3, e2e_sync_s * 1e3], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms, e2e_s * 1e3, e2e_sync_s * 1e3, -h2d_gbs, -d2h_gbs], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_ms, e2e_sync_ms = float(t[0]), float(t[1]), float(t[2])
+    ms, e2e_ms, e2e_sync_ms, h2d_gbs, d2h_gbs = float(t[0]), float(t[1]), float(t[2]), -float(t[3]), -float(t[4])  # copy rates: slowest rank
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -601,19 +663,21 @@ def run_ours(args, emit=print):
         "metric": METRIC if args.workload == "kitti" else f"frames/s ORB extract ({args.workload})",
         "value": value, "unit": "frames/s", "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": ms / K,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: offline batch of {w}x{h} frames, {wl['nfeatures']} features, {LEVELS} levels x{SCALE}, FAST {INI_TH}/{MIN_TH}",
-                   "frames_per_gpu_per_step": B, "sharding": "frame k -> rank k mod N, no collective",
-                   "l2": f"inputs {B * w * h / 1e6:.0f} MB + intermediates per step exceed the 126 MB L2", "mean_keypoints": float(counts.mean())},
+        "config": config_for(args), "mean_keypoints": float(counts.mean()),
         "clocks": clocks,
         "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": B * w * h,
                 "d2h_bytes_per_step": B * cap * 60 + B * 4 + 4, "ms_per_step": e2e_ms / K,
                 "path": "orbx_extract_batch_async / orbx_extract_batch_wait, two steps in flight, pinned host buffers",
+                "h2d_ceiling_gbs": h2d_gbs, "d2h_ceiling_gbs": d2h_gbs,
+                "h2d_bound_frames_per_s": world * h2d_gbs * 1e9 / (w * h),
+                "ceiling": "bare copies of the step's own pinned buffers, all ranks at once, slowest rank; e2e <= N x h2d_ceiling / bytes per frame on this box",
                 "sync": {"value": total_frames / (e2e_sync_ms * 1e-3), "ms_per_step": e2e_sync_ms / K,
                          "path": "blocking orbx_extract_batch, one step at a time"}},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": (NCU_TRAFFIC_PER_FRAME.get(args.workload, {}).get(dom) or 0) * B or None,
-                     "traffic_source": "ncu dram__bytes_read+write of this kernel on a 512-frame launch, scaled to this batch (profiles/r01_ncu_full_*.csv)",
+                     "traffic": (ncu_stage(args.workload, dom, "dram_bytes_per_frame") or 0) * B or None,
+                     "traffic_source": "ncu dram__bytes_read + dram__bytes_write of this stage's kernels per frame x frames per launch "
+                                       f"(profiles/ncu_latest.json; sources match: {(ncu_latest(args.workload) or {}).get('sources_match')})",
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": dom_bytes,
                      "avg_launch_ms": stage[dom],
                      "pipeline": {"bytes_per_frame": wl["bytes_per_frame"], "achieved": value / world * wl["bytes_per_frame"] / 1e9,
@@ -634,14 +698,18 @@ def run_ours(args, emit=print):
     if world == 1 and not args.no_latency:
         line["latency"] = latency_leg(X, wl, w, h, args.workload, cpu=not args.no_cpu_baseline and world == 1)
     if not args.no_cpu_baseline and world == 1:
-        threads = host_threads()
-        n = args.cpu_frames or max(threads, 16 * threads)
-        rate, secs, done = cpu_extract_rate(args.workload, n, threads, min_secs=12.0)
-        line["cpu_baseline"] = {"value": rate, "unit": "frames/s", "cores": threads, "kind": "port",
-                                "sample": f"{done} frames of the same workload ({n} distinct) in {secs:.1f} s, frame-parallel over {threads} threads"}
-        rate1, secs1, done1 = cpu_extract_rate(args.workload, 16, 1, min_secs=3.0)
-        line["cpu_baseline"]["single_thread_frames_per_s"] = rate1
-        line["cpu_baseline"]["single_thread_sample"] = f"{done1} frames in {secs1:.1f} s on 1 thread"
+        # the CPU arm runs in a FRESH process (this one holds pinned memory, a CUDA context and torch's thread pool, which made the
+        # in-process sample up to 30 % slower than `--impl reference` on the same box): the reference arm itself, bounded sample
+        def ref_arm(extra):
+            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--workload", args.workload] + extra,
+                               capture_output=True, text=True, timeout=900)
+            return json.loads(r.stdout.strip().splitlines()[-1])
+        ref = ref_arm(["--steps", "3", "--warmup", "1"])
+        line["cpu_baseline"] = dict(ref["cpu_baseline"])
+        line["cpu_baseline"]["how"] = "bench.py --impl reference in a fresh subprocess (the same code path as the reference arm)"
+        one = ref_arm(["--steps", "2", "--warmup", "1", "--cpu-threads", "1"])
+        line["cpu_baseline"]["single_thread_frames_per_s"] = one["value"]
+        line["cpu_baseline"]["single_thread_sample"] = one["cpu_baseline"]["sample"]
     emit(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()

@@ -247,6 +247,27 @@ int orbx_cvt_color_gray(const uint8_t* src, long long src_stride, int w, int h, 
 int orbx_cvt_color_gray_device(const uint8_t* d_src, long long src_stride, int w, int h, int channels, int flags, uint8_t* d_dst,
                                long long dst_stride, void* stream);
 
+/* ---- a frame that stays on the device between matcher calls (Frame::AssignFeaturesToGrid, src/Frame.cc:229-244) ----
+ * Tracking runs several matchers against the CURRENT frame (TrackWithMotionModel's SearchByProjection, src/Tracking.cc:962,968;
+ * SearchLocalPoints' :1270-1277).  orbx_frame_create uploads its undistorted keypoints (mvKeysUn), descriptors and right
+ * coordinates (mvuRight, may be NULL) once and bins the 64 x 48 grid (mGrid) on the device; the *_frame matcher entries take the
+ * handle where the host-array entries take k2 / n2 / desc2 / u_right2 / bounds, and skip the uploads and the binning.  Results are
+ * identical.  orbx_frame_grid_host copies the grid out for inspection: cell (ix, iy) = cell_start[ix*48 + iy] ..
+ * cell_start[ix*48 + iy + 1] of `sorted` (keypoint indices in mGrid's push_back order). */
+typedef struct orbx_frame orbx_frame;
+int orbx_frame_create(const orbx_keypoint* kps_un, int n, const uint8_t* desc, const float* u_right, const float bounds[4],
+                      orbx_frame** out);
+void orbx_frame_destroy(orbx_frame* f);
+int orbx_frame_size(const orbx_frame* f);
+int orbx_frame_grid_host(const orbx_frame* f, int* cell_start /* 64*48 + 1 */, int* sorted /* n */);
+int orbx_search_by_projection_frame(int n1, const float* x3dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mp_desc1,
+                                    const int* octave1, const float* angle1, const orbx_frame* f2, const uint8_t* occupied2,
+                                    const float cam[4], float mbf, const float* scale_factors, int nlevels, float th, int direction,
+                                    int check_ori, int orb_dist, int flags, int* match21, int* nmatches);
+int orbx_search_by_projection_map_frame(int n1, const float* proj, const float* view_cos, const int* level1, const uint8_t* valid1,
+                                        const uint8_t* obs1, const uint8_t* mp_desc1, const orbx_frame* f2, const uint8_t* occupied2,
+                                        const float* scale_factors, int nlevels, float th, float nnratio, int* match21, int* nmatches);
+
 /* Frame::UndistortKeyPoints (src/Frame.cc:403-433): cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) on the keypoint
  * coordinates — OpenCV's five-iteration inverse of the k1 k2 p1 p2 [k3] model in double, re-projected with the same K — every
  * other field of the keypoint copied (mvKeysUn[i] = mvKeys[i] with the new pt).  K = {fx, fy, cx, cy}; dist = ndist (0..5)

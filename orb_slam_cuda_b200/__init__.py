@@ -315,6 +315,41 @@ class ORBmatcher:
                                                    C.byref(n)))
         return n.value, m21[:n2]
 
+    def SearchByProjectionFrame(self, x3Dc, valid1, obs1, mp_desc1, octave1, angle1, frame2: "DeviceFrame", occupied2, cam, mbf, scale_factors,
+                                th: float, direction: int = 0, orb_dist: int = TH_HIGH, depth_test: bool = True):
+        """SearchByProjection against a frame that already lives on the device (orbx_search_by_projection_frame)."""
+        x3Dc = np.ascontiguousarray(x3Dc, dtype=np.float32)
+        valid1, obs1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, obs1, occupied2))
+        mp_desc1 = np.ascontiguousarray(mp_desc1, dtype=np.uint8)
+        octave1 = np.ascontiguousarray(octave1, dtype=np.int32)
+        angle1 = np.ascontiguousarray(angle1, dtype=np.float32)
+        cam = np.asarray(cam, dtype=np.float32)
+        sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+        n2 = frame2.n
+        m21 = np.empty(max(n2, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_search_by_projection_frame(valid1.size, _p(x3Dc), _p(valid1), _p(obs1), _p(mp_desc1), _p(octave1), _p(angle1),
+                                                     frame2._h, _p(occupied2), _p(cam), C.c_float(mbf), _p(sf), sf.size, C.c_float(th),
+                                                     int(direction), int(self.mbCheckOrientation), int(orb_dist), 0 if depth_test else 1,
+                                                     _p(m21), C.byref(n)))
+        return n.value, m21[:n2]
+
+    def SearchByProjectionMapFrame(self, proj, view_cos, level1, valid1, obs1, mp_desc1, frame2: "DeviceFrame", occupied2, scale_factors, th: float):
+        """SearchByProjection(F, vpMapPoints, th) against a device-resident frame (orbx_search_by_projection_map_frame)."""
+        proj = np.ascontiguousarray(proj, dtype=np.float32)
+        view_cos = np.ascontiguousarray(view_cos, dtype=np.float32)
+        level1 = np.ascontiguousarray(level1, dtype=np.int32)
+        valid1, obs1, occupied2 = (np.ascontiguousarray(a, dtype=np.uint8) for a in (valid1, obs1, occupied2))
+        mp_desc1 = np.ascontiguousarray(mp_desc1, dtype=np.uint8)
+        sf = np.ascontiguousarray(scale_factors, dtype=np.float32)
+        n2 = frame2.n
+        m21 = np.empty(max(n2, 1), np.int32)
+        n = C.c_int(0)
+        _check(lib().orbx_search_by_projection_map_frame(valid1.size, _p(proj), _p(view_cos), _p(level1), _p(valid1), _p(obs1), _p(mp_desc1),
+                                                         frame2._h, _p(occupied2), _p(sf), sf.size, C.c_float(th), C.c_float(self.mfNNratio),
+                                                         _p(m21), C.byref(n)))
+        return n.value, m21[:n2]
+
     def SearchByProjectionSim3(self, uvr, level1, valid1, mp_desc1, kps2, desc2, occupied2, bounds, th_dist: int = TH_LOW):
         """SearchByProjection(pKF, Scw, vpPoints, vpMatched, th), src/ORBmatcher.cc:290-403, from the radius search on.
         Returns (nmatches, match21)."""
@@ -529,3 +564,32 @@ def UndistortKeyPoints(kps: np.ndarray, K, dist) -> np.ndarray:
     out = np.empty_like(kps)
     _check(lib().orbx_undistort_keypoints(_p(kps), kps.size, _p(Kf), _p(d) if d.size else None, int(d.size), _p(out)))
     return out
+
+
+class DeviceFrame:
+    """orbx_frame: the undistorted keypoints, descriptors, right coordinates and the 64 x 48 grid (Frame::AssignFeaturesToGrid,
+    reference src/Frame.cc:229-244) of one frame, resident on the device between matcher calls."""
+
+    def __init__(self, kps_un, desc, bounds, u_right=None):
+        kps_un = np.ascontiguousarray(kps_un, dtype=KP_DTYPE)
+        desc = np.ascontiguousarray(desc, dtype=np.uint8)
+        ur = None if u_right is None else np.ascontiguousarray(u_right, dtype=np.float32)
+        b = np.asarray(bounds, dtype=np.float32)
+        self._h = C.c_void_p()
+        self.n = int(kps_un.size)
+        _check(lib().orbx_frame_create(_p(kps_un), self.n, _p(desc), _p(ur) if ur is not None else None, _p(b), C.byref(self._h)))
+
+    def grid(self):
+        """(cell_start [64*48 + 1], sorted [n]): cell (ix, iy) holds sorted[cell_start[ix*48 + iy] : cell_start[ix*48 + iy + 1]]."""
+        cs, so = np.empty(64 * 48 + 1, np.int32), np.empty(max(self.n, 1), np.int32)
+        lib().orbx_frame_grid_host.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        _check(lib().orbx_frame_grid_host(self._h, _p(cs), _p(so)))
+        return cs, so[:self.n]
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h and _lib is not None:
+            _lib.orbx_frame_destroy.argtypes = [C.c_void_p]
+            _lib.orbx_frame_destroy.restype = None
+            _lib.orbx_frame_destroy(h)
+            self._h = None

@@ -703,7 +703,7 @@ static int extract_batch_impl(orbx_extractor* ex, const uint8_t* frames, int bat
     // The batch is cut into chunks that flow through three streams — H2D | kernels | D2H — so the copies of chunk c+1 and
     // c-1 overlap the kernels of chunk c.  The scratch (pyramids, cell lists ...) holds TWO chunks: even and odd chunks
     // run their kernels on two streams ("lanes") over disjoint halves of it; small batches are a single chunk.
-    static const int chunkPref = []() { const char* e = getenv("ORBX_PIPE_CHUNK"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 64; }();
+    static const int chunkPref = []() { const char* e = getenv("ORBX_PIPE_CHUNK"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 128; }();
     static const bool taper = []() { const char* e = getenv("ORBX_PIPE_TAPER"); return !e || atoi(e) != 0; }();
     const int nFull = std::max(1, batch / chunkPref), C = (batch + nFull - 1) / nFull;
     // chunk sizes: C each; with >= 4 chunks the first and the last are halved, so the kernels start after a short first

@@ -502,8 +502,10 @@ int launch_search_by_projection(int n1, const float* x3Dc, const uint8_t* valid1
     }
     static size_t configured[ORBX_MAX_DEVICES] = {};
     if (int rcAttr = ensure_dynamic_smem((const void*)k_sbp_resolve, smem, configured)) return rcAttr;
-    k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
-    count_launch();
+    if (cellOf) {  // null: sorted / cellStart hold the frame's grid already (orbx_frame)
+        k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
+        count_launch();
+    }
     k_sbp_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(n1, x3Dc, valid1, reinterpret_cast<const uint4*>(mpDesc1), octave1, k2,
                                                     reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, nullptr, P,
                                                     sorted, cellStart, cand, candCap, candCnt, dStatus);
@@ -589,8 +591,10 @@ int launch_search_by_projection_map(int n1, const float* proj, const float* view
     }
     static size_t configured[ORBX_MAX_DEVICES] = {};
     if (int rcAttr = ensure_dynamic_smem((const void*)k_sbpm_resolve, smem, configured)) return rcAttr;
-    k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
-    count_launch();
+    if (cellOf) {  // null: sorted / cellStart hold the frame's grid already (orbx_frame)
+        k_sfi_grid<<<1, 1024, 0, s>>>(k2, n2, P.minX, P.minY, P.invW, P.invH, cellOf, sorted, cellStart);
+        count_launch();
+    }
     k_sbp_candidates<<<(n1 + 7) / 8, 256, 0, s>>>(n1, proj, valid1, reinterpret_cast<const uint4*>(mpDesc1), level1, k2,
                                                     reinterpret_cast<const uint4*>(desc2), uRight2, occupied2, scaleFactors, viewCos,
                                                     P, sorted, cellStart, cand, candCap, candCnt, dStatus);
@@ -705,6 +709,15 @@ int launch_fuse_match(int n1, const float* uvr, const float* ur1, const int* lev
     k_fuse_match<<<(n1 + 7) / 8, 256, 0, s>>>(n1, uvr, ur1, level1, valid1, reinterpret_cast<const uint4*>(mpDesc1), k2,
                                                 reinterpret_cast<const uint4*>(desc2), uRight2, invLevelSigma2, bounds[0], bounds[2], invW,
                                                 invH, sorted, cellStart, bestIdx, bestDist);
+    count_launch();
+    ORBX_CUDA(cudaGetLastError());
+    return ORBX_OK;
+}
+
+// Frame::AssignFeaturesToGrid (src/Frame.cc:229-244) on its own: the 64 x 48 grid of a frame that stays on the device (orbx_frame)
+int launch_frame_grid(const orbx_keypoint* k, int n, const float bounds[4], int* cellOf, int* sorted, int* cellStart, cudaStream_t s) {
+    const float invW = (float)GRID_COLS / (bounds[1] - bounds[0]), invH = (float)GRID_ROWS / (bounds[3] - bounds[2]);
+    k_sfi_grid<<<1, 1024, 0, s>>>(k, n, bounds[0], bounds[2], invW, invH, cellOf, sorted, cellStart);
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -37,6 +37,7 @@ struct Workspace {  // one per host thread and device
 
 thread_local Workspace tls[8];
 
+
 int workspace(Workspace** out) {
     int ndev = 0;
     cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -68,7 +69,66 @@ int upload(DevBuf& buf, const void* src, size_t bytes, cudaStream_t s) {
 
 }  // namespace
 
+// A frame whose undistorted keypoints, descriptors, right coordinates and 64 x 48 grid stay on the device between matcher calls
+struct orbx_frame {
+    int device = 0, n = 0;
+    bool hasRight = false;
+    float bounds[4] = {0, 0, 0, 0};
+    DevBuf kps, desc, uright, grid;  // grid: cellOf[n] | sorted[n] | cellStart[64 * 48 + 1]
+    int* sorted() const { return grid.as<int>() + n; }
+    int* cellStart() const { return grid.as<int>() + 2 * (size_t)n; }
+};
+
 extern "C" {
+
+int orbx_frame_create(const orbx_keypoint* kps_un, int n, const uint8_t* desc, const float* u_right, const float bounds[4], orbx_frame** out) {
+    if (!out || n < 0 || n > 65535 || !bounds || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2]) || (n > 0 && (!kps_un || !desc))) {
+        set_error("orbx_frame_create: bad argument (n <= 65535, bounds = {minX, maxX, minY, maxY})");
+        return ORBX_E_INVALID;
+    }
+    *out = nullptr;
+    Workspace* w;
+    int rc = workspace(&w);
+    if (rc) return rc;
+    orbx_frame* f = new orbx_frame();
+    f->device = w->device;
+    f->n = n;
+    f->hasRight = u_right != nullptr;
+    memcpy(f->bounds, bounds, sizeof f->bounds);
+    cudaStream_t s = w->stream;
+    const size_t nn = (size_t)std::max(n, 1);
+    if ((rc = upload(f->kps, kps_un, (size_t)n * sizeof(orbx_keypoint), s)) || (rc = upload(f->desc, desc, (size_t)n * 32, s)) ||
+        (rc = upload(f->uright, u_right, u_right ? (size_t)n * 4 : 0, s)) || (rc = f->grid.ensure((2 * nn + 64 * 48 + 1) * 4)) ||
+        (rc = launch_frame_grid(f->kps.as<orbx_keypoint>(), n, bounds, f->grid.as<int>(), f->sorted(), f->cellStart(), s))) {
+        orbx_frame_destroy(f);
+        return rc;
+    }
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) {
+        set_error("orbx_frame_create: %s", cudaGetErrorString(e));
+        orbx_frame_destroy(f);
+        return ORBX_E_CUDA;
+    }
+    *out = f;
+    return ORBX_OK;
+}
+
+void orbx_frame_destroy(orbx_frame* f) {
+    if (!f) return;
+    cudaSetDevice(f->device);
+    f->kps.release(); f->desc.release(); f->uright.release(); f->grid.release();
+    delete f;
+}
+
+int orbx_frame_size(const orbx_frame* f) { return f ? f->n : 0; }
+
+int orbx_frame_grid_host(const orbx_frame* f, int* cell_start, int* sorted) {
+    if (!f || !cell_start || (f->n > 0 && !sorted)) { set_error("orbx_frame_grid_host: bad argument"); return ORBX_E_INVALID; }
+    ORBX_CUDA(cudaSetDevice(f->device));
+    ORBX_CUDA(cudaMemcpy(cell_start, f->cellStart(), (64 * 48 + 1) * 4, cudaMemcpyDeviceToHost));
+    if (f->n > 0) ORBX_CUDA(cudaMemcpy(sorted, f->sorted(), (size_t)f->n * 4, cudaMemcpyDeviceToHost));
+    return ORBX_OK;
+}
 
 int orbx_hamming_distance(const uint8_t* a, const uint8_t* b, int n, int* dist) {
     if (n < 0 || (n > 0 && (!a || !b || !dist))) { set_error("orbx_hamming_distance: bad argument"); return ORBX_E_INVALID; }
@@ -343,14 +403,19 @@ int orbx_search_by_projection(int n1, const float* x3dc, const uint8_t* valid1, 
                                         nmatches);
 }
 
-int orbx_search_by_projection_ex(int n1, const float* x3dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mp_desc1,
-                                 const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
-                                 const float* u_right2, const uint8_t* occupied2, const float cam[4], float mbf,
-                                 const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
-                                 int check_ori, int orb_dist, int flags, int* match21, int* nmatches) {
+} // extern "C"
+static int sbp_impl(const orbx_frame* fr, int n1, const float* x3dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mp_desc1,
+                    const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
+                    const float* u_right2, const uint8_t* occupied2, const float cam[4], float mbf,
+                    const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
+                    int check_ori, int orb_dist, int flags, int* match21, int* nmatches) {
+    if (fr) {  // the frame's keypoints, descriptors, right coordinates and grid are on the device already
+        n2 = fr->n;
+        bounds = fr->bounds;
+    }
     if (n1 < 0 || n2 < 0 || !bounds || !cam || !nmatches || !scale_factors || nlevels < 1 || nlevels > ORBX_MAX_LEVELS ||
         direction < 0 || direction > 2 || (n1 > 0 && (!x3dc || !valid1 || !obs1 || !mp_desc1 || !octave1 || !angle1)) ||
-        (n2 > 0 && (!k2 || !desc2 || !occupied2 || !match21)) || n2 > 65535 || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) {
+        (n2 > 0 && ((!fr && (!k2 || !desc2)) || !occupied2 || !match21)) || n2 > 65535 || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) {
         set_error("orbx_search_by_projection: bad argument (n2 <= 65535, direction 0..2, bounds = {minX, maxX, minY, maxY})");
         return ORBX_E_INVALID;
     }
@@ -377,26 +442,27 @@ int orbx_search_by_projection_ex(int n1, const float* x3dc, const uint8_t* valid
     memcpy(hp + oO, octave1, (size_t)n1 * 4);
     memset(hp + oS, 0, ORBX_MAX_LEVELS * 4);
     memcpy(hp + oS, scale_factors, (size_t)nlevels * 4);
-    if (u_right2) memcpy(hp + oU, u_right2, (size_t)n2 * 4);
+    if (u_right2 && !fr) memcpy(hp + oU, u_right2, (size_t)n2 * 4);
     memcpy(hp + oD, mp_desc1, (size_t)n1 * 32);
     memcpy(hp + oV, valid1, n1);
     memcpy(hp + oB, obs1, n1);
     memcpy(hp + oC, occupied2, n2);
     ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
-    if ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
+    if ((!fr && ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)))) ||
         (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
         (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
     ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
     const uint8_t* dp = w->a.as<uint8_t>();
-    int* cellOf = w->f.as<int>();
-    int* sorted = cellOf + n2;
-    int* cellStart = sorted + n2;
+    int* cellOf = fr ? nullptr : w->f.as<int>();
+    int* sorted = fr ? fr->sorted() : cellOf + n2;
+    int* cellStart = fr ? fr->cellStart() : sorted + n2;
     int* dN = w->status.as<int>() + 1;
+    const float* dUr = fr ? (fr->hasRight ? fr->uright.as<float>() : nullptr) : (u_right2 ? reinterpret_cast<const float*>(dp + oU) : nullptr);
     if ((rc = launch_search_by_projection(n1, reinterpret_cast<const float*>(dp + oX), dp + oV, dp + oB, dp + oD,
                                           reinterpret_cast<const int*>(dp + oO), reinterpret_cast<const float*>(dp + oA),
-                                          w->c.as<orbx_keypoint>(), n2, w->d.as<uint8_t>(),
-                                          u_right2 ? reinterpret_cast<const float*>(dp + oU) : nullptr, dp + oC,
+                                          fr ? fr->kps.as<orbx_keypoint>() : w->c.as<orbx_keypoint>(), n2,
+                                          fr ? fr->desc.as<uint8_t>() : w->d.as<uint8_t>(), dUr, dp + oC,
                                           reinterpret_cast<const float*>(dp + oS), cam, mbf, bounds, th, direction, check_ori, orb_dist,
                                           flags & ORBX_SBP_NO_DEPTH_TEST ? 1 : 0, cellOf, sorted, cellStart, w->g.as<uint32_t>(), candCap, w->h.as<int>(), w->out0.as<int>(), dN,
                                           w->status.as<int>(), s)))
@@ -413,13 +479,37 @@ int orbx_search_by_projection_ex(int n1, const float* x3dc, const uint8_t* valid
     return ORBX_OK;
 }
 
-int orbx_search_by_projection_map(int n1, const float* proj, const float* view_cos, const int* level1, const uint8_t* valid1,
-                                  const uint8_t* obs1, const uint8_t* mp_desc1, const orbx_keypoint* k2, int n2,
-                                  const uint8_t* desc2, const float* u_right2, const uint8_t* occupied2, const float bounds[4],
-                                  const float* scale_factors, int nlevels, float th, float nnratio, int* match21, int* nmatches) {
+extern "C" {
+int orbx_search_by_projection_ex(int n1, const float* x3dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mp_desc1,
+                                 const int* octave1, const float* angle1, const orbx_keypoint* k2, int n2, const uint8_t* desc2,
+                                 const float* u_right2, const uint8_t* occupied2, const float cam[4], float mbf,
+                                 const float bounds[4], const float* scale_factors, int nlevels, float th, int direction,
+                                 int check_ori, int orb_dist, int flags, int* match21, int* nmatches) {
+    return sbp_impl(nullptr, n1, x3dc, valid1, obs1, mp_desc1, octave1, angle1, k2, n2, desc2, u_right2, occupied2, cam, mbf, bounds,
+                    scale_factors, nlevels, th, direction, check_ori, orb_dist, flags, match21, nmatches);
+}
+
+int orbx_search_by_projection_frame(int n1, const float* x3dc, const uint8_t* valid1, const uint8_t* obs1, const uint8_t* mp_desc1,
+                                    const int* octave1, const float* angle1, const orbx_frame* f2, const uint8_t* occupied2,
+                                    const float cam[4], float mbf, const float* scale_factors, int nlevels, float th, int direction,
+                                    int check_ori, int orb_dist, int flags, int* match21, int* nmatches) {
+    if (!f2) { set_error("orbx_search_by_projection_frame: null frame"); return ORBX_E_INVALID; }
+    return sbp_impl(f2, n1, x3dc, valid1, obs1, mp_desc1, octave1, angle1, nullptr, 0, nullptr, nullptr, occupied2, cam, mbf, nullptr,
+                    scale_factors, nlevels, th, direction, check_ori, orb_dist, flags, match21, nmatches);
+}
+
+} // extern "C"
+static int sbpm_impl(const orbx_frame* fr, int n1, const float* proj, const float* view_cos, const int* level1, const uint8_t* valid1,
+                     const uint8_t* obs1, const uint8_t* mp_desc1, const orbx_keypoint* k2, int n2,
+                     const uint8_t* desc2, const float* u_right2, const uint8_t* occupied2, const float bounds[4],
+                     const float* scale_factors, int nlevels, float th, float nnratio, int* match21, int* nmatches) {
+    if (fr) {
+        n2 = fr->n;
+        bounds = fr->bounds;
+    }
     if (n1 < 0 || n2 < 0 || !bounds || !nmatches || !scale_factors || nlevels < 1 || nlevels > ORBX_MAX_LEVELS ||
         (n1 > 0 && (!proj || !view_cos || !level1 || !valid1 || !obs1 || !mp_desc1)) ||
-        (n2 > 0 && (!k2 || !desc2 || !occupied2 || !match21)) || n2 > 65535 || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) {
+        (n2 > 0 && ((!fr && (!k2 || !desc2)) || !occupied2 || !match21)) || n2 > 65535 || !(bounds[1] > bounds[0]) || !(bounds[3] > bounds[2])) {
         set_error("orbx_search_by_projection_map: bad argument (n2 <= 65535, bounds = {minX, maxX, minY, maxY})");
         return ORBX_E_INVALID;
     }
@@ -446,26 +536,27 @@ int orbx_search_by_projection_map(int n1, const float* proj, const float* view_c
     memcpy(hp + oO, level1, (size_t)n1 * 4);
     memset(hp + oS, 0, ORBX_MAX_LEVELS * 4);
     memcpy(hp + oS, scale_factors, (size_t)nlevels * 4);
-    if (u_right2) memcpy(hp + oU, u_right2, (size_t)n2 * 4);
+    if (u_right2 && !fr) memcpy(hp + oU, u_right2, (size_t)n2 * 4);
     memcpy(hp + oD, mp_desc1, (size_t)n1 * 32);
     memcpy(hp + oV, valid1, n1);
     memcpy(hp + oB, obs1, n1);
     memcpy(hp + oC, occupied2, n2);
     ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
-    if ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
+    if ((!fr && ((rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)))) ||
         (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
         (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
     ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
     const uint8_t* dp = w->a.as<uint8_t>();
-    int* cellOf = w->f.as<int>();
-    int* sorted = cellOf + n2;
-    int* cellStart = sorted + n2;
+    int* cellOf = fr ? nullptr : w->f.as<int>();
+    int* sorted = fr ? fr->sorted() : cellOf + n2;
+    int* cellStart = fr ? fr->cellStart() : sorted + n2;
     int* dN = w->status.as<int>() + 1;
+    const float* dUr = fr ? (fr->hasRight ? fr->uright.as<float>() : nullptr) : (u_right2 ? reinterpret_cast<const float*>(dp + oU) : nullptr);
     if ((rc = launch_search_by_projection_map(n1, reinterpret_cast<const float*>(dp + oX), reinterpret_cast<const float*>(dp + oA),
                                               reinterpret_cast<const int*>(dp + oO), dp + oV, dp + oB, dp + oD,
-                                              w->c.as<orbx_keypoint>(), n2, w->d.as<uint8_t>(),
-                                              u_right2 ? reinterpret_cast<const float*>(dp + oU) : nullptr, dp + oC,
+                                              fr ? fr->kps.as<orbx_keypoint>() : w->c.as<orbx_keypoint>(), n2,
+                                              fr ? fr->desc.as<uint8_t>() : w->d.as<uint8_t>(), dUr, dp + oC,
                                               reinterpret_cast<const float*>(dp + oS), bounds, th, nnratio, cellOf, sorted, cellStart,
                                               w->g.as<uint32_t>(), candCap, w->h.as<int>(), w->out0.as<int>(), dN,
                                               w->status.as<int>(), s)))
@@ -480,6 +571,23 @@ int orbx_search_by_projection_map(int n1, const float* proj, const float* view_c
     }
     *nmatches = st[1];
     return ORBX_OK;
+}
+
+extern "C" {
+int orbx_search_by_projection_map(int n1, const float* proj, const float* view_cos, const int* level1, const uint8_t* valid1,
+                                  const uint8_t* obs1, const uint8_t* mp_desc1, const orbx_keypoint* k2, int n2,
+                                  const uint8_t* desc2, const float* u_right2, const uint8_t* occupied2, const float bounds[4],
+                                  const float* scale_factors, int nlevels, float th, float nnratio, int* match21, int* nmatches) {
+    return sbpm_impl(nullptr, n1, proj, view_cos, level1, valid1, obs1, mp_desc1, k2, n2, desc2, u_right2, occupied2, bounds, scale_factors,
+                     nlevels, th, nnratio, match21, nmatches);
+}
+
+int orbx_search_by_projection_map_frame(int n1, const float* proj, const float* view_cos, const int* level1, const uint8_t* valid1,
+                                        const uint8_t* obs1, const uint8_t* mp_desc1, const orbx_frame* f2, const uint8_t* occupied2,
+                                        const float* scale_factors, int nlevels, float th, float nnratio, int* match21, int* nmatches) {
+    if (!f2) { set_error("orbx_search_by_projection_map_frame: null frame"); return ORBX_E_INVALID; }
+    return sbpm_impl(f2, n1, proj, view_cos, level1, valid1, obs1, mp_desc1, nullptr, 0, nullptr, nullptr, occupied2, nullptr, scale_factors,
+                     nlevels, th, nnratio, match21, nmatches);
 }
 
 int orbx_search_by_projection_sim3(int n1, const float* uvr, const int* level1, const uint8_t* valid1, const uint8_t* mp_desc1,

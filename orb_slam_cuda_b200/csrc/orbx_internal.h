@@ -225,6 +225,7 @@ int launch_search_by_projection_sim3(int n1, const float* uvr, const int* level1
                                      const uint8_t* occupied2, const float bounds[4], int thDist, int* cellOf, int* sorted,
                                      int* cellStart, uint32_t* cand, int candCap, int* candCnt, int* match21, int* nmatches,
                                      int* dStatus, cudaStream_t s);
+int launch_frame_grid(const orbx_keypoint* k, int n, const float bounds[4], int* cellOf, int* sorted, int* cellStart, cudaStream_t s);
 int launch_search_by_bow(int nItems, const int* nodeOf, const uint32_t* idx1, const int* start2, const uint32_t* idx2, int n1,
                          const uint8_t* valid1, const uint8_t* desc1, const float* angle1, int n2, const uint8_t* valid2,
                          const uint8_t* desc2, const float* angle2, const int* candOff, uint32_t* cand, int* candCnt, int thDist,

@@ -355,3 +355,43 @@ def test_fuse_match_gpu(seed, stereo, gate, th):
     idx, dist = X.ORBmatcher().FuseMatch(uvr, ur1, s["level1"], s["valid1"], s["mp_desc1"], s["k2"], s["d2"], s["u_right2"], inv, s["bounds"])
     assert (r_idx >= 0).sum() > 50 and np.array_equal(idx, r_idx) and np.array_equal(dist, r_dist)
     assert ((r_dist <= 50) & (r_idx >= 0)).sum() > 20
+
+
+# ---- orbx_frame: the current frame resident on the device (Frame::AssignFeaturesToGrid, src/Frame.cc:229-244) -------------------------
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed,stereo", [(1, False), (3, True)])
+def test_device_frame_handle(seed, stereo):
+    """The grid binned on the device equals the reference's mGrid (cell contents in push_back order = ascending keypoint index:
+    checked through the oracle's GetFeaturesInArea, which tests/test_oracle_ref_matcher.py pins to the reference's Frame.cc), and the
+    handle entries of the two per-frame tracking matchers return exactly what the host-array entries return."""
+    import orb_slam_cuda_b200 as X
+    s = scenario(seed, stereo)
+    k2, n2 = s["k2"], s["k2"].size
+    fr = X.DeviceFrame(k2, s["d2"], s["bounds"], s["u_right2"])
+    cs, so = fr.grid()
+    assert cs[0] == 0 and cs[-1] == n2 and sorted(so.tolist()) == list(range(n2))
+    w, h = s["bounds"][1], s["bounds"][3]
+    for cell in (0, 64 * 48 // 2 + 7, 1000, 64 * 48 - 1):  # a cell = everything GetFeaturesInArea finds with the cell's box as the window
+        inside = so[cs[cell]:cs[cell + 1]]
+        assert list(inside) == sorted(inside)
+        ix, iy = cell // 48, cell % 48
+        px = np.floor((k2["x"] * (np.float32(64) / np.float32(w))).astype(np.float32) + np.float32(0.5)).astype(int)  # PosInGrid, src/Frame.cc:381-391
+        py = np.floor((k2["y"] * (np.float32(48) / np.float32(h))).astype(np.float32) + np.float32(0.5)).astype(int)
+        assert list(inside) == list(np.flatnonzero((px == ix) & (py == iy)))
+    m = X.ORBmatcher(0.9, True)
+    a = (s["x3Dc"], s["valid1"], s["obs1"], s["mp_desc1"], s["octave1"], s["angle1"])
+    n_h, m_h = m.SearchByProjection(*a, k2, s["d2"], s["u_right2"], s["occupied2"], s["cam"], s["mbf"], s["bounds"], s["scale_factors"], 15.0, 0)
+    n_f, m_f = m.SearchByProjectionFrame(*a, fr, s["occupied2"], s["cam"], s["mbf"], s["scale_factors"], 15.0, 0)
+    n_o, m_o = O.search_by_projection_frame(*a, k2, s["d2"], s["u_right2"], s["occupied2"], s["cam"], s["mbf"], s["bounds"], s["scale_factors"], 15.0, 0, True)
+    assert n_f == n_h == n_o > 50 and np.array_equal(m_f, m_h) and np.array_equal(m_f, m_o)
+    ms = map_scenario(seed, stereo)
+    mm = X.ORBmatcher(0.8, True)
+    b = (ms["proj"], ms["view_cos"], ms["level1"], ms["valid1"], ms["obs1"], ms["mp_desc1"])
+    n_h, m_h = mm.SearchByProjectionMap(*b, k2, ms["d2"], ms["u_right2"], ms["occupied2"], ms["bounds"], ms["scale_factors"], 3.0)
+    n_f, m_f = mm.SearchByProjectionMapFrame(*b, fr, ms["occupied2"], ms["scale_factors"], 3.0)
+    assert n_f == n_h > 50 and np.array_equal(m_f, m_h)
+    # an empty frame works too
+    e = X.DeviceFrame(k2[:0], s["d2"][:0], s["bounds"])
+    n_e, m_e = m.SearchByProjectionFrame(*a, e, np.zeros(0, np.uint8), s["cam"], s["mbf"], s["scale_factors"], 15.0, 0)
+    assert n_e == 0
