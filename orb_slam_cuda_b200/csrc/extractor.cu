@@ -65,9 +65,10 @@ struct orbx_extractor {
     int batchCap = 0;        // frames the scratch holds
     int outCap = 0;          // keypoints per frame the output staging holds
     FrameGeom g{};
-    TmaMaps fastMaps{}, blurMaps{};
+    TmaMaps fastMaps{}, blurMaps{}, resizeMaps{};  // resizeMaps.m[l]: SOURCE level l of the TMA-tiled resize
     std::vector<int> areaFast;
-    DevBuf planes[ORBX_MAX_LEVELS], blurs[ORBX_MAX_LEVELS], xtab[ORBX_MAX_LEVELS], ytab[ORBX_MAX_LEVELS];
+    DevBuf planes[ORBX_MAX_LEVELS], blurs[ORBX_MAX_LEVELS], xtab[ORBX_MAX_LEVELS], ytab[ORBX_MAX_LEVELS], rzTiles[ORBX_MAX_LEVELS];
+    int rzTilesX[ORBX_MAX_LEVELS] = {};  // rzTiles[l] = tileX0[tilesX] | tileY0[tilesY]
     DevBuf strips, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, lvlAngles, status, dDesc, dCounts;
     DevBuf dFrames[2], dKps[2];  // device input / output staging of host-buffer calls, one set per in-flight call (slot)
     PinBuf hFrames, hKps, hDesc, hCounts, hStatus;
@@ -296,7 +297,7 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
         }
         L.blurTilesX = (L.w + 127) / 128;
         L.blurTileBase = tileBase;
-        tileBase += L.blurTilesX * ((L.h + 31) / 32);
+        tileBase += L.blurTilesX * ((L.h + BLUR_TILE_H - 1) / BLUR_TILE_H);
         L.kpBase = L.slotBase;
     }
     g.nCellsTotal = std::max(cellBase, 1);
@@ -347,6 +348,44 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
                 if (hi >= 0 && hi - lo > 7) fits = false;
             }
             if (fits) ex->areaFast[l] |= 2;
+            // TMA-tiled kernel: the source window of every 128-byte x RZT_TH-row destination tile must fit the RZT_BW x RZT_BH box
+            // whose origin is 16-byte aligned in x
+            static const bool noTma = getenv("ORBX_RESIZE_NO_TMA") != nullptr;
+            if (fits && !noTma) {
+                const int tilesX = (L.pitch + 127) / 128, tilesY = (L.rows + RZT_TH - 1) / RZT_TH;
+                std::vector<int> org(tilesX + tilesY, 0);
+                bool ok = true;
+                auto refl = [](int d, int n) { while (d < 0 || d >= n) d = n == 1 ? 0 : (d < 0 ? -d : 2 * n - 2 - d); return d; };
+                for (int tx = 0; tx < tilesX && ok; ++tx) {
+                    int lo = INT_MAX, hi = -1;
+                    for (int b = tx * 128; b < std::min(tx * 128 + 128, L.pitch); ++b) {
+                        const int px = b - PADL;
+                        if (px < 0 || px >= L.w + 2 * EDGE) continue;
+                        const int d = refl(px - EDGE, L.w);
+                        lo = std::min(lo, (int)xt[d].s0);
+                        hi = std::max(hi, std::max((int)xt[d].s0, (int)xt[d].s1));
+                    }
+                    if (hi < 0) { lo = 0; hi = 0; }
+                    org[tx] = (XOFF + lo) & ~15;
+                    if (XOFF + hi + 12 - org[tx] > RZT_BW) ok = false;
+                }
+                for (int ty = 0; ty < tilesY && ok; ++ty) {
+                    int lo = INT_MAX, hi = -1;
+                    for (int r = ty * RZT_TH; r < std::min(ty * RZT_TH + RZT_TH, L.rows); ++r) {
+                        const int d = refl(r - EDGE, L.h);
+                        lo = std::min(lo, (int)yt[d].s0);
+                        hi = std::max(hi, std::max((int)yt[d].s0, (int)yt[d].s1));
+                    }
+                    org[tilesX + ty] = EDGE + lo;
+                    if (hi - lo + 1 > RZT_BH) ok = false;
+                }
+                if (ok) {
+                    ex->areaFast[l] |= 4;
+                    ex->rzTilesX[l] = tilesX;
+                    if ((rc = ex->rzTiles[l].ensure(org.size() * sizeof(int)))) return rc;
+                    ORBX_CUDA(cudaMemcpy(ex->rzTiles[l].p, org.data(), org.size() * sizeof(int), cudaMemcpyHostToDevice));
+                }
+            }
             if ((rc = ex->xtab[l].ensure(xt.size() * sizeof(ResizeTab)))) return rc;
             if ((rc = ex->ytab[l].ensure(yt.size() * sizeof(ResizeTab)))) return rc;
             ORBX_CUDA(cudaMemcpy(ex->xtab[l].p, xt.data(), xt.size() * sizeof(ResizeTab), cudaMemcpyHostToDevice));
@@ -367,7 +406,10 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
     for (int l = 0; l < nl; ++l) {
         const LevelGeom& L = g.lv[l];
         if ((rc = make_plane_map(&ex->fastMaps.m[l], L.plane, L.pitch, L.rows, L.planeStride, batch, g.fastBoxW, g.fastBoxH))) return rc;
-        if ((rc = make_plane_map(&ex->blurMaps.m[l], L.plane, L.pitch, L.rows, L.planeStride, batch, 160, 38))) return rc;
+        if ((rc = make_plane_map(&ex->blurMaps.m[l], L.plane, L.pitch, L.rows, L.planeStride, batch, 160, BLUR_TILE_H + 6))) return rc;
+        if (l + 1 < nl && (ex->areaFast[l + 1] & 4) &&
+            (rc = make_plane_map(&ex->resizeMaps.m[l], L.plane, L.pitch, L.rows, L.planeStride, batch, RZT_BW, RZT_BH)))
+            return rc;
     }
     ex->w = w;
     ex->h = h;
@@ -408,9 +450,14 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[0], s));
     if ((rc = launch_pyramid_base(g, dFrames, batch, stride, frameStride, s))) return rc;                 // ComputePyramid
     if ((rc = stage_sync("Pyramid/Resize level 0", s))) return rc;
-    for (int l = 1; l < nl; ++l)
-        if ((rc = launch_pyramid_level(g, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->areaFast[l], batch, s)))
-            return rc;
+    for (int l = 1; l < nl; ++l) {
+        if (ex->areaFast[l] & 4)
+            rc = launch_pyramid_level_tma(g, ex->resizeMaps, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->rzTiles[l].as<int>(),
+                                          ex->rzTiles[l].as<int>() + ex->rzTilesX[l], batch, s);
+        else
+            rc = launch_pyramid_level(g, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->areaFast[l], batch, s);
+        if (rc) return rc;
+    }
     if ((rc = stage_sync("Pyramid/Resize", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
     if ((rc = launch_fast(g, ex->fastMaps, ex->strips.as<FastStrip>(), batch, cellCnt, cellKeys, dStatus, s))) return rc;
@@ -552,7 +599,7 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : ex->subEv) cudaEventDestroy(e);
     for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
-        ex->planes[l].release(); ex->blurs[l].release(); ex->xtab[l].release(); ex->ytab[l].release();
+        ex->planes[l].release(); ex->blurs[l].release(); ex->xtab[l].release(); ex->ytab[l].release(); ex->rzTiles[l].release();
     }
     for (DevBuf* b : {&ex->strips, &ex->cellCnt, &ex->cellKeys, &ex->qtScratch, &ex->lvlCnt, &ex->lvlKeys, &ex->lvlAngles, &ex->status,
                       &ex->dFrames[0], &ex->dFrames[1], &ex->dKps[0], &ex->dKps[1], &ex->dDesc, &ex->dCounts})

@@ -14,8 +14,11 @@
 
 namespace orbx {
 
-constexpr int BLUR_TW = 128, BLUR_TH = 32, BLUR_BW = 160, BLUR_BH = 38;
-constexpr int BLUR_BAND = 16;                        // output rows per thread (a thread walks BLUR_BAND + 6 input rows)
+#ifndef ORBX_BLUR_BAND
+#define ORBX_BLUR_BAND 32  // = the tile height: ONE warp per CTA (measured on B200: 0.41 ms against 0.54 ms with two warps of 16 rows; profiles/r02_variants.txt)
+#endif
+constexpr int BLUR_TW = 128, BLUR_TH = BLUR_TILE_H, BLUR_BW = 160, BLUR_BH = BLUR_TH + 6;
+constexpr int BLUR_BAND = ORBX_BLUR_BAND;            // output rows per thread (a thread walks BLUR_BAND + 6 input rows)
 constexpr int BLUR_THREADS = 32 * (BLUR_TH / BLUR_BAND);
 
 // One CTA = one 128 x 32 output tile; one thread = 4 output columns x 16 output rows.  Walking down its band, a thread

@@ -95,7 +95,10 @@ __device__ __forceinline__ void glibc_sincosf(float y, float* sn, float* cs) {
 }
 
 constexpr int DESC_WARPS = 8;
-constexpr int DESC_PER_WARP = 4;   // keypoint slots a warp walks (amortises the table set-up of the CTA)
+#ifndef ORBX_DESC_PER_WARP
+#define ORBX_DESC_PER_WARP 4
+#endif
+constexpr int DESC_PER_WARP = ORBX_DESC_PER_WARP;   // keypoint slots a warp walks (amortises the table set-up of the CTA)
 constexpr int BP_HALF = 18;        // the rotated pattern reaches |coordinate| <= cvRound(18.38) = 18
 constexpr int BP_ROWS = 2 * BP_HALF + 1;  // 37 rows; a row is 48 bytes read from an 8-byte aligned address (6 x 64-bit loads)
 constexpr int BP_WORDS = 14, BP_STRIDE = BP_WORDS * 4;  // shared row stride: 56 bytes (8-byte aligned rows for cp.async)

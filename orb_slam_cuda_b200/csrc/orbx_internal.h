@@ -29,6 +29,15 @@ constexpr int HALF_PATCH = 15;
 constexpr int PATCH = 31;
 constexpr int CELL_CAP = 128;    // FAST keypoints per cell (overflow -> ORBX_E_OVERFLOW)
 constexpr int FAST_MAX_STRIP_CELLS = 8;  // cells one FAST CTA handles (a strip of one cell row)
+#ifndef ORBX_BLUR_TH
+#define ORBX_BLUR_TH 32  // output rows of a blur tile (the TMA box is 160 x (ORBX_BLUR_TH + 6))
+#endif
+constexpr int BLUR_TILE_H = ORBX_BLUR_TH;
+#ifndef ORBX_RZT_TH
+#define ORBX_RZT_TH 32  // destination rows of a TMA-tiled resize tile
+#endif
+constexpr int RZT_TH = ORBX_RZT_TH;
+constexpr int RZT_BW = 192, RZT_BH = (RZT_TH * 5 + 3) / 4 + 8;  // source box: 128 x 1.2 + alignment slack; TH x 1.25 + slack (48 rows for TH 32)
 constexpr int QT_THREADS = 256;
 constexpr int MAX_ROOTS = 64;
 constexpr int ORBX_MAX_DEVICES = 64;  // per-device attribute caches (ensure_dynamic_smem)
@@ -173,6 +182,8 @@ int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, s
                         cudaStream_t s);
 int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, const ResizeTab* ytab, int areaFast,
                          int batch, cudaStream_t s);
+int launch_pyramid_level_tma(const FrameGeom& g, const TmaMaps& maps, int level, const ResizeTab* xtab, const ResizeTab* ytab,
+                             const int* tileX0, const int* tileY0, int batch, cudaStream_t s);
 // per-cell FAST-9 + threshold fallback + NMS
 int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrips, int batch, int* cellCnt,
                 uint32_t* cellKeys, int* dStatus, cudaStream_t s);

@@ -110,14 +110,15 @@ def test_batch_equals_single():
 
 @pytest.mark.parametrize("pinned", [False, True])
 def test_chunked_host_batch(pinned):
-    """Host batches of >= 128 frames are pipelined in chunks over three streams (H2D | kernels | D2H): every frame
+    """Host batches of >= 256 frames are pipelined in chunks of about 128 over three streams (H2D | kernels | D2H): every frame
     must come out as if extracted alone, and the pyramid accessor serves the last chunk by batch index."""
     import torch
-    h, w, nf, b = 120, 160, 300, 131
+    h, w, nf, b = 120, 160, 300, 259
     gx, ox = X.ORBextractor(nf, 1.2, 8, 20, 7), O.Extractor(nf, 1.2, 8, 20, 7)
     pool = np.stack([synth.textured_frame(900 + i, h, w) for i in range(7)])
     frames = pool[np.arange(b) % 7].copy()
-    frames[:, 0, 0] = np.arange(b, dtype=np.uint8)  # make every frame distinct
+    frames[:, 0, 0] = (np.arange(b) % 256).astype(np.uint8)  # make every frame distinct
+    frames[:, 0, 1] = (np.arange(b) // 256).astype(np.uint8)
     cap = gx.default_cap()
     if pinned:
         tf = torch.from_numpy(frames).pin_memory()
@@ -127,7 +128,7 @@ def test_chunked_host_batch(pinned):
         kps, desc, counts = gx.extract_batch(tf.numpy(), tk.numpy().view(X.KP_DTYPE).reshape(b, cap), td.numpy(), tc.numpy(), cap)
     else:
         kps, desc, counts = gx.extract_batch(frames)
-    for f in [0, 1, 63, 64, 65, 66, 127, 128, 129, 130]:
+    for f in [0, 1, 63, 64, 127, 128, 129, 130, 131, 257, 258]:
         ok, od = ox.extract(frames[f])
         n = counts[f]
         assert n == len(ok), f
