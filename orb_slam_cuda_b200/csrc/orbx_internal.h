@@ -34,9 +34,11 @@ constexpr int FAST_MAX_STRIP_CELLS = 8;  // cells one FAST CTA handles (a strip 
 #endif
 constexpr int BLUR_TILE_H = ORBX_BLUR_TH;
 #ifndef ORBX_RZT_TH
-#define ORBX_RZT_TH 32  // destination rows of a TMA-tiled resize tile
+#define ORBX_RZT_TH 24  // destination rows of a TMA-tiled resize tile (<= 32: one lane prepares one row's constants); 16 / 24 / 32
+                       // measured 0.764 / 0.750 / 0.766 ms for the pyramid stage (profiles/r02_variants.txt)
 #endif
 constexpr int RZT_TH = ORBX_RZT_TH;
+static_assert(RZT_TH >= 4 && RZT_TH <= 32, "one lane per tile row");
 constexpr int RZT_BW = 192, RZT_BH = (RZT_TH * 5 + 3) / 4 + 8;  // source box: 128 x 1.2 + alignment slack; TH x 1.25 + slack (48 rows for TH 32)
 constexpr int QT_THREADS = 256;
 constexpr int MAX_ROOTS = 64;

@@ -52,6 +52,15 @@ ncu)  # ncu KERNEL_REGEX TAG SKIP COUNT [bench args]: --set full with source of 
     python bench.py --profile --steps 1 --warmup 1 --batch 512 "$@" > gpurun_out/ncu_$tag.log 2>&1; echo "ncu rc=$?"
   ls -la gpurun_out/ncu_$tag.ncu-rep
   ;;
+ncusum)  # ncusum WORKLOAD TAG [keep]: capture one step of WORKLOAD, write the per-kernel csv + profiles/ncu_latest.json entry, drop the
+         # 20+ MB report unless `keep` is given (gpurun brings back at most 64 MiB)
+  wl=$1; tag=$2; keep=$3
+  ncu --set full --import-source on --clock-control none -k regex:k_ -s 13 -c 13 -f -o gpurun_out/ncu_${tag}_$wl \
+    python bench.py --profile --steps 1 --warmup 1 --batch 512 --workload $wl > gpurun_out/ncu_${tag}_$wl.log 2>&1; echo "ncu $wl rc=$?"
+  python tools/ncu_summary.py gpurun_out/ncu_${tag}_$wl.ncu-rep --json $wl 512 > gpurun_out/ncu_full_${tag}_$wl.csv
+  cp profiles/ncu_latest.json gpurun_out/ncu_latest.json
+  [ "$keep" = keep ] || rm -f gpurun_out/ncu_${tag}_$wl.ncu-rep
+  ;;
 multi)
   n=$1
   python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29512 tools/multi_gpu_check.py \
