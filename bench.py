@@ -590,28 +590,35 @@ def run_ours(args, emit=print):
         ex.extract_batch_wait()
 
     e2e_s = e2e_sync_s = float("nan")
-    h2d_gbs = d2h_gbs = float("nan")
+    h2d_gbs = d2h_gbs = duplex_ms = float("nan")
     if not args.no_e2e:
         # what the box gives this rank while every rank copies at once: the bare pinned-host -> device and device -> pinned-host
         # rates of the step's own buffers (no kernels).  e2e cannot beat frames_per_step / (H2D time) on this box.
-        d_tmp = torch.empty_like(d_kps)
-        h_tmp = torch.empty((B, cap, 7), dtype=torch.int32).pin_memory()
-        for direction in ("h2d", "d2h"):
+        d_tmp = torch.empty((B, cap * 60 // 4), dtype=torch.int32, device="cuda")  # keypoints + descriptors of a step
+        h_tmp = torch.empty((B, cap * 60 // 4), dtype=torch.int32).pin_memory()
+        s_up, s_down = torch.cuda.Stream(), torch.cuda.Stream()
+        rates = {}
+        for direction in ("h2d", "d2h", "duplex"):
             barrier()
             c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             c0.record()
+            s_up.wait_stream(torch.cuda.current_stream())
+            s_down.wait_stream(torch.cuda.current_stream())
             for _ in range(5):
-                if direction == "h2d":
-                    d_frames.copy_(h_frames, non_blocking=True)
-                else:
-                    h_tmp.copy_(d_tmp, non_blocking=True)
+                if direction in ("h2d", "duplex"):
+                    with torch.cuda.stream(s_up):
+                        d_frames.copy_(h_frames, non_blocking=True)
+                if direction in ("d2h", "duplex"):
+                    with torch.cuda.stream(s_down):
+                        h_tmp.copy_(d_tmp, non_blocking=True)
+            torch.cuda.current_stream().wait_stream(s_up)
+            torch.cuda.current_stream().wait_stream(s_down)
             c1.record()
             barrier()
-            gbs = (B * w * h if direction == "h2d" else d_tmp.numel() * 4) * 5 / (c0.elapsed_time(c1) * 1e-3) / 1e9
-            if direction == "h2d":
-                h2d_gbs = gbs
-            else:
-                d2h_gbs = gbs
+            rates[direction] = c0.elapsed_time(c1) / 5  # ms per step's worth of copies
+        h2d_gbs = B * w * h / (rates["h2d"] * 1e-3) / 1e9
+        d2h_gbs = d_tmp.numel() * 4 / (rates["d2h"] * 1e-3) / 1e9
+        duplex_ms = rates["duplex"]
         del d_tmp, h_tmp
         for _ in range(W):
             step_host()
@@ -638,10 +645,11 @@ def run_ours(args, emit=print):
 
     match = None if args.no_match else match_leg(X, torch, dist, rank, world, stream, 2, args.keyframes)
 
-    t = torch.tensor([ms, e2e_s * 1e3, e2e_sync_s * 1e3, -h2d_gbs, -d2h_gbs], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms, e2e_s * 1e3, e2e_sync_s * 1e3, -h2d_gbs, -d2h_gbs, duplex_ms], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, e2e_ms, e2e_sync_ms, h2d_gbs, d2h_gbs = float(t[0]), float(t[1]), float(t[2]), -float(t[3]), -float(t[4])  # copy rates: slowest rank
+    ms, e2e_ms, e2e_sync_ms, h2d_gbs, d2h_gbs, duplex_ms = (float(t[0]), float(t[1]), float(t[2]), -float(t[3]), -float(t[4]),
+                                                            float(t[5]))  # copy rates: slowest rank
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -670,7 +678,9 @@ def run_ours(args, emit=print):
                 "path": "orbx_extract_batch_async / orbx_extract_batch_wait, two steps in flight, pinned host buffers",
                 "h2d_ceiling_gbs": h2d_gbs, "d2h_ceiling_gbs": d2h_gbs,
                 "h2d_bound_frames_per_s": world * h2d_gbs * 1e9 / (w * h),
-                "ceiling": "bare copies of the step's own pinned buffers, all ranks at once, slowest rank; e2e <= N x h2d_ceiling / bytes per frame on this box",
+                "copies_only_ms_per_step": duplex_ms, "copy_bound_frames_per_s": world * B / (duplex_ms * 1e-3),
+                "ceiling": "bare copies of the step's own pinned buffers (h2d: the frames; d2h: keypoints + descriptors; copies_only: both "
+                           "directions at once on two streams), all ranks at once, slowest rank, no kernels: what the box allows",
                 "sync": {"value": total_frames / (e2e_sync_ms * 1e-3), "ms_per_step": e2e_sync_ms / K,
                          "path": "blocking orbx_extract_batch, one step at a time"}},
         "gpu_launches": int(launches),

@@ -5,11 +5,16 @@
 // and bench.py's cpu_baseline / --impl reference legs may build, load or call it.  The product
 // (orb_slam_cuda_b200/, include/) never links or calls anything in this directory.
 //
-// Parity pinning: the reference ships no tests or golden vectors and its sources do
-// not compile here (VisionWorks/OpenVX/OpenCV C++ headers absent), so the control flow below follows the
-// reference line ranges cited at each function, and the five OpenCV primitives it calls (resize,
-// copyMakeBorder, FAST, GaussianBlur, fastAtan2) are pinned bit-exactly against cv2 4.13 by
-// tests/test_oracle_cv2.py and the committed fixtures under tests/golden/.
+// Parity pinning.  The reference ships no tests or golden vectors.
+//   * Matchers, Frame grid, ComputeStereoMatches: PINNED TO REFERENCE OBJECT CODE.  /root/reference's own src/ORBmatcher.cc and
+//     src/Frame.cc are compiled where they lie (oracle/ref_matcher/Makefile -> oracle/_ref/libref_matcher.so) and every matcher
+//     below equals them on 20 seeded cases, live and through tests/golden/ref_matcher.npz (tests/test_oracle_ref_matcher.py).
+//     The DBoW2 descent is pinned the same way against the reference's Thirdparty/DBoW2 (oracle/ref_dbow2).
+//   * Extractor (ORBextractor.cc): its source does not compile here (VisionWorks / OpenVX / OpenCV C++ headers absent), so the
+//     control flow follows the reference line ranges cited at each function, the five OpenCV primitives it calls (resize,
+//     copyMakeBorder, FAST, GaussianBlur, fastAtan2) are pinned bit-exactly against cv2 4.13 (tests/test_oracle_cv2.py and the
+//     fixtures under tests/golden/), and the 1024 pattern integers against the reference text and cv2.ORB.  PARITY UNPINNED
+//     against a reference BINARY for this part.
 #pragma once
 #include <cstddef>
 #include <cstdint>

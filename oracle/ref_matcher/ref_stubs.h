@@ -9,10 +9,17 @@
 #define ORBX_REF_STUBS_H
 #define MAPPOINT_H
 #define KEYFRAME_H
-#define ORBEXTRACTOR_H
 #define ORBVOCABULARY_H
 #define CONVERTER_H
 #include <opencv2/core/core.hpp>
+#ifdef ORBX_REF_USE_PRODUCT_CLASSES
+// ref_frame_unchanged: the reference's Frame.cc on top of THIS repository's ORBextractor / ORBmatcher classes (their headers use
+// the same include guards as the reference's, so the reference's own copies are skipped wherever they are included later)
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+#else
+#define ORBEXTRACTOR_H
+#endif
 
 #include "Thirdparty/DBoW2/DBoW2/BowVector.h"
 #include "Thirdparty/DBoW2/DBoW2/FeatureVector.h"
@@ -31,6 +38,7 @@ struct SurgeryOp {
 };
 extern std::vector<SurgeryOp> g_surgery;
 
+#ifndef ORBX_REF_USE_PRODUCT_CLASSES
 class ORBextractor {  // include/ORBextractor.h: the accessors src/Frame.cc:68-74 reads, operator() returning preset features
 public:
     std::vector<cv::KeyPoint> keys;
@@ -48,6 +56,7 @@ public:
     std::vector<float> GetScaleSigmaSquares() { return s2; }
     std::vector<float> GetInverseScaleSigmaSquares() { return is2; }
 };
+#endif
 
 class ORBVocabulary {  // Frame::ComputeBoW is not exercised here (the DBoW2 descent is pinned by oracle/ref_dbow2)
 public:

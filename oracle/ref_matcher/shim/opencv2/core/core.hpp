@@ -47,6 +47,16 @@ typedef Point_<int> Point;
 typedef Point_<int> Point2i;
 typedef Point_<float> Point2f;
 
+struct Size {
+    int width, height;
+    Size() : width(0), height(0) {}
+    Size(int w, int h) : width(w), height(h) {}
+};
+struct Range {
+    int start, end;
+    Range(int s, int e) : start(s), end(e) {}
+};
+
 class KeyPoint {  // field order of OpenCV's cv::KeyPoint
 public:
     Point2f pt;
@@ -63,6 +73,19 @@ public:
 
     Mat() : rows(0), cols(0), data(nullptr), step(0), type_(CV_8U) {}
     Mat(int r, int c, int type) : Mat() { create(r, c, type); }
+    Mat(int r, int c, int type, void* ext, size_t step_ = 0) : rows(r), cols(c), data((uchar*)ext), type_(type) {  // user-owned data
+        step = step_ ? step_ : (size_t)c * elemSize();
+    }
+    Mat operator()(const Range& rr, const Range& cr) const { return roi(rr.start, rr.end, cr.start, cr.end); }
+    bool isContinuous() const { return step == (size_t)cols * elemSize() || rows <= 1; }
+    int channels() const { return 1; }
+    Size size() const { return Size(cols, rows); }
+    void release() {
+        own_.reset();
+        data = nullptr;
+        rows = cols = 0;
+        step = 0;
+    }
     void create(int r, int c, int type) {
         type_ = type;
         rows = r;
@@ -147,6 +170,32 @@ private:
     int type_;
     std::shared_ptr<std::vector<uchar>> own_;
 };
+
+// cv::InputArray / cv::OutputArray as ORBextractor::operator() uses them (a Mat converts implicitly, like in OpenCV)
+class _InputArray {
+public:
+    _InputArray() : m_(nullptr) {}
+    _InputArray(const Mat& m) : m_(const_cast<Mat*>(&m)) {}
+    Mat getMat() const { return m_ ? *m_ : Mat(); }
+    bool empty() const { return !m_ || m_->empty(); }
+
+protected:
+    Mat* m_;
+};
+class _OutputArray : public _InputArray {
+public:
+    _OutputArray() {}
+    _OutputArray(Mat& m) { m_ = &m; }
+    void create(int r, int c, int type) const {
+        if (m_) m_->create(r, c, type);
+    }
+    void release() const {
+        if (m_) m_->release();
+    }
+    Mat& getMatRef() const { return *m_; }
+};
+typedef const _InputArray& InputArray;
+typedef const _OutputArray& OutputArray;
 
 template <class T> class Mat_ : public Mat {
 public:

@@ -419,3 +419,51 @@ def test_fuse_both_overloads_with_map_surgery(harness, tmp_path):
     assert np.array_equal(rd.arr(np.int32, n2), np.array([slot2.get(j, -1) for j in range(n2)], np.int32))
     assert rd.i32() == len(entries2)
     assert np.array_equal(rd.arr(np.int32, len(entries2)), replaced)
+
+
+REF_UNCHANGED = os.path.join(ROOT, "oracle", "_ref", "ref_frame_unchanged")
+
+
+@pytest.mark.gpu
+def test_reference_frame_cc_runs_unchanged_on_the_class_surface(tmp_path):
+    """BASELINE.json north_star: "Frame.cc ... and ComputeStereoMatches run unchanged on top of it".  oracle/_ref/ref_frame_unchanged is the
+    REFERENCE's own src/Frame.cc (compiled from /root/reference by oracle/ref_matcher/Makefile) linked against this repository's
+    ORBextractor / ORBmatcher classes and liborbx.so.  Its stereo constructor extracts both eyes through ORBextractor::operator() on two
+    threads and then runs its unchanged ComputeStereoMatches body over mvImagePyramid (host copies of the device pyramid) and
+    ORBmatcher::DescriptorDistance (one device call per pair).  Keypoints, descriptors, mvuRight / mvDepth (float bits) must equal the
+    oracle's — and therefore orbx_stereo_match, which test_matcher_gpu compares with the same oracle — and the reference's mGrid must
+    equal the grid orbx_frame bins on the device."""
+    if not os.path.exists(REF_UNCHANGED):
+        pytest.skip("oracle/_ref/ref_frame_unchanged is built where /root/reference exists")
+    w, h, nf, bf, fx = 752, 480, 1200, 47.90639384423901, 435.2046959714599
+    left, right = synth.stereo_pair("euroc", 9)
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(left.tobytes() + right.tobytes())
+    out = tmp_path / "out.bin"
+    r = subprocess.run([REF_UNCHANGED, str(raw), str(w), str(h), str(nf), repr(bf), repr(fx), str(out)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr
+    rd = Reader(out.read_bytes())
+    kL, dL = rd.keys()
+    kR, dR = rd.keys()
+    exL, exR = O.Extractor(nf, 1.2, 8, 20, 7), O.Extractor(nf, 1.2, 8, 20, 7)
+    okL, odL = exL.extract(left)
+    okR, odR = exR.extract(right)
+    assert np.array_equal(kL.view(np.uint8), okL.view(np.uint8)) and np.array_equal(dL, odL)
+    assert np.array_equal(kR.view(np.uint8), okR.view(np.uint8)) and np.array_equal(dR, odR)
+    ur, depth = rd.arr(np.float32, len(kL)), rd.arr(np.float32, len(kL))
+    our, odepth = O.stereo_matches(exL, exR, okL.copy(), odL.copy(), okR.copy(), odR.copy(), bf, fx)
+    assert (ur >= 0).sum() > 300
+    assert np.array_equal(ur.view(np.uint32), our.view(np.uint32)) and np.array_equal(depth.view(np.uint32), odepth.view(np.uint32))
+    gL, gR = X.ORBextractor(nf, 1.2, 8, 20, 7, w, h), X.ORBextractor(nf, 1.2, 8, 20, 7, w, h)
+    k1, d1 = gL(left)
+    k2, d2 = gR(right)
+    dur, ddepth = X.ComputeStereoMatches(gL, gR, k1, d1, k2, d2, bf, fx)
+    assert np.array_equal(dur.view(np.uint32), ur.view(np.uint32)) and np.array_equal(ddepth.view(np.uint32), depth.view(np.uint32))
+    # the reference's mGrid (Frame::AssignFeaturesToGrid) against the device-resident frame's grid
+    cells = []
+    for _ in range(64 * 48):
+        n = rd.i32()
+        cells.append(rd.arr(np.int32, n))
+    cs, so = X.DeviceFrame(kL, dL, (0.0, float(w), 0.0, float(h))).grid()
+    assert np.array_equal(np.concatenate([[0], np.cumsum([c.size for c in cells])]).astype(np.int32), cs)
+    assert np.array_equal(np.concatenate(cells), so)
