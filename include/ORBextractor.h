@@ -50,6 +50,10 @@ public:
     std::vector<cv::Mat> mvImagePyramid;
     bool keepImagePyramid = true;
 
+    // bit_pattern_31_ as the reference compiles it (default; element 96 = VX_FAILURE - 2 = -3, src/ORBextractor.cc:261-262) or the
+    // canonical ORB table of OpenCV / upstream ORB-SLAM2 (see orbx_extractor_set_pattern in orbx.h)
+    void UseCanonicalPattern(bool on) { orbx_extractor_set_pattern(mpHandle, on ? ORBX_PATTERN_CANONICAL : ORBX_PATTERN_REFERENCE); }
+
     // the C handle, for the matcher entry points that read the device-resident pyramid (orbx_stereo_match)
     orbx_extractor* handle() const { return mpHandle; }
 

@@ -66,6 +66,15 @@ void orbx_extractor_destroy(orbx_extractor* ex);
 int orbx_get_scale_tables(const orbx_extractor* ex, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
                           int* features_per_level);
 int orbx_get_umax(const orbx_extractor* ex, int* umax16);
+/* Which bit_pattern_31_ (src/ORBextractor.cc:236-494) the descriptors are computed with.  The reference's working copy has the
+ * token VX_FAILURE between two rows of the table (:261): `-8,-7, -6,-2,VX_FAILURE <newline> -2,11, ...` is the expression
+ * VX_FAILURE - 2, and OpenVX defines VX_FAILURE = -1 — so the reference AS IT COMPILES holds -3 in element 96 (x of the first
+ * point of pair 24: descriptor byte 3, bit 0) where the canonical ORB pattern of OpenCV / upstream ORB-SLAM2 holds -2.
+ *   ORBX_PATTERN_REFERENCE (default)  what the reference binary computes: parity with the reference's own CPU path
+ *   ORBX_PATTERN_CANONICAL            the canonical table (the one ORBvoc.txt was trained with) */
+#define ORBX_PATTERN_REFERENCE 0
+#define ORBX_PATTERN_CANONICAL 1
+int orbx_extractor_set_pattern(orbx_extractor* ex, int variant);
 /* the stream the handle launches on (cudaStream_t as void*) */
 void* orbx_extractor_stream(const orbx_extractor* ex);
 

@@ -116,6 +116,21 @@ def descriptor(plane: np.ndarray, x: int, y: int, angle: float) -> np.ndarray:
     return d
 
 
+PATTERN_REFERENCE, PATTERN_CANONICAL = 0, 1
+
+
+def set_pattern_variant(v: int) -> None:
+    """bit_pattern_31_ used by descriptor() / Extractor.extract: PATTERN_REFERENCE (default) = the reference as it compiles
+    (element 96 = VX_FAILURE - 2 = -3, src/ORBextractor.cc:261-262), PATTERN_CANONICAL = the ORB pattern of OpenCV / upstream."""
+    lib().orc_set_pattern_variant(int(v))
+
+
+def pattern_values() -> np.ndarray:
+    out = np.empty(1024, np.int32)
+    lib().orc_pattern_values(_p(out))
+    return out
+
+
 def descriptor_distance(a: np.ndarray, b: np.ndarray) -> int:
     a = np.ascontiguousarray(a, dtype=np.uint8)
     b = np.ascontiguousarray(b, dtype=np.uint8)

@@ -225,9 +225,28 @@ float fast_atan2(float y, float x) {
 // ================================================================================================
 // ORBextractor — src/ORBextractor.cc (CPU branches only)
 // ================================================================================================
-static const int kPattern[256 * 4] = {
+// bit_pattern_31_ (:236-494).  The table below is the CANONICAL ORB pattern (OpenCV, upstream ORB-SLAM2).  The reference's
+// working copy has the token VX_FAILURE between two rows (:261): `... -6,-2/*...*/,VX_FAILURE <newline> -2,11, ...` is the
+// expression VX_FAILURE - 2, and OpenVX defines VX_FAILURE = -1, so the reference AS IT COMPILES holds -3 where the canonical
+// table holds -2 (element 96: x of the first point of pair 24).  variant 0 = the reference as compiled (the default: parity is
+// with the reference's own CPU path), 1 = canonical.  tests/test_oracle_golden.py compiles the reference's lines to show it.
+static const int kPatternCanonical[256 * 4] = {
 #include "../orb_slam_cuda_b200/csrc/orb_pattern_31.inc"
 };
+static int g_patternVariant = 0;
+static const int* pattern_table() {
+    static int ref[256 * 4];
+    static bool init = false;
+    if (!init) {
+        for (int i = 0; i < 1024; ++i) ref[i] = kPatternCanonical[i];
+        ref[96] = -1 /* VX_FAILURE */ - 2;
+        init = true;
+    }
+    return g_patternVariant == 0 ? ref : kPatternCanonical;
+}
+void set_pattern_variant(int v) { g_patternVariant = v ? 1 : 0; }
+int pattern_variant() { return g_patternVariant; }
+const int* pattern_values() { return pattern_table(); }
 
 // Constructor tables — src/ORBextractor.cc:496-557 (buildGraph at :559 is the OpenVX path, not restated).
 Extractor::Extractor(int nf, float sf, int nl, int ini, int mn)
@@ -453,7 +472,7 @@ void orb_descriptor(float angle_deg, const uint8_t* center, size_t stepz, uint8_
     const float angle = angle_deg * factorPI;
     const float a = cosf(angle), b = sinf(angle);
     const int step = (int)stepz;
-    const int* pat = kPattern;
+    const int* pat = pattern_table();
     auto tap = [&](int idx) -> int {
         const int px = pat[2 * idx], py = pat[2 * idx + 1];
         return center[cv_round(px * b + py * a) * step + cv_round(px * a - py * b)];

@@ -74,6 +74,11 @@ struct Extractor {
     size_t level_step(int l) const { return (size_t)padded[l].w; }
 };
 
+// bit_pattern_31_ variant used by orb_descriptor / Extractor::extract: 0 = the reference as it compiles (element 96 = VX_FAILURE - 2
+// = -3, src/ORBextractor.cc:261-262; the default), 1 = the canonical ORB pattern (-2 there)
+void set_pattern_variant(int v);
+int pattern_variant();
+const int* pattern_values();  // the 1024 integers of the current variant
 float ic_angle(const uint8_t* center, size_t step, const std::vector<int>& umax);
 void orb_descriptor(float angle_deg, const uint8_t* center, size_t step, uint8_t* desc);
 

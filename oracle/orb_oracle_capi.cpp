@@ -85,6 +85,9 @@ void orc_descriptor(const uint8_t* plane, int step, int x, int y, float angle, u
     orb_descriptor(angle, plane + (size_t)y * step + x, step, desc);
 }
 int orc_descriptor_distance(const uint8_t* a, const uint8_t* b) { return descriptor_distance(a, b); }
+void orc_set_pattern_variant(int v) { set_pattern_variant(v); }
+int orc_pattern_variant() { return pattern_variant(); }
+void orc_pattern_values(int* out) { std::memcpy(out, pattern_values(), 1024 * sizeof(int)); }
 
 int orc_search_for_initialization(const KeyPoint* k1, int n1, const uint8_t* d1, const KeyPoint* k2, int n2, const uint8_t* d2,
                                   float minX, float maxX, float minY, float maxY, float* prevXY, int* matches12,

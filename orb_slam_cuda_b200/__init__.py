@@ -116,6 +116,14 @@ class ORBextractor:
     def GetInverseScaleSigmaSquares(self): return self._inv2.copy()
     def features_per_level(self): return self._quota.copy()
 
+    PATTERN_REFERENCE, PATTERN_CANONICAL = 0, 1
+
+    def set_pattern(self, variant: int):
+        """orbx_extractor_set_pattern: PATTERN_REFERENCE (default) = bit_pattern_31_ as the reference compiles it (element 96 = VX_FAILURE - 2
+        = -3, src/ORBextractor.cc:261-262), PATTERN_CANONICAL = the canonical ORB table."""
+        lib().orbx_extractor_set_pattern.argtypes = [C.c_void_p, C.c_int]
+        _check(lib().orbx_extractor_set_pattern(self._h, int(variant)))
+
     def umax(self):
         u = np.empty(16, np.int32)
         _check(lib().orbx_get_umax(self._h, _p(u)))

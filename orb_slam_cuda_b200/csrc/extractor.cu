@@ -105,6 +105,7 @@ struct orbx_extractor {
     int lastBatch = 0;
     int lastScratchBase = 0; // scratch frame holding frame `lastFrameBase` of the caller's batch
     int lastFrameBase = 0;   // index (within the caller's batch) of frame 0 of the scratch: > 0 after a chunked host batch
+    int patternVariant = ORBX_PATTERN_REFERENCE;
 };
 
 // ---- constructor tables (src/ORBextractor.cc:501-555) -----------------------------------------------------------
@@ -435,6 +436,7 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
                         bool resetStatus = true, int f0 = 0) {
     FrameGeom g = ex->g;
     g.f0 = f0;  // scratch frames [f0, f0 + batch)
+    g.patternVariant = ex->patternVariant;
     const int nl = g.nlevels;
     int* cellCnt = ex->cellCnt.as<int>() + (size_t)f0 * g.nCellsTotal;
     uint32_t* cellKeys = ex->cellKeys.as<uint32_t>() + (size_t)f0 * g.nCellsTotal * CELL_CAP;
@@ -651,6 +653,21 @@ const char* orbx_stage_name(int stage) {
     static const char* names[ORBX_NUM_STAGES] = {"Pyramid/Resize", "FAST+Grid", "Make quadtree", "Gaussian Blur",
                                                  "Compute angle + ORB descriptor + Compute scale"};
     return stage >= 0 && stage < ORBX_NUM_STAGES ? names[stage] : "";
+}
+
+int orbx_extractor_set_pattern(orbx_extractor* ex, int variant) {
+    if (!ex || (variant != ORBX_PATTERN_REFERENCE && variant != ORBX_PATTERN_CANONICAL)) {
+        set_error("orbx_extractor_set_pattern: variant must be ORBX_PATTERN_REFERENCE or ORBX_PATTERN_CANONICAL");
+        return ORBX_E_INVALID;
+    }
+    if (ex->patternVariant != variant && ex->graphExec) {  // the captured single-frame graph holds the old kernel parameters
+        cudaStreamSynchronize(ex->stream);
+        cudaGraphExecDestroy(ex->graphExec);
+        ex->graphExec = nullptr;
+        ex->graphSeen = false;
+    }
+    ex->patternVariant = variant;
+    return ORBX_OK;
 }
 
 int orbx_get_umax(const orbx_extractor* ex, int* umax16) {

@@ -22,9 +22,6 @@
 namespace orbx {
 
 __constant__ int c_umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
-__constant__ signed char c_pattern[1024] = {
-#include "orb_pattern_31.inc"
-};
 
 // cv::fastAtan2 (degrees in [0, 360)), float32, no contraction
 __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
@@ -104,10 +101,11 @@ constexpr int BP_ROWS = 2 * BP_HALF + 1;  // 37 rows; a row is 48 bytes read fro
 constexpr int BP_WORDS = 14, BP_STRIDE = BP_WORDS * 4;  // shared row stride: 56 bytes (8-byte aligned rows for cp.async)
 
 // Tables the kernel copies into shared memory, filled once per process by init_describe_tables():
-//   d_patF  : the 512 pattern points as floats, laid out [pair k of the lane][lane] as (x0, y0, x1, y1)
+//   d_patF  : the 512 pattern points as floats, laid out [pair k of the lane][lane] as (x0, y0, x1, y1), once per variant of
+//             bit_pattern_31_ (orbx_extractor_set_pattern)
 //   d_coefU : [row r = v + 15][word j] 4 signed bytes  u = 4j + q - 15  inside the circular patch (|u| <= umax[|v|]), else 0
 //   d_coefV : same mask, bytes = v
-__device__ float4 d_patF[8 * 32];
+__device__ float4 d_patF[2][8 * 32];  // [pattern variant]: 0 = the reference as it compiles (element 96 = -3), 1 = canonical
 __device__ uint32_t d_coefU[32 * 8];
 __device__ uint32_t d_coefV[32 * 8];
 
@@ -131,7 +129,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     __shared__ int sBefore[ORBX_MAX_LEVELS + 1];
     __shared__ unsigned char sLevelOf[DESC_WARPS * DESC_PER_WARP];  // pyramid level of each of the CTA's slots
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
-        patF[i] = d_patF[i];
+        patF[i] = d_patF[g.patternVariant & 1][i];
         coefU[i] = d_coefU[i];
         coefV[i] = d_coefV[i];
     }
@@ -281,12 +279,17 @@ static int init_describe_tables() {
 #include "orb_pattern_31.inc"
     };
     static const int umax[16] = {15, 15, 15, 15, 14, 14, 14, 13, 13, 12, 11, 10, 9, 8, 6, 3};
-    float4 pf[256];
-    for (int lane = 0; lane < 32; ++lane)
-        for (int k = 0; k < 8; ++k) {
-            const signed char* p = pat + lane * 32 + 4 * k;  // pair 8 * lane + k: (x0, y0, x1, y1)
-            pf[k * 32 + lane] = make_float4((float)p[0], (float)p[1], (float)p[2], (float)p[3]);
-        }
+    // variant 0 (ORBX_PATTERN_REFERENCE): the reference as it compiles — `-6,-2,VX_FAILURE <newline> -2,11` (src/ORBextractor.cc:261-262) is
+    // the expression VX_FAILURE - 2 = -3 in element 96; variant 1 (ORBX_PATTERN_CANONICAL): the table of OpenCV / upstream ORB-SLAM2
+    float4 pf[2][256];
+    for (int variant = 0; variant < 2; ++variant)
+        for (int lane = 0; lane < 32; ++lane)
+            for (int k = 0; k < 8; ++k) {
+                const int e = lane * 32 + 4 * k;  // pair 8 * lane + k: (x0, y0, x1, y1)
+                float v[4];
+                for (int q = 0; q < 4; ++q) v[q] = (float)((variant == 0 && e + q == 96) ? -3 : (int)pat[e + q]);
+                pf[variant][k * 32 + lane] = make_float4(v[0], v[1], v[2], v[3]);
+            }
     uint32_t cu[256], cv[256];
     for (int r = 0; r < 32; ++r)
         for (int j = 0; j < 8; ++j) {

@@ -77,6 +77,7 @@ struct FrameGeom {
     int nStrips;              // FAST strips per frame (all levels)
     int blurTilesTotal;
     int iniTh, minTh;
+    int patternVariant;       // ORBX_PATTERN_REFERENCE (0) / ORBX_PATTERN_CANONICAL (1): which bit_pattern_31_ the descriptors use
     int f0;                   // first scratch frame of this launch (lanes of the host-batch pipeline own disjoint ranges)
     LevelGeom lv[ORBX_MAX_LEVELS];
 };

@@ -215,6 +215,30 @@ def test_monocular_initialisation_extractor(kind, nfeatures):
     assert np.array_equal(k1.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d1, od)
 
 
+def test_pattern_variants():
+    """bit_pattern_31_ as the reference compiles it (default: element 96 = VX_FAILURE - 2 = -3, src/ORBextractor.cc:261-262) and the
+    canonical ORB table: both equal the oracle's variant bit for bit, they differ from each other in bit 0 of descriptor byte 3 only
+    (pair 24), keypoints are the same, and switching back and forth (incl. the replayed single-frame graph) takes effect."""
+    gx, ox = make("tum")
+    img = synth.frame("tum", 21)
+    try:
+        out = {}
+        for variant in (X.ORBextractor.PATTERN_REFERENCE, X.ORBextractor.PATTERN_CANONICAL, X.ORBextractor.PATTERN_REFERENCE):
+            gx.set_pattern(variant)
+            O.set_pattern_variant(variant)
+            for _ in range(3):  # the third call replays the captured graph
+                k, d = gx(img)
+            ok, od = ox.extract(img)
+            assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od), variant
+            out[variant] = (k.copy(), d.copy())
+        (k0, d0), (k1, d1) = out[0], out[1]
+        assert np.array_equal(k0.view(np.uint8), k1.view(np.uint8))
+        diff = d0 ^ d1
+        assert diff.any() and not np.delete(diff, 3, axis=1).any() and not (diff[:, 3] & 0xFE).any()
+    finally:
+        O.set_pattern_variant(O.PATTERN_REFERENCE)
+
+
 def test_strided_input_and_empty():
     gx, ox = make("tum")
     big = np.zeros((500, 700), np.uint8)

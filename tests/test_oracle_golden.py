@@ -98,20 +98,40 @@ PATTERN_SHA256 = "88df8ca875cc8db56799edd57bb914edad8acb2d48c202b7a464a575b55dbd
 
 
 def test_pattern_table():
-    """All 1024 integers of bit_pattern_31_ (src/ORBextractor.cc:236-494): pinned by a SHA-256 everywhere, and re-parsed from the
-    reference source where /root/reference is mounted (comments and the stray VX_FAILURE token of :261 removed)."""
+    """All 1024 integers of bit_pattern_31_ (src/ORBextractor.cc:236-494).  The CANONICAL table (csrc/orb_pattern_31.inc: OpenCV's ORB
+    pattern) is pinned by a SHA-256 everywhere.  The table the reference ACTUALLY holds is read off the reference itself where
+    /root/reference is mounted: its lines are compiled (from where they lie, into a temporary file) with OpenVX's VX_FAILURE = -1 in
+    scope — the token at :261 is not a syntax error, `-6,-2,VX_FAILURE <newline> -2,11` is the expression VX_FAILURE - 2 — and give
+    1024 integers that differ from the canonical ones in element 96 only (-3 for -2).  That is the oracle's and the product's
+    default variant (PATTERN_REFERENCE)."""
     import hashlib
-    import re
+    import subprocess
+    import tempfile
     vals = _pattern_values()
     assert len(vals) == 1024 and vals[:4] == [8, -3, 9, 5] and vals[-4:] == [-1, -6, 0, -11]
     assert max(abs(v) for v in vals) <= 13
     assert hashlib.sha256(",".join(map(str, vals)).encode()).hexdigest() == PATTERN_SHA256
+    O.set_pattern_variant(O.PATTERN_CANONICAL)
+    assert O.pattern_values().tolist() == vals
+    O.set_pattern_variant(O.PATTERN_REFERENCE)
+    as_compiled = O.pattern_values().tolist()
+    assert [i for i in range(1024) if as_compiled[i] != vals[i]] == [96] and as_compiled[96] == -3 and vals[96] == -2
     ref = "/root/reference/src/ORBextractor.cc"
     if os.path.exists(ref):
-        body = "\n".join(open(ref).read().split("\n")[235:495])
-        body = re.sub(r"//.*", "", re.sub(r"/\*.*?\*/", "", body, flags=re.S))
-        toks = [int(t) for t in re.findall(r"-?\d+", body[body.index("{") + 1:body.rindex("}")])]
-        assert toks == vals
+        text = open(ref).read()
+        begin = text.index("static int bit_pattern_31_[256*4]")
+        lines = text[begin:text.index("};", begin) + 2].split("\n")  # `static int bit_pattern_31_[256*4] =` ... `};`
+        assert len(lines) == 259
+        with tempfile.TemporaryDirectory() as d:
+            src = os.path.join(d, "pattern.cpp")
+            with open(src, "w") as f:
+                f.write("#include <cstdio>\nenum vx_status_e { VX_FAILURE = -1 };  // OpenVX 1.x, VX/vx_types.h\n" + "\n".join(lines) +
+                        "\nint main() { printf(\"%zu\\n\", sizeof(bit_pattern_31_) / sizeof(int));"
+                        " for (int i = 0; i < 1024; ++i) printf(\"%d\\n\", bit_pattern_31_[i]); }\n")
+            exe = os.path.join(d, "pattern")
+            subprocess.check_call(["g++", "-o", exe, src])
+            out = [int(t) for t in subprocess.check_output([exe]).split()]
+        assert out[0] == 1024 and out[1:] == as_compiled
 
 
 def test_pattern_against_cv2_orb():
@@ -128,9 +148,13 @@ def test_pattern_against_cv2_orb():
     kps, desc = orb.compute(img, kps)
     assert len(kps) == len(pts)
     blurred = np.clip(np.rint(cv2.GaussianBlur(img.astype(np.float32), (7, 7), 2, 2, borderType=cv2.BORDER_REFLECT_101)), 0, 255).astype(np.uint8)
-    for kp, d in zip(kps, desc):
-        ours = O.descriptor(blurred, int(kp.pt[0]), int(kp.pt[1]), 0.0)
-        assert np.array_equal(ours, d)
+    try:
+        O.set_pattern_variant(O.PATTERN_CANONICAL)  # OpenCV holds the canonical table
+        for kp, d in zip(kps, desc):
+            ours = O.descriptor(blurred, int(kp.pt[0]), int(kp.pt[1]), 0.0)
+            assert np.array_equal(ours, d)
+    finally:
+        O.set_pattern_variant(O.PATTERN_REFERENCE)
 
 
 def test_descriptor_distance_kat():
