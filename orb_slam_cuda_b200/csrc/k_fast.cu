@@ -49,10 +49,10 @@ constexpr int FS_THREADS = ORBX_FS_THREADS;
 #define ORBX_FS_WL 1280
 #endif
 #ifndef ORBX_FS_LIST1
-#define ORBX_FS_LIST1 2048
+#define ORBX_FS_LIST1 1536  // (with LIST2 768: 30.9 KB of shared memory per CTA, 7 CTAs per SM instead of 6; smaller lists overflow into the redo path: profiles/r02_variants.txt)
 #endif
 #ifndef ORBX_FS_LIST2
-#define ORBX_FS_LIST2 1024
+#define ORBX_FS_LIST2 768
 #endif
 #ifndef ORBX_FS_MAXCELLS
 #define ORBX_FS_MAXCELLS 4

@@ -984,6 +984,30 @@ int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypo
         set_error("orbx_stereo_match: both extractors must have extracted a frame on the same device with the same pyramid depth");
         return ORBX_E_INVALID;
     }
+    if (L.lastBatch != 1 || R.lastBatch != 1) {  // the scratch then holds exactly the frame orbx_pyramid_level_host(0, ...) serves
+        set_error("orbx_stereo_match: the last call of each extractor must have been a single-frame orbx_extract (left: %d frames, right: %d)",
+                  L.lastBatch, R.lastBatch);
+        return ORBX_E_INVALID;
+    }
+    // keypoints must lie where the extractor puts them (>= 16 px inside their level): the SAD windows read 5 + 5 px around the
+    // scaled position, which then stays inside the padded plane; stale or foreign keypoints are refused instead of read out of bounds
+    for (int pass = 0; pass < 2; ++pass) {
+        const orbx_keypoint* k = pass ? kR : kL;
+        const ExtractorView& V = pass ? R : L;
+        for (int i = 0; i < (pass ? nR : nL); ++i) {
+            const int o = k[i].octave;
+            bool ok = o >= 0 && o < V.g->nlevels;
+            if (ok) {
+                const float sx = k[i].x * L.invScale[o], sy = k[i].y * L.invScale[o];
+                ok = sx >= -1.f && sy >= -1.f && sx <= (float)V.g->lv[o].w && sy <= (float)V.g->lv[o].h;
+            }
+            if (!ok) {
+                set_error("orbx_stereo_match: %s keypoint %d (%.1f, %.1f, octave %d) lies outside its pyramid level", pass ? "right" : "left", i,
+                          k[i].x, k[i].y, o);
+                return ORBX_E_INVALID;
+            }
+        }
+    }
     if (nL == 0) return ORBX_OK;
     ORBX_CUDA(cudaSetDevice(L.device));
     Workspace* w;

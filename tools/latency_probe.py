@@ -1,0 +1,17 @@
+#!/usr/bin/env python3
+"""Single-frame latency probe (development tool): a few orbx_extract calls on one KITTI frame; run under
+`ncu --metrics gpu__time_duration.sum` (ORBX_NO_GRAPH=1 so that the kernels are separate launches) for the per-kernel times of ONE frame."""
+import os, sys, time
+import numpy as np
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import orb_slam_cuda_b200 as X
+from orb_slam_cuda_b200 import synth
+kind = sys.argv[1] if len(sys.argv) > 1 else "kitti"
+nf = {"kitti": 2000, "tum": 1000, "euroc": 1200}[kind]
+h, w = synth.SHAPES[kind]
+ex = X.ORBextractor(nf, 1.2, 8, 20, 7, w, h)
+img = synth.frame(kind, 5)
+ts = []
+for i in range(30):
+    t0 = time.perf_counter(); ex(img); ts.append((time.perf_counter() - t0) * 1e3)
+print(kind, "p50 ms", sorted(ts)[len(ts) // 2])
