@@ -78,6 +78,15 @@ def build_host(force: bool = False) -> str:
                                  any(os.path.getmtime(d) > os.path.getmtime(HARNESS) for d in hdrs + [hsrc, CLASSES_SO])):
         subprocess.check_call([cxx] + flags + [hsrc, "-o", HARNESS, "-L", HERE, "-lorbx_classes", "-lorbx", "-pthread",
                                                "-Wl,-rpath,$ORIGIN/../../orb_slam_cuda_b200"])
+    # the same harness with the class layer's ORBX_HAVE_OPENCV branches switched on: the test-only <opencv2/...> of
+    # oracle/ref_matcher/shim stands in for OpenCV (its cv::Mat expressions evaluate like OpenCV's CV_32F paths), and
+    # host/ORBextractor.cc is compiled along because cv::Mat then has that header's layout
+    shim = os.path.join(HERE, "..", "oracle", "ref_matcher", "shim")
+    hcv = HARNESS + "_cv"
+    if os.path.isdir(shim) and os.path.exists(hsrc) and (force or not os.path.exists(hcv) or any(
+            os.path.getmtime(d) > os.path.getmtime(hcv) for d in hdrs + [hsrc, src, SO, os.path.join(shim, "opencv2", "core", "core.hpp")])):
+        subprocess.check_call([cxx, "-std=c++17", "-O2", "-w", "-ffp-contract=off", "-pthread", "-I", shim, "-I", inc, hsrc, src, "-o", hcv,
+                               "-L", HERE, "-lorbx", "-Wl,-rpath,$ORIGIN/../../orb_slam_cuda_b200"])
     return CLASSES_SO
 
 

@@ -467,3 +467,31 @@ def test_reference_frame_cc_runs_unchanged_on_the_class_surface(tmp_path):
     cs, so = X.DeviceFrame(kL, dL, (0.0, float(w), 0.0, float(h))).grid()
     assert np.array_equal(np.concatenate([[0], np.cumsum([c.size for c in cells])]).astype(np.int32), cs)
     assert np.array_equal(np.concatenate(cells), so)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["mono", "stereo", "track", "fuse"])
+def test_opencv_branches_of_the_class_layer(harness, tmp_path, mode):
+    """include/ORBmatcher.h and host/ORBextractor.cc have `#if ORBX_HAVE_OPENCV` branches — the ones a real ORB-SLAM2 build uses: the
+    reference's own cv::Mat expressions for the pose arithmetic instead of the stand-in's scalar code.  tests/cpp/frame_harness_cv is the
+    same harness compiled with those branches on (the test-only <opencv2/...> of oracle/ref_matcher/shim as OpenCV: products, dot and
+    norm with a double accumulator like OpenCV's CV_32F paths).  Both builds must write the same bytes in every mode."""
+    cv = harness + "_cv"
+    if not os.path.exists(cv):
+        pytest.skip("frame_harness_cv not built")
+    kind = "euroc" if mode == "stereo" else "tum"
+    if mode == "stereo":
+        a, b = synth.stereo_pair(kind, 4)
+    else:
+        a, b = synth.frame(kind, 45), synth.shifted_frame(kind, 45)
+    h, w = a.shape
+    raw = tmp_path / "in.raw"
+    raw.write_bytes(a.tobytes() + b.tobytes())
+    extra = {"mono": [], "stereo": ["47.9", "435.2"], "track": ["15.0"], "fuse": ["3.0"]}[mode]
+    outs = []
+    for exe in (harness, cv):
+        out = tmp_path / (os.path.basename(exe) + ".bin")
+        r = subprocess.run([exe, mode, str(raw), str(w), str(h), "1000"] + extra + [str(out)], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr
+        outs.append(out.read_bytes())
+    assert len(outs[0]) > 1000 and outs[0] == outs[1]
