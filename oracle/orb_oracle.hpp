@@ -8,7 +8,7 @@
 // Parity pinning.  The reference ships no tests or golden vectors.
 //   * Matchers, Frame grid, ComputeStereoMatches: PINNED TO REFERENCE OBJECT CODE.  /root/reference's own src/ORBmatcher.cc and
 //     src/Frame.cc are compiled where they lie (oracle/ref_matcher/Makefile -> oracle/_ref/libref_matcher.so) and every matcher
-//     below equals them on 20 seeded cases, live and through tests/golden/ref_matcher.npz (tests/test_oracle_ref_matcher.py).
+//     below equals them on 25 seeded cases, live and through tests/golden/ref_matcher.npz (tests/test_oracle_ref_matcher.py).
 //     The DBoW2 descent is pinned the same way against the reference's Thirdparty/DBoW2 (oracle/ref_dbow2).
 //   * Extractor (ORBextractor.cc): its source does not compile here (VisionWorks / OpenVX / OpenCV C++ headers absent), so the
 //     control flow follows the reference line ranges cited at each function, the five OpenCV primitives it calls (resize,

@@ -476,6 +476,141 @@ int refm_fuse(int n1, const float* x3D, const float* normal, const float* minmax
     return n;
 }
 
+// ORBmatcher::SearchByProjection(Frame& CurrentFrame, KeyFrame*, const set<MapPoint*>& sAlreadyFound, th, ORBdist)
+// (src/ORBmatcher.cc:1472-1599, Tracking::Relocalization).  CurrentFrame.mTcw = identity: the positions handed in are x3Dc.
+// found1[i]: the keyframe's point i is in sAlreadyFound; level1 = what PredictScale returns; k1 = the keyframe's mvKeysUn (angles).
+int refm_search_by_projection_reloc(int n1, const float* x3D, const uint8_t* has1, const uint8_t* bad1, const uint8_t* found1,
+                                    const float* minmax, const int* level1, const uint8_t* mpDesc1, const cv::KeyPoint* k1,
+                                    const cv::KeyPoint* k2, int n2, const uint8_t* d2, const uint8_t* occupied2, const int* wh,
+                                    const float* cam, const float* sf, int nl, float th, int orbDist, int checkOri, int* match21) {
+    Cam c{wh[0], wh[1], cam[0], cam[1], cam[2], cam[3], 40.f};
+    std::vector<uint8_t> zero((size_t)std::max(n1, 1) * 32);
+    auto fk = make_frame(k1, n1, zero.data(), c, sf, nl);
+    auto cur = make_frame(k2, n2, d2, c, sf, nl);
+    KeyFrame kf;
+    fill_keyframe(kf, *fk->F, 1);
+    std::vector<std::unique_ptr<MapPoint>> mps;
+    std::set<MapPoint*> found;
+    for (int i = 0; i < n1; ++i) {
+        if (!has1[i]) continue;
+        mps.emplace_back(new MapPoint);
+        MapPoint* p = mps.back().get();
+        p->mnId = i;
+        p->mWorldPos = vec3(x3D + 3 * i);
+        p->mDescriptor = desc_mat(mpDesc1 + (size_t)i * 32, 1);
+        p->mbBad = bad1[i] != 0;
+        p->mfMinDistance = minmax[2 * i];
+        p->mfMaxDistance = minmax[2 * i + 1];
+        p->presetLevel = level1[i];
+        kf.mvpMapPoints[i] = p;
+        if (found1[i]) found.insert(p);
+    }
+    MapPoint occupied;
+    occupied.mnId = -100;
+    for (int i = 0; i < n2; ++i)
+        if (occupied2[i]) cur->F->mvpMapPoints[i] = &occupied;
+    cur->F->SetPose(pose(nullptr));
+    ORBmatcher m(0.9f, checkOri != 0);
+    const int n = m.SearchByProjection(*cur->F, &kf, found, th, orbDist);
+    for (int i = 0; i < n2; ++i) {
+        MapPoint* p = cur->F->mvpMapPoints[i];
+        match21[i] = !p || p == &occupied ? -1 : (int)p->mnId;
+    }
+    return n;
+}
+
+// ORBmatcher::Fuse(KeyFrame*, cv::Mat Scw, vpPoints, th, vpReplacePoint) (src/ORBmatcher.cc:977-1100); Scw = scale * [I | 0].
+// replaced[e] = id of the keyframe point reported for list entry e (-1: none); keyframe points are numbered n1 + feature index.
+int refm_fuse_sim3(int n1, const float* x3D, const float* normal, const float* minmax, const int* level1, const uint8_t* bad1,
+                   const uint8_t* mpDesc1, int nEntries, const int* entryPoint, const cv::KeyPoint* k2, int n2, const uint8_t* d2,
+                   const int* kfPointObs, const uint8_t* kfBad, const int* wh, const float* cam, const float* sf, int nl, float scale,
+                   float th, long* ops, int opsCap, int* nOps, int* replaced) {
+    Cam c{wh[0], wh[1], cam[0], cam[1], cam[2], cam[3], 40.f};
+    auto f = make_frame(k2, n2, d2, c, sf, nl);
+    KeyFrame kf;
+    fill_keyframe(kf, *f->F, 1);
+    std::vector<std::unique_ptr<MapPoint>> mps;
+    std::vector<MapPoint*> pts(n1);
+    for (int i = 0; i < n1; ++i) {
+        mps.emplace_back(new MapPoint);
+        MapPoint* p = mps.back().get();
+        p->mnId = i;
+        p->mWorldPos = vec3(x3D + 3 * i);
+        p->mNormalVector = vec3(normal + 3 * i);
+        p->mfMinDistance = minmax[2 * i];
+        p->mfMaxDistance = minmax[2 * i + 1];
+        p->presetLevel = level1[i];
+        p->mbBad = bad1[i] != 0;
+        p->mDescriptor = desc_mat(mpDesc1 + (size_t)i * 32, 1);
+        pts[i] = p;
+    }
+    for (int i = 0; i < n2; ++i)
+        if (kfPointObs[i] >= 0) {
+            mps.emplace_back(new MapPoint);
+            MapPoint* p = mps.back().get();
+            p->mnId = n1 + i;
+            p->mObservations[&kf] = i;
+            p->nObs = kfPointObs[i];
+            p->mbBad = kfBad[i] != 0;
+            kf.mvpMapPoints[i] = p;
+        }
+    std::vector<MapPoint*> vp(nEntries), rep(nEntries, nullptr);
+    for (int e = 0; e < nEntries; ++e) vp[e] = pts[entryPoint[e]];
+    float T[16] = {scale, 0, 0, 0, 0, scale, 0, 0, 0, 0, scale, 0, 0, 0, 0, 1};
+    g_surgery.clear();
+    ORBmatcher m(0.6f, true);
+    const int n = m.Fuse(&kf, pose(T), vp, th, rep);
+    *nOps = (int)g_surgery.size();
+    for (int i = 0; i < *nOps && i < opsCap; ++i) {
+        ops[3 * i] = g_surgery[i].op;
+        ops[3 * i + 1] = g_surgery[i].a;
+        ops[3 * i + 2] = g_surgery[i].b;
+    }
+    for (int e = 0; e < nEntries; ++e) replaced[e] = rep[e] ? (int)rep[e]->mnId : -1;
+    return n;
+}
+
+// ORBmatcher::SearchBySim3 (src/ORBmatcher.cc:1102-1326): both keyframes at the identity pose, Sim3 = (s12, I, t12); the points
+// of keyframe k sit at x3D_k in its camera frame; matched12[i] >= 0: vpMatches12[i] is set on entry to keyframe-2 point that
+// index (already matched).  out12[i] = index of the keyframe-2 point vpMatches12[i] holds afterwards, -1 = null.
+int refm_search_by_sim3(int n1, const cv::KeyPoint* k1, const uint8_t* d1, const uint8_t* has1, const uint8_t* bad1, const float* x3D1,
+                        const int* level1, int n2, const cv::KeyPoint* k2, const uint8_t* d2, const uint8_t* has2, const uint8_t* bad2,
+                        const float* x3D2, const int* level2, const float* minmax, const int* matched12, const int* wh, const float* cam,
+                        const float* sf, int nl, float s12, const float* t12, float th, int* out12) {
+    Cam c{wh[0], wh[1], cam[0], cam[1], cam[2], cam[3], 40.f};
+    auto f1 = make_frame(k1, n1, d1, c, sf, nl), f2 = make_frame(k2, n2, d2, c, sf, nl);
+    KeyFrame kf1, kf2;
+    fill_keyframe(kf1, *f1->F, 1);
+    fill_keyframe(kf2, *f2->F, 2);
+    std::vector<std::unique_ptr<MapPoint>> mps;
+    auto fill = [&](KeyFrame& kf, int n, const uint8_t* has, const uint8_t* bad, const float* x3D, const int* level, const uint8_t* d) {
+        for (int i = 0; i < n; ++i) {
+            if (!has[i]) continue;
+            mps.emplace_back(new MapPoint);
+            MapPoint* p = mps.back().get();
+            p->mnId = i;
+            p->mWorldPos = vec3(x3D + 3 * i);
+            p->mDescriptor = desc_mat(d + (size_t)i * 32, 1);
+            p->mbBad = bad[i] != 0;
+            p->mfMinDistance = minmax[0];
+            p->mfMaxDistance = minmax[1];
+            p->presetLevel = level[i];
+            p->mObservations[&kf] = i;
+            kf.mvpMapPoints[i] = p;
+        }
+    };
+    fill(kf1, n1, has1, bad1, x3D1, level1, d1);
+    fill(kf2, n2, has2, bad2, x3D2, level2, d2);
+    std::vector<MapPoint*> m12(n1, nullptr);
+    for (int i = 0; i < n1; ++i)
+        if (matched12[i] >= 0) m12[i] = kf2.mvpMapPoints[matched12[i]];
+    cv::Mat R12 = cv::Mat::eye(3, 3, CV_32F), t = vec3(t12);
+    ORBmatcher m(0.75f, true);
+    const int n = m.SearchBySim3(&kf1, &kf2, m12, s12, R12, t, th);
+    for (int i = 0; i < n1; ++i) out12[i] = m12[i] ? (int)m12[i]->mnId : -1;
+    return n;
+}
+
 // Frame::ComputeStereoMatches (src/Frame.cc:465-639) through the reference's stereo constructor (:61-116): the stand-in
 // extractors return the given keypoints / descriptors and hold the given pyramid levels (interior, tightly packed).
 int refm_stereo_matches(const cv::KeyPoint* kL, int nL, const uint8_t* dL, const cv::KeyPoint* kR, int nR, const uint8_t* dR,

@@ -187,3 +187,43 @@ def stereo_matches(kL, dL, kR, dR, levelsL, levelsR, wh, cam, bf, scale_factors)
     lib().refm_stereo_matches(_p(kL), kL.size, _p(dL), _p(kR), kR.size, _p(dR), arr_l, arr_r, _p(lwh), _p(np.array(wh, np.int32)), _p(cam),
                               C.c_float(bf), _p(sf), sf.size, _p(ur), _p(depth))
     return ur[:kL.size], depth[:kL.size]
+
+
+def search_by_projection_reloc(x3Dc, has1, bad1, found1, minmax, level1, mp_desc1, k1, k2, d2, occupied2, cam, bounds, scale_factors, th,
+                               orb_dist=100, check_ori=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) with CurrentFrame at the identity pose."""
+    x3, has1, bad1, found1, occupied2 = _f32(x3Dc), _u8(has1), _u8(bad1), _u8(found1), _u8(occupied2)
+    mm, level1, mp, k1, k2, d2 = _f32(minmax), _i32(level1), _u8(mp_desc1), _kp(k1), _kp(k2), _u8(d2)
+    cam, sf = _f32(cam), _f32(scale_factors)
+    m21 = np.empty(max(k2.size, 1), np.int32)
+    n = lib().refm_search_by_projection_reloc(has1.size, _p(x3), _p(has1), _p(bad1), _p(found1), _p(mm), _p(level1), _p(mp), _p(k1), _p(k2),
+                                              k2.size, _p(d2), _p(occupied2), _p(_wh(bounds)), _p(cam), _p(sf), sf.size, C.c_float(th),
+                                              int(orb_dist), int(check_ori), _p(m21))
+    return n, m21[:k2.size]
+
+
+def fuse_sim3(x3D, normal, minmax, level1, bad1, mp_desc1, entry_point, k2, d2, kf_point_obs, kf_bad, cam, bounds, scale_factors, scale, th):
+    """ORBmatcher::Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) with Scw = scale * [I | 0].  Returns (nFused, ops, replaced)."""
+    x3, nr, mm, level1 = _f32(x3D), _f32(normal), _f32(minmax), _i32(level1)
+    bad1, mp, ent, k2, d2 = _u8(bad1), _u8(mp_desc1), _i32(entry_point), _kp(k2), _u8(d2)
+    kpo, kfb, cam, sf = _i32(kf_point_obs), _u8(kf_bad), _f32(cam), _f32(scale_factors)
+    cap = 3 * (ent.size + 8)
+    ops = np.zeros((cap, 3), np.int64)
+    nops = C.c_int(0)
+    rep = np.empty(max(ent.size, 1), np.int32)
+    n = lib().refm_fuse_sim3(level1.size, _p(x3), _p(nr), _p(mm), _p(level1), _p(bad1), _p(mp), ent.size, _p(ent), _p(k2), k2.size, _p(d2),
+                             _p(kpo), _p(kfb), _p(_wh(bounds)), _p(cam), _p(sf), sf.size, C.c_float(scale), C.c_float(th), _p(ops), cap,
+                             C.byref(nops), _p(rep))
+    return n, ops[:nops.value].copy(), rep[:ent.size]
+
+
+def search_by_sim3(k1, d1, has1, bad1, x3D1, level1, k2, d2, has2, bad2, x3D2, level2, minmax, matched12, cam, bounds, scale_factors, s12, t12, th):
+    """ORBmatcher::SearchBySim3 with both keyframes at the identity pose and R12 = I.  Returns (nFound, vpMatches12 as keyframe-2 indices)."""
+    k1, d1, has1, bad1, x1, l1 = _kp(k1), _u8(d1), _u8(has1), _u8(bad1), _f32(x3D1), _i32(level1)
+    k2, d2, has2, bad2, x2, l2 = _kp(k2), _u8(d2), _u8(has2), _u8(bad2), _f32(x3D2), _i32(level2)
+    mm, m12, cam, sf, t = _f32(minmax), _i32(matched12), _f32(cam), _f32(scale_factors), _f32(t12)
+    out = np.empty(max(k1.size, 1), np.int32)
+    n = lib().refm_search_by_sim3(k1.size, _p(k1), _p(d1), _p(has1), _p(bad1), _p(x1), _p(l1), k2.size, _p(k2), _p(d2), _p(has2), _p(bad2),
+                                  _p(x2), _p(l2), _p(mm), _p(m12), _p(_wh(bounds)), _p(cam), _p(sf), sf.size, C.c_float(s12), _p(t),
+                                  C.c_float(th), _p(out))
+    return n, out[:k1.size]

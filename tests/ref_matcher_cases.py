@@ -291,6 +291,145 @@ def case_stereo(kind, k, nfeat, bf, fx):
     return oracle, reference
 
 
+def case_sbp_reloc(seed, th, orb_dist, ori):
+    """Relocalisation SearchByProjection (src/ORBmatcher.cc:1472-1599): acceptance distance ORBdist, no depth-sign test, levels
+    level-1 .. level+1, sAlreadyFound and bad points skipped, current keypoints that hold ANY map point are not candidates."""
+    s = TP.scenario(seed, False)
+    rng = np.random.default_rng(800 + seed)
+    x3 = s["x3Dc"].astype(F32)
+    n1 = x3.shape[0]
+    dist = np.sqrt((x3.astype(np.float64) ** 2).sum(1)).astype(F32)
+    lo, hi = (dist * rng.uniform(0.3, 1.1, n1)).astype(F32), (dist * rng.uniform(0.95, 2.5, n1)).astype(F32)
+    bad, found = (rng.random(n1) < 0.05).astype(np.uint8), (rng.random(n1) < 0.08).astype(np.uint8)
+    has = s["valid1"]
+    level = np.clip(s["octave1"] + rng.integers(-1, 2, n1), 0, 7).astype(np.int32)
+    ok = (has != 0) & (bad == 0) & (found == 0) & ~((dist < F32(0.8) * lo) | (dist > F32(1.2) * hi))
+    k1 = np.zeros(n1, O.KP_DTYPE)
+    k1["angle"], k1["octave"], k1["x"], k1["y"] = s["angle1"], s["octave1"], 40.0, 40.0
+
+    def oracle():
+        n, m = O.search_by_projection_frame(x3, ok.astype(np.uint8), np.ones(n1, np.uint8), s["mp_desc1"], level, s["angle1"], s["k2"], s["d2"],
+                                            None, s["occupied2"], s["cam"], s["mbf"], s["bounds"], s["scale_factors"], th, 0, ori, orb_dist, False)
+        return (np.array([n], np.int32), _null(m))
+
+    def reference():
+        n, m = R.search_by_projection_reloc(x3, has, bad, found, np.stack([lo, hi], 1), level, s["mp_desc1"], k1, s["k2"], s["d2"],
+                                            s["occupied2"], s["cam"], s["bounds"], s["scale_factors"], th, orb_dist, ori)
+        return (np.array([n], np.int32), m.copy())
+    return oracle, reference
+
+
+def fuse_sim3_replay(idx, dist, entry_point, usable, kf_point_obs, kf_bad, n1):
+    """Fuse(pKF, Scw, ...) after its candidate loop (src/ORBmatcher.cc:1077-1095): no Replace; a keypoint that holds a good point is
+    reported through vpReplacePoint, a free one takes the point.  usable[e]: the entry passed `!isBad() && !spAlreadyFound.count()`
+    and the projection tests."""
+    slot = {j: n1 + j for j in range(len(kf_point_obs)) if kf_point_obs[j] >= 0}
+    bad = set(n1 + j for j in range(len(kf_point_obs)) if kf_point_obs[j] >= 0 and kf_bad[j])
+    ops, rep, fused = [], np.full(len(entry_point), -1, np.int32), 0
+    for e, p in enumerate(entry_point):
+        if not usable[e] or idx[e] < 0 or dist[e] > 50:
+            continue
+        b = int(idx[e])
+        held = slot.get(b)
+        if held is not None:
+            if held not in bad:
+                rep[e] = held
+        else:
+            ops += [(0, int(p), b), (1, int(p), b)]
+            slot[b] = int(p)
+        fused += 1
+    return fused, np.array(ops, np.int64).reshape(-1, 3), rep
+
+
+def case_fuse_sim3(seed, th, scale):
+    s = TP.map_scenario(seed, False)
+    s.update({k: v for k, v in TP.scenario(seed, False).items() if k in ("x3Dc", "cam", "mbf")})
+    rng = np.random.default_rng(900 + seed)
+    x3, normal, minmax, level, bad, ok, uvr, invz, cam = _project(s, rng, th)
+    n1, n2 = level.size, s["k2"].size
+    # Scw = scale * [I | 0]: Rcw = I, tcw = 0, Ow = -0: the same projection; world positions stay x3
+    kf_point_obs = np.where(rng.random(n2) < 0.4, rng.integers(1, 6, n2), -1).astype(np.int32)
+    kf_bad = ((rng.random(n2) < 0.1) & (kf_point_obs >= 0)).astype(np.uint8)
+    entries = np.concatenate([np.arange(n1), rng.integers(0, n1, 40)]).astype(np.int32)  # some points are listed twice
+    inv = (F32(1.0) / (s["scale_factors"] * s["scale_factors"])).astype(F32)
+    usable = ok[entries]
+
+    def oracle():
+        idx, dist = O.fuse_match(uvr[entries], None, level[entries], usable.astype(np.uint8), s["mp_desc1"][entries], s["k2"], s["d2"], None, inv,
+                                 s["bounds"])
+        fused, ops, rep = fuse_sim3_replay(idx, dist, entries, usable, kf_point_obs, kf_bad, n1)
+        return (np.array([fused], np.int32), ops, rep)
+
+    def reference():
+        n, ops, rep = R.fuse_sim3(x3, normal, minmax, level, bad, s["mp_desc1"], entries, s["k2"], s["d2"], kf_point_obs, kf_bad, cam,
+                                  s["bounds"], s["scale_factors"], scale, th)
+        return (np.array([n], np.int32), ops, rep.copy())
+    return oracle, reference
+
+
+def case_sim3(k, th):
+    """SearchBySim3 (src/ORBmatcher.cc:1102-1326): both keyframes at the identity pose, points at depth 5 in their own camera, Sim3 =
+    the translation that the image shift (7, -4) of synth.shifted_frame corresponds to; expected = two candidate passes
+    (O.fuse_match without the gate, TH_HIGH) + the agreement check, with the reference's float order."""
+    k1, d1, (h, w) = _extract("tum", k, 1000)
+    k2, d2, _ = _extract("tum", k, 1000, shifted=True)
+    n1, n2 = k1.size, k2.size
+    cam = np.array([500.0, 500.0, 0.5 * w, 0.5 * h], F32)
+    sf = O.Extractor(1000, 1.2, 8, 20, 7).tables()["scale"]
+    bounds = (0.0, float(w), 0.0, float(h))
+    t12 = np.array([-0.07, 0.04, 0.0], F32)
+    i1, i2 = np.arange(n1), np.arange(n2)
+    has1, has2 = (i1 % 6 != 0).astype(np.uint8), (i2 % 7 != 0).astype(np.uint8)
+    bad1, bad2 = (i1 % 17 == 0).astype(np.uint8), (i2 % 17 == 0).astype(np.uint8)
+
+    def world(kp):
+        return np.stack([((kp["x"] - cam[2]) * F32(5.0) / cam[0]).astype(F32), ((kp["y"] - cam[3]) * F32(5.0) / cam[1]).astype(F32),
+                         np.full(kp.size, 5.0, F32)], 1).astype(F32)
+    x1, x2 = world(k1), world(k2)
+    matched12 = np.full(n1, -1, np.int32)
+    for i in range(4, n1, 25):
+        if has1[i]:
+            matched12[i] = 1  # keyframe-2 point 1 (has2[1] != 0): already matched, both ends are skipped
+    assert has2[1]
+    mm = np.array([3.5 / 0.8, 15.5 / 1.2], F32)  # GetMin/MaxDistanceInvariance = 0.8 * min, 1.2 * max
+
+    def one_pass(xsrc, t, has, bad, already, lvl, desc, kdst, ddst):
+        # p' = I * p + t with cv::Mat arithmetic: the product rounds to float, then a float addition
+        pc = (xsrc + t[None, :]).astype(F32)
+        invz = (1.0 / pc[:, 2].astype(np.float64)).astype(F32)
+        u = (cam[0] * (pc[:, 0] * invz).astype(F32)).astype(F32) + cam[2]
+        v = (cam[1] * (pc[:, 1] * invz).astype(F32)).astype(F32) + cam[3]
+        dist = np.sqrt((pc.astype(np.float64) ** 2).sum(1)).astype(F32)
+        ok = (has != 0) & ~already & (bad == 0) & (pc[:, 2] >= 0) & (u >= 0) & (u < w) & (v >= 0) & (v < h)
+        ok &= ~((dist < F32(0.8) * mm[0]) | (dist > F32(1.2) * mm[1]))
+        uvr = np.stack([u, v, (F32(th) * sf[lvl]).astype(F32)], 1).astype(F32)
+        inv = (F32(1.0) / (sf * sf)).astype(F32)
+        idx, dd = O.fuse_match(uvr, None, lvl, ok.astype(np.uint8), desc, kdst, ddst, None, inv, bounds)
+        return np.where((idx >= 0) & (dd <= 100), idx, -1)
+
+    def oracle():
+        a1 = matched12 >= 0
+        a2 = np.zeros(n2, bool)
+        a2[matched12[a1]] = True
+        t21 = (-(t12.astype(np.float64))).astype(F32)  # -sR21 * t12 with sR21 = I
+        m1 = one_pass(x1, t21, has1, bad1, a1, k1["octave"].astype(np.int32), d1, k2, d2)
+        m2 = one_pass(x2, t12, has2, bad2, a2, k2["octave"].astype(np.int32), d2, k1, d1)
+        out = matched12.copy()
+        found = 0
+        for i in range(n1):
+            j = m1[i]
+            if j >= 0 and m2[j] == i:
+                out[i] = j
+                found += 1
+        return (np.array([found], np.int32), out)
+
+    def reference():
+        n, out = R.search_by_sim3(k1, d1, has1, bad1, x1, k1["octave"], k2, d2, has2, bad2, x2, k2["octave"], mm, matched12, cam, bounds, sf,
+                                  1.0, t12, th)
+        return (np.array([n], np.int32), out.copy())
+    return oracle, reference
+
+
 CASES = {
     "descriptor_distance": lambda: case_descriptor_distance(),
     "features_in_area": lambda: case_features_in_area(),
@@ -311,5 +450,10 @@ CASES = {
     "sbp_sim3_tight": lambda: case_sbp_sim3(12, 4),
     "fuse_stereo": lambda: case_fuse(31, True, 3.0),
     "fuse_mono": lambda: case_fuse(32, False, 4.0),
+    "sbp_reloc": lambda: case_sbp_reloc(7, 10.0, 100, True),
+    "sbp_reloc_tight": lambda: case_sbp_reloc(8, 3.0, 64, False),
+    "fuse_sim3": lambda: case_fuse_sim3(33, 4.0, 2.0),
+    "fuse_sim3_unit": lambda: case_fuse_sim3(34, 10.0, 1.0),
+    "search_by_sim3": lambda: case_sim3(46, 7.5),
     "stereo_euroc": lambda: case_stereo("euroc", 9, 1200, 47.90639384423901, 435.2046959714599),
 }
