@@ -358,3 +358,27 @@ def test_full_size_batch_properties():
             ok, od = ox.extract(frames[f])
             assert n == len(ok) and np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(desc[f, :n], od)
     assert len(first_of) == pool
+
+
+@pytest.mark.parametrize("name", ["kitti_0", "tum_1", "euroc_2", "levels4_sf15", "noise", "blocks", "dim", "few"])
+def test_against_reference_object_code_golden(name):
+    """The CUDA extractor against the REFERENCE's own compiled ORBextractor.cc (tests/golden/ref_extractor.npz, written by
+    tools/gen_extractor_golden.py from oracle/_ref/libref_extractor.so): order, x, y, size, angle, response, octave and the
+    32 descriptor bytes, tolerance 0 — no oracle in between."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(__file__))
+    import ref_extractor_cases as RC
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_extractor.npz"))
+    make_img, kw = RC.CASES[name]
+    img = make_img()
+    assert int(g[name + "/img_sum"]) == int(img.astype(np.int64).sum())
+    a = RC.oracle_kwargs(kw)
+    gx = X.ORBextractor(a["nfeatures"], a["scale_factor"], a["nlevels"], a["ini_th"], a["min_th"])
+    k, d = gx(np.ascontiguousarray(img))
+    rk = g[name + "/kps"]
+    assert len(k) == len(rk) > 0
+    for i, f in enumerate(("x", "y", "size", "angle", "response")):
+        assert np.array_equal(k[f], rk[:, i]), f
+    assert np.array_equal(k["octave"], rk[:, 5].astype(np.int32))
+    assert np.array_equal(d, g[name + "/desc"])
