@@ -459,21 +459,31 @@ def tracking_leg(X, k1, d1, k2, d2, bounds, p50, cpu):
 
 
 def run_reference(args, emit=print):
-    """--impl reference: the reference's CPU ORBextractor path, restated in oracle/ (kind "port"), on all host threads."""
+    """--impl reference: the reference's CPU ORBextractor path on all host threads.  kind "reference" = the reference's own
+    src/ORBextractor.cc object code (oracle/_ref/libref_extractor.so, built by __graft_entry__.build() where /root/reference
+    exists and carried to the GPU box; its OpenCV pixel primitives are scalar C++ models, OpenCV itself is not on the image);
+    kind "port" = the oracle's restatement, when that library is absent."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     wl = WORKLOADS[args.workload]
     threads = args.cpu_threads or host_threads()
     per_step = max(64, 16 * threads) if threads > 1 else 24  # bounded sample of the workload per step
-    from oracle import oracle_lib as O
+    from oracle.ref_extractor import ref_extractor as RX
+    if os.path.exists(RX.SO) and not os.environ.get("ORBX_BENCH_CPU_PORT"):
+        kind, bench_extract = "reference", RX.bench_extract
+        what = "reference src/ORBextractor.cc object code (CPU branch; OpenCV primitives = scalar C++ models)"
+    else:
+        from oracle import oracle_lib as O
+        kind, bench_extract = "port", O.bench_extract
+        what = "oracle restatement"
     frames = make_frames(args.workload, per_step, first=1000)
     a = (wl["nfeatures"], SCALE, LEVELS, INI_TH, MIN_TH, threads)
     for _ in range(max(args.warmup, 1)):
-        O.bench_extract(frames[:threads], *a)
+        bench_extract(frames[:threads], *a)
     t = 0.0
     for _ in range(args.steps):
-        secs, _ = O.bench_extract(frames, *a)
+        secs, _ = bench_extract(frames, *a)
         t += secs
     value = per_step * args.steps / t
     h, w = wl["shape"]
@@ -483,8 +493,8 @@ def run_reference(args, emit=print):
         "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
         "config": config_for(args),
-        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": "port",
-                         "sample": f"{per_step} frames per step x {args.steps} steps, frame-parallel over {threads} threads"},
+        "cpu_baseline": {"value": value, "unit": "frames/s", "cores": threads, "kind": kind,
+                         "sample": f"{per_step} frames per step x {args.steps} steps, frame-parallel over {threads} threads; {what}"},
         "e2e": {"value": value, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }

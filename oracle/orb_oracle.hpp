@@ -10,11 +10,14 @@
 //     src/Frame.cc are compiled where they lie (oracle/ref_matcher/Makefile -> oracle/_ref/libref_matcher.so) and every matcher
 //     below equals them on 25 seeded cases, live and through tests/golden/ref_matcher.npz (tests/test_oracle_ref_matcher.py).
 //     The DBoW2 descent is pinned the same way against the reference's Thirdparty/DBoW2 (oracle/ref_dbow2).
-//   * Extractor (ORBextractor.cc): its source does not compile here (VisionWorks / OpenVX / OpenCV C++ headers absent), so the
-//     control flow follows the reference line ranges cited at each function, the five OpenCV primitives it calls (resize,
-//     copyMakeBorder, FAST, GaussianBlur, fastAtan2) are pinned bit-exactly against cv2 4.13 (tests/test_oracle_cv2.py and the
-//     fixtures under tests/golden/), and the 1024 pattern integers against the reference text and cv2.ORB.  PARITY UNPINNED
-//     against a reference BINARY for this part.
+//   * Extractor (ORBextractor.cc): CONTROL FLOW PINNED TO REFERENCE OBJECT CODE.  /root/reference's own src/ORBextractor.cc is
+//     compiled where it lies (oracle/ref_extractor/Makefile -> oracle/_ref/libref_extractor.so; OPENVX undefined = its CPU
+//     branch, a do-nothing OpenVX stand-in, a monotonic heap for quadtree nodes so its pointer tie-breaks are defined) and
+//     Extractor::extract below equals it bit for bit on 18 whole frames + quadtree tie cases, live and through
+//     tests/golden/ref_extractor.npz (tests/test_oracle_ref_extractor.py).  The five OpenCV pixel primitives it calls (resize,
+//     copyMakeBorder, FAST, GaussianBlur, fastAtan2) are not under /root/reference: they are pinned bit-exactly against cv2
+//     4.13 (tests/test_oracle_cv2.py and the fixtures under tests/golden/), the 1024 pattern integers against the reference
+//     text, the compiled reference and cv2.ORB.
 #pragma once
 #include <cstddef>
 #include <cstdint>

@@ -15,9 +15,13 @@
 // blocks of exactly one std::list<ExtractorNode> node come from a bump arena that never reuses memory, everything else from
 // malloc.  Node addresses then increase with creation time, so "higher address first" (the reference walks the sorted vector
 // from the back) reads "the node created last goes first" — the rule the oracle and the CUDA quadtree implement.
+#include <pthread.h>
+#include <atomic>
+#include <chrono>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <iostream>
 #include <cstring>
 #include <list>
 #include <new>
@@ -26,14 +30,49 @@
 
 namespace {
 const size_t kNodeBytes = sizeof(std::_List_node<ORB_SLAM2::ExtractorNode>);
-const size_t kArenaBytes = (size_t)256 << 20;
-char* g_arena = nullptr;
-size_t g_arenaUsed = 0;
-inline bool in_arena(const void* p) { return g_arena && (const char*)p >= g_arena && (const char*)p < g_arena + kArenaBytes; }
+const size_t kArenaBytes = (size_t)64 << 20;  // one frame creates a few 10^4 nodes of ~100 B
+thread_local char* g_arena = nullptr;         // per thread: the timed CPU arm runs one extractor per host thread
+thread_local size_t g_arenaUsed = 0;
+// every arena ever handed out (a block may be freed on another thread than the one that took it); arenas live until exit
+char* g_arenas[1024];
+std::atomic<int> g_nArenas{0};
+inline bool in_arena(const void* p) {
+    const int n = g_nArenas.load(std::memory_order_acquire);
+    for (int i = 0; i < n; ++i)
+        if ((const char*)p >= g_arenas[i] && (const char*)p < g_arenas[i] + kArenaBytes) return true;
+    return false;
+}
+char* g_idle[1024];  // arenas given back by finished bench threads
+int g_nIdle = 0;
+char* new_arena() {
+    if (g_nIdle > 0) return g_idle[--g_nIdle];
+    char* a = (char*)malloc(kArenaBytes);
+    const int i = g_nArenas.load(std::memory_order_relaxed);
+    if (!a || i >= 1024) {
+        fprintf(stderr, "ref_extractor: no memory for a node arena\n");
+        abort();
+    }
+    g_arenas[i] = a;  // callers serialise through g_arenaLock
+    g_nArenas.store(i + 1, std::memory_order_release);
+    return a;
+}
+pthread_mutex_t g_arenaLock = PTHREAD_MUTEX_INITIALIZER;
+void arena_give_back() {  // at the end of a worker thread
+    if (!g_arena) return;
+    pthread_mutex_lock(&g_arenaLock);
+    g_idle[g_nIdle++] = g_arena;
+    pthread_mutex_unlock(&g_arenaLock);
+    g_arena = nullptr;
+    g_arenaUsed = 0;
+}
 void arena_reset() { g_arenaUsed = 0; }  // called between frames: every list of the previous call is gone by then
 void* refx_alloc(size_t n) {
     if (n == kNodeBytes) {
-        if (!g_arena) g_arena = (char*)malloc(kArenaBytes);
+        if (!g_arena) {
+            pthread_mutex_lock(&g_arenaLock);
+            g_arena = new_arena();
+            pthread_mutex_unlock(&g_arenaLock);
+        }
         const size_t need = (n + 15) & ~(size_t)15;
         if (g_arena && g_arenaUsed + need <= kArenaBytes) {
             void* p = g_arena + g_arenaUsed;
@@ -78,12 +117,78 @@ struct Probe : public ORB_SLAM2::ORBextractor {
 };
 }  // namespace
 
+namespace {
+// the reference's constructor prints "w,h" and its destructor "Avg computed frame ORB: ..." on std::cout; bench.py's contract
+// is ONE line on stdout, so both run with cout parked
+struct QuietCout {
+    std::streambuf* old;
+    QuietCout() : old(std::cout.rdbuf(nullptr)) {}
+    ~QuietCout() {
+        std::cout.rdbuf(old);
+        std::cout.clear();
+    }
+};
+struct BenchArg {
+    const uint8_t* frames;
+    int nframes, w, h, t, threads;
+    long long count;
+    Probe* probe;
+};
+void* bench_thread(void* v) {
+    BenchArg* a = (BenchArg*)v;
+    std::vector<cv::KeyPoint> k;
+    for (int f = a->t; f < a->nframes; f += a->threads) {
+        arena_reset();
+        cv::Mat image(a->h, a->w, CV_8UC1, (void*)(a->frames + (size_t)f * a->w * a->h), (size_t)a->w), mask, d;
+        (*a->probe)(image, mask, k, d);
+        a->probe->quiet();
+        a->count += (long long)k.size();
+    }
+    arena_give_back();
+    return nullptr;
+}
+}  // namespace
+
 extern "C" {
 
 void* refx_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh, int width, int height) {
+    QuietCout q;
     return new Probe(nfeatures, scaleFactor, nlevels, iniTh, minTh, width, height);
 }
-void refx_destroy(void* h) { delete (Probe*)h; }
+void refx_destroy(void* h) {
+    QuietCout q;
+    delete (Probe*)h;
+}
+
+// The timed CPU arm of bench.py (--impl reference, cpu_baseline kind "reference"): `threads` host threads, one reference
+// ORBextractor each (the reference's extractor is single-threaded; src/Frame.cc:77-80 runs one per eye), frame f on thread
+// f mod threads.  Extractors are built before the clock starts.  Returns wall seconds; total keypoints in *nk.
+double refx_bench_extract(const uint8_t* frames, int nframes, int w, int h, int nf, float sf, int nl, int ini, int mn, int threads,
+                          long long* nk) {
+    std::vector<BenchArg> args((size_t)threads);
+    std::vector<pthread_t> tid((size_t)threads);
+    {
+        QuietCout q;
+        for (int t = 0; t < threads; ++t) {
+            args[t] = BenchArg{frames, nframes, w, h, t, threads, 0, nullptr};
+            args[t].probe = new Probe(nf, sf, nl, ini, mn, w, h);
+        }
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    for (int t = 0; t < threads; ++t) pthread_create(&tid[t], nullptr, bench_thread, &args[t]);
+    for (int t = 0; t < threads; ++t) pthread_join(tid[t], nullptr);
+    auto t1 = std::chrono::steady_clock::now();
+    long long s = 0;
+    {
+        QuietCout q;
+        for (int t = 0; t < threads; ++t) {
+            s += args[t].count;
+            delete args[t].probe;
+        }
+    }
+    if (nk) *nk = s;
+    return std::chrono::duration<double>(t1 - t0).count();
+}
 
 // tables the constructor builds: features per level, scale factors, umax, the 512 pattern points (x, y interleaved)
 void refx_tables(void* h, int* perLevel, float* scale, int* umax16, int* pattern1024) {

@@ -91,3 +91,15 @@ class RefExtractor:
         n = lib().refx_distribute(self._h, _p(xyr), len(keys), minX, maxX, minY, maxY, N, level, _p(out), len(out))
         assert n >= 0
         return out[:n].copy()
+
+
+def bench_extract(frames, nfeatures, scale_factor, nlevels, ini_th, min_th, threads):
+    """bench.py's CPU arm: wall seconds for `frames` (n, h, w) on `threads` host threads, one reference extractor per thread."""
+    frames = np.ascontiguousarray(frames, dtype=np.uint8)
+    n, h, w = frames.shape
+    nk = C.c_longlong(0)
+    f = lib().refx_bench_extract
+    f.restype = C.c_double
+    f.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_longlong)]
+    secs = f(_p(frames), n, w, h, nfeatures, C.c_float(scale_factor), nlevels, ini_th, min_th, threads, C.byref(nk))
+    return secs, nk.value
