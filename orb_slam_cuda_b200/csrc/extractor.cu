@@ -235,6 +235,7 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
     g.nlevels = nl;
     g.iniTh = ex->prm.ini_th_fast;
     g.minTh = ex->prm.min_th_fast;
+    long long keyBase = 0;
     int cellBase = 0, slotBase = 0, tileBase = 0, maxStripW = 0, maxHCell = 0;
     std::vector<FastStrip> strips;
     long long qtBase = 0;
@@ -278,10 +279,13 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
         }
         L.cellBase = cellBase;
         cellBase += L.nCols * L.nRows;
+        L.cellCap = cell_capacity(L.wCell, L.hCell);
+        L.keyBase = keyBase;
+        keyBase += (long long)L.nCols * L.nRows * L.cellCap;
         L.quota = ex->quota[l];
         L.slotBase = slotBase;
         slotBase += L.quota + 4;
-        L.candCap = std::max(32, std::min(L.nCols * L.nRows * CELL_CAP, 1 << 20));
+        L.candCap = (int)std::max<long long>(32, std::min<long long>((long long)L.nCols * L.nRows * L.cellCap, 1 << 20));
         L.qtBase = qtBase;
         qtBase += 2LL * L.candCap;
         L.scale = ex->scale[l];
@@ -302,6 +306,7 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
         L.kpBase = L.slotBase;
     }
     g.nCellsTotal = std::max(cellBase, 1);
+    g.keysPerFrame = std::max<long long>(keyBase, 1);
     g.slotsTotal = slotBase;
     g.qtFrameStride = qtBase;
     g.blurTilesTotal = tileBase;
@@ -396,7 +401,7 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
     if ((rc = ex->strips.ensure(std::max<size_t>(strips.size(), 1) * sizeof(FastStrip)))) return rc;
     ORBX_CUDA(cudaMemcpy(ex->strips.p, strips.data(), strips.size() * sizeof(FastStrip), cudaMemcpyHostToDevice));
     if ((rc = ex->cellCnt.ensure((size_t)batch * g.nCellsTotal * 4))) return rc;
-    if ((rc = ex->cellKeys.ensure((size_t)batch * g.nCellsTotal * CELL_CAP * 4))) return rc;
+    if ((rc = ex->cellKeys.ensure((size_t)batch * (size_t)g.keysPerFrame * 4))) return rc;
     if ((rc = ex->qtScratch.ensure((size_t)batch * g.qtFrameStride * 4))) return rc;
     if ((rc = ex->lvlCnt.ensure((size_t)batch * nl * 4))) return rc;
     if ((rc = ex->lvlKeys.ensure((size_t)batch * g.slotsTotal * 4))) return rc;
@@ -439,7 +444,7 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     g.patternVariant = ex->patternVariant;
     const int nl = g.nlevels;
     int* cellCnt = ex->cellCnt.as<int>() + (size_t)f0 * g.nCellsTotal;
-    uint32_t* cellKeys = ex->cellKeys.as<uint32_t>() + (size_t)f0 * g.nCellsTotal * CELL_CAP;
+    uint32_t* cellKeys = ex->cellKeys.as<uint32_t>() + (size_t)f0 * (size_t)g.keysPerFrame;
     uint32_t* qtScratch = ex->qtScratch.as<uint32_t>() + (size_t)f0 * g.qtFrameStride;
     int* lvlCnt = ex->lvlCnt.as<int>() + (size_t)f0 * nl;
     uint32_t* lvlKeys = ex->lvlKeys.as<uint32_t>() + (size_t)f0 * g.slotsTotal;
@@ -736,8 +741,7 @@ static bool is_pinned(const void* p) {
 }
 
 static int overflow_error(int cap) {
-    set_error("orbx_extract: a device buffer overflowed (more than %d keypoints in a FAST cell, or more than cap=%d keypoints in a frame)",
-              CELL_CAP, cap);
+    set_error("orbx_extract: a device buffer overflowed (more than cap=%d keypoints in a frame, or more than 2^20 FAST corners in one level)", cap);
     return ORBX_E_OVERFLOW;
 }
 
@@ -908,11 +912,7 @@ static int extract_batch_impl(orbx_extractor* ex, const uint8_t* frames, int bat
             counts[0] = hc[0];
             memcpy(kps, hk, (size_t)hc[0] * sizeof(orbx_keypoint));
             memcpy(desc, hd, (size_t)hc[0] * 32);
-            if (*hst != 0) {
-                set_error("orbx_extract: a device buffer overflowed (more than %d keypoints in a FAST cell, or more than cap=%d keypoints in a frame)",
-                          CELL_CAP, cap);
-                return ORBX_E_OVERFLOW;
-            }
+            if (*hst != 0) return overflow_error(cap);
             return ORBX_OK;
         }
     }
@@ -1068,19 +1068,19 @@ int orbx_debug_candidates(orbx_extractor* ex, int frame, int level, orbx_keypoin
     const LevelGeom& L = g.lv[level];
     const int nCells = L.nCols * L.nRows;
     std::vector<int> cnt(std::max(nCells, 1));
-    std::vector<uint32_t> keys((size_t)std::max(nCells, 1) * CELL_CAP);
+    std::vector<uint32_t> keys((size_t)std::max(nCells, 1) * L.cellCap);
     ORBX_CUDA(cudaStreamSynchronize(ex->stream));
     if (nCells > 0) {
         ORBX_CUDA(cudaMemcpy(cnt.data(), ex->cellCnt.as<int>() + (size_t)frame * g.nCellsTotal + L.cellBase, (size_t)nCells * 4,
                              cudaMemcpyDeviceToHost));
-        ORBX_CUDA(cudaMemcpy(keys.data(), ex->cellKeys.as<uint32_t>() + ((size_t)frame * g.nCellsTotal + L.cellBase) * CELL_CAP,
-                             (size_t)nCells * CELL_CAP * 4, cudaMemcpyDeviceToHost));
+        ORBX_CUDA(cudaMemcpy(keys.data(), ex->cellKeys.as<uint32_t>() + (size_t)frame * (size_t)g.keysPerFrame + (size_t)L.keyBase,
+                             (size_t)nCells * L.cellCap * 4, cudaMemcpyDeviceToHost));
     }
     int m = 0;
     for (int c = 0; c < nCells; ++c)
-        for (int k = 0; k < std::min(cnt[c], CELL_CAP); ++k, ++m)
+        for (int k = 0; k < std::min(cnt[c], L.cellCap); ++k, ++m)
             if (out && m < cap) {
-                const uint32_t key = keys[(size_t)c * CELL_CAP + k];
+                const uint32_t key = keys[(size_t)c * L.cellCap + k];
                 out[m] = orbx_keypoint{(float)key_x(key), (float)key_y(key), 7.f, -1.f, (float)key_resp(key), 0, -1};
             }
     *n = m;

@@ -467,7 +467,8 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
         const int n2all = cnt[2];
         {
             int* outCnt = cellCnt + (long long)f * g.nCellsTotal + cellGlobal0;
-            uint32_t* outKeys = cellKeys + ((long long)f * g.nCellsTotal + cellGlobal0) * CELL_CAP;
+            const int cellCap = L.cellCap;
+            uint32_t* outKeys = cellKeys + (long long)f * g.keysPerFrame + L.keyBase + (long long)(ci * L.nCols + cj0) * cellCap;
             for (int cj = warp; cj < nc; cj += FS_THREADS / 32) {
                 const int cx0 = X0 + min(cj * wCell, dW), cx1 = X0 + min(cj * wCell + wCell, dW);  // tile columns of the cell
                 int run = 0;
@@ -499,21 +500,21 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
                         while (lo) {
                             const int i = __ffs(lo) - 1;
                             lo &= lo - 1;
-                            if (rank < CELL_CAP) outKeys[cj * CELL_CAP + rank] = keyRow + (uint32_t)i + ((uint32_t)srow[i] << 24);
+                            if (rank < cellCap) outKeys[cj * cellCap + rank] = keyRow + (uint32_t)i + ((uint32_t)srow[i] << 24);
                             ++rank;
                         }
                         while (hi) {
                             const int i = __ffs(hi) + 31;
                             hi &= hi - 1;
-                            if (rank < CELL_CAP) outKeys[cj * CELL_CAP + rank] = keyRow + (uint32_t)i + ((uint32_t)srow[i] << 24);
+                            if (rank < cellCap) outKeys[cj * cellCap + rank] = keyRow + (uint32_t)i + ((uint32_t)srow[i] << 24);
                             ++rank;
                         }
                     }
                 }
                 if (lane == 0) {
-                    if (run > CELL_CAP) {
+                    if (run > cellCap) {  // cannot happen: cellCap is the NMS packing bound of the cell (cell_capacity)
                         atomicExch(dStatus, ORBX_E_OVERFLOW);
-                        run = CELL_CAP;
+                        run = cellCap;
                     }
                     outCnt[cj] = run;
                 }

@@ -381,7 +381,8 @@ __global__ void __launch_bounds__(QT_THREADS) k_quadtree(const __grid_constant__
     const LevelGeom& L = g.lv[level];
     const int nCells = L.nCols * L.nRows;
     const int* cnt = cellCnt + (long long)f * g.nCellsTotal + L.cellBase;
-    const uint32_t* keys = cellKeys + ((long long)f * g.nCellsTotal + L.cellBase) * CELL_CAP;
+    const uint32_t* keys = cellKeys + (long long)f * g.keysPerFrame + L.keyBase;
+    const int cellCap = L.cellCap;
     uint32_t* bufs = qtScratch + (long long)f * g.qtFrameStride + L.qtBase;
     // gather the per-cell slots into one list in cell order = vToDistributeKeys order (:1256-1299)
     for (int i = tid; i < nCells; i += blockDim.x) S.cellOff[i] = cnt[i];
@@ -392,9 +393,9 @@ __global__ void __launch_bounds__(QT_THREADS) k_quadtree(const __grid_constant__
         K = L.candCap;
     }
     for (int c = tid >> 5; c < nCells; c += blockDim.x >> 5) {  // a warp copies one cell's slot
-        const int nc = min(cnt[c], CELL_CAP), o = S.cellOff[c];
+        const int nc = min(cnt[c], cellCap), o = S.cellOff[c];
         for (int k = tid & 31; k < nc; k += 32)
-            if (o + k < K) bufs[o + k] = keys[(long long)c * CELL_CAP + k];
+            if (o + k < K) bufs[o + k] = keys[(long long)c * cellCap + k];
     }
     __syncthreads();
     uint32_t* out = lvlKeys + (long long)f * g.slotsTotal + L.slotBase;

@@ -8,7 +8,7 @@
 //   blur[l]    : uint8  [B][h_l][bpitch_l]        7x7 sigma-2 blurred level, interior only (descriptor taps stay
 //                                               >= 1 px inside, see k_describe.cu).
 //   cellCnt    : int32  [B][nCellsTotal]          FAST keypoints per 30-px cell (all levels concatenated)
-//   cellKeys   : uint32 [B][nCellsTotal][CELL_CAP] packed (resp << 24 | y << 12 | x), x,y relative to minBorder,
+//   cellKeys   : uint32 [B][level][cell][cellCap_l] packed (resp << 24 | y << 12 | x), x,y relative to minBorder,
 //                                               row-major inside the cell (cv::FAST output order)
 //   lvlCnt     : int32  [B][nlevels]              keypoints kept by the quadtree
 //   lvlKeys    : uint32 [B][slotsTotal]           packed kept keypoints, level l at slotBase[l], quota_l + 4 slots
@@ -27,7 +27,11 @@ constexpr int XOFF = 32;         // byte column of interior x = 0 inside a plane
 constexpr int PADL = XOFF - EDGE;  // byte column of padded x = 0  (13)
 constexpr int HALF_PATCH = 15;
 constexpr int PATCH = 31;
-constexpr int CELL_CAP = 128;    // FAST keypoints per cell (overflow -> ORBX_E_OVERFLOW)
+// Key slots per FAST cell.  cv::FAST's non-maximum suppression keeps a corner only if its score is strictly greater than
+// those of its 8 neighbours, so no two kept corners touch: a cell that evaluates w x h positions keeps at most
+// ceil(w / 2) * ceil(h / 2).  Sizing the slot by that bound means a cell can never overflow, whatever the image (white
+// noise included).  Rounded up to a multiple of 32.
+inline int cell_capacity(int wCell, int hCell) { return (((wCell + 1) / 2) * ((hCell + 1) / 2) + 31) / 32 * 32; }
 constexpr int FAST_MAX_STRIP_CELLS = 8;  // cells one FAST CTA handles (a strip of one cell row)
 #ifndef ORBX_BLUR_TH
 #define ORBX_BLUR_TH 32  // output rows of a blur tile (the TMA box is 160 x (ORBX_BLUR_TH + 6))
@@ -53,6 +57,8 @@ struct LevelGeom {
     // FAST grid (src/ORBextractor.cc:1133-1147)
     int minBX, minBY, maxBX, maxBY, nCols, nRows, wCell, hCell;
     int cellBase;           // first cell of this level in the per-frame cell arrays
+    int cellCap;            // key slots per cell of this level = the most corners FAST + 3x3 NMS can leave in a cell (cell_capacity)
+    long long keyBase;      // first key slot (uint32) of this level inside one frame's cellKeys
     int quota;              // mnFeaturesPerLevel[l]
     int slotBase;           // first slot of this level in lvlKeys
     int candCap;            // capacity of one quadtree key buffer
@@ -71,6 +77,7 @@ struct LevelGeom {
 struct FrameGeom {
     int nlevels;
     int nCellsTotal;
+    long long keysPerFrame;   // uint32 per frame in cellKeys (sum over levels of cells x cellCap)
     int slotsTotal;
     long long qtFrameStride;  // uint32 per frame in qtScratch
     int fastBoxW, fastBoxH;   // TMA box of the FAST kernel

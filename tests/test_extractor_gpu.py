@@ -285,7 +285,7 @@ def test_repeated_single_frames_graph_replay():
 @pytest.mark.parametrize("amp", [255, 120])
 def test_dense_noise_image(amp):
     """White noise: most pixels pass the FAST quick test, so the optimistic single-chunk survivor list of a strip
-    overflows and the pass is redone in row chunks; cells hold close to CELL_CAP keypoints."""
+    overflows and the pass is redone in row chunks; cells hold far more corners than a natural image gives."""
     rng = np.random.default_rng(5)
     img = (128 + (rng.random((240, 320)) - 0.5) * amp).astype(np.uint8)
     gx, ox = X.ORBextractor(500, 1.2, 8, 20, 7), O.Extractor(500, 1.2, 8, 20, 7)
@@ -296,6 +296,29 @@ def test_dense_noise_image(amp):
         assert kp_tuple(a) == kp_tuple(b), f"level {l}: {len(a)} vs {len(b)} candidates"
     assert len(k) == len(ok)
     assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od)
+
+
+def test_full_range_noise_cannot_overflow_a_cell():
+    """uniform 0..255 noise: up to ~200 corners survive NMS in a 31 x 32 cell (the r02 build had 128 slots per cell and
+    returned ORBX_E_OVERFLOW here); slots are now sized by the NMS packing bound ceil(w/2) * ceil(h/2) of the cell"""
+    rng = np.random.default_rng(15)
+    for shape, nf in (((300, 420), 1500), ((376, 1241), 2000), ((120, 150), 300)):
+        img = rng.integers(0, 256, shape, dtype=np.uint8)
+        gx, ox = X.ORBextractor(nf, 1.2, 8, 20, 7), O.Extractor(nf, 1.2, 8, 20, 7)
+        k, d = gx(img)
+        ok, od = ox.extract(img)
+        for l in range(8):
+            a, b = gx.debug_candidates(l), ox.level_candidates(l)
+            assert kp_tuple(a) == kp_tuple(b), f"level {l}: {len(a)} vs {len(b)} candidates"
+        assert len(k) == len(ok)
+        assert np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od)
+    # bright pixels on every second row and column: a periodic pattern whose corners appear in the resized levels only
+    img = np.zeros((200, 260), np.uint8)
+    img[::2, ::2] = 255
+    gx, ox = X.ORBextractor(1000, 1.2, 8, 20, 7), O.Extractor(1000, 1.2, 8, 20, 7)
+    k, d = gx(img)
+    ok, od = ox.extract(img)
+    assert len(k) == len(ok) and np.array_equal(k.view(np.uint8), ok.view(np.uint8)) and np.array_equal(d, od)
 
 
 def test_quadtree_standalone_random():
