@@ -28,7 +28,7 @@ extern "C" {
 #define ORBX_E_INVALID (-1)  /* bad argument / unsupported geometry */
 #define ORBX_E_CUDA (-2)     /* CUDA runtime or driver failure (includes "no device") */
 #define ORBX_E_OOM (-3)      /* allocation failure */
-#define ORBX_E_OVERFLOW (-4) /* a fixed-capacity device buffer overflowed (cell slots / candidate lists / output cap) */
+#define ORBX_E_OVERFLOW (-4) /* the caller's output capacity (cap) was exceeded, or one level held more than 2^20 FAST corners; a FAST cell cannot overflow (slots sized by the NMS packing bound) */
 
 #define ORBX_MAX_LEVELS 16
 
@@ -149,6 +149,19 @@ int orbx_match_bruteforce(const uint8_t* q, int nq, const uint8_t* d, int nd, in
                           int* d2, int* match);
 int orbx_match_bruteforce_device(const uint8_t* d_q, int nq, const uint8_t* d_d, int nd, int th, float ratio,
                                  int* d_idx, int* d_d1, int* d_d2, int* d_match, void* stream);
+
+/* The same matcher for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same kernel, same
+ * results as orbx_match_bruteforce_device, but its scratch (per-slice partials + arrival counters) is a file-scope
+ * __device__ array inside liborbx.so (4 MiB + 32 KiB per GPU, held from library load until process exit), so the call
+ * performs no cudaMalloc / cudaFree and creates no stream, event or workspace.  Limits: nq <= ORBX_NOALLOC_MAX_QUERIES,
+ * otherwise ORBX_E_INVALID with a message naming the limit (nd as above).  All calls on one device share the scratch:
+ * calls that overlap on the GPU (different streams or threads) RACE on it — serialise them.  The first call on each device
+ * resolves the array's device address (cudaGetSymbolAddress, once); stream NULL = the default stream.  Device buffers,
+ * asynchronous on `stream`. */
+#define ORBX_NOALLOC_MAX_QUERIES 8192
+int orbx_match_bruteforce_noalloc(const uint8_t* d_q, int nq, const uint8_t* d_d, int nd, int th, float ratio,
+                                  int* d_idx, int* d_d1, int* d_d2, int* d_match, void* stream);
 
 /* All-vs-all keyframe matching (relocalisation / loop-candidate workload; N x N DescriptorDistance tables as in
  * src/MapPoint.cc:280-305 generalised to keyframe pairs).  Query keyframes [kq] and database keyframes [kd] hold

@@ -443,12 +443,20 @@ class ORBmatcher:
         _check(lib().orbx_match_bruteforce_device(_p(d_q), nq, _p(d_d), nd, int(th), C.c_float(self.mfNNratio), _p(d_idx),
                                                   _p(d_d1), _p(d_d2), _p(d_match), _p(stream) if stream else None))
 
+    def match_bruteforce_noalloc(self, d_q: int, nq: int, d_d: int, nd: int, d_idx: int, d_d1: int, d_d2: int, d_match: int,
+                                 th: int = TH_LOW, stream: int = 0):
+        """orbx_match_bruteforce_noalloc: match_bruteforce_device with its scratch in a static device array of liborbx.so —
+        allocates nothing; nq <= NOALLOC_MAX_QUERIES; calls that overlap on the GPU race on the shared scratch."""
+        _check(lib().orbx_match_bruteforce_noalloc(_p(d_q), nq, _p(d_d), nd, int(th), C.c_float(self.mfNNratio), _p(d_idx),
+                                                   _p(d_d1), _p(d_d2), _p(d_match), _p(stream) if stream else None))
+
     def match_allpairs_device(self, d_q: int, kq: int, d_db: int, kd: int, n: int, d_score: int, th: int = TH_LOW, stream: int = 0):
         """score[i, j] = accepted matches of query keyframe i in database keyframe j (device buffers, asynchronous)."""
         _check(lib().orbx_match_allpairs_device(_p(d_q), kq, _p(d_db), kd, n, int(th), C.c_float(self.mfNNratio), _p(d_score),
                                                 _p(stream) if stream else None))
 
 
+NOALLOC_MAX_QUERIES = 8192  # ORBX_NOALLOC_MAX_QUERIES of include/orbx.h
 GRAY_BGR, GRAY_CV2_COEFFS = 1, 2
 
 

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "liborbx.so")
 SOURCES = ["extractor.cu", "k_pyramid.cu", "k_fast.cu", "k_quadtree.cu", "k_blur.cu", "k_describe.cu", "k_match.cu",
-           "k_search.cu", "k_bow.cu", "k_color.cu", "k_undistort.cu", "k_stereo.cu", "matcher.cu", "vocabulary.cu"]
+           "k_search.cu", "k_bow.cu", "k_color.cu", "k_undistort.cu", "k_stereo.cu", "matcher.cu", "vocabulary.cu", "noalloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "--fmad=false",
               "-Xcompiler", "-fPIC,-O2,-Wall,-ffp-contract=off", "-Xptxas", "-v", "-cudart", "static"]
 
