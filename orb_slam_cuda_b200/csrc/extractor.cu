@@ -48,6 +48,9 @@ static inline long long round_up(long long v, long long a) { return (v + a - 1) 
 
 using namespace orbx;
 
+#ifndef ORBX_BLUR_OVERLAP_DEFAULT
+#define ORBX_BLUR_OVERLAP_DEFAULT 0  // 1: GaussianBlur on a side stream beside FAST + quadtree; ORBX_BLUR_OVERLAP overrides
+#endif
 #ifndef ORBX_DESC_SUB_DEFAULT
 #define ORBX_DESC_SUB_DEFAULT 0  // frames per blur + describe sub-batch (0 = whole batch); ORBX_DESC_SUB overrides
 #endif
@@ -102,6 +105,14 @@ struct orbx_extractor {
     cudaEvent_t ev[ORBX_NUM_STAGES + 1] = {};
     std::vector<cudaEvent_t> subEv;  // timing of the blur / describe sub-batches: (blur done, describe done) per sub-batch
     int nSub = 0;
+    // GaussianBlur needs the pyramid only, so it runs on a side stream beside FAST + quadtree and joins before the descriptors
+    struct Side {
+        cudaStream_t main = nullptr, side = nullptr;
+        cudaEvent_t fork = nullptr, join = nullptr, t0 = nullptr, t1 = nullptr;
+    };
+    std::vector<Side> sides;  // one per stream the pipeline has been launched on
+    bool overlapped = false;  // the last timed call ran the blur on a side stream (stage_ms reads t0 / t1)
+    int timedSide = -1;
     int lastBatch = 0;
     int lastScratchBase = 0; // scratch frame holding frame `lastFrameBase` of the caller's batch
     int lastFrameBase = 0;   // index (within the caller's batch) of frame 0 of the scratch: > 0 after a chunked host batch
@@ -467,6 +478,36 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     }
     if ((rc = stage_sync("Pyramid/Resize", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
+    static const int subPref = []() { const char* e = getenv("ORBX_DESC_SUB"); return e ? atoi(e) : ORBX_DESC_SUB_DEFAULT; }();
+    static const bool overlapPref = []() { const char* e = getenv("ORBX_BLUR_OVERLAP"); return e ? atoi(e) != 0 : ORBX_BLUR_OVERLAP_DEFAULT != 0; }();
+    const bool overlap = overlapPref && !(subPref > 0 && batch > subPref) && !getenv("ORBX_SYNC_STAGES");
+    int sideIdx = -1;
+    if (overlap) {
+        for (size_t i = 0; i < ex->sides.size(); ++i)
+            if (ex->sides[i].main == s) sideIdx = (int)i;
+        if (sideIdx < 0) {
+            orbx_extractor::Side sd;
+            sd.main = s;
+            ORBX_CUDA(cudaStreamCreateWithFlags(&sd.side, cudaStreamNonBlocking));
+            ORBX_CUDA(cudaEventCreateWithFlags(&sd.fork, cudaEventDisableTiming));
+            ORBX_CUDA(cudaEventCreateWithFlags(&sd.join, cudaEventDisableTiming));
+            ORBX_CUDA(cudaEventCreate(&sd.t0));
+            ORBX_CUDA(cudaEventCreate(&sd.t1));
+            ex->sides.push_back(sd);
+            sideIdx = (int)ex->sides.size() - 1;
+        }
+        const orbx_extractor::Side& sd = ex->sides[sideIdx];
+        ORBX_CUDA(cudaEventRecord(sd.fork, s));
+        ORBX_CUDA(cudaStreamWaitEvent(sd.side, sd.fork, 0));
+        if (tm) ORBX_CUDA(cudaEventRecord(sd.t0, sd.side));
+        if ((rc = launch_blur(g, ex->blurMaps, batch, sd.side))) return rc;                                  // GaussianBlur
+        if (tm) ORBX_CUDA(cudaEventRecord(sd.t1, sd.side));
+        ORBX_CUDA(cudaEventRecord(sd.join, sd.side));
+    }
+    if (tm) {
+        ex->overlapped = overlap;
+        ex->timedSide = sideIdx;
+    }
     if ((rc = launch_fast(g, ex->fastMaps, ex->strips.as<FastStrip>(), batch, cellCnt, cellKeys, dStatus, s))) return rc;
     if ((rc = stage_sync("FAST+Grid", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[2], s));
@@ -476,15 +517,18 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     // GaussianBlur + descriptors run over SUB-BATCHES: the blurred levels of `sub` frames (1.47 MB per KITTI frame) are
     // still in the 126 MB L2 when the descriptor kernel gathers its 37 x 37 patches from them, instead of coming back from
     // HBM as they do when all frames are blurred first (ncu: 1.5 GB of DRAM reads for 62 MB of output on 512 frames).
-    static const int subPref = []() { const char* e = getenv("ORBX_DESC_SUB"); return e ? atoi(e) : ORBX_DESC_SUB_DEFAULT; }();
     const int sub = subPref > 0 && batch > subPref ? (batch + (batch + subPref - 1) / subPref - 1) / ((batch + subPref - 1) / subPref) : batch;
     ex->nSub = 0;
     for (int b0 = 0; b0 < batch; b0 += sub) {
         const int nb = std::min(sub, batch - b0);
         FrameGeom gs = g;
         gs.f0 = g.f0 + b0;
-        if ((rc = launch_blur(gs, ex->blurMaps, nb, s))) return rc;                                          // GaussianBlur
-        if ((rc = stage_sync("Gaussian Blur", s))) return rc;
+        if (overlap) {
+            ORBX_CUDA(cudaStreamWaitEvent(s, ex->sides[sideIdx].join, 0));
+        } else {
+            if ((rc = launch_blur(gs, ex->blurMaps, nb, s))) return rc;                                      // GaussianBlur
+            if ((rc = stage_sync("Gaussian Blur", s))) return rc;
+        }
         if (tm) {
             while ((int)ex->subEv.size() < 2 * (ex->nSub + 1)) {
                 cudaEvent_t e;
@@ -605,6 +649,10 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
     for (cudaEvent_t e : ex->ev)
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : ex->subEv) cudaEventDestroy(e);
+    for (auto& sd : ex->sides) {
+        cudaStreamDestroy(sd.side);
+        for (cudaEvent_t e : {sd.fork, sd.join, sd.t0, sd.t1}) cudaEventDestroy(e);
+    }
     for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
         ex->planes[l].release(); ex->blurs[l].release(); ex->xtab[l].release(); ex->ytab[l].release(); ex->rzTiles[l].release();
     }
@@ -651,6 +699,8 @@ int orbx_extractor_stage_ms(orbx_extractor* ex, float* ms) {
         ms[3] += a;
         ms[4] += b;
     }
+    if (ex->overlapped && ex->timedSide >= 0)  // the blur ran beside FAST + quadtree: its own span on the side stream
+        ORBX_CUDA(cudaEventElapsedTime(&ms[3], ex->sides[ex->timedSide].t0, ex->sides[ex->timedSide].t1));
     return ORBX_OK;
 }
 
