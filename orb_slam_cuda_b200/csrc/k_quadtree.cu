@@ -17,6 +17,9 @@
 //
 // Keys are 32-bit packed (resp << 24 | y << 12 | x); a node owns a contiguous segment of one of the two key
 // buffers, children own sub-segments of the other buffer, so no key is ever copied except when its node splits.
+#include <algorithm>
+#include <cstdlib>
+
 #include "orbx_internal.h"
 
 namespace orbx {
@@ -34,8 +37,15 @@ struct QtShared {  // carved out of dynamic shared memory
     int* sB;        // scan scratch (survivors)
     int* sC;        // processing order of the final phase
     int* cellOff;   // exclusive prefix of the per-cell counts
-    int* misc;      // [0..15] scalars, [16..31] warp sums, [32..32+MAX_ROOTS] root counters
+    int* misc;      // [0..15] scalars, [16..47] warp sums, [48..48+MAX_ROOTS] root counters
+    int* rootW;     // [warps][nIni] per-warp-chunk root counts, then running offsets (root partition)
+    uint4* bigCnt;  // [QT_MAXBIG][warps] child counts of the warp chunks of the nodes split by the whole block
+    int* bigList;   // [QT_MAXBIG] list positions of those nodes
 };
+
+constexpr int QT_THREADS_SMALL = 512;  // small batches (single-frame latency): the SMs are idle anyway, so a CTA gets 16 warps
+constexpr int QT_MAXBIG = 32;       // nodes per sweep that the whole block splits together
+constexpr uint32_t QT_BIG = 768;    // ... when they hold more keys than this (else: one warp per node)
 
 __device__ __forceinline__ int warp_incl_scan(int v, int lane) {
 #pragma unroll
@@ -48,7 +58,7 @@ __device__ __forceinline__ int warp_incl_scan(int v, int lane) {
 
 // In-place exclusive prefix sum of a[0..n) in shared memory by the whole block; returns the total.
 // Every thread owns a contiguous chunk, so the result is independent of the thread count.
-__device__ int block_exscan(int* a, int n, int* warpSums) {
+__device__ __forceinline__ int block_exscan(int* a, int n, int* warpSums) {
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
     const int chunk = (n + blockDim.x - 1) / blockDim.x;
     const int b = min(tid * chunk, n), e = min(b + chunk, n);
@@ -77,87 +87,172 @@ __device__ __forceinline__ int child_of(uint32_t key, int mx, int my) {
     return (key_x(key) < mx ? 0 : 1) + (key_y(key) < my ? 0 : 2);
 }
 
-// warp: count the keys of `nd` falling into each of the four children
-__device__ uint4 warp_count_children(const QNode& nd, const uint32_t* bufs, int candCap, int lane) {
-    const int mx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), my = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
-    const uint32_t* k = bufs + ((nd.begin >> 31) ? candCap : 0) + (nd.begin & 0x7FFFFFFFu);
+// warp: count the keys k[0..count) falling into each of the four children.  Four loads per lane are in flight per trip (the
+// keys live in global memory and a trip is otherwise one exposed L1 / L2 latency); long ranges count per lane and reduce once.
+__device__ __forceinline__ uint4 warp_count_range(const uint32_t* k, uint32_t count, int mx, int my, int lane) {
     int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
-    for (uint32_t base = 0; base < nd.count; base += 32) {
-        const uint32_t i = base + lane;
-        const int c = (i < nd.count) ? child_of(k[i], mx, my) : 4;
-        c0 += __popc(__ballot_sync(0xffffffffu, c == 0));
-        c1 += __popc(__ballot_sync(0xffffffffu, c == 1));
-        c2 += __popc(__ballot_sync(0xffffffffu, c == 2));
-        c3 += __popc(__ballot_sync(0xffffffffu, c == 3));
+    if (count <= 128u) {
+        int c[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t i = 32u * u + lane;
+            c[u] = (i < count) ? child_of(k[i], mx, my) : 4;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (32u * u >= count) break;
+            c0 += __popc(__ballot_sync(0xffffffffu, c[u] == 0));
+            c1 += __popc(__ballot_sync(0xffffffffu, c[u] == 1));
+            c2 += __popc(__ballot_sync(0xffffffffu, c[u] == 2));
+            c3 += __popc(__ballot_sync(0xffffffffu, c[u] == 3));
+        }
+        return make_uint4(c0, c1, c2, c3);
+    }
+    for (uint32_t base = 0; base < count; base += 128) {
+        uint32_t key[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t i = base + 32u * u + lane;
+            key[u] = (i < count) ? k[i] : 0xFFFFFFFFu;  // x = y = 4095: never a key (coordinates stay below 4096 - border)
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const bool ok = base + 32u * u + lane < count;
+            const int c = child_of(key[u], mx, my);
+            c0 += (ok && c == 0); c1 += (ok && c == 1); c2 += (ok && c == 2); c3 += (ok && c == 3);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        c0 += __shfl_xor_sync(0xffffffffu, c0, o);
+        c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+        c2 += __shfl_xor_sync(0xffffffffu, c2, o);
+        c3 += __shfl_xor_sync(0xffffffffu, c3, o);
     }
     return make_uint4(c0, c1, c2, c3);
 }
 
-// warp: write the child node records of `nd` (k-th non-empty child goes to list position firstPos - k) and move the
-// keys, stably, into the other buffer
-__device__ void warp_split(const QNode& nd, uint4 cc, uint32_t* bufs, int candCap, QNode* outList, int firstPos, int lane) {
-    const int mx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1), my = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
+__device__ __forceinline__ void node_mid(const QNode& nd, int& mx, int& my) {
+    mx = nd.x0 + ((nd.x1 - nd.x0 + 1) >> 1);
+    my = nd.y0 + ((nd.y1 - nd.y0 + 1) >> 1);
+}
+__device__ __forceinline__ const uint32_t* node_keys(const QNode& nd, const uint32_t* bufs, int candCap) {
+    return bufs + ((nd.begin >> 31) ? candCap : 0) + (nd.begin & 0x7FFFFFFFu);
+}
+
+__device__ __forceinline__ uint4 warp_count_children(const QNode& nd, const uint32_t* bufs, int candCap, int lane) {
+    int mx, my;
+    node_mid(nd, mx, my);
+    return warp_count_range(node_keys(nd, bufs, candCap), nd.count, mx, my, lane);
+}
+
+// lanes 0..3: lane c writes the record of child c of `nd` (the k-th non-empty child goes to list position firstPos - k)
+__device__ __forceinline__ void write_children(const QNode& nd, uint4 cc, QNode* outList, int firstPos, int lane) {
+    if (lane >= 4) return;
+    int mx, my;
+    node_mid(nd, mx, my);
+    const uint32_t srcBuf = nd.begin >> 31, first = nd.begin & 0x7FFFFFFFu;
+    const int c = lane;
+    const uint32_t cnt = c == 0 ? cc.x : c == 1 ? cc.y : c == 2 ? cc.z : cc.w;
+    const uint32_t off = c == 0 ? 0u : c == 1 ? cc.x : c == 2 ? cc.x + cc.y : cc.x + cc.y + cc.z;
+    const int k = (c > 0 && cc.x != 0) + (c > 1 && cc.y != 0) + (c > 2 && cc.z != 0);  // non-empty children before c
+    if (cnt == 0) return;
+    QNode ch;
+    ch.x0 = (c & 1) ? (uint16_t)mx : nd.x0;
+    ch.x1 = (c & 1) ? nd.x1 : (uint16_t)mx;
+    ch.y0 = (c & 2) ? (uint16_t)my : nd.y0;
+    ch.y1 = (c & 2) ? nd.y1 : (uint16_t)my;
+    ch.begin = ((srcBuf ^ 1u) << 31) | (first + off);
+    ch.count = cnt;
+    outList[firstPos - k] = ch;
+}
+
+// warp: move src[0..count) stably into the four child runs of dst that start at run0..run3 (four loads in flight per trip)
+__device__ __forceinline__ void warp_split_range(const uint32_t* src, uint32_t count, uint32_t* dst, uint32_t run0, uint32_t run1, uint32_t run2,
+                                 uint32_t run3, int mx, int my, int lane) {
+    const uint32_t below = (1u << lane) - 1;
+    for (uint32_t base = 0; base < count; base += 128) {
+        uint32_t key[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t i = base + 32u * u + lane;
+            key[u] = (i < count) ? src[i] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (base + 32u * u >= count) break;
+            const int c = (base + 32u * u + lane < count) ? child_of(key[u], mx, my) : 4;
+            const uint32_t b0 = __ballot_sync(0xffffffffu, c == 0), b1 = __ballot_sync(0xffffffffu, c == 1);
+            const uint32_t b2 = __ballot_sync(0xffffffffu, c == 2), b3 = __ballot_sync(0xffffffffu, c == 3);
+            if (c == 0) dst[run0 + __popc(b0 & below)] = key[u];
+            else if (c == 1) dst[run1 + __popc(b1 & below)] = key[u];
+            else if (c == 2) dst[run2 + __popc(b2 & below)] = key[u];
+            else if (c == 3) dst[run3 + __popc(b3 & below)] = key[u];
+            run0 += __popc(b0); run1 += __popc(b1); run2 += __popc(b2); run3 += __popc(b3);
+        }
+    }
+}
+
+// warp: write the child node records of `nd` and move its keys, stably, into the other buffer
+__device__ __forceinline__ void warp_split(const QNode& nd, uint4 cc, uint32_t* bufs, int candCap, QNode* outList, int firstPos, int lane) {
+    int mx, my;
+    node_mid(nd, mx, my);
     const uint32_t srcBuf = nd.begin >> 31, first = nd.begin & 0x7FFFFFFFu;
     const uint32_t* src = bufs + (srcBuf ? candCap : 0) + first;
     uint32_t* dst = bufs + (srcBuf ? 0 : candCap) + first;
-    const uint32_t cnt[4] = {cc.x, cc.y, cc.z, cc.w};
-    uint32_t off[4];
-    off[0] = 0; off[1] = cc.x; off[2] = cc.x + cc.y; off[3] = cc.x + cc.y + cc.z;
-    if (lane == 0) {
-        int k = 0;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            if (cnt[c] == 0) continue;
-            QNode ch;
-            ch.x0 = (c & 1) ? (uint16_t)mx : nd.x0;
-            ch.x1 = (c & 1) ? nd.x1 : (uint16_t)mx;
-            ch.y0 = (c & 2) ? (uint16_t)my : nd.y0;
-            ch.y1 = (c & 2) ? nd.y1 : (uint16_t)my;
-            ch.begin = ((srcBuf ^ 1u) << 31) | (first + off[c]);
-            ch.count = cnt[c];
-            outList[firstPos - k] = ch;
-            ++k;
-        }
-    }
-    uint32_t run0 = off[0], run1 = off[1], run2 = off[2], run3 = off[3];
-    const uint32_t below = (1u << lane) - 1;
-    for (uint32_t base = 0; base < nd.count; base += 32) {
-        const uint32_t i = base + lane;
-        uint32_t key = 0;
-        int c = 4;
-        if (i < nd.count) {
-            key = src[i];
-            c = child_of(key, mx, my);
-        }
-        const uint32_t b0 = __ballot_sync(0xffffffffu, c == 0), b1 = __ballot_sync(0xffffffffu, c == 1);
-        const uint32_t b2 = __ballot_sync(0xffffffffu, c == 2), b3 = __ballot_sync(0xffffffffu, c == 3);
-        if (c == 0) dst[run0 + __popc(b0 & below)] = key;
-        else if (c == 1) dst[run1 + __popc(b1 & below)] = key;
-        else if (c == 2) dst[run2 + __popc(b2 & below)] = key;
-        else if (c == 3) dst[run3 + __popc(b3 & below)] = key;
-        run0 += __popc(b0); run1 += __popc(b1); run2 += __popc(b2); run3 += __popc(b3);
-    }
+    write_children(nd, cc, outList, firstPos, lane);
+    warp_split_range(src, nd.count, dst, 0, cc.x, cc.x + cc.y, cc.x + cc.y + cc.z, mx, my, lane);
 }
 
 __device__ __forceinline__ int nonzero4(uint4 c) { return (c.x != 0) + (c.y != 0) + (c.z != 0) + (c.w != 0); }
 
 // Core: keys[0..K) sit in buffer 0 of `bufs` in the reference's vToDistributeKeys order.  Returns the number of
 // kept keys (written to outKeys with (addX, addY) added to the coordinates).
-__device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, int nIni, float hX, int N, int addX,
+__device__ __forceinline__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, int nIni, float hX, int N, int addX,
                              int addY, uint32_t* outKeys, int outCap, const QtShared& S) {
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
     int* misc = S.misc;
     int* warpSums = misc + 16;
-    int* rootCnt = misc + 32;
+    int* rootCnt = misc + 48;
     if (K == 0 || nIni < 1) return 0;
     if (nIni > MAX_ROOTS) nIni = MAX_ROOTS;  // rejected on the host; guard only
 
     // ---- roots: stable partition of the candidates by kp.pt.x / hX (:917-921) into buffer 1 ----
-    for (int i = tid; i < nIni; i += blockDim.x) rootCnt[i] = 0;
+    // Warp w owns the contiguous chunk w of the candidates: it counts its keys per root, a prefix over (root, warp) gives
+    // every (warp, root) its first slot, and the warp scatters its chunk in order — stable, and each key is read twice.
+    const int chunk = ((K + nw - 1) / nw + 31) & ~31;
+    const int cb = min(wid * chunk, K), ce = min(cb + chunk, K);
+    int* myRoot = S.rootW + wid * nIni;
+    for (int i = tid; i < nw * nIni; i += blockDim.x) S.rootW[i] = 0;
     __syncthreads();
-    for (int i = tid; i < K; i += blockDim.x) {
-        const int r = min((int)__fdiv_rn((float)key_x(bufs[i]), hX), nIni - 1);
-        atomicAdd(&rootCnt[r], 1);
+    const uint32_t laneBelow = (1u << lane) - 1;
+    for (int base = cb; base < ce; base += 128) {
+        int r[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int i = base + 32 * u + lane;
+            r[u] = (i < ce) ? min((int)__fdiv_rn((float)key_x(bufs[i]), hX), nIni - 1) : -1;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (base + 32 * u >= ce) break;
+            const uint32_t act = __ballot_sync(0xffffffffu, r[u] >= 0);
+            if (r[u] >= 0) {
+                const uint32_t peers = __match_any_sync(act, r[u]);
+                if ((peers & laneBelow) == 0) myRoot[r[u]] += __popc(peers);  // one leader per root present in this row
+            }
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    for (int r = tid; r < nIni; r += blockDim.x) {  // per root: exclusive prefix over the warps, total into rootCnt
+        int run = 0;
+        for (int w = 0; w < nw; ++w) {
+            const int c = S.rootW[w * nIni + r];
+            S.rootW[w * nIni + r] = run;
+            run += c;
+        }
+        rootCnt[r] = run;
     }
     __syncthreads();
     if (tid == 0) {
@@ -180,20 +275,30 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
         misc[0] = n;
     }
     __syncthreads();
-    for (int r = wid; r < nIni; r += nw) {  // warp r compacts its root's keys in candidate order
-        uint32_t* dst = bufs + candCap + rootCnt[r];
-        int run = 0;
-        for (int base = 0; base < K; base += 32) {
-            const int i = base + lane;
-            uint32_t key = 0;
-            bool mine = false;
-            if (i < K) {
-                key = bufs[i];
-                mine = min((int)__fdiv_rn((float)key_x(key), hX), nIni - 1) == r;
+    {
+        uint32_t* dst = bufs + candCap;
+        for (int base = cb; base < ce; base += 128) {
+            uint32_t key[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int i = base + 32 * u + lane;
+                key[u] = (i < ce) ? bufs[i] : 0u;
             }
-            const uint32_t b = __ballot_sync(0xffffffffu, mine);
-            if (mine) dst[run + __popc(b & ((1u << lane) - 1))] = key;
-            run += __popc(b);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (base + 32 * u >= ce) break;
+                const bool ok = base + 32 * u + lane < ce;
+                const int r = ok ? min((int)__fdiv_rn((float)key_x(key[u]), hX), nIni - 1) : -1;
+                const uint32_t act = __ballot_sync(0xffffffffu, ok);
+                uint32_t peers = 0;
+                if (ok) {
+                    peers = __match_any_sync(act, r);
+                    dst[rootCnt[r] + myRoot[r] + __popc(peers & laneBelow)] = key[u];
+                }
+                __syncwarp();
+                if (ok && (peers & laneBelow) == 0) myRoot[r] += __popc(peers);
+                __syncwarp();
+            }
         }
     }
     __syncthreads();
@@ -204,13 +309,32 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
     int P = 0;            // the first P list positions are the children pushed by the last pass
     bool finalPhase = false;
     while (true) {
-        QNode* L = S.list[cur];
-        QNode* Lnew = S.list[cur ^ 1];
+        // (constant indices + a select: indexing S.list with `cur` would put the whole struct into local memory)
+        QNode* L = cur ? S.list[1] : S.list[0];
+        QNode* Lnew = cur ? S.list[0] : S.list[1];
         const int prev = n;
         if (!finalPhase) {
             // ---- sweep ----
+            // nodes holding more than QT_BIG keys (the first passes: a handful of nodes own thousands of keys each) are
+            // counted and split by the whole block, warp w taking chunk w of the node's segment; all others by one warp each
+            if (tid == 0) {
+                misc[1] = n;  // cut
+                misc[3] = 0;  // nodes for the whole block
+            }
+            __syncthreads();
+            for (int i = tid; i < n; i += blockDim.x) {
+                int slot = -1;
+                if (L[i].count > QT_BIG) {
+                    slot = atomicAdd(&misc[3], 1);
+                    if (slot < QT_MAXBIG) S.bigList[slot] = i;
+                }
+                S.sC[i] = slot;
+            }
+            __syncthreads();
+            const int nBig = misc[3] <= QT_MAXBIG ? misc[3] : 0;  // more than the table holds: all of them go one warp each
             for (int i = wid; i < n; i += nw) {
                 const QNode nd = L[i];
+                if (nBig && S.sC[i] >= 0) continue;
                 uint4 cc = make_uint4(0, 0, 0, 0);
                 if (nd.count > 1) cc = warp_count_children(nd, bufs, candCap, lane);
                 if (lane == 0) {
@@ -218,7 +342,26 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
                     S.sA[i] = nd.count > 1 ? nonzero4(cc) - 1 : 0;
                 }
             }
-            if (tid == 0) misc[1] = n;  // cut
+            for (int b = 0; b < nBig; ++b) {
+                const QNode nd = L[S.bigList[b]];
+                int mx, my;
+                node_mid(nd, mx, my);
+                const uint32_t ch = ((nd.count + nw - 1) / nw + 31u) & ~31u;
+                const uint32_t c0 = min((uint32_t)wid * ch, nd.count), c1 = min(c0 + ch, nd.count);
+                const uint4 cc = warp_count_range(node_keys(nd, bufs, candCap) + c0, c1 - c0, mx, my, lane);
+                if (lane == 0) S.bigCnt[b * nw + wid] = cc;
+            }
+            __syncthreads();
+            for (int b = tid; b < nBig; b += blockDim.x) {
+                uint4 t = make_uint4(0, 0, 0, 0);
+                for (int w = 0; w < nw; ++w) {
+                    const uint4 c = S.bigCnt[b * nw + w];
+                    t.x += c.x; t.y += c.y; t.z += c.z; t.w += c.w;
+                }
+                const int i = S.bigList[b];
+                S.cc[i] = t;
+                S.sA[i] = nonzero4(t) - 1;
+            }
             __syncthreads();
             block_exscan(S.sA, n, warpSums);
             for (int i = tid; i < n; i += blockDim.x)
@@ -235,8 +378,30 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
             const int surv = block_exscan(S.sB, n, warpSums);
             for (int i = wid; i < n; i += nw) {
                 const QNode nd = L[i];
-                if (i < cut && nd.count > 1) warp_split(nd, S.cc[i], bufs, candCap, Lnew, pushed - 1 - S.sA[i], lane);
-                else if (lane == 0) Lnew[pushed + S.sB[i]] = nd;
+                if (i < cut && nd.count > 1) {
+                    if (!(nBig && S.sC[i] >= 0)) warp_split(nd, S.cc[i], bufs, candCap, Lnew, pushed - 1 - S.sA[i], lane);
+                } else if (lane == 0) {
+                    Lnew[pushed + S.sB[i]] = nd;
+                }
+            }
+            for (int b = 0; b < nBig; ++b) {
+                const int i = S.bigList[b];
+                if (i >= cut) continue;  // the walk stopped before this node: it survives unsplit (copied above)
+                const QNode nd = L[i];
+                const uint4 cc = S.cc[i];
+                int mx, my;
+                node_mid(nd, mx, my);
+                if (wid == 0) write_children(nd, cc, Lnew, pushed - 1 - S.sA[i], lane);
+                uint32_t r0 = 0, r1 = cc.x, r2 = cc.x + cc.y, r3 = cc.x + cc.y + cc.z;
+                for (int w = 0; w < wid; ++w) {  // keys of the chunks before mine
+                    const uint4 c = S.bigCnt[b * nw + w];
+                    r0 += c.x; r1 += c.y; r2 += c.z; r3 += c.w;
+                }
+                const uint32_t ch = ((nd.count + nw - 1) / nw + 31u) & ~31u;
+                const uint32_t c0 = min((uint32_t)wid * ch, nd.count), c1 = min(c0 + ch, nd.count);
+                const uint32_t srcBuf = nd.begin >> 31, first = nd.begin & 0x7FFFFFFFu;
+                warp_split_range(bufs + (srcBuf ? candCap : 0) + first + c0, c1 - c0, bufs + (srcBuf ? 0 : candCap) + first, r0, r1, r2, r3,
+                                 mx, my, lane);
             }
             __syncthreads();
             n = pushed + surv;
@@ -318,7 +483,7 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
             if (tid == 0) misc[2] = 0;
             __syncthreads();
             int mine = 0;
-            for (int i = tid; i < P; i += blockDim.x) mine += S.list[cur][i].count > 1 ? 1 : 0;
+            for (int i = tid; i < P; i += blockDim.x) mine += (cur ? S.list[1] : S.list[0])[i].count > 1 ? 1 : 0;
             if (mine) atomicAdd(&misc[2], mine);
             __syncthreads();
             if (n + 3 * misc[2] > N) finalPhase = true;
@@ -327,7 +492,7 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
     }
 
     // ---- keep the best key of every node (:1098-1117): first key of maximal response, list order ----
-    const QNode* L = S.list[cur];
+    const QNode* L = cur ? S.list[1] : S.list[0];
     const int nOut = min(n, outCap);
     // Final nodes hold few keys (about candidates / N), so four lanes share a node: 8 nodes per warp step
     for (int i0 = wid * 8; i0 < nOut; i0 += nw * 8) {
@@ -352,24 +517,31 @@ __device__ int quadtree_core(uint32_t* bufs, int candCap, int K, int W, int H, i
     return n;
 }
 
-__device__ void carve(uint8_t* smem, int maxNodes, int maxCells, QtShared& S) {
+__device__ __forceinline__ void carve(uint8_t* smem, int maxNodes, int maxCells, QtShared& S) {
+    const int warps = blockDim.x >> 5;
     size_t o = 0;
     S.list[0] = reinterpret_cast<QNode*>(smem + o); o += (size_t)maxNodes * sizeof(QNode);
     S.list[1] = reinterpret_cast<QNode*>(smem + o); o += (size_t)maxNodes * sizeof(QNode);
     S.cc = reinterpret_cast<uint4*>(smem + o); o += (size_t)maxNodes * sizeof(uint4);
+    S.bigCnt = reinterpret_cast<uint4*>(smem + o); o += (size_t)QT_MAXBIG * warps * sizeof(uint4);
     S.sA = reinterpret_cast<int*>(smem + o); o += (size_t)maxNodes * 4;
     S.sB = reinterpret_cast<int*>(smem + o); o += (size_t)maxNodes * 4;
     S.sC = reinterpret_cast<int*>(smem + o); o += (size_t)maxNodes * 4;
-    S.misc = reinterpret_cast<int*>(smem + o); o += (32 + MAX_ROOTS + 4) * 4;
+    S.misc = reinterpret_cast<int*>(smem + o); o += (48 + MAX_ROOTS + 4) * 4;
+    S.rootW = reinterpret_cast<int*>(smem + o); o += (size_t)warps * MAX_ROOTS * 4;
+    S.bigList = reinterpret_cast<int*>(smem + o); o += (size_t)QT_MAXBIG * 4;
     S.cellOff = reinterpret_cast<int*>(smem + o); o += (size_t)(maxCells + 1) * 4;
 }
 
-static size_t qt_smem(int maxNodes, int maxCells) {
-    return (size_t)maxNodes * (2 * sizeof(QNode) + sizeof(uint4) + 12) + (32 + MAX_ROOTS + 4) * 4 + (size_t)(maxCells + 1) * 4;
+static size_t qt_smem(int maxNodes, int maxCells, int threads = QT_THREADS) {
+    const int warps = threads / 32;
+    return (size_t)maxNodes * (2 * sizeof(QNode) + sizeof(uint4) + 12) + (48 + MAX_ROOTS + 4) * 4 + (size_t)(maxCells + 1) * 4 +
+           (size_t)QT_MAXBIG * warps * sizeof(uint4) + (size_t)warps * MAX_ROOTS * 4 + (size_t)QT_MAXBIG * 4;
 }
 
 // grid (nlevels, batch)
-__global__ void __launch_bounds__(QT_THREADS) k_quadtree(const __grid_constant__ FrameGeom g, int maxNodes, int maxCells,
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) k_quadtree(const __grid_constant__ FrameGeom g, int maxNodes, int maxCells,
                                                           const int* __restrict__ cellCnt,
                                                           const uint32_t* __restrict__ cellKeys, uint32_t* qtScratch,
                                                           int* __restrict__ lvlCnt, uint32_t* __restrict__ lvlKeys,
@@ -392,9 +564,10 @@ __global__ void __launch_bounds__(QT_THREADS) k_quadtree(const __grid_constant__
         if (tid == 0) atomicExch(dStatus, ORBX_E_OVERFLOW);
         K = L.candCap;
     }
-    for (int c = tid >> 5; c < nCells; c += blockDim.x >> 5) {  // a warp copies one cell's slot
+    // eight lanes copy one cell's slot (a cell of a natural image holds a handful of corners): four cells per warp trip
+    for (int c = tid >> 3; c < nCells; c += blockDim.x >> 3) {
         const int nc = min(cnt[c], cellCap), o = S.cellOff[c];
-        for (int k = tid & 31; k < nc; k += 32)
+        for (int k = tid & 7; k < nc; k += 8)
             if (o + k < K) bufs[o + k] = keys[(long long)c * cellCap + k];
     }
     __syncthreads();
@@ -431,10 +604,29 @@ int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uin
         set_error("quadtree: %zu bytes of shared memory needed (nfeatures per level %d, cells %d)", smem, maxQuota, maxCells);
         return ORBX_E_INVALID;
     }
-    static size_t configured[ORBX_MAX_DEVICES] = {};
-    if (int rcAttr = ensure_dynamic_smem((const void*)k_quadtree, smem, configured)) return rcAttr;
     dim3 grid(g.nlevels, batch);
-    k_quadtree<<<grid, QT_THREADS, smem, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
+    // up to one CTA per SM: nothing else would run beside it, so every (frame, level) gets 32 warps instead of 8 — the walk is
+    // a chain of short block-wide steps and single-frame latency is that chain (ORBX_QT_WIDE=0 switches it off)
+    // Small batches (single-frame latency; at most one CTA per SM): a CTA gets 512 threads instead of 256 — the walk is a chain
+    // of short block-wide steps, measured on one KITTI frame (level 0, cycles): 108 k at 256 threads, 88 k at 512, 103 k at
+    // 1024; keeping the key buffers in shared memory changed nothing (the chain is instruction latency, not memory latency).
+    // ORBX_QT_THREADS = 256 / 512 / 1024 overrides.
+    static const int threadsPref = []() { const char* e = getenv("ORBX_QT_THREADS"); return e ? atoi(e) : QT_THREADS_SMALL; }();
+    const bool small = g.nlevels * batch <= 148;
+    const int threads = small && (threadsPref == 512 || threadsPref == 1024) ? threadsPref : QT_THREADS;
+    const size_t smem2 = qt_smem(maxNodes, maxCells, threads);
+    static size_t configured[3][ORBX_MAX_DEVICES] = {};
+    int rcAttr;
+    if (threads == 1024) {
+        if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<1024>, smem2, configured[2]))) return rcAttr;
+        k_quadtree<1024><<<grid, 1024, smem2, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
+    } else if (threads == 512) {
+        if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<512>, smem2, configured[1]))) return rcAttr;
+        k_quadtree<512><<<grid, 512, smem2, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
+    } else {
+        if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<QT_THREADS>, smem2, configured[0]))) return rcAttr;
+        k_quadtree<QT_THREADS><<<grid, QT_THREADS, smem2, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
+    }
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
@@ -465,3 +657,4 @@ int launch_quadtree_single(const uint32_t* dKeysIn, int n, int minX, int maxX, i
 }
 
 }  // namespace orbx
+

@@ -15,3 +15,12 @@ ts = []
 for i in range(30):
     t0 = time.perf_counter(); ex(img); ts.append((time.perf_counter() - t0) * 1e3)
 print(kind, "p50 ms", sorted(ts)[len(ts) // 2])
+ex.enable_timing(True)  # events between the stages of a single frame (GPU time of each stage; the call no longer replays a graph)
+acc = {}
+for i in range(20):
+    ex(img)
+    if i >= 5:
+        for k, v in ex.stage_ms().items():
+            acc.setdefault(k, []).append(v)
+print(kind, "single-frame stage us:", {k.split()[0]: round(1e3 * sorted(v)[len(v) // 2], 1) for k, v in acc.items()},
+      "sum", round(1e3 * sum(sorted(v)[len(v) // 2] for v in acc.values()), 1))
