@@ -153,12 +153,19 @@ class ORBextractor:
             return np.empty(0, KP_DTYPE), np.empty((0, 32), np.uint8)
         assert image.dtype == np.uint8 and image.ndim == 2 and image.strides[1] == 1, "CV_8UC1 image expected"
         h, w = image.shape
-        cap = self.default_cap()
-        kps = np.empty(cap, KP_DTYPE)
-        desc = np.empty((cap, 32), np.uint8)
-        n = C.c_int(0)
-        _check(lib().orbx_extract(self._h, _p(image), w, h, C.c_size_t(image.strides[0]), _p(kps), _p(desc), cap, C.byref(n)))
-        return kps[:n.value].copy(), desc[:n.value].copy()
+        sc = getattr(self, "_single", None)
+        if sc is None:  # per-extractor scratch for the per-frame call: output arrays, their addresses, the bound C function
+            cap = self.default_cap()
+            kps, desc, n = np.empty(cap, KP_DTYPE), np.empty((cap, 32), np.uint8), C.c_int(0)
+            fn = lib().orbx_extract
+            fn.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+            sc = self._single = (fn, kps, desc, n, kps.ctypes.data, desc.ctypes.data, C.addressof(n), cap)
+        fn, kps, desc, n, pk, pd, pn, cap = sc
+        rc = fn(self._h, image.ctypes.data, w, h, image.strides[0], pk, pd, cap, pn)
+        if rc:
+            _check(rc)
+        m = n.value
+        return kps[:m].copy(), desc[:m].copy()
 
     def extract_batch(self, frames: np.ndarray, kps=None, desc=None, counts=None, cap=None):
         """frames: uint8 [B, h, w] host array (pinned or pageable) -> (kps [B, cap], desc [B, cap, 32], counts [B])"""

@@ -453,6 +453,12 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     FrameGeom g = ex->g;
     g.f0 = f0;  // scratch frames [f0, f0 + batch)
     g.patternVariant = ex->patternVariant;
+    // Single frames: the launches of the sequence overlap (programmatic dependent launch) — a kernel is resident, with its
+    // tables and constants loaded, when its predecessor completes.  ORBX_PDL=0 switches it off.
+    static const int pdlPref = []() { const char* e = getenv("ORBX_PDL"); return e ? atoi(e) : 2; }();  // 1: resize chain only, 2: all
+    const bool pdlOk = batch <= 2 && !getenv("ORBX_SYNC_STAGES") && !getenv("ORBX_BLUR_OVERLAP");
+    const bool pdl = pdlOk && pdlPref >= 1;
+    g.pdl = pdlOk && pdlPref >= 2 ? 1 : 0;
     const int nl = g.nlevels;
     int* cellCnt = ex->cellCnt.as<int>() + (size_t)f0 * g.nCellsTotal;
     uint32_t* cellKeys = ex->cellKeys.as<uint32_t>() + (size_t)f0 * (size_t)g.keysPerFrame;
@@ -471,7 +477,7 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     for (int l = 1; l < nl; ++l) {
         if (ex->areaFast[l] & 4)
             rc = launch_pyramid_level_tma(g, ex->resizeMaps, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->rzTiles[l].as<int>(),
-                                          ex->rzTiles[l].as<int>() + ex->rzTilesX[l], batch, s);
+                                          ex->rzTiles[l].as<int>() + ex->rzTilesX[l], batch, s, pdl);
         else
             rc = launch_pyramid_level(g, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->areaFast[l], batch, s);
         if (rc) return rc;

@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
                                                         const __grid_constant__ TmaMaps maps) {
     __shared__ __align__(128) uint8_t tile[BLUR_BH * BLUR_BW];
     __shared__ __align__(8) uint64_t bar;
+    if (g.pdl) griddep_launch_dependents();
     const int tid = threadIdx.x, f = blockIdx.y + g.f0;  // scratch frame
     int t = blockIdx.x, level = 0;
     while (level + 1 < g.nlevels && t >= g.lv[level + 1].blurTileBase) ++level;
@@ -42,6 +43,7 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
         fence_mbar_init();
     }
     __syncthreads();
+    if (g.pdl) griddep_wait();  // the pyramid comes from kernels further up the chain: complete once the predecessor is
     if (tid == 0) {
         mbar_expect_tx(&bar, BLUR_BH * BLUR_BW);
         tma_load_3d(tile, &maps.m[level], XOFF + x0 - 16, EDGE + y0 - 3, f, &bar);  // window = box columns 13..146
@@ -92,7 +94,7 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
 
 int launch_blur(const FrameGeom& g, const TmaMaps& maps, int batch, cudaStream_t s) {
     dim3 grid(g.blurTilesTotal, batch);
-    k_blur7<<<grid, BLUR_THREADS, 0, s>>>(g, maps);
+    ORBX_CUDA(launch_kernel(k_blur7, grid, dim3(BLUR_THREADS), 0, s, g.pdl != 0, g, maps));
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -18,6 +18,7 @@
 //          restatement against the host libm on millions of angles.
 // Output position = (number of keypoints of lower levels of the same frame) + index within the level.
 #include "orbx_internal.h"
+#include "tma.cuh"
 
 namespace orbx {
 
@@ -128,11 +129,13 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     __shared__ __align__(16) uint32_t bpatch[DESC_WARPS][BP_ROWS * BP_WORDS + 2];
     __shared__ int sBefore[ORBX_MAX_LEVELS + 1];
     __shared__ unsigned char sLevelOf[DESC_WARPS * DESC_PER_WARP];  // pyramid level of each of the CTA's slots
+    if (g.pdl) griddep_launch_dependents();
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {
         patF[i] = d_patF[g.patternVariant & 1][i];
         coefU[i] = d_coefU[i];
         coefV[i] = d_coefV[i];
     }
+    if (g.pdl) griddep_wait();  // the tables above are constants; everything below reads what the chain produced
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, f = blockIdx.y;
     const int* cnt = lvlCnt + (long long)f * g.nlevels;
@@ -316,7 +319,8 @@ int launch_describe(const FrameGeom& g, int batch, const int* lvlCnt, const uint
     if (rc) return rc;
     const int perCta = DESC_WARPS * DESC_PER_WARP;
     dim3 grid((g.slotsTotal + perCta - 1) / perCta, batch);
-    k_orient_describe<<<grid, DESC_WARPS * 32, 0, s>>>(g, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts, dLvlAngles, dStatus);
+    ORBX_CUDA(launch_kernel(k_orient_describe, grid, dim3(DESC_WARPS * 32), 0, s, g.pdl != 0, g, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts,
+                            dLvlAngles, dStatus));
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -143,6 +143,7 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
                                                              int* __restrict__ cellCnt, uint32_t* __restrict__ cellKeys,
                                                              int* __restrict__ dStatus, int batch, int fpc) {
     extern __shared__ __align__(128) uint8_t smem[];
+    if (g.pdl) griddep_launch_dependents();
     const int TW = g.fastBoxW, TH = g.fastBoxH, TN = TW * TH, TWq = TW >> 2;
     const int TNa = (TN + 127) & ~127;  // a ring stage (TMA destinations are 128-byte aligned)
     const int BW = (TW + 31) >> 5;      // keep-bitmap words per tile row
@@ -203,6 +204,7 @@ __global__ void __launch_bounds__(FS_THREADS, ORBX_FS_MINBLOCKS) k_fast_strips(c
     }
     if (tid < 32) cntAll[tid] = 0;
     __syncthreads();
+    if (g.pdl) griddep_wait();  // strip geometry and column tables are built; the pyramid is complete once the predecessor is
     if (tid == 0) {
         mbar_expect_tx(&bar[0], (uint32_t)TN);
         tma_load_3d(smem, &maps.m[st.level], boxX, boxY, fBeg + g.f0, &bar[0]);
@@ -582,7 +584,7 @@ int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrip
     int fpc = ORBX_FS_FPC;
     while (fpc > 1 && (long long)g.nStrips * ((batch + fpc - 1) / fpc) < 4LL * 148 * ORBX_FS_MINBLOCKS) fpc >>= 1;
     dim3 grid(g.nStrips, (batch + fpc - 1) / fpc);
-    k_fast_strips<<<grid, FS_THREADS, smem, s>>>(g, maps, dStrips, cellCnt, cellKeys, dStatus, batch, fpc);
+    ORBX_CUDA(launch_kernel(k_fast_strips, grid, dim3(FS_THREADS), smem, s, g.pdl != 0, g, maps, dStrips, cellCnt, cellKeys, dStatus, batch, fpc));
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -37,7 +37,8 @@ __device__ __forceinline__ int reflect101(int p, int n) {
 constexpr int RZ_ROWS = 64;  // minimum rows per CTA; launchers raise it (rowsPerCta) while the grid still fills the GPU
 __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plane, int w, int h, int pitch, int rows,
                                                       long long planeStride, const uint8_t* __restrict__ frames,
-                                                      long long stride, long long frameStride, int rowsPerCta) {
+                                                      long long stride, long long frameStride, int rowsPerCta, int pdl) {
+    if (pdl) griddep_launch_dependents();  // the edge kernel reads the same frames and writes other bytes: it runs beside this one
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int bx = blockIdx.x * 512 + lane * 16;
     const int f = blockIdx.z;
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(256) k_pyramid_base(uint8_t* __restrict__ plan
 // Level 0, row ends: one thread per (row, 16-byte group outside the fully interior range) gathers its bytes one by one at
 // the reflected coordinate (BORDER_REFLECT_101) and writes zeros into the row padding.  nEdge = groups per row it owns:
 // groups 0, 1 (left border) and the groups from the first not fully interior one to the end of the row.
-__global__ void __launch_bounds__(256) k_pyramid_base_edges(uint8_t* __restrict__ plane, int w, int h, int pitch, int rows,
+__device__ __forceinline__ void pyramid_base_edges_body(uint8_t* __restrict__ plane, int w, int h, int pitch, int rows,
                                                             long long planeStride, const uint8_t* __restrict__ frames,
                                                             long long stride, long long frameStride, int firstRight, int nEdge) {
     const int i = blockIdx.x * 256 + threadIdx.x;
@@ -93,6 +94,16 @@ __global__ void __launch_bounds__(256) k_pyramid_base_edges(uint8_t* __restrict_
         if (px >= 0 && px < w + 2 * EDGE) q[j >> 2] |= (uint32_t)__ldg(src + reflect101(px - EDGE, w)) << (8 * (j & 3));
     }
     *reinterpret_cast<uint4*>(plane + (long long)f * planeStride + (long long)py * pitch + bx) = make_uint4(q[0], q[1], q[2], q[3]);
+}
+
+__global__ void __launch_bounds__(256) k_pyramid_base_edges(uint8_t* __restrict__ plane, int w, int h, int pitch, int rows,
+                                                            long long planeStride, const uint8_t* __restrict__ frames,
+                                                            long long stride, long long frameStride, int firstRight, int nEdge, int pdl) {
+    // pdl: launched beside k_pyramid_base (same input, disjoint output).  Its successor waits for THIS grid only, so this grid
+    // does not end before k_pyramid_base has: every thread passes griddep_wait() before it exits.
+    if (pdl) griddep_launch_dependents();
+    pyramid_base_edges_body(plane, w, h, pitch, rows, planeStride, frames, stride, frameStride, firstRight, nEdge);
+    if (pdl) griddep_wait();
 }
 
 // Resize: a CTA of 8 warps produces a 128-px x 64-row tile of the padded destination plane.  A thread owns 4
@@ -239,21 +250,29 @@ __global__ void __launch_bounds__(256) k_pyramid_resize4(uint8_t* __restrict__ d
 __global__ void __launch_bounds__(32) k_pyramid_resize_tma(const __grid_constant__ TmaMaps maps, int srcLevel, uint8_t* __restrict__ dplane,
                                                            int dw, int dh, int dpitch, int drows, long long dStride,
                                                            const ResizeTab* __restrict__ xtab, const ResizeTab* __restrict__ ytab,
-                                                           const int* __restrict__ tileX0, const int* __restrict__ tileY0, int f0) {
+                                                           const int* __restrict__ tileX0, const int* __restrict__ tileY0, int f0, int pdl,
+                                                           int split) {
+    // pdl (single-frame latency path): this grid was launched while the level above was still being written, and lets the next
+    // level start in turn; everything up to the TMA load (tables, constants) overlaps the predecessor, the load waits for it
+    if (pdl) griddep_launch_dependents();
     __shared__ __align__(128) uint8_t tile[RZT_BH * RZT_BW];
     __shared__ __align__(8) uint64_t bar;
     __shared__ uint4 rowTab[RZT_TH];
     const int lane = threadIdx.x;
     const int bx = blockIdx.x * 128 + lane * 4;  // byte column of this thread's 4 pixels
     const int f = blockIdx.z;
-    const int bX0 = tileX0[blockIdx.x], bY0 = tileY0[blockIdx.y];  // box origin in the source plane (byte column, row)
+    // split > 1 (single frames: the GPU is empty and a tile's row loop is the critical path): `split` CTAs share one tile, each
+    // loads the tile's box and produces RZT_TH / split of its rows
+    const int tileY = blockIdx.y / split, part = blockIdx.y - tileY * split;
+    const int row0 = tileY * RZT_TH + part * (RZT_TH / split), rowEnd = min(row0 + RZT_TH / split, min(tileY * RZT_TH + RZT_TH, drows));
+    if (row0 >= rowEnd) return;
+    const int bX0 = tileX0[blockIdx.x], bY0 = tileY0[tileY];  // box origin in the source plane (byte column, row)
     if (lane == 0) {
         mbar_init(&bar, 1);
         fence_mbar_init();
         mbar_expect_tx(&bar, RZT_BH * RZT_BW);
-        tma_load_3d(tile, &maps.m[srcLevel], bX0, bY0, f + f0, &bar);
+        if (!pdl) tma_load_3d(tile, &maps.m[srcLevel], bX0, bY0, f + f0, &bar);
     }
-    const int row0 = blockIdx.y * RZT_TH, rowEnd = min(row0 + RZT_TH, drows);
     if (row0 + lane < rowEnd) {  // per-row constants: tile rows of the two source rows, vertical coefficients << 16
         const ResizeTab yt = ytab[reflect101(row0 + lane - EDGE, dh)];
         rowTab[lane] = make_uint4((uint32_t)(EDGE + (int)yt.s0 - bY0), (uint32_t)(EDGE + (int)yt.s1 - bY0), (uint32_t)(uint16_t)yt.c0 << 16,
@@ -285,6 +304,10 @@ __global__ void __launch_bounds__(32) k_pyramid_resize_tma(const __grid_constant
     const uint32_t sh = (uint32_t)(colByte & 3) * 8;
     const uint32_t* __restrict__ tq = reinterpret_cast<const uint32_t*>(tile) + (colByte >> 2);
     __syncwarp();
+    if (pdl) {
+        griddep_wait();
+        if (lane == 0) tma_load_3d(tile, &maps.m[srcLevel], bX0, bY0, f + f0, &bar);
+    }
     mbar_wait(&bar, 0);
     if (bx >= dpitch) return;
     uint8_t* __restrict__ dbase = dplane + (long long)(f + f0) * dStride + bx;
@@ -339,13 +362,14 @@ int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, s
     const int gx = (L.pitch + 511) / 512, rpc = rows_per_cta(L.rows, gx, batch);
     dim3 grid(gx, (L.rows + rpc - 1) / rpc, batch);
     uint8_t* plane = L.plane + (long long)g.f0 * L.planeStride;
-    k_pyramid_base<<<grid, 256, 0, s>>>(plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride, (long long)frameStride, rpc);
+    k_pyramid_base<<<grid, 256, 0, s>>>(plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride, (long long)frameStride, rpc,
+                                        g.pdl);
     count_launch();
     // row ends: groups 0, 1 and everything from the first group that is not fully interior (interior x0 + 16 > w)
     const int firstRight = std::max(2, XOFF / 16 + L.w / 16), nEdge = 2 + (L.pitch / 16 - firstRight);
     dim3 egrid((L.rows * nEdge + 255) / 256, batch);
-    k_pyramid_base_edges<<<egrid, 256, 0, s>>>(plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride,
-                                                 (long long)frameStride, firstRight, nEdge);
+    ORBX_CUDA(launch_kernel(k_pyramid_base_edges, egrid, dim3(256), 0, s, g.pdl != 0, plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames,
+                            (long long)stride, (long long)frameStride, firstRight, nEdge, g.pdl));
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;
@@ -372,11 +396,28 @@ int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, c
 
 // the TMA-tiled kernel (areaFast bit 2: the tile windows of this level fit the box); `maps` are the resize maps of the SOURCE levels
 int launch_pyramid_level_tma(const FrameGeom& g, const TmaMaps& maps, int level, const ResizeTab* xtab, const ResizeTab* ytab,
-                             const int* tileX0, const int* tileY0, int batch, cudaStream_t s) {
+                             const int* tileX0, const int* tileY0, int batch, cudaStream_t s, bool pdl) {
     const LevelGeom& D = g.lv[level];
     dim3 grid((D.pitch + 127) / 128, (D.rows + RZT_TH - 1) / RZT_TH, batch);
-    k_pyramid_resize_tma<<<grid, 32, 0, s>>>(maps, level - 1, D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, xtab, ytab, tileX0, tileY0,
-                                              g.f0);
+    static const int splitPref = []() { const char* e = getenv("ORBX_RZ_SPLIT"); return e ? atoi(e) : 6; }();
+    const int split = pdl && splitPref >= 1 && RZT_TH % splitPref == 0 ? splitPref : 1;
+    grid.y *= split;
+    if (pdl) {  // programmatic dependent launch: may start while the previous kernel of the stream still runs (the kernel waits itself)
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = grid;
+        cfg.blockDim = dim3(32);
+        cfg.stream = s;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        ORBX_CUDA(cudaLaunchKernelEx(&cfg, k_pyramid_resize_tma, maps, level - 1, D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, xtab, ytab,
+                                     tileX0, tileY0, g.f0, 1, split));
+    } else {
+        k_pyramid_resize_tma<<<grid, 32, 0, s>>>(maps, level - 1, D.plane, D.w, D.h, D.pitch, D.rows, D.planeStride, xtab, ytab, tileX0, tileY0,
+                                                  g.f0, 0, 1);
+    }
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

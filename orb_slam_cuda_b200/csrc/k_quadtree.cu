@@ -21,6 +21,7 @@
 #include <cstdlib>
 
 #include "orbx_internal.h"
+#include "tma.cuh"
 
 namespace orbx {
 
@@ -549,6 +550,10 @@ __global__ void __launch_bounds__(THREADS) k_quadtree(const __grid_constant__ Fr
     extern __shared__ __align__(16) uint8_t qsmem[];
     QtShared S;
     carve(qsmem, maxNodes, maxCells, S);
+    if (g.pdl) {
+        griddep_launch_dependents();
+        griddep_wait();
+    }
     const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
     const LevelGeom& L = g.lv[level];
     const int nCells = L.nCols * L.nRows;
@@ -619,13 +624,16 @@ int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uin
     int rcAttr;
     if (threads == 1024) {
         if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<1024>, smem2, configured[2]))) return rcAttr;
-        k_quadtree<1024><<<grid, 1024, smem2, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
+        ORBX_CUDA(launch_kernel(k_quadtree<1024>, grid, dim3(1024), smem2, s, g.pdl != 0, g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt,
+                                lvlKeys, dStatus));
     } else if (threads == 512) {
         if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<512>, smem2, configured[1]))) return rcAttr;
-        k_quadtree<512><<<grid, 512, smem2, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
+        ORBX_CUDA(launch_kernel(k_quadtree<512>, grid, dim3(512), smem2, s, g.pdl != 0, g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt,
+                                lvlKeys, dStatus));
     } else {
         if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<QT_THREADS>, smem2, configured[0]))) return rcAttr;
-        k_quadtree<QT_THREADS><<<grid, QT_THREADS, smem2, s>>>(g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus);
+        ORBX_CUDA(launch_kernel(k_quadtree<QT_THREADS>, grid, dim3(QT_THREADS), smem2, s, g.pdl != 0, g, maxNodes, maxCells, cellCnt, cellKeys,
+                                qtScratch, lvlCnt, lvlKeys, dStatus));
     }
     count_launch();
     ORBX_CUDA(cudaGetLastError());

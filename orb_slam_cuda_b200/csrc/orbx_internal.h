@@ -86,6 +86,9 @@ struct FrameGeom {
     int iniTh, minTh;
     int patternVariant;       // ORBX_PATTERN_REFERENCE (0) / ORBX_PATTERN_CANONICAL (1): which bit_pattern_31_ the descriptors use
     int f0;                   // first scratch frame of this launch (lanes of the host-batch pipeline own disjoint ranges)
+    int pdl;                  // 1: the kernels of this launch sequence are chained by programmatic dependent launch (single-frame
+                              //    latency path): each lets its successor become resident at once and waits for its predecessor
+                              //    itself (griddep_wait) before it touches anything the predecessor wrote
     LevelGeom lv[ORBX_MAX_LEVELS];
 };
 
@@ -104,6 +107,23 @@ struct ResizeTab {  // one entry per destination column / row: source index pair
 
 void count_launch();
 void set_error(const char* fmt, ...);
+
+// <<<grid, block, smem, s>>> with, when pdl is set, cudaLaunchAttributeProgrammaticStreamSerialization: the kernel may start while
+// its predecessor in the stream still runs; such a kernel calls griddep_wait() (tma.cuh) before its first dependent access
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_kernel(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, bool pdl, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 #define ORBX_CUDA(call)                                                                          \
     do {                                                                                         \
@@ -193,7 +213,7 @@ int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, s
 int launch_pyramid_level(const FrameGeom& g, int level, const ResizeTab* xtab, const ResizeTab* ytab, int areaFast,
                          int batch, cudaStream_t s);
 int launch_pyramid_level_tma(const FrameGeom& g, const TmaMaps& maps, int level, const ResizeTab* xtab, const ResizeTab* ytab,
-                             const int* tileX0, const int* tileY0, int batch, cudaStream_t s);
+                             const int* tileX0, const int* tileY0, int batch, cudaStream_t s, bool pdl = false);
 // per-cell FAST-9 + threshold fallback + NMS
 int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrips, int batch, int* cellCnt,
                 uint32_t* cellKeys, int* dStatus, cudaStream_t s);

@@ -13,6 +13,12 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)_
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
+// Programmatic dependent launch (a kernel launched with cudaLaunchAttributeProgrammaticStreamSerialization may start while its
+// predecessor in the stream still runs): wait = block until the predecessor grid has completed and its writes are visible
+// (a no-op for a plainly launched kernel); launch_dependents = let the successor start (a no-op without such a successor).
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ void fence_mbar_init() {
     // make the initialised barrier visible to the async (TMA) proxy
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");

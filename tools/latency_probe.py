@@ -12,9 +12,10 @@ h, w = synth.SHAPES[kind]
 ex = X.ORBextractor(nf, 1.2, 8, 20, 7, w, h)
 img = synth.frame(kind, 5)
 ts = []
-for i in range(30):
+for i in range(400):
     t0 = time.perf_counter(); ex(img); ts.append((time.perf_counter() - t0) * 1e3)
-print(kind, "p50 ms", sorted(ts)[len(ts) // 2])
+ts = sorted(ts[20:])
+print(kind, "p50 ms", round(ts[len(ts) // 2], 4), "p10", round(ts[len(ts) // 10], 4), "min", round(ts[0], 4))
 ex.enable_timing(True)  # events between the stages of a single frame (GPU time of each stage; the call no longer replays a graph)
 acc = {}
 for i in range(20):
