@@ -350,16 +350,17 @@ __global__ void __launch_bounds__(32) k_pyramid_resize_tma(const __grid_constant
 
 // Rows one CTA walks: the per-thread column set-up (x-table entries, PRMT selectors) is paid once per CTA, so a CTA
 // takes as many rows as possible while the grid keeps >= 2 full waves of 148 SMs x 8 CTAs.
-static int rows_per_cta(int rows, int gx, int batch) {
+static int rows_per_cta(int rows, int gx, int batch, int minRows = RZ_ROWS) {
     int rpc = (rows + RZ_ROWS - 1) / RZ_ROWS * RZ_ROWS;
-    while (rpc > RZ_ROWS && (long long)gx * ((rows + rpc - 1) / rpc) * batch < 2 * 148 * 8) rpc = (rpc / 2 + 7) / 8 * 8;
-    return rpc < RZ_ROWS ? RZ_ROWS : rpc;
+    while (rpc > minRows && (long long)gx * ((rows + rpc - 1) / rpc) * batch < 2 * 148 * 8) rpc = (rpc / 2 + 7) / 8 * 8;
+    return rpc < minRows ? minRows : rpc;
 }
 
 int launch_pyramid_base(const FrameGeom& g, const uint8_t* dFrames, int batch, size_t stride, size_t frameStride,
                         cudaStream_t s) {
     const LevelGeom& L = g.lv[0];
-    const int gx = (L.pitch + 511) / 512, rpc = rows_per_cta(L.rows, gx, batch);
+    // single frames (pdl): one row per warp, so that no warp walks a chain of dependent row loads
+    const int gx = (L.pitch + 511) / 512, rpc = rows_per_cta(L.rows, gx, batch, g.pdl ? 8 : RZ_ROWS);
     dim3 grid(gx, (L.rows + rpc - 1) / rpc, batch);
     uint8_t* plane = L.plane + (long long)g.f0 * L.planeStride;
     k_pyramid_base<<<grid, 256, 0, s>>>(plane, L.w, L.h, L.pitch, L.rows, L.planeStride, dFrames, (long long)stride, (long long)frameStride, rpc,
