@@ -323,9 +323,9 @@ def latency_leg(X, wl, w, h, kind, cpu=False):
         fl, fr = pool.submit(eye, "L", exL, left), pool.submit(eye, "R", exR, right)
         fl.result(); fr.result()
         (kl, dl), (kr, dr) = res["L"], res["R"]
-        res["u"] = X.ComputeStereoMatches(exL, exR, kl, dl, kr, dr, 47.90639384423901, 435.2046959714599)
+        res["u"] = X.ComputeStereoMatchesLast(exL, exR, len(kl), 47.90639384423901, 435.2046959714599)  # on the device-resident output
 
-    out["stereo_euroc"] = {"p50_ms": p50(stereo_frame), "what": "left + right extraction on two (pooled) host threads + ComputeStereoMatches, 752x480, 1200 features per eye"}
+    out["stereo_euroc"] = {"p50_ms": p50(stereo_frame), "what": "left + right extraction on two (pooled) host threads + ComputeStereoMatches on the extractors' device-resident output (orbx_stereo_match_last), 752x480, 1200 features per eye"}
     out["stereo_euroc"]["matched"] = int((res["u"][0] >= 0).sum())
     # config 4: frame-to-frame matching of two 2000-feature KITTI frames: SearchForInitialization (window 100, ratio 0.9)
     a, b = synth.frame("kitti", 40), synth.shifted_frame("kitti", 40)

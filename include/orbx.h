@@ -366,6 +366,12 @@ int orbx_vocabulary_transform(orbx_vocabulary* v, const uint8_t* desc, int n, in
 int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypoint* kL, int nL, const uint8_t* descL,
                       const orbx_keypoint* kR, int nR, const uint8_t* descR, float bf, float mb, float* u_right,
                       float* depth);
+/* The same on the keypoints and descriptors the two extractors produced in their last orbx_extract call, as they still
+ * sit on the device — what the Frame constructor does (src/Frame.cc:77-80 extracts both eyes, :94 calls
+ * ComputeStereoMatches on exactly those mvKeys / mvKeysRight / descriptors): nothing is uploaded.  cap = capacity of
+ * u_right / depth (>= the left extractor's last keypoint count, else ORBX_E_INVALID).  Any other extractor call in between
+ * (a batch, a device-buffer call) makes it fail with ORBX_E_INVALID rather than read stale data. */
+int orbx_stereo_match_last(orbx_extractor* exL, orbx_extractor* exR, float bf, float mb, float* u_right, float* depth, int cap);
 
 #ifdef __cplusplus
 }

@@ -579,6 +579,15 @@ def ComputeStereoMatches(exL: ORBextractor, exR: ORBextractor, kpsL, descL, kpsR
     return u[:kpsL.size], z[:kpsL.size]
 
 
+def ComputeStereoMatchesLast(exL: ORBextractor, exR: ORBextractor, n_left: int, bf: float, fx: float):
+    """orbx_stereo_match_last: Frame::ComputeStereoMatches on the keypoints / descriptors the two extractors produced in their
+    last single-frame call, still on the device (nothing is uploaded).  n_left = number of left keypoints of that call."""
+    u = np.empty(max(n_left, 1), np.float32)
+    z = np.empty(max(n_left, 1), np.float32)
+    _check(lib().orbx_stereo_match_last(exL._h, exR._h, C.c_float(bf), C.c_float(np.float32(bf) / np.float32(fx)), _p(u), _p(z), int(n_left)))
+    return u[:n_left], z[:n_left]
+
+
 def UndistortKeyPoints(kps: np.ndarray, K, dist) -> np.ndarray:
     """Frame::UndistortKeyPoints (reference src/Frame.cc:403-433): K = (fx, fy, cx, cy), dist = k1 k2 p1 p2 [k3]."""
     kps = np.ascontiguousarray(kps, dtype=KP_DTYPE)

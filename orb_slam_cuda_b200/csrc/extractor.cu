@@ -117,6 +117,10 @@ struct orbx_extractor {
     int lastScratchBase = 0; // scratch frame holding frame `lastFrameBase` of the caller's batch
     int lastFrameBase = 0;   // index (within the caller's batch) of frame 0 of the scratch: > 0 after a chunked host batch
     int patternVariant = ORBX_PATTERN_REFERENCE;
+    // output of the last synchronous single-frame host call, still on the device (orbx_stereo_match_last reads it)
+    const orbx_keypoint* lastDevKps = nullptr;
+    const uint8_t* lastDevDesc = nullptr;
+    int lastDevCount = 0;
 };
 
 // ---- constructor tables (src/ORBextractor.cc:501-555) -----------------------------------------------------------
@@ -553,6 +557,8 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
     ex->serial++;
     ex->lastBatch = batch;
+    ex->lastDevKps = nullptr;  // set again by the single-frame host paths once their output is complete
+    ex->lastDevDesc = nullptr;
     ex->lastScratchBase = f0;
     return ORBX_OK;
 }
@@ -579,6 +585,9 @@ int extractor_view(orbx_extractor* ex, ExtractorView* v) {
     v->invScale = ex->invScale.data();
     v->serial = ex->serial;
     v->lastBatch = ex->lastBatch;
+    v->lastKps = ex->lastDevKps;
+    v->lastDesc = ex->lastDevDesc;
+    v->lastCount = ex->lastDevCount;
     return ORBX_OK;
 }
 }  // namespace orbx
@@ -966,6 +975,9 @@ static int extract_batch_impl(orbx_extractor* ex, const uint8_t* frames, int bat
             ex->lastBatch = 1;
             ORBX_CUDA(cudaStreamSynchronize(s));
             counts[0] = hc[0];
+            ex->lastDevKps = dK;
+            ex->lastDevDesc = dD;
+            ex->lastDevCount = std::min(hc[0], cap);
             memcpy(kps, hk, (size_t)hc[0] * sizeof(orbx_keypoint));
             memcpy(desc, hd, (size_t)hc[0] * 32);
             if (*hst != 0) return overflow_error(cap);
@@ -1023,6 +1035,11 @@ static int extract_batch_impl(orbx_extractor* ex, const uint8_t* frames, int bat
         return ORBX_OK;
     }
     ORBX_CUDA(cudaStreamSynchronize(sOut));
+    if (batch == 1) {
+        ex->lastDevKps = dK;
+        ex->lastDevDesc = dD;
+        ex->lastDevCount = std::min(hc[0], cap);
+    }
     if (nChunks > 1) {
         ORBX_CUDA(cudaStreamSynchronize(sIn));
         ORBX_CUDA(cudaStreamSynchronize(ex->stream2));

@@ -26,7 +26,8 @@ constexpr int BLUR_THREADS = 32 * (BLUR_TH / BLUR_BAND);
 // bytes (18,34,48,56) and (48,34,18,0)), keeps the last rows as vertically packed 16-bit pairs in registers and forms the
 // vertical sum with three dp2a + one multiply-add.  The horizontal sums (<= 255 * 256) fit 16 bits, the vertical sum
 // + 32768 fits 32 bits, and the result byte is bits 16..23 of the accumulator (picked with PRMT, no shift).
-__global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ FrameGeom g,
+template <int BAND>  // output rows per warp: BLUR_BAND (= the tile height: one warp per CTA) in batches, 8 (four warps per CTA) for single frames
+__global__ void __launch_bounds__(32 * (BLUR_TH / BAND)) k_blur7(const __grid_constant__ FrameGeom g,
                                                         const __grid_constant__ TmaMaps maps) {
     __shared__ __align__(128) uint8_t tile[BLUR_BH * BLUR_BW];
     __shared__ __align__(8) uint64_t bar;
@@ -49,18 +50,18 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
         tma_load_3d(tile, &maps.m[level], XOFF + x0 - 16, EDGE + y0 - 3, f, &bar);  // window = box columns 13..146
     }
     const int cg = tid & 31, band = tid >> 5;
-    const int xo = x0 + 4 * cg, yb = y0 + band * BLUR_BAND;
+    const int xo = x0 + 4 * cg, yb = y0 + band * BAND;
     uint8_t* out = L.blur + (long long)f * L.blurStride + xo;
     const bool colOk = xo < L.bpitch;
     const uint32_t K0 = 18u | (34u << 8) | (48u << 16) | (56u << 24), K1 = 48u | (34u << 8) | (18u << 16);
     const uint32_t V0 = 18u | (34u << 8), V1 = 48u | (56u << 8), V2 = 48u | (34u << 8);
     mbar_wait(&bar, 0);
 
-    const uint32_t* rowp = reinterpret_cast<const uint32_t*>(tile + band * BLUR_BAND * BLUR_BW + 12) + cg;
+    const uint32_t* rowp = reinterpret_cast<const uint32_t*>(tile + band * BAND * BLUR_BW + 12) + cg;
     uint32_t pr[8][4];  // pr[i & 7][c] = (h(i), h(i + 1)) of column c as two 16-bit halves
     uint32_t hp[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int i = 0; i < BLUR_BAND + 6; ++i) {
+    for (int i = 0; i < BAND + 6; ++i) {
         // window bytes 4cg .. 4cg + 9 of input row i are bytes 1 .. 10 of these three words
         const uint32_t w0 = rowp[i * (BLUR_BW / 4)], w1 = rowp[i * (BLUR_BW / 4) + 1], w2 = rowp[i * (BLUR_BW / 4) + 2];
         uint32_t h[4];
@@ -94,7 +95,10 @@ __global__ void __launch_bounds__(BLUR_THREADS) k_blur7(const __grid_constant__ 
 
 int launch_blur(const FrameGeom& g, const TmaMaps& maps, int batch, cudaStream_t s) {
     dim3 grid(g.blurTilesTotal, batch);
-    ORBX_CUDA(launch_kernel(k_blur7, grid, dim3(BLUR_THREADS), 0, s, g.pdl != 0, g, maps));
+    if (g.pdl)  // single frames: four warps share a tile's box (the row walk of a warp is the critical path on an empty GPU)
+        ORBX_CUDA(launch_kernel(k_blur7<8>, grid, dim3(32 * (BLUR_TH / 8)), 0, s, true, g, maps));
+    else
+        ORBX_CUDA(launch_kernel(k_blur7<BLUR_BAND>, grid, dim3(BLUR_THREADS), 0, s, false, g, maps));
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -117,6 +117,7 @@ __device__ __forceinline__ int dp4a_us(uint32_t pixels, uint32_t coef, int acc) 
 }
 
 // grid (ceil(slotsTotal / (DESC_WARPS * DESC_PER_WARP)), batch)
+template <int perWarp>
 __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __grid_constant__ FrameGeom g,
                                                                      const int* __restrict__ lvlCnt,
                                                                      const uint32_t* __restrict__ lvlKeys,
@@ -124,6 +125,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
                                                                      uint8_t* __restrict__ desc, int cap,
                                                                      int* __restrict__ counts, float* __restrict__ lvlAngles,
                                                                      int* dStatus) {
+    // perWarp: keypoint slots a warp walks — DESC_PER_WARP in batches, 1 for single frames, where the walk is the critical path
     __shared__ float4 patF[8 * 32];
     __shared__ uint32_t coefU[32 * 8], coefV[32 * 8];
     __shared__ __align__(16) uint32_t bpatch[DESC_WARPS][BP_ROWS * BP_WORDS + 2];
@@ -139,8 +141,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, f = blockIdx.y;
     const int* cnt = lvlCnt + (long long)f * g.nlevels;
-    if (threadIdx.x >= 32 && threadIdx.x < 32 + DESC_WARPS * DESC_PER_WARP) {
-        const int slot = blockIdx.x * (DESC_WARPS * DESC_PER_WARP) + (threadIdx.x - 32);
+    if (threadIdx.x >= 32 && threadIdx.x < 32 + DESC_WARPS * perWarp) {
+        const int slot = blockIdx.x * (DESC_WARPS * perWarp) + (threadIdx.x - 32);
         int level = 0;
         while (level + 1 < g.nlevels && slot >= g.lv[level + 1].slotBase) ++level;
         sLevelOf[threadIdx.x - 32] = (unsigned char)level;
@@ -161,8 +163,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_orient_describe(const __gri
     uint32_t* bp = bpatch[warp];
     const uint8_t* bp8 = reinterpret_cast<const uint8_t*>(bp);
 
-    for (int it = 0; it < DESC_PER_WARP; ++it) {
-        const int slot = (blockIdx.x * DESC_PER_WARP + it) * DESC_WARPS + warp;
+    for (int it = 0; it < perWarp; ++it) {
+        const int slot = (blockIdx.x * perWarp + it) * DESC_WARPS + warp;
         if (slot >= g.slotsTotal) break;
         const int level = sLevelOf[it * DESC_WARPS + warp];
         const LevelGeom& L = g.lv[level];
@@ -317,10 +319,15 @@ int launch_describe(const FrameGeom& g, int batch, const int* lvlCnt, const uint
                     uint8_t* dDesc, int cap, int* dCounts, float* dLvlAngles, int* dStatus, cudaStream_t s) {
     int rc = init_describe_tables();
     if (rc) return rc;
-    const int perCta = DESC_WARPS * DESC_PER_WARP;
+    const int perWarp = g.pdl ? 1 : DESC_PER_WARP;
+    const int perCta = DESC_WARPS * perWarp;
     dim3 grid((g.slotsTotal + perCta - 1) / perCta, batch);
-    ORBX_CUDA(launch_kernel(k_orient_describe, grid, dim3(DESC_WARPS * 32), 0, s, g.pdl != 0, g, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts,
-                            dLvlAngles, dStatus));
+    if (perWarp == 1)
+        ORBX_CUDA(launch_kernel(k_orient_describe<1>, grid, dim3(DESC_WARPS * 32), 0, s, g.pdl != 0, g, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts,
+                                dLvlAngles, dStatus));
+    else
+        ORBX_CUDA(launch_kernel(k_orient_describe<DESC_PER_WARP>, grid, dim3(DESC_WARPS * 32), 0, s, g.pdl != 0, g, lvlCnt, lvlKeys, dKps, dDesc, cap,
+                                dCounts, dLvlAngles, dStatus));
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

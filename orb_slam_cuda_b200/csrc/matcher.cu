@@ -1043,4 +1043,56 @@ int orbx_stereo_match(orbx_extractor* exL, orbx_extractor* exR, const orbx_keypo
     return ORBX_OK;
 }
 
+
+int orbx_stereo_match_last(orbx_extractor* exL, orbx_extractor* exR, float bf, float mb, float* u_right, float* depth, int cap) {
+    ExtractorView L, R;
+    int rc;
+    if ((rc = extractor_view(exL, &L)) || (rc = extractor_view(exR, &R))) return rc;
+    if (L.serial == 0 || R.serial == 0 || L.device != R.device || L.g->nlevels != R.g->nlevels) {
+        set_error("orbx_stereo_match_last: both extractors must have extracted a frame on the same device with the same pyramid depth");
+        return ORBX_E_INVALID;
+    }
+    if (L.lastBatch != 1 || R.lastBatch != 1 || !L.lastKps || !R.lastKps) {
+        set_error("orbx_stereo_match_last: the last call of each extractor must have been a single-frame orbx_extract");
+        return ORBX_E_INVALID;
+    }
+    const int nL = L.lastCount, nR = R.lastCount;
+    if (nR > 65535 || cap < nL || (nL > 0 && (!u_right || !depth))) {
+        set_error("orbx_stereo_match_last: bad argument (%d left keypoints, cap %d; right keypoints %d <= 65535)", nL, cap, nR);
+        return ORBX_E_INVALID;
+    }
+    if (nL == 0) return ORBX_OK;
+    ORBX_CUDA(cudaSetDevice(L.device));
+    Workspace* w;
+    if ((rc = workspace(&w))) return rc;
+    cudaStream_t s = w->stream;
+    ORBX_CUDA(cudaStreamSynchronize(L.stream));  // the last extract calls were synchronous: these return at once
+    ORBX_CUDA(cudaStreamSynchronize(R.stream));
+    StereoLevels lv;
+    memset(&lv, 0, sizeof lv);
+    lv.nlevels = L.g->nlevels;
+    for (int l = 0; l < lv.nlevels; ++l) {
+        const LevelGeom &a = L.g->lv[l], &b = R.g->lv[l];
+        lv.left[l] = a.plane + (size_t)EDGE * a.pitch + XOFF;
+        lv.right[l] = b.plane + (size_t)EDGE * b.pitch + XOFF;
+        lv.pitchL[l] = a.pitch;
+        lv.pitchR[l] = b.pitch;
+        lv.widthR[l] = b.w;
+        lv.scale[l] = L.scale[l];
+        lv.invScale[l] = L.invScale[l];
+    }
+    const float maxD = bf / mb;
+    const size_t fb = (size_t)nL * 4;
+    if ((rc = w->out0.ensure(2 * fb)) || (rc = w->out2.ensure(fb))) return rc;  // u_right | depth in one buffer: one copy back
+    if ((rc = w->pin.ensure(2 * fb))) return rc;
+    if ((rc = launch_stereo(lv, L.lastKps, nL, L.lastDesc, R.lastKps, nR, R.lastDesc, bf, maxD, w->out0.as<float>(), w->out0.as<float>() + nL,
+                            w->out2.as<int>(), s)))
+        return rc;
+    ORBX_CUDA(cudaMemcpyAsync(w->pin.p, w->out0.p, 2 * fb, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaStreamSynchronize(s));
+    memcpy(u_right, w->pin.p, fb);
+    memcpy(depth, (const uint8_t*)w->pin.p + fb, fb);
+    return ORBX_OK;
+}
+
 }  // extern "C"

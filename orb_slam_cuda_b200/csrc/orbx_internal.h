@@ -194,6 +194,10 @@ struct ExtractorView {
     const float* invScale;
     long long serial;  // 0 = nothing extracted yet
     int lastBatch;
+    // the keypoints / descriptors of the last single-frame host call as they still sit on the device (null after any other call)
+    const orbx_keypoint* lastKps;
+    const uint8_t* lastDesc;
+    int lastCount;
 };
 int extractor_view(orbx_extractor* ex, ExtractorView* v);
 

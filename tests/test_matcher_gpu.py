@@ -143,6 +143,29 @@ def test_stereo_matches_kitti():
     assert np.array_equal(u.view(np.uint32), u_ref.view(np.uint32)) and np.array_equal(z.view(np.uint32), z_ref.view(np.uint32))
 
 
+def test_stereo_matches_on_device_resident_output():
+    """orbx_stereo_match_last: ComputeStereoMatches on what the two extractors left on the device = the host-array entry point,
+    bit for bit; refused after any call that is not a single-frame extract"""
+    for kind, nf, bf, fx, kw in (("euroc", 1200, 47.90639384423901, 435.2046959714599, {}), ("kitti", 2000, 386.1448, 718.856, dict(max_disp=60))):
+        left, right = synth.stereo_pair(kind, 7, **kw)
+        gxL, gxR = X.ORBextractor(nf, 1.2, 8, 20, 7), X.ORBextractor(nf, 1.2, 8, 20, 7)
+        for rep in range(3):  # the second and third call replay the captured graph
+            gkL, gdL = gxL(left)
+            gkR, gdR = gxR(right)
+            u_ref, z_ref = X.ComputeStereoMatches(gxL, gxR, gkL, gdL, gkR, gdR, bf, fx)
+            u, z = X.ComputeStereoMatchesLast(gxL, gxR, len(gkL), bf, fx)
+            assert (u_ref >= 0).sum() > 100
+            assert np.array_equal(u.view(np.uint32), u_ref.view(np.uint32)) and np.array_equal(z.view(np.uint32), z_ref.view(np.uint32))
+        with pytest.raises(X.OrbxError):  # output capacity below the left keypoint count
+            X.ComputeStereoMatchesLast(gxL, gxR, len(gkL) - 1, bf, fx)
+        gxL.extract_batch(np.stack([left, left]))  # a batch call: the single-frame output is gone
+        with pytest.raises(X.OrbxError):
+            X.ComputeStereoMatchesLast(gxL, gxR, len(gkL), bf, fx)
+        gxL(left)
+        u, z = X.ComputeStereoMatchesLast(gxL, gxR, len(gkL), bf, fx)
+        assert np.array_equal(u.view(np.uint32), u_ref.view(np.uint32))
+
+
 def test_allpairs_scores():
     import torch
     rng = np.random.default_rng(3)
