@@ -850,6 +850,19 @@ template <class FrameT> void ComputeStereoMatches(FrameT& F) {
                       "ComputeStereoMatches");
 }
 
+// The same for the place the reference calls it from — the stereo Frame constructor (src/Frame.cc:77-94), where mvKeys /
+// mvKeysRight and the descriptors are still exactly what the two operator() calls returned: they are read where the extractors
+// left them on the device, nothing is uploaded (orbx_stereo_match_last).  Throws if either extractor has run anything else since.
+template <class FrameT> void ComputeStereoMatchesOnDevice(FrameT& F) {
+    const int N = (int)F.mvKeys.size();
+    F.mvuRight = std::vector<float>(N, -1.0f);
+    F.mvDepth = std::vector<float>(N, -1.0f);
+    if (N == 0) return;
+    ORBmatcher::check(orbx_stereo_match_last(F.mpORBextractorLeft->handle(), F.mpORBextractorRight->handle(), F.mbf, F.mb, F.mvuRight.data(),
+                                             F.mvDepth.data(), N),
+                      "ComputeStereoMatchesOnDevice");
+}
+
 }  // namespace ORB_SLAM2
 
 #endif  // ORBMATCHER_H

@@ -197,6 +197,15 @@ int main(int argc, char** argv) {
             tl.join(); tr.join();
             F.N = (int)F.mvKeys.size();
             ComputeStereoMatches(F);
+            {  // the constructor-time form (device-resident keypoints, no uploads) must give the same floats
+                const std::vector<float> u = F.mvuRight, z = F.mvDepth;
+                ComputeStereoMatchesOnDevice(F);
+                if (u.size() != F.mvuRight.size() || memcmp(u.data(), F.mvuRight.data(), u.size() * 4) != 0 ||
+                    memcmp(z.data(), F.mvDepth.data(), z.size() * 4) != 0) {
+                    fprintf(stderr, "ComputeStereoMatchesOnDevice differs from ComputeStereoMatches\n");
+                    return 3;
+                }
+            }
             put_keys(out, F.mvKeys, F.mDescriptors);
             put_keys(out, F.mvKeysRight, F.mDescriptorsRight);
             put(out, F.mvuRight.data(), F.mvuRight.size() * 4);
