@@ -108,6 +108,44 @@ def test_batch_equals_single():
         assert np.array_equal(desc[f, :n], od)
 
 
+@pytest.mark.parametrize("kind", ["kitti", "euroc"])
+def test_single_frame_kernel_shapes(kind):
+    """Batches of 1 and 2 frames run the single-frame launch sequence (programmatic dependent launch, resize tiles shared by six
+    CTAs, four warps per blur tile, one keypoint per describe warp, 512-thread quadtree CTAs); a batch of 3 runs the throughput
+    shapes.  All must give the oracle's bytes, on the host-array path, on repeated calls (graph replay) and on device buffers."""
+    import torch
+    gx, ox = make(kind)
+    frames = synth.frame_batch(kind, 3, pool=3, first=20)
+    want = [ox.extract(frames[f]) for f in range(3)]
+    for b in (1, 2, 3, 2, 1):
+        kps, desc, counts = gx.extract_batch(frames[:b])
+        for f in range(b):
+            n = counts[f]
+            assert n == len(want[f][0])
+            assert np.array_equal(kps[f, :n].view(np.uint8), want[f][0].view(np.uint8)) and np.array_equal(desc[f, :n], want[f][1])
+    for rep in range(4):  # second call captures the graph, later ones replay it
+        for f in (0, 1):
+            k, d = gx(frames[f])
+            assert np.array_equal(k.view(np.uint8), want[f][0].view(np.uint8)) and np.array_equal(d, want[f][1])
+    cap = gx.default_cap()
+    h, w = frames.shape[1:]
+    for b in (2, 1):
+        d_frames = torch.from_numpy(frames[:b]).cuda()
+        d_kps = torch.zeros((b, cap, 7), dtype=torch.int32, device="cuda")
+        d_desc = torch.zeros((b, cap, 32), dtype=torch.uint8, device="cuda")
+        d_counts = torch.zeros(b, dtype=torch.int32, device="cuda")
+        st = torch.cuda.Stream()
+        with torch.cuda.stream(st):
+            for rep in range(3):  # back to back on one stream: a call's first kernel waits for the previous call's last
+                gx.extract_batch_device(d_frames.data_ptr(), b, w, h, d_kps.data_ptr(), d_desc.data_ptr(), cap, d_counts.data_ptr(), 0, st.cuda_stream)
+        st.synchronize()
+        for f in range(b):
+            n = int(d_counts[f])
+            assert n == len(want[f][0])
+            assert np.array_equal(d_kps[f, :n].cpu().numpy().view(np.uint8).reshape(-1), want[f][0].view(np.uint8).reshape(-1))
+            assert np.array_equal(d_desc[f, :n].cpu().numpy(), want[f][1])
+
+
 @pytest.mark.parametrize("pinned", [False, True])
 def test_chunked_host_batch(pinned):
     """Host batches of >= 256 frames are pipelined in chunks of about 128 over three streams (H2D | kernels | D2H): every frame
