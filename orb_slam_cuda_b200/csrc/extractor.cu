@@ -111,6 +111,13 @@ struct orbx_extractor {
         cudaEvent_t fork = nullptr, join = nullptr, t0 = nullptr, t1 = nullptr;
     };
     std::vector<Side> sides;  // one per stream the pipeline has been launched on
+    // single frames: every pyramid level is searched (FAST + quadtree) on a stream of its own as soon as it exists, the blur
+    // runs on another one; the main stream joins them before the descriptors
+    struct Dag {
+        cudaStream_t main = nullptr, lvl[ORBX_MAX_LEVELS] = {}, blur = nullptr;
+        cudaEvent_t ready[ORBX_MAX_LEVELS] = {}, done[ORBX_MAX_LEVELS] = {}, blurDone = nullptr;
+    };
+    std::vector<Dag> dags;
     bool overlapped = false;  // the last timed call ran the blur on a side stream (stage_ms reads t0 / t1)
     int timedSide = -1;
     int lastBatch = 0;
@@ -275,6 +282,7 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
         const float W = 30;
         L.nCols = width > 0 ? (int)(width / W) : 0;
         L.nRows = height > 0 ? (int)(height / W) : 0;
+        L.stripBase = (int)strips.size();
         if (L.nCols < 1 || L.nRows < 1) {  // the reference divides by zero here; such a level yields nothing
             L.nCols = L.nRows = 0;
             L.wCell = L.hCell = 1;
@@ -292,6 +300,7 @@ static int configure(orbx_extractor* ex, int w, int h, int batch) {
                     maxStripW = std::max(maxStripW, (j1 - j0) * L.wCell);
                 }
         }
+        L.stripCount = (int)strips.size() - L.stripBase;
         L.cellBase = cellBase;
         cellBase += L.nCols * L.nRows;
         L.cellCap = cell_capacity(L.wCell, L.hCell);
@@ -463,6 +472,7 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     const bool pdlOk = batch <= 2 && !getenv("ORBX_SYNC_STAGES") && !getenv("ORBX_BLUR_OVERLAP");
     const bool pdl = pdlOk && pdlPref >= 1;
     g.pdl = pdlOk && pdlPref >= 2 ? 1 : 0;
+    g.plainLaunch = 0;
     const int nl = g.nlevels;
     int* cellCnt = ex->cellCnt.as<int>() + (size_t)f0 * g.nCellsTotal;
     uint32_t* cellKeys = ex->cellKeys.as<uint32_t>() + (size_t)f0 * (size_t)g.keysPerFrame;
@@ -476,8 +486,44 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
     const bool tm = ex->timing && f0 == 0;
     ex->timed = tm;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[0], s));
+    // Single frames, untimed: a DAG instead of a chain.  Level l is searched (FAST + quadtree, on stream lvl[l]) as soon as it
+    // exists, while the levels below it are still being resized, and the blur runs beside the searches; only the descriptor
+    // kernel needs everything.  Critical path: level 0 + FAST(0) + quadtree(0) + describe instead of the sum of all 13 kernels.
+    static const bool dagPref = []() { const char* e = getenv("ORBX_DAG"); return e ? atoi(e) != 0 : true; }();
+    const bool dag = g.pdl && dagPref && !tm && !getenv("ORBX_DEBUG_SYNC");
+    orbx_extractor::Dag* D = nullptr;
+    if (dag) {
+        for (auto& d : ex->dags)
+            if (d.main == s) D = &d;
+        if (!D) {
+            orbx_extractor::Dag d;
+            d.main = s;
+            for (int l = 0; l < nl; ++l) {
+                ORBX_CUDA(cudaStreamCreateWithFlags(&d.lvl[l], cudaStreamNonBlocking));
+                ORBX_CUDA(cudaEventCreateWithFlags(&d.ready[l], cudaEventDisableTiming));
+                ORBX_CUDA(cudaEventCreateWithFlags(&d.done[l], cudaEventDisableTiming));
+            }
+            ORBX_CUDA(cudaStreamCreateWithFlags(&d.blur, cudaStreamNonBlocking));
+            ORBX_CUDA(cudaEventCreateWithFlags(&d.blurDone, cudaEventDisableTiming));
+            ex->dags.push_back(d);
+            D = &ex->dags.back();
+        }
+    }
+    auto search_level = [&](int l) -> int {  // FAST + quadtree of level l on its own stream, after ready[l]
+        FrameGeom gl = g;
+        gl.plainLaunch = 1;  // first kernel of the forked stream: an ordinary launch behind the event
+        ORBX_CUDA(cudaEventRecord(D->ready[l], s));
+        ORBX_CUDA(cudaStreamWaitEvent(D->lvl[l], D->ready[l], 0));
+        int r = launch_fast(gl, ex->fastMaps, ex->strips.as<FastStrip>(), batch, cellCnt, cellKeys, dStatus, D->lvl[l], l);
+        if (r) return r;
+        gl.plainLaunch = g.lv[l].stripCount == 0;  // the quadtree follows its FAST kernel by programmatic dependent launch
+        if ((r = launch_quadtree(gl, batch, cellCnt, cellKeys, qtScratch, lvlCnt, lvlKeys, dStatus, D->lvl[l], l))) return r;
+        ORBX_CUDA(cudaEventRecord(D->done[l], D->lvl[l]));
+        return ORBX_OK;
+    };
     if ((rc = launch_pyramid_base(g, dFrames, batch, stride, frameStride, s))) return rc;                 // ComputePyramid
     if ((rc = stage_sync("Pyramid/Resize level 0", s))) return rc;
+    if (dag && (rc = search_level(0))) return rc;
     for (int l = 1; l < nl; ++l) {
         if (ex->areaFast[l] & 4)
             rc = launch_pyramid_level_tma(g, ex->resizeMaps, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->rzTiles[l].as<int>(),
@@ -485,6 +531,24 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
         else
             rc = launch_pyramid_level(g, l, ex->xtab[l].as<ResizeTab>(), ex->ytab[l].as<ResizeTab>(), ex->areaFast[l], batch, s);
         if (rc) return rc;
+        if (dag && (rc = search_level(l))) return rc;
+    }
+    if (dag) {
+        FrameGeom gb = g;
+        gb.plainLaunch = 1;
+        ORBX_CUDA(cudaStreamWaitEvent(D->blur, D->ready[nl - 1], 0));  // the chain is sequential: the last level is the last to exist
+        if ((rc = launch_blur(gb, ex->blurMaps, batch, D->blur))) return rc;                                // GaussianBlur
+        ORBX_CUDA(cudaEventRecord(D->blurDone, D->blur));
+        for (int l = 0; l < nl; ++l) ORBX_CUDA(cudaStreamWaitEvent(s, D->done[l], 0));
+        ORBX_CUDA(cudaStreamWaitEvent(s, D->blurDone, 0));
+        if ((rc = launch_describe(gb, batch, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts, lvlAngles, dStatus, s))) return rc;
+        ex->timed = false;
+        ex->serial++;
+        ex->lastBatch = batch;
+        ex->lastDevKps = nullptr;
+        ex->lastDevDesc = nullptr;
+        ex->lastScratchBase = f0;
+        return ORBX_OK;
     }
     if ((rc = stage_sync("Pyramid/Resize", s))) return rc;
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[1], s));
@@ -664,6 +728,15 @@ void orbx_extractor_destroy(orbx_extractor* ex) {
     for (cudaEvent_t e : ex->ev)
         if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : ex->subEv) cudaEventDestroy(e);
+    for (auto& d : ex->dags) {
+        for (int l = 0; l < ORBX_MAX_LEVELS; ++l) {
+            if (d.lvl[l]) cudaStreamDestroy(d.lvl[l]);
+            if (d.ready[l]) cudaEventDestroy(d.ready[l]);
+            if (d.done[l]) cudaEventDestroy(d.done[l]);
+        }
+        if (d.blur) cudaStreamDestroy(d.blur);
+        if (d.blurDone) cudaEventDestroy(d.blurDone);
+    }
     for (auto& sd : ex->sides) {
         cudaStreamDestroy(sd.side);
         for (cudaEvent_t e : {sd.fork, sd.join, sd.t0, sd.t1}) cudaEventDestroy(e);

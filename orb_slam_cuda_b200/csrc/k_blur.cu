@@ -96,7 +96,7 @@ __global__ void __launch_bounds__(32 * (BLUR_TH / BAND)) k_blur7(const __grid_co
 int launch_blur(const FrameGeom& g, const TmaMaps& maps, int batch, cudaStream_t s) {
     dim3 grid(g.blurTilesTotal, batch);
     if (g.pdl)  // single frames: four warps share a tile's box (the row walk of a warp is the critical path on an empty GPU)
-        ORBX_CUDA(launch_kernel(k_blur7<8>, grid, dim3(32 * (BLUR_TH / 8)), 0, s, true, g, maps));
+        ORBX_CUDA(launch_kernel(k_blur7<8>, grid, dim3(32 * (BLUR_TH / 8)), 0, s, !g.plainLaunch, g, maps));
     else
         ORBX_CUDA(launch_kernel(k_blur7<BLUR_BAND>, grid, dim3(BLUR_THREADS), 0, s, false, g, maps));
     count_launch();

@@ -323,10 +323,10 @@ int launch_describe(const FrameGeom& g, int batch, const int* lvlCnt, const uint
     const int perCta = DESC_WARPS * perWarp;
     dim3 grid((g.slotsTotal + perCta - 1) / perCta, batch);
     if (perWarp == 1)
-        ORBX_CUDA(launch_kernel(k_orient_describe<1>, grid, dim3(DESC_WARPS * 32), 0, s, g.pdl != 0, g, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts,
+        ORBX_CUDA(launch_kernel(k_orient_describe<1>, grid, dim3(DESC_WARPS * 32), 0, s, g.pdl && !g.plainLaunch, g, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts,
                                 dLvlAngles, dStatus));
     else
-        ORBX_CUDA(launch_kernel(k_orient_describe<DESC_PER_WARP>, grid, dim3(DESC_WARPS * 32), 0, s, g.pdl != 0, g, lvlCnt, lvlKeys, dKps, dDesc, cap,
+        ORBX_CUDA(launch_kernel(k_orient_describe<DESC_PER_WARP>, grid, dim3(DESC_WARPS * 32), 0, s, g.pdl && !g.plainLaunch, g, lvlCnt, lvlKeys, dKps, dDesc, cap,
                                 dCounts, dLvlAngles, dStatus));
     count_launch();
     ORBX_CUDA(cudaGetLastError());

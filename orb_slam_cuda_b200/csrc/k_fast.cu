@@ -574,17 +574,20 @@ int ensure_dynamic_smem(const void* func, size_t bytes, size_t* perDevice /* [OR
 }
 
 int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrips, int batch, int* cellCnt,
-                uint32_t* cellKeys, int* dStatus, cudaStream_t s) {
-    if (g.nStrips == 0) return ORBX_OK;
+                uint32_t* cellKeys, int* dStatus, cudaStream_t s, int onlyLevel) {
+    // onlyLevel >= 0: the strips of that pyramid level only (single frames: a level is searched as soon as it exists)
+    const int strip0 = onlyLevel >= 0 ? g.lv[onlyLevel].stripBase : 0, nStrips = onlyLevel >= 0 ? g.lv[onlyLevel].stripCount : g.nStrips;
+    if (nStrips == 0) return ORBX_OK;
     const size_t smem = fast_smem_bytes(g);
     static size_t configured[ORBX_MAX_DEVICES] = {};
     int rc = ensure_dynamic_smem((const void*)k_fast_strips, smem, configured);
     if (rc) return rc;
     // frames per CTA: ORBX_FS_FPC while the grid keeps >= 4 waves of 148 SMs x 7 CTAs
     int fpc = ORBX_FS_FPC;
-    while (fpc > 1 && (long long)g.nStrips * ((batch + fpc - 1) / fpc) < 4LL * 148 * ORBX_FS_MINBLOCKS) fpc >>= 1;
-    dim3 grid(g.nStrips, (batch + fpc - 1) / fpc);
-    ORBX_CUDA(launch_kernel(k_fast_strips, grid, dim3(FS_THREADS), smem, s, g.pdl != 0, g, maps, dStrips, cellCnt, cellKeys, dStatus, batch, fpc));
+    while (fpc > 1 && (long long)nStrips * ((batch + fpc - 1) / fpc) < 4LL * 148 * ORBX_FS_MINBLOCKS) fpc >>= 1;
+    dim3 grid(nStrips, (batch + fpc - 1) / fpc);
+    ORBX_CUDA(launch_kernel(k_fast_strips, grid, dim3(FS_THREADS), smem, s, g.pdl && !g.plainLaunch, g, maps, dStrips + strip0, cellCnt, cellKeys,
+                            dStatus, batch, fpc));
     count_launch();
     ORBX_CUDA(cudaGetLastError());
     return ORBX_OK;

@@ -546,7 +546,7 @@ __global__ void __launch_bounds__(THREADS) k_quadtree(const __grid_constant__ Fr
                                                           const int* __restrict__ cellCnt,
                                                           const uint32_t* __restrict__ cellKeys, uint32_t* qtScratch,
                                                           int* __restrict__ lvlCnt, uint32_t* __restrict__ lvlKeys,
-                                                          int* dStatus) {
+                                                          int* dStatus, int levelBase) {
     extern __shared__ __align__(16) uint8_t qsmem[];
     QtShared S;
     carve(qsmem, maxNodes, maxCells, S);
@@ -554,7 +554,7 @@ __global__ void __launch_bounds__(THREADS) k_quadtree(const __grid_constant__ Fr
         griddep_launch_dependents();
         griddep_wait();
     }
-    const int level = blockIdx.x, f = blockIdx.y, tid = threadIdx.x;
+    const int level = blockIdx.x + levelBase, f = blockIdx.y, tid = threadIdx.x;
     const LevelGeom& L = g.lv[level];
     const int nCells = L.nCols * L.nRows;
     const int* cnt = cellCnt + (long long)f * g.nCellsTotal + L.cellBase;
@@ -597,7 +597,7 @@ __global__ void __launch_bounds__(QT_THREADS) k_quadtree_single(const uint32_t* 
 int quadtree_smem_bytes(int maxQuota) { return (int)qt_smem(maxQuota + MAX_ROOTS + 8, 0); }
 
 int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uint32_t* cellKeys, uint32_t* qtScratch,
-                    int* lvlCnt, uint32_t* lvlKeys, int* dStatus, cudaStream_t s) {
+                    int* lvlCnt, uint32_t* lvlKeys, int* dStatus, cudaStream_t s, int onlyLevel) {
     int maxQuota = 0, maxCells = 0;
     for (int l = 0; l < g.nlevels; ++l) {
         maxQuota = max(maxQuota, g.lv[l].quota);
@@ -609,9 +609,10 @@ int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uin
         set_error("quadtree: %zu bytes of shared memory needed (nfeatures per level %d, cells %d)", smem, maxQuota, maxCells);
         return ORBX_E_INVALID;
     }
-    dim3 grid(g.nlevels, batch);
-    // up to one CTA per SM: nothing else would run beside it, so every (frame, level) gets 32 warps instead of 8 — the walk is
-    // a chain of short block-wide steps and single-frame latency is that chain (ORBX_QT_WIDE=0 switches it off)
+    // onlyLevel >= 0: that pyramid level only (single frames: a level is distributed as soon as its corners exist)
+    dim3 grid(onlyLevel >= 0 ? 1 : g.nlevels, batch);
+    const int levelBase = onlyLevel >= 0 ? onlyLevel : 0;
+    const bool attr = g.pdl && !g.plainLaunch;
     // Small batches (single-frame latency; at most one CTA per SM): a CTA gets 512 threads instead of 256 — the walk is a chain
     // of short block-wide steps, measured on one KITTI frame (level 0, cycles): 108 k at 256 threads, 88 k at 512, 103 k at
     // 1024; keeping the key buffers in shared memory changed nothing (the chain is instruction latency, not memory latency).
@@ -624,16 +625,16 @@ int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uin
     int rcAttr;
     if (threads == 1024) {
         if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<1024>, smem2, configured[2]))) return rcAttr;
-        ORBX_CUDA(launch_kernel(k_quadtree<1024>, grid, dim3(1024), smem2, s, g.pdl != 0, g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt,
-                                lvlKeys, dStatus));
+        ORBX_CUDA(launch_kernel(k_quadtree<1024>, grid, dim3(1024), smem2, s, attr, g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt,
+                                lvlKeys, dStatus, levelBase));
     } else if (threads == 512) {
         if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<512>, smem2, configured[1]))) return rcAttr;
-        ORBX_CUDA(launch_kernel(k_quadtree<512>, grid, dim3(512), smem2, s, g.pdl != 0, g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt,
-                                lvlKeys, dStatus));
+        ORBX_CUDA(launch_kernel(k_quadtree<512>, grid, dim3(512), smem2, s, attr, g, maxNodes, maxCells, cellCnt, cellKeys, qtScratch, lvlCnt,
+                                lvlKeys, dStatus, levelBase));
     } else {
         if ((rcAttr = ensure_dynamic_smem((const void*)k_quadtree<QT_THREADS>, smem2, configured[0]))) return rcAttr;
-        ORBX_CUDA(launch_kernel(k_quadtree<QT_THREADS>, grid, dim3(QT_THREADS), smem2, s, g.pdl != 0, g, maxNodes, maxCells, cellCnt, cellKeys,
-                                qtScratch, lvlCnt, lvlKeys, dStatus));
+        ORBX_CUDA(launch_kernel(k_quadtree<QT_THREADS>, grid, dim3(QT_THREADS), smem2, s, attr, g, maxNodes, maxCells, cellCnt, cellKeys,
+                                qtScratch, lvlCnt, lvlKeys, dStatus, levelBase));
     }
     count_launch();
     ORBX_CUDA(cudaGetLastError());

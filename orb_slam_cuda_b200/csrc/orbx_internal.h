@@ -56,6 +56,7 @@ struct LevelGeom {
     long long blurStride;   // bytes per frame in blur[l]
     // FAST grid (src/ORBextractor.cc:1133-1147)
     int minBX, minBY, maxBX, maxBY, nCols, nRows, wCell, hCell;
+    int stripBase, stripCount;  // this level's FAST strips in the strip table
     int cellBase;           // first cell of this level in the per-frame cell arrays
     int cellCap;            // key slots per cell of this level = the most corners FAST + 3x3 NMS can leave in a cell (cell_capacity)
     long long keyBase;      // first key slot (uint32) of this level inside one frame's cellKeys
@@ -86,6 +87,8 @@ struct FrameGeom {
     int iniTh, minTh;
     int patternVariant;       // ORBX_PATTERN_REFERENCE (0) / ORBX_PATTERN_CANONICAL (1): which bit_pattern_31_ the descriptors use
     int f0;                   // first scratch frame of this launch (lanes of the host-batch pipeline own disjoint ranges)
+    int plainLaunch;          // with pdl: launch WITHOUT the programmatic attribute (first kernel of a forked stream; the kernel's
+                              // griddep instructions are then no-ops) — the single-frame kernel shapes stay selected
     int pdl;                  // 1: the kernels of this launch sequence are chained by programmatic dependent launch (single-frame
                               //    latency path): each lets its successor become resident at once and waits for its predecessor
                               //    itself (griddep_wait) before it touches anything the predecessor wrote
@@ -220,14 +223,14 @@ int launch_pyramid_level_tma(const FrameGeom& g, const TmaMaps& maps, int level,
                              const int* tileX0, const int* tileY0, int batch, cudaStream_t s, bool pdl = false);
 // per-cell FAST-9 + threshold fallback + NMS
 int launch_fast(const FrameGeom& g, const TmaMaps& maps, const FastStrip* dStrips, int batch, int* cellCnt,
-                uint32_t* cellKeys, int* dStatus, cudaStream_t s);
+                uint32_t* cellKeys, int* dStatus, cudaStream_t s, int onlyLevel = -1);
 int fast_cells_per_strip(int wCell, int nCols);
 // opt-in to > 48 KB of dynamic shared memory, once per (kernel, device): perDevice is the kernel's own
 // size_t[ORBX_MAX_DEVICES] cache (the attribute is per device; the cache is guarded by a mutex)
 int ensure_dynamic_smem(const void* func, size_t bytes, size_t* perDevice);
 // DistributeOctTree per (frame, level)
 int launch_quadtree(const FrameGeom& g, int batch, const int* cellCnt, const uint32_t* cellKeys, uint32_t* qtScratch,
-                    int* lvlCnt, uint32_t* lvlKeys, int* dStatus, cudaStream_t s);
+                    int* lvlCnt, uint32_t* lvlKeys, int* dStatus, cudaStream_t s, int onlyLevel = -1);
 int quadtree_smem_bytes(int maxQuota);
 // stand-alone quadtree on a caller-supplied candidate list (debug / parity entry)
 int launch_quadtree_single(const uint32_t* dKeysIn, int n, int minX, int maxX, int minY, int maxY, int N,
