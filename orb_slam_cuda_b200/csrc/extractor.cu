@@ -99,6 +99,8 @@ struct orbx_extractor {
         }
     } graphKey;
     cudaGraphExec_t graphExec = nullptr;
+    long long graphKernels = 0;  // kernel nodes of graphExec
+    int lastKernels = 0;         // kernels the last run_pipeline call launched
     bool graphSeen = false, graphOk = true;
     bool timing = false;
     bool timed = false;      // the last call recorded events
@@ -542,6 +544,8 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
         for (int l = 0; l < nl; ++l) ORBX_CUDA(cudaStreamWaitEvent(s, D->done[l], 0));
         ORBX_CUDA(cudaStreamWaitEvent(s, D->blurDone, 0));
         if ((rc = launch_describe(gb, batch, lvlCnt, lvlKeys, dKps, dDesc, cap, dCounts, lvlAngles, dStatus, s))) return rc;
+        ex->lastKernels = 2 + (nl - 1) + nl + 2;  // level 0 (two kernels), resizes, quadtrees, blur, describe
+        for (int l = 0; l < nl; ++l) ex->lastKernels += g.lv[l].stripCount > 0;  // + a FAST launch per level that has cells
         ex->timed = false;
         ex->serial++;
         ex->lastBatch = batch;
@@ -619,6 +623,7 @@ static int run_pipeline(orbx_extractor* ex, const uint8_t* dFrames, int batch, s
         ex->nSub++;
     }
     if (tm) ORBX_CUDA(cudaEventRecord(ex->ev[5], s));
+    ex->lastKernels = nl + 5 + (ex->nSub > 1 ? 2 * (ex->nSub - 1) : 0);
     ex->serial++;
     ex->lastBatch = batch;
     ex->lastDevKps = nullptr;  // set again by the single-frame host paths once their output is complete
@@ -1001,7 +1006,7 @@ static int extract_batch_impl(orbx_extractor* ex, const uint8_t* frames, int bat
         if (ex->graphExec && key == ex->graphKey) {
             ORBX_CUDA(cudaGraphLaunch(ex->graphExec, s));
             ex->serial++;
-            for (int i = 0; i < ex->prm.nlevels + 5; ++i) count_launch();  // the kernels of the replayed graph
+            for (long long i = 0; i < ex->graphKernels; ++i) count_launch();  // the kernels of the replayed graph
             launched = true;
         } else {
             if (ex->graphExec) {
@@ -1019,6 +1024,7 @@ static int extract_batch_impl(orbx_extractor* ex, const uint8_t* frames, int bat
                 cudaError_t ce = cudaMemsetAsync(dSt, 0, sizeof(int), s);
                 if (ce == cudaSuccess) ce = cudaMemcpyAsync(dF, st, frameBytes, cudaMemcpyHostToDevice, s);
                 if (ce == cudaSuccess) rc = run_pipeline(ex, dF, 1, rowBytes, frameBytes, dK, dD, cap, dC, dSt, s, false, 0);
+                if (capture) ex->graphKernels = ex->lastKernels;  // what one replay of the graph launches
                 if (ce == cudaSuccess && !rc) ce = cudaMemcpyAsync(hk, dOut, outBytes, cudaMemcpyDeviceToHost, s);
                 if (capture) {
                     cudaGraph_t graph = nullptr;
