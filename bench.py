@@ -296,6 +296,24 @@ def latency_leg(X, wl, w, h, kind, cpu=False):
     ts = np.sort(np.array(ts))
     out = {"p50_ms": float(ts[len(ts) // 2]), "p95_ms": float(ts[int(len(ts) * 0.95)]), "calls": len(ts),
            "path": "orbx_extract through the python binding, pageable host buffers"}
+    # the same call as a C++ caller of the class surface makes it (ORBextractor::operator(), tests/cpp/frame_harness latency):
+    # what a maintainer of the reference sees per frame, without the Python binding's share
+    harness = os.path.join(ROOT, "tests", "cpp", "frame_harness")
+    if os.path.exists(harness):
+        import subprocess
+        import tempfile
+        try:
+            with tempfile.NamedTemporaryFile(suffix=".raw") as f:
+                f.write(imgs[0].tobytes() + imgs[1].tobytes())
+                f.flush()
+                env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(ROOT, "orb_slam_cuda_b200") + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+                r = subprocess.run([harness, "latency", f.name, str(w), str(h), str(wl["nfeatures"]), "300"], capture_output=True, text=True,
+                                   timeout=120, env=env)
+            j = json.loads(r.stdout.strip().splitlines()[-1])
+            out["cpp_class_surface"] = {"p50_ms": j["p50_us"] / 1e3, "p95_ms": j["p95_us"] / 1e3, "calls": j["calls"],
+                                        "path": "ORBextractor::operator() of include/ORBextractor.h from C++ (tests/cpp/frame_harness latency)"}
+        except Exception as e:  # the Python figure above stands on its own
+            out["cpp_class_surface"] = {"unavailable": repr(e)[:200]}
 
     def p50(fn, n=100, warm=5):
         for _ in range(warm):

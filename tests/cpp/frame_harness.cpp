@@ -9,8 +9,11 @@
 //   frame_harness bow    in.raw w h nfeatures voc.txt out.bin  (System.cc:64 loadFromTextFile, Frame::ComputeBoW, SearchByBoW)
 //   frame_harness track  in.raw w h nfeatures th out.bin       (last, current: Tracking::TrackWithMotionModel's SearchByProjection, :962)
 //   frame_harness fuse   in.raw w h nfeatures th out.bin       (last, current: both ORBmatcher::Fuse overloads incl. their map surgery)
+//   frame_harness latency in.raw w h nfeatures iterations      (p50 / p95 of ORBextractor::operator() as one JSON line; no output file)
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
+#include <chrono>
 #include <cstring>
 #include <map>
 #include <set>
@@ -151,7 +154,24 @@ int main(int argc, char** argv) {
     fclose(in);
     cv::Mat im0(h, w, CV_8UC1, raw.data()), im1(h, w, CV_8UC1, raw.data() + (size_t)w * h);
     try {
-        if (mode == "mono") {
+        if (mode == "latency") {  // frame_harness latency in.raw w h nfeatures iterations: p50 of ORBextractor::operator() in microseconds
+            const int iters = atoi(argv[6]);
+            ORBextractor ex(nf, 1.2f, 8, 20, 7, w, h);
+            ex.keepImagePyramid = false;  // monocular tracking reads keypoints and descriptors only
+            std::vector<cv::KeyPoint> keys;
+            cv::Mat desc;
+            std::vector<double> us;
+            for (int i = 0; i < iters + 10; ++i) {
+                const cv::Mat& im = (i & 1) ? im1 : im0;
+                const auto t0 = std::chrono::steady_clock::now();
+                ex(im, cv::Mat(), keys, desc);
+                const auto t1 = std::chrono::steady_clock::now();
+                if (i >= 10) us.push_back(std::chrono::duration<double, std::micro>(t1 - t0).count());
+            }
+            std::sort(us.begin(), us.end());
+            printf("{\"p50_us\": %.1f, \"p95_us\": %.1f, \"calls\": %d, \"keypoints\": %d}\n", us[us.size() / 2], us[us.size() * 95 / 100], iters,
+                   (int)keys.size());
+        } else if (mode == "mono") {
             FILE* out = fopen(argv[6], "wb");
             ORBextractor ex(nf, 1.2f, 8, 20, 7, w, h);  // the reference's 7-argument constructor (src/Tracking.cc:127)
             Frame F1, F2;
