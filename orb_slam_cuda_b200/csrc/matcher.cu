@@ -364,27 +364,43 @@ int orbx_search_for_initialization(const orbx_keypoint* k1, int n1, const uint8_
     int n2lvl0 = 0;
     for (int i = 0; i < n2; ++i) n2lvl0 += k2[i].octave == 0 ? 1 : 0;
     const int candCap = std::max(n2lvl0, 1);
-    if ((rc = upload(w->a, k1, (size_t)n1 * sizeof(orbx_keypoint), s)) || (rc = upload(w->b, desc1, (size_t)n1 * 32, s)) ||
-        (rc = upload(w->c, k2, (size_t)n2 * sizeof(orbx_keypoint), s)) || (rc = upload(w->d, desc2, (size_t)n2 * 32, s)) ||
-        (rc = upload(w->e, prev_xy, (size_t)n1 * 8, s)) || (rc = w->out0.ensure((size_t)n1 * 4 + 16)) ||
+    // one packed upload [k1 | k2 | desc1 | desc2] through pinned memory, and one copy back of [matches12 | overflow flag | nmatches |
+    // prev_xy] (device layout: out0 = matches12 | status | prev_xy) — pageable cudaMemcpyAsync calls cost ~10 us each
+    const size_t kb = sizeof(orbx_keypoint);
+    const size_t oK1 = 0, oK2 = oK1 + (size_t)n1 * kb, oD1 = (oK2 + (size_t)n2 * kb + 15) / 16 * 16, oD2 = oD1 + (size_t)n1 * 32,
+                 total = oD2 + (size_t)n2 * 32;
+    const size_t rSt = ((size_t)n1 * 4 + 15) / 16 * 16, rXY = rSt + 16, rBytes = rXY + (size_t)n1 * 8;  // offsets inside out0 / the copy back
+    const size_t oR = (total + 15) / 16 * 16;
+    if ((rc = w->pin.ensure(oR + rBytes)) || (rc = w->a.ensure(std::max<size_t>(total, 16))) || (rc = w->out0.ensure(rBytes + 16)) ||
         (rc = w->f.ensure(((size_t)2 * std::max(n2, 1) + 64 * 48 + 1) * 4)) || (rc = w->g.ensure((size_t)n1 * candCap * 4)) ||
-        (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
+        (rc = w->h.ensure(resolve_aux_bytes(n1))))
         return rc;
-    ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
+    uint8_t* hp = w->pin.as<uint8_t>();
+    memcpy(hp + oK1, k1, (size_t)n1 * kb);
+    if (n2) memcpy(hp + oK2, k2, (size_t)n2 * kb);
+    memcpy(hp + oD1, desc1, (size_t)n1 * 32);
+    if (n2) memcpy(hp + oD2, desc2, (size_t)n2 * 32);
+    memset(hp + oR + rSt, 0, 16);
+    memcpy(hp + oR + rXY, prev_xy, (size_t)n1 * 8);
+    ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
+    uint8_t* dOut = w->out0.as<uint8_t>();
+    ORBX_CUDA(cudaMemcpyAsync(dOut + rSt, hp + oR + rSt, 16 + (size_t)n1 * 8, cudaMemcpyHostToDevice, s));  // cleared status + vbPrevMatched
+    const uint8_t* dp = w->a.as<uint8_t>();
     int* cellOf = w->f.as<int>();
     int* sorted = cellOf + std::max(n2, 1);
     int* cellStart = sorted + std::max(n2, 1);
-    int* dN = w->status.as<int>() + 1;
-    if ((rc = launch_search_for_initialization(w->a.as<orbx_keypoint>(), n1, w->b.as<uint8_t>(), w->c.as<orbx_keypoint>(), n2,
-                                               w->d.as<uint8_t>(), bounds, w->e.as<float>(), w->out0.as<int>(), window, nnratio,
-                                               check_ori, cellOf, sorted, cellStart, w->g.as<uint32_t>(), candCap, w->h.as<int>(),
-                                               dN, w->status.as<int>(), s)))
+    int* dSt = reinterpret_cast<int*>(dOut + rSt);
+    if ((rc = launch_search_for_initialization(reinterpret_cast<const orbx_keypoint*>(dp + oK1), n1, dp + oD1,
+                                               reinterpret_cast<const orbx_keypoint*>(dp + oK2), n2, dp + oD2, bounds,
+                                               reinterpret_cast<float*>(dOut + rXY), reinterpret_cast<int*>(dOut), window, nnratio, check_ori,
+                                               cellOf, sorted, cellStart, w->g.as<uint32_t>(), candCap, w->h.as<int>(), dSt + 1, dSt, s)))
         return rc;
-    int st[2] = {0, 0};
-    ORBX_CUDA(cudaMemcpyAsync(matches12, w->out0.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(prev_xy, w->e.p, (size_t)n1 * 8, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(st, w->status.p, 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(hp + oR, dOut, rBytes, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
+    memcpy(matches12, hp + oR, (size_t)n1 * 4);
+    memcpy(prev_xy, hp + oR + rXY, (size_t)n1 * 8);
+    int st[2];
+    memcpy(st, hp + oR + rSt, 8);
     if (st[0] != 0) {
         set_error("orbx_search_for_initialization: candidate list overflow");
         return ORBX_E_OVERFLOW;
@@ -435,7 +451,9 @@ static int sbp_impl(const orbx_frame* fr, int n1, const float* x3dc, const uint8
     // one packed upload: [x3dc | angle1 | octave1 | scale factors | u_right2 | mp_desc1 | valid1 | obs1 | occupied2]
     const size_t oX = 0, oA = oX + (size_t)n1 * 12, oO = oA + (size_t)n1 * 4, oS = oO + (size_t)n1 * 4, oU = oS + ORBX_MAX_LEVELS * 4,
                  oD = (oU + (size_t)n2 * 4 + 15) / 16 * 16, oV = oD + (size_t)n1 * 32, oB = oV + n1, oC = oB + n1, total = oC + n2;
-    if ((rc = w->pin.ensure(total)) || (rc = w->a.ensure(total))) return rc;
+    // the pinned buffer also takes the results back: [match21 | overflow flag | nmatches] in ONE copy behind the upload area
+    const size_t oR = (total + 15) / 16 * 16, rBytes = (size_t)n2 * 4 + 8;
+    if ((rc = w->pin.ensure(oR + rBytes)) || (rc = w->a.ensure(total))) return rc;
     uint8_t* hp = w->pin.as<uint8_t>();
     memcpy(hp + oX, x3dc, (size_t)n1 * 12);
     memcpy(hp + oA, angle1, (size_t)n1 * 4);
@@ -452,12 +470,13 @@ static int sbp_impl(const orbx_frame* fr, int n1, const float* x3dc, const uint8
         (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
         (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
-    ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
+    int* dSt = w->out0.as<int>() + n2;  // status words right behind match21
+    ORBX_CUDA(cudaMemsetAsync(dSt, 0, 8, s));
     const uint8_t* dp = w->a.as<uint8_t>();
     int* cellOf = fr ? nullptr : w->f.as<int>();
     int* sorted = fr ? fr->sorted() : cellOf + n2;
     int* cellStart = fr ? fr->cellStart() : sorted + n2;
-    int* dN = w->status.as<int>() + 1;
+    int* dN = dSt + 1;
     const float* dUr = fr ? (fr->hasRight ? fr->uright.as<float>() : nullptr) : (u_right2 ? reinterpret_cast<const float*>(dp + oU) : nullptr);
     if ((rc = launch_search_by_projection(n1, reinterpret_cast<const float*>(dp + oX), dp + oV, dp + oB, dp + oD,
                                           reinterpret_cast<const int*>(dp + oO), reinterpret_cast<const float*>(dp + oA),
@@ -465,12 +484,13 @@ static int sbp_impl(const orbx_frame* fr, int n1, const float* x3dc, const uint8
                                           fr ? fr->desc.as<uint8_t>() : w->d.as<uint8_t>(), dUr, dp + oC,
                                           reinterpret_cast<const float*>(dp + oS), cam, mbf, bounds, th, direction, check_ori, orb_dist,
                                           flags & ORBX_SBP_NO_DEPTH_TEST ? 1 : 0, cellOf, sorted, cellStart, w->g.as<uint32_t>(), candCap, w->h.as<int>(), w->out0.as<int>(), dN,
-                                          w->status.as<int>(), s)))
+                                          dSt, s)))
         return rc;
-    int st[2] = {0, 0};
-    ORBX_CUDA(cudaMemcpyAsync(match21, w->out0.p, (size_t)n2 * 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(st, w->status.p, 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(hp + oR, w->out0.p, rBytes, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
+    memcpy(match21, hp + oR, (size_t)n2 * 4);
+    int st[2];
+    memcpy(st, hp + oR + (size_t)n2 * 4, 8);
     if (st[0] != 0) {
         set_error("orbx_search_by_projection: candidate list overflow");
         return ORBX_E_OVERFLOW;
@@ -529,7 +549,9 @@ static int sbpm_impl(const orbx_frame* fr, int n1, const float* proj, const floa
     // one packed upload: [proj | view_cos | level1 | scale factors | u_right2 | mp_desc1 | valid1 | obs1 | occupied2]
     const size_t oX = 0, oA = oX + (size_t)n1 * 12, oO = oA + (size_t)n1 * 4, oS = oO + (size_t)n1 * 4, oU = oS + ORBX_MAX_LEVELS * 4,
                  oD = (oU + (size_t)n2 * 4 + 15) / 16 * 16, oV = oD + (size_t)n1 * 32, oB = oV + n1, oC = oB + n1, total = oC + n2;
-    if ((rc = w->pin.ensure(total)) || (rc = w->a.ensure(total))) return rc;
+    // the pinned buffer also takes the results back: [match21 | overflow flag | nmatches] in ONE copy behind the upload area
+    const size_t oR = (total + 15) / 16 * 16, rBytes = (size_t)n2 * 4 + 8;
+    if ((rc = w->pin.ensure(oR + rBytes)) || (rc = w->a.ensure(total))) return rc;
     uint8_t* hp = w->pin.as<uint8_t>();
     memcpy(hp + oX, proj, (size_t)n1 * 12);
     memcpy(hp + oA, view_cos, (size_t)n1 * 4);
@@ -546,12 +568,13 @@ static int sbpm_impl(const orbx_frame* fr, int n1, const float* proj, const floa
         (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
         (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
-    ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
+    int* dSt = w->out0.as<int>() + n2;  // status words right behind match21
+    ORBX_CUDA(cudaMemsetAsync(dSt, 0, 8, s));
     const uint8_t* dp = w->a.as<uint8_t>();
     int* cellOf = fr ? nullptr : w->f.as<int>();
     int* sorted = fr ? fr->sorted() : cellOf + n2;
     int* cellStart = fr ? fr->cellStart() : sorted + n2;
-    int* dN = w->status.as<int>() + 1;
+    int* dN = dSt + 1;
     const float* dUr = fr ? (fr->hasRight ? fr->uright.as<float>() : nullptr) : (u_right2 ? reinterpret_cast<const float*>(dp + oU) : nullptr);
     if ((rc = launch_search_by_projection_map(n1, reinterpret_cast<const float*>(dp + oX), reinterpret_cast<const float*>(dp + oA),
                                               reinterpret_cast<const int*>(dp + oO), dp + oV, dp + oB, dp + oD,
@@ -559,12 +582,13 @@ static int sbpm_impl(const orbx_frame* fr, int n1, const float* proj, const floa
                                               fr ? fr->desc.as<uint8_t>() : w->d.as<uint8_t>(), dUr, dp + oC,
                                               reinterpret_cast<const float*>(dp + oS), bounds, th, nnratio, cellOf, sorted, cellStart,
                                               w->g.as<uint32_t>(), candCap, w->h.as<int>(), w->out0.as<int>(), dN,
-                                              w->status.as<int>(), s)))
+                                              dSt, s)))
         return rc;
-    int st[2] = {0, 0};
-    ORBX_CUDA(cudaMemcpyAsync(match21, w->out0.p, (size_t)n2 * 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(st, w->status.p, 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(hp + oR, w->out0.p, rBytes, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
+    memcpy(match21, hp + oR, (size_t)n2 * 4);
+    int st[2];
+    memcpy(st, hp + oR + (size_t)n2 * 4, 8);
     if (st[0] != 0) {
         set_error("orbx_search_by_projection_map: candidate list overflow");
         return ORBX_E_OVERFLOW;
@@ -609,7 +633,9 @@ int orbx_search_by_projection_sim3(int n1, const float* uvr, const int* level1, 
     // one packed upload: [uvr | level1 | mp_desc1 | valid1 | ones | occupied2]
     const size_t oX = 0, oO = oX + (size_t)n1 * 12, oD = (oO + (size_t)n1 * 4 + 15) / 16 * 16, oV = oD + (size_t)n1 * 32, oB = oV + n1,
                  oC = oB + n1, total = oC + n2;
-    if ((rc = w->pin.ensure(total)) || (rc = w->a.ensure(total))) return rc;
+    // the pinned buffer also takes the results back: [match21 | overflow flag | nmatches] in ONE copy behind the upload area
+    const size_t oR = (total + 15) / 16 * 16, rBytes = (size_t)n2 * 4 + 8;
+    if ((rc = w->pin.ensure(oR + rBytes)) || (rc = w->a.ensure(total))) return rc;
     uint8_t* hp = w->pin.as<uint8_t>();
     memcpy(hp + oX, uvr, (size_t)n1 * 12);
     memcpy(hp + oO, level1, (size_t)n1 * 4);
@@ -622,21 +648,23 @@ int orbx_search_by_projection_sim3(int n1, const float* uvr, const int* level1, 
         (rc = w->out0.ensure((size_t)n2 * 4 + 16)) || (rc = w->f.ensure(((size_t)2 * n2 + 64 * 48 + 1) * 4)) ||
         (rc = w->g.ensure((size_t)n1 * candCap * 4)) || (rc = w->h.ensure(resolve_aux_bytes(n1))) || (rc = w->status.ensure(16)))
         return rc;
-    ORBX_CUDA(cudaMemsetAsync(w->status.p, 0, 8, s));
+    int* dSt = w->out0.as<int>() + n2;  // status words right behind match21
+    ORBX_CUDA(cudaMemsetAsync(dSt, 0, 8, s));
     const uint8_t* dp = w->a.as<uint8_t>();
     int* cellOf = w->f.as<int>();
     int* sorted = cellOf + n2;
     int* cellStart = sorted + n2;
-    int* dN = w->status.as<int>() + 1;
+    int* dN = dSt + 1;
     if ((rc = launch_search_by_projection_sim3(n1, reinterpret_cast<const float*>(dp + oX), reinterpret_cast<const int*>(dp + oO),
                                                dp + oV, dp + oB, dp + oD, w->c.as<orbx_keypoint>(), n2, w->d.as<uint8_t>(), dp + oC,
                                                bounds, th_dist, cellOf, sorted, cellStart, w->g.as<uint32_t>(), candCap,
-                                               w->h.as<int>(), w->out0.as<int>(), dN, w->status.as<int>(), s)))
+                                               w->h.as<int>(), w->out0.as<int>(), dN, dSt, s)))
         return rc;
-    int st[2] = {0, 0};
-    ORBX_CUDA(cudaMemcpyAsync(match21, w->out0.p, (size_t)n2 * 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(st, w->status.p, 8, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(hp + oR, w->out0.p, rBytes, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
+    memcpy(match21, hp + oR, (size_t)n2 * 4);
+    int st[2];
+    memcpy(st, hp + oR + (size_t)n2 * 4, 8);
     if (st[0] != 0) {
         set_error("orbx_search_by_projection_sim3: candidate list overflow");
         return ORBX_E_OVERFLOW;
