@@ -714,7 +714,9 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
                  oI2 = oS2 + (size_t)(n_nodes + 1) * 4, oA1 = oI2 + (size_t)nIdx2 * 4, oA2 = oA1 + (size_t)n1 * 4,
                  oD1 = (oA2 + (size_t)n2 * 4 + 15) / 16 * 16, oD2 = oD1 + (size_t)n1 * 32, oV1 = oD2 + (size_t)n2 * 32, oV2 = oV1 + n1,
                  total = oV2 + n2;
-    if ((rc = w->pin.ensure(total))) return rc;
+    // ... and one copy back of [match12 | match21 | nmatches] behind it
+    const size_t oR = (total + 15) / 16 * 16, rBytes = ((size_t)n1 + n2) * 4 + 4;
+    if ((rc = w->pin.ensure(oR + rBytes))) return rc;
     uint8_t* hp = w->pin.as<uint8_t>();
     int* hNode = reinterpret_cast<int*>(hp + oNode);
     int* hOff = reinterpret_cast<int*>(hp + oOff);
@@ -741,7 +743,7 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
     memcpy(hp + oV1, valid1, n1);
     memcpy(hp + oV2, valid2, n2);
     if ((rc = w->a.ensure(total)) || (rc = w->g.ensure((nCand + 1) * 4)) || (rc = w->h.ensure(resolve_aux_bytes(nItems))) ||
-        (rc = w->out0.ensure((size_t)n1 * 4 + 16)) || (rc = w->out1.ensure((size_t)n2 * 4 + 16)) || (rc = w->status.ensure(16)))
+        (rc = w->out0.ensure(rBytes + 16)))
         return rc;
     ORBX_CUDA(cudaMemcpyAsync(w->a.p, hp, total, cudaMemcpyHostToDevice, s));
     const uint8_t* dp = w->a.as<uint8_t>();
@@ -749,15 +751,14 @@ int orbx_search_by_bow(int n_nodes, const int* start1, const uint32_t* idx1, con
                                    reinterpret_cast<const int*>(dp + oS2), reinterpret_cast<const uint32_t*>(dp + oI2), n1, dp + oV1,
                                    dp + oD1, reinterpret_cast<const float*>(dp + oA1), n2, dp + oV2, dp + oD2,
                                    reinterpret_cast<const float*>(dp + oA2), reinterpret_cast<const int*>(dp + oOff), w->g.as<uint32_t>(),
-                                   w->h.as<int>(), th_dist, nnratio, check_ori, w->out0.as<int>(), w->out1.as<int>(),
-                                   w->status.as<int>(), s)))
+                                   w->h.as<int>(), th_dist, nnratio, check_ori, w->out0.as<int>(), w->out0.as<int>() + n1,
+                                   w->out0.as<int>() + n1 + n2, s)))
         return rc;
-    int st = 0;
-    ORBX_CUDA(cudaMemcpyAsync(match12, w->out0.p, (size_t)n1 * 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(match21, w->out1.p, (size_t)n2 * 4, cudaMemcpyDeviceToHost, s));
-    ORBX_CUDA(cudaMemcpyAsync(&st, w->status.p, 4, cudaMemcpyDeviceToHost, s));
+    ORBX_CUDA(cudaMemcpyAsync(hp + oR, w->out0.p, rBytes, cudaMemcpyDeviceToHost, s));
     ORBX_CUDA(cudaStreamSynchronize(s));
-    *nmatches = st;
+    memcpy(match12, hp + oR, (size_t)n1 * 4);
+    memcpy(match21, hp + oR + (size_t)n1 * 4, (size_t)n2 * 4);
+    memcpy(nmatches, hp + oR + ((size_t)n1 + n2) * 4, 4);
     return ORBX_OK;
 }
 
