@@ -299,7 +299,7 @@ def latency_leg(X, wl, w, h, kind, cpu=False):
     # the same call as a C++ caller of the class surface makes it (ORBextractor::operator(), tests/cpp/frame_harness latency):
     # what a maintainer of the reference sees per frame, without the Python binding's share
     harness = os.path.join(ROOT, "tests", "cpp", "frame_harness")
-    if os.path.exists(harness):
+    if os.path.exists(harness) and not os.environ.get("CUDA_INJECTION64_PATH"):  # not under ncu / another injected profiler
         import subprocess
         import tempfile
         try:
